@@ -1,0 +1,135 @@
+/*
+ * npge_anchor.h -- C ABI of the B200-native anchor finder.
+ *
+ * This is the drop-in boundary for ONE hot path of NPG-explorer: the
+ * AnchorFinder Processor.  Everything below is plain C99 (no STL, Boost or
+ * torch types); the library behind it (npge_b200/libnpge_anchor.so) is
+ * hand-written sm_100a CUDA and has NO CPU fallback: without a CUDA device
+ * every compute entry point returns NPGE_ANCHOR_ERR_CUDA.
+ *
+ * What each entry point replaces in the reference (paths relative to the
+ * reference tree):
+ *   npge_anchor_find          AnchorFinder::run_impl, src/algo/AnchorFinder.cpp:393-406
+ *                             (BloomTG/BloomTask :99-218, FragmentTG/FragmentTask
+ *                             :222-326, fragmenttg_postprocess :356-391) with the
+ *                             scanner src/algo/SeqI.hpp:45-119 and the hash
+ *                             src/util/make_hash.hpp:25-108
+ *   npge_anchor_params        AnchorFinderOptions, AnchorFinder.cpp:59-77
+ *                             (options declared at :37-53)
+ *   npge_anchor_result        the Blocks/Fragments run_impl inserts into the
+ *                             target BlockSet (FoundFragment::make_fragment
+ *                             :240-246, loop :366-387) and the hashes it appends
+ *                             to Impl::used_hashes_ (:28-35, :385)
+ *   npge_anchor_upload        Sequence storage feeding the scan: the 2-bit layout
+ *                             of CompactLowNSequence, src/model/Sequence.cpp:525-596
+ *   npge_anchor_last_error    npge::Exception / ASSERT_* text, src/util/Exception.hpp
+ *
+ * Semantics: codes A0 T1 G2 C3, first base in the low bits,
+ * canonical h = min(dir, rev), ori = +1 iff h == dir, windows containing N
+ * skipped, window starts 0..size-k per sequence (no circular wrap), sequences
+ * shorter than k ignored.  The first pass is EXACT (no Bloom false positives,
+ * one logical worker), i.e. the result equals the reference's with an ideal
+ * filter; see DESIGN.md for what that means for parity.
+ */
+#ifndef NPGE_ANCHOR_H_
+#define NPGE_ANCHOR_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NPGE_ANCHOR_MAX_SIZE 32 /* MAX_ANCHOR_SIZE, src/util/make_hash.hpp:19 */
+
+enum {
+    NPGE_ANCHOR_OK = 0,
+    NPGE_ANCHOR_ERR_PARAMS = 1,   /* option rules violated (AnchorFinder.cpp:49-51) */
+    NPGE_ANCHOR_ERR_CUDA = 2,     /* no device / CUDA runtime error */
+    NPGE_ANCHOR_ERR_MEMORY = 3,   /* host or device allocation failed */
+    NPGE_ANCHOR_ERR_CAPACITY = 4, /* input exceeds a documented limit */
+    NPGE_ANCHOR_ERR_INPUT = 5,    /* a byte outside ATGCN (input not to_atgcn-clean) */
+    NPGE_ANCHOR_ERR_STATE = 6     /* call order (e.g. find_device before upload) */
+};
+
+typedef struct npge_anchor_ctx npge_anchor_ctx; /* opaque: device, stream, scratch */
+
+typedef struct {
+    int32_t anchor_size;          /* option anchor-size, 1..32 */
+    int32_t anchor_similar;       /* option anchor-similar, 0/1 */
+    int64_t max_anchor_fragments; /* option max-anchor-fragments, >= 0 */
+} npge_anchor_params;
+
+/* Host result. All arrays are owned by the library until
+ * npge_anchor_result_free.  Blocks are in ascending canonical-hash order;
+ * fragments inside a block in scan order: sequences by size descending (ties by
+ * caller index, SeqBase::make_seqs), then min_pos. */
+typedef struct {
+    uint64_t n_blocks, n_fragments;
+    const uint64_t* block_offsets; /* [n_blocks+1] into the fragment arrays */
+    const uint64_t* block_hash;    /* [n_blocks] canonical k-mer of each block */
+    const uint32_t* frag_seq;      /* [n_fragments] index into caller's sequences */
+    const uint32_t* frag_min_pos;  /* [n_fragments]; max_pos = min_pos + k - 1 */
+    const int8_t* frag_ori;        /* [n_fragments] +1 / -1 */
+    uint64_t n_new_used;
+    const uint64_t* new_used;      /* hashes to append to used_hashes_ (F7) */
+    uint64_t digest[2];            /* order-independent digest, see below */
+    void* owner_;                  /* private */
+} npge_anchor_result;
+
+/* Counters and device timings of the last find; always available, also when
+ * the result itself stays on the device. */
+typedef struct {
+    uint64_t n_positions;   /* bases uploaded (sequences with size >= k) */
+    uint64_t n_windows;     /* N-free windows = records sorted */
+    uint64_t n_fragments;   /* after selection and truncation */
+    uint64_t n_blocks;
+    uint64_t digest[2];
+    uint32_t radix_passes;
+    uint32_t gpu_launches;  /* kernels launched by the last find_device */
+    float ms_hist, ms_sort, ms_group, ms_total; /* CUDA-event times */
+    float ms_pass[8];       /* per radix pass (pass 0 generates the keys) */
+    uint64_t bytes_algorithmic; /* N * A(k, f, b) */
+} npge_anchor_stats;
+
+/* digest: for every emitted fragment, t = (seq << 33) | (min_pos << 1) |
+ * (ori == +1), h = its block's hash, with splitmix64 as mix():
+ *   digest[0] = sum mix(h ^ mix(t)),  digest[1] = sum mix(t + mix(h))  (mod 2^64) */
+
+int npge_anchor_create(npge_anchor_ctx** ctx, int device);
+void npge_anchor_destroy(npge_anchor_ctx* ctx);
+
+/* Thread-local text of the last error returned to this thread. */
+const char* npge_anchor_last_error(void);
+
+/* The whole path with HOST buffers: bases = all sequences concatenated as
+ * upper-case ATGCN bytes, seq_offsets[n_seqs+1].  used_sorted = the
+ * Processor's used_hashes_ state (sorted ascending), may be NULL. */
+int npge_anchor_find(npge_anchor_ctx* ctx, const npge_anchor_params* p,
+                     const uint8_t* bases, const uint64_t* seq_offsets,
+                     uint32_t n_seqs, const uint64_t* used_sorted,
+                     uint64_t n_used, npge_anchor_result* out);
+void npge_anchor_result_free(npge_anchor_result* out);
+
+/* The same path in three steps, so that the scan can be timed with inputs
+ * resident in HBM and results left there:
+ *   upload       host ATGCN -> device, packed to 2 bits/base + N mask
+ *   find_device  hist -> radix sort -> grouping, everything on the device
+ *   fetch        device result -> host arrays (+ truncation fix-up, new_used) */
+int npge_anchor_upload(npge_anchor_ctx* ctx, int32_t anchor_size,
+                       const uint8_t* bases, const uint64_t* seq_offsets,
+                       uint32_t n_seqs);
+int npge_anchor_find_device(npge_anchor_ctx* ctx, const npge_anchor_params* p,
+                            const uint64_t* used_sorted, uint64_t n_used,
+                            npge_anchor_stats* stats);
+int npge_anchor_fetch(npge_anchor_ctx* ctx, npge_anchor_result* out);
+int npge_anchor_get_stats(npge_anchor_ctx* ctx, npge_anchor_stats* stats);
+
+/* Library self-description: "npge_anchor <version> sm_100a" */
+const char* npge_anchor_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,86 @@
+"""ctypes binding of include/npge_anchor.h.  The library is required: if it is
+missing or has no CUDA device the calls fail loudly (no CPU fallback)."""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libnpge_anchor.so")
+
+EXPORTS = [
+    "npge_anchor_create", "npge_anchor_destroy", "npge_anchor_last_error",
+    "npge_anchor_find", "npge_anchor_result_free", "npge_anchor_upload",
+    "npge_anchor_find_device", "npge_anchor_fetch", "npge_anchor_get_stats",
+    "npge_anchor_version",
+]
+
+OK, ERR_PARAMS, ERR_CUDA, ERR_MEMORY, ERR_CAPACITY, ERR_INPUT, ERR_STATE = range(7)
+
+
+class Params(C.Structure):
+    _fields_ = [("anchor_size", C.c_int32), ("anchor_similar", C.c_int32),
+                ("max_anchor_fragments", C.c_int64)]
+
+
+class Result(C.Structure):
+    _fields_ = [
+        ("n_blocks", C.c_uint64), ("n_fragments", C.c_uint64),
+        ("block_offsets", C.POINTER(C.c_uint64)),
+        ("block_hash", C.POINTER(C.c_uint64)),
+        ("frag_seq", C.POINTER(C.c_uint32)),
+        ("frag_min_pos", C.POINTER(C.c_uint32)),
+        ("frag_ori", C.POINTER(C.c_int8)),
+        ("n_new_used", C.c_uint64), ("new_used", C.POINTER(C.c_uint64)),
+        ("digest", C.c_uint64 * 2), ("owner_", C.c_void_p),
+    ]
+
+
+class Stats(C.Structure):
+    _fields_ = [
+        ("n_positions", C.c_uint64), ("n_windows", C.c_uint64),
+        ("n_fragments", C.c_uint64), ("n_blocks", C.c_uint64),
+        ("digest", C.c_uint64 * 2), ("radix_passes", C.c_uint32),
+        ("gpu_launches", C.c_uint32), ("ms_hist", C.c_float),
+        ("ms_sort", C.c_float), ("ms_group", C.c_float),
+        ("ms_total", C.c_float), ("ms_pass", C.c_float * 8),
+        ("bytes_algorithmic", C.c_uint64),
+    ]
+
+
+_lib = None
+
+
+def load():
+    """Loads libnpge_anchor.so; raises if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            "npge_b200/libnpge_anchor.so is missing: run "
+            "`python -m npge_b200.build` (there is no CPU fallback)")
+    L = C.CDLL(LIB_PATH)
+    ctx = C.c_void_p
+    L.npge_anchor_create.restype = C.c_int
+    L.npge_anchor_create.argtypes = [C.POINTER(ctx), C.c_int]
+    L.npge_anchor_destroy.restype = None
+    L.npge_anchor_destroy.argtypes = [ctx]
+    L.npge_anchor_last_error.restype = C.c_char_p
+    L.npge_anchor_version.restype = C.c_char_p
+    L.npge_anchor_find.restype = C.c_int
+    L.npge_anchor_find.argtypes = [ctx, C.POINTER(Params), C.c_void_p,
+                                   C.c_void_p, C.c_uint32, C.c_void_p,
+                                   C.c_uint64, C.POINTER(Result)]
+    L.npge_anchor_result_free.restype = None
+    L.npge_anchor_result_free.argtypes = [C.POINTER(Result)]
+    L.npge_anchor_upload.restype = C.c_int
+    L.npge_anchor_upload.argtypes = [ctx, C.c_int32, C.c_void_p, C.c_void_p,
+                                     C.c_uint32]
+    L.npge_anchor_find_device.restype = C.c_int
+    L.npge_anchor_find_device.argtypes = [ctx, C.POINTER(Params), C.c_void_p,
+                                          C.c_uint64, C.POINTER(Stats)]
+    L.npge_anchor_fetch.restype = C.c_int
+    L.npge_anchor_fetch.argtypes = [ctx, C.POINTER(Result)]
+    L.npge_anchor_get_stats.restype = C.c_int
+    L.npge_anchor_get_stats.argtypes = [ctx, C.POINTER(Stats)]
+    _lib = L
+    return L

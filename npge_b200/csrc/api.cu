@@ -1,0 +1,615 @@
+// api.cu -- the C ABI (include/npge_anchor.h): host orchestration of the CUDA
+// path.  No CPU fallback: every compute entry point needs a CUDA device.
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+
+#include "kernels.h"
+
+using namespace npge_b200;
+
+namespace {
+
+thread_local std::string g_last_error;
+
+int fail(int code, const std::string& msg) {
+    g_last_error = msg;
+    return code;
+}
+
+#define NPGE_CUDA(expr)                                                        \
+    do {                                                                       \
+        cudaError_t e__ = (expr);                                              \
+        if (e__ != cudaSuccess) {                                              \
+            return fail(e__ == cudaErrorMemoryAllocation                       \
+                            ? NPGE_ANCHOR_ERR_MEMORY : NPGE_ANCHOR_ERR_CUDA,    \
+                        std::string("CUDA error: ") + cudaGetErrorString(e__) + \
+                            " at " #expr);                                     \
+        }                                                                      \
+    } while (0)
+
+int ensure(DeviceBuffer& b, size_t bytes) {
+    if (bytes == 0) bytes = 256;
+    if (b.bytes >= bytes) return NPGE_ANCHOR_OK;
+    if (b.ptr) {
+        cudaFree(b.ptr);
+        b.ptr = nullptr;
+        b.bytes = 0;
+    }
+    // grow with some headroom so repeated runs on slightly larger inputs reuse
+    size_t want = bytes + bytes / 16 + 256;
+    cudaError_t e = cudaMalloc(&b.ptr, want);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        e = cudaMalloc(&b.ptr, bytes);
+        want = bytes;
+    }
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(NPGE_ANCHOR_ERR_MEMORY,
+                    "device allocation of " + std::to_string(bytes) + " bytes failed");
+    }
+    b.bytes = want;
+    return NPGE_ANCHOR_OK;
+}
+
+void release(DeviceBuffer& b) {
+    if (b.ptr) cudaFree(b.ptr);
+    b.ptr = nullptr;
+    b.bytes = 0;
+}
+
+#define NPGE_TRY(expr)                        \
+    do {                                      \
+        int rc__ = (expr);                    \
+        if (rc__ != NPGE_ANCHOR_OK) return rc__; \
+    } while (0)
+
+template <typename T>
+T* ptr(const DeviceBuffer& b) {
+    return static_cast<T*>(b.ptr);
+}
+
+int radix_passes(int k) {
+    return (2 * k + kRadixBits - 1) / kRadixBits;
+}
+
+struct HostResult {
+    std::vector<uint64_t> block_offsets, block_hash, new_used;
+    std::vector<uint32_t> frag_seq, frag_min_pos;
+    std::vector<int8_t> frag_ori;
+};
+
+int check_params(const npge_anchor_params* p) {
+    if (!p) return fail(NPGE_ANCHOR_ERR_PARAMS, "params is NULL");
+    // add_opt_rule("anchor-size > 0"), ("anchor-size <= 32"): AnchorFinder.cpp:49-51
+    if (p->anchor_size <= 0) {
+        return fail(NPGE_ANCHOR_ERR_PARAMS, "anchor-size > 0 is violated");
+    }
+    if (p->anchor_size > NPGE_ANCHOR_MAX_SIZE) {
+        return fail(NPGE_ANCHOR_ERR_PARAMS, "anchor-size <= 32 is violated");
+    }
+    if (p->max_anchor_fragments < 0) {
+        return fail(NPGE_ANCHOR_ERR_PARAMS, "max-anchor-fragments >= 0 is violated");
+    }
+    return NPGE_ANCHOR_OK;
+}
+
+}  // namespace
+
+extern "C" const char* npge_anchor_last_error(void) {
+    return g_last_error.c_str();
+}
+
+extern "C" const char* npge_anchor_version(void) {
+    return "npge_anchor 0.1 sm_100a";
+}
+
+extern "C" int npge_anchor_create(npge_anchor_ctx** out, int device) {
+    if (!out) return fail(NPGE_ANCHOR_ERR_PARAMS, "ctx is NULL");
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0) {
+        cudaGetLastError();
+        return fail(NPGE_ANCHOR_ERR_CUDA,
+                    "no CUDA device: the anchor finder has no CPU fallback");
+    }
+    if (device < 0 || device >= count) {
+        return fail(NPGE_ANCHOR_ERR_PARAMS, "device index out of range");
+    }
+    NPGE_CUDA(cudaSetDevice(device));
+    npge_anchor_ctx* ctx = new (std::nothrow) npge_anchor_ctx;
+    if (!ctx) return fail(NPGE_ANCHOR_ERR_MEMORY, "out of host memory");
+    ctx->device = device;
+    NPGE_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+    for (auto& ev : ctx->ev) NPGE_CUDA(cudaEventCreate(&ev));
+    for (auto& ev : ctx->ev_pass) NPGE_CUDA(cudaEventCreate(&ev));
+    *out = ctx;
+    return NPGE_ANCHOR_OK;
+}
+
+extern "C" void npge_anchor_destroy(npge_anchor_ctx* ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    DeviceBuffer* all[] = {&ctx->ascii, &ctx->packed, &ctx->nmask, &ctx->seq_start,
+                           &ctx->seq_caller, &ctx->klo[0], &ctx->klo[1],
+                           &ctx->khi[0], &ctx->khi[1], &ctx->pay[0], &ctx->pay[1],
+                           &ctx->hist, &ctx->status, &ctx->counters, &ctx->used,
+                           &ctx->found_bits, &ctx->head_idx, &ctx->sel,
+                           &ctx->r_seq, &ctx->r_pos, &ctx->r_ori,
+                           &ctx->r_block_off, &ctx->r_block_hash,
+                           &ctx->scan_status, &ctx->summary};
+    for (DeviceBuffer* b : all) release(*b);
+    for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
+    for (auto& ev : ctx->ev_pass) if (ev) cudaEventDestroy(ev);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+// ---- upload: host ATGCN -> packed device genome -------------------------------
+extern "C" int npge_anchor_upload(npge_anchor_ctx* ctx, int32_t anchor_size,
+                                  const uint8_t* bases,
+                                  const uint64_t* seq_offsets, uint32_t n_seqs) {
+    if (!ctx) return fail(NPGE_ANCHOR_ERR_PARAMS, "ctx is NULL");
+    npge_anchor_params probe = {anchor_size, 0, 0};
+    NPGE_TRY(check_params(&probe));
+    if (n_seqs && (!seq_offsets || (!bases && seq_offsets[n_seqs] > 0))) {
+        return fail(NPGE_ANCHOR_ERR_PARAMS, "bases / seq_offsets is NULL");
+    }
+    NPGE_CUDA(cudaSetDevice(ctx->device));
+    ctx->uploaded = false;
+    ctx->have_result = false;
+    // SeqBase::make_seqs (SeqI.hpp:45-57): size >= k, by size descending; ties
+    // by caller index (the reference's are unspecified)
+    ctx->seqs.clear();
+    for (uint32_t s = 0; s < n_seqs; s++) {
+        if (seq_offsets[s + 1] < seq_offsets[s]) {
+            return fail(NPGE_ANCHOR_ERR_PARAMS, "seq_offsets must be non-decreasing");
+        }
+        uint64_t size = seq_offsets[s + 1] - seq_offsets[s];
+        if (size >= uint64_t(anchor_size)) ctx->seqs.push_back({s, size, 0});
+    }
+    std::stable_sort(ctx->seqs.begin(), ctx->seqs.end(),
+                     [](const SeqEntry& a, const SeqEntry& b) { return a.size > b.size; });
+    uint64_t pos = 0, n_bases = 0;
+    for (SeqEntry& e : ctx->seqs) {
+        e.start = pos;
+        pos += e.size + 1;  // one N pad after every sequence
+        n_bases += e.size;
+    }
+    if (pos > kMaxPositions) {
+        return fail(NPGE_ANCHOR_ERR_CAPACITY,
+                    "more than 2^31-1 positions per device; shard the input");
+    }
+    ctx->n_positions = pos;
+    ctx->n_bases = n_bases;
+    ctx->n_padded = (pos + kPosAlign - 1) / kPosAlign * kPosAlign;
+    ctx->n_caller_seqs = n_seqs;
+    ctx->upload_k = anchor_size;
+    const uint64_t np = ctx->n_padded;
+    const size_t slack = 256;
+    NPGE_TRY(ensure(ctx->ascii, np + slack));
+    NPGE_TRY(ensure(ctx->packed, np / 4 + slack));
+    NPGE_TRY(ensure(ctx->nmask, np / 8 + slack));
+    NPGE_TRY(ensure(ctx->seq_start, (ctx->seqs.size() + 1) * 8));
+    NPGE_TRY(ensure(ctx->seq_caller, (ctx->seqs.size() + 1) * 4));
+    NPGE_TRY(ensure(ctx->counters, kCntWords * 4));
+    cudaStream_t st = ctx->stream;
+    NPGE_CUDA(cudaMemsetAsync(ctx->counters.ptr, 0, kCntWords * 4, st));
+    if (np) {
+        NPGE_CUDA(cudaMemsetAsync(ctx->ascii.ptr, 'N', np + slack, st));
+        NPGE_CUDA(cudaMemsetAsync(ptr<uint8_t>(ctx->packed) + np / 4, 0, slack, st));
+        NPGE_CUDA(cudaMemsetAsync(ptr<uint8_t>(ctx->nmask) + np / 8, 0xff, slack, st));
+        for (const SeqEntry& e : ctx->seqs) {
+            NPGE_CUDA(cudaMemcpyAsync(ptr<uint8_t>(ctx->ascii) + e.start,
+                                      bases + seq_offsets[e.caller_index], e.size,
+                                      cudaMemcpyHostToDevice, st));
+        }
+        std::vector<uint64_t> starts(ctx->seqs.size() + 1);
+        std::vector<uint32_t> callers(ctx->seqs.size() + 1, 0);
+        for (size_t i = 0; i < ctx->seqs.size(); i++) {
+            starts[i] = ctx->seqs[i].start;
+            callers[i] = ctx->seqs[i].caller_index;
+        }
+        starts[ctx->seqs.size()] = pos;
+        NPGE_CUDA(cudaMemcpyAsync(ctx->seq_start.ptr, starts.data(),
+                                  starts.size() * 8, cudaMemcpyHostToDevice, st));
+        NPGE_CUDA(cudaMemcpyAsync(ctx->seq_caller.ptr, callers.data(),
+                                  callers.size() * 4, cudaMemcpyHostToDevice, st));
+        launch_pack(ptr<uint8_t>(ctx->ascii), ptr<uint32_t>(ctx->packed),
+                    ptr<uint32_t>(ctx->nmask), np, ptr<uint32_t>(ctx->counters), st);
+        NPGE_CUDA(cudaGetLastError());
+        uint32_t bad = 0;
+        NPGE_CUDA(cudaMemcpyAsync(&bad, ptr<uint32_t>(ctx->counters) + kCntBadInput,
+                                  4, cudaMemcpyDeviceToHost, st));
+        NPGE_CUDA(cudaStreamSynchronize(st));
+        if (bad) {
+            return fail(NPGE_ANCHOR_ERR_INPUT,
+                        std::to_string(bad) + " bytes outside ATGCN: run "
+                        "Sequence::to_atgcn on the input first");
+        }
+    }
+    ctx->uploaded = true;
+    return NPGE_ANCHOR_OK;
+}
+
+// ---- find_device: hist -> radix sort -> grouping, all on the device ---------------
+extern "C" int npge_anchor_find_device(npge_anchor_ctx* ctx,
+                                       const npge_anchor_params* p,
+                                       const uint64_t* used_sorted,
+                                       uint64_t n_used,
+                                       npge_anchor_stats* stats) {
+    if (!ctx) return fail(NPGE_ANCHOR_ERR_PARAMS, "ctx is NULL");
+    NPGE_TRY(check_params(p));
+    if (!ctx->uploaded) {
+        return fail(NPGE_ANCHOR_ERR_STATE, "npge_anchor_upload has not been called");
+    }
+    if (p->anchor_size != ctx->upload_k) {
+        return fail(NPGE_ANCHOR_ERR_STATE,
+                    "anchor-size differs from the one given to npge_anchor_upload");
+    }
+    if (n_used && !used_sorted) {
+        return fail(NPGE_ANCHOR_ERR_PARAMS, "used_sorted is NULL");
+    }
+    NPGE_CUDA(cudaSetDevice(ctx->device));
+    ctx->have_result = false;
+    const int k = p->anchor_size;
+    const int passes = radix_passes(k);
+    const bool has_hi = k > 16;
+    const bool similar = p->anchor_similar != 0;
+    const uint64_t np = ctx->n_padded;
+    const uint64_t max_records = ctx->n_positions;  // upper bound on windows
+    if (max_records > kMaxRecords) {
+        return fail(NPGE_ANCHOR_ERR_CAPACITY,
+                    "more than 2^30-1 windows per device; shard the input");
+    }
+    const uint64_t limit = uint64_t(p->max_anchor_fragments);
+    const uint64_t max_frags = std::min<uint64_t>(max_records, limit);
+    const size_t tiles0 = size_t(np / kTile);
+    const size_t summary_words = group_summary_words();
+    const size_t scan_tiles = group_scan_tiles(max_records);
+    for (int b = 0; b < 2; b++) {
+        NPGE_TRY(ensure(ctx->klo[b], max_records * 4));
+        if (has_hi) NPGE_TRY(ensure(ctx->khi[b], max_records * 4));
+        NPGE_TRY(ensure(ctx->pay[b], max_records * 4));
+    }
+    NPGE_TRY(ensure(ctx->hist, kMaxPasses * kRadix * 4));
+    NPGE_TRY(ensure(ctx->status, size_t(passes) * tiles0 * kRadix * 4));
+    NPGE_TRY(ensure(ctx->counters, kCntWords * 4));
+    NPGE_TRY(ensure(ctx->summary, summary_words * 8));
+    NPGE_TRY(ensure(ctx->scan_status, scan_tiles * 8));
+    NPGE_TRY(ensure(ctx->used, n_used * 8));
+    NPGE_TRY(ensure(ctx->r_seq, max_frags * 4));
+    NPGE_TRY(ensure(ctx->r_pos, max_frags * 4));
+    NPGE_TRY(ensure(ctx->r_ori, max_frags));
+    NPGE_TRY(ensure(ctx->r_block_off, (max_frags / 2 + 2) * 8));
+    NPGE_TRY(ensure(ctx->r_block_hash, (max_frags / 2 + 2) * 8));
+    if (similar) {
+        NPGE_TRY(ensure(ctx->found_bits, np / 8 + 256));
+        NPGE_TRY(ensure(ctx->sel, max_records));
+    }
+    cudaStream_t st = ctx->stream;
+    uint32_t launches = 0;
+    if (n_used) {
+        NPGE_CUDA(cudaMemcpyAsync(ctx->used.ptr, used_sorted, n_used * 8,
+                                  cudaMemcpyHostToDevice, st));
+    }
+    NPGE_CUDA(cudaEventRecord(ctx->ev[0], st));
+    NPGE_CUDA(cudaMemsetAsync(ctx->hist.ptr, 0, kMaxPasses * kRadix * 4, st));
+    NPGE_CUDA(cudaMemsetAsync(ctx->status.ptr, 0,
+                              size_t(passes) * tiles0 * kRadix * 4, st));
+    NPGE_CUDA(cudaMemsetAsync(ctx->counters.ptr, 0, kCntWords * 4, st));
+    NPGE_CUDA(cudaMemsetAsync(ctx->summary.ptr, 0, summary_words * 8, st));
+    NPGE_CUDA(cudaMemsetAsync(ctx->scan_status.ptr, 0, scan_tiles * 8, st));
+    if (similar) {
+        NPGE_CUDA(cudaMemsetAsync(ctx->found_bits.ptr, 0, np / 8 + 256, st));
+        NPGE_CUDA(cudaMemsetAsync(ctx->sel.ptr, 0, std::max<uint64_t>(max_records, 1), st));
+    }
+    int final_buf = 0;
+    if (np) {
+        int n_sms = 148;
+        cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, ctx->device);
+        uint32_t* hist = ptr<uint32_t>(ctx->hist);
+        uint32_t* counters = ptr<uint32_t>(ctx->counters);
+        uint32_t* status = ptr<uint32_t>(ctx->status);
+        launch_hist(ptr<uint32_t>(ctx->packed), ptr<uint32_t>(ctx->nmask), np, k,
+                    passes, hist, n_sms, st);
+        launch_scan_hist(hist, passes, counters, st);
+        launches += 2;
+        NPGE_CUDA(cudaEventRecord(ctx->ev[1], st));
+        NPGE_CUDA(cudaEventRecord(ctx->ev_pass[0], st));
+        launch_sort_pass0(ptr<uint32_t>(ctx->packed), ptr<uint32_t>(ctx->nmask), np,
+                          k, hist, status, counters, ptr<uint32_t>(ctx->klo[0]),
+                          ptr<uint32_t>(ctx->khi[0]), ptr<uint32_t>(ctx->pay[0]), st);
+        launches++;
+        NPGE_CUDA(cudaEventRecord(ctx->ev_pass[1], st));
+        for (int pass = 1; pass < passes; pass++) {
+            int in = (pass - 1) & 1, out = pass & 1;
+            launch_sort_pass(pass, max_records, ptr<uint32_t>(ctx->klo[in]),
+                             ptr<uint32_t>(ctx->khi[in]), ptr<uint32_t>(ctx->pay[in]),
+                             hist, status + size_t(pass) * tiles0 * kRadix, counters,
+                             ptr<uint32_t>(ctx->klo[out]), ptr<uint32_t>(ctx->khi[out]),
+                             ptr<uint32_t>(ctx->pay[out]), has_hi, st);
+            launches++;
+            NPGE_CUDA(cudaEventRecord(ctx->ev_pass[pass + 1], st));
+        }
+        final_buf = (passes - 1) & 1;
+    } else {
+        NPGE_CUDA(cudaEventRecord(ctx->ev[1], st));
+    }
+    NPGE_CUDA(cudaEventRecord(ctx->ev[2], st));
+    GroupArgs a = {};
+    a.klo = ptr<uint32_t>(ctx->klo[final_buf]);
+    a.khi = has_hi ? ptr<uint32_t>(ctx->khi[final_buf]) : nullptr;
+    a.pay = ptr<uint32_t>(ctx->pay[final_buf]);
+    a.max_records = np ? max_records : 0;
+    a.counters = ptr<uint32_t>(ctx->counters);
+    a.used = ptr<uint64_t>(ctx->used);
+    a.n_used = n_used;
+    a.seq_start = ptr<uint64_t>(ctx->seq_start);
+    a.seq_caller = ptr<uint32_t>(ctx->seq_caller);
+    a.n_seqs = uint32_t(ctx->seqs.size());
+    a.max_fragments = limit;
+    a.found_bits = ptr<uint32_t>(ctx->found_bits);
+    a.head_idx = nullptr;
+    a.sel = ptr<uint8_t>(ctx->sel);
+    a.r_seq = ptr<uint32_t>(ctx->r_seq);
+    a.r_pos = ptr<uint32_t>(ctx->r_pos);
+    a.r_ori = ptr<int8_t>(ctx->r_ori);
+    a.r_block_off = ptr<uint64_t>(ctx->r_block_off);
+    a.r_block_hash = ptr<uint64_t>(ctx->r_block_hash);
+    a.scan_status = ptr<uint64_t>(ctx->scan_status);
+    a.tickets = ptr<uint32_t>(ctx->counters) + kCntScanTicket;
+    a.cut_index = ptr<uint32_t>(ctx->counters) + kCntCutIndex;
+    a.summary = ptr<uint64_t>(ctx->summary);
+    if (similar) launch_similar(a, np, st, &launches);
+    launch_group_emit(a, similar, st);
+    launches += a.max_records ? 2 : 1;
+    NPGE_CUDA(cudaGetLastError());
+    NPGE_CUDA(cudaEventRecord(ctx->ev[3], st));
+    uint64_t summary[kSumWords];
+    uint32_t counters_h[kCntWords];
+    NPGE_CUDA(cudaMemcpyAsync(summary, ctx->summary.ptr, sizeof(summary),
+                              cudaMemcpyDeviceToHost, st));
+    NPGE_CUDA(cudaMemcpyAsync(counters_h, ctx->counters.ptr, sizeof(counters_h),
+                              cudaMemcpyDeviceToHost, st));
+    NPGE_CUDA(cudaStreamSynchronize(st));
+    npge_anchor_stats& s = ctx->stats;
+    memset(&s, 0, sizeof(s));
+    s.n_positions = ctx->n_bases;
+    s.n_windows = counters_h[kCntValid];
+    s.n_fragments = summary[kSumEmitted];
+    s.n_blocks = summary[kSumBlocksEmitted];
+    s.digest[0] = summary[kSumDigest0];
+    s.digest[1] = summary[kSumDigest1];
+    s.radix_passes = uint32_t(passes);
+    s.gpu_launches = launches;
+    cudaEventElapsedTime(&s.ms_hist, ctx->ev[0], ctx->ev[1]);
+    cudaEventElapsedTime(&s.ms_sort, ctx->ev[1], ctx->ev[2]);
+    cudaEventElapsedTime(&s.ms_group, ctx->ev[2], ctx->ev[3]);
+    cudaEventElapsedTime(&s.ms_total, ctx->ev[0], ctx->ev[3]);
+    for (int pass = 0; np && pass < passes; pass++) {
+        cudaEventElapsedTime(&s.ms_pass[pass], ctx->ev_pass[pass], ctx->ev_pass[pass + 1]);
+    }
+    // N * (0.375 + 12 + 8 + 24 P + 12) + 9 F + 16 B
+    s.bytes_algorithmic = uint64_t(double(ctx->n_bases) * (32.375 + 24.0 * passes)) +
+                          9 * s.n_fragments + 16 * s.n_blocks;
+    ctx->total_selected = summary[kSumFragments];
+    ctx->result_buf = final_buf;
+    ctx->last_params = *p;
+    ctx->have_result = true;
+    if (stats) *stats = s;
+    return NPGE_ANCHOR_OK;
+}
+
+extern "C" int npge_anchor_get_stats(npge_anchor_ctx* ctx,
+                                     npge_anchor_stats* stats) {
+    if (!ctx || !stats) return fail(NPGE_ANCHOR_ERR_PARAMS, "NULL argument");
+    if (!ctx->have_result) return fail(NPGE_ANCHOR_ERR_STATE, "no result yet");
+    *stats = ctx->stats;
+    return NPGE_ANCHOR_OK;
+}
+
+// ---- fetch: device result -> host arrays ------------------------------------------
+namespace {
+
+int read_key(npge_anchor_ctx* ctx, uint64_t i, uint64_t* key) {
+    uint32_t lo = 0, hi = 0;
+    const int b = ctx->result_buf;
+    NPGE_CUDA(cudaMemcpyAsync(&lo, ptr<uint32_t>(ctx->klo[b]) + i, 4,
+                              cudaMemcpyDeviceToHost, ctx->stream));
+    if (ctx->last_params.anchor_size > 16) {
+        NPGE_CUDA(cudaMemcpyAsync(&hi, ptr<uint32_t>(ctx->khi[b]) + i, 4,
+                                  cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    NPGE_CUDA(cudaStreamSynchronize(ctx->stream));
+    *key = (uint64_t(hi) << 32) | lo;
+    return NPGE_ANCHOR_OK;
+}
+
+// The reference cuts the list sorted by (hash, Sequence*, pos') at
+// max-anchor-fragments (AnchorFinder.cpp:361-363), pos' = pos + size for the
+// reverse strand (:295-301).  The device order inside a group is (seq, pos), so
+// only the group the cut falls into can differ: rebuild its kept members here.
+int fix_cut_group(npge_anchor_ctx* ctx, HostResult& r, uint64_t limit) {
+    uint32_t cut = 0;
+    NPGE_CUDA(cudaMemcpyAsync(&cut, ptr<uint32_t>(ctx->counters) + kCntCutIndex, 4,
+                              cudaMemcpyDeviceToHost, ctx->stream));
+    NPGE_CUDA(cudaStreamSynchronize(ctx->stream));
+    uint64_t key = 0;
+    NPGE_TRY(read_key(ctx, cut, &key));
+    const uint64_t n = ctx->stats.n_windows;
+    // group bounds [gs, ge) in the sorted records, by binary search
+    uint64_t lo = 0, hi = cut;
+    while (lo < hi) {
+        uint64_t mid = (lo + hi) / 2, km = 0;
+        NPGE_TRY(read_key(ctx, mid, &km));
+        if (km < key) lo = mid + 1; else hi = mid;
+    }
+    const uint64_t gs = lo;
+    lo = cut + 1;
+    hi = n;
+    while (lo < hi) {
+        uint64_t mid = (lo + hi) / 2, km = 0;
+        NPGE_TRY(read_key(ctx, mid, &km));
+        if (km <= key) lo = mid + 1; else hi = mid;
+    }
+    const uint64_t ge = lo;
+    if (r.block_hash.empty() || r.block_hash.back() != key) {
+        return fail(NPGE_ANCHOR_ERR_CUDA, "internal: cut group is not the last block");
+    }
+    const uint64_t first = r.block_offsets[r.block_hash.size() - 1];
+    const uint64_t keep = limit - first;
+    if (ge - gs > keep) {
+        std::vector<uint32_t> pay(ge - gs);
+        NPGE_CUDA(cudaMemcpyAsync(pay.data(),
+                                  ptr<uint32_t>(ctx->pay[ctx->result_buf]) + gs,
+                                  (ge - gs) * 4, cudaMemcpyDeviceToHost, ctx->stream));
+        NPGE_CUDA(cudaStreamSynchronize(ctx->stream));
+        struct Member { uint32_t seq; uint64_t pos2; uint32_t pos; int8_t ori; };
+        std::vector<Member> members;
+        members.reserve(pay.size());
+        for (uint32_t pw : pay) {
+            uint64_t g = pw >> 1;
+            size_t a = 0, b = ctx->seqs.size();
+            while (b - a > 1) {
+                size_t mid = (a + b) / 2;
+                if (ctx->seqs[mid].start <= g) a = mid; else b = mid;
+            }
+            const SeqEntry& e = ctx->seqs[a];
+            uint32_t pos = uint32_t(g - e.start);
+            bool direct = pw & 1;
+            members.push_back({e.caller_index, direct ? pos : pos + e.size, pos,
+                               int8_t(direct ? 1 : -1)});
+        }
+        std::sort(members.begin(), members.end(), [](const Member& x, const Member& y) {
+            return x.seq != y.seq ? x.seq < y.seq : x.pos2 < y.pos2;
+        });
+        for (uint64_t j = 0; j < keep; j++) {
+            r.frag_seq[first + j] = members[j].seq;
+            r.frag_min_pos[first + j] = members[j].pos;
+            r.frag_ori[first + j] = members[j].ori;
+        }
+    }
+    return NPGE_ANCHOR_OK;
+}
+
+}  // namespace
+
+extern "C" int npge_anchor_fetch(npge_anchor_ctx* ctx, npge_anchor_result* out) {
+    if (!ctx || !out) return fail(NPGE_ANCHOR_ERR_PARAMS, "NULL argument");
+    memset(out, 0, sizeof(*out));
+    if (!ctx->have_result) {
+        return fail(NPGE_ANCHOR_ERR_STATE, "npge_anchor_find_device has not run");
+    }
+    NPGE_CUDA(cudaSetDevice(ctx->device));
+    HostResult* r = new (std::nothrow) HostResult;
+    if (!r) return fail(NPGE_ANCHOR_ERR_MEMORY, "out of host memory");
+    const uint64_t nf = ctx->stats.n_fragments, nb = ctx->stats.n_blocks;
+    const uint64_t limit = uint64_t(ctx->last_params.max_anchor_fragments);
+    int rc = NPGE_ANCHOR_OK;
+    try {
+        r->frag_seq.resize(nf);
+        r->frag_min_pos.resize(nf);
+        r->frag_ori.resize(nf);
+        r->block_offsets.resize(nb + 1);
+        r->block_hash.resize(nb);
+    } catch (std::bad_alloc&) {
+        delete r;
+        return fail(NPGE_ANCHOR_ERR_MEMORY, "out of host memory for the result");
+    }
+    auto body = [&]() -> int {
+        cudaStream_t st = ctx->stream;
+        if (nf) {
+            NPGE_CUDA(cudaMemcpyAsync(r->frag_seq.data(), ctx->r_seq.ptr, nf * 4,
+                                      cudaMemcpyDeviceToHost, st));
+            NPGE_CUDA(cudaMemcpyAsync(r->frag_min_pos.data(), ctx->r_pos.ptr, nf * 4,
+                                      cudaMemcpyDeviceToHost, st));
+            NPGE_CUDA(cudaMemcpyAsync(r->frag_ori.data(), ctx->r_ori.ptr, nf,
+                                      cudaMemcpyDeviceToHost, st));
+        }
+        NPGE_CUDA(cudaMemcpyAsync(r->block_offsets.data(), ctx->r_block_off.ptr,
+                                  (nb + 1) * 8, cudaMemcpyDeviceToHost, st));
+        if (nb) {
+            NPGE_CUDA(cudaMemcpyAsync(r->block_hash.data(), ctx->r_block_hash.ptr,
+                                      nb * 8, cudaMemcpyDeviceToHost, st));
+        }
+        NPGE_CUDA(cudaStreamSynchronize(st));
+        out->digest[0] = ctx->stats.digest[0];
+        out->digest[1] = ctx->stats.digest[1];
+        bool lone_tail = false;
+        uint64_t lone_hash = 0;
+        if (ctx->total_selected > limit && limit > 0) {
+            NPGE_TRY(fix_cut_group(ctx, *r, limit));
+            // a group cut down to one member is a singleton in the reference's
+            // list: no block, but its hash is still recorded as used (:385)
+            if (r->block_offsets[nb] - r->block_offsets[nb - 1] == 1) {
+                lone_tail = true;
+                lone_hash = r->block_hash[nb - 1];
+                r->block_hash.pop_back();
+                r->block_offsets.pop_back();
+                r->frag_seq.pop_back();
+                r->frag_min_pos.pop_back();
+                r->frag_ori.pop_back();
+            }
+            uint64_t d0 = 0, d1 = 0;
+            for (size_t b = 0; b < r->block_hash.size(); b++) {
+                uint64_t h = r->block_hash[b];
+                for (uint64_t f = r->block_offsets[b]; f < r->block_offsets[b + 1]; f++) {
+                    uint64_t t = (uint64_t(r->frag_seq[f]) << 33) |
+                                 (uint64_t(r->frag_min_pos[f]) << 1) |
+                                 (r->frag_ori[f] == 1 ? 1 : 0);
+                    d0 += splitmix64(h ^ splitmix64(t));
+                    d1 += splitmix64(t + splitmix64(h));
+                }
+            }
+            out->digest[0] = d0;
+            out->digest[1] = d1;
+        }
+        // used_hashes.push_back for every distinct hash of the list but the
+        // first (AnchorFinder.cpp:366-387)
+        for (size_t b = 1; b < r->block_hash.size(); b++) {
+            r->new_used.push_back(r->block_hash[b]);
+        }
+        if (lone_tail && !r->block_hash.empty()) r->new_used.push_back(lone_hash);
+        return NPGE_ANCHOR_OK;
+    };
+    rc = body();
+    if (rc != NPGE_ANCHOR_OK) {
+        delete r;
+        return rc;
+    }
+    out->n_blocks = r->block_hash.size();
+    out->n_fragments = r->frag_seq.size();
+    out->block_offsets = r->block_offsets.data();
+    out->block_hash = r->block_hash.data();
+    out->frag_seq = r->frag_seq.data();
+    out->frag_min_pos = r->frag_min_pos.data();
+    out->frag_ori = r->frag_ori.data();
+    out->n_new_used = r->new_used.size();
+    out->new_used = r->new_used.data();
+    out->owner_ = r;
+    return NPGE_ANCHOR_OK;
+}
+
+extern "C" void npge_anchor_result_free(npge_anchor_result* out) {
+    if (!out) return;
+    delete static_cast<HostResult*>(out->owner_);
+    memset(out, 0, sizeof(*out));
+}
+
+extern "C" int npge_anchor_find(npge_anchor_ctx* ctx, const npge_anchor_params* p,
+                                const uint8_t* bases, const uint64_t* seq_offsets,
+                                uint32_t n_seqs, const uint64_t* used_sorted,
+                                uint64_t n_used, npge_anchor_result* out) {
+    if (!out) return fail(NPGE_ANCHOR_ERR_PARAMS, "out is NULL");
+    memset(out, 0, sizeof(*out));
+    NPGE_TRY(check_params(p));
+    NPGE_TRY(npge_anchor_upload(ctx, p->anchor_size, bases, seq_offsets, n_seqs));
+    NPGE_TRY(npge_anchor_find_device(ctx, p, used_sorted, n_used, nullptr));
+    return npge_anchor_fetch(ctx, out);
+}

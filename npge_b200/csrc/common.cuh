@@ -1,0 +1,128 @@
+// common.cuh -- shared constants, device helpers and the context of the
+// B200 anchor finder.  sm_100a only.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/npge_anchor.h"
+
+namespace npge_b200 {
+
+// ---- device data layout ------------------------------------------------------
+// Sequences with size >= k are concatenated in SCAN ORDER (size descending,
+// ties by caller index: SeqBase::make_seqs, src/algo/SeqI.hpp:45-57) into one
+// global position space; one pad position marked N follows every sequence, so
+// a window that would cross a sequence end is invalid through the N mask alone
+// (no circular wrap).  Base at global position g:
+//   packed[g / 16] bits [2*(g%16), +2)   codes A0 T1 G2 C3 (char_to_size.hpp:24-36)
+//   nmask[g / 32]  bit  g % 32           1 = N or pad
+// which is the bit layout of CompactLowNSequence (Sequence.cpp:590-596) and of
+// make_hash (make_hash.hpp:29-42): the forward hash of the window at g is bits
+// [2g, 2g+2k) of the packed stream.
+
+constexpr int kTileThreads = 256;
+constexpr int kItemsPerThread = 16;
+constexpr int kTile = kTileThreads * kItemsPerThread;  // 4096 records / positions
+constexpr int kWarps = kTileThreads / 32;
+constexpr int kRadixBits = 8;
+constexpr int kRadix = 1 << kRadixBits;
+constexpr int kMaxPasses = 8;  // ceil(64 / 8)
+
+// positions are padded so every tile can bulk-copy tile + 16 B of halo
+constexpr uint64_t kPosAlign = 4096;
+
+// look-back status word: [31:30] flag, [29:0] value
+constexpr uint32_t kFlagAggregate = 1u << 30;
+constexpr uint32_t kFlagInclusive = 2u << 30;
+constexpr uint32_t kValueMask = (1u << 30) - 1;
+constexpr uint64_t kMaxRecords = kValueMask;         // per sort
+constexpr uint64_t kMaxPositions = (1ull << 31) - 1; // payload = gpos << 1 | ori
+
+__host__ __device__ inline uint64_t splitmix64(uint64_t x) {
+    x += 0x9E3779B97F4A7C15ull;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+    return x ^ (x >> 31);
+}
+
+#ifdef __CUDACC__
+// Canonical key of the window of k bases at global position p, read from
+// packed words `W` (16 bases per u32) whose word 0 holds position `base`.
+// dir: make_hash ori=+1; rev: ori=-1 (complement = code ^ 1, reversed), as
+// SeqI::init_state / next_hash maintain them (SeqI.hpp:86-119).
+__device__ __forceinline__ uint64_t forward_key(const uint32_t* W, uint32_t rel,
+                                                int k) {
+    uint32_t w = rel >> 4, s = (rel & 15) * 2;
+    uint32_t w0 = W[w], w1 = W[w + 1], w2 = W[w + 2];
+    uint32_t lo = __funnelshift_r(w0, w1, s);
+    uint32_t hi = __funnelshift_r(w1, w2, s);
+    uint64_t x = (uint64_t(hi) << 32) | lo;
+    return k == 32 ? x : (x & ((1ull << (2 * k)) - 1));
+}
+
+__device__ __forceinline__ uint64_t revcomp_key(uint64_t dir, int k) {
+    uint64_t x = __brevll(dir);
+    const uint64_t m = 0x5555555555555555ull;
+    x = ((x >> 1) & m) | ((x & m) << 1);  // undo the bit swap inside each base
+    x ^= m;                               // complement_letter: code ^ 1
+    return x >> (64 - 2 * k);
+}
+
+// 1 iff any of the k positions starting at rel is N / pad.
+__device__ __forceinline__ bool window_has_n(const uint32_t* M, uint32_t rel,
+                                             int k) {
+    uint32_t w = rel >> 5, s = rel & 31;
+    uint32_t m = __funnelshift_r(M[w], M[w + 1], s);
+    if (k < 32) m &= (1u << k) - 1;
+    return m != 0;
+}
+#endif
+
+// ---- host-side context ---------------------------------------------------------
+struct DeviceBuffer {
+    void* ptr = nullptr;
+    size_t bytes = 0;
+};
+
+struct SeqEntry {
+    uint32_t caller_index;
+    uint64_t size;
+    uint64_t start;  // global position of base 0
+};
+
+}  // namespace npge_b200
+
+struct npge_anchor_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t ev_pass[npge_b200::kMaxPasses + 1] = {};
+
+    // uploaded genome
+    bool uploaded = false;
+    int32_t upload_k = 0;
+    std::vector<npge_b200::SeqEntry> seqs;  // scan order
+    uint64_t n_positions = 0;               // sum(size + 1)
+    uint64_t n_padded = 0;                  // rounded up to kPosAlign
+    uint64_t n_bases = 0;                   // sum(size)
+    uint32_t n_caller_seqs = 0;
+    npge_b200::DeviceBuffer ascii, packed, nmask, seq_start, seq_caller;
+
+    // sort / grouping scratch
+    npge_b200::DeviceBuffer klo[2], khi[2], pay[2];
+    npge_b200::DeviceBuffer hist, status, counters, used;
+    npge_b200::DeviceBuffer found_bits, head_idx, sel;
+    // device result
+    npge_b200::DeviceBuffer r_seq, r_pos, r_ori, r_block_off, r_block_hash;
+    npge_b200::DeviceBuffer scan_status, summary;
+
+    bool have_result = false;
+    int result_buf = 0;       // which of the double buffers holds sorted records
+    npge_anchor_params last_params = {0, 0, 0};
+    npge_anchor_stats stats = {};
+    uint64_t total_selected = 0;  // before truncation
+};

@@ -1,0 +1,91 @@
+// kernels.h -- launchers of the hand-written sm_100a kernels (host-callable).
+#pragma once
+
+#include "common.cuh"
+
+namespace npge_b200 {
+
+// counters[] slots (u32 unless noted) in ctx->counters
+enum {
+    kCntValid = 0,      // number of N-free windows (records)
+    kCntBadInput = 1,   // bytes outside ATGCN seen by pack
+    kCntTicket0 = 2,    // tile tickets, one per radix pass (kMaxPasses slots)
+    kCntScanTicket = 10,  // tickets of the grouping scans (4 slots)
+    kCntCutIndex = 14,  // sorted index of the record with selected-rank M-1
+    kCntWords = 16
+};
+
+// summary[] slots (u64) in ctx->summary
+enum {
+    kSumFragments = 0,  // selected records (before truncation)
+    kSumBlocks = 1,
+    kSumDigest0 = 2,
+    kSumDigest1 = 3,
+    kSumEmitted = 4,    // fragments actually written (after truncation)
+    kSumBlocksEmitted = 5,
+    kSumWords = 8
+};
+
+void launch_pack(const uint8_t* ascii, uint32_t* packed, uint32_t* nmask,
+                 uint64_t n_padded, uint32_t* counters, cudaStream_t s);
+
+void launch_hist(const uint32_t* packed, const uint32_t* nmask,
+                 uint64_t n_padded, int k, int passes, uint32_t* hist,
+                 int n_sms, cudaStream_t s);
+
+// hist[passes][256] counts -> exclusive bases in place; counters[kCntValid] = n
+void launch_scan_hist(uint32_t* hist, int passes, uint32_t* counters,
+                      cudaStream_t s);
+
+// pass 0: generate keys from the packed genome and scatter by digit 0
+void launch_sort_pass0(const uint32_t* packed, const uint32_t* nmask,
+                       uint64_t n_padded, int k, const uint32_t* hist_base,
+                       uint32_t* status, uint32_t* counters, uint32_t* klo_out,
+                       uint32_t* khi_out, uint32_t* pay_out, cudaStream_t s);
+
+// pass p >= 1: scatter records by digit p (bits [8p, 8p+8) of the key)
+void launch_sort_pass(int pass, uint64_t max_records, const uint32_t* klo_in,
+                      const uint32_t* khi_in, const uint32_t* pay_in,
+                      const uint32_t* hist_base, uint32_t* status,
+                      uint32_t* counters, uint32_t* klo_out, uint32_t* khi_out,
+                      uint32_t* pay_out, bool has_hi, cudaStream_t s);
+
+struct GroupArgs {
+    const uint32_t* klo;
+    const uint32_t* khi;   // nullptr when k <= 16
+    const uint32_t* pay;
+    uint64_t max_records;  // upper bound used for the grid; real n on device
+    const uint32_t* counters;
+    const uint64_t* used;
+    uint64_t n_used;
+    const uint64_t* seq_start;    // [S+1] global start of each scan-order seq
+    const uint32_t* seq_caller;   // [S] caller index
+    uint32_t n_seqs;
+    uint64_t max_fragments;       // truncation M
+    // anchor-similar scratch
+    uint32_t* found_bits;         // 1 bit per global position
+    uint32_t* head_idx;           // per record: index of its group's first record
+    uint8_t* sel;                 // per record index: group selected (at head)
+    // outputs
+    uint32_t* r_seq;
+    uint32_t* r_pos;
+    int8_t* r_ori;
+    uint64_t* r_block_off;
+    uint64_t* r_block_hash;
+    uint64_t* scan_status;
+    uint32_t* tickets;            // counters + kCntScanTicket
+    uint32_t* cut_index;          // counters + kCntCutIndex
+    uint64_t* summary;
+};
+
+// anchor-similar: found bits, group heads, candidate -> group selection
+void launch_similar(const GroupArgs& a, uint64_t n_padded, cudaStream_t s,
+                    uint32_t* launches);
+// run-length grouping + compaction into the flat result arrays
+void launch_group_emit(const GroupArgs& a, bool similar, cudaStream_t s);
+
+// sizes of the grouping scratch (u64 words / tiles) for the host side
+size_t group_summary_words();
+size_t group_scan_tiles(uint64_t max_records);
+
+}  // namespace npge_b200

@@ -1,0 +1,153 @@
+"""Thin Python driver over the C ABI (include/npge_anchor.h): used by the tests,
+bench.py and the Processor mirror.  All compute happens in the CUDA library."""
+import ctypes as C
+
+import numpy as np
+
+from . import _abi
+
+
+class AnchorError(RuntimeError):
+    """npge::Exception equivalent: carries the C ABI status code."""
+
+    def __init__(self, code, message):
+        RuntimeError.__init__(self, message)
+        self.code = code
+
+
+def concat(seqs):
+    """list of str / bytes / uint8 arrays -> (uint8 array, uint64 offsets[S+1])"""
+    arrs = []
+    for s in seqs:
+        if isinstance(s, str):
+            s = s.encode()
+        if isinstance(s, (bytes, bytearray)):
+            s = np.frombuffer(bytes(s), dtype=np.uint8)
+        arrs.append(np.asarray(s, dtype=np.uint8))
+    offsets = np.zeros(len(arrs) + 1, dtype=np.uint64)
+    if arrs:
+        offsets[1:] = np.cumsum([len(a) for a in arrs])
+        bases = np.concatenate(arrs) if len(arrs) > 1 else arrs[0].copy()
+    else:
+        bases = np.zeros(0, dtype=np.uint8)
+    return np.ascontiguousarray(bases), offsets
+
+
+class AnchorResult:
+    """Flat anchor blocks: block b owns fragments block_offsets[b]:block_offsets[b+1]."""
+
+    def __init__(self, r):
+        nb, nf, nu = int(r.n_blocks), int(r.n_fragments), int(r.n_new_used)
+
+        def arr(p, n, dtype):
+            if n == 0:
+                return np.zeros(0, dtype)
+            return np.ctypeslib.as_array(p, (n,)).astype(dtype, copy=True)
+
+        self.block_offsets = (arr(r.block_offsets, nb + 1, np.uint64)
+                              if r.block_offsets else np.zeros(1, np.uint64))
+        self.block_hash = arr(r.block_hash, nb, np.uint64)
+        self.frag_seq = arr(r.frag_seq, nf, np.uint32)
+        self.frag_min_pos = arr(r.frag_min_pos, nf, np.uint32)
+        self.frag_ori = arr(r.frag_ori, nf, np.int8)
+        self.new_used = arr(r.new_used, nu, np.uint64)
+        self.digest = (int(r.digest[0]), int(r.digest[1]))
+
+    @property
+    def n_blocks(self):
+        return len(self.block_hash)
+
+    @property
+    def n_fragments(self):
+        return len(self.frag_seq)
+
+    def blocks(self):
+        """Canonical form: sorted list of blocks, each a sorted tuple of
+        (seq, min_pos, ori)."""
+        out = []
+        for b in range(self.n_blocks):
+            lo, hi = int(self.block_offsets[b]), int(self.block_offsets[b + 1])
+            out.append(tuple(sorted(
+                (int(self.frag_seq[f]), int(self.frag_min_pos[f]),
+                 int(self.frag_ori[f])) for f in range(lo, hi))))
+        return sorted(out)
+
+
+def _stats_dict(s):
+    d = {name: getattr(s, name) for name, _ in s._fields_
+         if name not in ("digest", "ms_pass")}
+    d["ms_pass"] = [float(x) for x in s.ms_pass][:int(s.radix_passes)]
+    d["digest"] = (int(s.digest[0]), int(s.digest[1]))
+    return d
+
+
+class AnchorEngine:
+    """One CUDA context of the anchor finder (not thread-safe, like the
+    reference's Processor instances)."""
+
+    def __init__(self, device=0):
+        self._lib = _abi.load()
+        self._ctx = C.c_void_p()
+        self._check(self._lib.npge_anchor_create(C.byref(self._ctx), device))
+
+    def close(self):
+        if self._ctx:
+            self._lib.npge_anchor_destroy(self._ctx)
+            self._ctx = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc):
+        if rc != _abi.OK:
+            raise AnchorError(rc, self._lib.npge_anchor_last_error().decode())
+
+    @staticmethod
+    def _used(used):
+        u = np.ascontiguousarray(np.sort(np.asarray(
+            used if used is not None else [], dtype=np.uint64)))
+        return u, (u.ctypes.data if len(u) else None)
+
+    def find(self, seqs, k, similar=True, max_frags=100000, used=None):
+        """npge_anchor_find with host buffers (the drop-in call)."""
+        bases, offsets = seqs if isinstance(seqs, tuple) else concat(seqs)
+        u, up = self._used(used)
+        p = _abi.Params(k, int(bool(similar)), int(max_frags))
+        r = _abi.Result()
+        self._check(self._lib.npge_anchor_find(
+            self._ctx, C.byref(p), bases.ctypes.data, offsets.ctypes.data,
+            len(offsets) - 1, up, len(u), C.byref(r)))
+        try:
+            return AnchorResult(r)
+        finally:
+            self._lib.npge_anchor_result_free(C.byref(r))
+
+    def upload(self, seqs, k):
+        bases, offsets = seqs if isinstance(seqs, tuple) else concat(seqs)
+        self._check(self._lib.npge_anchor_upload(
+            self._ctx, k, bases.ctypes.data, offsets.ctypes.data,
+            len(offsets) - 1))
+
+    def find_device(self, k, similar=True, max_frags=100000, used=None):
+        u, up = self._used(used)
+        p = _abi.Params(k, int(bool(similar)), int(max_frags))
+        s = _abi.Stats()
+        self._check(self._lib.npge_anchor_find_device(
+            self._ctx, C.byref(p), up, len(u), C.byref(s)))
+        return _stats_dict(s)
+
+    def fetch(self):
+        r = _abi.Result()
+        self._check(self._lib.npge_anchor_fetch(self._ctx, C.byref(r)))
+        try:
+            return AnchorResult(r)
+        finally:
+            self._lib.npge_anchor_result_free(C.byref(r))
+
+    def stats(self):
+        s = _abi.Stats()
+        self._check(self._lib.npge_anchor_get_stats(self._ctx, C.byref(s)))
+        return _stats_dict(s)
