@@ -89,8 +89,9 @@ typedef struct {
     uint32_t radix_passes;
     uint32_t gpu_launches;  /* kernels launched by the last find_device */
     float ms_hist, ms_sort, ms_group, ms_total; /* CUDA-event times */
-    float ms_pass[8];       /* per radix pass (pass 0 generates the keys) */
-    uint64_t bytes_algorithmic; /* N * A(k, f, b) */
+    float ms_pass[16];      /* per radix pass (pass 0 generates the keys) */
+    uint64_t bytes_algorithmic; /* SURVEY 8d model: N * A(k, f, b), byte digits */
+    uint64_t bytes_moved;       /* compulsory HBM bytes of the passes really run */
 } npge_anchor_stats;
 
 /* digest: for every emitted fragment, t = (seq << 33) | (min_pos << 1) |

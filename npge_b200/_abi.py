@@ -41,8 +41,8 @@ class Stats(C.Structure):
         ("digest", C.c_uint64 * 2), ("radix_passes", C.c_uint32),
         ("gpu_launches", C.c_uint32), ("ms_hist", C.c_float),
         ("ms_sort", C.c_float), ("ms_group", C.c_float),
-        ("ms_total", C.c_float), ("ms_pass", C.c_float * 8),
-        ("bytes_algorithmic", C.c_uint64),
+        ("ms_total", C.c_float), ("ms_pass", C.c_float * 16),
+        ("bytes_algorithmic", C.c_uint64), ("bytes_moved", C.c_uint64),
     ]
 
 

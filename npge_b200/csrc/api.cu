@@ -72,8 +72,11 @@ T* ptr(const DeviceBuffer& b) {
     return static_cast<T*>(b.ptr);
 }
 
-int radix_passes(int k) {
-    return (2 * k + kRadixBits - 1) / kRadixBits;
+int digit_bits_preference() {
+    // experiments only: NPGE_ANCHOR_DIGIT_BITS=8 restores byte digits
+    const char* e = getenv("NPGE_ANCHOR_DIGIT_BITS");
+    int b = e ? atoi(e) : kMaxDigitBits;
+    return b;
 }
 
 struct HostResult {
@@ -125,6 +128,7 @@ extern "C" int npge_anchor_create(npge_anchor_ctx** out, int device) {
     if (!ctx) return fail(NPGE_ANCHOR_ERR_MEMORY, "out of host memory");
     ctx->device = device;
     NPGE_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+    exp_set_nochain(getenv("NPGE_EXP_NOCHAIN") ? 1 : 0);
     for (auto& ev : ctx->ev) NPGE_CUDA(cudaEventCreate(&ev));
     for (auto& ev : ctx->ev_pass) NPGE_CUDA(cudaEventCreate(&ev));
     *out = ctx;
@@ -138,7 +142,7 @@ extern "C" void npge_anchor_destroy(npge_anchor_ctx* ctx) {
     DeviceBuffer* all[] = {&ctx->ascii, &ctx->packed, &ctx->nmask, &ctx->seq_start,
                            &ctx->seq_caller, &ctx->klo[0], &ctx->klo[1],
                            &ctx->khi[0], &ctx->khi[1], &ctx->pay[0], &ctx->pay[1],
-                           &ctx->hist, &ctx->status, &ctx->counters, &ctx->used,
+                           &ctx->hist, &ctx->status, &ctx->status2, &ctx->counters, &ctx->used,
                            &ctx->found_bits, &ctx->head_idx, &ctx->sel,
                            &ctx->r_seq, &ctx->r_pos, &ctx->r_ori,
                            &ctx->r_block_off, &ctx->r_block_hash,
@@ -258,7 +262,8 @@ extern "C" int npge_anchor_find_device(npge_anchor_ctx* ctx,
     NPGE_CUDA(cudaSetDevice(ctx->device));
     ctx->have_result = false;
     const int k = p->anchor_size;
-    const int passes = radix_passes(k);
+    const SortPlan plan = make_sort_plan(k, digit_bits_preference());
+    const int passes = plan.passes;
     const bool has_hi = k > 16;
     const bool similar = p->anchor_similar != 0;
     const uint64_t np = ctx->n_padded;
@@ -277,8 +282,11 @@ extern "C" int npge_anchor_find_device(npge_anchor_ctx* ctx,
         if (has_hi) NPGE_TRY(ensure(ctx->khi[b], max_records * 4));
         NPGE_TRY(ensure(ctx->pay[b], max_records * 4));
     }
-    NPGE_TRY(ensure(ctx->hist, kMaxPasses * kRadix * 4));
-    NPGE_TRY(ensure(ctx->status, size_t(passes) * tiles0 * kRadix * 4));
+    const size_t hist_bytes = size_t(passes) * plan.bins() * 4;
+    const size_t status_bytes = (tiles0 + 1) * plan.bins() * 4;  // one pass
+    NPGE_TRY(ensure(ctx->hist, hist_bytes));
+    NPGE_TRY(ensure(ctx->status, status_bytes));
+    NPGE_TRY(ensure(ctx->status2, status_bytes));
     NPGE_TRY(ensure(ctx->counters, kCntWords * 4));
     NPGE_TRY(ensure(ctx->summary, summary_words * 8));
     NPGE_TRY(ensure(ctx->scan_status, scan_tiles * 8));
@@ -299,9 +307,9 @@ extern "C" int npge_anchor_find_device(npge_anchor_ctx* ctx,
                                   cudaMemcpyHostToDevice, st));
     }
     NPGE_CUDA(cudaEventRecord(ctx->ev[0], st));
-    NPGE_CUDA(cudaMemsetAsync(ctx->hist.ptr, 0, kMaxPasses * kRadix * 4, st));
-    NPGE_CUDA(cudaMemsetAsync(ctx->status.ptr, 0,
-                              size_t(passes) * tiles0 * kRadix * 4, st));
+    NPGE_CUDA(cudaMemsetAsync(ctx->hist.ptr, 0, hist_bytes, st));
+    // look-back rows of pass 0; every pass clears the rows of the next one
+    NPGE_CUDA(cudaMemsetAsync(ctx->status.ptr, 0, status_bytes, st));
     NPGE_CUDA(cudaMemsetAsync(ctx->counters.ptr, 0, kCntWords * 4, st));
     NPGE_CUDA(cudaMemsetAsync(ctx->summary.ptr, 0, summary_words * 8, st));
     NPGE_CUDA(cudaMemsetAsync(ctx->scan_status.ptr, 0, scan_tiles * 8, st));
@@ -315,25 +323,29 @@ extern "C" int npge_anchor_find_device(npge_anchor_ctx* ctx,
         cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, ctx->device);
         uint32_t* hist = ptr<uint32_t>(ctx->hist);
         uint32_t* counters = ptr<uint32_t>(ctx->counters);
-        uint32_t* status = ptr<uint32_t>(ctx->status);
-        launch_hist(ptr<uint32_t>(ctx->packed), ptr<uint32_t>(ctx->nmask), np, k,
-                    passes, hist, n_sms, st);
-        launch_scan_hist(hist, passes, counters, st);
+        uint32_t* status[2] = {ptr<uint32_t>(ctx->status), ptr<uint32_t>(ctx->status2)};
+        launch_hist(plan, ptr<uint32_t>(ctx->packed), ptr<uint32_t>(ctx->nmask), np,
+                    k, hist, n_sms, st);
+        launch_scan_hist(plan, hist, counters, st);
         launches += 2;
         NPGE_CUDA(cudaEventRecord(ctx->ev[1], st));
         NPGE_CUDA(cudaEventRecord(ctx->ev_pass[0], st));
-        launch_sort_pass0(ptr<uint32_t>(ctx->packed), ptr<uint32_t>(ctx->nmask), np,
-                          k, hist, status, counters, ptr<uint32_t>(ctx->klo[0]),
-                          ptr<uint32_t>(ctx->khi[0]), ptr<uint32_t>(ctx->pay[0]), st);
+        launch_sort_pass0(plan, ptr<uint32_t>(ctx->packed),
+                          ptr<uint32_t>(ctx->nmask), np, k, hist, status[0],
+                          passes > 1 ? status[1] : nullptr, counters,
+                          ptr<uint32_t>(ctx->klo[0]), ptr<uint32_t>(ctx->khi[0]),
+                          ptr<uint32_t>(ctx->pay[0]), st);
         launches++;
         NPGE_CUDA(cudaEventRecord(ctx->ev_pass[1], st));
         for (int pass = 1; pass < passes; pass++) {
             int in = (pass - 1) & 1, out = pass & 1;
-            launch_sort_pass(pass, max_records, ptr<uint32_t>(ctx->klo[in]),
+            launch_sort_pass(plan, pass, k, max_records, ptr<uint32_t>(ctx->klo[in]),
                              ptr<uint32_t>(ctx->khi[in]), ptr<uint32_t>(ctx->pay[in]),
-                             hist, status + size_t(pass) * tiles0 * kRadix, counters,
-                             ptr<uint32_t>(ctx->klo[out]), ptr<uint32_t>(ctx->khi[out]),
-                             ptr<uint32_t>(ctx->pay[out]), has_hi, st);
+                             hist, status[pass & 1],
+                             pass + 1 < passes ? status[(pass + 1) & 1] : nullptr,
+                             counters, ptr<uint32_t>(ctx->klo[out]),
+                             ptr<uint32_t>(ctx->khi[out]), ptr<uint32_t>(ctx->pay[out]),
+                             st);
             launches++;
             NPGE_CUDA(cudaEventRecord(ctx->ev_pass[pass + 1], st));
         }
@@ -395,9 +407,18 @@ extern "C" int npge_anchor_find_device(npge_anchor_ctx* ctx,
     for (int pass = 0; np && pass < passes; pass++) {
         cudaEventElapsedTime(&s.ms_pass[pass], ctx->ev_pass[pass], ctx->ev_pass[pass + 1]);
     }
-    // N * (0.375 + 12 + 8 + 24 P + 12) + 9 F + 16 B
-    s.bytes_algorithmic = uint64_t(double(ctx->n_bases) * (32.375 + 24.0 * passes)) +
+    // SURVEY 8d model: N * (0.375 + 12 + 8 + 24 P(k) + 12) + 9 F + 16 B with
+    // P(k) = ceil(2k / 8) byte-digit passes, whatever this build really runs
+    const int model_passes = (2 * k + 7) / 8;
+    s.bytes_algorithmic = uint64_t(double(ctx->n_bases) * (32.375 + 24.0 * model_passes)) +
                           9 * s.n_fragments + 16 * s.n_blocks;
+    // compulsory traffic of the passes this build runs: genome read twice (hist,
+    // pass 0), records written once per pass and read once per later pass and
+    // by the grouping, results written
+    const double rec = has_hi ? 12.0 : 8.0;
+    s.bytes_moved = uint64_t(double(ctx->n_bases) * 0.75 +
+                             double(s.n_windows) * rec * (2.0 * passes)) +
+                    9 * s.n_fragments + 16 * s.n_blocks;
     ctx->total_selected = summary[kSumFragments];
     ctx->result_buf = final_buf;
     ctx->last_params = *p;

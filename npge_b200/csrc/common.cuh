@@ -24,13 +24,23 @@ namespace npge_b200 {
 // make_hash (make_hash.hpp:29-42): the forward hash of the window at g is bits
 // [2g, 2g+2k) of the packed stream.
 
-constexpr int kTileThreads = 256;
-constexpr int kItemsPerThread = 16;
-constexpr int kTile = kTileThreads * kItemsPerThread;  // 4096 records / positions
-constexpr int kWarps = kTileThreads / 32;
-constexpr int kRadixBits = 8;
-constexpr int kRadix = 1 << kRadixBits;
-constexpr int kMaxPasses = 8;  // ceil(64 / 8)
+constexpr int kSortThreads = 512;
+constexpr int kSortItems = 8;
+constexpr int kTile = kSortThreads * kSortItems;  // 4096 records / positions
+constexpr int kMaxDigitBits = 10;                 // widest radix digit
+constexpr int kMaxPasses = 16;                    // ceil(64 / 4)
+
+// Radix plan for 2k-bit keys: `passes` digits of `width` bits each (the last
+// may be narrower); histograms and look-back rows hold 1 << capbits bins.
+struct SortPlan {
+    int passes = 0, width = 0, capbits = 0;
+    __host__ __device__ int bins() const { return 1 << capbits; }
+    __host__ __device__ uint32_t mask(int pass, int k) const {
+        int left = 2 * k - pass * width;
+        int w = left < width ? left : width;
+        return (1u << w) - 1;
+    }
+};
 
 // positions are padded so every tile can bulk-copy tile + 16 B of halo
 constexpr uint64_t kPosAlign = 4096;
@@ -114,7 +124,7 @@ struct npge_anchor_ctx {
 
     // sort / grouping scratch
     npge_b200::DeviceBuffer klo[2], khi[2], pay[2];
-    npge_b200::DeviceBuffer hist, status, counters, used;
+    npge_b200::DeviceBuffer hist, status, status2, counters, used;
     npge_b200::DeviceBuffer found_bits, head_idx, sel;
     // device result
     npge_b200::DeviceBuffer r_seq, r_pos, r_ori, r_block_off, r_block_hash;

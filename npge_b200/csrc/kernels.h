@@ -10,9 +10,9 @@ enum {
     kCntValid = 0,      // number of N-free windows (records)
     kCntBadInput = 1,   // bytes outside ATGCN seen by pack
     kCntTicket0 = 2,    // tile tickets, one per radix pass (kMaxPasses slots)
-    kCntScanTicket = 10,  // tickets of the grouping scans (4 slots)
-    kCntCutIndex = 14,  // sorted index of the record with selected-rank M-1
-    kCntWords = 16
+    kCntScanTicket = 18,  // tickets of the grouping scans (4 slots)
+    kCntCutIndex = 22,  // sorted index of the record with selected-rank M-1
+    kCntWords = 24
 };
 
 // summary[] slots (u64) in ctx->summary
@@ -29,26 +29,33 @@ enum {
 void launch_pack(const uint8_t* ascii, uint32_t* packed, uint32_t* nmask,
                  uint64_t n_padded, uint32_t* counters, cudaStream_t s);
 
-void launch_hist(const uint32_t* packed, const uint32_t* nmask,
-                 uint64_t n_padded, int k, int passes, uint32_t* hist,
+SortPlan make_sort_plan(int k, int max_digit_bits);
+void exp_set_nochain(int v);
+
+// hist[passes][plan.bins()]: digit histograms of every valid canonical k-mer
+void launch_hist(const SortPlan& plan, const uint32_t* packed,
+                 const uint32_t* nmask, uint64_t n_padded, int k, uint32_t* hist,
                  int n_sms, cudaStream_t s);
 
-// hist[passes][256] counts -> exclusive bases in place; counters[kCntValid] = n
-void launch_scan_hist(uint32_t* hist, int passes, uint32_t* counters,
+// counts -> exclusive bases in place; counters[kCntValid] = n
+void launch_scan_hist(const SortPlan& plan, uint32_t* hist, uint32_t* counters,
                       cudaStream_t s);
 
 // pass 0: generate keys from the packed genome and scatter by digit 0
-void launch_sort_pass0(const uint32_t* packed, const uint32_t* nmask,
-                       uint64_t n_padded, int k, const uint32_t* hist_base,
-                       uint32_t* status, uint32_t* counters, uint32_t* klo_out,
-                       uint32_t* khi_out, uint32_t* pay_out, cudaStream_t s);
+void launch_sort_pass0(const SortPlan& plan, const uint32_t* packed,
+                       const uint32_t* nmask, uint64_t n_padded, int k,
+                       const uint32_t* hist_base, uint32_t* status,
+                       uint32_t* status_next, uint32_t* counters,
+                       uint32_t* klo_out, uint32_t* khi_out, uint32_t* pay_out,
+                       cudaStream_t s);
 
-// pass p >= 1: scatter records by digit p (bits [8p, 8p+8) of the key)
-void launch_sort_pass(int pass, uint64_t max_records, const uint32_t* klo_in,
-                      const uint32_t* khi_in, const uint32_t* pay_in,
-                      const uint32_t* hist_base, uint32_t* status,
-                      uint32_t* counters, uint32_t* klo_out, uint32_t* khi_out,
-                      uint32_t* pay_out, bool has_hi, cudaStream_t s);
+// pass p >= 1: scatter records by digit p (bits [p*width, (p+1)*width) of the key)
+void launch_sort_pass(const SortPlan& plan, int pass, int k, uint64_t max_records,
+                      const uint32_t* klo_in, const uint32_t* khi_in,
+                      const uint32_t* pay_in, const uint32_t* hist_base,
+                      uint32_t* status, uint32_t* status_next, uint32_t* counters,
+                      uint32_t* klo_out, uint32_t* khi_out, uint32_t* pay_out,
+                      cudaStream_t s);
 
 struct GroupArgs {
     const uint32_t* klo;

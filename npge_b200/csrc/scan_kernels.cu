@@ -65,22 +65,24 @@ void launch_pack(const uint8_t* ascii, uint32_t* packed, uint32_t* nmask,
 }
 
 // ---- digit histograms -------------------------------------------------------
-// One read of the packed genome produces the 256-bin histogram of every radix
-// digit of every valid canonical k-mer (the records are not materialised).
-// One thread walks 32 consecutive windows, sliding a 128-bit register window
-// with funnel shifts.  Persistent grid: CTAs loop over chunks and flush their
+// One read of the packed genome produces the histogram of every radix digit of
+// every valid canonical k-mer (the records are not materialised).  One thread
+// walks 32 consecutive windows, sliding a 128-bit register window with funnel
+// shifts.  Persistent grid: CTAs loop over chunks and flush their
 // shared-memory histograms once.
 template <int PASSES>
 __global__ void __launch_bounds__(256)
 hist_kernel(const uint32_t* __restrict__ packed,
             const uint32_t* __restrict__ nmask, uint64_t n_groups32, int k,
-            uint32_t* __restrict__ hist) {
-    __shared__ uint32_t sh[PASSES * kRadix];
-    for (int i = threadIdx.x; i < PASSES * kRadix; i += blockDim.x) sh[i] = 0;
+            int width, int capbits, uint32_t* __restrict__ hist) {
+    extern __shared__ uint32_t sh[];
+    const int cap = 1 << capbits;
+    for (int i = threadIdx.x; i < PASSES * cap; i += blockDim.x) sh[i] = 0;
     __syncthreads();
     const uint64_t stride = uint64_t(gridDim.x) * blockDim.x;
     const uint64_t kmask = k == 32 ? ~0ull : ((1ull << (2 * k)) - 1);
     const uint32_t nm = k == 32 ? ~0u : ((1u << k) - 1);
+    const uint32_t dmask = (1u << width) - 1;
     for (uint64_t t = blockIdx.x * uint64_t(blockDim.x) + threadIdx.x;
             t < n_groups32; t += stride) {
         // 64 bases of codes and 64 bits of N mask starting at position 32 t
@@ -99,7 +101,8 @@ hist_kernel(const uint32_t* __restrict__ packed,
                 uint64_t h = dir < rev ? dir : rev;
 #pragma unroll
                 for (int p = 0; p < PASSES; p++) {
-                    atomicAdd(&sh[p * kRadix + ((h >> (8 * p)) & 0xff)], 1u);
+                    // digits past the key's top bit are 0 (h < 2^(2k))
+                    atomicAdd(&sh[p * cap + (uint32_t(h >> (p * width)) & dmask)], 1u);
                 }
             }
             lo = (lo >> 2) | (hi << 62);
@@ -108,42 +111,44 @@ hist_kernel(const uint32_t* __restrict__ packed,
         }
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < PASSES * kRadix; i += blockDim.x) {
+    for (int i = threadIdx.x; i < PASSES * cap; i += blockDim.x) {
         uint32_t v = sh[i];
         if (v) atomicAdd(hist + i, v);
     }
 }
 
-void launch_hist(const uint32_t* packed, const uint32_t* nmask,
-                 uint64_t n_padded, int k, int passes, uint32_t* hist,
+void launch_hist(const SortPlan& plan, const uint32_t* packed,
+                 const uint32_t* nmask, uint64_t n_padded, int k, uint32_t* hist,
                  int n_sms, cudaStream_t s) {
     uint64_t groups = n_padded / 32;
     if (groups == 0) return;
     uint64_t want = (groups + 255) / 256;
-    uint32_t blocks = uint32_t(want < uint64_t(n_sms) * 8 ? want : uint64_t(n_sms) * 8);
-    switch (passes) {
-#define NPGE_HIST_CASE(P)                                                     \
-    case P:                                                                   \
-        hist_kernel<P><<<blocks, 256, 0, s>>>(packed, nmask, groups, k, hist); \
+    uint32_t blocks = uint32_t(want < uint64_t(n_sms) * 4 ? want : uint64_t(n_sms) * 4);
+    const size_t smem = size_t(plan.passes) * plan.bins() * 4;
+    switch (plan.passes) {
+#define NPGE_HIST_CASE(P)                                                      \
+    case P:                                                                    \
+        cudaFuncSetAttribute(hist_kernel<P>,                                   \
+                             cudaFuncAttributeMaxDynamicSharedMemorySize,      \
+                             int(smem));                                       \
+        hist_kernel<P><<<blocks, 256, smem, s>>>(packed, nmask, groups, k,     \
+                                                  plan.width, plan.capbits, hist); \
         break;
-        NPGE_HIST_CASE(1)
-        NPGE_HIST_CASE(2)
-        NPGE_HIST_CASE(3)
-        NPGE_HIST_CASE(4)
-        NPGE_HIST_CASE(5)
-        NPGE_HIST_CASE(6)
-        NPGE_HIST_CASE(7)
-        NPGE_HIST_CASE(8)
+        NPGE_HIST_CASE(1) NPGE_HIST_CASE(2) NPGE_HIST_CASE(3) NPGE_HIST_CASE(4)
+        NPGE_HIST_CASE(5) NPGE_HIST_CASE(6) NPGE_HIST_CASE(7) NPGE_HIST_CASE(8)
+        NPGE_HIST_CASE(9) NPGE_HIST_CASE(10) NPGE_HIST_CASE(11) NPGE_HIST_CASE(12)
+        NPGE_HIST_CASE(13) NPGE_HIST_CASE(14) NPGE_HIST_CASE(15) NPGE_HIST_CASE(16)
 #undef NPGE_HIST_CASE
     }
 }
 
 // ---- histogram scan -----------------------------------------------------------
-// counts -> exclusive digit bases, one warp-synchronous block per pass.
-__global__ void __launch_bounds__(kRadix)
+// counts -> exclusive digit bases, one block of `bins` threads per pass.
+__global__ void __launch_bounds__(1024)
 scan_hist_kernel(uint32_t* __restrict__ hist, uint32_t* __restrict__ counters) {
-    __shared__ uint32_t warp_sums[kRadix / 32];
-    uint32_t* h = hist + blockIdx.x * kRadix;
+    __shared__ uint32_t warp_sums[32];
+    const int bins = blockDim.x;
+    uint32_t* h = hist + blockIdx.x * bins;
     uint32_t v = h[threadIdx.x];
     uint32_t incl = v;
 #pragma unroll
@@ -156,14 +161,14 @@ scan_hist_kernel(uint32_t* __restrict__ hist, uint32_t* __restrict__ counters) {
     uint32_t base = 0;
     for (int w = 0; w < int(threadIdx.x >> 5); w++) base += warp_sums[w];
     h[threadIdx.x] = base + incl - v;
-    if (blockIdx.x == 0 && threadIdx.x == kRadix - 1) {
+    if (blockIdx.x == 0 && int(threadIdx.x) == bins - 1) {
         counters[kCntValid] = base + incl;
     }
 }
 
-void launch_scan_hist(uint32_t* hist, int passes, uint32_t* counters,
+void launch_scan_hist(const SortPlan& plan, uint32_t* hist, uint32_t* counters,
                       cudaStream_t s) {
-    scan_hist_kernel<<<passes, kRadix, 0, s>>>(hist, counters);
+    scan_hist_kernel<<<plan.passes, plan.bins(), 0, s>>>(hist, counters);
 }
 
 }  // namespace npge_b200

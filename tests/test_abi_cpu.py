@@ -25,7 +25,7 @@ def test_version_and_struct_layout():
     assert b"sm_100a" in lib.npge_anchor_version()
     assert C.sizeof(_abi.Params) == 16
     assert C.sizeof(_abi.Result) == 96
-    assert C.sizeof(_abi.Stats) == 112
+    assert C.sizeof(_abi.Stats) == 152
 
 
 @pytest.mark.skipif(has_gpu(), reason="checks the no-device error path")
