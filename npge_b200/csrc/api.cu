@@ -146,7 +146,10 @@ extern "C" void npge_anchor_destroy(npge_anchor_ctx* ctx) {
                            &ctx->found_bits, &ctx->head_idx, &ctx->sel,
                            &ctx->r_seq, &ctx->r_pos, &ctx->r_ori,
                            &ctx->r_block_off, &ctx->r_block_hash,
-                           &ctx->scan_status, &ctx->summary};
+                           &ctx->scan_status, &ctx->summary, &ctx->rows, &ctx->blk,
+                           &ctx->a_start, &ctx->tile_b, &ctx->win, &ctx->fine_start,
+                           &ctx->bstatus, &ctx->rec[0], &ctx->rec[1], &ctx->rhi[0],
+                           &ctx->rhi[1], &ctx->seq_lut};
     for (DeviceBuffer* b : all) release(*b);
     for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
     for (auto& ev : ctx->ev_pass) if (ev) cudaEventDestroy(ev);
@@ -224,6 +227,22 @@ extern "C" int npge_anchor_upload(npge_anchor_ctx* ctx, int32_t anchor_size,
                                   starts.size() * 8, cudaMemcpyHostToDevice, st));
         NPGE_CUDA(cudaMemcpyAsync(ctx->seq_caller.ptr, callers.data(),
                                   callers.size() * 4, cudaMemcpyHostToDevice, st));
+        // seq_lut[q] = scan-order sequence holding position q << lut_shift
+        // (pads count for the sequence before them)
+        const uint64_t n_chunks = (np >> ctx->lut_shift) + 2;
+        std::vector<uint32_t> lut(n_chunks);
+        {
+            size_t sidx = 0;
+            for (uint64_t q = 0; q < n_chunks; q++) {
+                const uint64_t g = q << ctx->lut_shift;
+                while (sidx + 1 < ctx->seqs.size() && ctx->seqs[sidx + 1].start <= g) sidx++;
+                lut[q] = uint32_t(sidx);
+            }
+        }
+        NPGE_TRY(ensure(ctx->seq_lut, n_chunks * 4));
+        NPGE_CUDA(cudaMemcpyAsync(ctx->seq_lut.ptr, lut.data(), n_chunks * 4,
+                                  cudaMemcpyHostToDevice, st));
+        NPGE_CUDA(cudaStreamSynchronize(st));  // lut is a local
         launch_pack(ptr<uint8_t>(ctx->ascii), ptr<uint32_t>(ctx->packed),
                     ptr<uint32_t>(ctx->nmask), np, ptr<uint32_t>(ctx->counters), st);
         NPGE_CUDA(cudaGetLastError());
@@ -240,6 +259,157 @@ extern "C" int npge_anchor_upload(npge_anchor_ctx* ctx, int32_t anchor_size,
     ctx->uploaded = true;
     return NPGE_ANCHOR_OK;
 }
+
+// ---- find_device, MSD partition + shared-memory bucket sort ---------------------------
+namespace {
+
+int find_device_msd(npge_anchor_ctx* ctx, const npge_anchor_params* p,
+                    const uint64_t* used_sorted, uint64_t n_used,
+                    npge_anchor_stats* stats) {
+    const int k = p->anchor_size;
+    const bool similar = p->anchor_similar != 0;
+    const uint64_t np = ctx->n_padded;
+    const uint64_t max_records = ctx->n_positions;  // upper bound on windows
+    if (max_records > kMaxRecords) {
+        return fail(NPGE_ANCHOR_ERR_CAPACITY,
+                    "more than 2^30-1 windows per device; shard the input");
+    }
+    const MsdPlan plan = make_msd_plan(k, max_records);
+    const uint64_t limit = uint64_t(p->max_anchor_fragments);
+    const uint64_t max_frags = std::min<uint64_t>(max_records, limit);
+    const size_t bins_a = size_t(1) << plan.capa;
+    const size_t summary_words = bucket_summary_words();
+    const uint32_t max_win = bucket_max_windows(plan, max_records);
+    NPGE_TRY(ensure(ctx->rows, msd_rows_needed(plan, np, max_records) * 4));
+    NPGE_TRY(ensure(ctx->blk, msd_blk_needed(plan, np, max_records) * 4));
+    NPGE_TRY(ensure(ctx->a_start, (bins_a + 1) * 4));
+    NPGE_TRY(ensure(ctx->tile_b, (bins_a + 1) * 4));
+    NPGE_TRY(ensure(ctx->win, (bins_a + 1) * 4));
+    NPGE_TRY(ensure(ctx->fine_start, ((bins_a << plan.wb) + 1) * 4));
+    for (int b = 0; b < 2; b++) {
+        NPGE_TRY(ensure(ctx->rec[b], (max_records + 16) * 8));
+        if (plan.wide) NPGE_TRY(ensure(ctx->rhi[b], (max_records + 16) * 4));
+    }
+    NPGE_TRY(ensure(ctx->bstatus, size_t(max_win + 1) * 8));
+    NPGE_TRY(ensure(ctx->counters, kCntWords * 4));
+    NPGE_TRY(ensure(ctx->summary, summary_words * 8));
+    NPGE_TRY(ensure(ctx->used, n_used * 8));
+    NPGE_TRY(ensure(ctx->r_seq, max_frags * 4));
+    NPGE_TRY(ensure(ctx->r_pos, max_frags * 4));
+    NPGE_TRY(ensure(ctx->r_ori, max_frags));
+    NPGE_TRY(ensure(ctx->r_block_off, (max_frags / 2 + 2) * 8));
+    NPGE_TRY(ensure(ctx->r_block_hash, (max_frags / 2 + 2) * 8));
+    if (similar) {
+        NPGE_TRY(ensure(ctx->found_bits, np / 8 + 256));
+        NPGE_TRY(ensure(ctx->sel, max_records + 16));
+    }
+    cudaStream_t st = ctx->stream;
+    uint32_t launches = 0;
+    if (n_used) {
+        NPGE_CUDA(cudaMemcpyAsync(ctx->used.ptr, used_sorted, n_used * 8,
+                                  cudaMemcpyHostToDevice, st));
+    }
+    NPGE_CUDA(cudaEventRecord(ctx->ev[0], st));
+    NPGE_CUDA(cudaMemsetAsync(ctx->counters.ptr, 0, kCntWords * 4, st));
+    NPGE_CUDA(cudaMemsetAsync(ctx->summary.ptr, 0, summary_words * 8, st));
+    NPGE_CUDA(cudaMemsetAsync(ctx->bstatus.ptr, 0, size_t(max_win + 1) * 8, st));
+    if (similar) {
+        NPGE_CUDA(cudaMemsetAsync(ctx->found_bits.ptr, 0, np / 8 + 256, st));
+        NPGE_CUDA(cudaMemsetAsync(ctx->sel.ptr, 0, max_records + 16, st));
+    }
+    MsdBuffers mb = {};
+    mb.rows = ptr<uint32_t>(ctx->rows);
+    mb.blk = ptr<uint32_t>(ctx->blk);
+    mb.a_start = ptr<uint32_t>(ctx->a_start);
+    mb.tile_b = ptr<uint32_t>(ctx->tile_b);
+    mb.win = ptr<uint32_t>(ctx->win);
+    mb.fine_start = ptr<uint32_t>(ctx->fine_start);
+    for (int b = 0; b < 2; b++) {
+        mb.rec[b] = ptr<uint64_t>(ctx->rec[b]);
+        mb.hi[b] = ptr<uint32_t>(ctx->rhi[b]);
+    }
+    if (np) {
+        launch_msd_partition(plan, ptr<uint32_t>(ctx->packed), ptr<uint32_t>(ctx->nmask),
+                             np, max_records, mb, ptr<uint32_t>(ctx->counters), st,
+                             ctx->ev_pass, &launches);
+    } else {
+        for (int i = 0; i < 4; i++) NPGE_CUDA(cudaEventRecord(ctx->ev_pass[i], st));
+    }
+    NPGE_CUDA(cudaEventRecord(ctx->ev[2], st));
+    BucketArgs a = {};
+    a.plan = plan;
+    a.rec_w = mb.rec[1];
+    a.hi_w = mb.hi[1];
+    a.scratch_rec = mb.rec[0];
+    a.scratch_hi = mb.hi[0];
+    a.a_start = mb.a_start;
+    a.win = mb.win;
+    a.fine_start = mb.fine_start;
+    a.counters = ptr<uint32_t>(ctx->counters);
+    a.used = ptr<uint64_t>(ctx->used);
+    a.n_used = n_used;
+    a.seq_start = ptr<uint64_t>(ctx->seq_start);
+    a.seq_caller = ptr<uint32_t>(ctx->seq_caller);
+    a.seq_lut = ptr<uint32_t>(ctx->seq_lut);
+    a.lut_shift = ctx->lut_shift;
+    a.max_fragments = limit;
+    a.found_bits = ptr<uint32_t>(ctx->found_bits);
+    a.sel = ptr<uint8_t>(ctx->sel);
+    a.r_seq = ptr<uint32_t>(ctx->r_seq);
+    a.r_pos = ptr<uint32_t>(ctx->r_pos);
+    a.r_ori = ptr<int8_t>(ctx->r_ori);
+    a.r_block_off = ptr<uint64_t>(ctx->r_block_off);
+    a.r_block_hash = ptr<uint64_t>(ctx->r_block_hash);
+    a.status = ptr<uint64_t>(ctx->bstatus);
+    a.summary = ptr<uint64_t>(ctx->summary);
+    launch_bucket(a, similar, np ? max_records : 0, st, &launches);
+    NPGE_CUDA(cudaGetLastError());
+    NPGE_CUDA(cudaEventRecord(ctx->ev[3], st));
+    uint64_t summary[kSumWords];
+    uint32_t counters_h[kCntWords];
+    NPGE_CUDA(cudaMemcpyAsync(summary, ctx->summary.ptr, sizeof(summary),
+                              cudaMemcpyDeviceToHost, st));
+    NPGE_CUDA(cudaMemcpyAsync(counters_h, ctx->counters.ptr, sizeof(counters_h),
+                              cudaMemcpyDeviceToHost, st));
+    NPGE_CUDA(cudaStreamSynchronize(st));
+    npge_anchor_stats& s = ctx->stats;
+    memset(&s, 0, sizeof(s));
+    s.n_positions = ctx->n_bases;
+    s.n_windows = counters_h[kCntValid];
+    s.n_fragments = summary[kSumEmitted];
+    s.n_blocks = summary[kSumBlocksEmitted];
+    s.digest[0] = summary[kSumDigest0];
+    s.digest[1] = summary[kSumDigest1];
+    s.radix_passes = uint32_t(2 + plan.smem_passes);
+    s.gpu_launches = launches;
+    // stages: [count A + scan] [pass A] [count B + scan] [pass B] [bucket sort + emit]
+    cudaEventElapsedTime(&s.ms_hist, ctx->ev[0], ctx->ev_pass[0]);
+    cudaEventElapsedTime(&s.ms_pass[0], ctx->ev_pass[0], ctx->ev_pass[1]);
+    cudaEventElapsedTime(&s.ms_pass[1], ctx->ev_pass[1], ctx->ev_pass[2]);
+    cudaEventElapsedTime(&s.ms_pass[2], ctx->ev_pass[2], ctx->ev_pass[3]);
+    cudaEventElapsedTime(&s.ms_sort, ctx->ev[0], ctx->ev[2]);
+    cudaEventElapsedTime(&s.ms_group, ctx->ev[2], ctx->ev[3]);
+    cudaEventElapsedTime(&s.ms_total, ctx->ev[0], ctx->ev[3]);
+    const int model_passes = (2 * k + 7) / 8;
+    s.bytes_algorithmic = uint64_t(double(ctx->n_bases) * (32.375 + 24.0 * model_passes)) +
+                          9 * s.n_fragments + 16 * s.n_blocks;
+    // compulsory traffic of this build: genome read twice; records written by
+    // pass A, read by count B and pass B, written by pass B, read by the bucket
+    // sort (twice more in anchor-similar mode); results written
+    const double rec = plan.wide ? 12.0 : 8.0;
+    s.bytes_moved = uint64_t(double(ctx->n_bases) * 0.75 +
+                             double(s.n_windows) * rec * (similar ? 7.0 : 5.0)) +
+                    9 * s.n_fragments + 16 * s.n_blocks;
+    ctx->total_selected = summary[kSumFragments];
+    ctx->plan = plan;
+    ctx->msd = true;
+    ctx->last_params = *p;
+    ctx->have_result = true;
+    if (stats) *stats = s;
+    return NPGE_ANCHOR_OK;
+}
+
+}  // namespace
 
 // ---- find_device: hist -> radix sort -> grouping, all on the device ---------------
 extern "C" int npge_anchor_find_device(npge_anchor_ctx* ctx,
@@ -261,6 +431,13 @@ extern "C" int npge_anchor_find_device(npge_anchor_ctx* ctx,
     }
     NPGE_CUDA(cudaSetDevice(ctx->device));
     ctx->have_result = false;
+    {
+        const char* path = getenv("NPGE_ANCHOR_PATH");  // experiments: "lsd"
+        if (!path || strcmp(path, "lsd") != 0) {
+            return find_device_msd(ctx, p, used_sorted, n_used, stats);
+        }
+    }
+    ctx->msd = false;
     const int k = p->anchor_size;
     const SortPlan plan = make_sort_plan(k, digit_bits_preference());
     const int passes = plan.passes;
@@ -452,6 +629,77 @@ int read_key(npge_anchor_ctx* ctx, uint64_t i, uint64_t* key) {
     return NPGE_ANCHOR_OK;
 }
 
+// Members of the cut group in the reference's order (caller sequence index,
+// pos') -> the first `keep` of them replace the device's (scan order) choice.
+void rebuild_cut_members(npge_anchor_ctx* ctx, HostResult& r,
+                         const std::vector<uint32_t>& pay, uint64_t first,
+                         uint64_t keep) {
+    struct Member { uint32_t seq; uint64_t pos2; uint32_t pos; int8_t ori; };
+    std::vector<Member> members;
+    members.reserve(pay.size());
+    for (uint32_t pw : pay) {
+        uint64_t g = pw >> 1;
+        size_t a = 0, b = ctx->seqs.size();
+        while (b - a > 1) {
+            size_t mid = (a + b) / 2;
+            if (ctx->seqs[mid].start <= g) a = mid; else b = mid;
+        }
+        const SeqEntry& e = ctx->seqs[a];
+        uint32_t pos = uint32_t(g - e.start);
+        bool direct = pw & 1;
+        members.push_back({e.caller_index, direct ? pos : pos + e.size, pos,
+                           int8_t(direct ? 1 : -1)});
+    }
+    std::sort(members.begin(), members.end(), [](const Member& x, const Member& y) {
+        return x.seq != y.seq ? x.seq < y.seq : x.pos2 < y.pos2;
+    });
+    for (uint64_t j = 0; j < keep; j++) {
+        r.frag_seq[first + j] = members[j].seq;
+        r.frag_min_pos[first + j] = members[j].pos;
+        r.frag_ori[first + j] = members[j].ori;
+    }
+}
+
+// MSD path: the unit holding the cut record was written back sorted; its
+// bounds and the cut record's index are in the counters.
+int fix_cut_group_msd(npge_anchor_ctx* ctx, HostResult& r, uint64_t limit) {
+    uint32_t c[kCntWords];
+    NPGE_CUDA(cudaMemcpyAsync(c, ctx->counters.ptr, sizeof(c), cudaMemcpyDeviceToHost,
+                              ctx->stream));
+    NPGE_CUDA(cudaStreamSynchronize(ctx->stream));
+    const uint32_t cut = c[kCntCutIndex], cs = c[kCntCutStart], cn = c[kCntCutSize];
+    if (cn == 0 || cut < cs || cut >= cs + cn) {
+        return fail(NPGE_ANCHOR_ERR_CUDA, "internal: cut record outside its unit");
+    }
+    std::vector<uint64_t> rec(cn);
+    std::vector<uint32_t> hi(ctx->plan.wide ? cn : 0);
+    NPGE_CUDA(cudaMemcpyAsync(rec.data(), ptr<uint64_t>(ctx->rec[1]) + cs, size_t(cn) * 8,
+                              cudaMemcpyDeviceToHost, ctx->stream));
+    if (ctx->plan.wide) {
+        NPGE_CUDA(cudaMemcpyAsync(hi.data(), ptr<uint32_t>(ctx->rhi[1]) + cs,
+                                  size_t(cn) * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    NPGE_CUDA(cudaStreamSynchronize(ctx->stream));
+    auto K = [&](uint32_t i) {
+        return (uint64_t(ctx->plan.wide ? hi[i] : 0u) << 32) | (rec[i] >> 32);
+    };
+    const uint32_t ci = cut - cs;
+    uint32_t gs = ci, ge = ci + 1;
+    while (gs > 0 && K(gs - 1) == K(ci)) gs--;
+    while (ge < cn && K(ge) == K(ci)) ge++;
+    if (r.block_hash.empty()) {
+        return fail(NPGE_ANCHOR_ERR_CUDA, "internal: cut group is not the last block");
+    }
+    const uint64_t first = r.block_offsets[r.block_hash.size() - 1];
+    const uint64_t keep = limit - first;
+    if (ge - gs > keep) {
+        std::vector<uint32_t> pay(ge - gs);
+        for (uint32_t i = gs; i < ge; i++) pay[i - gs] = uint32_t(rec[i]);
+        rebuild_cut_members(ctx, r, pay, first, keep);
+    }
+    return NPGE_ANCHOR_OK;
+}
+
 // The reference cuts the list sorted by (hash, Sequence*, pos') at
 // max-anchor-fragments (AnchorFinder.cpp:361-363), pos' = pos + size for the
 // reverse strand (:295-301).  The device order inside a group is (seq, pos), so
@@ -491,30 +739,7 @@ int fix_cut_group(npge_anchor_ctx* ctx, HostResult& r, uint64_t limit) {
                                   ptr<uint32_t>(ctx->pay[ctx->result_buf]) + gs,
                                   (ge - gs) * 4, cudaMemcpyDeviceToHost, ctx->stream));
         NPGE_CUDA(cudaStreamSynchronize(ctx->stream));
-        struct Member { uint32_t seq; uint64_t pos2; uint32_t pos; int8_t ori; };
-        std::vector<Member> members;
-        members.reserve(pay.size());
-        for (uint32_t pw : pay) {
-            uint64_t g = pw >> 1;
-            size_t a = 0, b = ctx->seqs.size();
-            while (b - a > 1) {
-                size_t mid = (a + b) / 2;
-                if (ctx->seqs[mid].start <= g) a = mid; else b = mid;
-            }
-            const SeqEntry& e = ctx->seqs[a];
-            uint32_t pos = uint32_t(g - e.start);
-            bool direct = pw & 1;
-            members.push_back({e.caller_index, direct ? pos : pos + e.size, pos,
-                               int8_t(direct ? 1 : -1)});
-        }
-        std::sort(members.begin(), members.end(), [](const Member& x, const Member& y) {
-            return x.seq != y.seq ? x.seq < y.seq : x.pos2 < y.pos2;
-        });
-        for (uint64_t j = 0; j < keep; j++) {
-            r.frag_seq[first + j] = members[j].seq;
-            r.frag_min_pos[first + j] = members[j].pos;
-            r.frag_ori[first + j] = members[j].ori;
-        }
+        rebuild_cut_members(ctx, r, pay, first, keep);
     }
     return NPGE_ANCHOR_OK;
 }
@@ -565,7 +790,11 @@ extern "C" int npge_anchor_fetch(npge_anchor_ctx* ctx, npge_anchor_result* out) 
         bool lone_tail = false;
         uint64_t lone_hash = 0;
         if (ctx->total_selected > limit && limit > 0) {
-            NPGE_TRY(fix_cut_group(ctx, *r, limit));
+            if (ctx->msd) {
+                NPGE_TRY(fix_cut_group_msd(ctx, *r, limit));
+            } else {
+                NPGE_TRY(fix_cut_group(ctx, *r, limit));
+            }
             // a group cut down to one member is a singleton in the reference's
             // list: no block, but its hash is still recorded as used (:385)
             if (r->block_offsets[nb] - r->block_offsets[nb - 1] == 1) {

@@ -1,0 +1,731 @@
+// bucket_kernels.cu -- last stage of the anchor sort, fused with the grouping:
+// every CTA takes one "unit" (the (A, B) bins that start inside one window of
+// kWindow records, at most kBucketCap records unless a bin is oversized), sorts
+// it by the remaining key bits with an LSD radix sort in shared memory (byte
+// digits, stable), finds the runs of equal canonical k-mers and writes the
+// anchor fragments and blocks.  Units are taken in ticket order, so a warp-wide
+// decoupled look-back over one 64-bit word per unit gives every unit its output
+// offsets and the result comes out in ascending (k-mer, position) order.
+//
+// Replaces fragmenttg_postprocess (src/algo/AnchorFinder.cpp:356-391): the
+// linear pass that opens a Block the first time a hash repeats,
+// FoundFragment::make_fragment (:240-246), the max-anchor-fragments cut
+// (:361-363), and -- in the two anchor-similar launches -- the neighbour rule of
+// BloomTask::test_and_add (:170-182) with an exact filter.
+//
+// A unit larger than kBucketCap (one (A, B) bin with thousands of records: a
+// k-mer repeated thousands of times, low-complexity sequence) takes the slow
+// path of the same CTA: the same passes, chunk by chunk, through global memory.
+#include "kernels.h"
+#include "rank.cuh"
+
+namespace npge_b200 {
+
+namespace {
+
+constexpr int kCap = kBucketCap;
+constexpr uint64_t kSFlagAggregate = 1ull << 62;
+constexpr uint64_t kSFlagInclusive = 2ull << 62;
+constexpr uint64_t kSValueMask = (1ull << 62) - 1;
+constexpr int kPartials = 64;
+// scan value: blocks << 31 | fragments (both < 2^31)
+
+__device__ __forceinline__ uint64_t ld_relaxed64(const uint64_t* p) {
+    uint64_t v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+
+__device__ __forceinline__ void st_relaxed64(uint64_t* p, uint64_t v) {
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+__device__ __forceinline__ uint64_t rem_key(uint64_t rec, uint32_t hi) {
+    return (uint64_t(hi) << 32) | (rec >> 32);
+}
+
+__device__ __forceinline__ uint32_t bucket_of(const uint32_t* __restrict__ table,
+                                              uint32_t n, uint32_t t) {
+    uint32_t lo = 0, hi = n;
+    while (hi - lo > 1) {
+        uint32_t mid = (lo + hi) >> 1;
+        if (table[mid] <= t) lo = mid; else hi = mid;
+    }
+    return lo;
+}
+
+// first f in [0, n] with table[f] >= v (table ascending, n + 1 entries)
+__device__ __forceinline__ uint32_t lower_bound_u32(const uint32_t* __restrict__ table,
+                                                    uint32_t n, uint32_t v) {
+    uint32_t lo = 0, hi = n;
+    while (lo < hi) {
+        uint32_t mid = (lo + hi) >> 1;
+        if (table[mid] < v) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+
+// SortedVector::has_elem (src/util/SortedVector.hpp:108-111) on the device
+__device__ __forceinline__ bool is_used(const BucketArgs& a, uint64_t key) {
+    uint64_t lo = 0, hi = a.n_used;
+    while (lo < hi) {
+        uint64_t mid = (lo + hi) >> 1;
+        if (a.used[mid] < key) lo = mid + 1; else hi = mid;
+    }
+    return lo < a.n_used && a.used[lo] == key;
+}
+
+__device__ __forceinline__ bool found_bit(const BucketArgs& a, uint32_t g) {
+    return (a.found_bits[g >> 5] >> (g & 31)) & 1u;
+}
+
+template <bool WIDE>
+struct __align__(16) BucketSmem {
+    uint64_t buf[2][kCap + 2];
+    uint32_t hib[2][WIDE ? kCap + 2 : 4];
+    RankSmem<8> rk;
+    uint32_t grun[256];       // slow path: running digit bases of the unit
+    uint64_t warp_tot[kRW];
+    int32_t warp_head[kRW];
+    uint64_t red[3][kRW];
+    uint64_t prefix;          // look-back result
+    uint64_t chunk_tot;
+    uint32_t ticket;
+    uint32_t cut;             // 1 + unit index of the record with rank M-1
+};
+
+// One sorted chunk of a unit in shared memory: records at K[1 .. cn], halo
+// records at K[0] / K[cn + 1] when has_prev / has_next.
+template <bool WIDE>
+struct Chunk {
+    const uint64_t* rec;   // shared: rec[0] = halo before, rec[1..cn], rec[cn+1] halo
+    const uint32_t* hi;
+    uint32_t cn;
+    bool has_prev, has_next;
+    uint32_t g0;           // global record index of rec[1]
+    uint32_t carry_head;   // global index of the head of rec[1]'s group
+    __device__ __forceinline__ uint64_t key(uint32_t j) const {  // j in 0 .. cn+1
+        return rem_key(rec[j], WIDE ? hi[j] : 0u);
+    }
+};
+
+
+// Item i of lane l of warp w is chunk element j = w * 32 * kRI + i * 32 + l.
+__device__ __forceinline__ uint32_t item_index(int i) {
+    return (threadIdx.x >> 5) * (32 * kRI) + i * 32 + (threadIdx.x & 31);
+}
+
+// Per-item flags of a sorted chunk, one bit per item round i:
+//   valid    the item exists
+//   preveq   same key as the record before it (= not the head of its group)
+//   inb      its group has at least two members
+template <bool WIDE>
+__device__ __forceinline__ void unit_flags(const Chunk<WIDE>& ch, uint32_t& valid,
+                                           uint32_t& preveq, uint32_t& inb) {
+    valid = preveq = inb = 0;
+#pragma unroll
+    for (int i = 0; i < kRI; i++) {
+        const uint32_t j = item_index(i);
+        if (j < ch.cn) {
+            const uint64_t key = ch.key(j + 1);
+            const bool pe = (j > 0 || ch.has_prev) && ch.key(j) == key;
+            const bool ne = (j + 1 < ch.cn || ch.has_next) && ch.key(j + 2) == key;
+            valid |= 1u << i;
+            preveq |= (pe ? 1u : 0u) << i;
+            inb |= ((pe || ne) ? 1u : 0u) << i;
+        }
+    }
+}
+
+// Global record index of the head of every item's group.  Contains barriers.
+template <bool WIDE>
+__device__ __forceinline__ void unit_heads(BucketSmem<WIDE>& sm, const Chunk<WIDE>& ch,
+                                           uint32_t valid, uint32_t preveq,
+                                           uint32_t (&hidx)[kRI]) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t le = (2u << lane) - 1;  // lanes <= lane
+    int32_t last = -1;
+    uint32_t hb[kRI];
+#pragma unroll
+    for (int i = 0; i < kRI; i++) {
+        const bool head = ((valid >> i) & 1) && !((preveq >> i) & 1);
+        hb[i] = __ballot_sync(0xffffffffu, head);
+        if (hb[i]) last = int32_t(warp * (32 * kRI) + i * 32 + (31 - __clz(hb[i])));
+    }
+    __syncthreads();  // warp_head may still be read by a previous call
+    if (lane == 0) sm.warp_head[warp] = last;
+    __syncthreads();
+    uint32_t carry = ch.carry_head;
+    for (int w = 0; w < warp; w++) {
+        int32_t h = sm.warp_head[w];
+        if (h >= 0) carry = ch.g0 + uint32_t(h);
+    }
+#pragma unroll
+    for (int i = 0; i < kRI; i++) {
+        const uint32_t m = hb[i] & le;
+        const uint32_t base = warp * (32 * kRI) + i * 32;
+        hidx[i] = m ? ch.g0 + base + (31 - __clz(m)) : carry;
+        if (hb[i]) carry = ch.g0 + base + (31 - __clz(hb[i]));
+    }
+}
+
+// Selection of the chunk's items and their count.  MODE 0: parity / exact
+// (every group of >= 2 whose hash is not used); MODE 2: anchor-similar (groups
+// holding a candidate: found(p) and not found(p-1), AnchorFinder.cpp:176).
+// Returns the CTA total (blocks << 31 | fragments) in every thread; leaves the
+// per-warp totals in sm.warp_tot for unit_write.  Contains barriers.
+template <bool WIDE, int MODE>
+__device__ __forceinline__ uint64_t unit_select(BucketSmem<WIDE>& sm,
+                                                const Chunk<WIDE>& ch,
+                                                const BucketArgs& a, uint64_t key_hi,
+                                                uint32_t valid, uint32_t preveq,
+                                                uint32_t inb, uint32_t& sel) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    sel = 0;
+    if (MODE == 0) {
+#pragma unroll
+        for (int i = 0; i < kRI; i++) {
+            if ((inb >> i) & 1) {
+                bool u = a.n_used &&
+                         is_used(a, key_hi | ch.key(item_index(i) + 1));
+                sel |= (u ? 0u : 1u) << i;
+            }
+        }
+    } else {
+        uint32_t hidx[kRI];
+        unit_heads<WIDE>(sm, ch, valid, preveq, hidx);
+#pragma unroll
+        for (int i = 0; i < kRI; i++) {
+            if ((preveq >> i) & 1) {
+                const uint32_t g = uint32_t(ch.rec[item_index(i) + 1]) >> 1;
+                if (found_bit(a, g) && !(g > 0 && found_bit(a, g - 1))) {
+                    a.sel[hidx[i]] = 1;
+                }
+            }
+        }
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < kRI; i++) {
+            if (((inb >> i) & 1) && a.sel[hidx[i]]) sel |= 1u << i;
+        }
+    }
+    uint32_t nf = 0, nb = 0;
+#pragma unroll
+    for (int i = 0; i < kRI; i++) {
+        const bool s = (sel >> i) & 1;
+        nf += __popc(__ballot_sync(0xffffffffu, s));
+        nb += __popc(__ballot_sync(0xffffffffu, s && !((preveq >> i) & 1)));
+    }
+    __syncthreads();  // warp_tot may still be read by a previous unit_write
+    if (lane == 0) sm.warp_tot[warp] = (uint64_t(nb) << 31) | nf;
+    __syncthreads();
+    uint64_t tot = 0;
+#pragma unroll
+    for (int w = 0; w < kRW; w++) tot += sm.warp_tot[w];
+    return tot;
+}
+
+struct Digest {
+    uint64_t d0 = 0, d1 = 0, nb = 0;
+};
+
+// (scan-order sequence, position in it) of global position g
+__device__ __forceinline__ void locate(const BucketArgs& a, uint32_t g, uint32_t& seq,
+                                       uint32_t& pos) {
+    const uint32_t q = g >> a.lut_shift;
+    uint32_t lo = a.seq_lut[q], hi = a.seq_lut[q + 1] + 1;  // answer in [lo, hi)
+    while (hi - lo > 1) {
+        uint32_t mid = (lo + hi) >> 1;
+        if (a.seq_start[mid] <= g) lo = mid; else hi = mid;
+    }
+    seq = a.seq_caller[lo];
+    pos = g - uint32_t(a.seq_start[lo]);
+}
+
+// Writes the selected items of the chunk; `base` = global ranks before it.
+template <bool WIDE>
+__device__ __forceinline__ void unit_write(BucketSmem<WIDE>& sm, const Chunk<WIDE>& ch,
+                                           const BucketArgs& a, uint64_t key_hi,
+                                           uint32_t preveq, uint32_t sel,
+                                           uint64_t base, Digest& dg) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t lt = (1u << lane) - 1;
+    for (int w = 0; w < warp; w++) base += sm.warp_tot[w];
+    uint64_t fr = base & 0x7fffffffull, br = base >> 31;
+    const uint64_t limit = a.max_fragments;
+#pragma unroll
+    for (int i = 0; i < kRI; i++) {
+        const bool s = (sel >> i) & 1;
+        const bool head = s && !((preveq >> i) & 1);
+        const uint32_t fb = __ballot_sync(0xffffffffu, s);
+        const uint32_t bb = __ballot_sync(0xffffffffu, head);
+        if (s) {
+            const uint64_t f = fr + __popc(fb & lt);
+            if (f < limit) {
+                const uint32_t j = item_index(i);
+                const uint32_t pay = uint32_t(ch.rec[j + 1]);
+                const uint64_t key = key_hi | ch.key(j + 1);
+                uint32_t seq, pos;
+                locate(a, pay >> 1, seq, pos);
+                a.r_seq[f] = seq;
+                a.r_pos[f] = pos;
+                a.r_ori[f] = (pay & 1) ? 1 : -1;
+                const uint64_t t = (uint64_t(seq) << 33) | (uint64_t(pos) << 1) | (pay & 1);
+                dg.d0 += splitmix64(key ^ splitmix64(t));
+                dg.d1 += splitmix64(t + splitmix64(key));
+                if (head) {
+                    const uint64_t b = br + __popc(bb & lt);
+                    a.r_block_off[b] = f;
+                    a.r_block_hash[b] = key;
+                    dg.nb++;
+                }
+                if (f + 1 == limit) {
+                    a.counters[kCntCutIndex] = ch.g0 + j;
+                    sm.cut = 1;
+                }
+            }
+        }
+        fr += __popc(fb);
+        br += __popc(bb);
+    }
+}
+
+
+// Warp-wide decoupled look-back over the units before `w` (one 64-bit status
+// word per unit).  Leaves the exclusive prefix in sm.prefix.  Contains a barrier.
+template <bool WIDE>
+__device__ __forceinline__ void unit_lookback(BucketSmem<WIDE>& sm, const BucketArgs& a,
+                                              uint32_t w, uint32_t n_win, uint64_t tot) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (warp == 0) {
+        uint64_t prefix = 0;
+        if (w == 0) {
+            if (lane == 0) st_relaxed64(a.status, kSFlagInclusive | tot);
+        } else {
+            if (lane == 0) st_relaxed64(a.status + w, kSFlagAggregate | tot);
+            int64_t j = int64_t(w) - 1;
+            while (true) {
+                const int64_t idx = j - lane;
+                const uint64_t v = idx >= 0 ? ld_relaxed64(a.status + idx)
+                                            : kSFlagInclusive;
+                const uint32_t fl = uint32_t(v >> 62);
+                const uint32_t inc = __ballot_sync(0xffffffffu, fl == 2);
+                const uint32_t nr = __ballot_sync(0xffffffffu, fl == 0);
+                uint64_t x = v & kSValueMask;
+                bool last = false;
+                if (inc) {
+                    const int L = __ffs(inc) - 1;
+                    if (nr & ((2u << L) - 1)) continue;  // a nearer unit is not ready
+                    if (lane > L) x = 0;
+                    last = true;
+                } else if (nr) {
+                    continue;
+                }
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+                prefix += x;
+                if (last) break;
+                j -= 32;
+            }
+            if (lane == 0) st_relaxed64(a.status + w, kSFlagInclusive | (prefix + tot));
+        }
+        if (lane == 0) {
+            sm.prefix = prefix;
+            if (w + 1 == n_win) {  // last unit: totals before truncation
+                const uint64_t all = prefix + tot;
+                a.summary[kSumFragments] = all & 0x7fffffffull;
+                a.summary[kSumBlocks] = all >> 31;
+            }
+        }
+    }
+    __syncthreads();
+}
+
+// head of the group of sorted record `i` (key == key of record i) inside
+// [lo_bound, i]: gallop back, then binary search (keys ascending)
+template <bool WIDE>
+__device__ uint32_t find_head_global(const uint64_t* rec, const uint32_t* hi,
+                                     uint32_t lo_bound, uint32_t i, uint64_t key) {
+    auto K = [&](uint32_t x) { return rem_key(rec[x], WIDE ? hi[x] : 0u); };
+    uint32_t hi_i = i, step = 1, lo;
+    while (true) {
+        if (hi_i - lo_bound < step) { lo = lo_bound; break; }
+        if (K(hi_i - step) != key) { lo = hi_i - step + 1; break; }
+        hi_i -= step;
+        step <<= 1;
+    }
+    while (lo < hi_i) {
+        uint32_t mid = (lo + hi_i) >> 1;
+        if (K(mid) == key) hi_i = mid; else lo = mid + 1;
+    }
+    return lo;
+}
+
+template <bool WIDE>
+__device__ __forceinline__ void mark_found(const Chunk<WIDE>& ch, const BucketArgs& a,
+                                           uint64_t key_hi, uint32_t preveq) {
+    // found(p): the window's hash is not used and was seen at an earlier scan
+    // position (BloomTask::test_and_add, AnchorFinder.cpp:170-182, exact filter):
+    // every member of a sorted group but the first
+#pragma unroll
+    for (int i = 0; i < kRI; i++) {
+        if ((preveq >> i) & 1) {
+            const uint32_t j = item_index(i);
+            if (a.n_used && is_used(a, key_hi | ch.key(j + 1))) continue;
+            const uint32_t g = uint32_t(ch.rec[j + 1]) >> 1;
+            atomicOr(a.found_bits + (g >> 5), 1u << (g & 31));
+        }
+    }
+}
+
+template <bool WIDE>
+__device__ __forceinline__ void flush_digest(BucketSmem<WIDE>& sm, const BucketArgs& a,
+                                             uint32_t w, Digest dg) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        dg.d0 += __shfl_xor_sync(0xffffffffu, dg.d0, o);
+        dg.d1 += __shfl_xor_sync(0xffffffffu, dg.d1, o);
+        dg.nb += __shfl_xor_sync(0xffffffffu, dg.nb, o);
+    }
+    if (lane == 0) {
+        sm.red[0][warp] = dg.d0;
+        sm.red[1][warp] = dg.d1;
+        sm.red[2][warp] = dg.nb;
+    }
+    __syncthreads();
+    if (threadIdx.x < 3) {
+        uint64_t v = 0;
+        for (int x = 0; x < kRW; x++) v += sm.red[threadIdx.x][x];
+        if (v) {
+            atomicAdd(reinterpret_cast<unsigned long long*>(
+                          a.summary + kSumWords + (w % kPartials) * 4 + threadIdx.x),
+                      (unsigned long long)v);
+        }
+    }
+}
+
+// MODE 0: sort + parity/exact emit.  MODE 1 (anchor-similar, first launch): sort,
+// set the found bits, write the sorted unit back.  MODE 2 (second launch): the
+// unit is already sorted; candidate rule + emit.
+template <bool WIDE, int MODE>
+__global__ void __launch_bounds__(kRT, 2)
+bucket_kernel(BucketArgs a) {
+    extern __shared__ __align__(16) unsigned char raw[];
+    BucketSmem<WIDE>& sm = *reinterpret_cast<BucketSmem<WIDE>*>(raw);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) {
+        sm.ticket = atomicAdd(a.counters + kCntScanTicket + MODE, 1u);
+        sm.cut = 0;
+    }
+    __syncthreads();
+    const uint32_t w = sm.ticket;
+    const uint32_t n_win = a.counters[kCntWindows];
+    if (w >= n_win) return;
+    const MsdPlan& pl = a.plan;
+    const uint32_t bins_a = 1u << pl.capa;
+    const uint32_t ab = bucket_of(a.win, bins_a, w);
+    const uint32_t lo_pos = a.a_start[ab] + (w - a.win[ab]) * uint32_t(kWindow);
+    const uint32_t hi_pos = min(lo_pos + uint32_t(kWindow), a.a_start[ab + 1]);
+    const uint32_t* fs = a.fine_start + (size_t(ab) << pl.wb);
+    const uint32_t f0 = lower_bound_u32(fs, 1u << pl.wb, lo_pos);
+    const uint32_t f1 = lower_bound_u32(fs, 1u << pl.wb, hi_pos);
+    const uint32_t s = fs[f0], n = fs[f1] - s;
+    const uint64_t key_hi = uint64_t(ab) << pl.rem;
+    Digest dg;
+    auto digit_at = [&](uint64_t r, uint32_t h, int shift) {
+        return uint32_t(rem_key(r, h) >> shift) & 255u;
+    };
+    if (n <= uint32_t(kCap)) {
+        // ---- fast path: the whole unit in shared memory ---------------------------
+#pragma unroll
+        for (int i = 0; i < kRI; i++) {
+            const uint32_t j = item_index(i);
+            if (j < n) {
+                sm.buf[0][1 + j] = a.rec_w[s + j];
+                if (WIDE) sm.hib[0][1 + j] = a.hi_w[s + j];
+            }
+        }
+        __syncthreads();
+        int cur = 0;
+        if (MODE != 2) {
+            const uint32_t first = warp * (32 * kRI);
+            const int rounds = first >= n ? 0 : int(min(uint32_t(kRI), (n - first + 31) / 32));
+#pragma unroll 1
+            for (int pass = 0; pass < pl.smem_passes; pass++) {
+                uint64_t rec[kRI];
+                uint32_t hi[kRI], digit[kRI], slot[kRI];
+#pragma unroll
+                for (int i = 0; i < kRI; i++) {
+                    const uint32_t j = item_index(i);
+                    const bool in = j < n;
+                    rec[i] = in ? sm.buf[cur][1 + j] : 0ull;
+                    hi[i] = (WIDE && in) ? sm.hib[cur][1 + j] : 0u;
+                    digit[i] = in ? digit_at(rec[i], hi[i], 8 * pass) : 256u;
+                }
+                uint32_t c0, c1;
+                tile_rank<8>(sm.rk, digit, rounds, slot, c0, c1);
+#pragma unroll
+                for (int i = 0; i < kRI; i++) {
+                    if (digit[i] < 256u) {
+                        sm.buf[cur ^ 1][1 + slot[i]] = rec[i];
+                        if (WIDE) sm.hib[cur ^ 1][1 + slot[i]] = hi[i];
+                    }
+                }
+                __syncthreads();
+                cur ^= 1;
+            }
+        }
+        Chunk<WIDE> ch;
+        ch.rec = sm.buf[cur];
+        ch.hi = sm.hib[cur];
+        ch.cn = n;
+        ch.has_prev = ch.has_next = false;
+        ch.g0 = s;
+        ch.carry_head = s;
+        uint32_t valid, preveq, inb, sel;
+        unit_flags<WIDE>(ch, valid, preveq, inb);
+        auto write_back = [&]() {
+#pragma unroll
+            for (int i = 0; i < kRI; i++) {
+                const uint32_t j = item_index(i);
+                if (j < n) {
+                    a.rec_w[s + j] = sm.buf[cur][1 + j];
+                    if (WIDE) a.hi_w[s + j] = sm.hib[cur][1 + j];
+                }
+            }
+        };
+        if (MODE == 1) {
+            mark_found<WIDE>(ch, a, key_hi, preveq);
+            write_back();
+            return;
+        }
+        const uint64_t tot =
+            unit_select<WIDE, MODE>(sm, ch, a, key_hi, valid, preveq, inb, sel);
+        unit_lookback<WIDE>(sm, a, w, n_win, tot);
+        unit_write<WIDE>(sm, ch, a, key_hi, preveq, sel, sm.prefix, dg);
+        __syncthreads();
+        if (sm.cut) {
+            if (MODE == 0) write_back();
+            if (tid == 0) {
+                a.counters[kCntCutStart] = s;
+                a.counters[kCntCutSize] = n;
+            }
+        }
+        flush_digest<WIDE>(sm, a, w, dg);
+        return;
+    }
+    // ---- slow path: an oversized unit, chunk by chunk through global memory -----
+    uint64_t* src = a.rec_w;
+    uint32_t* srch = a.hi_w;
+    uint64_t* dst = a.scratch_rec;
+    uint32_t* dsth = a.scratch_hi;
+    if (MODE != 2) {
+#pragma unroll 1
+        for (int pass = 0; pass < pl.smem_passes; pass++) {
+            const int shift = 8 * pass;
+            if (tid < 256) sm.grun[tid] = 0;
+            __syncthreads();
+            for (uint32_t x = tid; x < n; x += kRT) {
+                atomicAdd(&sm.grun[digit_at(src[s + x], WIDE ? srch[s + x] : 0u, shift)], 1u);
+            }
+            __syncthreads();
+            {   // exclusive scan of the 256 digit counts (warps 0..7 hold them)
+                uint32_t v = tid < 256 ? sm.grun[tid] : 0u;
+                uint32_t incl = v;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    uint32_t u = __shfl_up_sync(0xffffffffu, incl, o);
+                    if (lane >= o) incl += u;
+                }
+                if (lane == 31) sm.rk.scan_tmp[warp] = incl;
+                __syncthreads();
+                uint32_t base = 0;
+                for (int x = 0; x < warp; x++) base += sm.rk.scan_tmp[x];
+                if (tid < 256) sm.grun[tid] = base + incl - v;
+                __syncthreads();
+            }
+#pragma unroll 1
+            for (uint32_t c0 = 0; c0 < n; c0 += kCap) {
+                const uint32_t cn = min(uint32_t(kCap), n - c0);
+                uint64_t rec[kRI];
+                uint32_t hi[kRI], digit[kRI], slot[kRI];
+#pragma unroll
+                for (int i = 0; i < kRI; i++) {
+                    const uint32_t j = item_index(i);
+                    const bool in = j < cn;
+                    rec[i] = in ? src[s + c0 + j] : 0ull;
+                    hi[i] = (WIDE && in) ? srch[s + c0 + j] : 0u;
+                    digit[i] = in ? digit_at(rec[i], hi[i], shift) : 256u;
+                }
+                const uint32_t first = warp * (32 * kRI);
+                const int rounds =
+                    first >= cn ? 0 : int(min(uint32_t(kRI), (cn - first + 31) / 32));
+                uint32_t cnt0, cnt1;
+                tile_rank<8>(sm.rk, digit, rounds, slot, cnt0, cnt1);
+#pragma unroll
+                for (int i = 0; i < kRI; i++) {
+                    if (digit[i] < 256u) {
+                        sm.buf[0][slot[i]] = rec[i];
+                        if (WIDE) sm.hib[0][slot[i]] = hi[i];
+                    }
+                }
+                __syncthreads();
+#pragma unroll
+                for (int i = 0; i < kRI; i++) {
+                    const uint32_t j = tid + i * kRT;
+                    if (j < cn) {
+                        const uint64_t r = sm.buf[0][j];
+                        const uint32_t h = WIDE ? sm.hib[0][j] : 0u;
+                        const uint32_t d = digit_at(r, h, shift);
+                        const uint32_t at = s + sm.grun[d] + j - sm.rk.tile_off[d];
+                        dst[at] = r;
+                        if (WIDE) dsth[at] = h;
+                    }
+                }
+                __syncthreads();
+                if (tid < 256) sm.grun[tid] += cnt0;
+                __syncthreads();
+            }
+            uint64_t* t = src; src = dst; dst = t;
+            uint32_t* th = srch; srch = dsth; dsth = th;
+        }
+        if (src != a.rec_w) {  // odd number of passes: bring the unit home
+            for (uint32_t x = tid; x < n; x += kRT) {
+                a.rec_w[s + x] = src[s + x];
+                if (WIDE) a.hi_w[s + x] = srch[s + x];
+            }
+            __syncthreads();
+        }
+    }
+    const uint64_t* X = a.rec_w;
+    const uint32_t* XH = a.hi_w;
+    Chunk<WIDE> ch;
+    auto load_chunk = [&](uint32_t c0) {
+        const uint32_t cn = min(uint32_t(kCap), n - c0);
+        __syncthreads();  // the previous chunk is no longer read
+#pragma unroll
+        for (int i = 0; i < kRI; i++) {
+            const uint32_t j = item_index(i);
+            if (j < cn) {
+                sm.buf[0][1 + j] = X[s + c0 + j];
+                if (WIDE) sm.hib[0][1 + j] = XH[s + c0 + j];
+            }
+        }
+        if (tid == 0) {
+            sm.chunk_tot = s + c0;  // carry head, unless the group started earlier
+            if (c0 > 0) {
+                sm.buf[0][0] = X[s + c0 - 1];
+                if (WIDE) sm.hib[0][0] = XH[s + c0 - 1];
+                const uint64_t k0 = rem_key(X[s + c0 - 1], WIDE ? XH[s + c0 - 1] : 0u);
+                const uint64_t k1 = rem_key(X[s + c0], WIDE ? XH[s + c0] : 0u);
+                if (k0 == k1) {
+                    sm.chunk_tot = find_head_global<WIDE>(X, XH, s, s + c0 - 1, k0);
+                }
+            }
+            if (c0 + cn < n) {
+                sm.buf[0][cn + 1] = X[s + c0 + cn];
+                if (WIDE) sm.hib[0][cn + 1] = XH[s + c0 + cn];
+            }
+        }
+        __syncthreads();
+        ch.rec = sm.buf[0];
+        ch.hi = sm.hib[0];
+        ch.cn = cn;
+        ch.has_prev = c0 > 0;
+        ch.has_next = c0 + cn < n;
+        ch.g0 = s + c0;
+        ch.carry_head = uint32_t(sm.chunk_tot);
+    };
+    uint32_t valid, preveq, inb, sel;
+    if (MODE == 1) {
+        for (uint32_t c0 = 0; c0 < n; c0 += kCap) {
+            load_chunk(c0);
+            unit_flags<WIDE>(ch, valid, preveq, inb);
+            mark_found<WIDE>(ch, a, key_hi, preveq);
+        }
+        return;
+    }
+    uint64_t tot = 0;
+    for (int sweep = (MODE == 2 ? 0 : 1); sweep < 2; sweep++) {
+        // sweep 0 (anchor-similar): let every candidate mark its group first
+        tot = 0;
+        for (uint32_t c0 = 0; c0 < n; c0 += kCap) {
+            load_chunk(c0);
+            unit_flags<WIDE>(ch, valid, preveq, inb);
+            tot += unit_select<WIDE, MODE>(sm, ch, a, key_hi, valid, preveq, inb, sel);
+        }
+    }
+    unit_lookback<WIDE>(sm, a, w, n_win, tot);
+    uint64_t base = sm.prefix;
+    for (uint32_t c0 = 0; c0 < n; c0 += kCap) {
+        load_chunk(c0);
+        unit_flags<WIDE>(ch, valid, preveq, inb);
+        const uint64_t t =
+            unit_select<WIDE, MODE>(sm, ch, a, key_hi, valid, preveq, inb, sel);
+        unit_write<WIDE>(sm, ch, a, key_hi, preveq, sel, base, dg);
+        base += t;
+    }
+    __syncthreads();
+    if (sm.cut && tid == 0) {
+        a.counters[kCntCutStart] = s;
+        a.counters[kCntCutSize] = n;
+    }
+    flush_digest<WIDE>(sm, a, w, dg);
+}
+
+__global__ void bucket_finalize_kernel(BucketArgs a) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    uint64_t d0 = 0, d1 = 0, nb = 0;
+    for (int s = 0; s < kPartials; s++) {
+        d0 += a.summary[kSumWords + s * 4 + 0];
+        d1 += a.summary[kSumWords + s * 4 + 1];
+        nb += a.summary[kSumWords + s * 4 + 2];
+    }
+    uint64_t total = a.summary[kSumFragments];
+    uint64_t emitted = total < a.max_fragments ? total : a.max_fragments;
+    a.summary[kSumDigest0] = d0;
+    a.summary[kSumDigest1] = d1;
+    a.summary[kSumEmitted] = emitted;
+    a.summary[kSumBlocksEmitted] = nb;
+    a.r_block_off[nb] = emitted;
+}
+
+template <typename K>
+void set_smem(K kernel, size_t bytes) {
+    cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                         int(bytes));
+}
+
+}  // namespace
+
+size_t bucket_summary_words() { return kSumWords + kPartials * 4; }
+
+// windows (= units) of the bucket sort: an upper bound for the grid
+uint32_t bucket_max_windows(const MsdPlan& plan, uint64_t max_records) {
+    return uint32_t((max_records + kWindow - 1) / kWindow) + (1u << plan.capa);
+}
+
+void launch_bucket(const BucketArgs& a, bool similar, uint64_t max_records,
+                   cudaStream_t s, uint32_t* launches) {
+    const uint32_t grid = bucket_max_windows(a.plan, max_records);
+#define NPGE_BUCKET(W, M)                                                       \
+    do {                                                                        \
+        set_smem(bucket_kernel<W, M>, sizeof(BucketSmem<W>));                   \
+        bucket_kernel<W, M><<<grid, kRT, sizeof(BucketSmem<W>), s>>>(a);        \
+        *launches += 1;                                                         \
+    } while (0)
+    if (max_records) {
+        if (similar) {
+            if (a.plan.wide) { NPGE_BUCKET(true, 1); NPGE_BUCKET(true, 2); }
+            else { NPGE_BUCKET(false, 1); NPGE_BUCKET(false, 2); }
+        } else {
+            if (a.plan.wide) NPGE_BUCKET(true, 0); else NPGE_BUCKET(false, 0);
+        }
+    }
+#undef NPGE_BUCKET
+    bucket_finalize_kernel<<<1, 32, 0, s>>>(a);
+    *launches += 1;
+}
+
+}  // namespace npge_b200

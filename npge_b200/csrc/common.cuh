@@ -42,6 +42,19 @@ struct SortPlan {
     }
 };
 
+// Plan of the MSD partition + shared-memory bucket sort for 2k-bit keys
+// (msd_kernels.cu): pass A takes the top wa bits, pass B the next wb, the bucket
+// sort the low `rem` = 2k - wa bits (B included) in `smem_passes` byte digits.
+struct MsdPlan {
+    int k = 0, total = 0, wa = 0, wb = 0, rem = 0;
+    int capa = 8, capb = 8;  // histogram rows hold 1 << cap bins
+    int wide = 0;            // rem > 32: records carry a second u32 of key bits
+    int smem_passes = 0;
+};
+
+constexpr int kBucketCap = kTile;        // records one CTA sorts in shared memory
+constexpr int kWindow = kBucketCap / 2;  // bins starting in one window = one unit
+
 // positions are padded so every tile can bulk-copy tile + 16 B of halo
 constexpr uint64_t kPosAlign = 4096;
 
@@ -126,6 +139,12 @@ struct npge_anchor_ctx {
     npge_b200::DeviceBuffer klo[2], khi[2], pay[2];
     npge_b200::DeviceBuffer hist, status, status2, counters, used;
     npge_b200::DeviceBuffer found_bits, head_idx, sel;
+    // MSD partition + bucket sort (msd_kernels.cu, bucket_kernels.cu)
+    npge_b200::DeviceBuffer rows, blk, a_start, tile_b, win, fine_start, bstatus;
+    npge_b200::DeviceBuffer rec[2], rhi[2], seq_lut;
+    int lut_shift = 12;
+    npge_b200::MsdPlan plan;
+    bool msd = true;          // which path produced the result
     // device result
     npge_b200::DeviceBuffer r_seq, r_pos, r_ori, r_block_off, r_block_hash;
     npge_b200::DeviceBuffer scan_status, summary;

@@ -12,7 +12,10 @@ enum {
     kCntTicket0 = 2,    // tile tickets, one per radix pass (kMaxPasses slots)
     kCntScanTicket = 18,  // tickets of the grouping scans (4 slots)
     kCntCutIndex = 22,  // sorted index of the record with selected-rank M-1
-    kCntWords = 24
+    kCntWindows = 23,   // bucket-sort windows of the last partition
+    kCntCutStart = 24,  // unit holding the cut record: first record, size
+    kCntCutSize = 25,
+    kCntWords = 32
 };
 
 // summary[] slots (u64) in ctx->summary
@@ -56,6 +59,62 @@ void launch_sort_pass(const SortPlan& plan, int pass, int k, uint64_t max_record
                       uint32_t* status, uint32_t* status_next, uint32_t* counters,
                       uint32_t* klo_out, uint32_t* khi_out, uint32_t* pay_out,
                       cudaStream_t s);
+
+// ---- MSD partition + bucket sort (msd_kernels.cu, bucket_kernels.cu) -----------
+struct MsdBuffers {
+    uint32_t* rows;        // histogram rows / scatter bases of the current pass
+    uint32_t* blk;         // block sums of the row scan
+    uint32_t* a_start;     // [(1 << capa) + 1]
+    uint32_t* tile_b;      // [(1 << capa) + 1]
+    uint32_t* win;         // [(1 << capa) + 1]
+    uint32_t* fine_start;  // [((1 << capa) << wb) + 1]
+    uint64_t* rec[2];      // key bits [0, 32) << 32 | payload
+    uint32_t* hi[2];       // key bits [32, rem) when plan.wide
+};
+
+MsdPlan make_msd_plan(int k, uint64_t n_positions);
+size_t msd_rows_needed(const MsdPlan& plan, uint64_t n_padded, uint64_t max_records);
+size_t msd_blk_needed(const MsdPlan& plan, uint64_t n_padded, uint64_t max_records);
+// ev (optional, 4 events): after count A, pass A, count B, pass B
+void launch_msd_partition(const MsdPlan& plan, const uint32_t* packed,
+                          const uint32_t* nmask, uint64_t n_padded,
+                          uint64_t max_records, const MsdBuffers& b,
+                          uint32_t* counters, cudaStream_t s, cudaEvent_t* ev,
+                          uint32_t* launches);
+
+struct BucketArgs {
+    MsdPlan plan;
+    uint64_t* rec_w;        // records sorted by (A, B): buffer 1 of MsdBuffers
+    uint32_t* hi_w;
+    uint64_t* scratch_rec;  // buffer 0: scratch of oversized units
+    uint32_t* scratch_hi;
+    const uint32_t* a_start;
+    const uint32_t* win;
+    const uint32_t* fine_start;
+    uint32_t* counters;
+    const uint64_t* used;
+    uint64_t n_used;
+    const uint64_t* seq_start;   // [S+1] global start of each scan-order sequence
+    const uint32_t* seq_caller;  // [S] caller index
+    const uint32_t* seq_lut;     // sequence holding position q << lut_shift
+    int lut_shift;
+    uint64_t max_fragments;      // truncation M
+    uint32_t* found_bits;        // anchor-similar: 1 bit per global position
+    uint8_t* sel;                // anchor-similar: per record index of a group head
+    uint32_t* r_seq;
+    uint32_t* r_pos;
+    int8_t* r_ori;
+    uint64_t* r_block_off;
+    uint64_t* r_block_hash;
+    uint64_t* status;            // one look-back word per unit
+    uint64_t* summary;
+};
+
+size_t bucket_summary_words();
+uint32_t bucket_max_windows(const MsdPlan& plan, uint64_t max_records);
+// similar: two launches (found bits, then candidate rule + emit)
+void launch_bucket(const BucketArgs& a, bool similar, uint64_t max_records,
+                   cudaStream_t s, uint32_t* launches);
 
 struct GroupArgs {
     const uint32_t* klo;

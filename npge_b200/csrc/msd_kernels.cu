@@ -1,0 +1,521 @@
+// msd_kernels.cu -- the two partition passes of the anchor sort.
+//
+// (canonical k-mer, position, strand) records are ordered in three stages
+// (DESIGN.md "Sort"):
+//   pass A   regenerate the keys from the packed genome and partition them,
+//            stably, by the top `wa` bits of the canonical k-mer
+//   pass B   partition every A bucket, stably, by the next `wb` bits
+//   bucket   (bucket_kernels.cu) LSD radix sort of the remaining bits of each
+//            small run of (A, B) bins entirely in shared memory, fused with the
+//            run-length grouping and the anchor output
+// Both partition passes are chainless: a counting kernel writes one digit
+// histogram row per tile, a scan turns the rows into scatter bases, and the
+// scatter kernel never waits on another CTA.  Counting pass A costs one more
+// read of the 2-bit genome (0.375 B/base); counting pass B one read of the
+// records.  Ranking inside a tile is the stable warp-synchronous scheme of
+// rank.cuh, so records with equal keys stay in ascending position order, which
+// is the scan order of the reference (SeqI.hpp:45-57, AnchorFinder.cpp:184-196).
+//
+// Replaces std::sort of FoundFragments (src/algo/AnchorFinder.cpp:234-238,358;
+// src/util/SortedVector.hpp:47-49) together with bucket_kernels.cu.
+#include "kernels.h"
+#include "rank.cuh"
+
+namespace npge_b200 {
+
+MsdPlan make_msd_plan(int k, uint64_t n_positions) {
+    MsdPlan p;
+    p.k = k;
+    p.total = 2 * k;
+    int f = 2;  // fine bits so that a fine bin holds ~1024 records
+    while (f < 20 && (uint64_t(1024) << f) < n_positions) f++;
+    if (f > p.total) f = p.total;
+    const int need = p.total - 32;  // bits a narrow (8 B) record cannot hold
+    int wa = (f + 1) / 2;
+    if (need > 0 && need <= kMaxDigitBits && wa < need) wa = need;
+    if (wa > kMaxDigitBits) wa = kMaxDigitBits;
+    if (wa > p.total) wa = p.total;
+    if (wa < 1) wa = 1;
+    int wb = f - wa;
+    if (wb < 1) wb = 1;
+    if (wb > kMaxDigitBits) wb = kMaxDigitBits;
+    if (wb > p.total - wa) wb = p.total - wa;
+    p.wa = wa;
+    p.wb = wb;
+    p.rem = p.total - wa;
+    p.wide = p.rem > 32;
+    p.capa = wa <= 8 ? 8 : 10;
+    p.capb = wb <= 8 ? 8 : 10;
+    p.smem_passes = (p.rem + 7) / 8;
+    return p;
+}
+
+namespace {
+
+// canonical key and validity of the window at tile-relative position rel
+__device__ __forceinline__ bool window_key(const GenomeStage& st, uint32_t rel, int k,
+                                           uint64_t& h, uint32_t& ori_bit) {
+    const bool bad = window_has_n(st.m, rel, k);
+    const uint64_t dir = forward_key(st.w, rel, k);
+    const uint64_t rev = revcomp_key(dir, k);
+    h = dir < rev ? dir : rev;
+    ori_bit = h == dir ? 1u : 0u;  // ori = +1 iff h == dir (AnchorFinder.cpp:303-312)
+    return !bad;
+}
+
+// ---- count A: one histogram row per genome tile ---------------------------------
+__global__ void __launch_bounds__(kRT)
+count_a_kernel(const uint32_t* __restrict__ packed, const uint32_t* __restrict__ nmask,
+               MsdPlan plan, uint32_t* __restrict__ rows) {
+    extern __shared__ __align__(16) unsigned char raw[];
+    GenomeStage& st = *reinterpret_cast<GenomeStage*>(raw);
+    uint32_t* hist = reinterpret_cast<uint32_t*>(raw + sizeof(GenomeStage));
+    const int bins = 1 << plan.capa;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int i = tid; i < bins; i += kRT) hist[i] = 0;
+    stage_genome_tile(st, packed, nmask, blockIdx.x);
+    const int sa = plan.total - plan.wa;
+#pragma unroll
+    for (int i = 0; i < kRI; i++) {
+        uint32_t rel = warp * (32 * kRI) + i * 32 + lane;
+        uint64_t h;
+        uint32_t ob;
+        if (window_key(st, rel, plan.k, h, ob)) atomicAdd(&hist[uint32_t(h >> sa)], 1u);
+    }
+    __syncthreads();
+    uint32_t* row = rows + size_t(blockIdx.x) * bins;
+    for (int i = tid; i < bins; i += kRT) row[i] = hist[i];
+}
+
+// ---- column scan of the histogram rows ---------------------------------------------
+// rows[t][d] (t < n_rows) -> exclusive prefix over t of column d, in place; the
+// column totals go to rows[n_rows][d].  Three launches: block sums, scan of the
+// block sums (one CTA), row prefix.
+constexpr int kScanRows = 64;  // rows per block of the two-level scan
+
+__global__ void __launch_bounds__(1024)
+scan_rows_sum_kernel(const uint32_t* __restrict__ rows, uint32_t n_rows,
+                     uint32_t* __restrict__ blk) {
+    const int bins = blockDim.x, d = threadIdx.x;
+    const uint32_t r0 = blockIdx.x * kScanRows;
+    const uint32_t r1 = min(r0 + kScanRows, n_rows);
+    uint32_t s = 0;
+#pragma unroll 8
+    for (uint32_t r = r0; r < r1; r++) s += rows[size_t(r) * bins + d];
+    blk[size_t(blockIdx.x) * bins + d] = s;
+}
+
+__global__ void __launch_bounds__(1024)
+scan_rows_blk_kernel(uint32_t* __restrict__ blk, uint32_t n_blk,
+                     uint32_t* __restrict__ totals) {
+    const int bins = blockDim.x, d = threadIdx.x;
+    uint32_t run = 0;
+    uint32_t b = 0;
+    for (; b + 8 <= n_blk; b += 8) {
+        uint32_t v[8];
+#pragma unroll
+        for (int j = 0; j < 8; j++) v[j] = blk[size_t(b + j) * bins + d];
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            blk[size_t(b + j) * bins + d] = run;
+            run += v[j];
+        }
+    }
+    for (; b < n_blk; b++) {
+        uint32_t v = blk[size_t(b) * bins + d];
+        blk[size_t(b) * bins + d] = run;
+        run += v;
+    }
+    totals[d] = run;
+}
+
+__global__ void __launch_bounds__(1024)
+scan_rows_apply_kernel(uint32_t* __restrict__ rows, uint32_t n_rows,
+                       const uint32_t* __restrict__ blk,
+                       const uint32_t* __restrict__ add) {
+    const int bins = blockDim.x, d = threadIdx.x;
+    const uint32_t r0 = blockIdx.x * kScanRows;
+    const uint32_t r1 = min(r0 + kScanRows, n_rows);
+    uint32_t run = blk[size_t(blockIdx.x) * bins + d] + (add ? add[d] : 0u);
+    for (uint32_t r = r0; r < r1; r += 8) {
+        uint32_t v[8];
+#pragma unroll
+        for (int j = 0; j < 8; j++) v[j] = r + j < r1 ? rows[size_t(r + j) * bins + d] : 0;
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            if (r + j < r1) rows[size_t(r + j) * bins + d] = run;
+            run += v[j];
+        }
+    }
+}
+
+// block-wide exclusive scan of one value per thread (blockDim.x <= 1024)
+__device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t* warp_tmp,
+                                                    uint32_t* total) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t incl = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        uint32_t u = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += u;
+    }
+    __syncthreads();  // warp_tmp may still be read from a previous call
+    if (lane == 31) warp_tmp[warp] = incl;
+    __syncthreads();
+    uint32_t base = 0, all = 0;
+    const int nw = (blockDim.x + 31) / 32;
+    for (int w = 0; w < nw; w++) {
+        uint32_t t = warp_tmp[w];
+        if (w < warp) base += t;
+        all += t;
+    }
+    if (total) *total = all;
+    return base + incl - v;
+}
+
+// After the A rows are scanned: bucket starts, tile and window tables of the
+// A buckets.  One CTA of 1 << capa threads.
+//   a_start[a]  first record of bucket a (a_start[bins] = n)
+//   tile_b[a]   first B tile of bucket a (tiles of kTile records, bucket aligned)
+//   win[a]      first bucket-sort window of bucket a (windows of kWindow records)
+__global__ void __launch_bounds__(1024)
+a_tables_kernel(const uint32_t* __restrict__ totals, uint32_t* __restrict__ a_start,
+                uint32_t* __restrict__ tile_b, uint32_t* __restrict__ win,
+                uint32_t* __restrict__ counters) {
+    __shared__ uint32_t tmp[32];
+    const int bins = blockDim.x, d = threadIdx.x;
+    const uint32_t c = totals[d];
+    uint32_t all;
+    uint32_t s = block_excl_scan(c, tmp, &all);
+    a_start[d] = s;
+    if (d == bins - 1) {
+        a_start[bins] = all;
+        counters[kCntValid] = all;
+    }
+    uint32_t t = block_excl_scan((c + kTile - 1) / kTile, tmp, &all);
+    tile_b[d] = t;
+    if (d == bins - 1) tile_b[bins] = all;
+    uint32_t w = block_excl_scan((c + kWindow - 1) / kWindow, tmp, &all);
+    win[d] = w;
+    if (d == bins - 1) {
+        win[bins] = all;
+        counters[kCntWindows] = all;
+    }
+}
+
+
+// key bits kept in a record after pass A (the low `rem` bits of the k-mer)
+__device__ __forceinline__ uint64_t rem_key(uint64_t rec, uint32_t hi) {
+    return (uint64_t(hi) << 32) | (rec >> 32);
+}
+
+// last a with table[a] <= t (table ascending, n + 1 entries, table[n] > t)
+__device__ __forceinline__ uint32_t bucket_of(const uint32_t* __restrict__ table,
+                                              uint32_t n, uint32_t t) {
+    uint32_t lo = 0, hi = n;  // answer in [lo, hi)
+    while (hi - lo > 1) {
+        uint32_t mid = (lo + hi) >> 1;
+        if (table[mid] <= t) lo = mid; else hi = mid;
+    }
+    return lo;
+}
+
+template <int CAPBITS, bool WIDE>
+struct __align__(16) PassSmem {
+    static constexpr int BINS = 1 << CAPBITS;
+    GenomeStage st;  // pass A only
+    RankSmem<CAPBITS> rk;
+    uint32_t bin_base[BINS];
+    uint64_t rec[kTile];
+    uint32_t hi[WIDE ? kTile : 4];
+    uint16_t dig[kTile];  // pass A: the digit is not part of the record
+};
+
+// ---- pass A: generate + partition by the top wa bits -----------------------------
+template <int CAPBITS, bool WIDE>
+__global__ void __launch_bounds__(kRT, 2)
+pass_a_kernel(const uint32_t* __restrict__ packed, const uint32_t* __restrict__ nmask,
+              MsdPlan plan, const uint32_t* __restrict__ rows,
+              uint64_t* __restrict__ out_rec, uint32_t* __restrict__ out_hi) {
+    extern __shared__ __align__(16) unsigned char raw[];
+    using Smem = PassSmem<CAPBITS, WIDE>;
+    Smem& sm = *reinterpret_cast<Smem*>(raw);
+    constexpr int BINS = Smem::BINS;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t tile = blockIdx.x;
+    stage_genome_tile(sm.st, packed, nmask, tile);
+    const int sa = plan.rem;
+    const uint64_t rmask = (1ull << plan.rem) - 1;  // rem <= 63
+    const uint32_t gbase = tile * uint32_t(kTile);
+    uint64_t rec[kRI];
+    uint32_t hi[kRI], digit[kRI], slot[kRI];
+#pragma unroll
+    for (int i = 0; i < kRI; i++) {
+        uint32_t rel = warp * (32 * kRI) + i * 32 + lane;
+        uint64_t h;
+        uint32_t ob;
+        bool ok = window_key(sm.st, rel, plan.k, h, ob);
+        uint64_t kr = h & rmask;
+        // payload: global position << 1 | (ori == +1)
+        rec[i] = (uint64_t(uint32_t(kr)) << 32) | (((gbase + rel) << 1) | ob);
+        hi[i] = uint32_t(kr >> 32);
+        digit[i] = ok ? uint32_t(h >> sa) : uint32_t(BINS);
+    }
+    uint32_t c0, c1;
+    tile_rank<CAPBITS>(sm.rk, digit, kRI, slot, c0, c1);
+    const uint32_t* row = rows + size_t(tile) * BINS;
+    if (BINS > kRT) {
+        sm.bin_base[2 * tid] = row[2 * tid] - sm.rk.tile_off[2 * tid];
+        sm.bin_base[2 * tid + 1] = row[2 * tid + 1] - sm.rk.tile_off[2 * tid + 1];
+    } else if (tid < BINS) {
+        sm.bin_base[tid] = row[tid] - sm.rk.tile_off[tid];
+    }
+#pragma unroll
+    for (int i = 0; i < kRI; i++) {
+        if (digit[i] < BINS) {
+            sm.rec[slot[i]] = rec[i];
+            if (WIDE) sm.hi[slot[i]] = hi[i];
+            sm.dig[slot[i]] = uint16_t(digit[i]);
+        }
+    }
+    __syncthreads();
+    const uint32_t total = sm.rk.total;
+#pragma unroll
+    for (int i = 0; i < kRI; i++) {
+        uint32_t j = tid + i * kRT;
+        if (j < total) {
+            uint32_t idx = sm.bin_base[sm.dig[j]] + j;
+            out_rec[idx] = sm.rec[j];
+            if (WIDE) out_hi[idx] = sm.hi[j];
+        }
+    }
+}
+
+// ---- count B: one histogram row per bucket-aligned tile of A-sorted records ----------
+template <bool WIDE>
+__global__ void __launch_bounds__(kRT)
+count_b_kernel(const uint64_t* __restrict__ rec, const uint32_t* __restrict__ hi,
+               MsdPlan plan, const uint32_t* __restrict__ a_start,
+               const uint32_t* __restrict__ tile_b, uint32_t* __restrict__ rows) {
+    extern __shared__ __align__(16) unsigned char raw[];
+    uint32_t* hist = reinterpret_cast<uint32_t*>(raw);
+    const int bins = 1 << plan.capb, bins_a = 1 << plan.capa;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int i = tid; i < bins; i += kRT) hist[i] = 0;
+    __syncthreads();
+    const uint32_t tb = blockIdx.x;
+    if (tb < tile_b[bins_a]) {
+        const uint32_t a = bucket_of(tile_b, bins_a, tb);
+        const uint32_t s = a_start[a] + (tb - tile_b[a]) * uint32_t(kTile);
+        const uint32_t e = min(s + uint32_t(kTile), a_start[a + 1]);
+        const int sb = plan.rem - plan.wb;
+        const uint32_t mb = (1u << plan.wb) - 1;
+#pragma unroll
+        for (int i = 0; i < kRI; i++) {
+            uint32_t idx = s + warp * (32 * kRI) + i * 32 + lane;
+            if (idx < e) {
+                uint64_t kr = rem_key(rec[idx], WIDE ? hi[idx] : 0u);
+                atomicAdd(&hist[uint32_t(kr >> sb) & mb], 1u);
+            }
+        }
+    }
+    __syncthreads();
+    uint32_t* row = rows + size_t(tb) * bins;
+    for (int i = tid; i < bins; i += kRT) row[i] = hist[i];
+}
+
+// fine_start[(a << wb) + b] = first record of the (a, b) bin; one CTA per a.
+// rows hold the exclusive column prefix P over ALL B tiles (totals in row n_rows).
+__global__ void __launch_bounds__(1024)
+fine_tables_kernel(const uint32_t* __restrict__ rows, MsdPlan plan,
+                   const uint32_t* __restrict__ a_start,
+                   const uint32_t* __restrict__ tile_b, uint32_t* __restrict__ fine_start) {
+    __shared__ uint32_t tmp[32];
+    const int bins = blockDim.x, b = threadIdx.x;
+    const uint32_t a = blockIdx.x;
+    const uint32_t t0 = tile_b[a], t1 = tile_b[a + 1];
+    const uint32_t c = rows[size_t(t1) * bins + b] - rows[size_t(t0) * bins + b];
+    const uint32_t s = block_excl_scan(c, tmp, nullptr);
+    if (b < (1 << plan.wb)) fine_start[(a << plan.wb) + b] = a_start[a] + s;
+    if (a == gridDim.x - 1 && b == 0) {
+        fine_start[gridDim.x << plan.wb] = a_start[gridDim.x];
+    }
+}
+
+// ---- pass B: partition every A bucket by the next wb bits ------------------------------
+template <int CAPBITS, bool WIDE>
+__global__ void __launch_bounds__(kRT, 2)
+pass_b_kernel(const uint64_t* __restrict__ in_rec, const uint32_t* __restrict__ in_hi,
+              MsdPlan plan, const uint32_t* __restrict__ a_start,
+              const uint32_t* __restrict__ tile_b, const uint32_t* __restrict__ rows,
+              const uint32_t* __restrict__ fine_start,
+              uint64_t* __restrict__ out_rec, uint32_t* __restrict__ out_hi) {
+    extern __shared__ __align__(16) unsigned char raw[];
+    using Smem = PassSmem<CAPBITS, WIDE>;
+    Smem& sm = *reinterpret_cast<Smem*>(raw);
+    constexpr int BINS = Smem::BINS;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int bins_a = 1 << plan.capa;
+    const uint32_t tb = blockIdx.x;
+    if (tb >= tile_b[bins_a]) return;
+    const uint32_t a = bucket_of(tile_b, bins_a, tb);
+    const uint32_t t0 = tile_b[a];
+    const uint32_t s = a_start[a] + (tb - t0) * uint32_t(kTile);
+    const uint32_t e = min(s + uint32_t(kTile), a_start[a + 1]);
+    const int sb = plan.rem - plan.wb;
+    const uint32_t mb = (1u << plan.wb) - 1;
+    uint64_t rec[kRI];
+    uint32_t hi[kRI], digit[kRI], slot[kRI];
+#pragma unroll
+    for (int i = 0; i < kRI; i++) {
+        uint32_t idx = s + warp * (32 * kRI) + i * 32 + lane;
+        bool in = idx < e;
+        rec[i] = in ? in_rec[idx] : 0ull;
+        hi[i] = (WIDE && in) ? in_hi[idx] : 0u;
+    }
+#pragma unroll
+    for (int i = 0; i < kRI; i++) {
+        uint32_t idx = s + warp * (32 * kRI) + i * 32 + lane;
+        digit[i] = idx < e ? (uint32_t(rem_key(rec[i], hi[i]) >> sb) & mb)
+                           : uint32_t(BINS);
+    }
+    const uint32_t first = s + warp * (32 * kRI);
+    const int rounds = first >= e ? 0 : int(min(uint32_t(kRI), (e - first + 31) / 32));
+    uint32_t c0, c1;
+    tile_rank<CAPBITS>(sm.rk, digit, rounds, slot, c0, c1);
+    const uint32_t* row = rows + size_t(tb) * BINS;
+    const uint32_t* row0 = rows + size_t(t0) * BINS;
+    const uint32_t* fs = fine_start + (a << plan.wb);
+    if (BINS > kRT) {
+#pragma unroll
+        for (int q = 0; q < 2; q++) {
+            int d = 2 * tid + q;
+            sm.bin_base[d] = d <= int(mb) ? fs[d] + row[d] - row0[d] - sm.rk.tile_off[d]
+                                          : 0u;
+        }
+    } else if (tid < BINS) {
+        sm.bin_base[tid] = tid <= int(mb)
+                           ? fs[tid] + row[tid] - row0[tid] - sm.rk.tile_off[tid] : 0u;
+    }
+#pragma unroll
+    for (int i = 0; i < kRI; i++) {
+        if (digit[i] < BINS) {
+            sm.rec[slot[i]] = rec[i];
+            if (WIDE) sm.hi[slot[i]] = hi[i];
+        }
+    }
+    __syncthreads();
+    const uint32_t total = sm.rk.total;
+#pragma unroll
+    for (int i = 0; i < kRI; i++) {
+        uint32_t j = tid + i * kRT;
+        if (j < total) {
+            uint64_t r = sm.rec[j];
+            uint32_t h = WIDE ? sm.hi[j] : 0u;
+            uint32_t idx = sm.bin_base[uint32_t(rem_key(r, h) >> sb) & mb] + j;
+            out_rec[idx] = r;
+            if (WIDE) out_hi[idx] = h;
+        }
+    }
+}
+
+void scan_rows(uint32_t* rows, uint32_t n_rows, int bins, uint32_t* blk,
+               cudaStream_t s) {
+    const uint32_t n_blk = (n_rows + kScanRows - 1) / kScanRows;
+    scan_rows_sum_kernel<<<n_blk, bins, 0, s>>>(rows, n_rows, blk);
+    scan_rows_blk_kernel<<<1, bins, 0, s>>>(blk, n_blk, rows + size_t(n_rows) * bins);
+}
+
+void apply_rows(uint32_t* rows, uint32_t n_rows, int bins, const uint32_t* blk,
+                const uint32_t* add, cudaStream_t s) {
+    const uint32_t n_blk = (n_rows + kScanRows - 1) / kScanRows;
+    scan_rows_apply_kernel<<<n_blk, bins, 0, s>>>(rows, n_rows, blk, add);
+}
+
+template <typename K>
+void set_smem(K kernel, size_t bytes) {
+    cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                         int(bytes));
+}
+
+}  // namespace
+
+size_t msd_rows_needed(const MsdPlan& plan, uint64_t n_padded, uint64_t max_records) {
+    const size_t ta = size_t(n_padded / kTile);
+    const size_t tb = size_t((max_records + kTile - 1) / kTile) + (size_t(1) << plan.capa);
+    const size_t wa = (ta + 1) << plan.capa, wb = (tb + 1) << plan.capb;
+    return wa > wb ? wa : wb;  // u32 words
+}
+
+size_t msd_blk_needed(const MsdPlan& plan, uint64_t n_padded, uint64_t max_records) {
+    const size_t ta = size_t(n_padded / kTile);
+    const size_t tb = size_t((max_records + kTile - 1) / kTile) + (size_t(1) << plan.capa);
+    const size_t wa = ((ta + kScanRows - 1) / kScanRows + 1) << plan.capa;
+    const size_t wb = ((tb + kScanRows - 1) / kScanRows + 1) << plan.capb;
+    return wa > wb ? wa : wb;
+}
+
+// genome -> records sorted by (A, B), stable.  The sorted records end in
+// b.rec[1] / b.hi[1]; b.fine_start, b.a_start and b.win describe them.
+void launch_msd_partition(const MsdPlan& plan, const uint32_t* packed,
+                          const uint32_t* nmask, uint64_t n_padded,
+                          uint64_t max_records, const MsdBuffers& b,
+                          uint32_t* counters, cudaStream_t s, cudaEvent_t* ev,
+                          uint32_t* launches) {
+    const uint32_t tiles_a = uint32_t(n_padded / kTile);
+    if (tiles_a == 0) return;
+    const int bins_a = 1 << plan.capa, bins_b = 1 << plan.capb;
+    count_a_kernel<<<tiles_a, kRT, sizeof(GenomeStage) + bins_a * 4, s>>>(
+        packed, nmask, plan, b.rows);
+    scan_rows(b.rows, tiles_a, bins_a, b.blk, s);
+    a_tables_kernel<<<1, bins_a, 0, s>>>(b.rows + size_t(tiles_a) * bins_a, b.a_start,
+                                         b.tile_b, b.win, counters);
+    apply_rows(b.rows, tiles_a, bins_a, b.blk, b.a_start, s);
+    *launches += 5;
+    if (ev) cudaEventRecord(ev[0], s);
+#define NPGE_PASS_A(CB, W)                                                         \
+    do {                                                                           \
+        set_smem(pass_a_kernel<CB, W>, sizeof(PassSmem<CB, W>));                   \
+        pass_a_kernel<CB, W><<<tiles_a, kRT, sizeof(PassSmem<CB, W>), s>>>(        \
+            packed, nmask, plan, b.rows, b.rec[0], b.hi[0]);                       \
+    } while (0)
+    if (plan.capa == 8) {
+        if (plan.wide) NPGE_PASS_A(8, true); else NPGE_PASS_A(8, false);
+    } else {
+        if (plan.wide) NPGE_PASS_A(10, true); else NPGE_PASS_A(10, false);
+    }
+#undef NPGE_PASS_A
+    *launches += 1;
+    if (ev) cudaEventRecord(ev[1], s);
+    const uint32_t tiles_b = uint32_t((max_records + kTile - 1) / kTile) + (1u << plan.capa);
+    if (plan.wide) {
+        count_b_kernel<true><<<tiles_b, kRT, bins_b * 4, s>>>(
+            b.rec[0], b.hi[0], plan, b.a_start, b.tile_b, b.rows);
+    } else {
+        count_b_kernel<false><<<tiles_b, kRT, bins_b * 4, s>>>(
+            b.rec[0], b.hi[0], plan, b.a_start, b.tile_b, b.rows);
+    }
+    scan_rows(b.rows, tiles_b, bins_b, b.blk, s);
+    apply_rows(b.rows, tiles_b, bins_b, b.blk, nullptr, s);
+    fine_tables_kernel<<<bins_a, bins_b, 0, s>>>(b.rows, plan, b.a_start, b.tile_b,
+                                                 b.fine_start);
+    *launches += 5;
+    if (ev) cudaEventRecord(ev[2], s);
+#define NPGE_PASS_B(CB, W)                                                         \
+    do {                                                                           \
+        set_smem(pass_b_kernel<CB, W>, sizeof(PassSmem<CB, W>));                   \
+        pass_b_kernel<CB, W><<<tiles_b, kRT, sizeof(PassSmem<CB, W>), s>>>(        \
+            b.rec[0], b.hi[0], plan, b.a_start, b.tile_b, b.rows, b.fine_start,    \
+            b.rec[1], b.hi[1]);                                                    \
+    } while (0)
+    if (plan.capb == 8) {
+        if (plan.wide) NPGE_PASS_B(8, true); else NPGE_PASS_B(8, false);
+    } else {
+        if (plan.wide) NPGE_PASS_B(10, true); else NPGE_PASS_B(10, false);
+    }
+#undef NPGE_PASS_B
+    *launches += 1;
+    if (ev) cudaEventRecord(ev[3], s);
+}
+
+}  // namespace npge_b200
