@@ -312,7 +312,6 @@ int find_device_msd(npge_anchor_ctx* ctx, const npge_anchor_params* p,
     NPGE_CUDA(cudaEventRecord(ctx->ev[0], st));
     NPGE_CUDA(cudaMemsetAsync(ctx->counters.ptr, 0, kCntWords * 4, st));
     NPGE_CUDA(cudaMemsetAsync(ctx->summary.ptr, 0, summary_words * 8, st));
-    NPGE_CUDA(cudaMemsetAsync(ctx->bstatus.ptr, 0, size_t(max_win + 1) * 8, st));
     if (similar) {
         NPGE_CUDA(cudaMemsetAsync(ctx->found_bits.ptr, 0, np / 8 + 256, st));
         NPGE_CUDA(cudaMemsetAsync(ctx->sel.ptr, 0, max_records + 16, st));
@@ -360,9 +359,9 @@ int find_device_msd(npge_anchor_ctx* ctx, const npge_anchor_params* p,
     a.r_ori = ptr<int8_t>(ctx->r_ori);
     a.r_block_off = ptr<uint64_t>(ctx->r_block_off);
     a.r_block_hash = ptr<uint64_t>(ctx->r_block_hash);
-    a.status = ptr<uint64_t>(ctx->bstatus);
+    a.unit_tot = ptr<uint64_t>(ctx->bstatus);
     a.summary = ptr<uint64_t>(ctx->summary);
-    launch_bucket(a, similar, np ? max_records : 0, st, &launches);
+    launch_bucket(a, similar, np ? max_records : 0, st, &ctx->ev[4], &launches);
     NPGE_CUDA(cudaGetLastError());
     NPGE_CUDA(cudaEventRecord(ctx->ev[3], st));
     uint64_t summary[kSumWords];
@@ -382,11 +381,13 @@ int find_device_msd(npge_anchor_ctx* ctx, const npge_anchor_params* p,
     s.digest[1] = summary[kSumDigest1];
     s.radix_passes = uint32_t(2 + plan.smem_passes);
     s.gpu_launches = launches;
-    // stages: [count A + scan] [pass A] [count B + scan] [pass B] [bucket sort + emit]
+    // stages: [count A + scan] [pass A] [count B + scan] [pass B] [bucket sort] [emit]
     cudaEventElapsedTime(&s.ms_hist, ctx->ev[0], ctx->ev_pass[0]);
     cudaEventElapsedTime(&s.ms_pass[0], ctx->ev_pass[0], ctx->ev_pass[1]);
     cudaEventElapsedTime(&s.ms_pass[1], ctx->ev_pass[1], ctx->ev_pass[2]);
     cudaEventElapsedTime(&s.ms_pass[2], ctx->ev_pass[2], ctx->ev_pass[3]);
+    cudaEventElapsedTime(&s.ms_pass[3], ctx->ev[2], ctx->ev[4]);  // bucket sort
+    cudaEventElapsedTime(&s.ms_pass[4], ctx->ev[4], ctx->ev[3]);  // scan + emit
     cudaEventElapsedTime(&s.ms_sort, ctx->ev[0], ctx->ev[2]);
     cudaEventElapsedTime(&s.ms_group, ctx->ev[2], ctx->ev[3]);
     cudaEventElapsedTime(&s.ms_total, ctx->ev[0], ctx->ev[3]);

@@ -3,9 +3,9 @@
 // kWindow records, at most kBucketCap records unless a bin is oversized), sorts
 // it by the remaining key bits with an LSD radix sort in shared memory (byte
 // digits, stable), finds the runs of equal canonical k-mers and writes the
-// anchor fragments and blocks.  Units are taken in ticket order, so a warp-wide
-// decoupled look-back over one 64-bit word per unit gives every unit its output
-// offsets and the result comes out in ascending (k-mer, position) order.
+// anchor fragments and blocks.  Three launches, no CTA ever waits on another:
+// sort (+ count) -> scan of the per-unit totals -> emit from the sorted units, so
+// the result comes out in ascending (k-mer, position) order.
 //
 // Replaces fragmenttg_postprocess (src/algo/AnchorFinder.cpp:356-391): the
 // linear pass that opens a Block the first time a hash repeats,
@@ -24,21 +24,8 @@ namespace npge_b200 {
 namespace {
 
 constexpr int kCap = kBucketCap;
-constexpr uint64_t kSFlagAggregate = 1ull << 62;
-constexpr uint64_t kSFlagInclusive = 2ull << 62;
-constexpr uint64_t kSValueMask = (1ull << 62) - 1;
 constexpr int kPartials = 64;
-// scan value: blocks << 31 | fragments (both < 2^31)
-
-__device__ __forceinline__ uint64_t ld_relaxed64(const uint64_t* p) {
-    uint64_t v;
-    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-    return v;
-}
-
-__device__ __forceinline__ void st_relaxed64(uint64_t* p, uint64_t v) {
-    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
+// unit totals and prefixes: blocks << 31 | fragments (both < 2^31)
 
 __device__ __forceinline__ uint64_t rem_key(uint64_t rec, uint32_t hi) {
     return (uint64_t(hi) << 32) | (rec >> 32);
@@ -88,10 +75,9 @@ struct __align__(16) BucketSmem {
     uint64_t warp_tot[kRW];
     int32_t warp_head[kRW];
     uint64_t red[3][kRW];
-    uint64_t prefix;          // look-back result
-    uint64_t chunk_tot;
-    uint32_t ticket;
-    uint32_t cut;             // 1 + unit index of the record with rank M-1
+    uint32_t carry;           // slow path: head of the group entering a chunk
+    uint32_t u_s, u_n, u_ab;  // the CTA's unit: first record, size, A bucket
+    uint32_t cut;             // set by the thread that wrote the record of rank M-1
 };
 
 // One sorted chunk of a unit in shared memory: records at K[1 .. cn], halo
@@ -291,56 +277,6 @@ __device__ __forceinline__ void unit_write(BucketSmem<WIDE>& sm, const Chunk<WID
 }
 
 
-// Warp-wide decoupled look-back over the units before `w` (one 64-bit status
-// word per unit).  Leaves the exclusive prefix in sm.prefix.  Contains a barrier.
-template <bool WIDE>
-__device__ __forceinline__ void unit_lookback(BucketSmem<WIDE>& sm, const BucketArgs& a,
-                                              uint32_t w, uint32_t n_win, uint64_t tot) {
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    if (warp == 0) {
-        uint64_t prefix = 0;
-        if (w == 0) {
-            if (lane == 0) st_relaxed64(a.status, kSFlagInclusive | tot);
-        } else {
-            if (lane == 0) st_relaxed64(a.status + w, kSFlagAggregate | tot);
-            int64_t j = int64_t(w) - 1;
-            while (true) {
-                const int64_t idx = j - lane;
-                const uint64_t v = idx >= 0 ? ld_relaxed64(a.status + idx)
-                                            : kSFlagInclusive;
-                const uint32_t fl = uint32_t(v >> 62);
-                const uint32_t inc = __ballot_sync(0xffffffffu, fl == 2);
-                const uint32_t nr = __ballot_sync(0xffffffffu, fl == 0);
-                uint64_t x = v & kSValueMask;
-                bool last = false;
-                if (inc) {
-                    const int L = __ffs(inc) - 1;
-                    if (nr & ((2u << L) - 1)) continue;  // a nearer unit is not ready
-                    if (lane > L) x = 0;
-                    last = true;
-                } else if (nr) {
-                    continue;
-                }
-#pragma unroll
-                for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
-                prefix += x;
-                if (last) break;
-                j -= 32;
-            }
-            if (lane == 0) st_relaxed64(a.status + w, kSFlagInclusive | (prefix + tot));
-        }
-        if (lane == 0) {
-            sm.prefix = prefix;
-            if (w + 1 == n_win) {  // last unit: totals before truncation
-                const uint64_t all = prefix + tot;
-                a.summary[kSumFragments] = all & 0x7fffffffull;
-                a.summary[kSumBlocks] = all >> 31;
-            }
-        }
-    }
-    __syncthreads();
-}
-
 // head of the group of sorted record `i` (key == key of record i) inside
 // [lo_bound, i]: gallop back, then binary search (keys ascending)
 template <bool WIDE>
@@ -405,269 +341,379 @@ __device__ __forceinline__ void flush_digest(BucketSmem<WIDE>& sm, const BucketA
     }
 }
 
-// MODE 0: sort + parity/exact emit.  MODE 1 (anchor-similar, first launch): sort,
-// set the found bits, write the sorted unit back.  MODE 2 (second launch): the
-// unit is already sorted; candidate rule + emit.
-template <bool WIDE, int MODE>
-__global__ void __launch_bounds__(kRT, 2)
-bucket_kernel(BucketArgs a) {
-    extern __shared__ __align__(16) unsigned char raw[];
-    BucketSmem<WIDE>& sm = *reinterpret_cast<BucketSmem<WIDE>*>(raw);
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (tid == 0) {
-        sm.ticket = atomicAdd(a.counters + kCntScanTicket + MODE, 1u);
+// The unit of window w: thread 0 searches the tables, everybody gets (s, n, ab).
+// False when w is past the last window.  Contains a barrier.
+template <bool WIDE>
+__device__ __forceinline__ bool unit_of_window(BucketSmem<WIDE>& sm, const BucketArgs& a,
+                                               uint32_t w, uint32_t& s, uint32_t& n,
+                                               uint64_t& key_hi) {
+    if (w >= a.counters[kCntWindows]) return false;
+    if (threadIdx.x == 0) {
+        const MsdPlan& pl = a.plan;
+        const uint32_t ab = bucket_of(a.win, 1u << pl.capa, w);
+        const uint32_t lo_pos = a.a_start[ab] + (w - a.win[ab]) * uint32_t(kWindow);
+        const uint32_t hi_pos = min(lo_pos + uint32_t(kWindow), a.a_start[ab + 1]);
+        const uint32_t* fs = a.fine_start + (size_t(ab) << pl.wb);
+        const uint32_t f0 = lower_bound_u32(fs, 1u << pl.wb, lo_pos);
+        const uint32_t f1 = lower_bound_u32(fs, 1u << pl.wb, hi_pos);
+        sm.u_s = fs[f0];
+        sm.u_n = fs[f1] - fs[f0];
+        sm.u_ab = ab;
         sm.cut = 0;
     }
     __syncthreads();
-    const uint32_t w = sm.ticket;
-    const uint32_t n_win = a.counters[kCntWindows];
-    if (w >= n_win) return;
-    const MsdPlan& pl = a.plan;
-    const uint32_t bins_a = 1u << pl.capa;
-    const uint32_t ab = bucket_of(a.win, bins_a, w);
-    const uint32_t lo_pos = a.a_start[ab] + (w - a.win[ab]) * uint32_t(kWindow);
-    const uint32_t hi_pos = min(lo_pos + uint32_t(kWindow), a.a_start[ab + 1]);
-    const uint32_t* fs = a.fine_start + (size_t(ab) << pl.wb);
-    const uint32_t f0 = lower_bound_u32(fs, 1u << pl.wb, lo_pos);
-    const uint32_t f1 = lower_bound_u32(fs, 1u << pl.wb, hi_pos);
-    const uint32_t s = fs[f0], n = fs[f1] - s;
-    const uint64_t key_hi = uint64_t(ab) << pl.rem;
-    Digest dg;
-    auto digit_at = [&](uint64_t r, uint32_t h, int shift) {
-        return uint32_t(rem_key(r, h) >> shift) & 255u;
-    };
-    if (n <= uint32_t(kCap)) {
-        // ---- fast path: the whole unit in shared memory ---------------------------
+    s = sm.u_s;
+    n = sm.u_n;
+    key_hi = uint64_t(sm.u_ab) << a.plan.rem;
+    return true;
+}
+
+__device__ __forceinline__ uint32_t digit_at(uint64_t r, uint32_t h, int shift) {
+    return uint32_t(rem_key(r, h) >> shift) & 255u;
+}
+
+// Loads the unit (n <= kCap) into sm.buf[0][1..n].  Contains a barrier.
+template <bool WIDE>
+__device__ __forceinline__ void load_unit(BucketSmem<WIDE>& sm, const BucketArgs& a,
+                                          uint32_t s, uint32_t n) {
+#pragma unroll
+    for (int i = 0; i < kRI; i++) {
+        const uint32_t j = item_index(i);
+        if (j < n) {
+            sm.buf[0][1 + j] = a.rec_w[s + j];
+            if (WIDE) sm.hib[0][1 + j] = a.hi_w[s + j];
+        }
+    }
+    __syncthreads();
+}
+
+template <bool WIDE>
+__device__ __forceinline__ void store_unit(BucketSmem<WIDE>& sm, const BucketArgs& a,
+                                           uint32_t s, uint32_t n, int cur) {
+#pragma unroll
+    for (int i = 0; i < kRI; i++) {
+        const uint32_t j = item_index(i);
+        if (j < n) {
+            a.rec_w[s + j] = sm.buf[cur][1 + j];
+            if (WIDE) a.hi_w[s + j] = sm.hib[cur][1 + j];
+        }
+    }
+}
+
+// LSD radix sort of sm.buf[0][1..n] by the low `rem` key bits, byte digits,
+// stable.  Returns the buffer holding the result.  Contains barriers.
+template <bool WIDE>
+__device__ __forceinline__ int sort_unit_smem(BucketSmem<WIDE>& sm, const MsdPlan& pl,
+                                              uint32_t n) {
+    const int warp = threadIdx.x >> 5;
+    const uint32_t first = warp * (32 * kRI);
+    const int rounds = first >= n ? 0 : int(min(uint32_t(kRI), (n - first + 31) / 32));
+    int cur = 0;
+#pragma unroll 1
+    for (int pass = 0; pass < pl.smem_passes; pass++) {
+        uint64_t rec[kRI];
+        uint32_t hi[kRI], digit[kRI], slot[kRI];
 #pragma unroll
         for (int i = 0; i < kRI; i++) {
             const uint32_t j = item_index(i);
-            if (j < n) {
-                sm.buf[0][1 + j] = a.rec_w[s + j];
-                if (WIDE) sm.hib[0][1 + j] = a.hi_w[s + j];
+            const bool in = j < n;
+            rec[i] = in ? sm.buf[cur][1 + j] : 0ull;
+            hi[i] = (WIDE && in) ? sm.hib[cur][1 + j] : 0u;
+            digit[i] = in ? digit_at(rec[i], hi[i], 8 * pass) : 256u;
+        }
+        uint32_t c0, c1;
+        tile_rank<8>(sm.rk, digit, rounds, slot, c0, c1);
+#pragma unroll
+        for (int i = 0; i < kRI; i++) {
+            if (digit[i] < 256u) {
+                sm.buf[cur ^ 1][1 + slot[i]] = rec[i];
+                if (WIDE) sm.hib[cur ^ 1][1 + slot[i]] = hi[i];
             }
         }
         __syncthreads();
-        int cur = 0;
-        if (MODE != 2) {
-            const uint32_t first = warp * (32 * kRI);
-            const int rounds = first >= n ? 0 : int(min(uint32_t(kRI), (n - first + 31) / 32));
-#pragma unroll 1
-            for (int pass = 0; pass < pl.smem_passes; pass++) {
-                uint64_t rec[kRI];
-                uint32_t hi[kRI], digit[kRI], slot[kRI];
-#pragma unroll
-                for (int i = 0; i < kRI; i++) {
-                    const uint32_t j = item_index(i);
-                    const bool in = j < n;
-                    rec[i] = in ? sm.buf[cur][1 + j] : 0ull;
-                    hi[i] = (WIDE && in) ? sm.hib[cur][1 + j] : 0u;
-                    digit[i] = in ? digit_at(rec[i], hi[i], 8 * pass) : 256u;
-                }
-                uint32_t c0, c1;
-                tile_rank<8>(sm.rk, digit, rounds, slot, c0, c1);
-#pragma unroll
-                for (int i = 0; i < kRI; i++) {
-                    if (digit[i] < 256u) {
-                        sm.buf[cur ^ 1][1 + slot[i]] = rec[i];
-                        if (WIDE) sm.hib[cur ^ 1][1 + slot[i]] = hi[i];
-                    }
-                }
-                __syncthreads();
-                cur ^= 1;
-            }
-        }
-        Chunk<WIDE> ch;
-        ch.rec = sm.buf[cur];
-        ch.hi = sm.hib[cur];
-        ch.cn = n;
-        ch.has_prev = ch.has_next = false;
-        ch.g0 = s;
-        ch.carry_head = s;
-        uint32_t valid, preveq, inb, sel;
-        unit_flags<WIDE>(ch, valid, preveq, inb);
-        auto write_back = [&]() {
-#pragma unroll
-            for (int i = 0; i < kRI; i++) {
-                const uint32_t j = item_index(i);
-                if (j < n) {
-                    a.rec_w[s + j] = sm.buf[cur][1 + j];
-                    if (WIDE) a.hi_w[s + j] = sm.hib[cur][1 + j];
-                }
-            }
-        };
-        if (MODE == 1) {
-            mark_found<WIDE>(ch, a, key_hi, preveq);
-            write_back();
-            return;
-        }
-        const uint64_t tot =
-            unit_select<WIDE, MODE>(sm, ch, a, key_hi, valid, preveq, inb, sel);
-        unit_lookback<WIDE>(sm, a, w, n_win, tot);
-        unit_write<WIDE>(sm, ch, a, key_hi, preveq, sel, sm.prefix, dg);
-        __syncthreads();
-        if (sm.cut) {
-            if (MODE == 0) write_back();
-            if (tid == 0) {
-                a.counters[kCntCutStart] = s;
-                a.counters[kCntCutSize] = n;
-            }
-        }
-        flush_digest<WIDE>(sm, a, w, dg);
-        return;
+        cur ^= 1;
     }
-    // ---- slow path: an oversized unit, chunk by chunk through global memory -----
+    return cur;
+}
+
+// Oversized unit: the same passes chunk by chunk through global memory, ping-pong
+// between the unit's own range and the same range of the scratch buffer.
+template <bool WIDE>
+__device__ void sort_unit_global(BucketSmem<WIDE>& sm, const BucketArgs& a, uint32_t s,
+                                 uint32_t n) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const MsdPlan& pl = a.plan;
     uint64_t* src = a.rec_w;
     uint32_t* srch = a.hi_w;
     uint64_t* dst = a.scratch_rec;
     uint32_t* dsth = a.scratch_hi;
-    if (MODE != 2) {
 #pragma unroll 1
-        for (int pass = 0; pass < pl.smem_passes; pass++) {
-            const int shift = 8 * pass;
-            if (tid < 256) sm.grun[tid] = 0;
-            __syncthreads();
-            for (uint32_t x = tid; x < n; x += kRT) {
-                atomicAdd(&sm.grun[digit_at(src[s + x], WIDE ? srch[s + x] : 0u, shift)], 1u);
-            }
-            __syncthreads();
-            {   // exclusive scan of the 256 digit counts (warps 0..7 hold them)
-                uint32_t v = tid < 256 ? sm.grun[tid] : 0u;
-                uint32_t incl = v;
-#pragma unroll
-                for (int o = 1; o < 32; o <<= 1) {
-                    uint32_t u = __shfl_up_sync(0xffffffffu, incl, o);
-                    if (lane >= o) incl += u;
-                }
-                if (lane == 31) sm.rk.scan_tmp[warp] = incl;
-                __syncthreads();
-                uint32_t base = 0;
-                for (int x = 0; x < warp; x++) base += sm.rk.scan_tmp[x];
-                if (tid < 256) sm.grun[tid] = base + incl - v;
-                __syncthreads();
-            }
-#pragma unroll 1
-            for (uint32_t c0 = 0; c0 < n; c0 += kCap) {
-                const uint32_t cn = min(uint32_t(kCap), n - c0);
-                uint64_t rec[kRI];
-                uint32_t hi[kRI], digit[kRI], slot[kRI];
-#pragma unroll
-                for (int i = 0; i < kRI; i++) {
-                    const uint32_t j = item_index(i);
-                    const bool in = j < cn;
-                    rec[i] = in ? src[s + c0 + j] : 0ull;
-                    hi[i] = (WIDE && in) ? srch[s + c0 + j] : 0u;
-                    digit[i] = in ? digit_at(rec[i], hi[i], shift) : 256u;
-                }
-                const uint32_t first = warp * (32 * kRI);
-                const int rounds =
-                    first >= cn ? 0 : int(min(uint32_t(kRI), (cn - first + 31) / 32));
-                uint32_t cnt0, cnt1;
-                tile_rank<8>(sm.rk, digit, rounds, slot, cnt0, cnt1);
-#pragma unroll
-                for (int i = 0; i < kRI; i++) {
-                    if (digit[i] < 256u) {
-                        sm.buf[0][slot[i]] = rec[i];
-                        if (WIDE) sm.hib[0][slot[i]] = hi[i];
-                    }
-                }
-                __syncthreads();
-#pragma unroll
-                for (int i = 0; i < kRI; i++) {
-                    const uint32_t j = tid + i * kRT;
-                    if (j < cn) {
-                        const uint64_t r = sm.buf[0][j];
-                        const uint32_t h = WIDE ? sm.hib[0][j] : 0u;
-                        const uint32_t d = digit_at(r, h, shift);
-                        const uint32_t at = s + sm.grun[d] + j - sm.rk.tile_off[d];
-                        dst[at] = r;
-                        if (WIDE) dsth[at] = h;
-                    }
-                }
-                __syncthreads();
-                if (tid < 256) sm.grun[tid] += cnt0;
-                __syncthreads();
-            }
-            uint64_t* t = src; src = dst; dst = t;
-            uint32_t* th = srch; srch = dsth; dsth = th;
-        }
-        if (src != a.rec_w) {  // odd number of passes: bring the unit home
-            for (uint32_t x = tid; x < n; x += kRT) {
-                a.rec_w[s + x] = src[s + x];
-                if (WIDE) a.hi_w[s + x] = srch[s + x];
-            }
-            __syncthreads();
-        }
-    }
-    const uint64_t* X = a.rec_w;
-    const uint32_t* XH = a.hi_w;
-    Chunk<WIDE> ch;
-    auto load_chunk = [&](uint32_t c0) {
-        const uint32_t cn = min(uint32_t(kCap), n - c0);
-        __syncthreads();  // the previous chunk is no longer read
-#pragma unroll
-        for (int i = 0; i < kRI; i++) {
-            const uint32_t j = item_index(i);
-            if (j < cn) {
-                sm.buf[0][1 + j] = X[s + c0 + j];
-                if (WIDE) sm.hib[0][1 + j] = XH[s + c0 + j];
-            }
-        }
-        if (tid == 0) {
-            sm.chunk_tot = s + c0;  // carry head, unless the group started earlier
-            if (c0 > 0) {
-                sm.buf[0][0] = X[s + c0 - 1];
-                if (WIDE) sm.hib[0][0] = XH[s + c0 - 1];
-                const uint64_t k0 = rem_key(X[s + c0 - 1], WIDE ? XH[s + c0 - 1] : 0u);
-                const uint64_t k1 = rem_key(X[s + c0], WIDE ? XH[s + c0] : 0u);
-                if (k0 == k1) {
-                    sm.chunk_tot = find_head_global<WIDE>(X, XH, s, s + c0 - 1, k0);
-                }
-            }
-            if (c0 + cn < n) {
-                sm.buf[0][cn + 1] = X[s + c0 + cn];
-                if (WIDE) sm.hib[0][cn + 1] = XH[s + c0 + cn];
-            }
+    for (int pass = 0; pass < pl.smem_passes; pass++) {
+        const int shift = 8 * pass;
+        __syncthreads();
+        if (tid < 256) sm.grun[tid] = 0;
+        __syncthreads();
+        for (uint32_t x = tid; x < n; x += kRT) {
+            atomicAdd(&sm.grun[digit_at(src[s + x], WIDE ? srch[s + x] : 0u, shift)], 1u);
         }
         __syncthreads();
-        ch.rec = sm.buf[0];
-        ch.hi = sm.hib[0];
-        ch.cn = cn;
-        ch.has_prev = c0 > 0;
-        ch.has_next = c0 + cn < n;
-        ch.g0 = s + c0;
-        ch.carry_head = uint32_t(sm.chunk_tot);
-    };
-    uint32_t valid, preveq, inb, sel;
-    if (MODE == 1) {
-        for (uint32_t c0 = 0; c0 < n; c0 += kCap) {
-            load_chunk(c0);
-            unit_flags<WIDE>(ch, valid, preveq, inb);
-            mark_found<WIDE>(ch, a, key_hi, preveq);
+        {   // exclusive scan of the 256 digit counts (warps 0..7 hold them)
+            uint32_t v = tid < 256 ? sm.grun[tid] : 0u;
+            uint32_t incl = v;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                uint32_t u = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += u;
+            }
+            if (lane == 31) sm.rk.scan_tmp[warp] = incl;
+            __syncthreads();
+            uint32_t base = 0;
+            for (int x = 0; x < warp; x++) base += sm.rk.scan_tmp[x];
+            __syncthreads();
+            if (tid < 256) sm.grun[tid] = base + incl - v;
+            __syncthreads();
         }
-        return;
-    }
-    uint64_t tot = 0;
-    for (int sweep = (MODE == 2 ? 0 : 1); sweep < 2; sweep++) {
-        // sweep 0 (anchor-similar): let every candidate mark its group first
-        tot = 0;
+#pragma unroll 1
         for (uint32_t c0 = 0; c0 < n; c0 += kCap) {
-            load_chunk(c0);
-            unit_flags<WIDE>(ch, valid, preveq, inb);
-            tot += unit_select<WIDE, MODE>(sm, ch, a, key_hi, valid, preveq, inb, sel);
+            const uint32_t cn = min(uint32_t(kCap), n - c0);
+            uint64_t rec[kRI];
+            uint32_t hi[kRI], digit[kRI], slot[kRI];
+#pragma unroll
+            for (int i = 0; i < kRI; i++) {
+                const uint32_t j = item_index(i);
+                const bool in = j < cn;
+                rec[i] = in ? src[s + c0 + j] : 0ull;
+                hi[i] = (WIDE && in) ? srch[s + c0 + j] : 0u;
+                digit[i] = in ? digit_at(rec[i], hi[i], shift) : 256u;
+            }
+            const uint32_t first = warp * (32 * kRI);
+            const int rounds =
+                first >= cn ? 0 : int(min(uint32_t(kRI), (cn - first + 31) / 32));
+            uint32_t cnt0, cnt1;
+            tile_rank<8>(sm.rk, digit, rounds, slot, cnt0, cnt1);
+#pragma unroll
+            for (int i = 0; i < kRI; i++) {
+                if (digit[i] < 256u) {
+                    sm.buf[0][slot[i]] = rec[i];
+                    if (WIDE) sm.hib[0][slot[i]] = hi[i];
+                }
+            }
+            __syncthreads();
+#pragma unroll
+            for (int i = 0; i < kRI; i++) {
+                const uint32_t j = tid + i * kRT;
+                if (j < cn) {
+                    const uint64_t r = sm.buf[0][j];
+                    const uint32_t h = WIDE ? sm.hib[0][j] : 0u;
+                    const uint32_t d = digit_at(r, h, shift);
+                    const uint32_t at = s + sm.grun[d] + j - sm.rk.tile_off[d];
+                    dst[at] = r;
+                    if (WIDE) dsth[at] = h;
+                }
+            }
+            __syncthreads();
+            if (tid < 256) sm.grun[tid] += cnt0;
+            __syncthreads();
         }
+        uint64_t* t = src; src = dst; dst = t;
+        uint32_t* th = srch; srch = dsth; dsth = th;
     }
-    unit_lookback<WIDE>(sm, a, w, n_win, tot);
-    uint64_t base = sm.prefix;
-    for (uint32_t c0 = 0; c0 < n; c0 += kCap) {
-        load_chunk(c0);
-        unit_flags<WIDE>(ch, valid, preveq, inb);
-        const uint64_t t =
-            unit_select<WIDE, MODE>(sm, ch, a, key_hi, valid, preveq, inb, sel);
-        unit_write<WIDE>(sm, ch, a, key_hi, preveq, sel, base, dg);
-        base += t;
+    if (src != a.rec_w) {  // odd number of passes: bring the unit home
+        for (uint32_t x = tid; x < n; x += kRT) {
+            a.rec_w[s + x] = src[s + x];
+            if (WIDE) a.hi_w[s + x] = srch[s + x];
+        }
     }
     __syncthreads();
-    if (sm.cut && tid == 0) {
+}
+
+// Chunk c0 of a sorted oversized unit -> sm.buf[0] with halos.  Contains barriers.
+template <bool WIDE>
+__device__ __forceinline__ void load_chunk(BucketSmem<WIDE>& sm, const BucketArgs& a,
+                                           uint32_t s, uint32_t n, uint32_t c0,
+                                           Chunk<WIDE>& ch) {
+    const uint64_t* X = a.rec_w;
+    const uint32_t* XH = a.hi_w;
+    const uint32_t cn = min(uint32_t(kCap), n - c0);
+    __syncthreads();  // the previous chunk is no longer read
+#pragma unroll
+    for (int i = 0; i < kRI; i++) {
+        const uint32_t j = item_index(i);
+        if (j < cn) {
+            sm.buf[0][1 + j] = X[s + c0 + j];
+            if (WIDE) sm.hib[0][1 + j] = XH[s + c0 + j];
+        }
+    }
+    if (threadIdx.x == 0) {
+        sm.carry = s + c0;
+        if (c0 > 0) {
+            sm.buf[0][0] = X[s + c0 - 1];
+            if (WIDE) sm.hib[0][0] = XH[s + c0 - 1];
+            const uint64_t k0 = rem_key(X[s + c0 - 1], WIDE ? XH[s + c0 - 1] : 0u);
+            const uint64_t k1 = rem_key(X[s + c0], WIDE ? XH[s + c0] : 0u);
+            if (k0 == k1) sm.carry = find_head_global<WIDE>(X, XH, s, s + c0 - 1, k0);
+        }
+        if (c0 + cn < n) {
+            sm.buf[0][cn + 1] = X[s + c0 + cn];
+            if (WIDE) sm.hib[0][cn + 1] = XH[s + c0 + cn];
+        }
+    }
+    __syncthreads();
+    ch.rec = sm.buf[0];
+    ch.hi = sm.hib[0];
+    ch.cn = cn;
+    ch.has_prev = c0 > 0;
+    ch.has_next = c0 + cn < n;
+    ch.g0 = s + c0;
+    ch.carry_head = sm.carry;
+}
+
+template <bool WIDE>
+__device__ __forceinline__ void whole_unit_chunk(BucketSmem<WIDE>& sm, uint32_t s,
+                                                 uint32_t n, int cur, Chunk<WIDE>& ch) {
+    ch.rec = sm.buf[cur];
+    ch.hi = sm.hib[cur];
+    ch.cn = n;
+    ch.has_prev = ch.has_next = false;
+    ch.g0 = s;
+    ch.carry_head = s;
+}
+
+// ---- kernel 1: sort every unit; MODE 0 also counts its anchors, MODE 1
+// (anchor-similar) sets the found bits instead.  The sorted unit is written back.
+template <bool WIDE, int MODE>
+__global__ void __launch_bounds__(kRT, 2)
+bucket_sort_kernel(BucketArgs a) {
+    extern __shared__ __align__(16) unsigned char raw[];
+    BucketSmem<WIDE>& sm = *reinterpret_cast<BucketSmem<WIDE>*>(raw);
+    const uint32_t w = blockIdx.x;
+    uint32_t s, n;
+    uint64_t key_hi;
+    if (!unit_of_window<WIDE>(sm, a, w, s, n, key_hi)) return;
+    Chunk<WIDE> ch;
+    uint32_t valid, preveq, inb, sel;
+    uint64_t tot = 0;
+    if (n <= uint32_t(kCap)) {
+        load_unit<WIDE>(sm, a, s, n);
+        const int cur = sort_unit_smem<WIDE>(sm, a.plan, n);
+        whole_unit_chunk<WIDE>(sm, s, n, cur, ch);
+        unit_flags<WIDE>(ch, valid, preveq, inb);
+        if (MODE == 1) {
+            mark_found<WIDE>(ch, a, key_hi, preveq);
+        } else {
+            tot = unit_select<WIDE, 0>(sm, ch, a, key_hi, valid, preveq, inb, sel);
+        }
+        store_unit<WIDE>(sm, a, s, n, cur);
+    } else {
+        sort_unit_global<WIDE>(sm, a, s, n);
+        for (uint32_t c0 = 0; c0 < n; c0 += kCap) {
+            load_chunk<WIDE>(sm, a, s, n, c0, ch);
+            unit_flags<WIDE>(ch, valid, preveq, inb);
+            if (MODE == 1) {
+                mark_found<WIDE>(ch, a, key_hi, preveq);
+            } else {
+                tot += unit_select<WIDE, 0>(sm, ch, a, key_hi, valid, preveq, inb, sel);
+            }
+        }
+    }
+    if (MODE == 0 && threadIdx.x == 0) a.unit_tot[w] = tot;
+}
+
+// ---- kernel 1b (anchor-similar): candidate rule and count on the sorted units -----
+template <bool WIDE>
+__global__ void __launch_bounds__(kRT, 2)
+bucket_count_kernel(BucketArgs a) {
+    extern __shared__ __align__(16) unsigned char raw[];
+    BucketSmem<WIDE>& sm = *reinterpret_cast<BucketSmem<WIDE>*>(raw);
+    const uint32_t w = blockIdx.x;
+    uint32_t s, n;
+    uint64_t key_hi;
+    if (!unit_of_window<WIDE>(sm, a, w, s, n, key_hi)) return;
+    Chunk<WIDE> ch;
+    uint32_t valid, preveq, inb, sel;
+    uint64_t tot = 0;
+    if (n <= uint32_t(kCap)) {
+        load_unit<WIDE>(sm, a, s, n);
+        whole_unit_chunk<WIDE>(sm, s, n, 0, ch);
+        unit_flags<WIDE>(ch, valid, preveq, inb);
+        tot = unit_select<WIDE, 2>(sm, ch, a, key_hi, valid, preveq, inb, sel);
+    } else {
+        // sweep 0: every candidate marks its group, also across chunk borders
+        for (int sweep = 0; sweep < 2; sweep++) {
+            tot = 0;
+            for (uint32_t c0 = 0; c0 < n; c0 += kCap) {
+                load_chunk<WIDE>(sm, a, s, n, c0, ch);
+                unit_flags<WIDE>(ch, valid, preveq, inb);
+                tot += unit_select<WIDE, 2>(sm, ch, a, key_hi, valid, preveq, inb, sel);
+            }
+        }
+    }
+    if (threadIdx.x == 0) a.unit_tot[w] = tot;
+}
+
+// ---- kernel 2: exclusive scan of the unit totals (one CTA) -------------------------
+__global__ void __launch_bounds__(1024)
+unit_scan_kernel(BucketArgs a) {
+    __shared__ uint64_t part[1024];
+    const uint32_t n_win = a.counters[kCntWindows];
+    const uint32_t per = (n_win + 1023) / 1024;
+    const uint32_t b = threadIdx.x * per, e = min(b + per, n_win);
+    uint64_t sum = 0;
+    for (uint32_t i = b; i < e; i++) sum += a.unit_tot[i];
+    part[threadIdx.x] = sum;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint64_t run = 0;
+        for (int i = 0; i < 1024; i++) {
+            uint64_t v = part[i];
+            part[i] = run;
+            run += v;
+        }
+        a.summary[kSumFragments] = run & 0x7fffffffull;  // before truncation
+        a.summary[kSumBlocks] = run >> 31;
+    }
+    __syncthreads();
+    uint64_t run = part[threadIdx.x];
+    for (uint32_t i = b; i < e; i++) {
+        uint64_t v = a.unit_tot[i];
+        a.unit_tot[i] = run;
+        run += v;
+    }
+}
+
+// ---- kernel 3: write the anchors of every unit --------------------------------------
+template <bool WIDE, int MODE>
+__global__ void __launch_bounds__(kRT, 2)
+bucket_emit_kernel(BucketArgs a) {
+    extern __shared__ __align__(16) unsigned char raw[];
+    BucketSmem<WIDE>& sm = *reinterpret_cast<BucketSmem<WIDE>*>(raw);
+    const uint32_t w = blockIdx.x;
+    uint32_t s, n;
+    uint64_t key_hi;
+    if (!unit_of_window<WIDE>(sm, a, w, s, n, key_hi)) return;
+    uint64_t base = a.unit_tot[w];
+    if ((base & 0x7fffffffull) >= a.max_fragments) return;  // past the cut
+    Chunk<WIDE> ch;
+    uint32_t valid, preveq, inb, sel;
+    Digest dg;
+    if (n <= uint32_t(kCap)) {
+        load_unit<WIDE>(sm, a, s, n);
+        whole_unit_chunk<WIDE>(sm, s, n, 0, ch);
+        unit_flags<WIDE>(ch, valid, preveq, inb);
+        unit_select<WIDE, MODE>(sm, ch, a, key_hi, valid, preveq, inb, sel);
+        unit_write<WIDE>(sm, ch, a, key_hi, preveq, sel, base, dg);
+    } else {
+        for (uint32_t c0 = 0; c0 < n; c0 += kCap) {
+            load_chunk<WIDE>(sm, a, s, n, c0, ch);
+            unit_flags<WIDE>(ch, valid, preveq, inb);
+            const uint64_t t =
+                unit_select<WIDE, MODE>(sm, ch, a, key_hi, valid, preveq, inb, sel);
+            unit_write<WIDE>(sm, ch, a, key_hi, preveq, sel, base, dg);
+            base += t;
+        }
+    }
+    __syncthreads();
+    if (sm.cut && threadIdx.x == 0) {
         a.counters[kCntCutStart] = s;
         a.counters[kCntCutSize] = n;
     }
@@ -707,23 +753,41 @@ uint32_t bucket_max_windows(const MsdPlan& plan, uint64_t max_records) {
 }
 
 void launch_bucket(const BucketArgs& a, bool similar, uint64_t max_records,
-                   cudaStream_t s, uint32_t* launches) {
+                   cudaStream_t s, cudaEvent_t* ev, uint32_t* launches) {
     const uint32_t grid = bucket_max_windows(a.plan, max_records);
-#define NPGE_BUCKET(W, M)                                                       \
+#define NPGE_LAUNCH(KERNEL, W)                                                  \
     do {                                                                        \
-        set_smem(bucket_kernel<W, M>, sizeof(BucketSmem<W>));                   \
-        bucket_kernel<W, M><<<grid, kRT, sizeof(BucketSmem<W>), s>>>(a);        \
+        set_smem(KERNEL, sizeof(BucketSmem<W>));                                \
+        KERNEL<<<grid, kRT, sizeof(BucketSmem<W>), s>>>(a);                     \
         *launches += 1;                                                         \
     } while (0)
     if (max_records) {
         if (similar) {
-            if (a.plan.wide) { NPGE_BUCKET(true, 1); NPGE_BUCKET(true, 2); }
-            else { NPGE_BUCKET(false, 1); NPGE_BUCKET(false, 2); }
+            if (a.plan.wide) {
+                NPGE_LAUNCH((bucket_sort_kernel<true, 1>), true);
+                NPGE_LAUNCH((bucket_count_kernel<true>), true);
+            } else {
+                NPGE_LAUNCH((bucket_sort_kernel<false, 1>), false);
+                NPGE_LAUNCH((bucket_count_kernel<false>), false);
+            }
         } else {
-            if (a.plan.wide) NPGE_BUCKET(true, 0); else NPGE_BUCKET(false, 0);
+            if (a.plan.wide) NPGE_LAUNCH((bucket_sort_kernel<true, 0>), true);
+            else NPGE_LAUNCH((bucket_sort_kernel<false, 0>), false);
         }
+        if (ev) cudaEventRecord(ev[0], s);
+        unit_scan_kernel<<<1, 1024, 0, s>>>(a);
+        *launches += 1;
+        if (similar) {
+            if (a.plan.wide) NPGE_LAUNCH((bucket_emit_kernel<true, 2>), true);
+            else NPGE_LAUNCH((bucket_emit_kernel<false, 2>), false);
+        } else {
+            if (a.plan.wide) NPGE_LAUNCH((bucket_emit_kernel<true, 0>), true);
+            else NPGE_LAUNCH((bucket_emit_kernel<false, 0>), false);
+        }
+    } else if (ev) {
+        cudaEventRecord(ev[0], s);
     }
-#undef NPGE_BUCKET
+#undef NPGE_LAUNCH
     bucket_finalize_kernel<<<1, 32, 0, s>>>(a);
     *launches += 1;
 }

@@ -106,15 +106,16 @@ struct BucketArgs {
     int8_t* r_ori;
     uint64_t* r_block_off;
     uint64_t* r_block_hash;
-    uint64_t* status;            // one look-back word per unit
+    uint64_t* unit_tot;          // per unit: blocks << 31 | fragments, then its prefix
     uint64_t* summary;
 };
 
 size_t bucket_summary_words();
 uint32_t bucket_max_windows(const MsdPlan& plan, uint64_t max_records);
-// similar: two launches (found bits, then candidate rule + emit)
+// sort (+ found bits / count), scan of the unit totals, emit
+// ev (optional, 1 event): recorded after the sort (+ count) kernels
 void launch_bucket(const BucketArgs& a, bool similar, uint64_t max_records,
-                   cudaStream_t s, uint32_t* launches);
+                   cudaStream_t s, cudaEvent_t* ev, uint32_t* launches);
 
 struct GroupArgs {
     const uint32_t* klo;

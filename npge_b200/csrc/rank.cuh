@@ -164,9 +164,10 @@ __device__ __forceinline__ void tile_rank(RankSmem<CAPBITS>& sm,
     }
     if (lane == 31) sm.scan_tmp[warp] = incl;
     __syncthreads();
-    uint32_t wbase = 0;
+    // sum of the totals of the warps before this one: one load + a butterfly
+    uint32_t wbase = (lane < kRW && lane < warp) ? sm.scan_tmp[lane] : 0u;
 #pragma unroll
-    for (int w = 0; w < kRW; w++) wbase += (w < warp) ? sm.scan_tmp[w] : 0;
+    for (int o = 16; o > 0; o >>= 1) wbase += __shfl_xor_sync(0xffffffffu, wbase, o);
     const uint32_t toff0 = wbase + incl - mine;
     if (PER == 2) {
         sm.tile_off[2 * tid] = toff0;
