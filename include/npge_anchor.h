@@ -95,8 +95,10 @@ typedef struct {
 } npge_anchor_stats;
 
 /* digest: for every emitted fragment, t = (seq << 33) | (min_pos << 1) |
- * (ori == +1), h = its block's hash, with splitmix64 as mix():
- *   digest[0] = sum mix(h ^ mix(t)),  digest[1] = sum mix(t + mix(h))  (mod 2^64) */
+ * (ori == +1), h = its block's hash:
+ *   u = t * 0x9E3779B97F4A7C15 + h * 0xC2B2AE3D27D4EB4F;  u ^= u >> 32;
+ *   v = u * 0xD6E8FEB86659FD93;                           v ^= v >> 29;
+ *   digest[0] = sum u,  digest[1] = sum v   (all mod 2^64; order-independent) */
 
 int npge_anchor_create(npge_anchor_ctx** ctx, int device);
 void npge_anchor_destroy(npge_anchor_ctx* ctx);

@@ -148,7 +148,7 @@ extern "C" void npge_anchor_destroy(npge_anchor_ctx* ctx) {
                            &ctx->r_block_off, &ctx->r_block_hash,
                            &ctx->scan_status, &ctx->summary, &ctx->rows, &ctx->blk,
                            &ctx->a_start, &ctx->tile_b, &ctx->win, &ctx->fine_start,
-                           &ctx->bstatus, &ctx->rec[0], &ctx->rec[1], &ctx->rhi[0],
+                           &ctx->bstatus, &ctx->units, &ctx->rec[0], &ctx->rec[1], &ctx->rhi[0],
                            &ctx->rhi[1], &ctx->seq_lut};
     for (DeviceBuffer* b : all) release(*b);
     for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
@@ -290,7 +290,8 @@ int find_device_msd(npge_anchor_ctx* ctx, const npge_anchor_params* p,
         NPGE_TRY(ensure(ctx->rec[b], (max_records + 16) * 8));
         if (plan.wide) NPGE_TRY(ensure(ctx->rhi[b], (max_records + 16) * 4));
     }
-    NPGE_TRY(ensure(ctx->bstatus, size_t(max_win + 1) * 8));
+    NPGE_TRY(ensure(ctx->bstatus, size_t(max_win + 1) * 8 + bins_a * 4));
+    NPGE_TRY(ensure(ctx->units, size_t(max_win + 1) * 16));
     NPGE_TRY(ensure(ctx->counters, kCntWords * 4));
     NPGE_TRY(ensure(ctx->summary, summary_words * 8));
     NPGE_TRY(ensure(ctx->used, n_used * 8));
@@ -344,6 +345,7 @@ int find_device_msd(npge_anchor_ctx* ctx, const npge_anchor_params* p,
     a.a_start = mb.a_start;
     a.win = mb.win;
     a.fine_start = mb.fine_start;
+    a.units = static_cast<uint4*>(ctx->units.ptr);
     a.counters = ptr<uint32_t>(ctx->counters);
     a.used = ptr<uint64_t>(ctx->used);
     a.n_used = n_used;
@@ -814,8 +816,10 @@ extern "C" int npge_anchor_fetch(npge_anchor_ctx* ctx, npge_anchor_result* out) 
                     uint64_t t = (uint64_t(r->frag_seq[f]) << 33) |
                                  (uint64_t(r->frag_min_pos[f]) << 1) |
                                  (r->frag_ori[f] == 1 ? 1 : 0);
-                    d0 += splitmix64(h ^ splitmix64(t));
-                    d1 += splitmix64(t + splitmix64(h));
+                    uint64_t x, y;
+                    digest_terms(t, h, x, y);
+                    d0 += x;
+                    d1 += y;
                 }
             }
             out->digest[0] = d0;

@@ -31,27 +31,6 @@ __device__ __forceinline__ uint64_t rem_key(uint64_t rec, uint32_t hi) {
     return (uint64_t(hi) << 32) | (rec >> 32);
 }
 
-__device__ __forceinline__ uint32_t bucket_of(const uint32_t* __restrict__ table,
-                                              uint32_t n, uint32_t t) {
-    uint32_t lo = 0, hi = n;
-    while (hi - lo > 1) {
-        uint32_t mid = (lo + hi) >> 1;
-        if (table[mid] <= t) lo = mid; else hi = mid;
-    }
-    return lo;
-}
-
-// first f in [0, n] with table[f] >= v (table ascending, n + 1 entries)
-__device__ __forceinline__ uint32_t lower_bound_u32(const uint32_t* __restrict__ table,
-                                                    uint32_t n, uint32_t v) {
-    uint32_t lo = 0, hi = n;
-    while (lo < hi) {
-        uint32_t mid = (lo + hi) >> 1;
-        if (table[mid] < v) lo = mid + 1; else hi = mid;
-    }
-    return lo;
-}
-
 // SortedVector::has_elem (src/util/SortedVector.hpp:108-111) on the device
 __device__ __forceinline__ bool is_used(const BucketArgs& a, uint64_t key) {
     uint64_t lo = 0, hi = a.n_used;
@@ -76,7 +55,6 @@ struct __align__(16) BucketSmem {
     int32_t warp_head[kRW];
     uint64_t red[3][kRW];
     uint32_t carry;           // slow path: head of the group entering a chunk
-    uint32_t u_s, u_n, u_ab;  // the CTA's unit: first record, size, A bucket
     uint32_t cut;             // set by the thread that wrote the record of rank M-1
 };
 
@@ -257,8 +235,10 @@ __device__ __forceinline__ void unit_write(BucketSmem<WIDE>& sm, const Chunk<WID
                 a.r_pos[f] = pos;
                 a.r_ori[f] = (pay & 1) ? 1 : -1;
                 const uint64_t t = (uint64_t(seq) << 33) | (uint64_t(pos) << 1) | (pay & 1);
-                dg.d0 += splitmix64(key ^ splitmix64(t));
-                dg.d1 += splitmix64(t + splitmix64(key));
+                uint64_t x, y;
+                digest_terms(t, key, x, y);
+                dg.d0 += x;
+                dg.d1 += y;
                 if (head) {
                     const uint64_t b = br + __popc(bb & lt);
                     a.r_block_off[b] = f;
@@ -341,30 +321,63 @@ __device__ __forceinline__ void flush_digest(BucketSmem<WIDE>& sm, const BucketA
     }
 }
 
-// The unit of window w: thread 0 searches the tables, everybody gets (s, n, ab).
-// False when w is past the last window.  Contains a barrier.
+// Greedy packing of the (A, B) bins of one A bucket into units of at most kCap
+// records (a bin larger than that is a unit of its own: slow path).  One warp per
+// bucket: the lanes probe the next 32 bin ends at once.  WRITE = false counts the
+// units of every bucket; WRITE = true writes them at the bucket's prefix.
+template <bool WRITE>
+__global__ void __launch_bounds__(256)
+unit_build_kernel(BucketArgs a, uint32_t* __restrict__ unit_cnt) {
+    const int lane = threadIdx.x & 31;
+    const uint32_t ab = blockIdx.x * (blockDim.x / 32) + (threadIdx.x >> 5);
+    const uint32_t bins_a = 1u << a.plan.capa, nb = 1u << a.plan.wb;
+    if (ab >= bins_a) return;
+    const uint32_t* fs = a.fine_start + (size_t(ab) << a.plan.wb);
+    uint32_t out = 0;
+    if (WRITE) {  // units of the buckets before this one
+        for (uint32_t x = lane; x < ab; x += 32) out += unit_cnt[x];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) out += __shfl_xor_sync(0xffffffffu, out, o);
+    }
+    const uint32_t end_all = fs[nb];
+    uint32_t cur = 0, count = 0;
+    while (cur < nb) {
+        const uint32_t s = fs[cur];
+        if (s == end_all) break;  // only empty bins are left
+        uint32_t e = cur + 1;     // the unit is [cur, e); grows while it fits
+        while (true) {
+            const uint32_t probe = e + lane;  // candidate bin to add: [cur, probe]
+            const bool fits = probe < nb && fs[probe + 1] - s <= uint32_t(kCap);
+            const uint32_t m = __ballot_sync(0xffffffffu, fits);
+            const int run = m == 0xffffffffu ? 32 : __ffs(~m) - 1;
+            e += run;
+            if (run < 32) break;
+        }
+        if (WRITE && lane == 0) {
+            a.units[out + count] = make_uint4(s, fs[e] - s, ab, 0u);
+        }
+        count++;
+        cur = e;
+    }
+    if (lane == 0) {
+        if (!WRITE) unit_cnt[ab] = count;
+        if (WRITE && ab == bins_a - 1) a.counters[kCntWindows] = out + count;
+    }
+}
+
+// The unit w of the CTA: (first record, size, A bucket).  False past the last
+// unit.  Contains a barrier when true.
 template <bool WIDE>
 __device__ __forceinline__ bool unit_of_window(BucketSmem<WIDE>& sm, const BucketArgs& a,
                                                uint32_t w, uint32_t& s, uint32_t& n,
                                                uint64_t& key_hi) {
     if (w >= a.counters[kCntWindows]) return false;
-    if (threadIdx.x == 0) {
-        const MsdPlan& pl = a.plan;
-        const uint32_t ab = bucket_of(a.win, 1u << pl.capa, w);
-        const uint32_t lo_pos = a.a_start[ab] + (w - a.win[ab]) * uint32_t(kWindow);
-        const uint32_t hi_pos = min(lo_pos + uint32_t(kWindow), a.a_start[ab + 1]);
-        const uint32_t* fs = a.fine_start + (size_t(ab) << pl.wb);
-        const uint32_t f0 = lower_bound_u32(fs, 1u << pl.wb, lo_pos);
-        const uint32_t f1 = lower_bound_u32(fs, 1u << pl.wb, hi_pos);
-        sm.u_s = fs[f0];
-        sm.u_n = fs[f1] - fs[f0];
-        sm.u_ab = ab;
-        sm.cut = 0;
-    }
+    const uint4 u = a.units[w];
+    if (threadIdx.x == 0) sm.cut = 0;
     __syncthreads();
-    s = sm.u_s;
-    n = sm.u_n;
-    key_hi = uint64_t(sm.u_ab) << a.plan.rem;
+    s = u.x;
+    n = u.y;
+    key_hi = uint64_t(u.z) << a.plan.rem;
     return true;
 }
 
@@ -747,14 +760,22 @@ void set_smem(K kernel, size_t bytes) {
 
 size_t bucket_summary_words() { return kSumWords + kPartials * 4; }
 
-// windows (= units) of the bucket sort: an upper bound for the grid
+// upper bound on the units of the bucket sort (two neighbours never fit in one):
+// the grid of its kernels and the size of the unit tables
 uint32_t bucket_max_windows(const MsdPlan& plan, uint64_t max_records) {
-    return uint32_t((max_records + kWindow - 1) / kWindow) + (1u << plan.capa);
+    return uint32_t((max_records + kWindow - 1) / kWindow) + (2u << plan.capa) + 1;
 }
 
 void launch_bucket(const BucketArgs& a, bool similar, uint64_t max_records,
                    cudaStream_t s, cudaEvent_t* ev, uint32_t* launches) {
     const uint32_t grid = bucket_max_windows(a.plan, max_records);
+    if (max_records) {
+        const uint32_t bins_a = 1u << a.plan.capa;
+        uint32_t* unit_cnt = reinterpret_cast<uint32_t*>(a.unit_tot);  // free until the sort
+        unit_build_kernel<false><<<(bins_a + 7) / 8, 256, 0, s>>>(a, unit_cnt);
+        unit_build_kernel<true><<<(bins_a + 7) / 8, 256, 0, s>>>(a, unit_cnt);
+        *launches += 2;
+    }
 #define NPGE_LAUNCH(KERNEL, W)                                                  \
     do {                                                                        \
         set_smem(KERNEL, sizeof(BucketSmem<W>));                                \

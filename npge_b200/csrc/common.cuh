@@ -72,6 +72,16 @@ __host__ __device__ inline uint64_t splitmix64(uint64_t x) {
     return x ^ (x >> 31);
 }
 
+// The two digest terms of one fragment (include/npge_anchor.h).
+__host__ __device__ inline void digest_terms(uint64_t t, uint64_t h, uint64_t& a,
+                                             uint64_t& b) {
+    uint64_t u = t * 0x9E3779B97F4A7C15ull + h * 0xC2B2AE3D27D4EB4Full;
+    u ^= u >> 32;
+    a = u;
+    uint64_t v = u * 0xD6E8FEB86659FD93ull;
+    b = v ^ (v >> 29);
+}
+
 #ifdef __CUDACC__
 // Canonical key of the window of k bases at global position p, read from
 // packed words `W` (16 bases per u32) whose word 0 holds position `base`.
@@ -140,7 +150,7 @@ struct npge_anchor_ctx {
     npge_b200::DeviceBuffer hist, status, status2, counters, used;
     npge_b200::DeviceBuffer found_bits, head_idx, sel;
     // MSD partition + bucket sort (msd_kernels.cu, bucket_kernels.cu)
-    npge_b200::DeviceBuffer rows, blk, a_start, tile_b, win, fine_start, bstatus;
+    npge_b200::DeviceBuffer rows, blk, a_start, tile_b, win, fine_start, bstatus, units;
     npge_b200::DeviceBuffer rec[2], rhi[2], seq_lut;
     int lut_shift = 12;
     npge_b200::MsdPlan plan;

@@ -265,8 +265,10 @@ group_emit_kernel(GroupArgs a) {
             a.r_pos[frag_rank] = pos;
             a.r_ori[frag_rank] = (pay & 1) ? 1 : -1;
             uint64_t t = (uint64_t(seq) << 33) | (uint64_t(pos) << 1) | (pay & 1);
-            d0 += splitmix64(keys[e] ^ splitmix64(t));
-            d1 += splitmix64(t + splitmix64(keys[e]));
+            uint64_t x, y;
+            digest_terms(t, keys[e], x, y);
+            d0 += x;
+            d1 += y;
             if (head) {
                 a.r_block_off[block_rank] = frag_rank;
                 a.r_block_hash[block_rank] = keys[e];

@@ -91,6 +91,7 @@ struct BucketArgs {
     const uint32_t* a_start;
     const uint32_t* win;
     const uint32_t* fine_start;
+    uint4* units;                // (first record, size, A bucket, -) of every unit
     uint32_t* counters;
     const uint64_t* used;
     uint64_t n_used;

@@ -82,6 +82,40 @@ struct __align__(16) RankSmem {
     uint32_t total;                 // items in the tile
 };
 
+// Rank of every item among the items of its own warp with the same digit, and
+// the warp's digit counts in sm.warp_hist[warp].  FULL: all kRI rounds hold
+// items (straight-line code); otherwise rounds >= `rounds` are skipped.
+template <int CAPBITS, bool FULL>
+__device__ __forceinline__ void warp_rank(RankSmem<CAPBITS>& sm,
+                                          const uint32_t (&digit)[kRI], int rounds,
+                                          uint32_t (&rank)[kRI]) {
+    constexpr int BINS = 1 << CAPBITS;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t lt = (1u << lane) - 1;
+    uint16_t* wh = sm.warp_hist[warp];
+    uint32_t peers[kRI];
+#pragma unroll
+    for (int i = 0; i < kRI; i++) {
+        peers[i] = (FULL || i < rounds) ? __match_any_sync(0xffffffffu, digit[i]) : 0u;
+    }
+#pragma unroll
+    for (int i = 0; i < kRI; i++) {
+        rank[i] = 0;
+        if (FULL || i < rounds) {
+            const uint32_t d = digit[i];
+            const int leader = __ffs(peers[i]) - 1;
+            uint32_t old = 0;
+            if (lane == leader && d < BINS) {
+                old = wh[d];
+                wh[d] = uint16_t(old + __popc(peers[i]));
+            }
+            old = __shfl_sync(0xffffffffu, old, leader);
+            rank[i] = old + __popc(peers[i] & lt);
+            __syncwarp();
+        }
+    }
+}
+
 // Stable rank of the tile's items by digit.  Item i of lane l of warp w is
 // element w * 32 * kRI + i * 32 + l of the tile (ascending input order);
 // digit == BINS means "no item".  `rounds` (warp-uniform) = item rounds of this
@@ -102,34 +136,17 @@ __device__ __forceinline__ void tile_rank(RankSmem<CAPBITS>& sm,
     constexpr int PER = BINS / kRT > 0 ? BINS / kRT : 1;
     static_assert(PER == 1 || PER == 2, "one or two digits per thread");
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint32_t lt = (1u << lane) - 1;
     {
         uint4* wh = reinterpret_cast<uint4*>(sm.warp_hist[warp]);
 #pragma unroll
         for (int i = 0; i < BINS / 256; i++) wh[lane + 32 * i] = make_uint4(0, 0, 0, 0);
     }
     __syncwarp();
-    uint32_t peers[kRI];
-#pragma unroll
-    for (int i = 0; i < kRI; i++) {
-        peers[i] = i < rounds ? __match_any_sync(0xffffffffu, digit[i]) : 0u;
-    }
     uint32_t rank[kRI];
-#pragma unroll
-    for (int i = 0; i < kRI; i++) {
-        rank[i] = 0;
-        if (i < rounds) {
-            const uint32_t d = digit[i];
-            const int leader = __ffs(peers[i]) - 1;
-            uint32_t old = 0;
-            if (lane == leader && d < BINS) {
-                old = sm.warp_hist[warp][d];
-                sm.warp_hist[warp][d] = uint16_t(old + __popc(peers[i]));
-            }
-            old = __shfl_sync(0xffffffffu, old, leader);
-            rank[i] = old + __popc(peers[i] & lt);
-            __syncwarp();
-        }
+    if (rounds == kRI) {
+        warp_rank<CAPBITS, true>(sm, digit, rounds, rank);
+    } else {
+        warp_rank<CAPBITS, false>(sm, digit, rounds, rank);
     }
     __syncthreads();
     c0 = 0;

@@ -765,11 +765,13 @@ hash_t one_block_hash(const std::vector<std::string>& dir_in,
     return a;
 }
 
-inline uint64_t splitmix64(uint64_t x) {
-    x += 0x9E3779B97F4A7C15ull;
-    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
-    x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
-    return x ^ (x >> 31);
+// one fragment's two digest terms (three 64-bit multiplies)
+inline void digest_terms(uint64_t t, uint64_t h, uint64_t& a, uint64_t& b) {
+    uint64_t u = t * 0x9E3779B97F4A7C15ull + h * 0xC2B2AE3D27D4EB4Full;
+    u ^= u >> 32;
+    a = u;
+    uint64_t v = u * 0xD6E8FEB86659FD93ull;
+    b = v ^ (v >> 29);
 }
 
 }  // namespace
@@ -801,8 +803,9 @@ extern "C" uint64_t oracle_blockset_hash(const char* const* names,
 
 /* Same definition as npge_anchor_result.digest (include/npge_anchor.h):
  * per fragment t = (seq << 33) | (min_pos << 1) | (ori == +1), h = block hash;
- * digest[0] = sum of splitmix64(h ^ splitmix64(t)),
- * digest[1] = sum of splitmix64(t + splitmix64(h)), both mod 2^64. */
+ * u = t * 0x9E3779B97F4A7C15 + h * 0xC2B2AE3D27D4EB4F, u ^= u >> 32,
+ * v = u * 0xD6E8FEB86659FD93, v ^= v >> 29;
+ * digest[0] = sum of u, digest[1] = sum of v, all mod 2^64. */
 extern "C" void oracle_digest(const oracle_result* r, uint64_t digest[2]) {
     uint64_t d0 = 0, d1 = 0;
     for (uint64_t b = 0; b < r->n_blocks; b++) {
@@ -811,8 +814,10 @@ extern "C" void oracle_digest(const oracle_result* r, uint64_t digest[2]) {
             uint64_t t = (uint64_t(r->frag_seq[f]) << 33) |
                          (uint64_t(r->frag_min_pos[f]) << 1) |
                          (r->frag_ori[f] == 1 ? 1 : 0);
-            d0 += splitmix64(h ^ splitmix64(t));
-            d1 += splitmix64(t + splitmix64(h));
+            uint64_t x, y;
+            digest_terms(t, h, x, y);
+            d0 += x;
+            d1 += y;
         }
     }
     digest[0] = d0;
