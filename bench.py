@@ -318,18 +318,33 @@ def run_gpu(args, rank, world, local_rank):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_t = float(t.item())
     h2d = int(bases.nbytes + offsets.nbytes)
+    runner.find_host(pinned_np, offsets, K, True, 100000)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        d2h_default = runner.find_host(pinned_np, offsets, K, True, 100000)
+    barrier()
+    e2e_default_t = time.perf_counter() - t0
 
     if rank != 0:
         return
     value = n_total * args.steps / t_dev / 1e9
     nw = parity_stats["n_windows"]
     passes = parity_stats["radix_passes"]
-    # dominant kernel: the radix scatter pass (passes 1..P-1 read 12 B and
-    # write 12 B per record; pass 0 regenerates keys from the packed genome)
-    later = [p[i] for p in pass_ms for i in range(1, passes)]
-    sort_ms = float(np.mean(later)) if later else float("nan")
-    sort_bytes = 24.0 * nw
+    # stages of one step (CUDA events inside npge_anchor_find_device):
+    # count A + scan | pass A | count B + scan | pass B | bucket sort | scan + emit
+    names = ["pass_a", "count_b_scan", "pass_b", "bucket_sort", "scan_emit"]
+    stage = {"count_a_scan": hist_ms / args.steps}
+    for i, nm in enumerate(names):
+        stage[nm] = float(np.mean([p[i] for p in pass_ms]))
+    # dominant kernel: bucket_sort_kernel reads every record once and writes the
+    # sorted unit back (8 B each way at k <= 21, 12 B above)
+    rec_bytes = 12.0 if K > 21 else 8.0
+    sort_ms = stage["bucket_sort"]
+    sort_bytes = 2.0 * rec_bytes * nw
     achieved = sort_bytes / (sort_ms * 1e-3) / 1e9
+    moved = parity_stats["bytes_moved"]
+    moved_gbs = moved * args.steps / (ev_ms * 1e-3) / 1e9
     pipeline_bytes = parity_stats["bytes_algorithmic"]
     pipeline_gbs = pipeline_bytes * args.steps / (ev_ms * 1e-3) / 1e9
     line = {
@@ -354,10 +369,7 @@ def run_gpu(args, rank, world, local_rank):
         "blocks": parity_stats["n_blocks_global"],
         "windows": parity_stats["n_windows_global"],
         "wall_ms_per_step": 1e3 * wall / args.steps,
-        "stage_ms": {"hist": hist_ms / args.steps,
-                     "sort_pass": [float(np.mean([p[i] for p in pass_ms]))
-                                   for i in range(passes)],
-                     "group": group_ms / args.steps},
+        "stage_ms": stage,
         "default_mode": {
             "value": n_total * dsteps / (dflt_ms * 1e-3) / 1e9, "unit": UNIT,
             "options": "anchor-similar=true, max-anchor-fragments=100000",
@@ -369,15 +381,24 @@ def run_gpu(args, rank, world, local_rank):
             "frac": achieved / hbm_peak, "traffic": runner.ncu_traffic(nw),
             "peak_source": peak_src,
             "bytes_per_launch": sort_bytes, "ms_per_launch": sort_ms,
-            "pipeline": {"bytes_algorithmic_per_step": pipeline_bytes,
-                         "achieved": pipeline_gbs,
-                         "frac": pipeline_gbs / hbm_peak,
-                         "bytes_per_base": pipeline_bytes / float(n_local)}},
+            "note": "the bucket sort is bound by shared-memory ranking, not by "
+                    "HBM; see pipeline for the whole step",
+            "pipeline": {"survey_model_bytes_per_step": pipeline_bytes,
+                         "survey_model_gbs": pipeline_gbs,
+                         "survey_model_frac": pipeline_gbs / hbm_peak,
+                         "survey_model_bytes_per_base":
+                             pipeline_bytes / float(n_local),
+                         "compulsory_bytes_per_step": moved,
+                         "compulsory_gbs": moved_gbs,
+                         "compulsory_frac": moved_gbs / hbm_peak}},
         "e2e": {"value": n_total * e2e_steps / e2e_t / 1e9, "unit": UNIT,
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": int(d2h),
                 "steps": e2e_steps,
                 "call": "npge_anchor_find (pinned ASCII bases in, fragment "
-                        "arrays out)"},
+                        "arrays out, pinned)",
+                "default_mode": {
+                    "value": n_total * e2e_steps / e2e_default_t / 1e9,
+                    "d2h_bytes_per_step": int(d2h_default)}},
         "gpu_launches": int(kern_launches),
         "clocks": clocks,
     }
@@ -387,7 +408,7 @@ def run_gpu(args, rank, world, local_rank):
 
 
 class SingleRunner:
-    dominant_kernel = "sort_pass_kernel"
+    dominant_kernel = "bucket_sort_kernel"
 
     def __init__(self, eng, bases, offsets):
         self.eng, self.bases, self.offsets = eng, bases, offsets
@@ -403,16 +424,15 @@ class SingleRunner:
         return st
 
     def find_host(self, bases, offsets, k, similar, max_frags):
-        r = self.eng.find((bases, offsets), k, similar=similar,
-                          max_frags=max_frags)
-        return (r.frag_seq.nbytes + r.frag_min_pos.nbytes + r.frag_ori.nbytes
-                + r.block_offsets.nbytes + r.block_hash.nbytes)
+        r = self.eng.find_counts((bases, offsets), k, similar=similar,
+                                 max_frags=max_frags)
+        return r["result_bytes"]
 
     def ncu_traffic(self, n_windows):
-        """dram bytes (read + write) of one sort_pass_kernel launch from the
+        """dram bytes (read + write) of one bucket_sort_kernel launch from the
         committed ncu --set full capture, scaled to this run's record count
         when the capture used the same workload; None when there is none."""
-        path = os.path.join(ROOT, "profiles", "sort_pass_traffic.json")
+        path = os.path.join(ROOT, "profiles", "bucket_sort_traffic.json")
         if os.path.exists(path):
             with open(path) as f:
                 t = json.load(f)
@@ -422,7 +442,7 @@ class SingleRunner:
 
 
 class DistRunner(SingleRunner):
-    dominant_kernel = "sort_pass_kernel"
+    dominant_kernel = "bucket_sort_kernel"
 
     def __init__(self, finder, bases, offsets, seq_base, n_seqs_total):
         self.f, self.bases, self.offsets = finder, bases, offsets

@@ -4,7 +4,9 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <new>
+#include <utility>
 
 #include "kernels.h"
 
@@ -79,10 +81,87 @@ int digit_bits_preference() {
     return b;
 }
 
+// Pinned host memory for the result arrays: device -> host copies run at PCIe
+// speed only into page-locked memory, and cudaHostAlloc is far too slow to call
+// per result, so freed blocks are kept (up to kPoolLimit bytes) and reused.
+class PinnedPool {
+public:
+    void* take(size_t bytes) {
+        {
+            std::lock_guard<std::mutex> lock(mu_);
+            for (size_t i = 0; i < free_.size(); i++) {
+                if (free_[i].second == bytes) {
+                    void* p = free_[i].first;
+                    free_[i] = free_.back();
+                    free_.pop_back();
+                    pooled_ -= bytes;
+                    return p;
+                }
+            }
+        }
+        void* p = nullptr;
+        if (cudaHostAlloc(&p, bytes, cudaHostAllocDefault) != cudaSuccess) {
+            cudaGetLastError();
+            throw std::bad_alloc();
+        }
+        return p;
+    }
+    void give(void* p, size_t bytes) {
+        {
+            std::lock_guard<std::mutex> lock(mu_);
+            if (pooled_ + bytes <= kPoolLimit) {
+                free_.push_back({p, bytes});
+                pooled_ += bytes;
+                return;
+            }
+        }
+        cudaFreeHost(p);
+    }
+    static PinnedPool& instance() {
+        static PinnedPool* pool = new PinnedPool;  // never destroyed: outlives CUDA
+        return *pool;
+    }
+    static size_t round_up(size_t bytes) {
+        size_t b = 4096;
+        while (b < bytes) b <<= 1;
+        return b;
+    }
+private:
+    static constexpr size_t kPoolLimit = size_t(8) << 30;
+    std::mutex mu_;
+    std::vector<std::pair<void*, size_t>> free_;
+    size_t pooled_ = 0;
+};
+
+// std::vector allocator on the pool; default construction leaves the element
+// uninitialised (resize() must not memset half a gigabyte before the copy).
+template <typename T>
+struct PinnedAlloc {
+    typedef T value_type;
+    PinnedAlloc() {}
+    template <typename U> PinnedAlloc(const PinnedAlloc<U>&) {}
+    T* allocate(size_t n) {
+        return static_cast<T*>(PinnedPool::instance().take(
+            PinnedPool::round_up(n * sizeof(T))));
+    }
+    void deallocate(T* p, size_t n) {
+        PinnedPool::instance().give(p, PinnedPool::round_up(n * sizeof(T)));
+    }
+    template <typename U> void construct(U*) {}
+    template <typename U, typename... A> void construct(U* p, A&&... a) {
+        ::new (static_cast<void*>(p)) U(std::forward<A>(a)...);
+    }
+    template <typename U> bool operator==(const PinnedAlloc<U>&) const { return true; }
+    template <typename U> bool operator!=(const PinnedAlloc<U>&) const { return false; }
+};
+
+template <typename T> using PinnedVector = std::vector<T, PinnedAlloc<T>>;
+
 struct HostResult {
-    std::vector<uint64_t> block_offsets, block_hash, new_used;
-    std::vector<uint32_t> frag_seq, frag_min_pos;
-    std::vector<int8_t> frag_ori;
+    PinnedVector<uint64_t> block_offsets, block_hash;
+    std::vector<uint64_t> new_used;
+    PinnedVector<uint32_t> frag_seq, frag_min_pos;
+    PinnedVector<int8_t> frag_ori;
 };
 
 int check_params(const npge_anchor_params* p) {
