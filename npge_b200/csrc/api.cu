@@ -226,7 +226,7 @@ extern "C" void npge_anchor_destroy(npge_anchor_ctx* ctx) {
                            &ctx->r_seq, &ctx->r_pos, &ctx->r_ori,
                            &ctx->r_block_off, &ctx->r_block_hash,
                            &ctx->scan_status, &ctx->summary, &ctx->rows, &ctx->blk,
-                           &ctx->a_start, &ctx->tile_b, &ctx->win, &ctx->fine_start,
+                           &ctx->segtab, &ctx->fine_start,
                            &ctx->bstatus, &ctx->units, &ctx->rec[0], &ctx->rec[1], &ctx->rhi[0],
                            &ctx->rhi[1], &ctx->seq_lut};
     for (DeviceBuffer* b : all) release(*b);
@@ -359,11 +359,10 @@ int find_device_msd(npge_anchor_ctx* ctx, const npge_anchor_params* p,
     const size_t bins_a = size_t(1) << plan.capa;
     const size_t summary_words = bucket_summary_words();
     const uint32_t max_win = bucket_max_windows(plan, max_records);
-    NPGE_TRY(ensure(ctx->rows, msd_rows_needed(plan, np, max_records) * 4));
-    NPGE_TRY(ensure(ctx->blk, msd_blk_needed(plan, np, max_records) * 4));
-    NPGE_TRY(ensure(ctx->a_start, (bins_a + 1) * 4));
-    NPGE_TRY(ensure(ctx->tile_b, (bins_a + 1) * 4));
-    NPGE_TRY(ensure(ctx->win, (bins_a + 1) * 4));
+    const uint32_t max_seg = uint32_t(bins_a);
+    NPGE_TRY(ensure(ctx->rows, msd_rows_needed(plan, np, max_records, max_seg) * 4));
+    NPGE_TRY(ensure(ctx->blk, msd_blk_needed(plan, np, max_records, max_seg) * 4));
+    NPGE_TRY(ensure(ctx->segtab, seg_table_words(max_seg, plan) * 4));
     NPGE_TRY(ensure(ctx->fine_start, ((bins_a << plan.wb) + 1) * 4));
     for (int b = 0; b < 2; b++) {
         NPGE_TRY(ensure(ctx->rec[b], (max_records + 16) * 8));
@@ -399,18 +398,19 @@ int find_device_msd(npge_anchor_ctx* ctx, const npge_anchor_params* p,
     MsdBuffers mb = {};
     mb.rows = ptr<uint32_t>(ctx->rows);
     mb.blk = ptr<uint32_t>(ctx->blk);
-    mb.a_start = ptr<uint32_t>(ctx->a_start);
-    mb.tile_b = ptr<uint32_t>(ctx->tile_b);
-    mb.win = ptr<uint32_t>(ctx->win);
+    mb.seg = carve_seg_tables(ptr<uint32_t>(ctx->segtab), max_seg, plan);
     mb.fine_start = ptr<uint32_t>(ctx->fine_start);
     for (int b = 0; b < 2; b++) {
         mb.rec[b] = ptr<uint64_t>(ctx->rec[b]);
         mb.hi[b] = ptr<uint32_t>(ctx->rhi[b]);
     }
     if (np) {
-        launch_msd_partition(plan, ptr<uint32_t>(ctx->packed), ptr<uint32_t>(ctx->nmask),
-                             np, max_records, mb, ptr<uint32_t>(ctx->counters), st,
-                             ctx->ev_pass, &launches);
+        PosMap pm = {};
+        launch_msd_pass_a(plan, ptr<uint32_t>(ctx->packed), ptr<uint32_t>(ctx->nmask),
+                          np, mb, pm, ptr<uint32_t>(ctx->counters), st, ctx->ev_pass,
+                          &launches);
+        launch_msd_pass_b(plan, mb.rec[0], mb.hi[0], max_records, max_seg, mb, st,
+                          ctx->ev_pass, &launches);
     } else {
         for (int i = 0; i < 4; i++) NPGE_CUDA(cudaEventRecord(ctx->ev_pass[i], st));
     }
@@ -421,8 +421,6 @@ int find_device_msd(npge_anchor_ctx* ctx, const npge_anchor_params* p,
     a.hi_w = mb.hi[1];
     a.scratch_rec = mb.rec[0];
     a.scratch_hi = mb.hi[0];
-    a.a_start = mb.a_start;
-    a.win = mb.win;
     a.fine_start = mb.fine_start;
     a.units = static_cast<uint4*>(ctx->units.ptr);
     a.counters = ptr<uint32_t>(ctx->counters);

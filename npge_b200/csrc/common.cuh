@@ -150,7 +150,7 @@ struct npge_anchor_ctx {
     npge_b200::DeviceBuffer hist, status, status2, counters, used;
     npge_b200::DeviceBuffer found_bits, head_idx, sel;
     // MSD partition + bucket sort (msd_kernels.cu, bucket_kernels.cu)
-    npge_b200::DeviceBuffer rows, blk, a_start, tile_b, win, fine_start, bstatus, units;
+    npge_b200::DeviceBuffer rows, blk, segtab, fine_start, bstatus, units;
     npge_b200::DeviceBuffer rec[2], rhi[2], seq_lut;
     int lut_shift = 12;
     npge_b200::MsdPlan plan;

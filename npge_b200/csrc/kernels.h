@@ -61,26 +61,52 @@ void launch_sort_pass(const SortPlan& plan, int pass, int k, uint64_t max_record
                       cudaStream_t s);
 
 // ---- MSD partition + bucket sort (msd_kernels.cu, bucket_kernels.cu) -----------
+// Segments of pass B: segment s holds records [seg_begin[s], seg_end[s]) of the
+// input buffer, all of A bucket seg_a[s]; segments are ordered by (bucket,
+// source), tiles of kTile records never cross a segment.  One GPU: segment =
+// bucket.  Several GPUs: one segment per (bucket, source rank).
+struct SegTables {
+    uint32_t n_seg;
+    uint32_t* seg_begin;
+    uint32_t* seg_end;
+    uint32_t* seg_a;
+    uint32_t* seg_tile;  // [n_seg + 1] first tile of every segment
+    uint32_t* a_tile0;   // [(1 << capa) + 1] first tile of every bucket
+    uint32_t* a_start;   // [(1 << capa) + 1] first OUTPUT record of every bucket
+};
+
+// local position -> job-wide position (several GPUs): delta of the sequence
+struct PosMap {
+    const uint32_t* delta;      // [S] per local scan-order sequence; nullptr: identity
+    const uint64_t* seq_start;  // [S + 1] local starts
+    const uint32_t* lut;
+    int lut_shift;
+};
+
 struct MsdBuffers {
     uint32_t* rows;        // histogram rows / scatter bases of the current pass
     uint32_t* blk;         // block sums of the row scan
-    uint32_t* a_start;     // [(1 << capa) + 1]
-    uint32_t* tile_b;      // [(1 << capa) + 1]
-    uint32_t* win;         // [(1 << capa) + 1]
+    SegTables seg;
     uint32_t* fine_start;  // [((1 << capa) << wb) + 1]
     uint64_t* rec[2];      // key bits [0, 32) << 32 | payload
     uint32_t* hi[2];       // key bits [32, rem) when plan.wide
 };
 
 MsdPlan make_msd_plan(int k, uint64_t n_positions);
-size_t msd_rows_needed(const MsdPlan& plan, uint64_t n_padded, uint64_t max_records);
-size_t msd_blk_needed(const MsdPlan& plan, uint64_t n_padded, uint64_t max_records);
-// ev (optional, 4 events): after count A, pass A, count B, pass B
-void launch_msd_partition(const MsdPlan& plan, const uint32_t* packed,
-                          const uint32_t* nmask, uint64_t n_padded,
-                          uint64_t max_records, const MsdBuffers& b,
-                          uint32_t* counters, cudaStream_t s, cudaEvent_t* ev,
-                          uint32_t* launches);
+size_t msd_rows_needed(const MsdPlan& plan, uint64_t n_padded, uint64_t max_records,
+                       uint32_t max_seg);
+size_t msd_blk_needed(const MsdPlan& plan, uint64_t n_padded, uint64_t max_records,
+                      uint32_t max_seg);
+size_t seg_table_words(uint32_t max_seg, const MsdPlan& plan);
+SegTables carve_seg_tables(uint32_t* base, uint32_t max_seg, const MsdPlan& plan);
+// ev (optional): [0] after count A, [1] after pass A, [2] after count B, [3] pass B
+void launch_msd_pass_a(const MsdPlan& plan, const uint32_t* packed,
+                       const uint32_t* nmask, uint64_t n_padded, const MsdBuffers& b,
+                       const PosMap& pm, uint32_t* counters, cudaStream_t s,
+                       cudaEvent_t* ev, uint32_t* launches);
+void launch_msd_pass_b(const MsdPlan& plan, const uint64_t* in_rec, const uint32_t* in_hi,
+                       uint64_t max_records, uint32_t max_seg, const MsdBuffers& b,
+                       cudaStream_t s, cudaEvent_t* ev, uint32_t* launches);
 
 struct BucketArgs {
     MsdPlan plan;
@@ -88,8 +114,6 @@ struct BucketArgs {
     uint32_t* hi_w;
     uint64_t* scratch_rec;  // buffer 0: scratch of oversized units
     uint32_t* scratch_hi;
-    const uint32_t* a_start;
-    const uint32_t* win;
     const uint32_t* fine_start;
     uint4* units;                // (first record, size, A bucket, -) of every unit
     uint32_t* counters;

@@ -173,36 +173,34 @@ __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t* warp_t
     return base + incl - v;
 }
 
-// After the A rows are scanned: bucket starts, tile and window tables of the
-// A buckets.  One CTA of 1 << capa threads.
-//   a_start[a]  first record of bucket a (a_start[bins] = n)
-//   tile_b[a]   first B tile of bucket a (tiles of kTile records, bucket aligned)
-//   win[a]      first bucket-sort window of bucket a (windows of kWindow records)
+// After the A rows are scanned: the segment tables of pass B for one GPU, where
+// segment a = A bucket a of this GPU's own pass A output.  One CTA of 1 << capa
+// threads.  (With several GPUs the host builds the same tables from the
+// all-gathered histograms: one segment per (A bucket, source rank).)
 __global__ void __launch_bounds__(1024)
-a_tables_kernel(const uint32_t* __restrict__ totals, uint32_t* __restrict__ a_start,
-                uint32_t* __restrict__ tile_b, uint32_t* __restrict__ win,
+a_tables_kernel(const uint32_t* __restrict__ totals, SegTables t,
                 uint32_t* __restrict__ counters) {
     __shared__ uint32_t tmp[32];
     const int bins = blockDim.x, d = threadIdx.x;
     const uint32_t c = totals[d];
     uint32_t all;
     uint32_t s = block_excl_scan(c, tmp, &all);
-    a_start[d] = s;
+    t.a_start[d] = s;
+    t.seg_begin[d] = s;
+    t.seg_end[d] = s + c;
+    t.seg_a[d] = d;
     if (d == bins - 1) {
-        a_start[bins] = all;
+        t.a_start[bins] = all;
         counters[kCntValid] = all;
     }
-    uint32_t t = block_excl_scan((c + kTile - 1) / kTile, tmp, &all);
-    tile_b[d] = t;
-    if (d == bins - 1) tile_b[bins] = all;
-    uint32_t w = block_excl_scan((c + kWindow - 1) / kWindow, tmp, &all);
-    win[d] = w;
+    uint32_t tl = block_excl_scan((c + kTile - 1) / kTile, tmp, &all);
+    t.seg_tile[d] = tl;
+    t.a_tile0[d] = tl;
     if (d == bins - 1) {
-        win[bins] = all;
-        counters[kCntWindows] = all;
+        t.seg_tile[bins] = all;
+        t.a_tile0[bins] = all;
     }
 }
-
 
 // key bits kept in a record after pass A (the low `rem` bits of the k-mer)
 __device__ __forceinline__ uint64_t rem_key(uint64_t rec, uint32_t hi) {
@@ -232,10 +230,12 @@ struct __align__(16) PassSmem {
 };
 
 // ---- pass A: generate + partition by the top wa bits -----------------------------
-template <int CAPBITS, bool WIDE>
+// GLOBAL: the payload carries the position in the job-wide scan order of all
+// ranks' sequences (local position + the sequence's delta) instead of the local one.
+template <int CAPBITS, bool WIDE, bool GLOBAL>
 __global__ void __launch_bounds__(kRT, 2)
 pass_a_kernel(const uint32_t* __restrict__ packed, const uint32_t* __restrict__ nmask,
-              MsdPlan plan, const uint32_t* __restrict__ rows,
+              MsdPlan plan, const uint32_t* __restrict__ rows, PosMap pm,
               uint64_t* __restrict__ out_rec, uint32_t* __restrict__ out_hi) {
     extern __shared__ __align__(16) unsigned char raw[];
     using Smem = PassSmem<CAPBITS, WIDE>;
@@ -256,8 +256,18 @@ pass_a_kernel(const uint32_t* __restrict__ packed, const uint32_t* __restrict__ 
         uint32_t ob;
         bool ok = window_key(sm.st, rel, plan.k, h, ob);
         uint64_t kr = h & rmask;
-        // payload: global position << 1 | (ori == +1)
-        rec[i] = (uint64_t(uint32_t(kr)) << 32) | (((gbase + rel) << 1) | ob);
+        // payload: position << 1 | (ori == +1)
+        uint32_t g = gbase + rel;
+        if (GLOBAL && ok) {
+            const uint32_t q = g >> pm.lut_shift;
+            uint32_t lo = pm.lut[q], hi2 = pm.lut[q + 1] + 1;  // answer in [lo, hi2)
+            while (hi2 - lo > 1) {
+                uint32_t mid = (lo + hi2) >> 1;
+                if (pm.seq_start[mid] <= g) lo = mid; else hi2 = mid;
+            }
+            g += pm.delta[lo];
+        }
+        rec[i] = (uint64_t(uint32_t(kr)) << 32) | ((g << 1) | ob);
         hi[i] = uint32_t(kr >> 32);
         digit[i] = ok ? uint32_t(h >> sa) : uint32_t(BINS);
     }
@@ -295,19 +305,18 @@ pass_a_kernel(const uint32_t* __restrict__ packed, const uint32_t* __restrict__ 
 template <bool WIDE>
 __global__ void __launch_bounds__(kRT)
 count_b_kernel(const uint64_t* __restrict__ rec, const uint32_t* __restrict__ hi,
-               MsdPlan plan, const uint32_t* __restrict__ a_start,
-               const uint32_t* __restrict__ tile_b, uint32_t* __restrict__ rows) {
+               MsdPlan plan, SegTables t, uint32_t* __restrict__ rows) {
     extern __shared__ __align__(16) unsigned char raw[];
     uint32_t* hist = reinterpret_cast<uint32_t*>(raw);
-    const int bins = 1 << plan.capb, bins_a = 1 << plan.capa;
+    const int bins = 1 << plan.capb;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     for (int i = tid; i < bins; i += kRT) hist[i] = 0;
     __syncthreads();
     const uint32_t tb = blockIdx.x;
-    if (tb < tile_b[bins_a]) {
-        const uint32_t a = bucket_of(tile_b, bins_a, tb);
-        const uint32_t s = a_start[a] + (tb - tile_b[a]) * uint32_t(kTile);
-        const uint32_t e = min(s + uint32_t(kTile), a_start[a + 1]);
+    if (tb < t.seg_tile[t.n_seg]) {
+        const uint32_t sg = bucket_of(t.seg_tile, t.n_seg, tb);
+        const uint32_t s = t.seg_begin[sg] + (tb - t.seg_tile[sg]) * uint32_t(kTile);
+        const uint32_t e = min(s + uint32_t(kTile), t.seg_end[sg]);
         const int sb = plan.rem - plan.wb;
         const uint32_t mb = (1u << plan.wb) - 1;
 #pragma unroll
@@ -327,13 +336,13 @@ count_b_kernel(const uint64_t* __restrict__ rec, const uint32_t* __restrict__ hi
 // fine_start[(a << wb) + b] = first record of the (a, b) bin; one CTA per a.
 // rows hold the exclusive column prefix P over ALL B tiles (totals in row n_rows).
 __global__ void __launch_bounds__(1024)
-fine_tables_kernel(const uint32_t* __restrict__ rows, MsdPlan plan,
-                   const uint32_t* __restrict__ a_start,
-                   const uint32_t* __restrict__ tile_b, uint32_t* __restrict__ fine_start) {
+fine_tables_kernel(const uint32_t* __restrict__ rows, MsdPlan plan, SegTables t,
+                   uint32_t* __restrict__ fine_start) {
     __shared__ uint32_t tmp[32];
     const int bins = blockDim.x, b = threadIdx.x;
     const uint32_t a = blockIdx.x;
-    const uint32_t t0 = tile_b[a], t1 = tile_b[a + 1];
+    const uint32_t* a_start = t.a_start;
+    const uint32_t t0 = t.a_tile0[a], t1 = t.a_tile0[a + 1];
     const uint32_t c = rows[size_t(t1) * bins + b] - rows[size_t(t0) * bins + b];
     const uint32_t s = block_excl_scan(c, tmp, nullptr);
     if (b < (1 << plan.wb)) fine_start[(a << plan.wb) + b] = a_start[a] + s;
@@ -346,8 +355,7 @@ fine_tables_kernel(const uint32_t* __restrict__ rows, MsdPlan plan,
 template <int CAPBITS, bool WIDE>
 __global__ void __launch_bounds__(kRT, 2)
 pass_b_kernel(const uint64_t* __restrict__ in_rec, const uint32_t* __restrict__ in_hi,
-              MsdPlan plan, const uint32_t* __restrict__ a_start,
-              const uint32_t* __restrict__ tile_b, const uint32_t* __restrict__ rows,
+              MsdPlan plan, SegTables t, const uint32_t* __restrict__ rows,
               const uint32_t* __restrict__ fine_start,
               uint64_t* __restrict__ out_rec, uint32_t* __restrict__ out_hi) {
     extern __shared__ __align__(16) unsigned char raw[];
@@ -355,13 +363,13 @@ pass_b_kernel(const uint64_t* __restrict__ in_rec, const uint32_t* __restrict__ 
     Smem& sm = *reinterpret_cast<Smem*>(raw);
     constexpr int BINS = Smem::BINS;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int bins_a = 1 << plan.capa;
     const uint32_t tb = blockIdx.x;
-    if (tb >= tile_b[bins_a]) return;
-    const uint32_t a = bucket_of(tile_b, bins_a, tb);
-    const uint32_t t0 = tile_b[a];
-    const uint32_t s = a_start[a] + (tb - t0) * uint32_t(kTile);
-    const uint32_t e = min(s + uint32_t(kTile), a_start[a + 1]);
+    if (tb >= t.seg_tile[t.n_seg]) return;
+    const uint32_t sg = bucket_of(t.seg_tile, t.n_seg, tb);
+    const uint32_t a = t.seg_a[sg];
+    const uint32_t t0 = t.a_tile0[a];  // first tile of the bucket (all sources)
+    const uint32_t s = t.seg_begin[sg] + (tb - t.seg_tile[sg]) * uint32_t(kTile);
+    const uint32_t e = min(s + uint32_t(kTile), t.seg_end[sg]);
     const int sb = plan.rem - plan.wb;
     const uint32_t mb = (1u << plan.wb) - 1;
     uint64_t rec[kRI];
@@ -440,73 +448,103 @@ void set_smem(K kernel, size_t bytes) {
 
 }  // namespace
 
-size_t msd_rows_needed(const MsdPlan& plan, uint64_t n_padded, uint64_t max_records) {
+size_t msd_rows_needed(const MsdPlan& plan, uint64_t n_padded, uint64_t max_records,
+                       uint32_t max_seg) {
     const size_t ta = size_t(n_padded / kTile);
-    const size_t tb = size_t((max_records + kTile - 1) / kTile) + (size_t(1) << plan.capa);
+    const size_t tb = size_t((max_records + kTile - 1) / kTile) + max_seg;
     const size_t wa = (ta + 1) << plan.capa, wb = (tb + 1) << plan.capb;
     return wa > wb ? wa : wb;  // u32 words
 }
 
-size_t msd_blk_needed(const MsdPlan& plan, uint64_t n_padded, uint64_t max_records) {
+size_t msd_blk_needed(const MsdPlan& plan, uint64_t n_padded, uint64_t max_records,
+                      uint32_t max_seg) {
     const size_t ta = size_t(n_padded / kTile);
-    const size_t tb = size_t((max_records + kTile - 1) / kTile) + (size_t(1) << plan.capa);
+    const size_t tb = size_t((max_records + kTile - 1) / kTile) + max_seg;
     const size_t wa = ((ta + kScanRows - 1) / kScanRows + 1) << plan.capa;
     const size_t wb = ((tb + kScanRows - 1) / kScanRows + 1) << plan.capb;
     return wa > wb ? wa : wb;
 }
 
-// genome -> records sorted by (A, B), stable.  The sorted records end in
-// b.rec[1] / b.hi[1]; b.fine_start, b.a_start and b.win describe them.
-void launch_msd_partition(const MsdPlan& plan, const uint32_t* packed,
-                          const uint32_t* nmask, uint64_t n_padded,
-                          uint64_t max_records, const MsdBuffers& b,
-                          uint32_t* counters, cudaStream_t s, cudaEvent_t* ev,
-                          uint32_t* launches) {
+SegTables carve_seg_tables(uint32_t* base, uint32_t max_seg, const MsdPlan& plan) {
+    SegTables t;
+    const uint32_t bins_a = 1u << plan.capa;
+    t.n_seg = bins_a;
+    t.seg_begin = base;
+    t.seg_end = t.seg_begin + max_seg;
+    t.seg_a = t.seg_end + max_seg;
+    t.seg_tile = t.seg_a + max_seg;
+    t.a_tile0 = t.seg_tile + max_seg + 1;
+    t.a_start = t.a_tile0 + bins_a + 1;
+    return t;
+}
+
+size_t seg_table_words(uint32_t max_seg, const MsdPlan& plan) {
+    return size_t(4) * max_seg + 1 + 2 * ((size_t(1) << plan.capa) + 1);
+}
+
+// genome -> records partitioned by the top wa key bits (stable) in b.rec[0] /
+// b.hi[0]; on one GPU also the segment tables of pass B (b.seg).
+void launch_msd_pass_a(const MsdPlan& plan, const uint32_t* packed,
+                       const uint32_t* nmask, uint64_t n_padded, const MsdBuffers& b,
+                       const PosMap& pm, uint32_t* counters, cudaStream_t s,
+                       cudaEvent_t* ev, uint32_t* launches) {
     const uint32_t tiles_a = uint32_t(n_padded / kTile);
     if (tiles_a == 0) return;
-    const int bins_a = 1 << plan.capa, bins_b = 1 << plan.capb;
+    const int bins_a = 1 << plan.capa;
     count_a_kernel<<<tiles_a, kRT, sizeof(GenomeStage) + bins_a * 4, s>>>(
         packed, nmask, plan, b.rows);
     scan_rows(b.rows, tiles_a, bins_a, b.blk, s);
-    a_tables_kernel<<<1, bins_a, 0, s>>>(b.rows + size_t(tiles_a) * bins_a, b.a_start,
-                                         b.tile_b, b.win, counters);
-    apply_rows(b.rows, tiles_a, bins_a, b.blk, b.a_start, s);
+    a_tables_kernel<<<1, bins_a, 0, s>>>(b.rows + size_t(tiles_a) * bins_a, b.seg,
+                                         counters);
+    apply_rows(b.rows, tiles_a, bins_a, b.blk, b.seg.a_start, s);
     *launches += 5;
     if (ev) cudaEventRecord(ev[0], s);
-#define NPGE_PASS_A(CB, W)                                                         \
+#define NPGE_PASS_A(CB, W, G)                                                      \
     do {                                                                           \
-        set_smem(pass_a_kernel<CB, W>, sizeof(PassSmem<CB, W>));                   \
-        pass_a_kernel<CB, W><<<tiles_a, kRT, sizeof(PassSmem<CB, W>), s>>>(        \
-            packed, nmask, plan, b.rows, b.rec[0], b.hi[0]);                       \
+        set_smem(pass_a_kernel<CB, W, G>, sizeof(PassSmem<CB, W>));                \
+        pass_a_kernel<CB, W, G><<<tiles_a, kRT, sizeof(PassSmem<CB, W>), s>>>(     \
+            packed, nmask, plan, b.rows, pm, b.rec[0], b.hi[0]);                   \
+    } while (0)
+#define NPGE_PASS_A2(CB, W)                                                        \
+    do {                                                                           \
+        if (pm.delta) NPGE_PASS_A(CB, W, true); else NPGE_PASS_A(CB, W, false);    \
     } while (0)
     if (plan.capa == 8) {
-        if (plan.wide) NPGE_PASS_A(8, true); else NPGE_PASS_A(8, false);
+        if (plan.wide) NPGE_PASS_A2(8, true); else NPGE_PASS_A2(8, false);
     } else {
-        if (plan.wide) NPGE_PASS_A(10, true); else NPGE_PASS_A(10, false);
+        if (plan.wide) NPGE_PASS_A2(10, true); else NPGE_PASS_A2(10, false);
     }
+#undef NPGE_PASS_A2
 #undef NPGE_PASS_A
     *launches += 1;
     if (ev) cudaEventRecord(ev[1], s);
-    const uint32_t tiles_b = uint32_t((max_records + kTile - 1) / kTile) + (1u << plan.capa);
+}
+
+// records of the segments b.seg describes (in in_rec / in_hi, each segment
+// holding one A bucket) -> sorted by (A, B), stable in segment order, in
+// b.rec[1] / b.hi[1]; b.fine_start gives the first record of every (A, B) bin.
+void launch_msd_pass_b(const MsdPlan& plan, const uint64_t* in_rec, const uint32_t* in_hi,
+                       uint64_t max_records, uint32_t max_seg, const MsdBuffers& b,
+                       cudaStream_t s, cudaEvent_t* ev, uint32_t* launches) {
+    const int bins_a = 1 << plan.capa, bins_b = 1 << plan.capb;
+    const uint32_t tiles_b = uint32_t((max_records + kTile - 1) / kTile) + max_seg;
     if (plan.wide) {
-        count_b_kernel<true><<<tiles_b, kRT, bins_b * 4, s>>>(
-            b.rec[0], b.hi[0], plan, b.a_start, b.tile_b, b.rows);
+        count_b_kernel<true><<<tiles_b, kRT, bins_b * 4, s>>>(in_rec, in_hi, plan, b.seg,
+                                                            b.rows);
     } else {
-        count_b_kernel<false><<<tiles_b, kRT, bins_b * 4, s>>>(
-            b.rec[0], b.hi[0], plan, b.a_start, b.tile_b, b.rows);
+        count_b_kernel<false><<<tiles_b, kRT, bins_b * 4, s>>>(in_rec, in_hi, plan, b.seg,
+                                                             b.rows);
     }
     scan_rows(b.rows, tiles_b, bins_b, b.blk, s);
     apply_rows(b.rows, tiles_b, bins_b, b.blk, nullptr, s);
-    fine_tables_kernel<<<bins_a, bins_b, 0, s>>>(b.rows, plan, b.a_start, b.tile_b,
-                                                 b.fine_start);
+    fine_tables_kernel<<<bins_a, bins_b, 0, s>>>(b.rows, plan, b.seg, b.fine_start);
     *launches += 5;
     if (ev) cudaEventRecord(ev[2], s);
 #define NPGE_PASS_B(CB, W)                                                         \
     do {                                                                           \
         set_smem(pass_b_kernel<CB, W>, sizeof(PassSmem<CB, W>));                   \
         pass_b_kernel<CB, W><<<tiles_b, kRT, sizeof(PassSmem<CB, W>), s>>>(        \
-            b.rec[0], b.hi[0], plan, b.a_start, b.tile_b, b.rows, b.fine_start,    \
-            b.rec[1], b.hi[1]);                                                    \
+            in_rec, in_hi, plan, b.seg, b.rows, b.fine_start, b.rec[1], b.hi[1]);  \
     } while (0)
     if (plan.capb == 8) {
         if (plan.wide) NPGE_PASS_B(8, true); else NPGE_PASS_B(8, false);
