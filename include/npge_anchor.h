@@ -129,6 +129,65 @@ int npge_anchor_find_device(npge_anchor_ctx* ctx, const npge_anchor_params* p,
 int npge_anchor_fetch(npge_anchor_ctx* ctx, npge_anchor_result* out);
 int npge_anchor_get_stats(npge_anchor_ctx* ctx, npge_anchor_stats* stats);
 
+/* ---- several GPUs, one process and one context per GPU ---------------
+ * Every rank scans its own sequences; canonical k-mers are repartitioned by
+ * hash range between pass A and pass B.  The caller owns the collectives
+ * (npge_b200/dist.py uses torch.distributed / NCCL); these entry points are the
+ * per-rank stages between them:
+ *   dist_upload    local sequences + the job-wide sequence table (positions in
+ *                  the payload follow the job-wide scan order, so every rank's
+ *                  result is the slice of the one-GPU result it owns)
+ *   dist_pass_a    count A + pass A; returns the records per A bucket
+ *   [all-gather of the histograms; contiguous bucket ranges are assigned to ranks]
+ *   dist_buffers   device pointers of the send / receive buffers
+ *   [all-to-all of the records]
+ *   dist_sort      stage 0: pass B over the (bucket, source rank) segments of
+ *                  the receive buffer (tables built by the caller from the
+ *                  all-gathered histograms), bucket sort, and either the
+ *                  anchor count (exact mode: totals valid) or the found bits
+ *                  (anchor-similar: totals are 0)
+ *                  [anchor-similar: all-reduce of the found bitmap; every bit
+ *                  is set by exactly one rank, so SUM of the words is OR]
+ *                  stage 1 (anchor-similar only): candidate rule + count
+ *                  returns the rank's totals {fragments, blocks} before the cut
+ *   [all-gather of the totals -> every rank's share of max-anchor-fragments]
+ *   dist_emit      writes the rank's anchors; npge_anchor_fetch then works as usual,
+ *                  except that new_used holds EVERY hash of the rank's list (the
+ *                  caller concatenates the ranks and drops the job's first one)
+ * Every rank must hold a contiguous range of the job-wide scan order (sequences by
+ * size, descending; ties by caller index), ranges ascending with the rank: then the
+ * source-rank order of the exchange is the position order and the sort stays stable.
+ */
+typedef struct {
+    void* send_rec;      /* u64 records after pass A, bucket a at a_start[a] */
+    void* send_hi;       /* u32, NULL unless wide (anchor-size >= 22) */
+    void* recv_rec;      /* room for n_recv records */
+    void* recv_hi;
+    void* found_bits;    /* u32 words, one bit per job-wide position */
+    uint64_t found_words;
+    int32_t wide;
+    int32_t n_bins;      /* A buckets (1 << capa) */
+} npge_anchor_dist_ptrs;
+
+int npge_anchor_dist_upload(npge_anchor_ctx* ctx, int32_t anchor_size,
+                            const uint8_t* bases, const uint64_t* seq_offsets,
+                            uint32_t n_seqs, const uint64_t* local_gstart,
+                            const uint64_t* global_start,
+                            const uint32_t* global_caller, uint32_t n_global);
+int npge_anchor_dist_pass_a(npge_anchor_ctx* ctx, const npge_anchor_params* p,
+                            uint32_t* hist_out, uint32_t hist_cap, uint32_t* n_bins);
+int npge_anchor_dist_buffers(npge_anchor_ctx* ctx, uint64_t n_recv,
+                             npge_anchor_dist_ptrs* out);
+int npge_anchor_dist_sort(npge_anchor_ctx* ctx, const npge_anchor_params* p,
+                          int32_t stage, uint64_t n_recv, uint32_t n_seg,
+                          const uint32_t* seg_begin, const uint32_t* seg_end,
+                          const uint32_t* seg_a, const uint32_t* seg_tile,
+                          const uint32_t* a_tile0, const uint32_t* a_start,
+                          const uint64_t* used_sorted, uint64_t n_used,
+                          uint64_t totals[2]);
+int npge_anchor_dist_emit(npge_anchor_ctx* ctx, const npge_anchor_params* p,
+                          uint64_t local_limit, npge_anchor_stats* stats);
+
 /* Library self-description: "npge_anchor <version> sm_100a" */
 const char* npge_anchor_version(void);
 

@@ -11,6 +11,8 @@ EXPORTS = [
     "npge_anchor_find", "npge_anchor_result_free", "npge_anchor_upload",
     "npge_anchor_find_device", "npge_anchor_fetch", "npge_anchor_get_stats",
     "npge_anchor_version",
+    "npge_anchor_dist_upload", "npge_anchor_dist_pass_a",
+    "npge_anchor_dist_buffers", "npge_anchor_dist_sort", "npge_anchor_dist_emit",
 ]
 
 OK, ERR_PARAMS, ERR_CUDA, ERR_MEMORY, ERR_CAPACITY, ERR_INPUT, ERR_STATE = range(7)
@@ -43,6 +45,15 @@ class Stats(C.Structure):
         ("ms_sort", C.c_float), ("ms_group", C.c_float),
         ("ms_total", C.c_float), ("ms_pass", C.c_float * 16),
         ("bytes_algorithmic", C.c_uint64), ("bytes_moved", C.c_uint64),
+    ]
+
+
+class DistPtrs(C.Structure):
+    _fields_ = [
+        ("send_rec", C.c_void_p), ("send_hi", C.c_void_p),
+        ("recv_rec", C.c_void_p), ("recv_hi", C.c_void_p),
+        ("found_bits", C.c_void_p), ("found_words", C.c_uint64),
+        ("wide", C.c_int32), ("n_bins", C.c_int32),
     ]
 
 
@@ -82,5 +93,21 @@ def load():
     L.npge_anchor_fetch.argtypes = [ctx, C.POINTER(Result)]
     L.npge_anchor_get_stats.restype = C.c_int
     L.npge_anchor_get_stats.argtypes = [ctx, C.POINTER(Stats)]
+    L.npge_anchor_dist_upload.restype = C.c_int
+    L.npge_anchor_dist_upload.argtypes = [ctx, C.c_int32, C.c_void_p, C.c_void_p,
+                                          C.c_uint32, C.c_void_p, C.c_void_p,
+                                          C.c_void_p, C.c_uint32]
+    L.npge_anchor_dist_pass_a.restype = C.c_int
+    L.npge_anchor_dist_pass_a.argtypes = [ctx, C.POINTER(Params), C.c_void_p,
+                                          C.c_uint32, C.POINTER(C.c_uint32)]
+    L.npge_anchor_dist_buffers.restype = C.c_int
+    L.npge_anchor_dist_buffers.argtypes = [ctx, C.c_uint64, C.POINTER(DistPtrs)]
+    L.npge_anchor_dist_sort.restype = C.c_int
+    L.npge_anchor_dist_sort.argtypes = [ctx, C.POINTER(Params), C.c_int32,
+                                        C.c_uint64, C.c_uint32] + [C.c_void_p] * 7 + [
+                                            C.c_uint64, C.POINTER(C.c_uint64 * 2)]
+    L.npge_anchor_dist_emit.restype = C.c_int
+    L.npge_anchor_dist_emit.argtypes = [ctx, C.POINTER(Params), C.c_uint64,
+                                        C.POINTER(Stats)]
     _lib = L
     return L

@@ -228,7 +228,8 @@ extern "C" void npge_anchor_destroy(npge_anchor_ctx* ctx) {
                            &ctx->scan_status, &ctx->summary, &ctx->rows, &ctx->blk,
                            &ctx->segtab, &ctx->fine_start,
                            &ctx->bstatus, &ctx->units, &ctx->rec[0], &ctx->rec[1], &ctx->rhi[0],
-                           &ctx->rhi[1], &ctx->seq_lut};
+                           &ctx->rhi[1], &ctx->seq_lut, &ctx->g_seq_start, &ctx->g_seq_caller,
+                           &ctx->g_seq_lut, &ctx->pos_delta, &ctx->recv_rec, &ctx->recv_hi};
     for (DeviceBuffer* b : all) release(*b);
     for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
     for (auto& ev : ctx->ev_pass) if (ev) cudaEventDestroy(ev);
@@ -336,11 +337,53 @@ extern "C" int npge_anchor_upload(npge_anchor_ctx* ctx, int32_t anchor_size,
         }
     }
     ctx->uploaded = true;
+    ctx->dist = false;
+    ctx->gseqs = ctx->seqs;
+    ctx->g_positions = ctx->n_positions;
+    ctx->g_padded = ctx->n_padded;
     return NPGE_ANCHOR_OK;
 }
 
 // ---- find_device, MSD partition + shared-memory bucket sort ---------------------------
 namespace {
+
+// The arguments of the bucket-sort kernels from the context's buffers.
+BucketArgs bucket_args(npge_anchor_ctx* ctx, const MsdPlan& plan, const MsdBuffers& mb,
+                       uint64_t* scratch_rec, uint32_t* scratch_hi, uint64_t n_used,
+                       uint64_t limit) {
+    BucketArgs a = {};
+    a.plan = plan;
+    a.rec_w = mb.rec[1];
+    a.hi_w = mb.hi[1];
+    a.scratch_rec = scratch_rec;
+    a.scratch_hi = scratch_hi;
+    a.fine_start = mb.fine_start;
+    a.units = static_cast<uint4*>(ctx->units.ptr);
+    a.counters = ptr<uint32_t>(ctx->counters);
+    a.used = ptr<uint64_t>(ctx->used);
+    a.n_used = n_used;
+    if (ctx->dist) {  // positions are job-wide: map them with the job-wide table
+        a.seq_start = ptr<uint64_t>(ctx->g_seq_start);
+        a.seq_caller = ptr<uint32_t>(ctx->g_seq_caller);
+        a.seq_lut = ptr<uint32_t>(ctx->g_seq_lut);
+    } else {
+        a.seq_start = ptr<uint64_t>(ctx->seq_start);
+        a.seq_caller = ptr<uint32_t>(ctx->seq_caller);
+        a.seq_lut = ptr<uint32_t>(ctx->seq_lut);
+    }
+    a.lut_shift = ctx->lut_shift;
+    a.max_fragments = limit;
+    a.found_bits = ptr<uint32_t>(ctx->found_bits);
+    a.sel = ptr<uint8_t>(ctx->sel);
+    a.r_seq = ptr<uint32_t>(ctx->r_seq);
+    a.r_pos = ptr<uint32_t>(ctx->r_pos);
+    a.r_ori = ptr<int8_t>(ctx->r_ori);
+    a.r_block_off = ptr<uint64_t>(ctx->r_block_off);
+    a.r_block_hash = ptr<uint64_t>(ctx->r_block_hash);
+    a.unit_tot = ptr<uint64_t>(ctx->bstatus);
+    a.summary = ptr<uint64_t>(ctx->summary);
+    return a;
+}
 
 int find_device_msd(npge_anchor_ctx* ctx, const npge_anchor_params* p,
                     const uint64_t* used_sorted, uint64_t n_used,
@@ -415,31 +458,7 @@ int find_device_msd(npge_anchor_ctx* ctx, const npge_anchor_params* p,
         for (int i = 0; i < 4; i++) NPGE_CUDA(cudaEventRecord(ctx->ev_pass[i], st));
     }
     NPGE_CUDA(cudaEventRecord(ctx->ev[2], st));
-    BucketArgs a = {};
-    a.plan = plan;
-    a.rec_w = mb.rec[1];
-    a.hi_w = mb.hi[1];
-    a.scratch_rec = mb.rec[0];
-    a.scratch_hi = mb.hi[0];
-    a.fine_start = mb.fine_start;
-    a.units = static_cast<uint4*>(ctx->units.ptr);
-    a.counters = ptr<uint32_t>(ctx->counters);
-    a.used = ptr<uint64_t>(ctx->used);
-    a.n_used = n_used;
-    a.seq_start = ptr<uint64_t>(ctx->seq_start);
-    a.seq_caller = ptr<uint32_t>(ctx->seq_caller);
-    a.seq_lut = ptr<uint32_t>(ctx->seq_lut);
-    a.lut_shift = ctx->lut_shift;
-    a.max_fragments = limit;
-    a.found_bits = ptr<uint32_t>(ctx->found_bits);
-    a.sel = ptr<uint8_t>(ctx->sel);
-    a.r_seq = ptr<uint32_t>(ctx->r_seq);
-    a.r_pos = ptr<uint32_t>(ctx->r_pos);
-    a.r_ori = ptr<int8_t>(ctx->r_ori);
-    a.r_block_off = ptr<uint64_t>(ctx->r_block_off);
-    a.r_block_hash = ptr<uint64_t>(ctx->r_block_hash);
-    a.unit_tot = ptr<uint64_t>(ctx->bstatus);
-    a.summary = ptr<uint64_t>(ctx->summary);
+    BucketArgs a = bucket_args(ctx, plan, mb, mb.rec[0], mb.hi[0], n_used, limit);
     launch_bucket(a, similar, np ? max_records : 0, st, &ctx->ev[4], &launches);
     NPGE_CUDA(cudaGetLastError());
     NPGE_CUDA(cudaEventRecord(ctx->ev[3], st));
@@ -719,12 +738,12 @@ void rebuild_cut_members(npge_anchor_ctx* ctx, HostResult& r,
     members.reserve(pay.size());
     for (uint32_t pw : pay) {
         uint64_t g = pw >> 1;
-        size_t a = 0, b = ctx->seqs.size();
+        size_t a = 0, b = ctx->gseqs.size();
         while (b - a > 1) {
             size_t mid = (a + b) / 2;
-            if (ctx->seqs[mid].start <= g) a = mid; else b = mid;
+            if (ctx->gseqs[mid].start <= g) a = mid; else b = mid;
         }
-        const SeqEntry& e = ctx->seqs[a];
+        const SeqEntry& e = ctx->gseqs[a];
         uint32_t pos = uint32_t(g - e.start);
         bool direct = pw & 1;
         members.push_back({e.caller_index, direct ? pos : pos + e.size, pos,
@@ -904,10 +923,14 @@ extern "C" int npge_anchor_fetch(npge_anchor_ctx* ctx, npge_anchor_result* out) 
         }
         // used_hashes.push_back for every distinct hash of the list but the
         // first (AnchorFinder.cpp:366-387)
-        for (size_t b = 1; b < r->block_hash.size(); b++) {
+        // (several GPUs: every hash of this rank's range; the caller drops the
+        // job's first one)
+        for (size_t b = ctx->dist ? 0 : 1; b < r->block_hash.size(); b++) {
             r->new_used.push_back(r->block_hash[b]);
         }
-        if (lone_tail && !r->block_hash.empty()) r->new_used.push_back(lone_hash);
+        if (lone_tail && (ctx->dist || !r->block_hash.empty())) {
+            r->new_used.push_back(lone_hash);
+        }
         return NPGE_ANCHOR_OK;
     };
     rc = body();
@@ -944,4 +967,345 @@ extern "C" int npge_anchor_find(npge_anchor_ctx* ctx, const npge_anchor_params* 
     NPGE_TRY(npge_anchor_upload(ctx, p->anchor_size, bases, seq_offsets, n_seqs));
     NPGE_TRY(npge_anchor_find_device(ctx, p, used_sorted, n_used, nullptr));
     return npge_anchor_fetch(ctx, out);
+}
+
+// ==== several GPUs: the per-rank stages between the caller's collectives ==========
+namespace {
+
+MsdBuffers dist_msd_buffers(npge_anchor_ctx* ctx, const MsdPlan& plan, uint32_t max_seg) {
+    MsdBuffers mb = {};
+    mb.rows = ptr<uint32_t>(ctx->rows);
+    mb.blk = ptr<uint32_t>(ctx->blk);
+    mb.seg = carve_seg_tables(ptr<uint32_t>(ctx->segtab), max_seg, plan);
+    mb.fine_start = ptr<uint32_t>(ctx->fine_start);
+    for (int b = 0; b < 2; b++) {
+        mb.rec[b] = ptr<uint64_t>(ctx->rec[b]);
+        mb.hi[b] = ptr<uint32_t>(ctx->rhi[b]);
+    }
+    return mb;
+}
+
+}  // namespace
+
+extern "C" int npge_anchor_dist_upload(npge_anchor_ctx* ctx, int32_t anchor_size,
+                                       const uint8_t* bases, const uint64_t* seq_offsets,
+                                       uint32_t n_seqs, const uint64_t* local_gstart,
+                                       const uint64_t* global_start,
+                                       const uint32_t* global_caller, uint32_t n_global) {
+    if (!ctx) return fail(NPGE_ANCHOR_ERR_PARAMS, "ctx is NULL");
+    if ((n_seqs && !local_gstart) || !global_start || (n_global && !global_caller)) {
+        return fail(NPGE_ANCHOR_ERR_PARAMS, "NULL sequence table");
+    }
+    NPGE_TRY(npge_anchor_upload(ctx, anchor_size, bases, seq_offsets, n_seqs));
+    ctx->uploaded = false;
+    const uint64_t g_positions = global_start[n_global];
+    if (g_positions > kMaxPositions) {
+        return fail(NPGE_ANCHOR_ERR_CAPACITY, "more than 2^31-1 positions in the job");
+    }
+    cudaStream_t st = ctx->stream;
+    // delta of every local scan-order sequence: job-wide start - local start
+    std::vector<uint32_t> delta(ctx->seqs.size() + 1, 0);
+    for (size_t i = 0; i < ctx->seqs.size(); i++) {
+        const SeqEntry& e = ctx->seqs[i];
+        delta[i] = uint32_t(local_gstart[e.caller_index] - e.start);
+    }
+    NPGE_TRY(ensure(ctx->pos_delta, delta.size() * 4));
+    NPGE_CUDA(cudaMemcpyAsync(ctx->pos_delta.ptr, delta.data(), delta.size() * 4,
+                              cudaMemcpyHostToDevice, st));
+    // the job-wide table (the same on every rank) for the emit side
+    ctx->gseqs.clear();
+    for (uint32_t i = 0; i < n_global; i++) {
+        if (global_start[i + 1] <= global_start[i]) {
+            return fail(NPGE_ANCHOR_ERR_PARAMS, "global_start must be increasing");
+        }
+        ctx->gseqs.push_back({global_caller[i], global_start[i + 1] - global_start[i] - 1,
+                              global_start[i]});
+    }
+    ctx->g_positions = g_positions;
+    ctx->g_padded = (g_positions + kPosAlign - 1) / kPosAlign * kPosAlign;
+    const uint64_t n_chunks = (ctx->g_padded >> ctx->lut_shift) + 2;
+    std::vector<uint32_t> lut(n_chunks);
+    {
+        size_t sidx = 0;
+        for (uint64_t q = 0; q < n_chunks; q++) {
+            const uint64_t g = q << ctx->lut_shift;
+            while (sidx + 1 < n_global && global_start[sidx + 1] <= g) sidx++;
+            lut[q] = uint32_t(sidx);
+        }
+    }
+    std::vector<uint32_t> callers(n_global + 1, 0);
+    for (uint32_t i = 0; i < n_global; i++) callers[i] = global_caller[i];
+    NPGE_TRY(ensure(ctx->g_seq_start, (size_t(n_global) + 1) * 8));
+    NPGE_TRY(ensure(ctx->g_seq_caller, (size_t(n_global) + 1) * 4));
+    NPGE_TRY(ensure(ctx->g_seq_lut, n_chunks * 4));
+    NPGE_CUDA(cudaMemcpyAsync(ctx->g_seq_start.ptr, global_start, (size_t(n_global) + 1) * 8,
+                              cudaMemcpyHostToDevice, st));
+    NPGE_CUDA(cudaMemcpyAsync(ctx->g_seq_caller.ptr, callers.data(), callers.size() * 4,
+                              cudaMemcpyHostToDevice, st));
+    NPGE_CUDA(cudaMemcpyAsync(ctx->g_seq_lut.ptr, lut.data(), n_chunks * 4,
+                              cudaMemcpyHostToDevice, st));
+    NPGE_CUDA(cudaStreamSynchronize(st));
+    ctx->dist = true;
+    ctx->uploaded = true;
+    return NPGE_ANCHOR_OK;
+}
+
+extern "C" int npge_anchor_dist_pass_a(npge_anchor_ctx* ctx, const npge_anchor_params* p,
+                                       uint32_t* hist_out, uint32_t hist_cap,
+                                       uint32_t* n_bins) {
+    if (!ctx || !hist_out || !n_bins) return fail(NPGE_ANCHOR_ERR_PARAMS, "NULL argument");
+    NPGE_TRY(check_params(p));
+    if (!ctx->uploaded || !ctx->dist) {
+        return fail(NPGE_ANCHOR_ERR_STATE, "npge_anchor_dist_upload has not been called");
+    }
+    if (p->anchor_size != ctx->upload_k) {
+        return fail(NPGE_ANCHOR_ERR_STATE, "anchor-size differs from the uploaded one");
+    }
+    NPGE_CUDA(cudaSetDevice(ctx->device));
+    ctx->have_result = false;
+    const MsdPlan plan = make_msd_plan(p->anchor_size, ctx->g_positions);
+    const uint32_t bins_a = 1u << plan.capa;
+    if (hist_cap < bins_a) return fail(NPGE_ANCHOR_ERR_PARAMS, "hist_out too small");
+    *n_bins = bins_a;
+    const uint64_t np = ctx->n_padded, max_records = ctx->n_positions;
+    NPGE_TRY(ensure(ctx->rows, msd_rows_needed(plan, np, max_records, bins_a) * 4));
+    NPGE_TRY(ensure(ctx->blk, msd_blk_needed(plan, np, max_records, bins_a) * 4));
+    NPGE_TRY(ensure(ctx->segtab, seg_table_words(bins_a, plan) * 4));
+    NPGE_TRY(ensure(ctx->rec[0], (max_records + 16) * 8));
+    if (plan.wide) NPGE_TRY(ensure(ctx->rhi[0], (max_records + 16) * 4));
+    NPGE_TRY(ensure(ctx->counters, kCntWords * 4));
+    cudaStream_t st = ctx->stream;
+    memset(ctx->dist_ms, 0, sizeof(ctx->dist_ms));
+    ctx->dist_launches = 0;
+    NPGE_CUDA(cudaMemsetAsync(ctx->counters.ptr, 0, kCntWords * 4, st));
+    MsdBuffers mb = dist_msd_buffers(ctx, plan, bins_a);
+    std::vector<uint32_t> a_start(bins_a + 1, 0);
+    if (np) {
+        PosMap pm = {};
+        pm.delta = ptr<uint32_t>(ctx->pos_delta);
+        pm.seq_start = ptr<uint64_t>(ctx->seq_start);
+        pm.lut = ptr<uint32_t>(ctx->seq_lut);
+        pm.lut_shift = ctx->lut_shift;
+        NPGE_CUDA(cudaEventRecord(ctx->ev[0], st));
+        launch_msd_pass_a(plan, ptr<uint32_t>(ctx->packed), ptr<uint32_t>(ctx->nmask), np,
+                          mb, pm, ptr<uint32_t>(ctx->counters), st, ctx->ev_pass,
+                          &ctx->dist_launches);
+        NPGE_CUDA(cudaGetLastError());
+        NPGE_CUDA(cudaMemcpyAsync(a_start.data(), mb.seg.a_start, (bins_a + 1) * 4,
+                                  cudaMemcpyDeviceToHost, st));
+        NPGE_CUDA(cudaStreamSynchronize(st));
+        cudaEventElapsedTime(&ctx->dist_ms[0], ctx->ev[0], ctx->ev_pass[0]);
+        cudaEventElapsedTime(&ctx->dist_ms[1], ctx->ev_pass[0], ctx->ev_pass[1]);
+    }
+    for (uint32_t a = 0; a < bins_a; a++) hist_out[a] = a_start[a + 1] - a_start[a];
+    ctx->plan = plan;
+    return NPGE_ANCHOR_OK;
+}
+
+extern "C" int npge_anchor_dist_buffers(npge_anchor_ctx* ctx, uint64_t n_recv,
+                                        npge_anchor_dist_ptrs* out) {
+    if (!ctx || !out) return fail(NPGE_ANCHOR_ERR_PARAMS, "NULL argument");
+    if (!ctx->dist) return fail(NPGE_ANCHOR_ERR_STATE, "not a multi-GPU context");
+    if (n_recv > kMaxRecords) {
+        return fail(NPGE_ANCHOR_ERR_CAPACITY, "more than 2^30-1 records on one rank");
+    }
+    NPGE_CUDA(cudaSetDevice(ctx->device));
+    const MsdPlan& plan = ctx->plan;
+    NPGE_TRY(ensure(ctx->recv_rec, (n_recv + 16) * 8));
+    if (plan.wide) NPGE_TRY(ensure(ctx->recv_hi, (n_recv + 16) * 4));
+    const size_t found_bytes = ctx->g_padded / 8 + 256;
+    NPGE_TRY(ensure(ctx->found_bits, found_bytes));
+    ctx->n_recv = n_recv;
+    memset(out, 0, sizeof(*out));
+    out->send_rec = ctx->rec[0].ptr;
+    out->send_hi = plan.wide ? ctx->rhi[0].ptr : nullptr;
+    out->recv_rec = ctx->recv_rec.ptr;
+    out->recv_hi = plan.wide ? ctx->recv_hi.ptr : nullptr;
+    out->found_bits = ctx->found_bits.ptr;
+    out->found_words = found_bytes / 4;
+    out->wide = plan.wide;
+    out->n_bins = 1 << plan.capa;
+    return NPGE_ANCHOR_OK;
+}
+
+// Stage 0: pass B over the received (bucket, source) segments, unit packing, and
+// the first bucket stage (exact: sort + count + scan -> totals; anchor-similar:
+// sort + found bits).  Stage 1 (anchor-similar, after the caller has OR-reduced
+// the found bitmap): candidate rule + count + scan -> totals.
+extern "C" int npge_anchor_dist_sort(npge_anchor_ctx* ctx, const npge_anchor_params* p,
+                                     int32_t stage, uint64_t n_recv, uint32_t n_seg,
+                                     const uint32_t* seg_begin, const uint32_t* seg_end,
+                                     const uint32_t* seg_a, const uint32_t* seg_tile,
+                                     const uint32_t* a_tile0, const uint32_t* a_start,
+                                     const uint64_t* used_sorted, uint64_t n_used,
+                                     uint64_t* totals) {
+    if (!ctx || !totals) return fail(NPGE_ANCHOR_ERR_PARAMS, "NULL argument");
+    NPGE_TRY(check_params(p));
+    if (!ctx->dist || !ctx->uploaded) {
+        return fail(NPGE_ANCHOR_ERR_STATE, "npge_anchor_dist_upload has not been called");
+    }
+    if (n_recv != ctx->n_recv) {
+        return fail(NPGE_ANCHOR_ERR_STATE, "n_recv differs from npge_anchor_dist_buffers");
+    }
+    if (n_used && !used_sorted) return fail(NPGE_ANCHOR_ERR_PARAMS, "used_sorted is NULL");
+    NPGE_CUDA(cudaSetDevice(ctx->device));
+    const MsdPlan plan = ctx->plan;
+    const bool similar = p->anchor_similar != 0;
+    const uint32_t bins_a = 1u << plan.capa;
+    const uint64_t max_records = n_recv;
+    const uint32_t max_win = bucket_max_windows(plan, max_records);
+    const size_t summary_words = bucket_summary_words();
+    cudaStream_t st = ctx->stream;
+    totals[0] = totals[1] = 0;
+    if (stage == 0) {
+        if (!seg_begin || !seg_end || !seg_a || !seg_tile || !a_tile0 || !a_start) {
+            return fail(NPGE_ANCHOR_ERR_PARAMS, "NULL segment table");
+        }
+        if (n_seg == 0 || seg_tile[n_seg] > (max_records + kTile - 1) / kTile + n_seg) {
+            return fail(NPGE_ANCHOR_ERR_PARAMS, "bad segment tables");
+        }
+        const uint32_t max_seg = std::max(n_seg, bins_a);
+        NPGE_TRY(ensure(ctx->rows, msd_rows_needed(plan, ctx->n_padded, max_records, max_seg) * 4));
+        NPGE_TRY(ensure(ctx->blk, msd_blk_needed(plan, ctx->n_padded, max_records, max_seg) * 4));
+        NPGE_TRY(ensure(ctx->segtab, seg_table_words(max_seg, plan) * 4));
+        NPGE_TRY(ensure(ctx->fine_start, ((size_t(bins_a) << plan.wb) + 1) * 4));
+        NPGE_TRY(ensure(ctx->rec[1], (max_records + 16) * 8));
+        if (plan.wide) NPGE_TRY(ensure(ctx->rhi[1], (max_records + 16) * 4));
+        NPGE_TRY(ensure(ctx->bstatus, size_t(max_win + 1) * 8 + bins_a * 4));
+        NPGE_TRY(ensure(ctx->units, size_t(max_win + 1) * 16));
+        NPGE_TRY(ensure(ctx->summary, summary_words * 8));
+        NPGE_TRY(ensure(ctx->used, n_used * 8));
+        if (similar) NPGE_TRY(ensure(ctx->sel, max_records + 16));
+        ctx->dist_max_seg = max_seg;
+        MsdBuffers mb = dist_msd_buffers(ctx, plan, max_seg);
+        mb.seg.n_seg = n_seg;
+        if (n_used) {
+            NPGE_CUDA(cudaMemcpyAsync(ctx->used.ptr, used_sorted, n_used * 8,
+                                      cudaMemcpyHostToDevice, st));
+        }
+        NPGE_CUDA(cudaMemcpyAsync(mb.seg.seg_begin, seg_begin, n_seg * 4, cudaMemcpyHostToDevice, st));
+        NPGE_CUDA(cudaMemcpyAsync(mb.seg.seg_end, seg_end, n_seg * 4, cudaMemcpyHostToDevice, st));
+        NPGE_CUDA(cudaMemcpyAsync(mb.seg.seg_a, seg_a, n_seg * 4, cudaMemcpyHostToDevice, st));
+        NPGE_CUDA(cudaMemcpyAsync(mb.seg.seg_tile, seg_tile, (n_seg + 1) * 4, cudaMemcpyHostToDevice, st));
+        NPGE_CUDA(cudaMemcpyAsync(mb.seg.a_tile0, a_tile0, (bins_a + 1) * 4, cudaMemcpyHostToDevice, st));
+        NPGE_CUDA(cudaMemcpyAsync(mb.seg.a_start, a_start, (bins_a + 1) * 4, cudaMemcpyHostToDevice, st));
+        NPGE_CUDA(cudaMemsetAsync(ctx->summary.ptr, 0, summary_words * 8, st));
+        if (similar) {
+            NPGE_CUDA(cudaMemsetAsync(ctx->found_bits.ptr, 0, ctx->g_padded / 8 + 256, st));
+            NPGE_CUDA(cudaMemsetAsync(ctx->sel.ptr, 0, max_records + 16, st));
+        }
+        NPGE_CUDA(cudaEventRecord(ctx->ev[0], st));
+        if (max_records) {
+            launch_msd_pass_b(plan, ptr<uint64_t>(ctx->recv_rec), ptr<uint32_t>(ctx->recv_hi),
+                              max_records, max_seg, mb, st, ctx->ev_pass, &ctx->dist_launches);
+        } else {
+            NPGE_CUDA(cudaEventRecord(ctx->ev_pass[2], st));
+            NPGE_CUDA(cudaEventRecord(ctx->ev_pass[3], st));
+        }
+        BucketArgs a = bucket_args(ctx, plan, mb, ptr<uint64_t>(ctx->recv_rec),
+                                   ptr<uint32_t>(ctx->recv_hi), n_used, 0);
+        launch_bucket_stage(a, kBucketUnits, max_records, st, &ctx->dist_launches);
+        launch_bucket_stage(a, similar ? kBucketMark : kBucketSort, max_records, st,
+                            &ctx->dist_launches);
+        NPGE_CUDA(cudaEventRecord(ctx->ev[1], st));
+        if (!similar) launch_bucket_stage(a, kBucketScan, max_records, st, &ctx->dist_launches);
+        NPGE_CUDA(cudaGetLastError());
+        ctx->dist_n_used = n_used;
+    } else if (stage == 1) {
+        if (!similar) return fail(NPGE_ANCHOR_ERR_PARAMS, "stage 1 is for anchor-similar");
+        MsdBuffers mb = dist_msd_buffers(ctx, plan, ctx->dist_max_seg);
+        BucketArgs a = bucket_args(ctx, plan, mb, ptr<uint64_t>(ctx->recv_rec),
+                                   ptr<uint32_t>(ctx->recv_hi), ctx->dist_n_used, 0);
+        NPGE_CUDA(cudaEventRecord(ctx->ev[0], st));
+        launch_bucket_stage(a, kBucketCount, max_records, st, &ctx->dist_launches);
+        launch_bucket_stage(a, kBucketScan, max_records, st, &ctx->dist_launches);
+        NPGE_CUDA(cudaGetLastError());
+        NPGE_CUDA(cudaEventRecord(ctx->ev[1], st));
+    } else {
+        return fail(NPGE_ANCHOR_ERR_PARAMS, "stage must be 0 or 1");
+    }
+    uint64_t summary[kSumWords] = {};
+    if (max_records && (stage == 1 || !similar)) {
+        NPGE_CUDA(cudaMemcpyAsync(summary, ctx->summary.ptr, sizeof(summary),
+                                  cudaMemcpyDeviceToHost, st));
+    }
+    NPGE_CUDA(cudaStreamSynchronize(st));
+    float ms = 0;
+    if (stage == 0) {
+        cudaEventElapsedTime(&ctx->dist_ms[2], ctx->ev[0], ctx->ev_pass[2]);
+        cudaEventElapsedTime(&ctx->dist_ms[3], ctx->ev_pass[2], ctx->ev_pass[3]);
+        cudaEventElapsedTime(&ctx->dist_ms[4], ctx->ev_pass[3], ctx->ev[1]);
+    } else {
+        cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]);
+        ctx->dist_ms[5] += ms;
+    }
+    totals[0] = summary[kSumFragments];
+    totals[1] = summary[kSumBlocks];
+    return NPGE_ANCHOR_OK;
+}
+
+// Write the anchors of this rank's hash range, at most local_limit fragments
+// (the job's max-anchor-fragments minus the totals of the ranks before this one).
+extern "C" int npge_anchor_dist_emit(npge_anchor_ctx* ctx, const npge_anchor_params* p,
+                                     uint64_t local_limit, npge_anchor_stats* stats) {
+    if (!ctx) return fail(NPGE_ANCHOR_ERR_PARAMS, "ctx is NULL");
+    NPGE_TRY(check_params(p));
+    if (!ctx->dist || !ctx->uploaded) {
+        return fail(NPGE_ANCHOR_ERR_STATE, "npge_anchor_dist_upload has not been called");
+    }
+    NPGE_CUDA(cudaSetDevice(ctx->device));
+    const MsdPlan plan = ctx->plan;
+    const bool similar = p->anchor_similar != 0;
+    const uint64_t max_records = ctx->n_recv;
+    const uint64_t max_frags = std::min<uint64_t>(max_records, local_limit);
+    NPGE_TRY(ensure(ctx->r_seq, max_frags * 4));
+    NPGE_TRY(ensure(ctx->r_pos, max_frags * 4));
+    NPGE_TRY(ensure(ctx->r_ori, max_frags));
+    NPGE_TRY(ensure(ctx->r_block_off, (max_frags / 2 + 2) * 8));
+    NPGE_TRY(ensure(ctx->r_block_hash, (max_frags / 2 + 2) * 8));
+    cudaStream_t st = ctx->stream;
+    MsdBuffers mb = dist_msd_buffers(ctx, plan, ctx->dist_max_seg);
+    BucketArgs a = bucket_args(ctx, plan, mb, ptr<uint64_t>(ctx->recv_rec),
+                               ptr<uint32_t>(ctx->recv_hi), ctx->dist_n_used, local_limit);
+    NPGE_CUDA(cudaEventRecord(ctx->ev[0], st));
+    launch_bucket_stage(a, similar ? kBucketEmitSimilar : kBucketEmit, max_records, st,
+                        &ctx->dist_launches);
+    launch_bucket_stage(a, kBucketFinal, max_records, st, &ctx->dist_launches);
+    NPGE_CUDA(cudaGetLastError());
+    NPGE_CUDA(cudaEventRecord(ctx->ev[1], st));
+    uint64_t summary[kSumWords];
+    NPGE_CUDA(cudaMemcpyAsync(summary, ctx->summary.ptr, sizeof(summary),
+                              cudaMemcpyDeviceToHost, st));
+    NPGE_CUDA(cudaStreamSynchronize(st));
+    cudaEventElapsedTime(&ctx->dist_ms[6], ctx->ev[0], ctx->ev[1]);
+    npge_anchor_stats& s = ctx->stats;
+    memset(&s, 0, sizeof(s));
+    s.n_positions = ctx->n_bases;
+    s.n_windows = max_records;  // records this rank sorted
+    s.n_fragments = summary[kSumEmitted];
+    s.n_blocks = summary[kSumBlocksEmitted];
+    s.digest[0] = summary[kSumDigest0];
+    s.digest[1] = summary[kSumDigest1];
+    s.radix_passes = uint32_t(2 + plan.smem_passes);
+    s.gpu_launches = ctx->dist_launches;
+    // stages: [count A] [pass A] [count B] [pass B] [bucket sort] [count (similar)] [emit]
+    s.ms_hist = ctx->dist_ms[0];
+    for (int i = 0; i < 6; i++) s.ms_pass[i] = ctx->dist_ms[i + 1];
+    s.ms_sort = ctx->dist_ms[0] + ctx->dist_ms[1] + ctx->dist_ms[2] + ctx->dist_ms[3];
+    s.ms_group = ctx->dist_ms[4] + ctx->dist_ms[5] + ctx->dist_ms[6];
+    s.ms_total = s.ms_sort + s.ms_group;  // device time of this rank's kernels
+    const int model_passes = (2 * p->anchor_size + 7) / 8;
+    s.bytes_algorithmic = uint64_t(double(ctx->n_bases) * (32.375 + 24.0 * model_passes)) +
+                          9 * s.n_fragments + 16 * s.n_blocks;
+    const double rec = plan.wide ? 12.0 : 8.0;
+    s.bytes_moved = uint64_t(double(ctx->n_bases) * 0.75 + double(ctx->n_positions) * rec +
+                             double(max_records) * rec * (similar ? 6.0 : 4.0)) +
+                    9 * s.n_fragments + 16 * s.n_blocks;
+    ctx->total_selected = summary[kSumFragments];
+    ctx->msd = true;
+    ctx->last_params = *p;
+    ctx->last_params.max_anchor_fragments = int64_t(std::min<uint64_t>(local_limit, uint64_t(INT64_MAX)));
+    ctx->have_result = true;
+    if (stats) *stats = s;
+    return NPGE_ANCHOR_OK;
 }

@@ -766,51 +766,72 @@ uint32_t bucket_max_windows(const MsdPlan& plan, uint64_t max_records) {
     return uint32_t((max_records + kWindow - 1) / kWindow) + (2u << plan.capa) + 1;
 }
 
-void launch_bucket(const BucketArgs& a, bool similar, uint64_t max_records,
-                   cudaStream_t s, cudaEvent_t* ev, uint32_t* launches) {
+// The stages of the bucket sort, one launcher each so that the multi-GPU driver
+// can put its collectives between them (found bitmap, totals).
+//   kBucketUnits   pack the bins into units
+//   kBucketSort    sort every unit + count its anchors (parity / exact)
+//   kBucketMark    sort every unit + set the found bits (anchor-similar)
+//   kBucketCount   candidate rule + count on the sorted units (anchor-similar)
+//   kBucketScan    exclusive scan of the unit totals (summary: totals before the cut)
+//   kBucketEmit / kBucketEmitSimilar   write the anchors
+//   kBucketFinal   digest, emitted counts, closing block offset
+void launch_bucket_stage(const BucketArgs& a, int stage, uint64_t max_records,
+                         cudaStream_t s, uint32_t* launches) {
     const uint32_t grid = bucket_max_windows(a.plan, max_records);
-    if (max_records) {
-        const uint32_t bins_a = 1u << a.plan.capa;
-        uint32_t* unit_cnt = reinterpret_cast<uint32_t*>(a.unit_tot);  // free until the sort
-        unit_build_kernel<false><<<(bins_a + 7) / 8, 256, 0, s>>>(a, unit_cnt);
-        unit_build_kernel<true><<<(bins_a + 7) / 8, 256, 0, s>>>(a, unit_cnt);
-        *launches += 2;
-    }
 #define NPGE_LAUNCH(KERNEL, W)                                                  \
     do {                                                                        \
         set_smem(KERNEL, sizeof(BucketSmem<W>));                                \
         KERNEL<<<grid, kRT, sizeof(BucketSmem<W>), s>>>(a);                     \
         *launches += 1;                                                         \
     } while (0)
-    if (max_records) {
-        if (similar) {
-            if (a.plan.wide) {
-                NPGE_LAUNCH((bucket_sort_kernel<true, 1>), true);
-                NPGE_LAUNCH((bucket_count_kernel<true>), true);
-            } else {
-                NPGE_LAUNCH((bucket_sort_kernel<false, 1>), false);
-                NPGE_LAUNCH((bucket_count_kernel<false>), false);
-            }
-        } else {
-            if (a.plan.wide) NPGE_LAUNCH((bucket_sort_kernel<true, 0>), true);
-            else NPGE_LAUNCH((bucket_sort_kernel<false, 0>), false);
-        }
-        if (ev) cudaEventRecord(ev[0], s);
+#define NPGE_LAUNCH_W(NAME, ...)                                                \
+    do {                                                                        \
+        if (a.plan.wide) NPGE_LAUNCH((NAME<true, ##__VA_ARGS__>), true);        \
+        else NPGE_LAUNCH((NAME<false, ##__VA_ARGS__>), false);                  \
+    } while (0)
+    if (stage == kBucketFinal) {
+        bucket_finalize_kernel<<<1, 32, 0, s>>>(a);
+        *launches += 1;
+        return;
+    }
+    if (max_records == 0) return;
+    switch (stage) {
+    case kBucketUnits: {
+        const uint32_t bins_a = 1u << a.plan.capa;
+        uint32_t* unit_cnt = reinterpret_cast<uint32_t*>(a.unit_tot);  // free until the sort
+        unit_build_kernel<false><<<(bins_a + 7) / 8, 256, 0, s>>>(a, unit_cnt);
+        unit_build_kernel<true><<<(bins_a + 7) / 8, 256, 0, s>>>(a, unit_cnt);
+        *launches += 2;
+        break;
+    }
+    case kBucketSort: NPGE_LAUNCH_W(bucket_sort_kernel, 0); break;
+    case kBucketMark: NPGE_LAUNCH_W(bucket_sort_kernel, 1); break;
+    case kBucketCount: NPGE_LAUNCH_W(bucket_count_kernel); break;
+    case kBucketScan:
         unit_scan_kernel<<<1, 1024, 0, s>>>(a);
         *launches += 1;
-        if (similar) {
-            if (a.plan.wide) NPGE_LAUNCH((bucket_emit_kernel<true, 2>), true);
-            else NPGE_LAUNCH((bucket_emit_kernel<false, 2>), false);
-        } else {
-            if (a.plan.wide) NPGE_LAUNCH((bucket_emit_kernel<true, 0>), true);
-            else NPGE_LAUNCH((bucket_emit_kernel<false, 0>), false);
-        }
-    } else if (ev) {
-        cudaEventRecord(ev[0], s);
+        break;
+    case kBucketEmit: NPGE_LAUNCH_W(bucket_emit_kernel, 0); break;
+    case kBucketEmitSimilar: NPGE_LAUNCH_W(bucket_emit_kernel, 2); break;
     }
+#undef NPGE_LAUNCH_W
 #undef NPGE_LAUNCH
-    bucket_finalize_kernel<<<1, 32, 0, s>>>(a);
-    *launches += 1;
+}
+
+void launch_bucket(const BucketArgs& a, bool similar, uint64_t max_records,
+                   cudaStream_t s, cudaEvent_t* ev, uint32_t* launches) {
+    launch_bucket_stage(a, kBucketUnits, max_records, s, launches);
+    if (similar) {
+        launch_bucket_stage(a, kBucketMark, max_records, s, launches);
+        launch_bucket_stage(a, kBucketCount, max_records, s, launches);
+    } else {
+        launch_bucket_stage(a, kBucketSort, max_records, s, launches);
+    }
+    if (ev) cudaEventRecord(ev[0], s);
+    launch_bucket_stage(a, kBucketScan, max_records, s, launches);
+    launch_bucket_stage(a, similar ? kBucketEmitSimilar : kBucketEmit, max_records, s,
+                        launches);
+    launch_bucket_stage(a, kBucketFinal, max_records, s, launches);
 }
 
 }  // namespace npge_b200

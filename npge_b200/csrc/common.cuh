@@ -155,6 +155,18 @@ struct npge_anchor_ctx {
     int lut_shift = 12;
     npge_b200::MsdPlan plan;
     bool msd = true;          // which path produced the result
+    // several GPUs (npge_anchor_dist_*): job-wide sequence table and exchange
+    bool dist = false;
+    std::vector<npge_b200::SeqEntry> gseqs;  // ALL sequences, job-wide scan order
+    uint64_t g_positions = 0;                // job-wide positions (with pads)
+    uint64_t g_padded = 0;
+    npge_b200::DeviceBuffer g_seq_start, g_seq_caller, g_seq_lut, pos_delta;
+    npge_b200::DeviceBuffer recv_rec, recv_hi;
+    uint64_t n_recv = 0;
+    uint32_t dist_launches = 0;
+    uint32_t dist_max_seg = 0;
+    uint64_t dist_n_used = 0;
+    float dist_ms[8] = {};
     // device result
     npge_b200::DeviceBuffer r_seq, r_pos, r_ori, r_block_off, r_block_hash;
     npge_b200::DeviceBuffer scan_status, summary;

@@ -138,6 +138,12 @@ struct BucketArgs {
 size_t bucket_summary_words();
 uint32_t bucket_max_windows(const MsdPlan& plan, uint64_t max_records);
 // sort (+ found bits / count), scan of the unit totals, emit
+enum {
+    kBucketUnits, kBucketSort, kBucketMark, kBucketCount, kBucketScan, kBucketEmit,
+    kBucketEmitSimilar, kBucketFinal
+};
+void launch_bucket_stage(const BucketArgs& a, int stage, uint64_t max_records,
+                         cudaStream_t s, uint32_t* launches);
 // ev (optional, 1 event): recorded after the sort (+ count) kernels
 void launch_bucket(const BucketArgs& a, bool similar, uint64_t max_records,
                    cudaStream_t s, cudaEvent_t* ev, uint32_t* launches);
