@@ -1,0 +1,468 @@
+"""AnchorFinder over several GPUs: one process and one CUDA context per GPU.
+
+SURVEY 8e: the reference parallelises AnchorFinder over sequences with a
+thread pool that shares one Bloom filter and one hash -> positions map
+(src/algo/AnchorFinder.cpp:252-292, 330-357).  Here positions are sharded
+over the ranks and canonical k-mers are repartitioned by hash range:
+
+  upload       every rank ends up with a contiguous range of the job-wide scan
+               order (sequences by size, descending; ties by caller index),
+               whatever the placement it was given (an all-to-all of the
+               sequences moves what is misplaced)
+  pass A       local: k-mers -> records partitioned by the top key bits
+  all-gather   of the per-bucket counts; contiguous bucket ranges are cut so that
+               every rank receives about the same number of records
+  all-to-all   of the records (NCCL over NVLink; the only bulk exchange)
+  pass B, bucket sort, count   local, over (bucket, source rank) segments
+  all-reduce   of the found bitmap (anchor-similar only: found(p - 1) may
+               belong to another rank's hash range)
+  all-gather   of the totals -> every rank's share of max-anchor-fragments
+  emit         local: rank r holds the r-th slice of the one-GPU result
+
+The per-rank stages are the npge_anchor_dist_* entry points of the C ABI
+(include/npge_anchor.h); this module owns the collectives and the small host
+tables between them.  `stages` can be replaced by an object with the same
+methods (the CPU tests drive the host logic with a numpy stand-in).
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _abi
+from .engine import AnchorEngine, AnchorError, AnchorResult, _stats_dict, concat
+
+TILE = 4096  # records per pass-B tile (kTile in csrc/common.cuh)
+
+
+# ---- host tables (pure functions; tests/test_dist_cpu.py) --------------------------
+def scan_order(sizes, k):
+    """Job-wide scan order: indices of the sequences with size >= k, by size
+    descending, ties by caller index (SeqI.hpp:45-57; api.cu upload)."""
+    sizes = np.asarray(sizes, dtype=np.int64)
+    idx = np.flatnonzero(sizes >= k)
+    return idx[np.argsort(-sizes[idx], kind="stable")]
+
+
+def plan_shards(sizes, k, world):
+    """Cuts the scan order into `world` contiguous ranges of about equal bases.
+
+    Returns (order, cuts): rank r owns order[cuts[r]:cuts[r + 1]]."""
+    order = scan_order(sizes, k)
+    sz = np.asarray(sizes, dtype=np.int64)[order]
+    csum = np.concatenate([[0], np.cumsum(sz)])
+    total = int(csum[-1])
+    cuts = [0]
+    for r in range(1, world):
+        target = total * r / world
+        # the boundary whose prefix sum is nearest to the target
+        j = int(np.searchsorted(csum, target))
+        if j > 0 and target - csum[j - 1] < csum[min(j, len(sz))] - target:
+            j -= 1
+        cuts.append(min(max(j, cuts[-1]), len(sz)))
+    cuts.append(len(sz))
+    return order, np.asarray(cuts, dtype=np.int64)
+
+
+def global_starts(sizes_in_scan_order):
+    """First job-wide position of every sequence (+ the end): one pad position
+    after each sequence, as in the one-GPU layout."""
+    s = np.asarray(sizes_in_scan_order, dtype=np.uint64)
+    out = np.zeros(len(s) + 1, dtype=np.uint64)
+    out[1:] = np.cumsum(s + np.uint64(1))
+    return out
+
+
+def bucket_ranges(hist_all, world):
+    """Contiguous A-bucket ranges, balanced by records.
+
+    hist_all: [world, bins] records of every source rank per bucket.  Returns
+    cuts[world + 1]: rank r receives the buckets cuts[r] .. cuts[r + 1] - 1."""
+    tot = np.asarray(hist_all, dtype=np.int64).sum(axis=0)
+    csum = np.concatenate([[0], np.cumsum(tot)])
+    total = int(csum[-1])
+    cuts = [0]
+    for r in range(1, world):
+        target = total * r / world
+        j = int(np.searchsorted(csum, target))
+        if j > 0 and target - csum[j - 1] < csum[min(j, len(tot))] - target:
+            j -= 1
+        cuts.append(min(max(j, cuts[-1]), len(tot)))
+    cuts.append(len(tot))
+    return np.asarray(cuts, dtype=np.int64)
+
+
+def exchange_splits(hist_all, cuts, rank):
+    """(send_splits, recv_splits) of the record all-to-all, in records."""
+    h = np.asarray(hist_all, dtype=np.int64)
+    world = h.shape[0]
+    send = [int(h[rank, cuts[d]:cuts[d + 1]].sum()) for d in range(world)]
+    recv = [int(h[s, cuts[rank]:cuts[rank + 1]].sum()) for s in range(world)]
+    return send, recv
+
+
+def segment_tables(hist_all, cuts, rank):
+    """Pass-B tables of rank `rank`: one segment per (owned bucket, source rank)
+    with records, bucket-major so that every bucket's tiles are consecutive
+    and its sources come in rank (= position) order.
+
+    The receive buffer holds source 0's slice, then source 1's, ...; inside a
+    slice the buckets ascend.  Returns a dict of uint32 arrays (SegTables in
+    csrc/kernels.h) and n_recv."""
+    h = np.asarray(hist_all, dtype=np.int64)
+    world, bins = h.shape
+    lo, hi = int(cuts[rank]), int(cuts[rank + 1])
+    mine = h[:, lo:hi]                                   # [world, owned]
+    src_base = np.concatenate([[0], np.cumsum(mine.sum(axis=1))])[:-1]
+    inside = np.cumsum(mine, axis=1) - mine              # offset inside the slice
+    begin = (src_base[:, None] + inside)                 # [world, owned]
+    seg_begin, seg_end, seg_a = [], [], []
+    a_count = np.zeros(bins, dtype=np.int64)
+    a_tiles = np.zeros(bins, dtype=np.int64)
+    for j in range(hi - lo):
+        for s in range(world):
+            c = int(mine[s, j])
+            if c == 0:
+                continue
+            seg_begin.append(int(begin[s, j]))
+            seg_end.append(int(begin[s, j]) + c)
+            seg_a.append(lo + j)
+            a_tiles[lo + j] += (c + TILE - 1) // TILE
+        a_count[lo + j] = int(mine[:, j].sum())
+    if not seg_a:  # nothing received: one empty segment keeps the tables valid
+        seg_begin, seg_end, seg_a = [0], [0], [lo if lo < bins else 0]
+    sb = np.asarray(seg_begin, dtype=np.int64)
+    se = np.asarray(seg_end, dtype=np.int64)
+    tiles = (se - sb + TILE - 1) // TILE
+    u32 = lambda x: np.ascontiguousarray(np.asarray(x, dtype=np.uint32))
+    return dict(
+        n_seg=len(sb), seg_begin=u32(sb), seg_end=u32(se), seg_a=u32(seg_a),
+        seg_tile=u32(np.concatenate([[0], np.cumsum(tiles)])),
+        a_tile0=u32(np.concatenate([[0], np.cumsum(a_tiles)])),
+        a_start=u32(np.concatenate([[0], np.cumsum(a_count)])),
+        n_recv=int(mine.sum()))
+
+
+def local_limits(totals, limit):
+    """Share of max-anchor-fragments of every rank: the cut runs over the list
+    ordered by hash, and the ranks own ascending hash ranges."""
+    out, before = [], 0
+    for t in totals:
+        out.append(int(min(max(limit - before, 0), t)))
+        before += int(t)
+    return out
+
+
+# ---- the per-rank device stages (C ABI) ----------------------------------------------
+class _DevMem:
+    """__cuda_array_interface__ view of a device buffer the library owns."""
+
+    def __init__(self, ptr, n, typestr):
+        self.__cuda_array_interface__ = {
+            "shape": (int(n),), "typestr": typestr, "data": (int(ptr), False),
+            "version": 3, "strides": None}
+
+
+class CudaStages(AnchorEngine):
+    """npge_anchor_dist_* on one GPU.  Tensors returned by buffers() alias the
+    library's device memory and stay valid until the next upload / buffers()."""
+
+    def __init__(self, device=0):
+        AnchorEngine.__init__(self, device)
+        self.device = device
+
+    def dist_upload(self, k, seqs, local_gstart, global_start, global_caller):
+        bases, offsets = concat(seqs)
+        lg = np.ascontiguousarray(local_gstart, dtype=np.uint64)
+        gs = np.ascontiguousarray(global_start, dtype=np.uint64)
+        gc = np.ascontiguousarray(global_caller, dtype=np.uint32)
+        self._check(self._lib.npge_anchor_dist_upload(
+            self._ctx, k, bases.ctypes.data, offsets.ctypes.data, len(offsets) - 1,
+            lg.ctypes.data, gs.ctypes.data, gc.ctypes.data, len(gc)))
+
+    def dist_pass_a(self, params):
+        hist = np.zeros(1024, dtype=np.uint32)
+        n_bins = C.c_uint32()
+        self._check(self._lib.npge_anchor_dist_pass_a(
+            self._ctx, C.byref(params), hist.ctypes.data, len(hist), C.byref(n_bins)))
+        return hist[:n_bins.value].copy()
+
+    def dist_buffers(self, n_send, n_recv):
+        import torch
+        p = _abi.DistPtrs()
+        self._check(self._lib.npge_anchor_dist_buffers(self._ctx, n_recv, C.byref(p)))
+        dev = torch.device("cuda", self.device)
+
+        def view(ptr, n, typestr):
+            if not ptr:
+                return None
+            if n == 0:
+                return torch.zeros(0, device=dev,
+                                   dtype=torch.int64 if typestr == "<i8" else torch.int32)
+            return torch.as_tensor(_DevMem(ptr, n, typestr), device=dev)
+
+        return dict(send_rec=view(p.send_rec, n_send, "<i8"),
+                    send_hi=view(p.send_hi, n_send, "<i4") if p.wide else None,
+                    recv_rec=view(p.recv_rec, n_recv, "<i8"),
+                    recv_hi=view(p.recv_hi, n_recv, "<i4") if p.wide else None,
+                    found=view(p.found_bits, p.found_words, "<i4"))
+
+    def dist_sort(self, params, stage, tables, used):
+        u, up = self._used(used)
+        totals = (C.c_uint64 * 2)()
+        t = tables
+        self._check(self._lib.npge_anchor_dist_sort(
+            self._ctx, C.byref(params), stage, t["n_recv"], t["n_seg"],
+            t["seg_begin"].ctypes.data, t["seg_end"].ctypes.data,
+            t["seg_a"].ctypes.data, t["seg_tile"].ctypes.data,
+            t["a_tile0"].ctypes.data, t["a_start"].ctypes.data, up, len(u),
+            C.byref(totals)))
+        return int(totals[0]), int(totals[1])
+
+    def dist_emit(self, params, local_limit):
+        s = _abi.Stats()
+        self._check(self._lib.npge_anchor_dist_emit(
+            self._ctx, C.byref(params), local_limit, C.byref(s)))
+        return _stats_dict(s)
+
+
+# ---- collectives -----------------------------------------------------------------------
+class _Comm:
+    """torch.distributed with the tensors where the backend wants them: NCCL
+    works on the device buffers in place; gloo (CPU tests, or several ranks on
+    one GPU) goes through host copies."""
+
+    def __init__(self, group=None):
+        import torch
+        import torch.distributed as dist
+        self.torch, self.dist, self.group = torch, dist, group
+        self.rank = dist.get_rank(group)
+        self.world = dist.get_world_size(group)
+        self.nccl = dist.get_backend(group) == "nccl"
+
+    def gather_objects(self, obj):
+        out = [None] * self.world
+        self.dist.all_gather_object(out, obj, group=self.group)
+        return out
+
+    def gather_array(self, arr, device=None):
+        """all-gather of equal-length int64 numpy arrays -> [world, n]"""
+        t = self.torch.from_numpy(np.ascontiguousarray(arr, dtype=np.int64))
+        if self.nccl:
+            t = t.to(device)
+        out = self.torch.empty(self.world * t.numel(), dtype=t.dtype, device=t.device)
+        self.dist.all_gather_into_tensor(out, t.reshape(-1), group=self.group)
+        return out.cpu().numpy().reshape((self.world,) + tuple(t.shape))
+
+    def all_to_all(self, out, inp, out_splits, in_splits):
+        if self.nccl or not out.is_cuda:
+            self.dist.all_to_all_single(out, inp, list(out_splits), list(in_splits),
+                                        group=self.group)
+            return
+        o, i = out.cpu(), inp.cpu()
+        self._a2a_host(o, i, out_splits, in_splits)
+        out.copy_(o)
+
+    def _a2a_host(self, o, i, out_splits, in_splits):
+        try:
+            self.dist.all_to_all_single(o, i, list(out_splits), list(in_splits),
+                                        group=self.group)
+        except RuntimeError:  # gloo builds without alltoall: pairwise exchange
+            ins = list(i.split(list(in_splits)))
+            outs = list(o.split(list(out_splits)))
+            outs[self.rank].copy_(ins[self.rank])
+            for step in range(1, self.world):
+                dst = (self.rank + step) % self.world
+                src = (self.rank - step) % self.world
+                req = self.dist.isend(ins[dst].contiguous(), dst, group=self.group)
+                self.dist.recv(outs[src], src, group=self.group)
+                req.wait()
+
+    def sum_(self, t):
+        if self.nccl or not t.is_cuda:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM, group=self.group)
+            return
+        h = t.cpu()
+        self.dist.all_reduce(h, op=self.dist.ReduceOp.SUM, group=self.group)
+        t.copy_(h)
+
+    def barrier(self):
+        self.dist.barrier(group=self.group)
+
+
+class DistAnchorFinder:
+    """AnchorFinder of one job over all ranks of a process group.
+
+    Every rank calls the same methods with its own sequences (any placement);
+    fetch() returns the rank's slice of the job's result (ascending hash
+    ranges), with frag_seq = job-wide caller index: the ranks' sequences
+    numbered one after the other in rank order."""
+
+    def __init__(self, device=0, group=None, stages=None):
+        self.comm = _Comm(group)
+        self.rank, self.world = self.comm.rank, self.comm.world
+        self.stages = stages if stages is not None else CudaStages(device)
+        self.device = device
+        self._k = None
+        self.exchange_ms = {}
+
+    # -- upload ------------------------------------------------------------------------
+    def _rebalance(self, seqs, k):
+        """Moves the sequences so that every rank holds a contiguous range of the
+        job-wide scan order.  Returns (local seqs in scan order, their job-wide
+        scan indices, sizes of all sequences in scan order, their job-wide
+        caller indices)."""
+        torch = self.comm.torch
+        sizes_by_rank = self.comm.gather_objects([int(len(s)) for s in seqs])
+        counts = [len(x) for x in sizes_by_rank]
+        base = np.concatenate([[0], np.cumsum(counts)]).astype(np.int64)
+        sizes = np.asarray([x for r in sizes_by_rank for x in r], dtype=np.int64)
+        origin = np.repeat(np.arange(self.world), counts)
+        order, cuts = plan_shards(sizes, k, self.world)
+        owner = np.repeat(np.arange(self.world), np.diff(cuts))  # per scan index
+        src_of = origin[order]
+        # what I send to d / receive from s, in scan order
+        send_idx = [[int(i) for i in np.flatnonzero((src_of == self.rank) & (owner == d))]
+                    for d in range(self.world)]
+        recv_idx = [[int(i) for i in np.flatnonzero((src_of == s) & (owner == self.rank))]
+                    for s in range(self.world)]
+        mine = {}
+        moved = any(int(((src_of == s) & (owner != s)).sum()) for s in range(self.world))
+        if moved:
+            def local(i):
+                return np.asarray(seqs[int(order[i] - base[self.rank])], dtype=np.uint8)
+            parts = [local(i) for d in range(self.world) for i in send_idx[d]]
+            send = torch.from_numpy(np.concatenate(parts) if parts
+                                    else np.zeros(0, np.uint8))
+            in_splits = [int(sum(sizes[order[i]] for i in send_idx[d]))
+                         for d in range(self.world)]
+            out_splits = [int(sum(sizes[order[i]] for i in recv_idx[s]))
+                          for s in range(self.world)]
+            recv = torch.empty(sum(out_splits), dtype=torch.uint8)
+            if self.comm.nccl:
+                dev = torch.device("cuda", self.device)
+                send, recv_d = send.to(dev), recv.to(dev)
+                self.comm.all_to_all(recv_d, send, out_splits, in_splits)
+                recv = recv_d.cpu()
+            else:
+                self.comm._a2a_host(recv, send, out_splits, in_splits)
+            buf, off = recv.numpy(), 0
+            for s in range(self.world):
+                for i in recv_idx[s]:
+                    n = int(sizes[order[i]])
+                    mine[i] = buf[off:off + n]
+                    off += n
+        else:
+            for i in recv_idx[self.rank]:
+                mine[i] = np.asarray(seqs[int(order[i] - base[self.rank])], dtype=np.uint8)
+        idx = sorted(mine)
+        return [mine[i] for i in idx], np.asarray(idx, dtype=np.int64), sizes[order], order
+
+    def upload(self, seqs, k):
+        if isinstance(seqs, tuple):
+            bases, offsets = seqs
+            seqs = [bases[int(offsets[i]):int(offsets[i + 1])]
+                    for i in range(len(offsets) - 1)]
+        local, idx, job_sizes, job_caller = self._rebalance(seqs, k)
+        gstart = global_starts(job_sizes)
+        self.n_job_bases = int(job_sizes.sum())
+        self.n_local_bases = int(sum(len(s) for s in local))
+        self.stages.dist_upload(k, local, gstart[idx], gstart, job_caller)
+        self._k = k
+
+    # -- find --------------------------------------------------------------------------
+    def _timed(self, name, fn):
+        """Device time of a collective (CUDA events when the tensors are on a GPU)."""
+        torch = self.comm.torch
+        if not (self.comm.nccl and torch.cuda.is_available()):
+            fn()
+            return
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        fn()
+        e1.record()
+        e1.synchronize()
+        self.exchange_ms[name] = self.exchange_ms.get(name, 0.0) + e0.elapsed_time(e1)
+
+    def find_device(self, k=None, similar=True, max_frags=100000, used=None):
+        """All stages up to the anchors in device memory.  Returns job-wide
+        counts and digest (the same on every rank) + this rank's stage times."""
+        k = self._k if k is None else k
+        if k != self._k:
+            raise AnchorError(_abi.ERR_STATE, "anchor-size differs from the uploaded one")
+        st, comm = self.stages, self.comm
+        params = _abi.Params(k, int(bool(similar)), int(max_frags))
+        self.exchange_ms = {}
+        dev = comm.torch.device("cuda", self.device) if comm.nccl else None
+        hist = st.dist_pass_a(params)
+        hist_all = comm.gather_array(hist, dev)
+        cuts = bucket_ranges(hist_all, self.world)
+        send_splits, recv_splits = exchange_splits(hist_all, cuts, self.rank)
+        tables = segment_tables(hist_all, cuts, self.rank)
+        buf = st.dist_buffers(sum(send_splits), tables["n_recv"])
+        self._timed("records", lambda: comm.all_to_all(
+            buf["recv_rec"], buf["send_rec"], recv_splits, send_splits))
+        if buf["send_hi"] is not None:
+            self._timed("records", lambda: comm.all_to_all(
+                buf["recv_hi"], buf["send_hi"], recv_splits, send_splits))
+        totals = st.dist_sort(params, 0, tables, used)
+        if similar:
+            self._timed("found_bits", lambda: comm.sum_(buf["found"]))
+            totals = st.dist_sort(params, 1, tables, used)
+        tot_all = comm.gather_array(np.asarray(totals, dtype=np.int64), dev)
+        limits = local_limits(tot_all[:, 0], int(max_frags))
+        s = st.dist_emit(params, limits[self.rank])
+        self.local_stats = s
+        d = np.asarray([s["n_fragments"], s["n_blocks"], s["n_windows"],
+                        s["gpu_launches"]], dtype=np.int64)
+        dg = np.asarray([s["digest"][0], s["digest"][1]], dtype=np.uint64).view(np.int64)
+        job = comm.gather_array(np.concatenate([d, dg]), dev)
+        mask = (1 << 64) - 1
+        out = dict(s)
+        out.update(
+            n_fragments=int(job[:, 0].sum()), n_blocks=int(job[:, 1].sum()),
+            n_windows=int(job[:, 2].sum()), gpu_launches=int(job[:, 3].sum()),
+            digest=(sum(int(x) & mask for x in job[:, 4]) & mask,
+                    sum(int(x) & mask for x in job[:, 5]) & mask),
+            n_positions=self.n_job_bases, local_fragments=s["n_fragments"],
+            local_records=s["n_windows"], total_selected=int(tot_all[:, 0].sum()),
+            exchange_ms=dict(self.exchange_ms),
+            bucket_cuts=[int(c) for c in cuts])
+        return out
+
+    def fetch(self):
+        """This rank's slice of the job's anchors.  new_used is the job's list
+        (every distinct hash but the job's first), the same on every rank."""
+        r = self.stages.fetch()
+        parts = self.comm.gather_objects((r.new_used, r.digest))
+        alln = np.concatenate([np.asarray(p[0], dtype=np.uint64) for p in parts])
+        r.new_used = alln[1:]
+        mask = (1 << 64) - 1
+        r.job_digest = (sum(p[1][0] for p in parts) & mask,
+                        sum(p[1][1] for p in parts) & mask)
+        return r
+
+    def find(self, seqs, k, similar=True, max_frags=100000, used=None):
+        """upload + find_device + fetch (host buffers in, host arrays out)."""
+        self.upload(seqs, k)
+        stats = self.find_device(k, similar=similar, max_frags=max_frags, used=used)
+        r = self.fetch()
+        r.job = stats
+        return r
+
+    def gather(self, r):
+        """The whole job's result on every rank (tests, small jobs)."""
+        parts = self.comm.gather_objects(
+            (r.block_offsets, r.block_hash, r.frag_seq, r.frag_min_pos, r.frag_ori))
+        out = AnchorResult.__new__(AnchorResult)
+        offs, base = [np.zeros(1, np.uint64)], 0
+        for p in parts:
+            offs.append(p[0][1:] + np.uint64(base))
+            base += int(p[0][-1])
+        out.block_offsets = np.concatenate(offs)
+        out.block_hash = np.concatenate([p[1] for p in parts])
+        out.frag_seq = np.concatenate([p[2] for p in parts])
+        out.frag_min_pos = np.concatenate([p[3] for p in parts])
+        out.frag_ori = np.concatenate([p[4] for p in parts])
+        out.new_used = r.new_used
+        out.digest = getattr(r, "job_digest", None)
+        return out

@@ -1,0 +1,23 @@
+"""Multi-GPU path on real devices: world_size-2 / -3 jobs through the
+npge_anchor_dist_* entry points of the C ABI, compared with the oracle on the
+whole job (bit-exact).  With fewer GPUs than ranks the ranks share cuda:0 and
+the collectives go through gloo; with enough GPUs they use NCCL."""
+import pytest
+
+from test_dist_cpu import launch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("k", [12, 20, 27])
+def test_two_ranks_tiny(k):
+    launch(2, ["cuda", "tiny", 1.0, k, "interleaved"])
+
+
+def test_three_ranks_tiny_blocks():
+    launch(3, ["cuda", "tiny", 1.0, 16, "blocks"])
+
+
+def test_two_ranks_small():
+    out = launch(2, ["cuda", "small", 1.0, 20, "interleaved"])
+    assert "blocks" in out[0]
