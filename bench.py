@@ -225,11 +225,9 @@ def run_gpu(args, rank, world, local_rank):
         runner = SingleRunner(eng, bases, offsets)
     else:
         from npge_b200.dist import DistAnchorFinder
-        names, seqs, seq_base, n_seqs_total = synth.generate_shard(
-            WORKLOAD, rank, world)
+        names, seqs = synth.generate_shard(WORKLOAD, rank, world)
         bases, offsets = concat(seqs)
-        runner = DistRunner(DistAnchorFinder(local_rank, rank, world), bases,
-                            offsets, seq_base, n_seqs_total)
+        runner = DistRunner(DistAnchorFinder(local_rank), bases, offsets)
     n_local = int(offsets[-1])
     n_total = n_local
     if world > 1:
@@ -256,12 +254,20 @@ def run_gpu(args, rank, world, local_rank):
         sampler.start()
     barrier()
     ev_ms, pass_ms, kern_launches = 0.0, [], 0
-    hist_ms = group_ms = 0.0
+    hist_ms = group_ms = step_ms = 0.0
+    exch_ms = {}
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     wall0 = time.perf_counter()
     for _ in range(args.steps):
         flush.fill_(1)
         torch.cuda.synchronize()
+        e0.record()
         stats = runner.step(K, False, BIG)
+        e1.record()
+        e1.synchronize()
+        step_ms += e0.elapsed_time(e1)
+        for nm, v in stats.get("exchange_ms", {}).items():
+            exch_ms[nm] = exch_ms.get(nm, 0.0) + v
         ev_ms += stats["ms_total"]
         hist_ms += stats["ms_hist"]
         group_ms += stats["ms_group"]
@@ -270,7 +276,10 @@ def run_gpu(args, rank, world, local_rank):
     barrier()
     wall = time.perf_counter() - wall0
     clocks = sampler.stop() if rank == 0 else None
-    t_dev = ev_ms / 1e3
+    # one GPU: the library's own events on its stream (first kernel .. last
+    # kernel of every step); several GPUs: events around the whole step, i.e.
+    # kernels + collectives + the host tables between them
+    t_dev = (ev_ms if world == 1 else step_ms) / 1e3
     if world > 1:
         t = torch.tensor([t_dev], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -292,8 +301,11 @@ def run_gpu(args, rank, world, local_rank):
     for _ in range(dsteps):
         flush.fill_(1)
         torch.cuda.synchronize()
+        e0.record()
         st = runner.step(K, True, 100000)
-        dflt_ms += st["ms_total"]
+        e1.record()
+        e1.synchronize()
+        dflt_ms += st["ms_total"] if world == 1 else e0.elapsed_time(e1)
         kern_launches += 0  # not part of the timed headline region
     if world > 1:
         t = torch.tensor([dflt_ms], dtype=torch.float64, device="cuda")
@@ -318,6 +330,10 @@ def run_gpu(args, rank, world, local_rank):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_t = float(t.item())
     h2d = int(bases.nbytes + offsets.nbytes)
+    if world > 1:  # job totals of the copies
+        t = torch.tensor([h2d, int(d2h)], dtype=torch.int64, device="cuda")
+        dist.all_reduce(t)
+        h2d, d2h = int(t[0].item()), int(t[1].item())
     runner.find_host(pinned_np, offsets, K, True, 100000)
     barrier()
     t0 = time.perf_counter()
@@ -329,7 +345,7 @@ def run_gpu(args, rank, world, local_rank):
     if rank != 0:
         return
     value = n_total * args.steps / t_dev / 1e9
-    nw = parity_stats["n_windows"]
+    nw = parity_stats.get("local_records", parity_stats["n_windows"])  # rank 0's
     passes = parity_stats["radix_passes"]
     # stages of one step (CUDA events inside npge_anchor_find_device):
     # count A + scan | pass A | count B + scan | pass B | bucket sort | scan + emit
@@ -337,6 +353,13 @@ def run_gpu(args, rank, world, local_rank):
     stage = {"count_a_scan": hist_ms / args.steps}
     for i, nm in enumerate(names):
         stage[nm] = float(np.mean([p[i] for p in pass_ms]))
+    if world > 1:  # rank 0's view of the step
+        for nm, v in exch_ms.items():
+            stage["exchange_" + nm] = v / args.steps
+        stage["kernels"] = ev_ms / args.steps
+        stage["step"] = step_ms / args.steps
+        stage["host_tables_and_syncs"] = (
+            stage["step"] - stage["kernels"] - sum(exch_ms.values()) / args.steps)
     # dominant kernel: bucket_sort_kernel reads every record once and writes the
     # sorted unit back (8 B each way at k <= 21, 12 B above)
     rec_bytes = 12.0 if K > 21 else 8.0
@@ -354,14 +377,19 @@ def run_gpu(args, rank, world, local_rank):
         "scaling": "weak", "vs_baseline": None, "dtype": "u64",
         "data": "synthetic",
         "config": {
-            "workload": WORKLOAD + (" x%d (17 strains per GPU, one ancestor)"
-                                    % world if world > 1 else ""),
+            "workload": WORKLOAD + (" x%d (one 17-strain cluster per GPU, "
+                                    "independent ancestors)" % world
+                                    if world > 1 else ""),
             "anchor_size": K,
             "mode": "parity (anchor-similar=false, no truncation)",
             "bases_per_step": n_total, "sequences": int(len(offsets) - 1) * world,
             "l2": "512 MiB flush buffer rewritten between timed steps",
+            "timed": ("library CUDA events on its stream, first to last kernel "
+                      "of the step" if world == 1 else
+                      "CUDA events around the whole step (kernels, NCCL "
+                      "exchanges, host tables), max over ranks"),
             "parallelism": ("1 GPU" if world == 1 else
-                            "positions sharded per GPU; k-mers repartitioned by "
+                            "sequences sharded per GPU; k-mers repartitioned by "
                             "hash range, NCCL all-to-all x%d" % world),
         },
         "anchors_per_s": parity_stats["n_fragments_global"] * args.steps / t_dev,
@@ -444,19 +472,26 @@ class SingleRunner:
 class DistRunner(SingleRunner):
     dominant_kernel = "bucket_sort_kernel"
 
-    def __init__(self, finder, bases, offsets, seq_base, n_seqs_total):
+    def __init__(self, finder, bases, offsets):
         self.f, self.bases, self.offsets = finder, bases, offsets
-        self.seq_base, self.n_seqs_total = seq_base, n_seqs_total
 
     def upload(self, k):
-        self.f.upload(self.bases, self.offsets, k, self.seq_base)
+        self.f.upload((self.bases, self.offsets), k)
+
+    @staticmethod
+    def _job(st):
+        st["n_fragments_global"] = st["n_fragments"]
+        st["n_blocks_global"] = st["n_blocks"]
+        st["n_windows_global"] = st["n_windows"]
+        return st
 
     def step(self, k, similar, max_frags):
-        return self.f.find_device(k, similar=similar, max_frags=max_frags)
+        return self._job(self.f.find_device(k, similar=similar, max_frags=max_frags))
 
     def find_host(self, bases, offsets, k, similar, max_frags):
-        return self.f.find_host(bases, offsets, k, self.seq_base,
-                                similar=similar, max_frags=max_frags)
+        st = self.f.find_counts((bases, offsets), k, similar=similar,
+                                max_frags=max_frags)
+        return st["result_bytes"]
 
     def ncu_traffic(self, n_windows):
         return None

@@ -1288,9 +1288,12 @@ extern "C" int npge_anchor_dist_emit(npge_anchor_ctx* ctx, const npge_anchor_par
     s.digest[1] = summary[kSumDigest1];
     s.radix_passes = uint32_t(2 + plan.smem_passes);
     s.gpu_launches = ctx->dist_launches;
-    // stages: [count A] [pass A] [count B] [pass B] [bucket sort] [count (similar)] [emit]
+    // stages as on one GPU: [count A] | [pass A] [count B] [pass B] [bucket sort
+    // (+ candidate count)] [scan + emit]
     s.ms_hist = ctx->dist_ms[0];
-    for (int i = 0; i < 6; i++) s.ms_pass[i] = ctx->dist_ms[i + 1];
+    for (int i = 0; i < 3; i++) s.ms_pass[i] = ctx->dist_ms[i + 1];
+    s.ms_pass[3] = ctx->dist_ms[4] + ctx->dist_ms[5];
+    s.ms_pass[4] = ctx->dist_ms[6];
     s.ms_sort = ctx->dist_ms[0] + ctx->dist_ms[1] + ctx->dist_ms[2] + ctx->dist_ms[3];
     s.ms_group = ctx->dist_ms[4] + ctx->dist_ms[5] + ctx->dist_ms[6];
     s.ms_total = s.ms_sort + s.ms_group;  // device time of this rank's kernels

@@ -253,10 +253,17 @@ class _Comm:
         self.dist.all_gather_into_tensor(out, t.reshape(-1), group=self.group)
         return out.cpu().numpy().reshape((self.world,) + tuple(t.shape))
 
+    def _done(self, t):
+        # the library's kernels run on its own stream: the collective must have
+        # finished (not just been enqueued) before the next stage is launched
+        if t.is_cuda:
+            self.torch.cuda.current_stream(t.device).synchronize()
+
     def all_to_all(self, out, inp, out_splits, in_splits):
         if self.nccl or not out.is_cuda:
             self.dist.all_to_all_single(out, inp, list(out_splits), list(in_splits),
                                         group=self.group)
+            self._done(out)
             return
         o, i = out.cpu(), inp.cpu()
         self._a2a_host(o, i, out_splits, in_splits)
@@ -280,6 +287,7 @@ class _Comm:
     def sum_(self, t):
         if self.nccl or not t.is_cuda:
             self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM, group=self.group)
+            self._done(t)
             return
         h = t.cpu()
         self.dist.all_reduce(h, op=self.dist.ReduceOp.SUM, group=self.group)
@@ -440,6 +448,13 @@ class DistAnchorFinder:
         r.job_digest = (sum(p[1][0] for p in parts) & mask,
                         sum(p[1][1] for p in parts) & mask)
         return r
+
+    def find_counts(self, seqs, k, similar=True, max_frags=100000, used=None):
+        """find(), keeping only the sizes of this rank's host arrays (benchmarks)."""
+        self.upload(seqs, k)
+        stats = self.find_device(k, similar=similar, max_frags=max_frags, used=used)
+        stats["result_bytes"] = self.stages.fetch_counts()["result_bytes"]
+        return stats
 
     def find(self, seqs, k, similar=True, max_frags=100000, used=None):
         """upload + find_device + fetch (host buffers in, host arrays out)."""

@@ -165,6 +165,15 @@ class AnchorEngine:
         finally:
             self._lib.npge_anchor_result_free(C.byref(r))
 
+    def fetch_counts(self):
+        """npge_anchor_fetch, keeping only the sizes (see find_counts)."""
+        r = _abi.Result()
+        self._check(self._lib.npge_anchor_fetch(self._ctx, C.byref(r)))
+        nb, nf = int(r.n_blocks), int(r.n_fragments)
+        self._lib.npge_anchor_result_free(C.byref(r))
+        return {"n_blocks": nb, "n_fragments": nf,
+                "result_bytes": nf * 9 + (nb + 1) * 8 + nb * 8}
+
     def stats(self):
         s = _abi.Stats()
         self._check(self._lib.npge_anchor_get_stats(self._ctx, C.byref(s)))

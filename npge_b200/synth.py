@@ -171,6 +171,15 @@ def generate(config, scale=1.0, seed=None):
     return names, seqs
 
 
+def generate_shard(config, rank, world, scale=1.0):
+    """Weak-scaling input of rank `rank`: its own cluster of the job (same
+    shape as `config`, an independent ancestor per rank).  Returns (names,
+    seqs); names carry the rank so that genomes stay distinct job-wide."""
+    cfg = dict(CONFIGS[config]) if isinstance(config, str) else dict(config)
+    names, seqs = generate(cfg, scale=scale, seed=cfg["seed"] + 7919 * rank)
+    return ["R%02d%s" % (rank, n) for n in names], seqs
+
+
 def genome_ids(names):
     """Integer labels for Sequence::genome() (src/model/Sequence.cpp:193-202)."""
     ids, table = [], {}
