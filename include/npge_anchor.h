@@ -176,6 +176,30 @@ int npge_anchor_dist_upload(npge_anchor_ctx* ctx, int32_t anchor_size,
                             const uint32_t* global_caller, uint32_t n_global);
 int npge_anchor_dist_pass_a(npge_anchor_ctx* ctx, const npge_anchor_params* p,
                             uint32_t* hist_out, uint32_t hist_cap, uint32_t* n_bins);
+/* The exchange without a separate all-to-all: pass A scatters every bucket
+ * straight into the owning rank's receive buffer (peer memory over NVLink,
+ * mapped through CUDA IPC).
+ *   dist_peer_alloc    (re)allocates this rank's receive buffers for `capacity`
+ *                      records and returns their IPC handles
+ *   [all-gather of the handles]
+ *   dist_peer_open     maps the other ranks' buffers; dist_peer_close unmaps them
+ *                      (before any rank reallocates)
+ *   dist_count_a       count A only; returns the records per A bucket
+ *   [all-gather of the histograms, as above]
+ *   dist_scatter_peer  pass A; bucket a goes to rank dest_rank[a], at record
+ *                      index dest_off[a] + (index in this rank's A-sorted order)
+ *   [barrier: every rank's scatter has finished]  then dist_buffers / dist_sort */
+#define NPGE_ANCHOR_IPC_BYTES 128
+int npge_anchor_dist_peer_alloc(npge_anchor_ctx* ctx, uint64_t capacity,
+                                uint8_t handles_out[NPGE_ANCHOR_IPC_BYTES]);
+int npge_anchor_dist_peer_open(npge_anchor_ctx* ctx, uint32_t world, uint32_t rank,
+                               const uint8_t* handles_all);
+int npge_anchor_dist_peer_close(npge_anchor_ctx* ctx);
+int npge_anchor_dist_count_a(npge_anchor_ctx* ctx, const npge_anchor_params* p,
+                             uint32_t* hist_out, uint32_t hist_cap, uint32_t* n_bins);
+int npge_anchor_dist_scatter_peer(npge_anchor_ctx* ctx, const npge_anchor_params* p,
+                                  const uint32_t* dest_rank, const int64_t* dest_off,
+                                  uint32_t n_bins);
 int npge_anchor_dist_buffers(npge_anchor_ctx* ctx, uint64_t n_recv,
                              npge_anchor_dist_ptrs* out);
 int npge_anchor_dist_sort(npge_anchor_ctx* ctx, const npge_anchor_params* p,

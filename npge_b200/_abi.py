@@ -13,7 +13,11 @@ EXPORTS = [
     "npge_anchor_version",
     "npge_anchor_dist_upload", "npge_anchor_dist_pass_a",
     "npge_anchor_dist_buffers", "npge_anchor_dist_sort", "npge_anchor_dist_emit",
+    "npge_anchor_dist_peer_alloc", "npge_anchor_dist_peer_open",
+    "npge_anchor_dist_peer_close", "npge_anchor_dist_count_a",
+    "npge_anchor_dist_scatter_peer",
 ]
+IPC_BYTES = 128
 
 OK, ERR_PARAMS, ERR_CUDA, ERR_MEMORY, ERR_CAPACITY, ERR_INPUT, ERR_STATE = range(7)
 
@@ -100,6 +104,17 @@ def load():
     L.npge_anchor_dist_pass_a.restype = C.c_int
     L.npge_anchor_dist_pass_a.argtypes = [ctx, C.POINTER(Params), C.c_void_p,
                                           C.c_uint32, C.POINTER(C.c_uint32)]
+    L.npge_anchor_dist_count_a.restype = C.c_int
+    L.npge_anchor_dist_count_a.argtypes = L.npge_anchor_dist_pass_a.argtypes
+    L.npge_anchor_dist_peer_alloc.restype = C.c_int
+    L.npge_anchor_dist_peer_alloc.argtypes = [ctx, C.c_uint64, C.c_void_p]
+    L.npge_anchor_dist_peer_open.restype = C.c_int
+    L.npge_anchor_dist_peer_open.argtypes = [ctx, C.c_uint32, C.c_uint32, C.c_void_p]
+    L.npge_anchor_dist_peer_close.restype = C.c_int
+    L.npge_anchor_dist_peer_close.argtypes = [ctx]
+    L.npge_anchor_dist_scatter_peer.restype = C.c_int
+    L.npge_anchor_dist_scatter_peer.argtypes = [ctx, C.POINTER(Params), C.c_void_p,
+                                                C.c_void_p, C.c_uint32]
     L.npge_anchor_dist_buffers.restype = C.c_int
     L.npge_anchor_dist_buffers.argtypes = [ctx, C.c_uint64, C.POINTER(DistPtrs)]
     L.npge_anchor_dist_sort.restype = C.c_int

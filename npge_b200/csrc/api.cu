@@ -229,7 +229,9 @@ extern "C" void npge_anchor_destroy(npge_anchor_ctx* ctx) {
                            &ctx->segtab, &ctx->fine_start,
                            &ctx->bstatus, &ctx->units, &ctx->rec[0], &ctx->rec[1], &ctx->rhi[0],
                            &ctx->rhi[1], &ctx->seq_lut, &ctx->g_seq_start, &ctx->g_seq_caller,
-                           &ctx->g_seq_lut, &ctx->pos_delta, &ctx->recv_rec, &ctx->recv_hi};
+                           &ctx->g_seq_lut, &ctx->pos_delta, &ctx->recv_rec, &ctx->recv_hi,
+                           &ctx->peer_tab};
+    for (void* q : ctx->peer_opened) cudaIpcCloseMemHandle(q);
     for (DeviceBuffer* b : all) release(*b);
     for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
     for (auto& ev : ctx->ev_pass) if (ev) cudaEventDestroy(ev);
@@ -1050,9 +1052,21 @@ extern "C" int npge_anchor_dist_upload(npge_anchor_ctx* ctx, int32_t anchor_size
     return NPGE_ANCHOR_OK;
 }
 
-extern "C" int npge_anchor_dist_pass_a(npge_anchor_ctx* ctx, const npge_anchor_params* p,
-                                       uint32_t* hist_out, uint32_t hist_cap,
-                                       uint32_t* n_bins) {
+namespace {
+
+PosMap dist_pos_map(npge_anchor_ctx* ctx) {
+    PosMap pm = {};
+    pm.delta = ptr<uint32_t>(ctx->pos_delta);
+    pm.seq_start = ptr<uint64_t>(ctx->seq_start);
+    pm.lut = ptr<uint32_t>(ctx->seq_lut);
+    pm.lut_shift = ctx->lut_shift;
+    return pm;
+}
+
+// count A (+ the local scatter when `scatter`); fills hist_out with the records
+// per A bucket
+int dist_count_a(npge_anchor_ctx* ctx, const npge_anchor_params* p, bool scatter,
+                 uint32_t* hist_out, uint32_t hist_cap, uint32_t* n_bins) {
     if (!ctx || !hist_out || !n_bins) return fail(NPGE_ANCHOR_ERR_PARAMS, "NULL argument");
     NPGE_TRY(check_params(p));
     if (!ctx->uploaded || !ctx->dist) {
@@ -1063,6 +1077,7 @@ extern "C" int npge_anchor_dist_pass_a(npge_anchor_ctx* ctx, const npge_anchor_p
     }
     NPGE_CUDA(cudaSetDevice(ctx->device));
     ctx->have_result = false;
+    ctx->a_counted = false;
     const MsdPlan plan = make_msd_plan(p->anchor_size, ctx->g_positions);
     const uint32_t bins_a = 1u << plan.capa;
     if (hist_cap < bins_a) return fail(NPGE_ANCHOR_ERR_PARAMS, "hist_out too small");
@@ -1071,8 +1086,10 @@ extern "C" int npge_anchor_dist_pass_a(npge_anchor_ctx* ctx, const npge_anchor_p
     NPGE_TRY(ensure(ctx->rows, msd_rows_needed(plan, np, max_records, bins_a) * 4));
     NPGE_TRY(ensure(ctx->blk, msd_blk_needed(plan, np, max_records, bins_a) * 4));
     NPGE_TRY(ensure(ctx->segtab, seg_table_words(bins_a, plan) * 4));
-    NPGE_TRY(ensure(ctx->rec[0], (max_records + 16) * 8));
-    if (plan.wide) NPGE_TRY(ensure(ctx->rhi[0], (max_records + 16) * 4));
+    if (scatter) {
+        NPGE_TRY(ensure(ctx->rec[0], (max_records + 16) * 8));
+        if (plan.wide) NPGE_TRY(ensure(ctx->rhi[0], (max_records + 16) * 4));
+    }
     NPGE_TRY(ensure(ctx->counters, kCntWords * 4));
     cudaStream_t st = ctx->stream;
     memset(ctx->dist_ms, 0, sizeof(ctx->dist_ms));
@@ -1081,24 +1098,154 @@ extern "C" int npge_anchor_dist_pass_a(npge_anchor_ctx* ctx, const npge_anchor_p
     MsdBuffers mb = dist_msd_buffers(ctx, plan, bins_a);
     std::vector<uint32_t> a_start(bins_a + 1, 0);
     if (np) {
-        PosMap pm = {};
-        pm.delta = ptr<uint32_t>(ctx->pos_delta);
-        pm.seq_start = ptr<uint64_t>(ctx->seq_start);
-        pm.lut = ptr<uint32_t>(ctx->seq_lut);
-        pm.lut_shift = ctx->lut_shift;
         NPGE_CUDA(cudaEventRecord(ctx->ev[0], st));
         launch_msd_pass_a(plan, ptr<uint32_t>(ctx->packed), ptr<uint32_t>(ctx->nmask), np,
-                          mb, pm, ptr<uint32_t>(ctx->counters), st, ctx->ev_pass,
-                          &ctx->dist_launches);
+                          mb, dist_pos_map(ctx), ptr<uint32_t>(ctx->counters), st,
+                          ctx->ev_pass, &ctx->dist_launches, scatter ? 0 : 1);
         NPGE_CUDA(cudaGetLastError());
         NPGE_CUDA(cudaMemcpyAsync(a_start.data(), mb.seg.a_start, (bins_a + 1) * 4,
                                   cudaMemcpyDeviceToHost, st));
         NPGE_CUDA(cudaStreamSynchronize(st));
         cudaEventElapsedTime(&ctx->dist_ms[0], ctx->ev[0], ctx->ev_pass[0]);
-        cudaEventElapsedTime(&ctx->dist_ms[1], ctx->ev_pass[0], ctx->ev_pass[1]);
+        if (scatter) cudaEventElapsedTime(&ctx->dist_ms[1], ctx->ev_pass[0], ctx->ev_pass[1]);
     }
     for (uint32_t a = 0; a < bins_a; a++) hist_out[a] = a_start[a + 1] - a_start[a];
     ctx->plan = plan;
+    ctx->a_counted = true;
+    return NPGE_ANCHOR_OK;
+}
+
+}  // namespace
+
+extern "C" int npge_anchor_dist_pass_a(npge_anchor_ctx* ctx, const npge_anchor_params* p,
+                                       uint32_t* hist_out, uint32_t hist_cap,
+                                       uint32_t* n_bins) {
+    return dist_count_a(ctx, p, true, hist_out, hist_cap, n_bins);
+}
+
+extern "C" int npge_anchor_dist_count_a(npge_anchor_ctx* ctx, const npge_anchor_params* p,
+                                        uint32_t* hist_out, uint32_t hist_cap,
+                                        uint32_t* n_bins) {
+    return dist_count_a(ctx, p, false, hist_out, hist_cap, n_bins);
+}
+
+// ---- peer exchange: receive buffers shared through CUDA IPC -------------------------
+extern "C" int npge_anchor_dist_peer_close(npge_anchor_ctx* ctx) {
+    if (!ctx) return fail(NPGE_ANCHOR_ERR_PARAMS, "ctx is NULL");
+    NPGE_CUDA(cudaSetDevice(ctx->device));
+    NPGE_CUDA(cudaStreamSynchronize(ctx->stream));
+    for (void* q : ctx->peer_opened) cudaIpcCloseMemHandle(q);
+    ctx->peer_opened.clear();
+    ctx->peer_rec.clear();
+    ctx->peer_hi.clear();
+    return NPGE_ANCHOR_OK;
+}
+
+extern "C" int npge_anchor_dist_peer_alloc(npge_anchor_ctx* ctx, uint64_t capacity,
+                                           uint8_t* handles_out) {
+    if (!ctx || !handles_out) return fail(NPGE_ANCHOR_ERR_PARAMS, "NULL argument");
+    static_assert(2 * sizeof(cudaIpcMemHandle_t) <= NPGE_ANCHOR_IPC_BYTES, "handle size");
+    if (capacity > kMaxRecords) {
+        return fail(NPGE_ANCHOR_ERR_CAPACITY, "more than 2^30-1 records on one rank");
+    }
+    if (!ctx->peer_opened.empty()) {
+        return fail(NPGE_ANCHOR_ERR_STATE, "npge_anchor_dist_peer_close first");
+    }
+    NPGE_CUDA(cudaSetDevice(ctx->device));
+    NPGE_TRY(ensure(ctx->recv_rec, (capacity + 16) * 8));
+    NPGE_TRY(ensure(ctx->recv_hi, (capacity + 16) * 4));
+    ctx->peer_capacity = capacity;
+    cudaIpcMemHandle_t h[2];
+    NPGE_CUDA(cudaIpcGetMemHandle(&h[0], ctx->recv_rec.ptr));
+    NPGE_CUDA(cudaIpcGetMemHandle(&h[1], ctx->recv_hi.ptr));
+    memset(handles_out, 0, NPGE_ANCHOR_IPC_BYTES);
+    memcpy(handles_out, h, sizeof(h));
+    return NPGE_ANCHOR_OK;
+}
+
+extern "C" int npge_anchor_dist_peer_open(npge_anchor_ctx* ctx, uint32_t world,
+                                          uint32_t rank, const uint8_t* handles_all) {
+    if (!ctx || !handles_all) return fail(NPGE_ANCHOR_ERR_PARAMS, "NULL argument");
+    if (rank >= world) return fail(NPGE_ANCHOR_ERR_PARAMS, "rank >= world");
+    if (!ctx->recv_rec.ptr || !ctx->peer_capacity) {
+        return fail(NPGE_ANCHOR_ERR_STATE, "npge_anchor_dist_peer_alloc first");
+    }
+    NPGE_TRY(npge_anchor_dist_peer_close(ctx));
+    ctx->peer_rec.assign(world, nullptr);
+    ctx->peer_hi.assign(world, nullptr);
+    for (uint32_t r = 0; r < world; r++) {
+        if (r == rank) {
+            ctx->peer_rec[r] = ctx->recv_rec.ptr;
+            ctx->peer_hi[r] = ctx->recv_hi.ptr;
+            continue;
+        }
+        cudaIpcMemHandle_t h[2];
+        memcpy(h, handles_all + size_t(r) * NPGE_ANCHOR_IPC_BYTES, sizeof(h));
+        void* q[2] = {nullptr, nullptr};
+        for (int i = 0; i < 2; i++) {
+            cudaError_t e = cudaIpcOpenMemHandle(&q[i], h[i], cudaIpcMemLazyEnablePeerAccess);
+            if (e != cudaSuccess) {
+                cudaGetLastError();
+                npge_anchor_dist_peer_close(ctx);
+                return fail(NPGE_ANCHOR_ERR_CUDA,
+                            std::string("cudaIpcOpenMemHandle (no peer access between "
+                                        "the ranks' GPUs?): ") + cudaGetErrorString(e));
+            }
+            ctx->peer_opened.push_back(q[i]);
+        }
+        ctx->peer_rec[r] = q[0];
+        ctx->peer_hi[r] = q[1];
+    }
+    return NPGE_ANCHOR_OK;
+}
+
+extern "C" int npge_anchor_dist_scatter_peer(npge_anchor_ctx* ctx,
+                                             const npge_anchor_params* p,
+                                             const uint32_t* dest_rank,
+                                             const int64_t* dest_off, uint32_t n_bins) {
+    if (!ctx || !dest_rank || !dest_off) return fail(NPGE_ANCHOR_ERR_PARAMS, "NULL argument");
+    NPGE_TRY(check_params(p));
+    if (!ctx->dist || !ctx->a_counted) {
+        return fail(NPGE_ANCHOR_ERR_STATE, "npge_anchor_dist_count_a has not run");
+    }
+    const MsdPlan plan = ctx->plan;
+    const uint32_t bins_a = 1u << plan.capa;
+    if (n_bins != bins_a) return fail(NPGE_ANCHOR_ERR_PARAMS, "n_bins differs from the plan");
+    if (ctx->peer_rec.empty()) {
+        return fail(NPGE_ANCHOR_ERR_STATE, "npge_anchor_dist_peer_open has not been called");
+    }
+    NPGE_CUDA(cudaSetDevice(ctx->device));
+    std::vector<unsigned long long> tab(2 * size_t(bins_a));
+    for (uint32_t a = 0; a < bins_a; a++) {
+        if (dest_rank[a] >= ctx->peer_rec.size()) {
+            return fail(NPGE_ANCHOR_ERR_PARAMS, "dest_rank out of range");
+        }
+        // addresses may lie before the buffer; only in-range elements are written
+        tab[a] = (unsigned long long)(uintptr_t(ctx->peer_rec[dest_rank[a]]) +
+                                      dest_off[a] * 8);
+        tab[bins_a + a] = (unsigned long long)(uintptr_t(ctx->peer_hi[dest_rank[a]]) +
+                                               dest_off[a] * 4);
+    }
+    cudaStream_t st = ctx->stream;
+    NPGE_TRY(ensure(ctx->peer_tab, tab.size() * 8));
+    NPGE_CUDA(cudaMemcpyAsync(ctx->peer_tab.ptr, tab.data(), tab.size() * 8,
+                              cudaMemcpyHostToDevice, st));
+    const uint64_t np = ctx->n_padded;
+    if (np) {
+        MsdBuffers mb = dist_msd_buffers(ctx, plan, bins_a);
+        PosMap pm = dist_pos_map(ctx);
+        pm.peer_rec = ptr<unsigned long long>(ctx->peer_tab);
+        pm.peer_hi = pm.peer_rec + bins_a;
+        NPGE_CUDA(cudaEventRecord(ctx->ev[0], st));
+        launch_msd_pass_a(plan, ptr<uint32_t>(ctx->packed), ptr<uint32_t>(ctx->nmask), np,
+                          mb, pm, ptr<uint32_t>(ctx->counters), st, nullptr,
+                          &ctx->dist_launches, 2);
+        NPGE_CUDA(cudaGetLastError());
+        NPGE_CUDA(cudaEventRecord(ctx->ev[1], st));
+    }
+    NPGE_CUDA(cudaStreamSynchronize(st));  // the peers may read after their barrier
+    if (np) cudaEventElapsedTime(&ctx->dist_ms[1], ctx->ev[0], ctx->ev[1]);
+    ctx->a_counted = false;
     return NPGE_ANCHOR_OK;
 }
 
@@ -1111,8 +1258,14 @@ extern "C" int npge_anchor_dist_buffers(npge_anchor_ctx* ctx, uint64_t n_recv,
     }
     NPGE_CUDA(cudaSetDevice(ctx->device));
     const MsdPlan& plan = ctx->plan;
-    NPGE_TRY(ensure(ctx->recv_rec, (n_recv + 16) * 8));
-    if (plan.wide) NPGE_TRY(ensure(ctx->recv_hi, (n_recv + 16) * 4));
+    if (!ctx->peer_rec.empty()) {  // mapped by the peers: must not move
+        if (n_recv > ctx->peer_capacity) {
+            return fail(NPGE_ANCHOR_ERR_STATE, "n_recv exceeds the peer buffers' capacity");
+        }
+    } else {
+        NPGE_TRY(ensure(ctx->recv_rec, (n_recv + 16) * 8));
+        if (plan.wide) NPGE_TRY(ensure(ctx->recv_hi, (n_recv + 16) * 4));
+    }
     const size_t found_bytes = ctx->g_padded / 8 + 256;
     NPGE_TRY(ensure(ctx->found_bits, found_bytes));
     ctx->n_recv = n_recv;

@@ -165,6 +165,12 @@ struct npge_anchor_ctx {
     uint64_t n_recv = 0;
     uint32_t dist_launches = 0;
     uint32_t dist_max_seg = 0;
+    // peer exchange: receive buffers of all ranks mapped through CUDA IPC
+    std::vector<void*> peer_opened;          // to close
+    std::vector<void*> peer_rec, peer_hi;    // [world]; own rank: recv_rec / recv_hi
+    uint64_t peer_capacity = 0;              // records every receive buffer can take
+    npge_b200::DeviceBuffer peer_tab;        // per-bucket destination addresses
+    bool a_counted = false;
     uint64_t dist_n_used = 0;
     float dist_ms[8] = {};
     // device result

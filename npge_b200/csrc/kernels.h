@@ -81,6 +81,11 @@ struct PosMap {
     const uint64_t* seq_start;  // [S + 1] local starts
     const uint32_t* lut;
     int lut_shift;
+    // optional, per A bucket: where the bucket's records go, as addresses such
+    // that element idx (the index in this rank's A-sorted order) lands in the
+    // owning rank's receive buffer -- peer memory over NVLink.  nullptr: local.
+    const unsigned long long* peer_rec;
+    const unsigned long long* peer_hi;
 };
 
 struct MsdBuffers {
@@ -100,10 +105,11 @@ size_t msd_blk_needed(const MsdPlan& plan, uint64_t n_padded, uint64_t max_recor
 size_t seg_table_words(uint32_t max_seg, const MsdPlan& plan);
 SegTables carve_seg_tables(uint32_t* base, uint32_t max_seg, const MsdPlan& plan);
 // ev (optional): [0] after count A, [1] after pass A, [2] after count B, [3] pass B
+// part: 0 = count + scatter, 1 = count A and the tables only, 2 = the scatter only
 void launch_msd_pass_a(const MsdPlan& plan, const uint32_t* packed,
                        const uint32_t* nmask, uint64_t n_padded, const MsdBuffers& b,
                        const PosMap& pm, uint32_t* counters, cudaStream_t s,
-                       cudaEvent_t* ev, uint32_t* launches);
+                       cudaEvent_t* ev, uint32_t* launches, int part = 0);
 void launch_msd_pass_b(const MsdPlan& plan, const uint64_t* in_rec, const uint32_t* in_hi,
                        uint64_t max_records, uint32_t max_seg, const MsdBuffers& b,
                        cudaStream_t s, cudaEvent_t* ev, uint32_t* launches);

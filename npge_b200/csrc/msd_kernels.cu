@@ -294,9 +294,15 @@ pass_a_kernel(const uint32_t* __restrict__ packed, const uint32_t* __restrict__ 
     for (int i = 0; i < kRI; i++) {
         uint32_t j = tid + i * kRT;
         if (j < total) {
-            uint32_t idx = sm.bin_base[sm.dig[j]] + j;
-            out_rec[idx] = sm.rec[j];
-            if (WIDE) out_hi[idx] = sm.hi[j];
+            const uint32_t d = sm.dig[j];
+            uint32_t idx = sm.bin_base[d] + j;
+            if (GLOBAL && pm.peer_rec) {  // straight into the owner's HBM
+                reinterpret_cast<uint64_t*>(pm.peer_rec[d])[idx] = sm.rec[j];
+                if (WIDE) reinterpret_cast<uint32_t*>(pm.peer_hi[d])[idx] = sm.hi[j];
+            } else {
+                out_rec[idx] = sm.rec[j];
+                if (WIDE) out_hi[idx] = sm.hi[j];
+            }
         }
     }
 }
@@ -487,18 +493,21 @@ size_t seg_table_words(uint32_t max_seg, const MsdPlan& plan) {
 void launch_msd_pass_a(const MsdPlan& plan, const uint32_t* packed,
                        const uint32_t* nmask, uint64_t n_padded, const MsdBuffers& b,
                        const PosMap& pm, uint32_t* counters, cudaStream_t s,
-                       cudaEvent_t* ev, uint32_t* launches) {
+                       cudaEvent_t* ev, uint32_t* launches, int part) {
     const uint32_t tiles_a = uint32_t(n_padded / kTile);
     if (tiles_a == 0) return;
     const int bins_a = 1 << plan.capa;
-    count_a_kernel<<<tiles_a, kRT, sizeof(GenomeStage) + bins_a * 4, s>>>(
-        packed, nmask, plan, b.rows);
-    scan_rows(b.rows, tiles_a, bins_a, b.blk, s);
-    a_tables_kernel<<<1, bins_a, 0, s>>>(b.rows + size_t(tiles_a) * bins_a, b.seg,
-                                         counters);
-    apply_rows(b.rows, tiles_a, bins_a, b.blk, b.seg.a_start, s);
-    *launches += 5;
-    if (ev) cudaEventRecord(ev[0], s);
+    if (part != 2) {
+        count_a_kernel<<<tiles_a, kRT, sizeof(GenomeStage) + bins_a * 4, s>>>(
+            packed, nmask, plan, b.rows);
+        scan_rows(b.rows, tiles_a, bins_a, b.blk, s);
+        a_tables_kernel<<<1, bins_a, 0, s>>>(b.rows + size_t(tiles_a) * bins_a, b.seg,
+                                             counters);
+        apply_rows(b.rows, tiles_a, bins_a, b.blk, b.seg.a_start, s);
+        *launches += 5;
+        if (ev) cudaEventRecord(ev[0], s);
+    }
+    if (part == 1) return;
 #define NPGE_PASS_A(CB, W, G)                                                      \
     do {                                                                           \
         set_smem(pass_a_kernel<CB, W, G>, sizeof(PassSmem<CB, W>));                \

@@ -142,6 +142,26 @@ def segment_tables(hist_all, cuts, rank):
         n_recv=int(mine.sum()))
 
 
+def peer_destinations(hist_all, cuts, rank):
+    """Per A bucket: the rank that owns it, and the record offset in that rank's
+    receive buffer of element 0 of THIS rank's A-sorted order (so that element
+    idx of the bucket's run lands at offset + idx; see segment_tables for the
+    receive layout).  Also the records every rank receives."""
+    h = np.asarray(hist_all, dtype=np.int64)
+    world, bins = h.shape
+    a_start = np.concatenate([[0], np.cumsum(h[rank])])
+    dest_rank = np.zeros(bins, dtype=np.uint32)
+    dest_off = np.zeros(bins, dtype=np.int64)
+    n_recv = []
+    for d in range(world):
+        lo, hi = int(cuts[d]), int(cuts[d + 1])
+        per_src = h[:, lo:hi].sum(axis=1)
+        n_recv.append(int(per_src.sum()))
+        dest_rank[lo:hi] = d
+        dest_off[lo:hi] = int(per_src[:rank].sum()) - int(a_start[lo])
+    return dest_rank, dest_off, n_recv
+
+
 def local_limits(totals, limit):
     """Share of max-anchor-fragments of every rank: the cut runs over the list
     ordered by hash, and the ranks own ascending hash ranges."""
@@ -185,6 +205,34 @@ class CudaStages(AnchorEngine):
         self._check(self._lib.npge_anchor_dist_pass_a(
             self._ctx, C.byref(params), hist.ctypes.data, len(hist), C.byref(n_bins)))
         return hist[:n_bins.value].copy()
+
+    def dist_count_a(self, params):
+        hist = np.zeros(1024, dtype=np.uint32)
+        n_bins = C.c_uint32()
+        self._check(self._lib.npge_anchor_dist_count_a(
+            self._ctx, C.byref(params), hist.ctypes.data, len(hist), C.byref(n_bins)))
+        return hist[:n_bins.value].copy()
+
+    def dist_peer_close(self):
+        self._check(self._lib.npge_anchor_dist_peer_close(self._ctx))
+
+    def dist_peer_alloc(self, capacity):
+        h = np.zeros(_abi.IPC_BYTES, dtype=np.uint8)
+        self._check(self._lib.npge_anchor_dist_peer_alloc(self._ctx, capacity,
+                                                          h.ctypes.data))
+        return h
+
+    def dist_peer_open(self, world, rank, handles):
+        h = np.ascontiguousarray(handles, dtype=np.uint8)
+        assert h.size == world * _abi.IPC_BYTES
+        self._check(self._lib.npge_anchor_dist_peer_open(self._ctx, world, rank,
+                                                         h.ctypes.data))
+
+    def dist_scatter_peer(self, params, dest_rank, dest_off):
+        dr = np.ascontiguousarray(dest_rank, dtype=np.uint32)
+        do = np.ascontiguousarray(dest_off, dtype=np.int64)
+        self._check(self._lib.npge_anchor_dist_scatter_peer(
+            self._ctx, C.byref(params), dr.ctypes.data, do.ctypes.data, len(dr)))
 
     def dist_buffers(self, n_send, n_recv):
         import torch
@@ -305,13 +353,51 @@ class DistAnchorFinder:
     ranges), with frag_seq = job-wide caller index: the ranks' sequences
     numbered one after the other in rank order."""
 
-    def __init__(self, device=0, group=None, stages=None):
+    def __init__(self, device=0, group=None, stages=None, exchange=None):
+        """exchange: "peer" = pass A writes into the owners' HBM over NVLink (CUDA
+        IPC); "collective" = local pass A + all-to-all.  Default: peer when the
+        stages support it and every rank could map every other's buffer."""
+        import os
         self.comm = _Comm(group)
         self.rank, self.world = self.comm.rank, self.comm.world
         self.stages = stages if stages is not None else CudaStages(device)
         self.device = device
         self._k = None
         self.exchange_ms = {}
+        want = exchange or os.environ.get("NPGE_ANCHOR_EXCHANGE") or "auto"
+        if want not in ("auto", "peer", "collective"):
+            raise ValueError("exchange must be peer, collective or auto")
+        if not hasattr(self.stages, "dist_peer_alloc"):
+            if want == "peer":
+                raise ValueError("these stages have no peer exchange")
+            want = "collective"
+        self._want = want
+        self.exchange = "collective"
+        self._capacity = 0
+
+    def _peer_setup(self, capacity):
+        """(Re)allocates the receive buffers and maps them on every rank.
+        Collective.  Falls back to the all-to-all when a rank cannot map a peer
+        (only when exchange was left to "auto")."""
+        st = self.stages
+        st.dist_peer_close()
+        self.comm.barrier()  # nobody still has the old buffers mapped
+        handle = st.dist_peer_alloc(capacity)
+        handles = np.concatenate(self.comm.gather_objects(handle))
+        err = None
+        try:
+            st.dist_peer_open(self.world, self.rank, handles)
+        except AnchorError as e:
+            err = str(e)
+        errs = [e for e in self.comm.gather_objects(err) if e]
+        if errs:
+            st.dist_peer_close()
+            if self._want == "peer":
+                raise AnchorError(_abi.ERR_CUDA, errs[0])
+            self.exchange = "collective"
+            return
+        self.exchange = "peer"
+        self._capacity = capacity
 
     # -- upload ------------------------------------------------------------------------
     def _rebalance(self, seqs, k):
@@ -376,6 +462,11 @@ class DistAnchorFinder:
         self.n_local_bases = int(sum(len(s) for s in local))
         self.stages.dist_upload(k, local, gstart[idx], gstart, job_caller)
         self._k = k
+        if self._want != "collective":
+            # room for an uneven split of the job's windows; grown on demand
+            need = int(gstart[-1]) // self.world * 5 // 4 + 65536
+            if need > self._capacity or self.exchange != "peer":
+                self._peer_setup(need)
 
     # -- find --------------------------------------------------------------------------
     def _timed(self, name, fn):
@@ -401,17 +492,30 @@ class DistAnchorFinder:
         params = _abi.Params(k, int(bool(similar)), int(max_frags))
         self.exchange_ms = {}
         dev = comm.torch.device("cuda", self.device) if comm.nccl else None
-        hist = st.dist_pass_a(params)
+        peer = self.exchange == "peer"
+        hist = st.dist_count_a(params) if peer else st.dist_pass_a(params)
+        # (also the step's barrier: no rank scatters into a receive buffer whose
+        # owner has not finished its previous step)
         hist_all = comm.gather_array(hist, dev)
         cuts = bucket_ranges(hist_all, self.world)
-        send_splits, recv_splits = exchange_splits(hist_all, cuts, self.rank)
         tables = segment_tables(hist_all, cuts, self.rank)
-        buf = st.dist_buffers(sum(send_splits), tables["n_recv"])
-        self._timed("records", lambda: comm.all_to_all(
-            buf["recv_rec"], buf["send_rec"], recv_splits, send_splits))
-        if buf["send_hi"] is not None:
+        if peer:
+            dest_rank, dest_off, n_recv = peer_destinations(hist_all, cuts, self.rank)
+            if max(n_recv) > self._capacity:  # the same decision on every rank
+                self._peer_setup(max(n_recv) * 9 // 8 + 65536)
+                if self.exchange != "peer":
+                    raise AnchorError(_abi.ERR_CUDA, "peer buffers could not be regrown")
+            st.dist_scatter_peer(params, dest_rank, dest_off)
+            self._timed("barrier", comm.barrier)  # every rank's scatter has landed
+            buf = st.dist_buffers(0, tables["n_recv"])
+        else:
+            send_splits, recv_splits = exchange_splits(hist_all, cuts, self.rank)
+            buf = st.dist_buffers(sum(send_splits), tables["n_recv"])
             self._timed("records", lambda: comm.all_to_all(
-                buf["recv_hi"], buf["send_hi"], recv_splits, send_splits))
+                buf["recv_rec"], buf["send_rec"], recv_splits, send_splits))
+            if buf["send_hi"] is not None:
+                self._timed("records", lambda: comm.all_to_all(
+                    buf["recv_hi"], buf["send_hi"], recv_splits, send_splits))
         totals = st.dist_sort(params, 0, tables, used)
         if similar:
             self._timed("found_bits", lambda: comm.sum_(buf["found"]))
@@ -433,7 +537,7 @@ class DistAnchorFinder:
                     sum(int(x) & mask for x in job[:, 5]) & mask),
             n_positions=self.n_job_bases, local_fragments=s["n_fragments"],
             local_records=s["n_windows"], total_selected=int(tot_all[:, 0].sum()),
-            exchange_ms=dict(self.exchange_ms),
+            exchange_ms=dict(self.exchange_ms), exchange=self.exchange,
             bucket_cuts=[int(c) for c in cuts])
         return out
 

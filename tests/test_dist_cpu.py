@@ -23,11 +23,12 @@ def free_port():
     return port
 
 
-def launch(world, args, timeout=600):
+def launch(world, args, timeout=600, extra_env=None):
     port = free_port()
     procs = []
     for r in range(world):
-        env = dict(os.environ, RANK=str(r), WORLD_SIZE=str(world), LOCAL_RANK=str(r),
+        env = dict(os.environ, **(extra_env or {}))
+        env.update(RANK=str(r), WORLD_SIZE=str(world), LOCAL_RANK=str(r),
                    MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
         procs.append(subprocess.Popen(
             [sys.executable, os.path.join(HERE, "dist_worker.py")] + [str(a) for a in args],
@@ -97,6 +98,30 @@ def test_segment_tables():
     assert t["n_recv"] == 8192 and list(t["seg_tile"]) == [0, 2]
     empty = D.segment_tables(np.zeros((2, 8), dtype=np.int64), np.asarray([0, 4, 8]), 1)
     assert empty["n_recv"] == 0 and empty["n_seg"] == 1 and list(empty["seg_tile"]) == [0, 0]
+
+
+def test_peer_destinations_match_the_receive_layout():
+    rng = np.random.default_rng(5)
+    h = rng.integers(0, 50, size=(3, 16))
+    cuts = D.bucket_ranges(h, 3)
+    # scatter element numbers through the destination tables and compare with
+    # the layout an all-to-all of the A-sorted slices would produce
+    recv = [dict() for _ in range(3)]
+    for src in range(3):
+        dest_rank, dest_off, n_recv = D.peer_destinations(h, cuts, src)
+        a_start = np.concatenate([[0], np.cumsum(h[src])])
+        for a in range(16):
+            for i in range(int(a_start[a]), int(a_start[a + 1])):
+                slot = int(dest_off[a]) + i
+                assert slot not in recv[dest_rank[a]]
+                recv[dest_rank[a]][slot] = (src, a, i - int(a_start[a]))
+    for d in range(3):
+        t = D.segment_tables(h, cuts, d)
+        assert sorted(recv[d]) == list(range(t["n_recv"])) and n_recv[d] == t["n_recv"]
+        for b, e, a in zip(t["seg_begin"], t["seg_end"], t["seg_a"]):
+            got = [recv[d][i] for i in range(int(b), int(e))]
+            assert len({g[0] for g in got}) <= 1 and all(g[1] == a for g in got)
+            assert [g[2] for g in got] == list(range(len(got)))
 
 
 def test_local_limits():

@@ -9,15 +9,24 @@ from test_dist_cpu import launch
 pytestmark = pytest.mark.gpu
 
 
+EXCHANGES = ["peer", "collective"]
+
+
+@pytest.mark.parametrize("exchange", EXCHANGES)
 @pytest.mark.parametrize("k", [12, 20, 27])
-def test_two_ranks_tiny(k):
-    launch(2, ["cuda", "tiny", 1.0, k, "interleaved"])
+def test_two_ranks_tiny(k, exchange):
+    launch(2, ["cuda", "tiny", 1.0, k, "interleaved"],
+           extra_env={"NPGE_ANCHOR_EXCHANGE": exchange})
 
 
-def test_three_ranks_tiny_blocks():
-    launch(3, ["cuda", "tiny", 1.0, 16, "blocks"])
+@pytest.mark.parametrize("exchange", EXCHANGES)
+def test_three_ranks_tiny_blocks(exchange):
+    launch(3, ["cuda", "tiny", 1.0, 16, "blocks"],
+           extra_env={"NPGE_ANCHOR_EXCHANGE": exchange})
 
 
-def test_two_ranks_small():
-    out = launch(2, ["cuda", "small", 1.0, 20, "interleaved"])
+@pytest.mark.parametrize("exchange", EXCHANGES)
+def test_two_ranks_small(exchange):
+    out = launch(2, ["cuda", "small", 1.0, 20, "interleaved"],
+                 extra_env={"NPGE_ANCHOR_EXCHANGE": exchange})
     assert "blocks" in out[0]
