@@ -255,7 +255,7 @@ def run_gpu(args, rank, world, local_rank):
     barrier()
     ev_ms, pass_ms, kern_launches = 0.0, [], 0
     hist_ms = group_ms = step_ms = 0.0
-    exch_ms = {}
+    exch_ms, host_ms = {}, {}
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     wall0 = time.perf_counter()
     for _ in range(args.steps):
@@ -268,6 +268,8 @@ def run_gpu(args, rank, world, local_rank):
         step_ms += e0.elapsed_time(e1)
         for nm, v in stats.get("exchange_ms", {}).items():
             exch_ms[nm] = exch_ms.get(nm, 0.0) + v
+        for nm, v in stats.get("host_ms", {}).items():
+            host_ms[nm] = host_ms.get(nm, 0.0) + v
         ev_ms += stats["ms_total"]
         hist_ms += stats["ms_hist"]
         group_ms += stats["ms_group"]
@@ -284,7 +286,7 @@ def run_gpu(args, rank, world, local_rank):
         t = torch.tensor([t_dev], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         t_dev = float(t.item())
-    parity_stats = stats
+    parity_stats = runner.finish(stats)
     if args.profile:
         if rank == 0:
             print(json.dumps({"profile_run": True, "steps": args.steps,
@@ -311,7 +313,7 @@ def run_gpu(args, rank, world, local_rank):
         t = torch.tensor([dflt_ms], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dflt_ms = float(t.item())
-    default_stats = st
+    default_stats = runner.finish(st)
 
     # ---- end to end through the drop-in call, host buffers -------------------
     pinned = torch.from_numpy(bases).pin_memory()
@@ -330,10 +332,10 @@ def run_gpu(args, rank, world, local_rank):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_t = float(t.item())
     h2d = int(bases.nbytes + offsets.nbytes)
-    if world > 1:  # job totals of the copies
-        t = torch.tensor([h2d, int(d2h)], dtype=torch.int64, device="cuda")
+    if world > 1:  # job totals of the copies and of the launches
+        t = torch.tensor([h2d, int(d2h), kern_launches], dtype=torch.int64, device="cuda")
         dist.all_reduce(t)
-        h2d, d2h = int(t[0].item()), int(t[1].item())
+        h2d, d2h, kern_launches = (int(x) for x in t.tolist())
     runner.find_host(pinned_np, offsets, K, True, 100000)
     barrier()
     t0 = time.perf_counter()
@@ -358,6 +360,7 @@ def run_gpu(args, rank, world, local_rank):
             stage["exchange_" + nm] = v / args.steps
         stage["kernels"] = ev_ms / args.steps
         stage["step"] = step_ms / args.steps
+        stage["host_wall_by_phase"] = {nm: v / args.steps for nm, v in host_ms.items()}
         stage["host_tables_and_syncs"] = (
             stage["step"] - stage["kernels"] - sum(exch_ms.values()) / args.steps)
     # dominant kernel: bucket_sort_kernel reads every record once and writes the
@@ -451,6 +454,9 @@ class SingleRunner:
         st["n_windows_global"] = st["n_windows"]
         return st
 
+    def finish(self, st):
+        return st
+
     def find_host(self, bases, offsets, k, similar, max_frags):
         r = self.eng.find_counts((bases, offsets), k, similar=similar,
                                  max_frags=max_frags)
@@ -486,7 +492,12 @@ class DistRunner(SingleRunner):
         return st
 
     def step(self, k, similar, max_frags):
-        return self._job(self.f.find_device(k, similar=similar, max_frags=max_frags))
+        # job-wide block count / digest: one more all-gather, after the timing
+        return self.f.find_device(k, similar=similar, max_frags=max_frags,
+                                  job_stats=False)
+
+    def finish(self, st):
+        return self._job(self.f.job_stats()) if st is self.f._last else self._job(st)
 
     def find_host(self, bases, offsets, k, similar, max_frags):
         st = self.f.find_counts((bases, offsets), k, similar=similar,

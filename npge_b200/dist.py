@@ -115,24 +115,18 @@ def segment_tables(hist_all, cuts, rank):
     src_base = np.concatenate([[0], np.cumsum(mine.sum(axis=1))])[:-1]
     inside = np.cumsum(mine, axis=1) - mine              # offset inside the slice
     begin = (src_base[:, None] + inside)                 # [world, owned]
-    seg_begin, seg_end, seg_a = [], [], []
+    c = mine.T.reshape(-1)                               # bucket-major, then source
+    keep = c > 0
+    sb = begin.T.reshape(-1)[keep]
+    se = sb + c[keep]
+    seg_a = np.repeat(np.arange(lo, hi), world)[keep]
     a_count = np.zeros(bins, dtype=np.int64)
-    a_tiles = np.zeros(bins, dtype=np.int64)
-    for j in range(hi - lo):
-        for s in range(world):
-            c = int(mine[s, j])
-            if c == 0:
-                continue
-            seg_begin.append(int(begin[s, j]))
-            seg_end.append(int(begin[s, j]) + c)
-            seg_a.append(lo + j)
-            a_tiles[lo + j] += (c + TILE - 1) // TILE
-        a_count[lo + j] = int(mine[:, j].sum())
-    if not seg_a:  # nothing received: one empty segment keeps the tables valid
-        seg_begin, seg_end, seg_a = [0], [0], [lo if lo < bins else 0]
-    sb = np.asarray(seg_begin, dtype=np.int64)
-    se = np.asarray(seg_end, dtype=np.int64)
+    a_count[lo:hi] = mine.sum(axis=0)
+    if len(sb) == 0:  # nothing received: one empty segment keeps the tables valid
+        sb, se = np.zeros(1, np.int64), np.zeros(1, np.int64)
+        seg_a = np.asarray([lo if lo < bins else 0])
     tiles = (se - sb + TILE - 1) // TILE
+    a_tiles = np.bincount(seg_a, weights=tiles, minlength=bins).astype(np.int64)
     u32 = lambda x: np.ascontiguousarray(np.asarray(x, dtype=np.uint32))
     return dict(
         n_seg=len(sb), seg_begin=u32(sb), seg_end=u32(se), seg_a=u32(seg_a),
@@ -341,7 +335,15 @@ class _Comm:
         self.dist.all_reduce(h, op=self.dist.ReduceOp.SUM, group=self.group)
         t.copy_(h)
 
-    def barrier(self):
+    def barrier(self, device=None):
+        """Every rank has arrived (and, for a CUDA device, the host has seen it:
+        the next kernels go to the library's own stream)."""
+        if self.nccl and device is not None:
+            if getattr(self, "_one", None) is None:
+                self._one = self.torch.zeros(1, dtype=self.torch.int32, device=device)
+            self.dist.all_reduce(self._one, group=self.group)
+            self.torch.cuda.current_stream(device).synchronize()
+            return
         self.dist.barrier(group=self.group)
 
 
@@ -482,63 +484,98 @@ class DistAnchorFinder:
         e1.synchronize()
         self.exchange_ms[name] = self.exchange_ms.get(name, 0.0) + e0.elapsed_time(e1)
 
-    def find_device(self, k=None, similar=True, max_frags=100000, used=None):
-        """All stages up to the anchors in device memory.  Returns job-wide
-        counts and digest (the same on every rank) + this rank's stage times."""
+    def find_device(self, k=None, similar=True, max_frags=100000, used=None,
+                    job_stats=True):
+        """All stages up to the anchors in device memory.  Returns the job's
+        fragment count + this rank's stage times; with job_stats also the job's
+        block count and digest (one more small all-gather; job_stats() does it
+        later)."""
+        import time
         k = self._k if k is None else k
         if k != self._k:
             raise AnchorError(_abi.ERR_STATE, "anchor-size differs from the uploaded one")
         st, comm = self.stages, self.comm
         params = _abi.Params(k, int(bool(similar)), int(max_frags))
         self.exchange_ms = {}
+        trace, t_prev = {}, [time.perf_counter()]
+
+        def lap(name):  # host wall clock of every phase of the step, ms
+            now = time.perf_counter()
+            trace[name] = trace.get(name, 0.0) + 1e3 * (now - t_prev[0])
+            t_prev[0] = now
+
         dev = comm.torch.device("cuda", self.device) if comm.nccl else None
         peer = self.exchange == "peer"
         hist = st.dist_count_a(params) if peer else st.dist_pass_a(params)
+        lap("count_a" if peer else "pass_a")
         # (also the step's barrier: no rank scatters into a receive buffer whose
         # owner has not finished its previous step)
         hist_all = comm.gather_array(hist, dev)
+        lap("gather_hist")
         cuts = bucket_ranges(hist_all, self.world)
         tables = segment_tables(hist_all, cuts, self.rank)
         if peer:
             dest_rank, dest_off, n_recv = peer_destinations(hist_all, cuts, self.rank)
+            lap("tables")
             if max(n_recv) > self._capacity:  # the same decision on every rank
                 self._peer_setup(max(n_recv) * 9 // 8 + 65536)
                 if self.exchange != "peer":
                     raise AnchorError(_abi.ERR_CUDA, "peer buffers could not be regrown")
             st.dist_scatter_peer(params, dest_rank, dest_off)
-            self._timed("barrier", comm.barrier)  # every rank's scatter has landed
+            lap("scatter_peer")
+            self._timed("barrier", lambda: comm.barrier(dev))  # every scatter has landed
+            lap("barrier")
             buf = st.dist_buffers(0, tables["n_recv"])
         else:
             send_splits, recv_splits = exchange_splits(hist_all, cuts, self.rank)
+            lap("tables")
             buf = st.dist_buffers(sum(send_splits), tables["n_recv"])
             self._timed("records", lambda: comm.all_to_all(
                 buf["recv_rec"], buf["send_rec"], recv_splits, send_splits))
             if buf["send_hi"] is not None:
                 self._timed("records", lambda: comm.all_to_all(
                     buf["recv_hi"], buf["send_hi"], recv_splits, send_splits))
+            lap("all_to_all")
         totals = st.dist_sort(params, 0, tables, used)
+        lap("sort")
         if similar:
             self._timed("found_bits", lambda: comm.sum_(buf["found"]))
+            lap("reduce_found")
             totals = st.dist_sort(params, 1, tables, used)
+            lap("count")
         tot_all = comm.gather_array(np.asarray(totals, dtype=np.int64), dev)
+        lap("gather_totals")
         limits = local_limits(tot_all[:, 0], int(max_frags))
         s = st.dist_emit(params, limits[self.rank])
+        lap("emit")
         self.local_stats = s
-        d = np.asarray([s["n_fragments"], s["n_blocks"], s["n_windows"],
-                        s["gpu_launches"]], dtype=np.int64)
-        dg = np.asarray([s["digest"][0], s["digest"][1]], dtype=np.uint64).view(np.int64)
-        job = comm.gather_array(np.concatenate([d, dg]), dev)
-        mask = (1 << 64) - 1
         out = dict(s)
+        cut = int(tot_all[:, 0].sum()) > int(max_frags)
         out.update(
-            n_fragments=int(job[:, 0].sum()), n_blocks=int(job[:, 1].sum()),
-            n_windows=int(job[:, 2].sum()), gpu_launches=int(job[:, 3].sum()),
-            digest=(sum(int(x) & mask for x in job[:, 4]) & mask,
-                    sum(int(x) & mask for x in job[:, 5]) & mask),
+            n_fragments=int(sum(limits)),
+            n_blocks=None if cut else int(tot_all[:, 1].sum()),
+            n_windows=int(hist_all.sum()), digest=None,
             n_positions=self.n_job_bases, local_fragments=s["n_fragments"],
             local_records=s["n_windows"], total_selected=int(tot_all[:, 0].sum()),
             exchange_ms=dict(self.exchange_ms), exchange=self.exchange,
-            bucket_cuts=[int(c) for c in cuts])
+            host_ms=trace, bucket_cuts=[int(c) for c in cuts])
+        self._last = out
+        if job_stats:
+            self.job_stats()
+        return out
+
+    def job_stats(self):
+        """Completes the last find_device's dict with the job's block count,
+        launches and digest (collective)."""
+        s, out = self.local_stats, self._last
+        dev = self.comm.torch.device("cuda", self.device) if self.comm.nccl else None
+        d = np.asarray([s["n_blocks"], s["gpu_launches"]], dtype=np.int64)
+        dg = np.asarray([s["digest"][0], s["digest"][1]], dtype=np.uint64).view(np.int64)
+        job = self.comm.gather_array(np.concatenate([d, dg]), dev)
+        mask = (1 << 64) - 1
+        out.update(n_blocks=int(job[:, 0].sum()), job_launches=int(job[:, 1].sum()),
+                   digest=(sum(int(x) & mask for x in job[:, 2]) & mask,
+                           sum(int(x) & mask for x in job[:, 3]) & mask))
         return out
 
     def fetch(self):
