@@ -173,7 +173,7 @@ def run_reference(args, rank, world):
                 "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    emit(line)
 
 
 # ---------------------------------------------------------------------------
@@ -212,6 +212,7 @@ def run_gpu(args, rank, world, local_rank):
     torch.cuda.set_device(local_rank)
     dist = None
     if world > 1:
+        guard_stdout()
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     from npge_b200 import synth
@@ -435,7 +436,7 @@ def run_gpu(args, rank, world, local_rank):
     }
     if world == 1 and not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline(args.cpu_scale)
-    print(json.dumps(line))
+    emit(line)
 
 
 class SingleRunner:
@@ -506,6 +507,29 @@ class DistRunner(SingleRunner):
 
     def ncu_traffic(self, n_windows):
         return None
+
+
+_RESULT_FD = None
+
+
+def guard_stdout():
+    """Libraries (NCCL's version banner) write to fd 1; the contract is ONE JSON
+    line on stdout.  Everything but emit() goes to stderr from here on."""
+    global _RESULT_FD
+    if _RESULT_FD is None:
+        sys.stdout.flush()
+        _RESULT_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    text = json.dumps(line) + "\n"
+    if _RESULT_FD is None:
+        sys.stdout.write(text)
+        sys.stdout.flush()
+    else:
+        sys.stdout.flush()
+        os.write(_RESULT_FD, text.encode())
 
 
 def main():
