@@ -35,5 +35,33 @@ def build(force=False, verbose=False):
     return LIB
 
 
+HOST = os.path.join(HERE, "host")
+SHIM_LIB = os.path.join(HOST, "libnpge_gpu_processors.so")
+SHIM_TEST = os.path.join(HOST, "test_gpu_anchor_finder")
+SHIM_SOURCES = ["gpu_anchor_finder.cpp", "gpu_anchor_finder.hpp", "npge_facade.hpp",
+                "test_gpu_anchor_finder.cpp"]
+
+
+def build_shim(force=False):
+    """The C++ host side: npge::gpu::AnchorFinder (libnpge_gpu_processors.so,
+    linked against libnpge_anchor.so) and its unit-test binary."""
+    build(force=False)
+    srcs = [os.path.join(HOST, f) for f in SHIM_SOURCES] + [LIB]
+    if (not force and os.path.exists(SHIM_LIB) and os.path.exists(SHIM_TEST) and
+            all(os.path.getmtime(f) <= min(os.path.getmtime(SHIM_LIB),
+                                           os.path.getmtime(SHIM_TEST)) for f in srcs)):
+        return SHIM_TEST
+    cxx = os.environ.get("CXX", "g++")
+    common = ["-std=c++17", "-O2", "-Wall", "-Wextra", "-I", HOST]
+    link = ["-L", HERE, "-lnpge_anchor", "-Wl,-rpath,$ORIGIN/..", "-Wl,-rpath,$ORIGIN"]
+    subprocess.check_call([cxx] + common + ["-fPIC", "-shared", "-o", SHIM_LIB,
+                                            os.path.join(HOST, "gpu_anchor_finder.cpp")] + link)
+    subprocess.check_call([cxx] + common + ["-o", SHIM_TEST,
+                                            os.path.join(HOST, "test_gpu_anchor_finder.cpp"),
+                                            "-L", HOST, "-lnpge_gpu_processors"] + link)
+    return SHIM_TEST
+
+
 if __name__ == "__main__":
     print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    print(build_shim(force="--force" in sys.argv))

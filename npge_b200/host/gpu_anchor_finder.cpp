@@ -1,0 +1,158 @@
+// gpu_anchor_finder.cpp -- see gpu_anchor_finder.hpp.
+//
+// Mirrors, call for call, what the reference's processor does around its two
+// passes (src/algo/AnchorFinder.cpp):
+//   ctor        :37-53    options, rules, declare_bs
+//   run_impl    :393-406  read options, collect sequences, find, build blocks
+//   postprocess :356-391  one Block per hash group, Fragment(seq, min, max, ori),
+//                         check_block, used_hashes_ update
+// Linearising the sequences and rebuilding the object graph are the only host
+// work; everything between is one call into the C ABI.
+#include "gpu_anchor_finder.hpp"
+
+#include <algorithm>
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include "../../include/npge_anchor.h"
+
+#ifdef NPGE_B200_REAL_HEADERS
+#include "Sequence.hpp"
+#include "Fragment.hpp"
+#include "Block.hpp"
+#include "BlockSet.hpp"
+#include "Exception.hpp"
+#endif
+
+namespace npge {
+namespace gpu {
+
+struct AnchorFinder::Impl {
+    npge_anchor_ctx* ctx = nullptr;
+    int device = 0;
+    std::vector<uint64_t> used_hashes;  // sorted; AnchorFinderImpl::used_hashes_ (:30-32)
+};
+
+AnchorFinder::AnchorFinder() : impl_(new Impl) {
+#ifdef NPGE_B200_REAL_HEADERS
+    add_gopt("anchor-size", "anchor size", "ANCHOR_SIZE");
+    add_gopt("anchor-fp",
+             "Probability of false positive in Bloom filter "
+             "(accepted for compatibility: the GPU method is exact)", "ANCHOR_FP");
+    add_opt("anchor-similar", "If neighbour anchors are skipped", true);
+    add_gopt("max-anchor-fragments", "Maximum number of anchors fragments to return",
+             "MAX_ANCHOR_FRAGMENTS");
+    add_opt_rule("anchor-size > 0");
+    add_opt_rule("anchor-size <= 32");
+#else
+    // defaults of the globals: CMakeLists.txt:41-46 of the reference
+    add_gopt("anchor-size", "anchor size", "ANCHOR_SIZE", 20);
+    add_gopt("anchor-fp",
+             "Probability of false positive in Bloom filter "
+             "(accepted for compatibility: the GPU method is exact)", "ANCHOR_FP", 0.1);
+    add_opt("anchor-similar", "If neighbour anchors are skipped", true);
+    add_gopt("max-anchor-fragments", "Maximum number of anchors fragments to return",
+             "MAX_ANCHOR_FRAGMENTS", 100000);
+    add_opt_rule([this](std::string& m) {
+        m = "anchor-size > 0";
+        return opt_value("anchor-size").as<int>() > 0;
+    });
+    add_opt_rule([this](std::string& m) {
+        m = "anchor-size <= 32";
+        return opt_value("anchor-size").as<int>() <= 32;
+    });
+#endif
+    declare_bs("target", "Blockset to search anchors in");
+}
+
+AnchorFinder::~AnchorFinder() {
+    if (impl_->ctx) npge_anchor_destroy(impl_->ctx);
+    delete impl_;
+}
+
+void AnchorFinder::set_device(int device) {
+    if (impl_->ctx) {
+        npge_anchor_destroy(impl_->ctx);
+        impl_->ctx = nullptr;
+    }
+    impl_->device = device;
+}
+
+namespace {
+
+void check(int rc, const char* what) {
+    if (rc != NPGE_ANCHOR_OK) {
+        throw Exception(std::string("AnchorFinder (GPU): ") + what + ": " +
+                        npge_anchor_last_error());
+    }
+}
+
+// The letters of the anchors of one block must agree up to the strand
+// (check_block, AnchorFinder.cpp:342-354): a cheap end-to-end self-check of the
+// device result against the sequences it was computed from.
+void check_block(const Block* block) {
+    if (block->size() < 2) throw Exception("AnchorFinder (GPU): block of one fragment");
+    const std::string first = block->front()->str();
+    for (Block::const_iterator it = block->begin(); it != block->end(); ++it) {
+        if ((*it)->str() != first) {
+            throw Exception("AnchorFinder (GPU): fragments of a block differ: " +
+                            first + " vs " + (*it)->str());
+        }
+    }
+}
+
+}  // namespace
+
+void AnchorFinder::run_impl() const {
+    Impl& st = *impl_;
+    npge_anchor_params params;
+    params.anchor_size = opt_value("anchor-size").as<int>();
+    params.anchor_similar = opt_value("anchor-similar").as<bool>() ? 1 : 0;
+    params.max_anchor_fragments = opt_value("max-anchor-fragments").as<int>();
+    BlockSet& bs = *block_set();
+    // one contiguous ASCII buffer + offsets; the caller index of a sequence is
+    // its index in `seqs` and comes back in frag_seq
+    std::vector<SequencePtr> seqs = bs.seqs();
+    std::vector<uint64_t> offsets(seqs.size() + 1, 0);
+    for (size_t i = 0; i < seqs.size(); i++) offsets[i + 1] = offsets[i] + seqs[i]->size();
+    std::string bases;
+    bases.reserve(offsets.back());
+    for (size_t i = 0; i < seqs.size(); i++) bases += seqs[i]->contents();
+    if (!st.ctx) check(npge_anchor_create(&st.ctx, st.device), "no CUDA device");
+    npge_anchor_result r;
+    check(npge_anchor_find(st.ctx, &params,
+                           reinterpret_cast<const uint8_t*>(bases.data()), offsets.data(),
+                           uint32_t(seqs.size()), st.used_hashes.data(),
+                           st.used_hashes.size(), &r),
+          "npge_anchor_find");
+    const size_t k = size_t(params.anchor_size);
+    try {
+        for (uint64_t b = 0; b < r.n_blocks; b++) {
+            Block* block = new Block;
+            for (uint64_t f = r.block_offsets[b]; f < r.block_offsets[b + 1]; f++) {
+                const size_t min_pos = r.frag_min_pos[f];
+                block->insert(new Fragment(seqs[r.frag_seq[f]].get(), min_pos,
+                                           min_pos + k - 1, r.frag_ori[f]));
+            }
+            bs.insert(block);  // the blockset owns it from here on
+            check_block(block);
+        }
+        // used_hashes_ stays sorted (SortedVector::extend + sort, :385-389)
+        st.used_hashes.insert(st.used_hashes.end(), r.new_used, r.new_used + r.n_new_used);
+        std::sort(st.used_hashes.begin(), st.used_hashes.end());
+        st.used_hashes.erase(std::unique(st.used_hashes.begin(), st.used_hashes.end()),
+                             st.used_hashes.end());
+    } catch (...) {
+        npge_anchor_result_free(&r);
+        throw;
+    }
+    npge_anchor_result_free(&r);
+}
+
+const char* AnchorFinder::name_impl() const {
+    return "Find anchors";  // AnchorFinder.cpp:408-410
+}
+
+}  // namespace gpu
+}  // namespace npge

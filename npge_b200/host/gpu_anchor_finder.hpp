@@ -1,0 +1,41 @@
+// gpu_anchor_finder.hpp -- npge::gpu::AnchorFinder, the drop-in for the
+// reference's AnchorFinder processor (src/algo/AnchorFinder.hpp:20-51).
+// Same options, same target blockset contract, same cross-run state
+// (used_hashes_); the work happens in libnpge_anchor.so (include/npge_anchor.h).
+#pragma once
+
+#ifdef NPGE_B200_REAL_HEADERS   // inside an NPGE checkout
+#include "Processor.hpp"
+#else
+#include "npge_facade.hpp"
+#endif
+
+namespace npge {
+namespace gpu {
+
+class AnchorFinder : public Processor {
+public:
+    AnchorFinder();
+    ~AnchorFinder();
+
+    // the CUDA device of this instance (default 0); call before run()
+    void set_device(int device);
+
+protected:
+    void run_impl() const;          // Processor.hpp:482
+    const char* name_impl() const;  // Processor.hpp:492
+
+private:
+    struct Impl;  // run_impl is const: the state lives behind a pointer, as in
+    Impl* impl_;  // the reference (AnchorFinder.hpp:48-50)
+};
+
+// Meta registration: replaces the built-in factory (Meta.hpp:83-87), so every
+// pipeline, Lua script and the CLI that asks for "AnchorFinder" gets this one.
+template <typename MetaT>
+inline void register_processors(MetaT* meta) {
+    meta->template set_processor<AnchorFinder>("AnchorFinder", true);
+}
+
+}  // namespace gpu
+}  // namespace npge

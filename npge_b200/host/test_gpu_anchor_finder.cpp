@@ -1,0 +1,231 @@
+// test_gpu_anchor_finder.cpp -- the reference's unit tests of AnchorFinder
+// (src/test/anchor_finder.cpp:18-110), run against npge::gpu::AnchorFinder.
+// BOOST_CHECK -> CHECK (counted as failure), BOOST_WARN -> WARN (printed only).
+//
+//   test_gpu_anchor_finder            all cases (needs a CUDA device)
+//   test_gpu_anchor_finder --no-gpu   only the cases that never reach the device
+#include <cstdio>
+#include <cstring>
+#include <memory>
+#include <string>
+
+#include "gpu_anchor_finder.hpp"
+
+using namespace npge;
+
+static int failures = 0, warnings = 0, checks = 0;
+
+#define CHECK(cond)                                                             \
+    do {                                                                        \
+        checks++;                                                               \
+        if (!(cond)) {                                                          \
+            failures++;                                                         \
+            std::printf("FAIL %s:%d: %s\n", __FILE__, __LINE__, #cond);         \
+        }                                                                       \
+    } while (0)
+#define WARN(cond)                                                              \
+    do {                                                                        \
+        if (!(cond)) {                                                          \
+            warnings++;                                                         \
+            std::printf("warn %s:%d: %s\n", __FILE__, __LINE__, #cond);         \
+        }                                                                       \
+    } while (0)
+
+static BlockSetPtr blockset_of(std::initializer_list<const char*> texts) {
+    BlockSetPtr bs = new_bs();
+    for (const char* t : texts) bs->add_sequence(std::make_shared<InMemorySequence>(t));
+    return bs;
+}
+
+// ---- cases that need no device ---------------------------------------------------
+static void options_and_rules() {
+    gpu::AnchorFinder af;
+    CHECK(af.opt_value("anchor-size").as<int>() == 20);
+    CHECK(af.opt_value("anchor-similar").as<bool>() == true);
+    CHECK(af.opt_value("max-anchor-fragments").as<int>() == 100000);
+    CHECK(af.opt_value("anchor-fp").as<double>() > 0.09);
+    CHECK(af.has_opt("workers") && af.has_opt("timing"));
+    CHECK(std::string(af.name()) == "Find anchors");
+    af.set_block_set(blockset_of({"ATGC"}));
+    for (int bad : {0, -5, 33}) {
+        af.set_opt_value("anchor-size", bad);
+        bool thrown = false;
+        try {
+            af.run();
+        } catch (const Exception& e) {
+            thrown = std::strstr(e.what(), "options") != nullptr;
+        }
+        CHECK(thrown);
+    }
+    bool thrown = false;
+    try {
+        af.set_opt_value("no-such-option", 1);
+    } catch (const Exception&) {
+        thrown = true;
+    }
+    CHECK(thrown);
+    af.set_options("--anchor-size 7 --anchor-similar 0 --max-anchor-fragments 12");
+    CHECK(af.opt_value("anchor-size").as<int>() == 7);
+    CHECK(af.opt_value("anchor-similar").as<bool>() == false);
+    CHECK(af.opt_value("max-anchor-fragments").as<int>() == 12);
+}
+
+static void workers_zero_skips_the_run() {  // Processor.cpp:667
+    gpu::AnchorFinder af;
+    BlockSetPtr bs = blockset_of({"GAAAGAAA"});
+    af.set_block_set(bs);
+    af.set_opt_value("anchor-size", 3);
+    af.set_workers(0);
+    af.run();  // must not touch the device
+    CHECK(bs->size() == 0);
+}
+
+static void meta_registration() {
+    Meta meta;
+    gpu::register_processors(&meta);
+    CHECK(meta.has("AnchorFinder"));
+    std::shared_ptr<Processor> p = meta.get("AnchorFinder");
+    CHECK(p->key() == "AnchorFinder");
+    CHECK(p->has_opt("anchor-size"));
+}
+
+static void sequence_normalisation() {  // test-lua/sequence.lua:1-40
+    InMemorySequence s("AT-G-C-A#T$N .C");
+    CHECK(s.contents() == "ATGCATNC");
+    InMemorySequence r("acgtRYn");
+    CHECK(r.contents() == "ACGTNNN");
+    InMemorySequence named("ATGC", "BRUAB&chr1&c");
+    CHECK(named.genome() == "BRUAB");
+    InMemorySequence plain("ATGC", "plasmid");
+    CHECK(plain.genome() == "");
+}
+
+// ---- src/test/anchor_finder.cpp ----------------------------------------------------
+static void AnchorFinder_main() {
+    BlockSetPtr bs = blockset_of({"tgGTCCGagCGGACggcc"});
+    gpu::AnchorFinder af;
+    af.set_block_set(bs);
+    af.set_opt_value("anchor-size", 5);
+    af.run();
+    WARN(bs->size() == 1);
+    if (bs->size() == 1) {
+        Fragment* f = bs->front()->front();
+        CHECK(f->str() == "GTCCG" || f->str() == "CGGAC");
+    }
+}
+
+static void AnchorFinder_n_negative() {
+    BlockSetPtr bs = blockset_of({"tgGTNCGagCGNACggcc"});
+    gpu::AnchorFinder af;
+    af.set_block_set(bs);
+    af.set_opt_value("anchor-size", 5);
+    af.run();
+    CHECK(bs->size() == 0);
+}
+
+static void AnchorFinder_n_positive() {
+    BlockSetPtr bs = blockset_of({"GTNCGATAnnnGTNCGATA"});
+    gpu::AnchorFinder af;
+    af.set_block_set(bs);
+    af.set_opt_value("anchor-size", 5);
+    af.run();
+    CHECK(bs->size() > 0);
+}
+
+static void AnchorFinder_palindrome_elimination() {
+    BlockSetPtr bs = blockset_of({"ATGCAT"});
+    gpu::AnchorFinder af;
+    af.set_block_set(bs);
+    af.set_opt_value("anchor-size", 6);
+    af.run();
+    CHECK(bs->size() == 0);
+}
+
+static void AnchorFinder_one_from_long_repeat() {
+    BlockSetPtr bs = blockset_of({"GAAAGAAA"});
+    gpu::AnchorFinder af;
+    af.set_block_set(bs);
+    af.set_opt_value("anchor-size", 3);
+    af.run();
+    WARN(bs->size() == 1);
+}
+
+static void AnchorFinder_several_sequences(int workers) {
+    BlockSetPtr bs = blockset_of({"GAAAGAAA", "GAAAGAAA"});
+    gpu::AnchorFinder af;
+    af.set_block_set(bs);
+    af.set_opt_value("anchor-size", 3);
+    if (workers) af.set_workers(workers);  // AnchorFinder_two_workers
+    af.run();
+    WARN(bs->size() >= 1 && bs->front()->size() == 4);
+    for (BlockSet::const_iterator b = bs->begin(); b != bs->end(); ++b) {
+        CHECK((*b)->size() >= 2);
+        for (Block::const_iterator f = (*b)->begin(); f != (*b)->end(); ++f) {
+            CHECK((*f)->length() == 3 && (*f)->str() == (*b)->front()->str());
+        }
+    }
+}
+
+// the processor's cross-run state: hashes already returned are not found again
+// by the same instance (used_hashes_, AnchorFinder.cpp:385-389)
+static void used_hashes_across_runs() {
+    gpu::AnchorFinder af;
+    af.set_opt_value("anchor-size", 4);
+    af.set_opt_value("anchor-similar", false);
+    BlockSetPtr bs1 = blockset_of({"ACGGTTCAACGGTTCA"});
+    af.set_block_set(bs1);
+    af.run();
+    const size_t first = bs1->size();
+    CHECK(first >= 2);
+    BlockSetPtr bs2 = blockset_of({"ACGGTTCAACGGTTCA"});
+    af.set_block_set(bs2);
+    af.run();
+    CHECK(bs2->size() <= 1 && bs2->size() < first);  // all but the first hash were used
+    gpu::AnchorFinder fresh;
+    fresh.set_opt_value("anchor-size", 4);
+    fresh.set_opt_value("anchor-similar", false);
+    BlockSetPtr bs3 = blockset_of({"ACGGTTCAACGGTTCA"});
+    fresh.set_block_set(bs3);
+    fresh.run();
+    CHECK(bs3->size() == first);
+}
+
+static void truncation() {
+    gpu::AnchorFinder af;
+    af.set_opt_value("anchor-size", 4);
+    af.set_opt_value("anchor-similar", false);
+    af.set_opt_value("max-anchor-fragments", 4);
+    BlockSetPtr bs = blockset_of({"ACGGTTCAACGGTTCAACGGTTCA"});
+    af.set_block_set(bs);
+    af.run();
+    size_t frags = 0;
+    for (BlockSet::const_iterator b = bs->begin(); b != bs->end(); ++b) frags += (*b)->size();
+    CHECK(frags <= 4 && bs->size() >= 1);
+}
+
+int main(int argc, char** argv) {
+    const bool no_gpu = argc > 1 && std::strcmp(argv[1], "--no-gpu") == 0;
+    options_and_rules();
+    workers_zero_skips_the_run();
+    meta_registration();
+    sequence_normalisation();
+    if (!no_gpu) {
+        try {
+            AnchorFinder_main();
+            AnchorFinder_n_negative();
+            AnchorFinder_n_positive();
+            AnchorFinder_palindrome_elimination();
+            AnchorFinder_one_from_long_repeat();
+            AnchorFinder_several_sequences(0);
+            AnchorFinder_several_sequences(2);
+            used_hashes_across_runs();
+            truncation();
+        } catch (const std::exception& e) {
+            failures++;
+            std::printf("FAIL exception: %s\n", e.what());
+        }
+    }
+    std::printf("%d checks, %d failures, %d warnings%s\n", checks, failures, warnings,
+                no_gpu ? " (no-gpu subset)" : "");
+    return failures ? 1 : 0;
+}
