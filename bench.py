@@ -290,10 +290,9 @@ def run_gpu(args, rank, world, local_rank):
     parity_stats = runner.finish(stats)
     if args.profile:
         if rank == 0:
-            print(json.dumps({"profile_run": True, "steps": args.steps,
-                              "ms_per_step": 1e3 * t_dev / args.steps,
-                              "stats": {k: v for k, v in stats.items()
-                                        if k != "digest"}}))
+            emit({"profile_run": True, "steps": args.steps,
+                  "ms_per_step": 1e3 * t_dev / args.steps,
+                  "stats": {k: v for k, v in stats.items() if k != "digest"}})
         return
 
     # ---- default options (anchor-similar=true, 100000 fragments) -----------

@@ -200,6 +200,12 @@ int npge_anchor_dist_count_a(npge_anchor_ctx* ctx, const npge_anchor_params* p,
 int npge_anchor_dist_scatter_peer(npge_anchor_ctx* ctx, const npge_anchor_params* p,
                                   const uint32_t* dest_rank, const int64_t* dest_off,
                                   uint32_t n_bins);
+/* The bulk variant of the peer exchange: after dist_pass_a (local pass A) the
+ * contiguous slice of every destination is copied into its receive buffer by a
+ * copy kernel (same dest_rank / dest_off tables as dist_scatter_peer). */
+int npge_anchor_dist_copy_peer(npge_anchor_ctx* ctx, const npge_anchor_params* p,
+                               const uint32_t* dest_rank, const int64_t* dest_off,
+                               uint32_t n_bins);
 int npge_anchor_dist_buffers(npge_anchor_ctx* ctx, uint64_t n_recv,
                              npge_anchor_dist_ptrs* out);
 int npge_anchor_dist_sort(npge_anchor_ctx* ctx, const npge_anchor_params* p,

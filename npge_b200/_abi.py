@@ -15,7 +15,7 @@ EXPORTS = [
     "npge_anchor_dist_buffers", "npge_anchor_dist_sort", "npge_anchor_dist_emit",
     "npge_anchor_dist_peer_alloc", "npge_anchor_dist_peer_open",
     "npge_anchor_dist_peer_close", "npge_anchor_dist_count_a",
-    "npge_anchor_dist_scatter_peer",
+    "npge_anchor_dist_scatter_peer", "npge_anchor_dist_copy_peer",
 ]
 IPC_BYTES = 128
 
@@ -115,6 +115,8 @@ def load():
     L.npge_anchor_dist_scatter_peer.restype = C.c_int
     L.npge_anchor_dist_scatter_peer.argtypes = [ctx, C.POINTER(Params), C.c_void_p,
                                                 C.c_void_p, C.c_uint32]
+    L.npge_anchor_dist_copy_peer.restype = C.c_int
+    L.npge_anchor_dist_copy_peer.argtypes = L.npge_anchor_dist_scatter_peer.argtypes
     L.npge_anchor_dist_buffers.restype = C.c_int
     L.npge_anchor_dist_buffers.argtypes = [ctx, C.c_uint64, C.POINTER(DistPtrs)]
     L.npge_anchor_dist_sort.restype = C.c_int

@@ -1112,6 +1112,8 @@ int dist_count_a(npge_anchor_ctx* ctx, const npge_anchor_params* p, bool scatter
     for (uint32_t a = 0; a < bins_a; a++) hist_out[a] = a_start[a + 1] - a_start[a];
     ctx->plan = plan;
     ctx->a_counted = true;
+    ctx->a_scattered = scatter;
+    ctx->a_start_h = a_start;
     return NPGE_ANCHOR_OK;
 }
 
@@ -1245,6 +1247,49 @@ extern "C" int npge_anchor_dist_scatter_peer(npge_anchor_ctx* ctx,
     }
     NPGE_CUDA(cudaStreamSynchronize(st));  // the peers may read after their barrier
     if (np) cudaEventElapsedTime(&ctx->dist_ms[1], ctx->ev[0], ctx->ev[1]);
+    ctx->a_counted = false;
+    return NPGE_ANCHOR_OK;
+}
+
+extern "C" int npge_anchor_dist_copy_peer(npge_anchor_ctx* ctx, const npge_anchor_params* p,
+                                          const uint32_t* dest_rank, const int64_t* dest_off,
+                                          uint32_t n_bins) {
+    if (!ctx || !dest_rank || !dest_off) return fail(NPGE_ANCHOR_ERR_PARAMS, "NULL argument");
+    NPGE_TRY(check_params(p));
+    if (!ctx->dist || !ctx->a_counted || !ctx->a_scattered) {
+        return fail(NPGE_ANCHOR_ERR_STATE, "npge_anchor_dist_pass_a has not run");
+    }
+    const MsdPlan plan = ctx->plan;
+    const uint32_t bins_a = 1u << plan.capa;
+    if (n_bins != bins_a) return fail(NPGE_ANCHOR_ERR_PARAMS, "n_bins differs from the plan");
+    if (ctx->peer_rec.empty()) {
+        return fail(NPGE_ANCHOR_ERR_STATE, "npge_anchor_dist_peer_open has not been called");
+    }
+    NPGE_CUDA(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    const std::vector<uint32_t>& as = ctx->a_start_h;
+    NPGE_CUDA(cudaEventRecord(ctx->ev[0], st));
+    for (uint32_t a = 0; a < bins_a;) {  // one copy per run of buckets with one owner
+        uint32_t e = a + 1;
+        while (e < bins_a && dest_rank[e] == dest_rank[a] && dest_off[e] == dest_off[a]) e++;
+        const uint32_t d = dest_rank[a];
+        if (d >= ctx->peer_rec.size()) return fail(NPGE_ANCHOR_ERR_PARAMS, "dest_rank out of range");
+        const uint64_t first = as[a], n = as[e] - as[a];
+        const int64_t to = dest_off[a] + int64_t(first);
+        if (n && (to < 0 || uint64_t(to) + n > ctx->peer_capacity)) {
+            return fail(NPGE_ANCHOR_ERR_PARAMS, "destination outside the receive buffer");
+        }
+        launch_peer_copy(ptr<uint64_t>(ctx->rec[0]) + first,
+                         static_cast<uint64_t*>(ctx->peer_rec[d]) + to,
+                         plan.wide ? ptr<uint32_t>(ctx->rhi[0]) + first : nullptr,
+                         plan.wide ? static_cast<uint32_t*>(ctx->peer_hi[d]) + to : nullptr,
+                         n, st, &ctx->dist_launches);
+        a = e;
+    }
+    NPGE_CUDA(cudaGetLastError());
+    NPGE_CUDA(cudaEventRecord(ctx->ev[1], st));
+    NPGE_CUDA(cudaStreamSynchronize(st));
+    cudaEventElapsedTime(&ctx->dist_ms[7], ctx->ev[0], ctx->ev[1]);
     ctx->a_counted = false;
     return NPGE_ANCHOR_OK;
 }
@@ -1445,9 +1490,12 @@ extern "C" int npge_anchor_dist_emit(npge_anchor_ctx* ctx, const npge_anchor_par
     // (+ candidate count)] [scan + emit]
     s.ms_hist = ctx->dist_ms[0];
     for (int i = 0; i < 3; i++) s.ms_pass[i] = ctx->dist_ms[i + 1];
+    s.ms_pass[0] += ctx->dist_ms[7];  // bulk exchange: the peer copies belong to pass A
+    s.ms_pass[5] = ctx->dist_ms[7];
     s.ms_pass[3] = ctx->dist_ms[4] + ctx->dist_ms[5];
     s.ms_pass[4] = ctx->dist_ms[6];
-    s.ms_sort = ctx->dist_ms[0] + ctx->dist_ms[1] + ctx->dist_ms[2] + ctx->dist_ms[3];
+    s.ms_sort = ctx->dist_ms[0] + ctx->dist_ms[1] + ctx->dist_ms[2] + ctx->dist_ms[3] +
+                ctx->dist_ms[7];
     s.ms_group = ctx->dist_ms[4] + ctx->dist_ms[5] + ctx->dist_ms[6];
     s.ms_total = s.ms_sort + s.ms_group;  // device time of this rank's kernels
     const int model_passes = (2 * p->anchor_size + 7) / 8;

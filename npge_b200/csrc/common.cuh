@@ -171,6 +171,8 @@ struct npge_anchor_ctx {
     uint64_t peer_capacity = 0;              // records every receive buffer can take
     npge_b200::DeviceBuffer peer_tab;        // per-bucket destination addresses
     bool a_counted = false;
+    std::vector<uint32_t> a_start_h;         // host copy of this rank's a_start
+    bool a_scattered = false;                // rec[0] holds the local pass A output
     uint64_t dist_n_used = 0;
     float dist_ms[8] = {};
     // device result

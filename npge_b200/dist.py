@@ -228,6 +228,12 @@ class CudaStages(AnchorEngine):
         self._check(self._lib.npge_anchor_dist_scatter_peer(
             self._ctx, C.byref(params), dr.ctypes.data, do.ctypes.data, len(dr)))
 
+    def dist_copy_peer(self, params, dest_rank, dest_off):
+        dr = np.ascontiguousarray(dest_rank, dtype=np.uint32)
+        do = np.ascontiguousarray(dest_off, dtype=np.int64)
+        self._check(self._lib.npge_anchor_dist_copy_peer(
+            self._ctx, C.byref(params), dr.ctypes.data, do.ctypes.data, len(dr)))
+
     def dist_buffers(self, n_send, n_recv):
         import torch
         p = _abi.DistPtrs()
@@ -356,9 +362,13 @@ class DistAnchorFinder:
     numbered one after the other in rank order."""
 
     def __init__(self, device=0, group=None, stages=None, exchange=None):
-        """exchange: "peer" = pass A writes into the owners' HBM over NVLink (CUDA
-        IPC); "collective" = local pass A + all-to-all.  Default: peer when the
-        stages support it and every rank could map every other's buffer."""
+        """exchange: how the records reach the rank that owns their hash range.
+        "peer": pass A scatters straight into the owners' HBM over NVLink (CUDA
+        IPC; no extra pass, best at 2 GPUs); "bulk": local pass A, then a copy
+        kernel writes every destination's contiguous slice into its receive
+        buffer (large NVLink writes, best at 4+ GPUs); "collective": local pass
+        A + all_to_all_single.  Default ("auto"): peer at 2 ranks, bulk above,
+        collective when a rank cannot map a peer's buffer."""
         import os
         self.comm = _Comm(group)
         self.rank, self.world = self.comm.rank, self.comm.world
@@ -367,10 +377,10 @@ class DistAnchorFinder:
         self._k = None
         self.exchange_ms = {}
         want = exchange or os.environ.get("NPGE_ANCHOR_EXCHANGE") or "auto"
-        if want not in ("auto", "peer", "collective"):
-            raise ValueError("exchange must be peer, collective or auto")
+        if want not in ("auto", "peer", "bulk", "collective"):
+            raise ValueError("exchange must be peer, bulk, collective or auto")
         if not hasattr(self.stages, "dist_peer_alloc"):
-            if want == "peer":
+            if want in ("peer", "bulk"):
                 raise ValueError("these stages have no peer exchange")
             want = "collective"
         self._want = want
@@ -394,11 +404,12 @@ class DistAnchorFinder:
         errs = [e for e in self.comm.gather_objects(err) if e]
         if errs:
             st.dist_peer_close()
-            if self._want == "peer":
+            if self._want in ("peer", "bulk"):
                 raise AnchorError(_abi.ERR_CUDA, errs[0])
             self.exchange = "collective"
             return
-        self.exchange = "peer"
+        self.exchange = (self._want if self._want != "auto"
+                         else ("peer" if self.world <= 2 else "bulk"))
         self._capacity = capacity
 
     # -- upload ------------------------------------------------------------------------
@@ -467,7 +478,7 @@ class DistAnchorFinder:
         if self._want != "collective":
             # room for an uneven split of the job's windows; grown on demand
             need = int(gstart[-1]) // self.world * 5 // 4 + 65536
-            if need > self._capacity or self.exchange != "peer":
+            if need > self._capacity or self.exchange == "collective":
                 self._peer_setup(need)
 
     # -- find --------------------------------------------------------------------------
@@ -505,9 +516,10 @@ class DistAnchorFinder:
             t_prev[0] = now
 
         dev = comm.torch.device("cuda", self.device) if comm.nccl else None
-        peer = self.exchange == "peer"
-        hist = st.dist_count_a(params) if peer else st.dist_pass_a(params)
-        lap("count_a" if peer else "pass_a")
+        fused = self.exchange == "peer"
+        peer = self.exchange in ("peer", "bulk")
+        hist = st.dist_count_a(params) if fused else st.dist_pass_a(params)
+        lap("count_a" if fused else "pass_a")
         # (also the step's barrier: no rank scatters into a receive buffer whose
         # owner has not finished its previous step)
         hist_all = comm.gather_array(hist, dev)
@@ -519,10 +531,14 @@ class DistAnchorFinder:
             lap("tables")
             if max(n_recv) > self._capacity:  # the same decision on every rank
                 self._peer_setup(max(n_recv) * 9 // 8 + 65536)
-                if self.exchange != "peer":
+                if self.exchange == "collective":
                     raise AnchorError(_abi.ERR_CUDA, "peer buffers could not be regrown")
-            st.dist_scatter_peer(params, dest_rank, dest_off)
-            lap("scatter_peer")
+            if fused:
+                st.dist_scatter_peer(params, dest_rank, dest_off)
+                lap("scatter_peer")
+            else:
+                st.dist_copy_peer(params, dest_rank, dest_off)
+                lap("copy_peer")
             self._timed("barrier", lambda: comm.barrier(dev))  # every scatter has landed
             lap("barrier")
             buf = st.dist_buffers(0, tables["n_recv"])

@@ -9,7 +9,7 @@ from test_dist_cpu import launch
 pytestmark = pytest.mark.gpu
 
 
-EXCHANGES = ["peer", "collective"]
+EXCHANGES = ["peer", "bulk", "collective"]
 
 
 @pytest.mark.parametrize("exchange", EXCHANGES)
