@@ -1175,6 +1175,7 @@ extern "C" int npge_anchor_dist_peer_open(npge_anchor_ctx* ctx, uint32_t world,
     NPGE_TRY(npge_anchor_dist_peer_close(ctx));
     ctx->peer_rec.assign(world, nullptr);
     ctx->peer_hi.assign(world, nullptr);
+    ctx->dist_rank = rank;
     for (uint32_t r = 0; r < world; r++) {
         if (r == rank) {
             ctx->peer_rec[r] = ctx->recv_rec.ptr;
@@ -1269,7 +1270,10 @@ extern "C" int npge_anchor_dist_copy_peer(npge_anchor_ctx* ctx, const npge_ancho
     cudaStream_t st = ctx->stream;
     const std::vector<uint32_t>& as = ctx->a_start_h;
     NPGE_CUDA(cudaEventRecord(ctx->ev[0], st));
-    for (uint32_t a = 0; a < bins_a;) {  // one copy per run of buckets with one owner
+    // one copy per run of buckets with one owner
+    struct Run { uint32_t d; uint64_t first, n; int64_t to; };
+    std::vector<Run> runs;
+    for (uint32_t a = 0; a < bins_a;) {
         uint32_t e = a + 1;
         while (e < bins_a && dest_rank[e] == dest_rank[a] && dest_off[e] == dest_off[a]) e++;
         const uint32_t d = dest_rank[a];
@@ -1279,12 +1283,21 @@ extern "C" int npge_anchor_dist_copy_peer(npge_anchor_ctx* ctx, const npge_ancho
         if (n && (to < 0 || uint64_t(to) + n > ctx->peer_capacity)) {
             return fail(NPGE_ANCHOR_ERR_PARAMS, "destination outside the receive buffer");
         }
-        launch_peer_copy(ptr<uint64_t>(ctx->rec[0]) + first,
-                         static_cast<uint64_t*>(ctx->peer_rec[d]) + to,
-                         plan.wide ? ptr<uint32_t>(ctx->rhi[0]) + first : nullptr,
-                         plan.wide ? static_cast<uint32_t*>(ctx->peer_hi[d]) + to : nullptr,
-                         n, st, &ctx->dist_launches);
+        if (n) runs.push_back({d, first, n, to});
         a = e;
+    }
+    // ring order: rank r starts with the owner after itself, so that in every
+    // round each receive buffer is written by one sender (no incast on a link)
+    const uint32_t world = uint32_t(ctx->peer_rec.size());
+    std::stable_sort(runs.begin(), runs.end(), [&](const Run& x, const Run& y) {
+        return (x.d + world - ctx->dist_rank - 1) % world < (y.d + world - ctx->dist_rank - 1) % world;
+    });
+    for (const Run& r : runs) {
+        launch_peer_copy(ptr<uint64_t>(ctx->rec[0]) + r.first,
+                         static_cast<uint64_t*>(ctx->peer_rec[r.d]) + r.to,
+                         plan.wide ? ptr<uint32_t>(ctx->rhi[0]) + r.first : nullptr,
+                         plan.wide ? static_cast<uint32_t*>(ctx->peer_hi[r.d]) + r.to : nullptr,
+                         r.n, st, &ctx->dist_launches);
     }
     NPGE_CUDA(cudaGetLastError());
     NPGE_CUDA(cudaEventRecord(ctx->ev[1], st));

@@ -168,6 +168,7 @@ struct npge_anchor_ctx {
     // peer exchange: receive buffers of all ranks mapped through CUDA IPC
     std::vector<void*> peer_opened;          // to close
     std::vector<void*> peer_rec, peer_hi;    // [world]; own rank: recv_rec / recv_hi
+    uint32_t dist_rank = 0;                  // this rank's index in peer_rec
     uint64_t peer_capacity = 0;              // records every receive buffer can take
     npge_b200::DeviceBuffer peer_tab;        // per-bucket destination addresses
     bool a_counted = false;

@@ -233,6 +233,7 @@ struct __align__(16) PassSmem {
     uint64_t rec[kTile];
     uint32_t hi[WIDE ? kTile : 4];
     uint16_t dig[kTile];  // pass A: the digit is not part of the record
+    uint32_t tile_seq[2]; // pass A, job-wide positions: sequence of the tile's ends
 };
 
 // ---- pass A: generate + partition by the top wa bits -----------------------------
@@ -249,10 +250,22 @@ pass_a_kernel(const uint32_t* __restrict__ packed, const uint32_t* __restrict__ 
     constexpr int BINS = Smem::BINS;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t tile = blockIdx.x;
-    stage_genome_tile(sm.st, packed, nmask, tile);
+    const uint32_t gbase = tile * uint32_t(kTile);
+    if (GLOBAL && tid < 2) {  // most tiles lie inside one sequence: one delta for all
+        const uint32_t g = gbase + (tid ? uint32_t(kTile) - 1 : 0u);
+        const uint32_t q = g >> pm.lut_shift;
+        uint32_t lo = pm.lut[q], hi2 = pm.lut[q + 1] + 1;
+        while (hi2 - lo > 1) {
+            uint32_t mid = (lo + hi2) >> 1;
+            if (pm.seq_start[mid] <= g) lo = mid; else hi2 = mid;
+        }
+        sm.tile_seq[tid] = lo;
+    }
+    stage_genome_tile(sm.st, packed, nmask, tile);  // (barrier inside)
     const int sa = plan.rem;
     const uint64_t rmask = (1ull << plan.rem) - 1;  // rem <= 63
-    const uint32_t gbase = tile * uint32_t(kTile);
+    const bool one_seq = GLOBAL && sm.tile_seq[0] == sm.tile_seq[1];
+    const uint32_t delta0 = one_seq ? pm.delta[sm.tile_seq[0]] : 0u;
     uint64_t rec[kRI];
     uint32_t hi[kRI], digit[kRI], slot[kRI];
 #pragma unroll
@@ -264,7 +277,9 @@ pass_a_kernel(const uint32_t* __restrict__ packed, const uint32_t* __restrict__ 
         uint64_t kr = h & rmask;
         // payload: position << 1 | (ori == +1)
         uint32_t g = gbase + rel;
-        if (GLOBAL && ok) {
+        if (GLOBAL && one_seq) {
+            g += delta0;
+        } else if (GLOBAL && ok) {
             const uint32_t q = g >> pm.lut_shift;
             uint32_t lo = pm.lut[q], hi2 = pm.lut[q + 1] + 1;  // answer in [lo, hi2)
             while (hi2 - lo > 1) {
