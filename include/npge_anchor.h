@@ -218,6 +218,32 @@ int npge_anchor_dist_sort(npge_anchor_ctx* ctx, const npge_anchor_params* p,
 int npge_anchor_dist_emit(npge_anchor_ctx* ctx, const npge_anchor_params* p,
                           uint64_t local_limit, npge_anchor_stats* stats);
 
+/* ---- FragmentFinder (src/algo/FragmentFinder.cpp:42-171) ---------------------------
+ * Every exact occurrence of `pattern` (ATGCN bytes, N matches only N) on either
+ * strand of the sequences: ori = +1 where the text equals the pattern, -1 where
+ * its reverse complement does (both at a palindrome).  Order: sequences by size
+ * descending (ties by caller index), position ascending, +1 before -1 -- the
+ * order of a one-worker run of the reference -- cut to max_matches (option
+ * max-matches, >= 1).  One single-fragment Block per match on the host side. */
+typedef struct {
+    uint64_t n_matches;            /* min(total_matches, max_matches) */
+    uint64_t total_matches;        /* before the cut */
+    const uint32_t* frag_seq;      /* index of the sequence as passed */
+    const uint32_t* frag_min_pos;  /* max_pos = min_pos + pattern_len - 1 */
+    const int8_t* frag_ori;
+    void* owner_;
+} npge_fragment_result;
+int npge_fragment_find(npge_anchor_ctx* ctx, const uint8_t* pattern, uint32_t pattern_len,
+                       int64_t max_matches, const uint8_t* bases,
+                       const uint64_t* seq_offsets, uint32_t n_seqs,
+                       npge_fragment_result* out);
+/* on the sequences of the last npge_anchor_upload (its anchor_size must not
+ * exceed pattern_len: shorter sequences were dropped at upload) */
+int npge_fragment_find_device(npge_anchor_ctx* ctx, const uint8_t* pattern,
+                              uint32_t pattern_len, int64_t max_matches,
+                              npge_fragment_result* out);
+void npge_fragment_result_free(npge_fragment_result* out);
+
 /* Library self-description: "npge_anchor <version> sm_100a" */
 const char* npge_anchor_version(void);
 

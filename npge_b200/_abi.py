@@ -16,6 +16,7 @@ EXPORTS = [
     "npge_anchor_dist_peer_alloc", "npge_anchor_dist_peer_open",
     "npge_anchor_dist_peer_close", "npge_anchor_dist_count_a",
     "npge_anchor_dist_scatter_peer", "npge_anchor_dist_copy_peer",
+    "npge_fragment_find", "npge_fragment_find_device", "npge_fragment_result_free",
 ]
 IPC_BYTES = 128
 
@@ -49,6 +50,14 @@ class Stats(C.Structure):
         ("ms_sort", C.c_float), ("ms_group", C.c_float),
         ("ms_total", C.c_float), ("ms_pass", C.c_float * 16),
         ("bytes_algorithmic", C.c_uint64), ("bytes_moved", C.c_uint64),
+    ]
+
+
+class FragmentResult(C.Structure):
+    _fields_ = [
+        ("n_matches", C.c_uint64), ("total_matches", C.c_uint64),
+        ("frag_seq", C.POINTER(C.c_uint32)), ("frag_min_pos", C.POINTER(C.c_uint32)),
+        ("frag_ori", C.POINTER(C.c_int8)), ("owner_", C.c_void_p),
     ]
 
 
@@ -126,5 +135,13 @@ def load():
     L.npge_anchor_dist_emit.restype = C.c_int
     L.npge_anchor_dist_emit.argtypes = [ctx, C.POINTER(Params), C.c_uint64,
                                         C.POINTER(Stats)]
+    L.npge_fragment_find.restype = C.c_int
+    L.npge_fragment_find.argtypes = [ctx, C.c_char_p, C.c_uint32, C.c_int64, C.c_void_p,
+                                     C.c_void_p, C.c_uint32, C.POINTER(FragmentResult)]
+    L.npge_fragment_find_device.restype = C.c_int
+    L.npge_fragment_find_device.argtypes = [ctx, C.c_char_p, C.c_uint32, C.c_int64,
+                                            C.POINTER(FragmentResult)]
+    L.npge_fragment_result_free.restype = None
+    L.npge_fragment_result_free.argtypes = [C.POINTER(FragmentResult)]
     _lib = L
     return L

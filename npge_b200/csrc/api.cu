@@ -230,7 +230,7 @@ extern "C" void npge_anchor_destroy(npge_anchor_ctx* ctx) {
                            &ctx->bstatus, &ctx->units, &ctx->rec[0], &ctx->rec[1], &ctx->rhi[0],
                            &ctx->rhi[1], &ctx->seq_lut, &ctx->g_seq_start, &ctx->g_seq_caller,
                            &ctx->g_seq_lut, &ctx->pos_delta, &ctx->recv_rec, &ctx->recv_hi,
-                           &ctx->peer_tab};
+                           &ctx->peer_tab, &ctx->frag_pat, &ctx->frag_tiles, &ctx->frag_out};
     for (void* q : ctx->peer_opened) cudaIpcCloseMemHandle(q);
     for (DeviceBuffer* b : all) release(*b);
     for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
@@ -1525,4 +1525,156 @@ extern "C" int npge_anchor_dist_emit(npge_anchor_ctx* ctx, const npge_anchor_par
     ctx->have_result = true;
     if (stats) *stats = s;
     return NPGE_ANCHOR_OK;
+}
+
+// ==== FragmentFinder (src/algo/FragmentFinder.cpp) =================================
+namespace {
+
+// 2-bit codes of the reference (A0 T1 G2 C3; char_to_size.hpp:24-36); N -> code 0
+// + mask bit, like pack_kernel.  Returns false for a byte outside ATGCN.
+bool pack_pattern(const std::string& p, std::vector<uint64_t>& key, std::vector<uint32_t>& mask) {
+    const size_t chunks = (p.size() + 31) / 32;
+    key.assign(chunks, 0);
+    mask.assign(chunks, 0);
+    for (size_t i = 0; i < p.size(); i++) {
+        uint64_t code = 0;
+        switch (p[i]) {
+        case 'A': code = 0; break;
+        case 'T': code = 1; break;
+        case 'G': code = 2; break;
+        case 'C': code = 3; break;
+        case 'N': mask[i / 32] |= 1u << (i % 32); break;
+        default: return false;
+        }
+        key[i / 32] |= code << (2 * (i % 32));
+    }
+    return true;
+}
+
+struct FragmentHost {
+    PinnedVector<uint32_t> seq, pos;
+    PinnedVector<int8_t> ori;
+};
+
+}  // namespace
+
+extern "C" int npge_fragment_find_device(npge_anchor_ctx* ctx, const uint8_t* pattern,
+                                         uint32_t pattern_len, int64_t max_matches,
+                                         npge_fragment_result* out) {
+    if (!out) return fail(NPGE_ANCHOR_ERR_PARAMS, "out is NULL");
+    memset(out, 0, sizeof(*out));
+    if (!ctx || !pattern) return fail(NPGE_ANCHOR_ERR_PARAMS, "NULL argument");
+    // the option checks of the processor: FragmentFinder.cpp:18-28, :37
+    if (pattern_len == 0) return fail(NPGE_ANCHOR_ERR_PARAMS, "'pattern' should not be empty");
+    if (max_matches < 1) return fail(NPGE_ANCHOR_ERR_PARAMS, "max-matches >= 1 is violated");
+    if (!ctx->uploaded || ctx->dist) {
+        return fail(NPGE_ANCHOR_ERR_STATE, "npge_anchor_upload has not been called");
+    }
+    if (uint32_t(ctx->upload_k) > pattern_len) {
+        return fail(NPGE_ANCHOR_ERR_STATE,
+                    "sequences were uploaded with an anchor-size above the pattern length");
+    }
+    std::string fwd(reinterpret_cast<const char*>(pattern), pattern_len), rc(pattern_len, 'N');
+    for (uint32_t i = 0; i < pattern_len; i++) {
+        char c = fwd[pattern_len - 1 - i];  // complement.hpp:19-32: N stays N
+        rc[i] = c == 'A' ? 'T' : c == 'T' ? 'A' : c == 'G' ? 'C' : c == 'C' ? 'G' : c;
+    }
+    std::vector<uint64_t> key[2];
+    std::vector<uint32_t> mask[2];
+    if (!pack_pattern(fwd, key[0], mask[0]) || !pack_pattern(rc, key[1], mask[1])) {
+        return fail(NPGE_ANCHOR_ERR_INPUT, "pattern holds a byte outside ATGCN (to_atgcn first)");
+    }
+    NPGE_CUDA(cudaSetDevice(ctx->device));
+    const uint32_t chunks = uint32_t(key[0].size());
+    const uint32_t tiles = fragment_tiles(ctx->n_padded);
+    const uint64_t cap = std::min<uint64_t>(uint64_t(max_matches), 2 * ctx->n_positions);
+    NPGE_TRY(ensure(ctx->frag_pat, size_t(chunks) * 24));
+    NPGE_TRY(ensure(ctx->frag_tiles, size_t(tiles + 1) * 12 + 16));
+    NPGE_TRY(ensure(ctx->frag_out, cap * 9 + 64));
+    cudaStream_t st = ctx->stream;
+    uint8_t* pat = ptr<uint8_t>(ctx->frag_pat);
+    for (int s = 0; s < 2; s++) {
+        NPGE_CUDA(cudaMemcpyAsync(pat + size_t(s) * chunks * 8, key[s].data(), chunks * 8,
+                                  cudaMemcpyHostToDevice, st));
+        NPGE_CUDA(cudaMemcpyAsync(pat + size_t(chunks) * 16 + size_t(s) * chunks * 4,
+                                  mask[s].data(), chunks * 4, cudaMemcpyHostToDevice, st));
+    }
+    FragmentArgs a = {};
+    a.packed = ptr<uint32_t>(ctx->packed);
+    a.nmask = ptr<uint32_t>(ctx->nmask);
+    a.n_positions = ctx->n_positions;
+    a.n_padded = ctx->n_padded;
+    a.pat_key = reinterpret_cast<const uint64_t*>(pat);
+    a.pat_mask = reinterpret_cast<const uint32_t*>(pat + size_t(chunks) * 16);
+    a.pattern_len = pattern_len;
+    a.n_chunks = chunks;
+    a.seq_start = ptr<uint64_t>(ctx->seq_start);
+    a.seq_caller = ptr<uint32_t>(ctx->seq_caller);
+    a.seq_lut = ptr<uint32_t>(ctx->seq_lut);
+    a.lut_shift = ctx->lut_shift;
+    a.max_matches = cap;
+    uint8_t* tl = ptr<uint8_t>(ctx->frag_tiles);
+    a.summary = reinterpret_cast<uint64_t*>(tl);
+    a.tile_offset = reinterpret_cast<uint64_t*>(tl + 16);
+    a.tile_count = reinterpret_cast<uint32_t*>(tl + 16 + size_t(tiles) * 8);
+    uint8_t* ro = ptr<uint8_t>(ctx->frag_out);
+    a.r_seq = reinterpret_cast<uint32_t*>(ro);
+    a.r_pos = reinterpret_cast<uint32_t*>(ro + cap * 4 + 16 - (cap * 4) % 16);
+    a.r_ori = reinterpret_cast<int8_t*>(reinterpret_cast<uint8_t*>(a.r_pos) + cap * 4);
+    uint32_t launches = 0;
+    uint64_t total = 0;
+    if (tiles) {
+        launch_fragment_find(a, 0, st, &launches);
+        launch_fragment_find(a, 1, st, &launches);
+        NPGE_CUDA(cudaGetLastError());
+        NPGE_CUDA(cudaMemcpyAsync(&total, a.summary, 8, cudaMemcpyDeviceToHost, st));
+    }
+    NPGE_CUDA(cudaStreamSynchronize(st));
+    const uint64_t n = std::min<uint64_t>(total, cap);
+    FragmentHost* r = new (std::nothrow) FragmentHost;
+    if (!r) return fail(NPGE_ANCHOR_ERR_MEMORY, "out of host memory");
+    try {
+        r->seq.resize(n);
+        r->pos.resize(n);
+        r->ori.resize(n);
+    } catch (std::bad_alloc&) {
+        delete r;
+        return fail(NPGE_ANCHOR_ERR_MEMORY, "out of host memory for the result");
+    }
+    if (n) {
+        cudaMemcpyAsync(r->seq.data(), a.r_seq, n * 4, cudaMemcpyDeviceToHost, st);
+        cudaMemcpyAsync(r->pos.data(), a.r_pos, n * 4, cudaMemcpyDeviceToHost, st);
+        cudaMemcpyAsync(r->ori.data(), a.r_ori, n, cudaMemcpyDeviceToHost, st);
+        cudaError_t e = cudaStreamSynchronize(st);
+        if (e != cudaSuccess) {
+            delete r;
+            return fail(NPGE_ANCHOR_ERR_CUDA, cudaGetErrorString(e));
+        }
+    }
+    out->n_matches = n;
+    out->total_matches = total;
+    out->frag_seq = r->seq.data();
+    out->frag_min_pos = r->pos.data();
+    out->frag_ori = r->ori.data();
+    out->owner_ = r;
+    ctx->stats.gpu_launches = launches;
+    return NPGE_ANCHOR_OK;
+}
+
+extern "C" int npge_fragment_find(npge_anchor_ctx* ctx, const uint8_t* pattern,
+                                  uint32_t pattern_len, int64_t max_matches,
+                                  const uint8_t* bases, const uint64_t* seq_offsets,
+                                  uint32_t n_seqs, npge_fragment_result* out) {
+    if (!out) return fail(NPGE_ANCHOR_ERR_PARAMS, "out is NULL");
+    memset(out, 0, sizeof(*out));
+    if (pattern_len == 0) return fail(NPGE_ANCHOR_ERR_PARAMS, "'pattern' should not be empty");
+    const int32_t k = int32_t(std::min<uint32_t>(pattern_len, NPGE_ANCHOR_MAX_SIZE));
+    NPGE_TRY(npge_anchor_upload(ctx, k, bases, seq_offsets, n_seqs));
+    return npge_fragment_find_device(ctx, pattern, pattern_len, max_matches, out);
+}
+
+extern "C" void npge_fragment_result_free(npge_fragment_result* out) {
+    if (!out) return;
+    delete static_cast<FragmentHost*>(out->owner_);
+    memset(out, 0, sizeof(*out));
 }

@@ -157,6 +157,30 @@ void launch_bucket_stage(const BucketArgs& a, int stage, uint64_t max_records,
 void launch_bucket(const BucketArgs& a, bool similar, uint64_t max_records,
                    cudaStream_t s, cudaEvent_t* ev, uint32_t* launches);
 
+// ---- FragmentFinder (fragment_kernels.cu) --------------------------------------------
+struct FragmentArgs {
+    const uint32_t* packed;
+    const uint32_t* nmask;
+    uint64_t n_positions, n_padded;
+    const uint64_t* pat_key;   // [2][n_chunks]: pattern, reverse complement of it
+    const uint32_t* pat_mask;  // [2][n_chunks]: N positions
+    uint32_t pattern_len, n_chunks;
+    const uint64_t* seq_start;
+    const uint32_t* seq_caller;
+    const uint32_t* seq_lut;
+    int lut_shift;
+    uint64_t max_matches;
+    uint32_t* tile_count;
+    uint64_t* tile_offset;
+    uint64_t* summary;         // [0] matches before the cut
+    uint32_t* r_seq;
+    uint32_t* r_pos;
+    int8_t* r_ori;
+};
+uint32_t fragment_tiles(uint64_t n_padded);
+void launch_fragment_find(const FragmentArgs& a, int stage, cudaStream_t s,
+                          uint32_t* launches);
+
 struct GroupArgs {
     const uint32_t* klo;
     const uint32_t* khi;   // nullptr when k <= 16

@@ -174,6 +174,42 @@ class AnchorEngine:
         return {"n_blocks": nb, "n_fragments": nf,
                 "result_bytes": nf * 9 + (nb + 1) * 8 + nb * 8}
 
+    # ---- FragmentFinder (src/algo/FragmentFinder.cpp) --------------------------------
+    def _matches(self, r):
+        n = int(r.n_matches)
+        try:
+            if n == 0:
+                out = []
+            else:
+                seq = np.ctypeslib.as_array(r.frag_seq, (n,))
+                pos = np.ctypeslib.as_array(r.frag_min_pos, (n,))
+                ori = np.ctypeslib.as_array(r.frag_ori, (n,))
+                out = list(zip(seq.tolist(), pos.tolist(), ori.tolist()))
+            return out, int(r.total_matches)
+        finally:
+            self._lib.npge_fragment_result_free(C.byref(r))
+
+    def find_fragments(self, seqs, pattern, max_matches=100, with_total=False):
+        """Every occurrence of `pattern` (ATGCN text) on either strand:
+        [(seq, min_pos, ori)] in scan order, cut to max_matches."""
+        bases, offsets = seqs if isinstance(seqs, tuple) else concat(seqs)
+        p = pattern.encode() if isinstance(pattern, str) else bytes(pattern)
+        r = _abi.FragmentResult()
+        self._check(self._lib.npge_fragment_find(
+            self._ctx, p, len(p), int(max_matches), bases.ctypes.data,
+            offsets.ctypes.data, len(offsets) - 1, C.byref(r)))
+        out, total = self._matches(r)
+        return (out, total) if with_total else out
+
+    def find_fragments_device(self, pattern, max_matches=100, with_total=False):
+        """The same on the sequences of the last upload()."""
+        p = pattern.encode() if isinstance(pattern, str) else bytes(pattern)
+        r = _abi.FragmentResult()
+        self._check(self._lib.npge_fragment_find_device(
+            self._ctx, p, len(p), int(max_matches), C.byref(r)))
+        out, total = self._matches(r)
+        return (out, total) if with_total else out
+
     def stats(self):
         s = _abi.Stats()
         self._check(self._lib.npge_anchor_get_stats(self._ctx, C.byref(s)))

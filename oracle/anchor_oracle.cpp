@@ -823,3 +823,79 @@ extern "C" void oracle_digest(const oracle_result* r, uint64_t digest[2]) {
     digest[0] = d0;
     digest[1] = d1;
 }
+
+/* ====================================================================== */
+/* FragmentFinder: src/algo/FragmentFinder.cpp:42-171   */
+/* ====================================================================== */
+/* One worker (the reference's result order depends on thread timing with
+ * more): sequences by size descending (make_seqs), positions ascending, the
+ * forward match before the reverse one at a position (test(), :110-117);
+ * the scan of a sequence stops once more than max_matches were collected
+ * (:125-127) and the list is cut to max_matches (:155-164).
+ * Output: one (seq, min_pos, ori) per match, arrays malloc'ed here.        */
+extern "C" int oracle_fragment_find(const char* pattern, uint32_t pattern_len,
+                                    int64_t max_matches, const char* bases,
+                                    const uint64_t* offsets, uint32_t n_seqs,
+                                    uint64_t* n_out, uint32_t** seq_out,
+                                    uint32_t** pos_out, int8_t** ori_out) {
+    if (pattern_len == 0 || max_matches < 1) {
+        return 1;  /* the option checks of the processor (:18-28, :37) */
+    }
+    try {
+        const std::string p(pattern, pattern_len);  /* already to_atgcn-clean */
+        const int L = int(pattern_len);
+        const hash_t ph = hash_of([&](int j) { return p[j]; }, L, 1);
+        const bool has_n = p.find('N') != std::string::npos;
+        std::vector<SeqView> seqs = make_seqs(bases, offsets, n_seqs, L, true);
+        std::vector<uint32_t> fs, fp;
+        std::vector<int8_t> fo;
+        for (size_t si = 0; si < seqs.size(); si++) {
+            const SeqView& seq = seqs[si];
+            Scanner sc(&seq, L);
+            /* add_match, :97-108: trust the hash only for short N-free input */
+            auto add_match = [&](int ori) {
+                bool ok = !has_n && sc.ns == 0 && L <= MAX_ANCHOR;
+                if (!ok) {  /* seq_->substr(begin, anchor_, ori) == p_ */
+                    ok = true;
+                    for (int j = 0; j < L && ok; j++) {
+                        char c = ori == 1 ? seq.data[sc.pos + j]
+                                          : complement_char(seq.data[sc.pos + L - 1 - j]);
+                        ok = c == p[j];
+                    }
+                }
+                if (ok) {
+                    fs.push_back(seq.index);
+                    fp.push_back(uint32_t(sc.pos));
+                    fo.push_back(int8_t(ori));
+                }
+            };
+            auto test = [&]() {
+                if (sc.dir == ph) add_match(1);
+                if (sc.rev == ph) add_match(-1);
+            };
+            sc.init_state();
+            test();
+            const long n = long(seq.size) - L;
+            for (long i = 0; i < n; i++) {
+                sc.next_hash();
+                test();
+                if (int64_t(fs.size()) > max_matches) break;
+            }
+        }
+        uint64_t keep = std::min<uint64_t>(fs.size(), uint64_t(max_matches));
+        *n_out = keep;
+        *seq_out = (uint32_t*)malloc(4 * (keep + 1));
+        *pos_out = (uint32_t*)malloc(4 * (keep + 1));
+        *ori_out = (int8_t*)malloc(keep + 1);
+        memcpy(*seq_out, fs.data(), 4 * keep);
+        memcpy(*pos_out, fp.data(), 4 * keep);
+        memcpy(*ori_out, fo.data(), keep);
+        return 0;
+    } catch (std::exception&) {
+        return 2;
+    }
+}
+
+extern "C" void oracle_free(void* p) {
+    free(p);
+}

@@ -257,3 +257,27 @@ def blockset_hash(names, blocks):
     return lib().oracle_blockset_hash(
         arr, len(blocks), offs.ctypes.data, seq.ctypes.data, mn.ctypes.data,
         mx.ctypes.data, ori.ctypes.data)
+
+
+def fragment_find(seqs, pattern, max_matches=100):
+    """FragmentFinder restatement: list of (seq, min_pos, ori), in the order of
+    a one-worker run of the reference, cut to max_matches."""
+    bases, offsets = concat(seqs)
+    p = to_atgcn(pattern).encode()
+    n = C.c_uint64()
+    ps, pp, po = C.POINTER(C.c_uint32)(), C.POINTER(C.c_uint32)(), C.POINTER(C.c_int8)()
+    L = lib()
+    L.oracle_fragment_find.argtypes = [
+        C.c_char_p, C.c_uint32, C.c_int64, C.c_void_p, C.c_void_p, C.c_uint32,
+        C.POINTER(C.c_uint64), C.POINTER(C.POINTER(C.c_uint32)),
+        C.POINTER(C.POINTER(C.c_uint32)), C.POINTER(C.POINTER(C.c_int8))]
+    L.oracle_free.argtypes = [C.c_void_p]
+    rc = L.oracle_fragment_find(p, len(p), int(max_matches), bases.ctypes.data,
+                                offsets.ctypes.data, len(offsets) - 1, C.byref(n),
+                                C.byref(ps), C.byref(pp), C.byref(po))
+    if rc != 0:
+        raise ValueError("oracle_fragment_find failed: %d" % rc)
+    out = [(int(ps[i]), int(pp[i]), int(po[i])) for i in range(n.value)]
+    for q in (ps, pp, po):
+        L.oracle_free(q)
+    return out
