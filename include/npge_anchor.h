@@ -123,6 +123,14 @@ void npge_anchor_result_free(npge_anchor_result* out);
 int npge_anchor_upload(npge_anchor_ctx* ctx, int32_t anchor_size,
                        const uint8_t* bases, const uint64_t* seq_offsets,
                        uint32_t n_seqs);
+/* upload with Sequence::to_atgcn done on the device (Sequence.cpp:151-179): `raw`
+ * is sequence text as it sits in a FASTA file -- any case, line breaks, gaps,
+ * IUPAC ambiguity codes (-> N); every other byte is dropped.  clean_sizes
+ * (optional, [n_seqs]) receives the size of every sequence after cleaning;
+ * positions in the results refer to the cleaned sequences, as in the reference. */
+int npge_anchor_upload_raw(npge_anchor_ctx* ctx, int32_t anchor_size,
+                           const uint8_t* raw, const uint64_t* raw_offsets,
+                           uint32_t n_seqs, uint64_t* clean_sizes);
 int npge_anchor_find_device(npge_anchor_ctx* ctx, const npge_anchor_params* p,
                             const uint64_t* used_sorted, uint64_t n_used,
                             npge_anchor_stats* stats);

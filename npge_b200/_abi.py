@@ -17,6 +17,7 @@ EXPORTS = [
     "npge_anchor_dist_peer_close", "npge_anchor_dist_count_a",
     "npge_anchor_dist_scatter_peer", "npge_anchor_dist_copy_peer",
     "npge_fragment_find", "npge_fragment_find_device", "npge_fragment_result_free",
+    "npge_anchor_upload_raw",
 ]
 IPC_BYTES = 128
 
@@ -135,6 +136,9 @@ def load():
     L.npge_anchor_dist_emit.restype = C.c_int
     L.npge_anchor_dist_emit.argtypes = [ctx, C.POINTER(Params), C.c_uint64,
                                         C.POINTER(Stats)]
+    L.npge_anchor_upload_raw.restype = C.c_int
+    L.npge_anchor_upload_raw.argtypes = [ctx, C.c_int32, C.c_void_p, C.c_void_p,
+                                         C.c_uint32, C.c_void_p]
     L.npge_fragment_find.restype = C.c_int
     L.npge_fragment_find.argtypes = [ctx, C.c_char_p, C.c_uint32, C.c_int64, C.c_void_p,
                                      C.c_void_p, C.c_uint32, C.POINTER(FragmentResult)]

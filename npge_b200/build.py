@@ -7,7 +7,8 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 SOURCES = ["api.cu", "scan_kernels.cu", "sort_kernels.cu", "group_kernels.cu",
-           "msd_kernels.cu", "bucket_kernels.cu", "fragment_kernels.cu"]
+           "msd_kernels.cu", "bucket_kernels.cu", "fragment_kernels.cu",
+           "ingest_kernels.cu"]
 HEADERS = ["common.cuh", "kernels.h", "rank.cuh", os.path.join("..", "..", "include",
                                                      "npge_anchor.h")]
 LIB = os.path.join(HERE, "libnpge_anchor.so")

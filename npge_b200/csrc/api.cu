@@ -1,6 +1,7 @@
 // api.cu -- the C ABI (include/npge_anchor.h): host orchestration of the CUDA
 // path.  No CPU fallback: every compute entry point needs a CUDA device.
 #include <algorithm>
+#include <functional>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -230,7 +231,8 @@ extern "C" void npge_anchor_destroy(npge_anchor_ctx* ctx) {
                            &ctx->bstatus, &ctx->units, &ctx->rec[0], &ctx->rec[1], &ctx->rhi[0],
                            &ctx->rhi[1], &ctx->seq_lut, &ctx->g_seq_start, &ctx->g_seq_caller,
                            &ctx->g_seq_lut, &ctx->pos_delta, &ctx->recv_rec, &ctx->recv_hi,
-                           &ctx->peer_tab, &ctx->frag_pat, &ctx->frag_tiles, &ctx->frag_out};
+                           &ctx->peer_tab, &ctx->frag_pat, &ctx->frag_tiles, &ctx->frag_out,
+                           &ctx->raw, &ctx->ingest};
     for (void* q : ctx->peer_opened) cudaIpcCloseMemHandle(q);
     for (DeviceBuffer* b : all) release(*b);
     for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
@@ -239,27 +241,21 @@ extern "C" void npge_anchor_destroy(npge_anchor_ctx* ctx) {
     delete ctx;
 }
 
-// ---- upload: host ATGCN -> packed device genome -------------------------------
-extern "C" int npge_anchor_upload(npge_anchor_ctx* ctx, int32_t anchor_size,
-                                  const uint8_t* bases,
-                                  const uint64_t* seq_offsets, uint32_t n_seqs) {
-    if (!ctx) return fail(NPGE_ANCHOR_ERR_PARAMS, "ctx is NULL");
-    npge_anchor_params probe = {anchor_size, 0, 0};
-    NPGE_TRY(check_params(&probe));
-    if (n_seqs && (!seq_offsets || (!bases && seq_offsets[n_seqs] > 0))) {
-        return fail(NPGE_ANCHOR_ERR_PARAMS, "bases / seq_offsets is NULL");
-    }
-    NPGE_CUDA(cudaSetDevice(ctx->device));
+// ---- upload: ATGCN text -> packed device genome ---------------------------------
+namespace {
+
+// Lays the sequences out in scan order (sizes[s] = clean size of caller sequence
+// s), lets `fill` write the ASCII bytes of every kept sequence at its start
+// (ctx->seqs: caller_index, size, start), then packs and builds the tables.
+int upload_common(npge_anchor_ctx* ctx, int32_t anchor_size, const uint64_t* sizes,
+                  uint32_t n_seqs, const std::function<int(cudaStream_t)>& fill) {
     ctx->uploaded = false;
     ctx->have_result = false;
     // SeqBase::make_seqs (SeqI.hpp:45-57): size >= k, by size descending; ties
     // by caller index (the reference's are unspecified)
     ctx->seqs.clear();
     for (uint32_t s = 0; s < n_seqs; s++) {
-        if (seq_offsets[s + 1] < seq_offsets[s]) {
-            return fail(NPGE_ANCHOR_ERR_PARAMS, "seq_offsets must be non-decreasing");
-        }
-        uint64_t size = seq_offsets[s + 1] - seq_offsets[s];
+        uint64_t size = sizes[s];
         if (size >= uint64_t(anchor_size)) ctx->seqs.push_back({s, size, 0});
     }
     std::stable_sort(ctx->seqs.begin(), ctx->seqs.end(),
@@ -293,11 +289,7 @@ extern "C" int npge_anchor_upload(npge_anchor_ctx* ctx, int32_t anchor_size,
         NPGE_CUDA(cudaMemsetAsync(ctx->ascii.ptr, 'N', np + slack, st));
         NPGE_CUDA(cudaMemsetAsync(ptr<uint8_t>(ctx->packed) + np / 4, 0, slack, st));
         NPGE_CUDA(cudaMemsetAsync(ptr<uint8_t>(ctx->nmask) + np / 8, 0xff, slack, st));
-        for (const SeqEntry& e : ctx->seqs) {
-            NPGE_CUDA(cudaMemcpyAsync(ptr<uint8_t>(ctx->ascii) + e.start,
-                                      bases + seq_offsets[e.caller_index], e.size,
-                                      cudaMemcpyHostToDevice, st));
-        }
+        NPGE_TRY(fill(st));
         std::vector<uint64_t> starts(ctx->seqs.size() + 1);
         std::vector<uint32_t> callers(ctx->seqs.size() + 1, 0);
         for (size_t i = 0; i < ctx->seqs.size(); i++) {
@@ -344,6 +336,98 @@ extern "C" int npge_anchor_upload(npge_anchor_ctx* ctx, int32_t anchor_size,
     ctx->g_positions = ctx->n_positions;
     ctx->g_padded = ctx->n_padded;
     return NPGE_ANCHOR_OK;
+}
+
+}  // namespace
+
+extern "C" int npge_anchor_upload(npge_anchor_ctx* ctx, int32_t anchor_size,
+                                  const uint8_t* bases,
+                                  const uint64_t* seq_offsets, uint32_t n_seqs) {
+    if (!ctx) return fail(NPGE_ANCHOR_ERR_PARAMS, "ctx is NULL");
+    npge_anchor_params probe = {anchor_size, 0, 0};
+    NPGE_TRY(check_params(&probe));
+    if (n_seqs && (!seq_offsets || (!bases && seq_offsets[n_seqs] > 0))) {
+        return fail(NPGE_ANCHOR_ERR_PARAMS, "bases / seq_offsets is NULL");
+    }
+    std::vector<uint64_t> sizes(n_seqs);
+    for (uint32_t s = 0; s < n_seqs; s++) {
+        if (seq_offsets[s + 1] < seq_offsets[s]) {
+            return fail(NPGE_ANCHOR_ERR_PARAMS, "seq_offsets must be non-decreasing");
+        }
+        sizes[s] = seq_offsets[s + 1] - seq_offsets[s];
+    }
+    NPGE_CUDA(cudaSetDevice(ctx->device));
+    return upload_common(ctx, anchor_size, sizes.data(), n_seqs, [&](cudaStream_t st) -> int {
+        for (const SeqEntry& e : ctx->seqs) {
+            NPGE_CUDA(cudaMemcpyAsync(ptr<uint8_t>(ctx->ascii) + e.start,
+                                      bases + seq_offsets[e.caller_index], e.size,
+                                      cudaMemcpyHostToDevice, st));
+        }
+        return NPGE_ANCHOR_OK;
+    });
+}
+
+// ---- upload_raw: to_atgcn on the device ---------------------------
+extern "C" int npge_anchor_upload_raw(npge_anchor_ctx* ctx, int32_t anchor_size,
+                                      const uint8_t* raw, const uint64_t* raw_offsets,
+                                      uint32_t n_seqs, uint64_t* clean_sizes) {
+    if (!ctx) return fail(NPGE_ANCHOR_ERR_PARAMS, "ctx is NULL");
+    npge_anchor_params probe = {anchor_size, 0, 0};
+    NPGE_TRY(check_params(&probe));
+    if (n_seqs && (!raw_offsets || (!raw && raw_offsets[n_seqs] > 0))) {
+        return fail(NPGE_ANCHOR_ERR_PARAMS, "raw / raw_offsets is NULL");
+    }
+    for (uint32_t s = 0; s < n_seqs; s++) {
+        if (raw_offsets[s + 1] < raw_offsets[s]) {
+            return fail(NPGE_ANCHOR_ERR_PARAMS, "raw_offsets must be non-decreasing");
+        }
+    }
+    NPGE_CUDA(cudaSetDevice(ctx->device));
+    ctx->uploaded = false;
+    const uint64_t n_raw = n_seqs ? raw_offsets[n_seqs] - raw_offsets[0] : 0;
+    const uint32_t tiles = ingest_tiles(n_raw);
+    cudaStream_t st = ctx->stream;
+    NPGE_TRY(ensure(ctx->raw, n_raw + 16));
+    NPGE_TRY(ensure(ctx->ingest, size_t(tiles + 1) * 12 + (size_t(n_seqs) + 1) * 24 + 64));
+    uint8_t* w = ptr<uint8_t>(ctx->ingest);
+    IngestArgs a = {};
+    a.raw = ptr<uint8_t>(ctx->raw);
+    a.n_raw = n_raw;
+    a.n_seqs = n_seqs;
+    a.tile_offset = reinterpret_cast<uint64_t*>(w);
+    a.seq_rank = a.tile_offset + tiles + 1;
+    uint64_t* d_offsets = a.seq_rank + n_seqs + 1;
+    uint64_t* d_base = d_offsets + n_seqs + 1;
+    a.raw_offsets = d_offsets;
+    a.dst_base = d_base;
+    a.tile_count = reinterpret_cast<uint32_t*>(d_base + n_seqs + 1);
+    std::vector<uint64_t> rel(n_seqs + 1, 0);  // offsets relative to the first byte
+    for (uint32_t s = 0; s <= n_seqs && n_seqs; s++) rel[s] = raw_offsets[s] - raw_offsets[0];
+    if (n_raw) {
+        NPGE_CUDA(cudaMemcpyAsync(ctx->raw.ptr, raw + raw_offsets[0], n_raw,
+                                  cudaMemcpyHostToDevice, st));
+    }
+    NPGE_CUDA(cudaMemcpyAsync(d_offsets, rel.data(), rel.size() * 8, cudaMemcpyHostToDevice, st));
+    uint32_t launches = 0;
+    launch_ingest(a, 0, st, &launches);
+    NPGE_CUDA(cudaGetLastError());
+    std::vector<uint64_t> rank(n_seqs + 1, 0), sizes(n_seqs, 0);
+    NPGE_CUDA(cudaMemcpyAsync(rank.data(), a.seq_rank, rank.size() * 8, cudaMemcpyDeviceToHost, st));
+    NPGE_CUDA(cudaStreamSynchronize(st));
+    for (uint32_t s = 0; s < n_seqs; s++) sizes[s] = rank[s + 1] - rank[s];
+    if (clean_sizes) std::copy(sizes.begin(), sizes.end(), clean_sizes);
+    return upload_common(ctx, anchor_size, sizes.data(), n_seqs, [&](cudaStream_t s2) -> int {
+        std::vector<uint64_t> base(n_seqs + 1, ~0ull);  // dropped sequences: no place
+        for (const SeqEntry& e : ctx->seqs) base[e.caller_index] = e.start;
+        IngestArgs b = a;
+        b.ascii = ptr<uint8_t>(ctx->ascii);
+        NPGE_CUDA(cudaMemcpyAsync(d_base, base.data(), base.size() * 8,
+                                  cudaMemcpyHostToDevice, s2));
+        launch_ingest(b, 1, s2, &launches);
+        NPGE_CUDA(cudaGetLastError());
+        NPGE_CUDA(cudaStreamSynchronize(s2));  // `base` is a local
+        return NPGE_ANCHOR_OK;
+    });
 }
 
 // ---- find_device, MSD partition + shared-memory bucket sort ---------------------------

@@ -171,6 +171,7 @@ struct npge_anchor_ctx {
     uint32_t dist_rank = 0;                  // this rank's index in peer_rec
     uint64_t peer_capacity = 0;              // records every receive buffer can take
     npge_b200::DeviceBuffer frag_pat, frag_tiles, frag_out;  // FragmentFinder scratch
+    npge_b200::DeviceBuffer raw, ingest;                     // upload_raw scratch
     npge_b200::DeviceBuffer peer_tab;        // per-bucket destination addresses
     bool a_counted = false;
     std::vector<uint32_t> a_start_h;         // host copy of this rank's a_start

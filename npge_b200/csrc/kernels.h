@@ -157,6 +157,21 @@ void launch_bucket_stage(const BucketArgs& a, int stage, uint64_t max_records,
 void launch_bucket(const BucketArgs& a, bool similar, uint64_t max_records,
                    cudaStream_t s, cudaEvent_t* ev, uint32_t* launches);
 
+// ---- ingest (ingest_kernels.cu): raw text -> to_atgcn -> padded ASCII layout -----------
+struct IngestArgs {
+    const uint8_t* raw;
+    uint64_t n_raw;
+    uint32_t n_seqs;
+    const uint64_t* raw_offsets;  // [n_seqs + 1], relative to raw
+    uint32_t* tile_count;
+    uint64_t* tile_offset;        // [tiles + 1] kept bytes before every tile
+    uint64_t* seq_rank;           // [n_seqs + 1] kept bytes before every sequence
+    const uint64_t* dst_base;     // [n_seqs] start in `ascii`, ~0 = dropped
+    uint8_t* ascii;
+};
+uint32_t ingest_tiles(uint64_t n_raw);
+void launch_ingest(const IngestArgs& a, int stage, cudaStream_t s, uint32_t* launches);
+
 // ---- FragmentFinder (fragment_kernels.cu) --------------------------------------------
 struct FragmentArgs {
     const uint32_t* packed;

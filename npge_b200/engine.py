@@ -149,6 +149,17 @@ class AnchorEngine:
             self._ctx, k, bases.ctypes.data, offsets.ctypes.data,
             len(offsets) - 1))
 
+    def upload_raw(self, raw_seqs, k):
+        """upload() of raw sequence text (FASTA body lines, any case, gaps, IUPAC
+        codes): Sequence::to_atgcn runs on the device.  Returns the sizes of the
+        cleaned sequences."""
+        raw, offsets = raw_seqs if isinstance(raw_seqs, tuple) else concat(raw_seqs)
+        sizes = np.zeros(len(offsets) - 1, dtype=np.uint64)
+        self._check(self._lib.npge_anchor_upload_raw(
+            self._ctx, k, raw.ctypes.data, offsets.ctypes.data, len(offsets) - 1,
+            sizes.ctypes.data if len(sizes) else None))
+        return sizes
+
     def find_device(self, k, similar=True, max_frags=100000, used=None):
         u, up = self._used(used)
         p = _abi.Params(k, int(bool(similar)), int(max_frags))

@@ -154,5 +154,84 @@ const char* AnchorFinder::name_impl() const {
     return "Find anchors";  // AnchorFinder.cpp:408-410
 }
 
+// ---- FragmentFinder (src/algo/FragmentFinder.cpp) ---------------------------------
+struct FragmentFinder::Impl {
+    npge_anchor_ctx* ctx = nullptr;
+    int device = 0;
+};
+
+FragmentFinder::FragmentFinder() : impl_(new Impl) {
+    add_opt("pattern", "Sequence searched for", std::string(""));
+#ifdef NPGE_B200_REAL_HEADERS
+    add_opt_check(boost::bind(pattern_length, this, _1));  // as FragmentFinder.cpp:18-35
+    add_gopt("max-matches", "Maximum number of matches", "MAX_MATCHES");
+    add_opt_rule("max-matches >= 1");
+#else
+    add_opt_rule([this](std::string& m) {  // pattern_length, FragmentFinder.cpp:18-28
+        std::string p = opt_value("pattern").as<std::string>();
+        Sequence::to_atgcn(p);
+        m = "'pattern' should not be empty";
+        return !p.empty();
+    });
+    add_gopt("max-matches", "Maximum number of matches", "MAX_MATCHES", 1000);
+    add_opt_rule([this](std::string& m) {
+        m = "max-matches >= 1";
+        return opt_value("max-matches").as<int>() >= 1;
+    });
+#endif
+    declare_bs("target", "search in sequences, add fragments");
+}
+
+FragmentFinder::~FragmentFinder() {
+    if (impl_->ctx) npge_anchor_destroy(impl_->ctx);
+    delete impl_;
+}
+
+void FragmentFinder::set_device(int device) {
+    if (impl_->ctx) {
+        npge_anchor_destroy(impl_->ctx);
+        impl_->ctx = nullptr;
+    }
+    impl_->device = device;
+}
+
+void FragmentFinder::run_impl() const {
+    Impl& st = *impl_;
+    std::string pattern = opt_value("pattern").as<std::string>();
+    Sequence::to_atgcn(pattern);  // FinderTG, :52-53
+    const int max_matches = opt_value("max-matches").as<int>();
+    BlockSet& bs = *block_set();
+    std::vector<SequencePtr> seqs = bs.seqs();
+    std::vector<uint64_t> offsets(seqs.size() + 1, 0);
+    for (size_t i = 0; i < seqs.size(); i++) offsets[i + 1] = offsets[i] + seqs[i]->size();
+    std::string bases;
+    bases.reserve(offsets.back());
+    for (size_t i = 0; i < seqs.size(); i++) bases += seqs[i]->contents();
+    if (!st.ctx) check(npge_anchor_create(&st.ctx, st.device), "no CUDA device");
+    npge_fragment_result r;
+    check(npge_fragment_find(st.ctx, reinterpret_cast<const uint8_t*>(pattern.data()),
+                             uint32_t(pattern.size()), max_matches,
+                             reinterpret_cast<const uint8_t*>(bases.data()), offsets.data(),
+                             uint32_t(seqs.size()), &r),
+          "npge_fragment_find");
+    try {
+        for (uint64_t f = 0; f < r.n_matches; f++) {  // :155-164: one block per match
+            Block* block = new Block;
+            const size_t min_pos = r.frag_min_pos[f];
+            block->insert(new Fragment(seqs[r.frag_seq[f]].get(), min_pos,
+                                       min_pos + pattern.size() - 1, r.frag_ori[f]));
+            bs.insert(block);
+        }
+    } catch (...) {
+        npge_fragment_result_free(&r);
+        throw;
+    }
+    npge_fragment_result_free(&r);
+}
+
+const char* FragmentFinder::name_impl() const {
+    return "Locate fragment by its sequence";  // FragmentFinder.cpp:168-170
+}
+
 }  // namespace gpu
 }  // namespace npge

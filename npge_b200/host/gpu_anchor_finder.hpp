@@ -30,11 +30,30 @@ private:
     Impl* impl_;  // the reference (AnchorFinder.hpp:48-50)
 };
 
+// Drop-in for the reference's FragmentFinder (src/algo/FragmentFinder.hpp:
+// "Locate fragment by its sequence"): options `pattern`, `max-matches`; adds one
+// single-fragment block per occurrence of the pattern, either strand.
+class FragmentFinder : public Processor {
+public:
+    FragmentFinder();
+    ~FragmentFinder();
+    void set_device(int device);
+
+protected:
+    void run_impl() const;
+    const char* name_impl() const;
+
+private:
+    struct Impl;
+    Impl* impl_;
+};
+
 // Meta registration: replaces the built-in factory (Meta.hpp:83-87), so every
 // pipeline, Lua script and the CLI that asks for "AnchorFinder" gets this one.
 template <typename MetaT>
 inline void register_processors(MetaT* meta) {
     meta->template set_processor<AnchorFinder>("AnchorFinder", true);
+    meta->template set_processor<FragmentFinder>("FragmentFinder", true);
 }
 
 }  // namespace gpu

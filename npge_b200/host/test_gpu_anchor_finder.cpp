@@ -203,12 +203,71 @@ static void truncation() {
     CHECK(frags <= 4 && bs->size() >= 1);
 }
 
+// ---- FragmentFinder ---------------------------------------------------------------
+static void fragment_finder_options() {
+    gpu::FragmentFinder ff;
+    CHECK(ff.opt_value("max-matches").as<int>() == 1000);
+    CHECK(std::string(ff.name()) == "Locate fragment by its sequence");
+    ff.set_block_set(blockset_of({"ATGC"}));
+    bool thrown = false;
+    try {
+        ff.run();  // empty pattern
+    } catch (const Exception& e) {
+        thrown = std::strstr(e.what(), "pattern") != nullptr;
+    }
+    CHECK(thrown);
+    ff.set_opt_value("pattern", std::string("--"));  // nothing left after to_atgcn
+    thrown = false;
+    try {
+        ff.run();
+    } catch (const Exception&) {
+        thrown = true;
+    }
+    CHECK(thrown);
+    ff.set_opt_value("pattern", std::string("AT"));
+    ff.set_opt_value("max-matches", 0);
+    thrown = false;
+    try {
+        ff.run();
+    } catch (const Exception&) {
+        thrown = true;
+    }
+    CHECK(thrown);
+    Meta meta;
+    gpu::register_processors(&meta);
+    CHECK(meta.has("FragmentFinder") && meta.get("FragmentFinder")->has_opt("pattern"));
+}
+
+static void fragment_finder_run() {
+    BlockSetPtr bs = blockset_of({"tgGTCCGagCGGACggcc", "aaGTCCGnn"});
+    gpu::FragmentFinder ff;
+    ff.set_block_set(bs);
+    ff.set_opt_value("pattern", std::string("gtccg"));
+    ff.run();
+    CHECK(bs->size() == 3);
+    int forward = 0, reverse = 0;
+    for (BlockSet::const_iterator b = bs->begin(); b != bs->end(); ++b) {
+        CHECK((*b)->size() == 1);
+        Fragment* f = (*b)->front();
+        CHECK(f->str() == "GTCCG" && f->length() == 5);
+        (f->ori() == 1 ? forward : reverse)++;
+    }
+    CHECK(forward == 2 && reverse == 1);
+    BlockSetPtr cut = blockset_of({"ATATATATAT"});
+    ff.set_block_set(cut);
+    ff.set_opt_value("pattern", std::string("AT"));
+    ff.set_opt_value("max-matches", 3);
+    ff.run();
+    CHECK(cut->size() == 3);
+}
+
 int main(int argc, char** argv) {
     const bool no_gpu = argc > 1 && std::strcmp(argv[1], "--no-gpu") == 0;
     options_and_rules();
     workers_zero_skips_the_run();
     meta_registration();
     sequence_normalisation();
+    fragment_finder_options();
     if (!no_gpu) {
         try {
             AnchorFinder_main();
@@ -220,6 +279,7 @@ int main(int argc, char** argv) {
             AnchorFinder_several_sequences(2);
             used_hashes_across_runs();
             truncation();
+            fragment_finder_run();
         } catch (const std::exception& e) {
             failures++;
             std::printf("FAIL exception: %s\n", e.what());
