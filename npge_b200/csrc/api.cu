@@ -953,6 +953,8 @@ extern "C" int npge_anchor_fetch(npge_anchor_ctx* ctx, npge_anchor_result* out) 
         delete r;
         return fail(NPGE_ANCHOR_ERR_MEMORY, "out of host memory for the result");
     }
+    const uint64_t* used_ptr = nullptr;
+    uint64_t used_n = 0;
     auto body = [&]() -> int {
         cudaStream_t st = ctx->stream;
         if (nf) {
@@ -1011,11 +1013,18 @@ extern "C" int npge_anchor_fetch(npge_anchor_ctx* ctx, npge_anchor_result* out) 
         // first (AnchorFinder.cpp:366-387)
         // (several GPUs: every hash of this rank's range; the caller drops the
         // job's first one)
-        for (size_t b = ctx->dist ? 0 : 1; b < r->block_hash.size(); b++) {
-            r->new_used.push_back(r->block_hash[b]);
-        }
+        const size_t b0 = ctx->dist ? 0 : 1;
         if (lone_tail && (ctx->dist || !r->block_hash.empty())) {
+            r->new_used.assign(r->block_hash.begin() + std::min(b0, r->block_hash.size()),
+                               r->block_hash.end());
             r->new_used.push_back(lone_hash);
+            used_ptr = r->new_used.data();
+            used_n = r->new_used.size();
+        } else if (r->block_hash.size() > b0) {
+            // the list IS the tail of block_hash: no copy (millions of blocks in
+            // parity mode)
+            used_ptr = r->block_hash.data() + b0;
+            used_n = r->block_hash.size() - b0;
         }
         return NPGE_ANCHOR_OK;
     };
@@ -1031,8 +1040,8 @@ extern "C" int npge_anchor_fetch(npge_anchor_ctx* ctx, npge_anchor_result* out) 
     out->frag_seq = r->frag_seq.data();
     out->frag_min_pos = r->frag_min_pos.data();
     out->frag_ori = r->frag_ori.data();
-    out->n_new_used = r->new_used.size();
-    out->new_used = r->new_used.data();
+    out->n_new_used = used_n;
+    out->new_used = used_ptr;
     out->owner_ = r;
     return NPGE_ANCHOR_OK;
 }
