@@ -210,7 +210,11 @@ int npge_anchor_dist_scatter_peer(npge_anchor_ctx* ctx, const npge_anchor_params
                                   uint32_t n_bins);
 /* The bulk variant of the peer exchange: after dist_pass_a (local pass A) the
  * contiguous slice of every destination is copied into its receive buffer by a
- * copy kernel (same dest_rank / dest_off tables as dist_scatter_peer). */
+ * copy kernel (same dest_rank / dest_off tables as dist_scatter_peer).
+ * dist_count_a + dist_scatter_local is dist_pass_a in two steps; the second only
+ * enqueues pass A, so that the all-gather of the histograms and the host tables
+ * overlap it. */
+int npge_anchor_dist_scatter_local(npge_anchor_ctx* ctx, const npge_anchor_params* p);
 int npge_anchor_dist_copy_peer(npge_anchor_ctx* ctx, const npge_anchor_params* p,
                                const uint32_t* dest_rank, const int64_t* dest_off,
                                uint32_t n_bins);

@@ -17,7 +17,7 @@ EXPORTS = [
     "npge_anchor_dist_peer_close", "npge_anchor_dist_count_a",
     "npge_anchor_dist_scatter_peer", "npge_anchor_dist_copy_peer",
     "npge_fragment_find", "npge_fragment_find_device", "npge_fragment_result_free",
-    "npge_anchor_upload_raw",
+    "npge_anchor_upload_raw", "npge_anchor_dist_scatter_local",
 ]
 IPC_BYTES = 128
 
@@ -125,6 +125,8 @@ def load():
     L.npge_anchor_dist_scatter_peer.restype = C.c_int
     L.npge_anchor_dist_scatter_peer.argtypes = [ctx, C.POINTER(Params), C.c_void_p,
                                                 C.c_void_p, C.c_uint32]
+    L.npge_anchor_dist_scatter_local.restype = C.c_int
+    L.npge_anchor_dist_scatter_local.argtypes = [ctx, C.POINTER(Params)]
     L.npge_anchor_dist_copy_peer.restype = C.c_int
     L.npge_anchor_dist_copy_peer.argtypes = L.npge_anchor_dist_scatter_peer.argtypes
     L.npge_anchor_dist_buffers.restype = C.c_int

@@ -1345,6 +1345,37 @@ extern "C" int npge_anchor_dist_scatter_peer(npge_anchor_ctx* ctx,
     return NPGE_ANCHOR_OK;
 }
 
+// pass A into this rank's own memory, asynchronously: the caller overlaps the
+// histogram all-gather and its host tables with it; npge_anchor_dist_copy_peer
+// (same stream) follows
+extern "C" int npge_anchor_dist_scatter_local(npge_anchor_ctx* ctx,
+                                              const npge_anchor_params* p) {
+    if (!ctx) return fail(NPGE_ANCHOR_ERR_PARAMS, "ctx is NULL");
+    NPGE_TRY(check_params(p));
+    if (!ctx->dist || !ctx->a_counted) {
+        return fail(NPGE_ANCHOR_ERR_STATE, "npge_anchor_dist_count_a has not run");
+    }
+    NPGE_CUDA(cudaSetDevice(ctx->device));
+    const MsdPlan plan = ctx->plan;
+    const uint32_t bins_a = 1u << plan.capa;
+    const uint64_t np = ctx->n_padded, max_records = ctx->n_positions;
+    NPGE_TRY(ensure(ctx->rec[0], (max_records + 16) * 8));
+    if (plan.wide) NPGE_TRY(ensure(ctx->rhi[0], (max_records + 16) * 4));
+    cudaStream_t st = ctx->stream;
+    NPGE_CUDA(cudaEventRecord(ctx->ev_pass[0], st));
+    if (np) {
+        MsdBuffers mb = dist_msd_buffers(ctx, plan, bins_a);
+        launch_msd_pass_a(plan, ptr<uint32_t>(ctx->packed), ptr<uint32_t>(ctx->nmask), np,
+                          mb, dist_pos_map(ctx), ptr<uint32_t>(ctx->counters), st, nullptr,
+                          &ctx->dist_launches, 2);
+        NPGE_CUDA(cudaGetLastError());
+    }
+    NPGE_CUDA(cudaEventRecord(ctx->ev_pass[1], st));
+    ctx->a_scattered = true;
+    ctx->a_scatter_async = true;
+    return NPGE_ANCHOR_OK;
+}
+
 extern "C" int npge_anchor_dist_copy_peer(npge_anchor_ctx* ctx, const npge_anchor_params* p,
                                           const uint32_t* dest_rank, const int64_t* dest_off,
                                           uint32_t n_bins) {
@@ -1396,6 +1427,10 @@ extern "C" int npge_anchor_dist_copy_peer(npge_anchor_ctx* ctx, const npge_ancho
     NPGE_CUDA(cudaEventRecord(ctx->ev[1], st));
     NPGE_CUDA(cudaStreamSynchronize(st));
     cudaEventElapsedTime(&ctx->dist_ms[7], ctx->ev[0], ctx->ev[1]);
+    if (ctx->a_scatter_async) {
+        cudaEventElapsedTime(&ctx->dist_ms[1], ctx->ev_pass[0], ctx->ev_pass[1]);
+        ctx->a_scatter_async = false;
+    }
     ctx->a_counted = false;
     return NPGE_ANCHOR_OK;
 }

@@ -175,6 +175,7 @@ struct npge_anchor_ctx {
     npge_b200::DeviceBuffer peer_tab;        // per-bucket destination addresses
     bool a_counted = false;
     std::vector<uint32_t> a_start_h;         // host copy of this rank's a_start
+    bool a_scatter_async = false;            // pass A still in flight on the stream
     bool a_scattered = false;                // rec[0] holds the local pass A output
     uint64_t dist_n_used = 0;
     float dist_ms[8] = {};

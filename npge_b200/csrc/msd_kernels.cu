@@ -53,6 +53,7 @@ MsdPlan make_msd_plan(int k, uint64_t n_positions) {
     p.capa = wa <= 8 ? 8 : 10;
     p.capb = wb <= 8 ? 8 : 10;
     p.smem_passes = (p.rem + 7) / 8;
+    if (const char* e = getenv("NPGE_EXP_SMEM_PASSES")) p.smem_passes = atoi(e);  // timing only
     return p;
 }
 

@@ -228,6 +228,9 @@ class CudaStages(AnchorEngine):
         self._check(self._lib.npge_anchor_dist_scatter_peer(
             self._ctx, C.byref(params), dr.ctypes.data, do.ctypes.data, len(dr)))
 
+    def dist_scatter_local(self, params):
+        self._check(self._lib.npge_anchor_dist_scatter_local(self._ctx, C.byref(params)))
+
     def dist_copy_peer(self, params, dest_rank, dest_off):
         dr = np.ascontiguousarray(dest_rank, dtype=np.uint32)
         do = np.ascontiguousarray(dest_off, dtype=np.int64)
@@ -518,8 +521,14 @@ class DistAnchorFinder:
         dev = comm.torch.device("cuda", self.device) if comm.nccl else None
         fused = self.exchange == "peer"
         peer = self.exchange in ("peer", "bulk")
-        hist = st.dist_count_a(params) if fused else st.dist_pass_a(params)
-        lap("count_a" if fused else "pass_a")
+        if peer:
+            hist = st.dist_count_a(params)
+            if not fused:  # bulk: pass A runs while the histograms are gathered
+                st.dist_scatter_local(params)
+            lap("count_a")
+        else:
+            hist = st.dist_pass_a(params)
+            lap("pass_a")
         # (also the step's barrier: no rank scatters into a receive buffer whose
         # owner has not finished its previous step)
         hist_all = comm.gather_array(hist, dev)
