@@ -289,6 +289,17 @@ class _Comm:
         self.rank = dist.get_rank(group)
         self.world = dist.get_world_size(group)
         self.nccl = dist.get_backend(group) == "nccl"
+        if self.nccl and self.world > 1:
+            # the small collectives run while the library's kernels fill the GPU
+            # (pass A overlaps the histogram all-gather): give NCCL a
+            # high-priority stream so that its kernels are scheduled at once
+            try:
+                opts = dist.ProcessGroupNCCL.Options()
+                opts.is_high_priority_stream = True
+                ranks = dist.get_process_group_ranks(group) if group is not None else None
+                self.group = dist.new_group(ranks=ranks, backend="nccl", pg_options=opts)
+            except Exception:  # older torch: keep the given group
+                self.group = group
 
     def gather_objects(self, obj):
         out = [None] * self.world
