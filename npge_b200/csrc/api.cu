@@ -359,9 +359,11 @@ extern "C" int npge_anchor_upload(npge_anchor_ctx* ctx, int32_t anchor_size,
     NPGE_CUDA(cudaSetDevice(ctx->device));
     return upload_common(ctx, anchor_size, sizes.data(), n_seqs, [&](cudaStream_t st) -> int {
         for (const SeqEntry& e : ctx->seqs) {
+            // (cudaMemcpyDefault: `bases` may also be device memory, e.g. the
+            // sequences a multi-GPU job has just exchanged)
             NPGE_CUDA(cudaMemcpyAsync(ptr<uint8_t>(ctx->ascii) + e.start,
                                       bases + seq_offsets[e.caller_index], e.size,
-                                      cudaMemcpyHostToDevice, st));
+                                      cudaMemcpyDefault, st));
         }
         return NPGE_ANCHOR_OK;
     });

@@ -185,12 +185,19 @@ class CudaStages(AnchorEngine):
         self.device = device
 
     def dist_upload(self, k, seqs, local_gstart, global_start, global_caller):
-        bases, offsets = concat(seqs)
+        """seqs: list of sequences, or (bases, offsets) with bases a numpy array
+        or a CUDA uint8 tensor (sequences already on the device)."""
+        if isinstance(seqs, tuple):
+            bases, offsets = seqs
+            offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
+        else:
+            bases, offsets = concat(seqs)
+        base_ptr = bases.data_ptr() if hasattr(bases, "data_ptr") else bases.ctypes.data
         lg = np.ascontiguousarray(local_gstart, dtype=np.uint64)
         gs = np.ascontiguousarray(global_start, dtype=np.uint64)
         gc = np.ascontiguousarray(global_caller, dtype=np.uint32)
         self._check(self._lib.npge_anchor_dist_upload(
-            self._ctx, k, bases.ctypes.data, offsets.ctypes.data, len(offsets) - 1,
+            self._ctx, k, base_ptr, offsets.ctypes.data, len(offsets) - 1,
             lg.ctypes.data, gs.ctypes.data, gc.ctypes.data, len(gc)))
 
     def dist_pass_a(self, params):
@@ -493,66 +500,80 @@ class DistAnchorFinder:
         self._capacity = capacity
 
     # -- upload ------------------------------------------------------------------------
-    def _rebalance(self, seqs, k):
-        """Moves the sequences so that every rank holds a contiguous range of the
-        job-wide scan order.  Returns (local seqs in scan order, their job-wide
-        scan indices, sizes of all sequences in scan order, their job-wide
-        caller indices)."""
-        torch = self.comm.torch
-        sizes_by_rank = self.comm.gather_objects([int(len(s)) for s in seqs])
+    def _plan(self, local_sizes, k):
+        """Job-wide plan from every rank's sequence sizes: (sizes in caller order,
+        first caller index of every rank, scan order, owner rank and source rank
+        of every scan position)."""
+        sizes_by_rank = self.comm.gather_objects([int(x) for x in local_sizes])
         counts = [len(x) for x in sizes_by_rank]
         base = np.concatenate([[0], np.cumsum(counts)]).astype(np.int64)
         sizes = np.asarray([x for r in sizes_by_rank for x in r], dtype=np.int64)
         origin = np.repeat(np.arange(self.world), counts)
         order, cuts = plan_shards(sizes, k, self.world)
         owner = np.repeat(np.arange(self.world), np.diff(cuts))  # per scan index
-        src_of = origin[order]
+        return sizes, base, order, owner, origin[order]
+
+    def _rebalance(self, bases, offsets, k):
+        """Moves the sequences so that every rank holds a contiguous range of the
+        job-wide scan order (one all-to-all of bytes; on the device with NCCL).
+        Returns ((bases, offsets) of the local sequences in scan order, their
+        job-wide scan indices, sizes of all sequences in scan order, their
+        job-wide caller indices)."""
+        torch = self.comm.torch
+        off = np.asarray(offsets, dtype=np.int64)
+        sizes, base, order, owner, src_of = self._plan(np.diff(off), k)
+        me = self.rank
         # what I send to d / receive from s, in scan order
-        send_idx = [[int(i) for i in np.flatnonzero((src_of == self.rank) & (owner == d))]
-                    for d in range(self.world)]
-        recv_idx = [[int(i) for i in np.flatnonzero((src_of == s) & (owner == self.rank))]
-                    for s in range(self.world)]
-        mine = {}
-        moved = any(int(((src_of == s) & (owner != s)).sum()) for s in range(self.world))
-        if moved:
-            def local(i):
-                return np.asarray(seqs[int(order[i] - base[self.rank])], dtype=np.uint8)
-            parts = [local(i) for d in range(self.world) for i in send_idx[d]]
-            send = torch.from_numpy(np.concatenate(parts) if parts
-                                    else np.zeros(0, np.uint8))
-            in_splits = [int(sum(sizes[order[i]] for i in send_idx[d]))
-                         for d in range(self.world)]
-            out_splits = [int(sum(sizes[order[i]] for i in recv_idx[s]))
-                          for s in range(self.world)]
-            recv = torch.empty(sum(out_splits), dtype=torch.uint8)
-            if self.comm.nccl:
-                dev = torch.device("cuda", self.device)
-                send, recv_d = send.to(dev), recv.to(dev)
-                self.comm.all_to_all(recv_d, send, out_splits, in_splits)
-                recv = recv_d.cpu()
-            else:
-                self.comm._a2a_host(recv, send, out_splits, in_splits)
-            buf, off = recv.numpy(), 0
-            for s in range(self.world):
-                for i in recv_idx[s]:
-                    n = int(sizes[order[i]])
-                    mine[i] = buf[off:off + n]
-                    off += n
+        send_idx = [np.flatnonzero((src_of == me) & (owner == d)) for d in range(self.world)]
+        recv_idx = [np.flatnonzero((src_of == s) & (owner == me)) for s in range(self.world)]
+        size_at = sizes[order]
+        in_splits = [int(size_at[ix].sum()) for ix in send_idx]
+        out_splits = [int(size_at[ix].sum()) for ix in recv_idx]
+        on_device = self.comm.nccl and isinstance(self.stages, CudaStages)
+        if on_device:
+            dev = torch.device("cuda", self.device)
+            src = torch.from_numpy(np.ascontiguousarray(bases)).to(dev, non_blocking=True)
         else:
-            for i in recv_idx[self.rank]:
-                mine[i] = np.asarray(seqs[int(order[i] - base[self.rank])], dtype=np.uint8)
-        idx = sorted(mine)
-        return [mine[i] for i in idx], np.asarray(idx, dtype=np.int64), sizes[order], order
+            src = torch.from_numpy(np.ascontiguousarray(bases))
+
+        def pieces(t, spans):
+            spans = [(a, n) for a, n in spans if n]
+            if not spans:
+                return t[:0]
+            if all(spans[i][0] + spans[i][1] == spans[i + 1][0] for i in range(len(spans) - 1)):
+                return t[spans[0][0]:spans[-1][0] + spans[-1][1]]  # already contiguous
+            return torch.cat([t[a:a + n] for a, n in spans])
+
+        local_of = lambda i: int(order[i] - base[me])  # scan index -> my caller index
+        send = pieces(src, [(int(off[local_of(i)]), int(size_at[i]))
+                            for ix in send_idx for i in ix])
+        recv = torch.empty(sum(out_splits), dtype=torch.uint8, device=src.device)
+        if on_device:
+            self.comm.all_to_all(recv, send.contiguous(), out_splits, in_splits)
+        else:
+            self.comm._a2a_host(recv, send.contiguous(), out_splits, in_splits)
+        # received: source by source, each in scan order -> one run in scan order
+        where, at = {}, 0
+        for ix in recv_idx:
+            for i in ix:
+                where[int(i)] = (at, int(size_at[i]))
+                at += int(size_at[i])
+        idx = sorted(where)
+        local = pieces(recv, [where[i] for i in idx])
+        local_off = np.zeros(len(idx) + 1, dtype=np.uint64)
+        local_off[1:] = np.cumsum([where[i][1] for i in idx])
+        if on_device:
+            torch.cuda.current_stream(dev).synchronize()  # the library reads it on its own stream
+        else:
+            local = local.numpy()
+        return (local, local_off), np.asarray(idx, dtype=np.int64), size_at, order
 
     def upload(self, seqs, k):
-        if isinstance(seqs, tuple):
-            bases, offsets = seqs
-            seqs = [bases[int(offsets[i]):int(offsets[i + 1])]
-                    for i in range(len(offsets) - 1)]
-        local, idx, job_sizes, job_caller = self._rebalance(seqs, k)
+        bases, offsets = seqs if isinstance(seqs, tuple) else concat(seqs)
+        local, idx, job_sizes, job_caller = self._rebalance(bases, offsets, k)
         gstart = global_starts(job_sizes)
         self.n_job_bases = int(job_sizes.sum())
-        self.n_local_bases = int(sum(len(s) for s in local))
+        self.n_local_bases = int(local[1][-1])
         self.stages.dist_upload(k, local, gstart[idx], gstart, job_caller)
         self._k = k
         if self._want != "collective":

@@ -47,6 +47,9 @@ class Result:
 class NumpyStages:
     def dist_upload(self, k, seqs, local_gstart, global_start, global_caller):
         self.k = k
+        if isinstance(seqs, tuple):
+            b, o = seqs
+            seqs = [b[int(o[i]):int(o[i + 1])] for i in range(len(o) - 1)]
         self.seqs = [np.asarray(s, dtype=np.uint8) for s in seqs]
         self.lstart = np.asarray(local_gstart, dtype=np.uint64)
         self.gstart = np.asarray(global_start, dtype=np.uint64)
