@@ -47,8 +47,6 @@ __device__ __forceinline__ bool found_bit(const BucketArgs& a, uint32_t g) {
 
 template <bool WIDE>
 struct __align__(16) BucketSmem {
-    uint64_t buf[2][kCap + 2];
-    uint32_t hib[2][WIDE ? kCap + 2 : 4];
     RankSmem<8> rk;
     uint32_t grun[256];       // slow path: running digit bases of the unit
     uint64_t warp_tot[kRW];
@@ -56,6 +54,13 @@ struct __align__(16) BucketSmem {
     uint64_t red[3][kRW];
     uint32_t carry;           // slow path: head of the group entering a chunk
     uint32_t cut;             // set by the thread that wrote the record of rank M-1
+    // the unit: half[0] is enough for the kernels that only read a sorted unit
+    // (count, emit), which are launched with the smaller size (kSingle)
+    struct __align__(16) Half {
+        uint64_t buf[kCap + 2];
+        uint32_t hib[WIDE ? kCap + 2 : 4];
+    } half[2];
+    static constexpr size_t kSingle() { return sizeof(BucketSmem) - sizeof(Half); }
 };
 
 // One sorted chunk of a unit in shared memory: records at K[1 .. cn], halo
@@ -385,7 +390,7 @@ __device__ __forceinline__ uint32_t digit_at(uint64_t r, uint32_t h, int shift) 
     return uint32_t(rem_key(r, h) >> shift) & 255u;
 }
 
-// Loads the unit (n <= kCap) into sm.buf[0][1..n].  Contains a barrier.
+// Loads the unit (n <= kCap) into sm.half[0].buf[1..n].  Contains a barrier.
 template <bool WIDE>
 __device__ __forceinline__ void load_unit(BucketSmem<WIDE>& sm, const BucketArgs& a,
                                           uint32_t s, uint32_t n) {
@@ -393,8 +398,8 @@ __device__ __forceinline__ void load_unit(BucketSmem<WIDE>& sm, const BucketArgs
     for (int i = 0; i < kRI; i++) {
         const uint32_t j = item_index(i);
         if (j < n) {
-            sm.buf[0][1 + j] = a.rec_w[s + j];
-            if (WIDE) sm.hib[0][1 + j] = a.hi_w[s + j];
+            sm.half[0].buf[1 + j] = a.rec_w[s + j];
+            if (WIDE) sm.half[0].hib[1 + j] = a.hi_w[s + j];
         }
     }
     __syncthreads();
@@ -407,13 +412,13 @@ __device__ __forceinline__ void store_unit(BucketSmem<WIDE>& sm, const BucketArg
     for (int i = 0; i < kRI; i++) {
         const uint32_t j = item_index(i);
         if (j < n) {
-            a.rec_w[s + j] = sm.buf[cur][1 + j];
-            if (WIDE) a.hi_w[s + j] = sm.hib[cur][1 + j];
+            a.rec_w[s + j] = sm.half[cur].buf[1 + j];
+            if (WIDE) a.hi_w[s + j] = sm.half[cur].hib[1 + j];
         }
     }
 }
 
-// LSD radix sort of sm.buf[0][1..n] by the low `rem` key bits, byte digits,
+// LSD radix sort of sm.half[0].buf[1..n] by the low `rem` key bits, byte digits,
 // stable.  Returns the buffer holding the result.  Contains barriers.
 template <bool WIDE>
 __device__ __forceinline__ int sort_unit_smem(BucketSmem<WIDE>& sm, const MsdPlan& pl,
@@ -430,8 +435,8 @@ __device__ __forceinline__ int sort_unit_smem(BucketSmem<WIDE>& sm, const MsdPla
         for (int i = 0; i < kRI; i++) {
             const uint32_t j = item_index(i);
             const bool in = j < n;
-            rec[i] = in ? sm.buf[cur][1 + j] : 0ull;
-            hi[i] = (WIDE && in) ? sm.hib[cur][1 + j] : 0u;
+            rec[i] = in ? sm.half[cur].buf[1 + j] : 0ull;
+            hi[i] = (WIDE && in) ? sm.half[cur].hib[1 + j] : 0u;
             digit[i] = in ? digit_at(rec[i], hi[i], 8 * pass) : 256u;
         }
         uint32_t c0, c1;
@@ -439,8 +444,8 @@ __device__ __forceinline__ int sort_unit_smem(BucketSmem<WIDE>& sm, const MsdPla
 #pragma unroll
         for (int i = 0; i < kRI; i++) {
             if (digit[i] < 256u) {
-                sm.buf[cur ^ 1][1 + slot[i]] = rec[i];
-                if (WIDE) sm.hib[cur ^ 1][1 + slot[i]] = hi[i];
+                sm.half[cur ^ 1].buf[1 + slot[i]] = rec[i];
+                if (WIDE) sm.half[cur ^ 1].hib[1 + slot[i]] = hi[i];
             }
         }
         __syncthreads();
@@ -507,8 +512,8 @@ __device__ void sort_unit_global(BucketSmem<WIDE>& sm, const BucketArgs& a, uint
 #pragma unroll
             for (int i = 0; i < kRI; i++) {
                 if (digit[i] < 256u) {
-                    sm.buf[0][slot[i]] = rec[i];
-                    if (WIDE) sm.hib[0][slot[i]] = hi[i];
+                    sm.half[0].buf[slot[i]] = rec[i];
+                    if (WIDE) sm.half[0].hib[slot[i]] = hi[i];
                 }
             }
             __syncthreads();
@@ -516,8 +521,8 @@ __device__ void sort_unit_global(BucketSmem<WIDE>& sm, const BucketArgs& a, uint
             for (int i = 0; i < kRI; i++) {
                 const uint32_t j = tid + i * kRT;
                 if (j < cn) {
-                    const uint64_t r = sm.buf[0][j];
-                    const uint32_t h = WIDE ? sm.hib[0][j] : 0u;
+                    const uint64_t r = sm.half[0].buf[j];
+                    const uint32_t h = WIDE ? sm.half[0].hib[j] : 0u;
                     const uint32_t d = digit_at(r, h, shift);
                     const uint32_t at = s + sm.grun[d] + j - sm.rk.tile_off[d];
                     dst[at] = r;
@@ -540,7 +545,7 @@ __device__ void sort_unit_global(BucketSmem<WIDE>& sm, const BucketArgs& a, uint
     __syncthreads();
 }
 
-// Chunk c0 of a sorted oversized unit -> sm.buf[0] with halos.  Contains barriers.
+// Chunk c0 of a sorted oversized unit -> sm.half[0].buf with halos.  Contains barriers.
 template <bool WIDE>
 __device__ __forceinline__ void load_chunk(BucketSmem<WIDE>& sm, const BucketArgs& a,
                                            uint32_t s, uint32_t n, uint32_t c0,
@@ -553,27 +558,27 @@ __device__ __forceinline__ void load_chunk(BucketSmem<WIDE>& sm, const BucketArg
     for (int i = 0; i < kRI; i++) {
         const uint32_t j = item_index(i);
         if (j < cn) {
-            sm.buf[0][1 + j] = X[s + c0 + j];
-            if (WIDE) sm.hib[0][1 + j] = XH[s + c0 + j];
+            sm.half[0].buf[1 + j] = X[s + c0 + j];
+            if (WIDE) sm.half[0].hib[1 + j] = XH[s + c0 + j];
         }
     }
     if (threadIdx.x == 0) {
         sm.carry = s + c0;
         if (c0 > 0) {
-            sm.buf[0][0] = X[s + c0 - 1];
-            if (WIDE) sm.hib[0][0] = XH[s + c0 - 1];
+            sm.half[0].buf[0] = X[s + c0 - 1];
+            if (WIDE) sm.half[0].hib[0] = XH[s + c0 - 1];
             const uint64_t k0 = rem_key(X[s + c0 - 1], WIDE ? XH[s + c0 - 1] : 0u);
             const uint64_t k1 = rem_key(X[s + c0], WIDE ? XH[s + c0] : 0u);
             if (k0 == k1) sm.carry = find_head_global<WIDE>(X, XH, s, s + c0 - 1, k0);
         }
         if (c0 + cn < n) {
-            sm.buf[0][cn + 1] = X[s + c0 + cn];
-            if (WIDE) sm.hib[0][cn + 1] = XH[s + c0 + cn];
+            sm.half[0].buf[cn + 1] = X[s + c0 + cn];
+            if (WIDE) sm.half[0].hib[cn + 1] = XH[s + c0 + cn];
         }
     }
     __syncthreads();
-    ch.rec = sm.buf[0];
-    ch.hi = sm.hib[0];
+    ch.rec = sm.half[0].buf;
+    ch.hi = sm.half[0].hib;
     ch.cn = cn;
     ch.has_prev = c0 > 0;
     ch.has_next = c0 + cn < n;
@@ -584,8 +589,8 @@ __device__ __forceinline__ void load_chunk(BucketSmem<WIDE>& sm, const BucketArg
 template <bool WIDE>
 __device__ __forceinline__ void whole_unit_chunk(BucketSmem<WIDE>& sm, uint32_t s,
                                                  uint32_t n, int cur, Chunk<WIDE>& ch) {
-    ch.rec = sm.buf[cur];
-    ch.hi = sm.hib[cur];
+    ch.rec = sm.half[cur].buf;
+    ch.hi = sm.half[cur].hib;
     ch.cn = n;
     ch.has_prev = ch.has_next = false;
     ch.g0 = s;
@@ -634,7 +639,7 @@ bucket_sort_kernel(BucketArgs a) {
 
 // ---- kernel 1b (anchor-similar): candidate rule and count on the sorted units -----
 template <bool WIDE>
-__global__ void __launch_bounds__(kRT, 2)
+__global__ void __launch_bounds__(kRT, WIDE ? 2 : 3)
 bucket_count_kernel(BucketArgs a) {
     extern __shared__ __align__(16) unsigned char raw[];
     BucketSmem<WIDE>& sm = *reinterpret_cast<BucketSmem<WIDE>*>(raw);
@@ -696,7 +701,7 @@ unit_scan_kernel(BucketArgs a) {
 
 // ---- kernel 3: write the anchors of every unit --------------------------------------
 template <bool WIDE, int MODE>
-__global__ void __launch_bounds__(kRT, 2)
+__global__ void __launch_bounds__(kRT, WIDE ? 2 : 3)
 bucket_emit_kernel(BucketArgs a) {
     extern __shared__ __align__(16) unsigned char raw[];
     BucketSmem<WIDE>& sm = *reinterpret_cast<BucketSmem<WIDE>*>(raw);
@@ -778,16 +783,19 @@ uint32_t bucket_max_windows(const MsdPlan& plan, uint64_t max_records) {
 void launch_bucket_stage(const BucketArgs& a, int stage, uint64_t max_records,
                          cudaStream_t s, uint32_t* launches) {
     const uint32_t grid = bucket_max_windows(a.plan, max_records);
-#define NPGE_LAUNCH(KERNEL, W)                                                  \
+#define NPGE_LAUNCH(KERNEL, BYTES)                                              \
     do {                                                                        \
-        set_smem(KERNEL, sizeof(BucketSmem<W>));                                \
-        KERNEL<<<grid, kRT, sizeof(BucketSmem<W>), s>>>(a);                     \
+        set_smem(KERNEL, BYTES);                                                \
+        KERNEL<<<grid, kRT, BYTES, s>>>(a);                                     \
         *launches += 1;                                                         \
     } while (0)
-#define NPGE_LAUNCH_W(NAME, ...)                                                \
+// FULL: both halves of the unit buffer (the sort ping-pongs between them)
+#define NPGE_LAUNCH_W(FULL, NAME, ...)                                          \
     do {                                                                        \
-        if (a.plan.wide) NPGE_LAUNCH((NAME<true, ##__VA_ARGS__>), true);        \
-        else NPGE_LAUNCH((NAME<false, ##__VA_ARGS__>), false);                  \
+        if (a.plan.wide) NPGE_LAUNCH((NAME<true, ##__VA_ARGS__>),               \
+            FULL ? sizeof(BucketSmem<true>) : BucketSmem<true>::kSingle());     \
+        else NPGE_LAUNCH((NAME<false, ##__VA_ARGS__>),                          \
+            FULL ? sizeof(BucketSmem<false>) : BucketSmem<false>::kSingle());   \
     } while (0)
     if (stage == kBucketFinal) {
         bucket_finalize_kernel<<<1, 32, 0, s>>>(a);
@@ -804,15 +812,15 @@ void launch_bucket_stage(const BucketArgs& a, int stage, uint64_t max_records,
         *launches += 2;
         break;
     }
-    case kBucketSort: NPGE_LAUNCH_W(bucket_sort_kernel, 0); break;
-    case kBucketMark: NPGE_LAUNCH_W(bucket_sort_kernel, 1); break;
-    case kBucketCount: NPGE_LAUNCH_W(bucket_count_kernel); break;
+    case kBucketSort: NPGE_LAUNCH_W(true, bucket_sort_kernel, 0); break;
+    case kBucketMark: NPGE_LAUNCH_W(true, bucket_sort_kernel, 1); break;
+    case kBucketCount: NPGE_LAUNCH_W(false, bucket_count_kernel); break;
     case kBucketScan:
         unit_scan_kernel<<<1, 1024, 0, s>>>(a);
         *launches += 1;
         break;
-    case kBucketEmit: NPGE_LAUNCH_W(bucket_emit_kernel, 0); break;
-    case kBucketEmitSimilar: NPGE_LAUNCH_W(bucket_emit_kernel, 2); break;
+    case kBucketEmit: NPGE_LAUNCH_W(false, bucket_emit_kernel, 0); break;
+    case kBucketEmitSimilar: NPGE_LAUNCH_W(false, bucket_emit_kernel, 2); break;
     }
 #undef NPGE_LAUNCH_W
 #undef NPGE_LAUNCH

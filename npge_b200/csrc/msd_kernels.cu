@@ -240,8 +240,12 @@ struct __align__(16) PassSmem {
 // ---- pass A: generate + partition by the top wa bits -----------------------------
 // GLOBAL: the payload carries the position in the job-wide scan order of all
 // ranks' sequences (local position + the sequence's delta) instead of the local one.
+// 8-bit digits with narrow records: 52 KB of shared memory and (at some spill) 32
+// registers let four CTAs share an SM; the kernel is latency-bound, occupancy pays
+// (measured on brucella17: 0.545 ms at 2 CTAs, 0.483 at 3, 0.467 at 4; pass B is
+// best at 3: 0.608 / 0.495 / 0.522).
 template <int CAPBITS, bool WIDE, bool GLOBAL>
-__global__ void __launch_bounds__(kRT, 2)
+__global__ void __launch_bounds__(kRT, (CAPBITS == 8 && !WIDE) ? 4 : 2)
 pass_a_kernel(const uint32_t* __restrict__ packed, const uint32_t* __restrict__ nmask,
               MsdPlan plan, const uint32_t* __restrict__ rows, PosMap pm,
               uint64_t* __restrict__ out_rec, uint32_t* __restrict__ out_hi) {
@@ -381,7 +385,7 @@ fine_tables_kernel(const uint32_t* __restrict__ rows, MsdPlan plan, SegTables t,
 
 // ---- pass B: partition every A bucket by the next wb bits ------------------------------
 template <int CAPBITS, bool WIDE>
-__global__ void __launch_bounds__(kRT, 2)
+__global__ void __launch_bounds__(kRT, (CAPBITS == 8 && !WIDE) ? 3 : 2)
 pass_b_kernel(const uint64_t* __restrict__ in_rec, const uint32_t* __restrict__ in_hi,
               MsdPlan plan, SegTables t, const uint32_t* __restrict__ rows,
               const uint32_t* __restrict__ fine_start,
