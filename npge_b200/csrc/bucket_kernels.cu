@@ -337,7 +337,15 @@ unit_build_kernel(BucketArgs a, uint32_t* __restrict__ unit_cnt) {
     const uint32_t ab = blockIdx.x * (blockDim.x / 32) + (threadIdx.x >> 5);
     const uint32_t bins_a = 1u << a.plan.capa, nb = 1u << a.plan.wb;
     if (ab >= bins_a) return;
-    const uint32_t* fs = a.fine_start + (size_t(ab) << a.plan.wb);
+    // the bucket's row of bin starts (2^wb + 1 <= 1025 words) in shared memory: the
+    // greedy loop below is a chain of dependent reads
+    __shared__ uint32_t rows_sm[8][1025];
+    uint32_t* fs = rows_sm[threadIdx.x >> 5];
+    {
+        const uint32_t* src = a.fine_start + (size_t(ab) << a.plan.wb);
+        for (uint32_t x = lane; x <= nb; x += 32) fs[x] = src[x];
+        __syncwarp();
+    }
     uint32_t out = 0;
     if (WRITE) {  // units of the buckets before this one
         for (uint32_t x = lane; x < ab; x += 32) out += unit_cnt[x];
@@ -678,20 +686,32 @@ unit_scan_kernel(BucketArgs a) {
     const uint32_t b = threadIdx.x * per, e = min(b + per, n_win);
     uint64_t sum = 0;
     for (uint32_t i = b; i < e; i++) sum += a.unit_tot[i];
-    part[threadIdx.x] = sum;
+    // block-wide exclusive scan of the 1024 partial sums
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint64_t incl = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint64_t u = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += u;
+    }
+    if (lane == 31) part[warp] = incl;
     __syncthreads();
-    if (threadIdx.x == 0) {
-        uint64_t run = 0;
-        for (int i = 0; i < 1024; i++) {
-            uint64_t v = part[i];
-            part[i] = run;
-            run += v;
+    if (warp == 0) {
+        const uint64_t v = part[lane];
+        uint64_t wi = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint64_t u = __shfl_up_sync(0xffffffffu, wi, o);
+            if (lane >= o) wi += u;
         }
-        a.summary[kSumFragments] = run & 0x7fffffffull;  // before truncation
-        a.summary[kSumBlocks] = run >> 31;
+        part[32 + lane] = wi - v;  // sum of the warps before this one
+        if (lane == 31) {
+            a.summary[kSumFragments] = wi & 0x7fffffffull;  // before truncation
+            a.summary[kSumBlocks] = wi >> 31;
+        }
     }
     __syncthreads();
-    uint64_t run = part[threadIdx.x];
+    uint64_t run = part[32 + warp] + incl - sum;
     for (uint32_t i = b; i < e; i++) {
         uint64_t v = a.unit_tot[i];
         a.unit_tot[i] = run;
@@ -739,13 +759,20 @@ bucket_emit_kernel(BucketArgs a) {
 }
 
 __global__ void bucket_finalize_kernel(BucketArgs a) {
-    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    if (threadIdx.x >= 32 || blockIdx.x != 0) return;
     uint64_t d0 = 0, d1 = 0, nb = 0;
-    for (int s = 0; s < kPartials; s++) {
+    for (int s = threadIdx.x; s < kPartials; s += 32) {
         d0 += a.summary[kSumWords + s * 4 + 0];
         d1 += a.summary[kSumWords + s * 4 + 1];
         nb += a.summary[kSumWords + s * 4 + 2];
     }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        d0 += __shfl_xor_sync(0xffffffffu, d0, o);
+        d1 += __shfl_xor_sync(0xffffffffu, d1, o);
+        nb += __shfl_xor_sync(0xffffffffu, nb, o);
+    }
+    if (threadIdx.x != 0) return;
     uint64_t total = a.summary[kSumFragments];
     uint64_t emitted = total < a.max_fragments ? total : a.max_fragments;
     a.summary[kSumDigest0] = d0;

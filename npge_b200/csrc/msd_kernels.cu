@@ -98,7 +98,7 @@ count_a_kernel(const uint32_t* __restrict__ packed, const uint32_t* __restrict__
 // rows[t][d] (t < n_rows) -> exclusive prefix over t of column d, in place; the
 // column totals go to rows[n_rows][d].  Three launches: block sums, scan of the
 // block sums (one CTA), row prefix.
-constexpr int kScanRows = 64;  // rows per block of the two-level scan
+constexpr int kScanRows = 16;  // rows per block of the two-level scan
 
 __global__ void __launch_bounds__(1024)
 scan_rows_sum_kernel(const uint32_t* __restrict__ rows, uint32_t n_rows,
@@ -112,28 +112,40 @@ scan_rows_sum_kernel(const uint32_t* __restrict__ rows, uint32_t n_rows,
     blk[size_t(blockIdx.x) * bins + d] = s;
 }
 
+// 32 columns x 32 groups of blocks per CTA (grid = bins / 32): every group sums
+// its share of the block sums, a warp shuffle scans the 32 group sums of a column,
+// the group writes its exclusive prefixes.  Loads are 128-byte rows of 32 columns.
 __global__ void __launch_bounds__(1024)
-scan_rows_blk_kernel(uint32_t* __restrict__ blk, uint32_t n_blk,
+scan_rows_blk_kernel(uint32_t* __restrict__ blk, uint32_t n_blk, int bins,
                      uint32_t* __restrict__ totals) {
-    const int bins = blockDim.x, d = threadIdx.x;
-    uint32_t run = 0;
-    uint32_t b = 0;
-    for (; b + 8 <= n_blk; b += 8) {
-        uint32_t v[8];
+    __shared__ uint32_t part[32][33];
+    const int c = threadIdx.x & 31, g = threadIdx.x >> 5;
+    const int d = blockIdx.x * 32 + c;
+    const uint32_t per = (n_blk + 31) / 32;
+    const uint32_t b0 = min(uint32_t(g) * per, n_blk), b1 = min(b0 + per, n_blk);
+    uint32_t sum = 0;
+#pragma unroll 4
+    for (uint32_t b = b0; b < b1; b++) sum += blk[size_t(b) * bins + d];
+    part[g][c] = sum;
+    __syncthreads();
+    {   // warp g scans column g: lane = group
+        const uint32_t v = part[c][g];
+        uint32_t incl = v;
 #pragma unroll
-        for (int j = 0; j < 8; j++) v[j] = blk[size_t(b + j) * bins + d];
-#pragma unroll
-        for (int j = 0; j < 8; j++) {
-            blk[size_t(b + j) * bins + d] = run;
-            run += v[j];
+        for (int o = 1; o < 32; o <<= 1) {
+            uint32_t u = __shfl_up_sync(0xffffffffu, incl, o);
+            if (c >= o) incl += u;
         }
+        part[c][g] = incl - v;
+        if (c == 31) totals[blockIdx.x * 32 + g] = incl;
     }
-    for (; b < n_blk; b++) {
-        uint32_t v = blk[size_t(b) * bins + d];
+    __syncthreads();
+    uint32_t run = part[g][c];
+    for (uint32_t b = b0; b < b1; b++) {
+        const uint32_t v = blk[size_t(b) * bins + d];
         blk[size_t(b) * bins + d] = run;
         run += v;
     }
-    totals[d] = run;
 }
 
 __global__ void __launch_bounds__(1024)
@@ -463,7 +475,8 @@ void scan_rows(uint32_t* rows, uint32_t n_rows, int bins, uint32_t* blk,
                cudaStream_t s) {
     const uint32_t n_blk = (n_rows + kScanRows - 1) / kScanRows;
     scan_rows_sum_kernel<<<n_blk, bins, 0, s>>>(rows, n_rows, blk);
-    scan_rows_blk_kernel<<<1, bins, 0, s>>>(blk, n_blk, rows + size_t(n_rows) * bins);
+    scan_rows_blk_kernel<<<bins / 32, 1024, 0, s>>>(blk, n_blk, bins,
+                                                    rows + size_t(n_rows) * bins);
 }
 
 void apply_rows(uint32_t* rows, uint32_t n_rows, int bins, const uint32_t* blk,
