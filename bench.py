@@ -392,8 +392,11 @@ def run_gpu(args, rank, world, local_rank):
                       "CUDA events around the whole step (kernels, NCCL "
                       "exchanges, host tables), max over ranks"),
             "parallelism": ("1 GPU" if world == 1 else
-                            "sequences sharded per GPU; k-mers repartitioned by "
-                            "hash range, NCCL all-to-all x%d" % world),
+                            "sequences sharded per GPU; k-mers repartitioned by hash "
+                            "range x%d, exchange=%s (peer: pass A scatters into the "
+                            "owners' HBM over NVLink; bulk: copy kernel into peer "
+                            "memory; collective: NCCL all-to-all)"
+                            % (world, parity_stats.get("exchange", "?"))),
         },
         "anchors_per_s": parity_stats["n_fragments_global"] * args.steps / t_dev,
         "fragments": parity_stats["n_fragments_global"],
