@@ -31,6 +31,10 @@ MsdPlan make_msd_plan(int k, uint64_t n_positions) {
     p.total = 2 * k;
     int f = 2;  // fine bits so that a fine bin holds ~1024 records
     while (f < 20 && (uint64_t(1024) << f) < n_positions) f++;
+    if (const char* e = getenv("NPGE_EXP_F")) {  // tests: exercise the wider digit plans
+        const int v = atoi(e);
+        if (v >= 2 && v <= 20) f = v;
+    }
     if (f > p.total) f = p.total;
     const int need = p.total - 32;  // bits a narrow (8 B) record cannot hold
     int wa = (f + 1) / 2;
@@ -50,8 +54,8 @@ MsdPlan make_msd_plan(int k, uint64_t n_positions) {
     p.wb = wb;
     p.rem = p.total - wa;
     p.wide = p.rem > 32;
-    p.capa = wa <= 8 ? 8 : 10;
-    p.capb = wb <= 8 ? 8 : 10;
+    p.capa = wa <= 8 ? 8 : (wa == 9 ? 9 : 10);  // histogram rows of 256 / 512 / 1024 bins
+    p.capb = wb <= 8 ? 8 : (wb == 9 ? 9 : 10);
     p.smem_passes = (p.rem + 7) / 8;
     if (const char* e = getenv("NPGE_EXP_SMEM_PASSES")) p.smem_passes = atoi(e);  // timing only
     return p;
@@ -257,7 +261,7 @@ struct __align__(16) PassSmem {
 // (measured on brucella17: 0.545 ms at 2 CTAs, 0.483 at 3, 0.467 at 4; pass B is
 // best at 3: 0.608 / 0.495 / 0.522).
 template <int CAPBITS, bool WIDE, bool GLOBAL>
-__global__ void __launch_bounds__(kRT, (CAPBITS == 8 && !WIDE) ? 4 : 2)
+__global__ void __launch_bounds__(kRT, WIDE ? 2 : (CAPBITS == 8 ? 4 : (CAPBITS == 9 ? 3 : 2)))
 pass_a_kernel(const uint32_t* __restrict__ packed, const uint32_t* __restrict__ nmask,
               MsdPlan plan, const uint32_t* __restrict__ rows, PosMap pm,
               uint64_t* __restrict__ out_rec, uint32_t* __restrict__ out_hi) {
@@ -397,7 +401,7 @@ fine_tables_kernel(const uint32_t* __restrict__ rows, MsdPlan plan, SegTables t,
 
 // ---- pass B: partition every A bucket by the next wb bits ------------------------------
 template <int CAPBITS, bool WIDE>
-__global__ void __launch_bounds__(kRT, (CAPBITS == 8 && !WIDE) ? 3 : 2)
+__global__ void __launch_bounds__(kRT, (CAPBITS <= 9 && !WIDE) ? 3 : 2)
 pass_b_kernel(const uint64_t* __restrict__ in_rec, const uint32_t* __restrict__ in_hi,
               MsdPlan plan, SegTables t, const uint32_t* __restrict__ rows,
               const uint32_t* __restrict__ fine_start,
@@ -559,6 +563,8 @@ void launch_msd_pass_a(const MsdPlan& plan, const uint32_t* packed,
     } while (0)
     if (plan.capa == 8) {
         if (plan.wide) NPGE_PASS_A2(8, true); else NPGE_PASS_A2(8, false);
+    } else if (plan.capa == 9) {
+        if (plan.wide) NPGE_PASS_A2(9, true); else NPGE_PASS_A2(9, false);
     } else {
         if (plan.wide) NPGE_PASS_A2(10, true); else NPGE_PASS_A2(10, false);
     }
@@ -637,6 +643,8 @@ void launch_msd_pass_b(const MsdPlan& plan, const uint64_t* in_rec, const uint32
     } while (0)
     if (plan.capb == 8) {
         if (plan.wide) NPGE_PASS_B(8, true); else NPGE_PASS_B(8, false);
+    } else if (plan.capb == 9) {
+        if (plan.wide) NPGE_PASS_B(9, true); else NPGE_PASS_B(9, false);
     } else {
         if (plan.wide) NPGE_PASS_B(10, true); else NPGE_PASS_B(10, false);
     }
