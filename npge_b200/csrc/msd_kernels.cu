@@ -37,7 +37,10 @@ MsdPlan make_msd_plan(int k, uint64_t n_positions) {
     }
     if (f > p.total) f = p.total;
     const int need = p.total - 32;  // bits a narrow (8 B) record cannot hold
-    int wa = (f + 1) / 2;
+    // the smaller half goes to pass A: fewer buckets = longer scatter runs (and
+    // larger pieces for the multi-GPU exchange), and its kernel gains most from
+    // the occupancy of narrow rows
+    int wa = f / 2;
     if (need > 0 && need <= kMaxDigitBits && wa < need) wa = need;
     if (wa > kMaxDigitBits) wa = kMaxDigitBits;
     if (const char* e = getenv("NPGE_EXP_WA")) {  // experiments: force the first split
