@@ -256,6 +256,42 @@ int npge_fragment_find_device(npge_anchor_ctx* ctx, const uint8_t* pattern,
                               npge_fragment_result* out);
 void npge_fragment_result_free(npge_fragment_result* out);
 
+/* ---- block_hash / blockset_hash (src/model/block_hash.cpp:29-54,125-130) ------------
+ * The reference's own fingerprint of a block: the ids "name_begin_last"
+ * (Fragment::id, src/model/Fragment.cpp:173-183) of its fragments, as they are
+ * and inverted, sorted; the smaller list joined with ' ' and folded with
+ * multiply / xor.  MoveUnchanged (src/algo/MoveUnchanged.cpp:37-49) keeps a
+ * sorted list of these values between the iterations of AnchorLoop
+ * (src/algo/lua_lib.lua:719-721) and moves the blocks whose hash it has seen;
+ * blockset_hash is their XOR over the blocks with more than one fragment.
+ * Computed on the device for all blocks of a flat block list at once.
+ *
+ *  names[s]          name of sequence s (Sequence::name()), NUL-terminated; no
+ *                    bytes <= ' ', and no name + "_" may be a prefix of another
+ *                    name + "_" (NPGE_ANCHOR_ERR_PARAMS otherwise: the ids
+ *                    would not be ordered by name)
+ *  block_offsets     [n_blocks + 1] into the fragment arrays, ascending
+ *  frag_max_pos      NULL: every fragment is frag_len long (anchors)
+ *  hashes            [n_blocks] out (may be NULL)
+ *  blockset_hash     out (may be NULL)
+ * All pointers are host memory. */
+int npge_block_hashes(npge_anchor_ctx* ctx, const char* const* names, uint32_t n_seqs,
+                      uint64_t n_blocks, const uint64_t* block_offsets,
+                      const uint32_t* frag_seq, const uint32_t* frag_min_pos,
+                      const uint32_t* frag_max_pos, uint32_t frag_len,
+                      const int8_t* frag_ori, uint64_t* hashes, uint64_t* blockset_hash);
+/* The same over the device-resident result of the last npge_anchor_find_device
+ * (nothing but the hashes crosses PCIe).  names[s]: the sequences as passed to
+ * npge_anchor_upload.  NPGE_ANCHOR_ERR_STATE when max_anchor_fragments cut the
+ * list inside a block: that block is completed on the host by
+ * npge_anchor_fetch, so hash the fetched arrays with npge_block_hashes. */
+int npge_anchor_block_hashes(npge_anchor_ctx* ctx, const char* const* names,
+                             uint32_t n_seqs, uint64_t* hashes, uint64_t* blockset_hash);
+
+/* device time (ms, CUDA events around the hash kernels) of the last call of
+ * either function on this context */
+float npge_block_hashes_last_ms(npge_anchor_ctx* ctx);
+
 /* Library self-description: "npge_anchor <version> sm_100a" */
 const char* npge_anchor_version(void);
 

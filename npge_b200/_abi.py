@@ -18,6 +18,7 @@ EXPORTS = [
     "npge_anchor_dist_scatter_peer", "npge_anchor_dist_copy_peer",
     "npge_fragment_find", "npge_fragment_find_device", "npge_fragment_result_free",
     "npge_anchor_upload_raw", "npge_anchor_dist_scatter_local",
+    "npge_block_hashes", "npge_anchor_block_hashes", "npge_block_hashes_last_ms",
 ]
 IPC_BYTES = 128
 
@@ -149,5 +150,15 @@ def load():
                                             C.POINTER(FragmentResult)]
     L.npge_fragment_result_free.restype = None
     L.npge_fragment_result_free.argtypes = [C.POINTER(FragmentResult)]
+    L.npge_block_hashes.restype = C.c_int
+    L.npge_block_hashes.argtypes = [ctx, C.POINTER(C.c_char_p), C.c_uint32, C.c_uint64,
+                                    C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                    C.c_uint32, C.c_void_p, C.c_void_p,
+                                    C.POINTER(C.c_uint64)]
+    L.npge_anchor_block_hashes.restype = C.c_int
+    L.npge_anchor_block_hashes.argtypes = [ctx, C.POINTER(C.c_char_p), C.c_uint32,
+                                           C.c_void_p, C.POINTER(C.c_uint64)]
+    L.npge_block_hashes_last_ms.restype = C.c_float
+    L.npge_block_hashes_last_ms.argtypes = [ctx]
     _lib = L
     return L

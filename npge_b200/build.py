@@ -8,8 +8,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 SOURCES = ["api.cu", "scan_kernels.cu", "sort_kernels.cu", "group_kernels.cu",
            "msd_kernels.cu", "bucket_kernels.cu", "fragment_kernels.cu",
-           "ingest_kernels.cu"]
-HEADERS = ["common.cuh", "kernels.h", "rank.cuh", os.path.join("..", "..", "include",
+           "ingest_kernels.cu", "block_hash_kernels.cu"]
+HEADERS = ["common.cuh", "kernels.h", "rank.cuh", "block_hash_core.h", "block_hash_names.h", os.path.join("..", "..", "include",
                                                      "npge_anchor.h")]
 LIB = os.path.join(HERE, "libnpge_anchor.so")
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3",
@@ -39,8 +39,9 @@ def build(force=False, verbose=False):
 HOST = os.path.join(HERE, "host")
 SHIM_LIB = os.path.join(HOST, "libnpge_gpu_processors.so")
 SHIM_TEST = os.path.join(HOST, "test_gpu_anchor_finder")
+SHIM_TEST_MOVE = os.path.join(HOST, "test_gpu_move_unchanged")
 SHIM_SOURCES = ["gpu_anchor_finder.cpp", "gpu_anchor_finder.hpp", "npge_facade.hpp",
-                "test_gpu_anchor_finder.cpp"]
+                "test_gpu_anchor_finder.cpp", "test_gpu_move_unchanged.cpp"]
 
 
 def build_shim(force=False):
@@ -48,9 +49,9 @@ def build_shim(force=False):
     linked against libnpge_anchor.so) and its unit-test binary."""
     build(force=False)
     srcs = [os.path.join(HOST, f) for f in SHIM_SOURCES] + [LIB]
-    if (not force and os.path.exists(SHIM_LIB) and os.path.exists(SHIM_TEST) and
-            all(os.path.getmtime(f) <= min(os.path.getmtime(SHIM_LIB),
-                                           os.path.getmtime(SHIM_TEST)) for f in srcs)):
+    outs = [SHIM_LIB, SHIM_TEST, SHIM_TEST_MOVE]
+    if (not force and all(os.path.exists(f) for f in outs) and
+            all(os.path.getmtime(f) <= min(os.path.getmtime(o) for o in outs) for f in srcs)):
         return SHIM_TEST
     cxx = os.environ.get("CXX", "g++")
     common = ["-std=c++17", "-O2", "-Wall", "-Wextra", "-I", HOST]
@@ -59,6 +60,9 @@ def build_shim(force=False):
                                             os.path.join(HOST, "gpu_anchor_finder.cpp")] + link)
     subprocess.check_call([cxx] + common + ["-o", SHIM_TEST,
                                             os.path.join(HOST, "test_gpu_anchor_finder.cpp"),
+                                            "-L", HOST, "-lnpge_gpu_processors"] + link)
+    subprocess.check_call([cxx] + common + ["-o", SHIM_TEST_MOVE,
+                                            os.path.join(HOST, "test_gpu_move_unchanged.cpp"),
                                             "-L", HOST, "-lnpge_gpu_processors"] + link)
     return SHIM_TEST
 

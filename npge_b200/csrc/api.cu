@@ -9,6 +9,8 @@
 #include <new>
 #include <utility>
 
+#include "block_hash_core.h"
+#include "block_hash_names.h"
 #include "kernels.h"
 
 using namespace npge_b200;
@@ -232,7 +234,8 @@ extern "C" void npge_anchor_destroy(npge_anchor_ctx* ctx) {
                            &ctx->rhi[1], &ctx->seq_lut, &ctx->g_seq_start, &ctx->g_seq_caller,
                            &ctx->g_seq_lut, &ctx->pos_delta, &ctx->recv_rec, &ctx->recv_hi,
                            &ctx->peer_tab, &ctx->frag_pat, &ctx->frag_tiles, &ctx->frag_out,
-                           &ctx->raw, &ctx->ingest};
+                           &ctx->raw, &ctx->ingest, &ctx->bh_in, &ctx->bh_names,
+                           &ctx->bh_scratch, &ctx->bh_out};
     for (void* q : ctx->peer_opened) cudaIpcCloseMemHandle(q);
     for (DeviceBuffer* b : all) release(*b);
     for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
@@ -1807,4 +1810,187 @@ extern "C" void npge_fragment_result_free(npge_fragment_result* out) {
     if (!out) return;
     delete static_cast<FragmentHost*>(out->owner_);
     memset(out, 0, sizeof(*out));
+}
+
+// ==== block_hash of flat block lists (block_hash_kernels.cu) ========================
+namespace {
+
+// Fragments per launch: bounds the key scratch (32 B per fragment) at 1 GiB.
+// NPGE_BLOCK_HASH_BATCH overrides it (the tests run many small batches).
+uint64_t block_hash_batch() {
+    const char* e = getenv("NPGE_BLOCK_HASH_BATCH");
+    const long long v = e ? atoll(e) : 0;
+    return v > 0 ? uint64_t(v) : uint64_t(1) << 25;
+}
+
+// Device pointers of a flat block list; hashes of all blocks -> host.
+int block_hashes_device(npge_anchor_ctx* ctx, const char* const* names, uint32_t n_seqs,
+                        uint64_t n_blocks, uint64_t n_fragments, const uint64_t* d_block_off,
+                        const uint32_t* d_seq, const uint32_t* d_min, const uint32_t* d_max,
+                        uint32_t frag_len, const int8_t* d_ori, uint64_t* hashes,
+                        uint64_t* blockset_hash) {
+    if (!names && n_seqs) return fail(NPGE_ANCHOR_ERR_PARAMS, "names is NULL");
+    NameTable table;
+    const std::string why = build_name_table(names, n_seqs, table);
+    if (!why.empty()) return fail(NPGE_ANCHOR_ERR_PARAMS, why);
+    if (blockset_hash) *blockset_hash = 0;
+    if (n_blocks == 0) return NPGE_ANCHOR_OK;
+    cudaStream_t st = ctx->stream;
+    // names: [seq_rank u32 x n_seqs][name_off u32 x ranks + 1][bytes]
+    const size_t n_off = table.off.size();
+    const size_t names_bytes = (size_t(n_seqs) + n_off) * 4 + table.bytes.size();
+    NPGE_TRY(ensure(ctx->bh_names, names_bytes));
+    uint32_t* d_rank = ptr<uint32_t>(ctx->bh_names);
+    uint32_t* d_off = d_rank + n_seqs;
+    uint8_t* d_bytes = reinterpret_cast<uint8_t*>(d_off + n_off);
+    if (n_seqs) {
+        NPGE_CUDA(cudaMemcpyAsync(d_rank, table.seq_rank.data(), size_t(n_seqs) * 4,
+                                  cudaMemcpyHostToDevice, st));
+    }
+    NPGE_CUDA(cudaMemcpyAsync(d_off, table.off.data(), n_off * 4, cudaMemcpyHostToDevice, st));
+    NPGE_CUDA(cudaMemcpyAsync(d_bytes, table.bytes.data(), table.bytes.size(),
+                              cudaMemcpyHostToDevice, st));
+    // out: [hashes u64 x n_blocks][xor u64][error u32, pad][cut_block][cut_frag]
+    const uint64_t batch = block_hash_batch();
+    if ((n_fragments + batch - 1) / batch > (1u << 20)) {
+        return fail(NPGE_ANCHOR_ERR_PARAMS, "NPGE_BLOCK_HASH_BATCH is too small");
+    }
+    const uint32_t n_cuts = std::max<uint32_t>(1, uint32_t((n_fragments + batch - 1) / batch));
+    NPGE_TRY(ensure(ctx->bh_out, (n_blocks + 2 + 2 * (size_t(n_cuts) + 1)) * 8));
+    uint64_t* d_hashes = ptr<uint64_t>(ctx->bh_out);
+    uint64_t* d_xor = d_hashes + n_blocks;
+    uint32_t* d_error = reinterpret_cast<uint32_t*>(d_xor + 1);
+    uint64_t* d_cut_block = d_xor + 2;
+    uint64_t* d_cut_frag = d_cut_block + n_cuts + 1;
+    NPGE_CUDA(cudaMemsetAsync(d_xor, 0, 16, st));
+    std::vector<uint64_t> cuts(2 * (size_t(n_cuts) + 1), 0);
+    launch_block_hash_cuts(d_block_off, n_blocks, batch, n_cuts, d_cut_block,
+                           d_cut_frag, st);
+    NPGE_CUDA(cudaGetLastError());
+    NPGE_CUDA(cudaMemcpyAsync(cuts.data(), d_cut_block, cuts.size() * 8,
+                              cudaMemcpyDeviceToHost, st));
+    NPGE_CUDA(cudaStreamSynchronize(st));
+    const uint64_t* cut_block = cuts.data();
+    const uint64_t* cut_frag = cuts.data() + n_cuts + 1;
+    const uint32_t n_launch = n_cuts;
+    uint64_t max_batch = 0;
+    for (uint32_t i = 0; i < n_launch; i++) {
+        if (cut_block[i] > cut_block[i + 1] || cut_frag[i] > cut_frag[i + 1] ||
+            cut_frag[i + 1] > n_fragments) {
+            return fail(NPGE_ANCHOR_ERR_PARAMS, "block_offsets are not ascending");
+        }
+        max_batch = std::max(max_batch, cut_frag[i + 1] - cut_frag[i]);
+    }
+    NPGE_TRY(ensure(ctx->bh_scratch, max_batch * 2 * sizeof(IdKey)));
+    NPGE_CUDA(cudaEventRecord(ctx->ev[0], st));
+    BlockHashArgs a = {};
+    a.block_off = d_block_off;
+    a.n_fragments = n_fragments;
+    a.frag_seq = d_seq;
+    a.min_pos = d_min;
+    a.max_pos = d_max;
+    a.frag_len = frag_len;
+    a.frag_ori = d_ori;
+    a.n_seqs = n_seqs;
+    a.seq_rank = d_rank;
+    a.name_bytes = d_bytes;
+    a.name_off = d_off;
+    a.scratch = ctx->bh_scratch.ptr;
+    a.hashes = d_hashes;
+    a.xor_out = d_xor;
+    a.error = d_error;
+    // one launch per batch of blocks between two cuts (cut 0 = block 0)
+    for (uint32_t i = 0; i < n_launch; i++) {
+        a.b0 = cut_block[i];
+        a.b1 = cut_block[i + 1];
+        a.f_base = cut_frag[i];
+        a.f_end = cut_frag[i + 1];
+        launch_block_hash(a, st);
+        NPGE_CUDA(cudaGetLastError());
+    }
+    NPGE_CUDA(cudaEventRecord(ctx->ev[1], st));
+    uint64_t tail[2] = {0, 0};
+    NPGE_CUDA(cudaMemcpyAsync(tail, d_xor, 16, cudaMemcpyDeviceToHost, st));
+    if (hashes) {
+        NPGE_CUDA(cudaMemcpyAsync(hashes, d_hashes, n_blocks * 8, cudaMemcpyDeviceToHost, st));
+    }
+    NPGE_CUDA(cudaStreamSynchronize(st));
+    NPGE_CUDA(cudaEventElapsedTime(&ctx->bh_ms, ctx->ev[0], ctx->ev[1]));
+    const uint32_t err = uint32_t(tail[1]);
+    if (err & 1) return fail(NPGE_ANCHOR_ERR_PARAMS, "block_offsets are not ascending");
+    if (err & 2) return fail(NPGE_ANCHOR_ERR_PARAMS, "frag_seq out of range");
+    if (blockset_hash) *blockset_hash = tail[0];
+    return NPGE_ANCHOR_OK;
+}
+
+}  // namespace
+
+extern "C" int npge_block_hashes(npge_anchor_ctx* ctx, const char* const* names,
+                                 uint32_t n_seqs, uint64_t n_blocks,
+                                 const uint64_t* block_offsets, const uint32_t* frag_seq,
+                                 const uint32_t* frag_min_pos, const uint32_t* frag_max_pos,
+                                 uint32_t frag_len, const int8_t* frag_ori, uint64_t* hashes,
+                                 uint64_t* blockset_hash) {
+    if (!ctx) return fail(NPGE_ANCHOR_ERR_PARAMS, "ctx is NULL");
+    if (!block_offsets) return fail(NPGE_ANCHOR_ERR_PARAMS, "block_offsets is NULL");
+    if (block_offsets[0] != 0) return fail(NPGE_ANCHOR_ERR_PARAMS, "block_offsets[0] must be 0");
+    const uint64_t nf = block_offsets[n_blocks];
+    if (nf && (!frag_seq || !frag_min_pos || !frag_ori)) {
+        return fail(NPGE_ANCHOR_ERR_PARAMS, "NULL fragment array");
+    }
+    if (!frag_max_pos && frag_len == 0 && nf) {
+        return fail(NPGE_ANCHOR_ERR_PARAMS, "frag_len must be > 0 without frag_max_pos");
+    }
+    NPGE_CUDA(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    // in: [block_off u64 x n_blocks + 1][seq u32][min u32][max u32][ori i8]
+    const size_t off_bytes = (n_blocks + 1) * 8;
+    NPGE_TRY(ensure(ctx->bh_in, off_bytes + nf * 13 + 64));
+    uint8_t* base = static_cast<uint8_t*>(ctx->bh_in.ptr);
+    uint64_t* d_off = reinterpret_cast<uint64_t*>(base);
+    uint32_t* d_seq = reinterpret_cast<uint32_t*>(base + off_bytes);
+    uint32_t* d_min = d_seq + nf;
+    uint32_t* d_max = d_min + nf;
+    int8_t* d_ori = reinterpret_cast<int8_t*>(d_max + nf);
+    NPGE_CUDA(cudaMemcpyAsync(d_off, block_offsets, off_bytes, cudaMemcpyHostToDevice, st));
+    if (nf) {
+        NPGE_CUDA(cudaMemcpyAsync(d_seq, frag_seq, nf * 4, cudaMemcpyHostToDevice, st));
+        NPGE_CUDA(cudaMemcpyAsync(d_min, frag_min_pos, nf * 4, cudaMemcpyHostToDevice, st));
+        if (frag_max_pos) {
+            NPGE_CUDA(cudaMemcpyAsync(d_max, frag_max_pos, nf * 4, cudaMemcpyHostToDevice, st));
+        }
+        NPGE_CUDA(cudaMemcpyAsync(d_ori, frag_ori, nf, cudaMemcpyHostToDevice, st));
+    }
+    return block_hashes_device(ctx, names, n_seqs, n_blocks, nf, d_off, d_seq, d_min,
+                               frag_max_pos ? d_max : nullptr, frag_len, d_ori, hashes,
+                               blockset_hash);
+}
+
+extern "C" int npge_anchor_block_hashes(npge_anchor_ctx* ctx, const char* const* names,
+                                        uint32_t n_seqs, uint64_t* hashes,
+                                        uint64_t* blockset_hash) {
+    if (!ctx) return fail(NPGE_ANCHOR_ERR_PARAMS, "ctx is NULL");
+    if (!ctx->have_result) {
+        return fail(NPGE_ANCHOR_ERR_STATE, "npge_anchor_find_device has not run");
+    }
+    const uint64_t limit = uint64_t(ctx->last_params.max_anchor_fragments);
+    if (ctx->total_selected > limit && limit > 0) {
+        return fail(NPGE_ANCHOR_ERR_STATE,
+                    "max-anchor-fragments cut the list: the last block is completed by "
+                    "npge_anchor_fetch; hash the fetched arrays with npge_block_hashes");
+    }
+    const uint32_t need = ctx->dist ? uint32_t(ctx->gseqs.size()) : ctx->n_caller_seqs;
+    if (n_seqs < need) {
+        return fail(NPGE_ANCHOR_ERR_PARAMS, "fewer names than uploaded sequences");
+    }
+    NPGE_CUDA(cudaSetDevice(ctx->device));
+    return block_hashes_device(ctx, names, n_seqs, ctx->stats.n_blocks,
+                               ctx->stats.n_fragments, ptr<uint64_t>(ctx->r_block_off),
+                               ptr<uint32_t>(ctx->r_seq), ptr<uint32_t>(ctx->r_pos), nullptr,
+                               uint32_t(ctx->last_params.anchor_size), ptr<int8_t>(ctx->r_ori),
+                               hashes, blockset_hash);
+}
+
+extern "C" float npge_block_hashes_last_ms(npge_anchor_ctx* ctx) {
+    return ctx ? ctx->bh_ms : 0.f;
 }

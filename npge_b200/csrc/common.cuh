@@ -172,6 +172,8 @@ struct npge_anchor_ctx {
     uint64_t peer_capacity = 0;              // records every receive buffer can take
     npge_b200::DeviceBuffer frag_pat, frag_tiles, frag_out;  // FragmentFinder scratch
     npge_b200::DeviceBuffer raw, ingest;                     // upload_raw scratch
+    npge_b200::DeviceBuffer bh_in, bh_names, bh_scratch, bh_out;  // block_hash
+    float bh_ms = 0.f;                       // device time of the last block-hash call
     npge_b200::DeviceBuffer peer_tab;        // per-bucket destination addresses
     bool a_counted = false;
     std::vector<uint32_t> a_start_h;         // host copy of this rank's a_start

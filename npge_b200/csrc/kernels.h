@@ -196,6 +196,31 @@ uint32_t fragment_tiles(uint64_t n_padded);
 void launch_fragment_find(const FragmentArgs& a, int stage, cudaStream_t s,
                           uint32_t* launches);
 
+// ---- block_hash of flat block lists (block_hash_kernels.cu) ----------------------
+struct BlockHashArgs {
+    const uint64_t* block_off;   // [n_blocks + 1]
+    uint64_t b0, b1;             // blocks of this launch
+    uint64_t f_base, f_end;      // fragments of the launch (f_base = scratch origin)
+    uint64_t n_fragments;
+    const uint32_t* frag_seq;
+    const uint32_t* min_pos;
+    const uint32_t* max_pos;     // nullptr: min_pos + frag_len - 1
+    uint32_t frag_len;
+    const int8_t* frag_ori;
+    uint32_t n_seqs;
+    const uint32_t* seq_rank;    // [n_seqs] rank of the sequence's name
+    const uint8_t* name_bytes;   // names in rank order
+    const uint32_t* name_off;    // [ranks + 1]
+    void* scratch;               // 2 IdKey per fragment of the launch
+    uint64_t* hashes;            // [n_blocks]
+    uint64_t* xor_out;           // XOR of the hashes of blocks with > 1 fragment
+    uint32_t* error;             // bit 0: bad offsets, bit 1: bad sequence index
+};
+void launch_block_hash_cuts(const uint64_t* block_off, uint64_t n_blocks, uint64_t cap,
+                            uint32_t n_cuts, uint64_t* cut_block, uint64_t* cut_frag,
+                            cudaStream_t s);
+void launch_block_hash(const BlockHashArgs& a, cudaStream_t s);
+
 struct GroupArgs {
     const uint32_t* klo;
     const uint32_t* khi;   // nullptr when k <= 16

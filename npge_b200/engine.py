@@ -221,6 +221,47 @@ class AnchorEngine:
         out, total = self._matches(r)
         return (out, total) if with_total else out
 
+    # ---- block_hash / blockset_hash (src/model/block_hash.cpp) -----------------------
+    @staticmethod
+    def _names(names):
+        return (C.c_char_p * max(1, len(names)))(
+            *[n.encode() if isinstance(n, str) else bytes(n) for n in names])
+
+    def block_hashes(self, names, block_offsets, frag_seq, frag_min_pos, frag_ori,
+                     frag_max_pos=None, frag_len=0):
+        """The reference's block_hash of every block of a flat block list and
+        their XOR over the blocks of more than one fragment (blockset_hash):
+        (hashes u64 [B], blockset_hash).  frag_max_pos None: every fragment is
+        frag_len long."""
+        offs = np.ascontiguousarray(block_offsets, dtype=np.uint64)
+        seq = np.ascontiguousarray(frag_seq, dtype=np.uint32)
+        mn = np.ascontiguousarray(frag_min_pos, dtype=np.uint32)
+        ori = np.ascontiguousarray(frag_ori, dtype=np.int8)
+        mx = (np.ascontiguousarray(frag_max_pos, dtype=np.uint32)
+              if frag_max_pos is not None else None)
+        nb = len(offs) - 1
+        out = np.zeros(max(nb, 1), dtype=np.uint64)
+        total = C.c_uint64(0)
+        self._check(self._lib.npge_block_hashes(
+            self._ctx, self._names(names), len(names), nb, offs.ctypes.data,
+            seq.ctypes.data, mn.ctypes.data, mx.ctypes.data if mx is not None else None,
+            int(frag_len), ori.ctypes.data, out.ctypes.data, C.byref(total)))
+        return out[:nb], int(total.value)
+
+    def anchor_block_hashes(self, names, want_hashes=True):
+        """The same over the device-resident result of the last find_device():
+        only the hashes cross PCIe."""
+        nb = int(self.stats()["n_blocks"])
+        out = np.zeros(max(nb, 1), dtype=np.uint64) if want_hashes else None
+        total = C.c_uint64(0)
+        self._check(self._lib.npge_anchor_block_hashes(
+            self._ctx, self._names(names), len(names),
+            out.ctypes.data if want_hashes else None, C.byref(total)))
+        return (out[:nb] if want_hashes else None), int(total.value)
+
+    def block_hashes_ms(self):
+        return float(self._lib.npge_block_hashes_last_ms(self._ctx))
+
     def stats(self):
         s = _abi.Stats()
         self._check(self._lib.npge_anchor_get_stats(self._ctx, C.byref(s)))

@@ -233,5 +233,92 @@ const char* FragmentFinder::name_impl() const {
     return "Locate fragment by its sequence";  // FragmentFinder.cpp:168-170
 }
 
+// ---- MoveUnchanged (src/algo/MoveUnchanged.cpp) -----------------------------------
+struct MoveUnchanged::Impl {
+    npge_anchor_ctx* ctx = nullptr;
+    int device = 0;
+    std::vector<uint64_t> hashes;  // sorted, unique: MoveUnchanged::hashes_
+    std::vector<uint64_t> last;
+};
+
+MoveUnchanged::MoveUnchanged() : impl_(new Impl) {
+    declare_bs("other", "Where unchanged blocks are looked for");
+    declare_bs("target", "Where unchanged blocks are moved to");
+}
+
+MoveUnchanged::~MoveUnchanged() {
+    if (impl_->ctx) npge_anchor_destroy(impl_->ctx);
+    delete impl_;
+}
+
+void MoveUnchanged::set_device(int device) {
+    if (impl_->ctx) {
+        npge_anchor_destroy(impl_->ctx);
+        impl_->ctx = nullptr;
+    }
+    impl_->device = device;
+}
+
+void MoveUnchanged::clear() {
+    impl_->hashes.clear();
+}
+
+const std::vector<uint64_t>& MoveUnchanged::last_hashes() const {
+    return impl_->last;
+}
+
+void MoveUnchanged::run_impl() const {
+    Impl& st = *impl_;
+    BlockSet& t = *block_set();
+    BlockSet& o = *other();
+    // flat copy of `other`: fragments as (sequence index, min, max, ori)
+    std::vector<Block*> blocks(o.begin(), o.end());
+    std::vector<Sequence*> seq_of;
+    std::vector<const char*> names;
+    std::vector<uint64_t> offsets(1, 0);
+    std::vector<uint32_t> frag_seq, min_pos, max_pos;
+    std::vector<int8_t> ori;
+    for (size_t b = 0; b < blocks.size(); b++) {
+        for (Block::const_iterator it = blocks[b]->begin(); it != blocks[b]->end(); ++it) {
+            const Fragment* f = *it;
+            size_t s = 0;
+            while (s < seq_of.size() && seq_of[s] != f->seq()) s++;  // few sequences
+            if (s == seq_of.size()) seq_of.push_back(f->seq());
+            frag_seq.push_back(uint32_t(s));
+            min_pos.push_back(uint32_t(f->min_pos()));
+            max_pos.push_back(uint32_t(f->max_pos()));
+            ori.push_back(int8_t(f->ori()));
+        }
+        offsets.push_back(frag_seq.size());
+    }
+    for (size_t s = 0; s < seq_of.size(); s++) names.push_back(seq_of[s]->name().c_str());
+    st.last.assign(blocks.size(), 0);
+    if (!blocks.empty()) {
+        if (!st.ctx) check(npge_anchor_create(&st.ctx, st.device), "no CUDA device");
+        check(npge_block_hashes(st.ctx, names.data(), uint32_t(names.size()), blocks.size(),
+                                offsets.data(), frag_seq.data(), min_pos.data(),
+                                max_pos.data(), 0, ori.data(), st.last.data(), nullptr),
+              "npge_block_hashes");
+    }
+    // process_block_impl (:37-49): seen in an EARLIER run -> move, else memorize;
+    // the hashes of this run join the set only afterwards (after_thread_impl)
+    std::vector<uint64_t> fresh;
+    for (size_t b = 0; b < blocks.size(); b++) {
+        if (std::binary_search(st.hashes.begin(), st.hashes.end(), st.last[b])) {
+            o.detach(blocks[b]);
+            t.insert(blocks[b]);
+        } else {
+            fresh.push_back(st.last[b]);
+        }
+    }
+    st.hashes.insert(st.hashes.end(), fresh.begin(), fresh.end());
+    std::sort(st.hashes.begin(), st.hashes.end());  // finish_work_impl: sort_unique
+    st.hashes.erase(std::unique(st.hashes.begin(), st.hashes.end()), st.hashes.end());
+}
+
+const char* MoveUnchanged::name_impl() const {
+    return "Move unchanged blocks from other to target";  // MoveUnchanged.cpp:71-73
+}
+
 }  // namespace gpu
 }  // namespace npge

@@ -4,6 +4,10 @@
 // (used_hashes_); the work happens in libnpge_anchor.so (include/npge_anchor.h).
 #pragma once
 
+#include <stdint.h>
+
+#include <vector>
+
 #ifdef NPGE_B200_REAL_HEADERS   // inside an NPGE checkout
 #include "Processor.hpp"
 #else
@@ -48,12 +52,38 @@ private:
     Impl* impl_;
 };
 
+// Drop-in for the reference's MoveUnchanged (src/algo/MoveUnchanged.hpp:
+// "Move unchanged blocks from other to target"): remembers block_hash
+// (src/model/block_hash.cpp:29-54) of every block of `other` it has seen; a
+// block whose hash was seen in an earlier run moves to `target`.  AnchorLoop
+// runs it right after AnchorFinder (src/algo/lua_lib.lua:719-721).  The hashes
+// of all blocks are computed in one call on the device (npge_block_hashes).
+class MoveUnchanged : public Processor {
+public:
+    MoveUnchanged();
+    ~MoveUnchanged();
+    void set_device(int device);
+    void clear();  // forget the hashes (MoveUnchanged.cpp:24-26)
+    // block_hash of the blocks of the last run, in the order of `other` before
+    // the run (for tests and diagnostics)
+    const std::vector<uint64_t>& last_hashes() const;
+
+protected:
+    void run_impl() const;
+    const char* name_impl() const;
+
+private:
+    struct Impl;
+    Impl* impl_;
+};
+
 // Meta registration: replaces the built-in factory (Meta.hpp:83-87), so every
 // pipeline, Lua script and the CLI that asks for "AnchorFinder" gets this one.
 template <typename MetaT>
 inline void register_processors(MetaT* meta) {
     meta->template set_processor<AnchorFinder>("AnchorFinder", true);
     meta->template set_processor<FragmentFinder>("FragmentFinder", true);
+    meta->template set_processor<MoveUnchanged>("MoveUnchanged", true);
 }
 
 }  // namespace gpu

@@ -117,8 +117,9 @@ public:
     // NAME_BEGIN_LAST, last = end position in the fragment's direction (Fragment.cpp:173-183)
     std::string id() const {
         std::ostringstream s;
-        s << seq_->name() << "_" << begin_pos() << "_"
-          << (ori_ == 1 ? (long long)max_pos_ : (long long)min_pos_);
+        long long last = ori_ == 1 ? (long long)max_pos_ : (long long)min_pos_;
+        if (min_pos_ == max_pos_ && ori_ == -1) last = -1;  // one-letter reverse fragment
+        s << seq_->name() << "_" << begin_pos() << "_" << last;
         return s.str();
     }
 
@@ -160,6 +161,8 @@ public:
         return std::vector<SequencePtr>(seqs_.begin(), seqs_.end());
     }
     void insert(Block* block) { blocks_.insert(block); }  // the set owns block
+    void detach(Block* block) { blocks_.erase(block); }   // the caller owns it now (BlockSet.cpp)
+    bool has(Block* block) const { return blocks_.count(block) != 0; }
     size_t size() const { return blocks_.size(); }
     bool empty() const { return blocks_.empty(); }
     Block* front() const { return blocks_.empty() ? nullptr : *blocks_.begin(); }
@@ -229,6 +232,9 @@ public:
 
     void set_block_set(BlockSetPtr bs) { target_ = bs; }
     BlockSetPtr block_set() const { return target_; }
+    // the second blockset of two-blockset processors (Processor::other(), "other")
+    void set_other(BlockSetPtr bs) { other_ = bs; }
+    BlockSetPtr other() const { return other_; }
 
     bool has_opt(const std::string& name) const { return opts_.count(name) != 0; }
     AnyAs opt_value(const std::string& name) const {
@@ -315,7 +321,7 @@ private:
     };
     std::map<std::string, Opt> opts_;
     std::vector<Rule> rules_;
-    BlockSetPtr target_;
+    BlockSetPtr target_, other_;
     std::string key_;
     int workers_;
     bool interrupted_;

@@ -776,6 +776,26 @@ inline void digest_terms(uint64_t t, uint64_t h, uint64_t& a, uint64_t& b) {
 
 }  // namespace
 
+/* block_hash (block_hash.cpp:29-54) of every block of a flat block list, as
+ * MoveUnchanged (MoveUnchanged.cpp:37-49) computes it block by block */
+extern "C" void oracle_block_hashes(const char* const* names,
+        uint64_t n_blocks, const uint64_t* block_offsets,
+        const uint32_t* frag_seq, const uint32_t* frag_min_pos,
+        const uint32_t* frag_max_pos, const int8_t* frag_ori,
+        uint64_t* hashes) {
+    for (uint64_t b = 0; b < n_blocks; b++) {
+        std::vector<std::string> dir, inv;
+        for (uint64_t f = block_offsets[b]; f < block_offsets[b + 1]; f++) {
+            const char* name = names[frag_seq[f]];
+            dir.push_back(fragment_id(name, frag_min_pos[f], frag_max_pos[f],
+                                      frag_ori[f]));
+            inv.push_back(fragment_id(name, frag_min_pos[f], frag_max_pos[f],
+                                      -frag_ori[f]));
+        }
+        hashes[b] = one_block_hash(dir, inv);
+    }
+}
+
 /* blockset_hash, block_hash.cpp:125-130 (+ HashGroup::create_task_impl
  * :101-113: blocks with <= 1 fragment are skipped) */
 extern "C" uint64_t oracle_blockset_hash(const char* const* names,

@@ -92,6 +92,14 @@ uint64_t oracle_blockset_hash(const char* const* names, uint64_t n_blocks,
                               const uint32_t* frag_max_pos,
                               const int8_t* frag_ori);
 
+/* block_hash (block_hash.cpp:29-54) of every block, hashes[n_blocks] */
+void oracle_block_hashes(const char* const* names, uint64_t n_blocks,
+                         const uint64_t* block_offsets,
+                         const uint32_t* frag_seq,
+                         const uint32_t* frag_min_pos,
+                         const uint32_t* frag_max_pos,
+                         const int8_t* frag_ori, uint64_t* hashes);
+
 /* Order-independent 128-bit digest of (seq, min_pos, ori, h) tuples; the same
  * definition as npge_anchor_result.digest (include/npge_anchor.h). */
 void oracle_digest(const oracle_result* r, uint64_t digest[2]);

@@ -259,6 +259,25 @@ def blockset_hash(names, blocks):
         mx.ctypes.data, ori.ctypes.data)
 
 
+def block_hashes(names, offsets, seq, min_pos, max_pos, ori):
+    """Reference block_hash of every block of a flat block list (numpy arrays:
+    offsets u64 [B+1], seq / min_pos / max_pos u32 [F], ori i8 [F])."""
+    offs = np.ascontiguousarray(offsets, dtype=np.uint64)
+    seq = np.ascontiguousarray(seq, dtype=np.uint32)
+    mn = np.ascontiguousarray(min_pos, dtype=np.uint32)
+    mx = np.ascontiguousarray(max_pos, dtype=np.uint32)
+    ori = np.ascontiguousarray(ori, dtype=np.int8)
+    out = np.zeros(len(offs) - 1, dtype=np.uint64)
+    arr = (C.c_char_p * len(names))(*[n.encode() for n in names])
+    L = lib()
+    L.oracle_block_hashes.restype = None
+    L.oracle_block_hashes.argtypes = [C.POINTER(C.c_char_p), C.c_uint64] + [C.c_void_p] * 6
+    L.oracle_block_hashes(arr, len(offs) - 1, offs.ctypes.data, seq.ctypes.data,
+                          mn.ctypes.data, mx.ctypes.data, ori.ctypes.data,
+                          out.ctypes.data)
+    return out
+
+
 def fragment_find(seqs, pattern, max_matches=100):
     """FragmentFinder restatement: list of (seq, min_pos, ori), in the order of
     a one-worker run of the reference, cut to max_matches."""

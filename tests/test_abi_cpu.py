@@ -14,7 +14,7 @@ def test_library_builds_and_exports_all_declared_symbols():
     path = build.build()
     lib = C.CDLL(path)
     header = open(os.path.join(ROOT, "include", "npge_anchor.h")).read()
-    declared = set(re.findall(r"\b(npge_(?:anchor|fragment)_[a-z_]+)\s*\(", header))
+    declared = set(re.findall(r"\b(npge_(?:anchor|fragment|block)_[a-z_]+)\s*\(", header))
     assert declared == set(_abi.EXPORTS)
     for name in declared:
         assert hasattr(lib, name), name
