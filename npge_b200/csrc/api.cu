@@ -1836,20 +1836,25 @@ int block_hashes_device(npge_anchor_ctx* ctx, const char* const* names, uint32_t
     if (blockset_hash) *blockset_hash = 0;
     if (n_blocks == 0) return NPGE_ANCHOR_OK;
     cudaStream_t st = ctx->stream;
-    // names: [seq_rank u32 x n_seqs][name_off u32 x ranks + 1][bytes]
-    const size_t n_off = table.off.size();
-    const size_t names_bytes = (size_t(n_seqs) + n_off) * 4 + table.bytes.size();
-    NPGE_TRY(ensure(ctx->bh_names, names_bytes));
-    uint32_t* d_rank = ptr<uint32_t>(ctx->bh_names);
-    uint32_t* d_off = d_rank + n_seqs;
-    uint8_t* d_bytes = reinterpret_cast<uint8_t*>(d_off + n_off);
+    // names: [words u64][seq_rank u32 x n_seqs][pos u32 x ranks][len u32 x ranks]
+    const size_t n_words = table.words.size(), n_ranks = table.pos.size();
+    static const std::vector<uint16_t> bcd4 = make_bcd4();
+    NPGE_TRY(ensure(ctx->bh_names,
+                    n_words * 8 + (size_t(n_seqs) + 2 * n_ranks) * 4 + bcd4.size() * 2));
+    uint64_t* d_words = ptr<uint64_t>(ctx->bh_names);
+    uint32_t* d_rank = reinterpret_cast<uint32_t*>(d_words + n_words);
+    uint32_t* d_pos = d_rank + n_seqs;
+    uint32_t* d_len = d_pos + n_ranks;
+    uint16_t* d_bcd4 = reinterpret_cast<uint16_t*>(d_len + n_ranks);
+    NPGE_CUDA(cudaMemcpyAsync(d_bcd4, bcd4.data(), bcd4.size() * 2, cudaMemcpyHostToDevice, st));
+    NPGE_CUDA(cudaMemcpyAsync(d_words, table.words.data(), n_words * 8, cudaMemcpyHostToDevice,
+                              st));
     if (n_seqs) {
         NPGE_CUDA(cudaMemcpyAsync(d_rank, table.seq_rank.data(), size_t(n_seqs) * 4,
                                   cudaMemcpyHostToDevice, st));
     }
-    NPGE_CUDA(cudaMemcpyAsync(d_off, table.off.data(), n_off * 4, cudaMemcpyHostToDevice, st));
-    NPGE_CUDA(cudaMemcpyAsync(d_bytes, table.bytes.data(), table.bytes.size(),
-                              cudaMemcpyHostToDevice, st));
+    NPGE_CUDA(cudaMemcpyAsync(d_pos, table.pos.data(), n_ranks * 4, cudaMemcpyHostToDevice, st));
+    NPGE_CUDA(cudaMemcpyAsync(d_len, table.len.data(), n_ranks * 4, cudaMemcpyHostToDevice, st));
     // out: [hashes u64 x n_blocks][xor u64][error u32, pad][cut_block][cut_frag]
     const uint64_t batch = block_hash_batch();
     if ((n_fragments + batch - 1) / batch > (1u << 20)) {
@@ -1893,8 +1898,10 @@ int block_hashes_device(npge_anchor_ctx* ctx, const char* const* names, uint32_t
     a.frag_ori = d_ori;
     a.n_seqs = n_seqs;
     a.seq_rank = d_rank;
-    a.name_bytes = d_bytes;
-    a.name_off = d_off;
+    a.name_words = d_words;
+    a.name_pos = d_pos;
+    a.name_len = d_len;
+    a.bcd4 = d_bcd4;
     a.scratch = ctx->bh_scratch.ptr;
     a.hashes = d_hashes;
     a.xor_out = d_xor;

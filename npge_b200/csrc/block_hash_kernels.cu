@@ -4,11 +4,16 @@
 // (block_hash.cpp:125-130) are built from.  SURVEY 8(f) rank 1 / 8(a) a19.
 //
 // One thread per block (anchor blocks hold a few fragments each, and there are
-// millions of them): keys of the ids (block_hash_core.h) -> sort -> pick the
-// smaller of the two id lists -> fold the bytes of the joint string.  Blocks
-// of up to kLocalFrags fragments keep their keys in local memory (interleaved
-// per thread, so a warp's accesses coalesce); larger ones use a slice of a
-// global scratch buffer and a heap sort.
+// millions of them): keys of the ids (block_hash_core.h) -> which of the two id
+// lists is the smaller one (by their minima) -> sort that list -> fold the bytes
+// of the joint string.  Blocks of up to kFastFrags fragments keep their keys in
+// shared memory, interleaved by thread (a warp working on key i of its 32
+// blocks touches 512 contiguous bytes).  Larger blocks, and blocks whose two
+// lists start with the same id, build both lists in a slice of a global scratch
+// buffer (heap sort above 24 keys).
+// The first version kept the keys in per-thread local memory (768 B a thread):
+// with every SM full that is more than the L2 holds, and the kernel moved 2 GB
+// through DRAM for 150 MB of input (profiles/r01j_block_hash.md).
 #include "block_hash_core.h"
 #include "kernels.h"
 
@@ -16,7 +21,7 @@ namespace npge_b200 {
 
 namespace {
 
-constexpr int kLocalFrags = 24;  // = the insertion-sort range of sort_keys
+constexpr int kFastFrags = 20;   // keys per thread in shared memory (40 KB per CTA)
 constexpr int kThreads = 128;
 
 __global__ void __launch_bounds__(kThreads) block_hash_kernel(BlockHashArgs a) {
@@ -33,12 +38,12 @@ __global__ void __launch_bounds__(kThreads) block_hash_kernel(BlockHashArgs a) {
             if (!ok) {
                 atomicOr(a.error, 2u);  // sequence index out of range
             } else {
-                IdKey local[2 * kLocalFrags];
-                IdKey* scratch = (f1 - f0 <= kLocalFrags)
-                                     ? local
-                                     : reinterpret_cast<IdKey*>(a.scratch) + 2 * (f0 - a.f_base);
-                h = block_hash_flat(f0, f1, a.frag_seq, a.min_pos, a.max_pos, a.frag_len,
-                                    a.frag_ori, a.seq_rank, a.name_bytes, a.name_off, scratch);
+                extern __shared__ __align__(16) unsigned char raw[];
+                const KeySlots slots = {reinterpret_cast<IdKey*>(raw) + threadIdx.x, kThreads};
+                const FlatBlocks fb = {a.frag_seq, a.min_pos, a.max_pos, a.frag_len, a.frag_ori,
+                                       a.seq_rank, a.name_words, a.name_pos, a.name_len, a.bcd4};
+                h = block_hash_flat(fb, f0, f1, slots, kFastFrags,
+                                    reinterpret_cast<IdKey*>(a.scratch) + 2 * (f0 - a.f_base));
                 // blockset_hash skips blocks of <= 1 fragment (HashGroup::
                 // create_task_impl, block_hash.cpp:101-113)
                 counted = f1 - f0 > 1;
@@ -88,7 +93,8 @@ void launch_block_hash_cuts(const uint64_t* block_off, uint64_t n_blocks, uint64
 void launch_block_hash(const BlockHashArgs& a, cudaStream_t s) {
     if (a.b1 <= a.b0) return;
     const uint64_t n = a.b1 - a.b0;
-    block_hash_kernel<<<uint32_t((n + kThreads - 1) / kThreads), kThreads, 0, s>>>(a);
+    block_hash_kernel<<<uint32_t((n + kThreads - 1) / kThreads), kThreads,
+                        kFastFrags * kThreads * sizeof(IdKey), s>>>(a);
 }
 
 }  // namespace npge_b200

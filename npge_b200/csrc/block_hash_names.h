@@ -19,9 +19,20 @@ namespace npge_b200 {
 
 struct NameTable {
     std::vector<uint32_t> seq_rank;  // [n_seqs] rank of the sequence's name
-    std::vector<uint8_t> bytes;      // names in rank order, concatenated
-    std::vector<uint32_t> off;       // [ranks + 1]
+    std::vector<uint64_t> words;     // names in rank order, 8 bytes per word, little-endian,
+                                     // every name starting a new word (zero padded)
+    std::vector<uint32_t> pos;       // [ranks] first word of the name
+    std::vector<uint32_t> len;       // [ranks] its length in bytes
 };
+
+// bcd4[v] = the decimal digits of v < 10000, one per nibble (block_hash_core.h: bcd10)
+inline std::vector<uint16_t> make_bcd4() {
+    std::vector<uint16_t> t(10000);
+    for (uint32_t v = 0; v < 10000; v++) {
+        t[v] = uint16_t(((v / 1000) << 12) | ((v / 100 % 10) << 8) | ((v / 10 % 10) << 4) | (v % 10));
+    }
+    return t;
+}
 
 // Returns "" or the reason the names cannot be used.
 inline std::string build_name_table(const char* const* names, uint32_t n_seqs,
@@ -54,13 +65,26 @@ inline std::string build_name_table(const char* const* names, uint32_t n_seqs,
         t.seq_rank[i] = uint32_t(std::lower_bound(sorted.begin(), sorted.end(), key[i]) -
                                  sorted.begin());
     }
-    t.bytes.clear();
-    t.off.assign(1, 0);
+    t.words.clear();
+    t.pos.clear();
+    t.len.clear();
     for (const std::string& s : sorted) {
-        t.bytes.insert(t.bytes.end(), s.begin(), s.end() - 1);  // without the '_'
-        t.off.push_back(uint32_t(t.bytes.size()));
+        const size_t n = s.size() - 1;  // without the '_'
+        t.pos.push_back(uint32_t(t.words.size()));
+        t.len.push_back(uint32_t(n));
+        for (size_t i = 0; i < n; i += 8) {
+            uint64_t w = 0;
+            for (size_t j = i; j < n && j < i + 8; j++) {
+                w |= uint64_t(static_cast<unsigned char>(s[j])) << (8 * (j - i));
+            }
+            t.words.push_back(w);
+        }
     }
-    if (t.bytes.empty()) t.bytes.push_back(0);  // never a zero-sized upload
+    if (t.words.empty()) t.words.push_back(0);  // never a zero-sized upload
+    if (t.pos.empty()) {
+        t.pos.push_back(0);
+        t.len.push_back(0);
+    }
     return "";
 }
 

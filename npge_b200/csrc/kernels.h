@@ -209,8 +209,10 @@ struct BlockHashArgs {
     const int8_t* frag_ori;
     uint32_t n_seqs;
     const uint32_t* seq_rank;    // [n_seqs] rank of the sequence's name
-    const uint8_t* name_bytes;   // names in rank order
-    const uint32_t* name_off;    // [ranks + 1]
+    const uint64_t* name_words;  // names in rank order, 8 bytes per word
+    const uint32_t* name_pos;    // [ranks] first word of the name
+    const uint32_t* name_len;    // [ranks] bytes
+    const uint16_t* bcd4;        // [10000] decimal digits of v, one per nibble
     void* scratch;               // 2 IdKey per fragment of the launch
     uint64_t* hashes;            // [n_blocks]
     uint64_t* xor_out;           // XOR of the hashes of blocks with > 1 fragment

@@ -93,6 +93,7 @@ def host_core(tmp_path_factory):
                            os.path.join(ROOT, "tests", "block_hash_host.cpp")])
     lib = C.CDLL(so)
     lib.bh_host_error.restype = C.c_char_p
+    lib.bh_host_set_fast_cap.argtypes = [C.c_uint32]
     lib.bh_host_block_hashes.argtypes = (
         [C.POINTER(C.c_char_p), C.c_uint32, C.c_uint64] + [C.c_void_p] * 4 +
         [C.c_uint32, C.c_void_p, C.c_void_p])
@@ -107,6 +108,7 @@ def host_core(tmp_path_factory):
         if rc:
             raise ValueError(lib.bh_host_error().decode())
         return out[:len(offs) - 1]
+    run.set_fast_cap = lib.bh_host_set_fast_cap
     return run
 
 
@@ -142,6 +144,35 @@ def test_core_digit_boundaries_and_one_letter_fragments(host_core):
         want = oracle.block_hashes(NAMES, offs, seq, mn, mx, ori)
         assert np.array_equal(host_core(NAMES, offs, seq, mn, None, length, ori), want)
         assert int(want[0]) == py_block_hash(NAMES, as_lists(offs, seq, mn, mx, ori)[0])
+
+
+def test_core_ties_between_the_two_lists(host_core):
+    # an id of one fragment equals the inverted id of another: the lists start
+    # with the same id and the one-list shortcut must hand over to the full path
+    frags = [(3, 5, 10, 1), (3, 5, 10, -1), (4, 7, 7, 1), (4, 7, 7, -1), (3, 0, 4, 1)]
+    for take in (frags[:2], frags[2:4], frags, frags[::-1], frags[:3]):
+        offs = np.array([0, len(take)], np.uint64)
+        seq = np.array([f[0] for f in take], np.uint32)
+        mn = np.array([f[1] for f in take], np.uint32)
+        mx = np.array([f[2] for f in take], np.uint32)
+        ori = np.array([f[3] for f in take], np.int8)
+        want = oracle.block_hashes(NAMES, offs, seq, mn, mx, ori)
+        assert int(want[0]) == py_block_hash(NAMES, as_lists(offs, seq, mn, mx, ori)[0])
+        assert np.array_equal(host_core(NAMES, offs, seq, mn, mx, 0, ori), want)
+
+
+def test_core_fast_path_capacity(host_core):
+    # the shared-memory capacity of the kernel's fast path does not change results
+    rng = np.random.default_rng(4)
+    offs, seq, mn, ori, length = random_blocks(rng, NAMES, max_blocks=60)
+    mx = mn + np.uint32(length - 1)
+    want = oracle.block_hashes(NAMES, offs, seq, mn, mx, ori)
+    try:
+        for cap in (1, 2, 5, 17, 64, 300):
+            host_core.set_fast_cap(cap)
+            assert np.array_equal(host_core(NAMES, offs, seq, mn, None, length, ori), want)
+    finally:
+        host_core.set_fast_cap(0)
 
 
 def test_core_large_block_heap_sort(host_core):
