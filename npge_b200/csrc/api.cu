@@ -5,7 +5,13 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#if defined(__x86_64__)
+#include <immintrin.h>
+#endif
+#include <atomic>
+#include <condition_variable>
 #include <mutex>
+#include <thread>
 #include <new>
 #include <utility>
 
@@ -167,6 +173,19 @@ struct HostResult {
     PinnedVector<int8_t> frag_ori;
 };
 
+// How large results come back (npge_anchor_fetch): plain copies of the three
+// fragment arrays, or the compact transfer (fetch_compact below).  NPGE_FETCH =
+// plain | compact | auto overrides the default.
+enum { kFetchPlain, kFetchCompact, kFetchAuto };
+constexpr int kFetchDefault = kFetchPlain;
+int fetch_mode() {
+    const char* e = getenv("NPGE_FETCH");
+    if (e && strcmp(e, "plain") == 0) return kFetchPlain;
+    if (e && strcmp(e, "compact") == 0) return kFetchCompact;
+    if (e && strcmp(e, "auto") == 0) return kFetchAuto;
+    return kFetchDefault;
+}
+
 int check_params(const npge_anchor_params* p) {
     if (!p) return fail(NPGE_ANCHOR_ERR_PARAMS, "params is NULL");
     // add_opt_rule("anchor-size > 0"), ("anchor-size <= 32"): AnchorFinder.cpp:49-51
@@ -235,11 +254,12 @@ extern "C" void npge_anchor_destroy(npge_anchor_ctx* ctx) {
                            &ctx->g_seq_lut, &ctx->pos_delta, &ctx->recv_rec, &ctx->recv_hi,
                            &ctx->peer_tab, &ctx->frag_pat, &ctx->frag_tiles, &ctx->frag_out,
                            &ctx->raw, &ctx->ingest, &ctx->bh_in, &ctx->bh_names,
-                           &ctx->bh_scratch, &ctx->bh_out};
+                           &ctx->bh_scratch, &ctx->bh_out, &ctx->r_pay};
     for (void* q : ctx->peer_opened) cudaIpcCloseMemHandle(q);
     for (DeviceBuffer* b : all) release(*b);
     for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
     for (auto& ev : ctx->ev_pass) if (ev) cudaEventDestroy(ev);
+    for (auto& ev : ctx->fetch_ev) if (ev) cudaEventDestroy(ev);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -316,6 +336,10 @@ int upload_common(npge_anchor_ctx* ctx, int32_t anchor_size, const uint64_t* siz
                 lut[q] = uint32_t(sidx);
             }
         }
+        ctx->h_lut = lut;
+        ctx->h_caller = callers;
+        ctx->h_start32.resize(starts.size());
+        for (size_t i = 0; i < starts.size(); i++) ctx->h_start32[i] = uint32_t(starts[i]);
         NPGE_TRY(ensure(ctx->seq_lut, n_chunks * 4));
         NPGE_CUDA(cudaMemcpyAsync(ctx->seq_lut.ptr, lut.data(), n_chunks * 4,
                                   cudaMemcpyHostToDevice, st));
@@ -510,6 +534,7 @@ int find_device_msd(npge_anchor_ctx* ctx, const npge_anchor_params* p,
     NPGE_TRY(ensure(ctx->r_seq, max_frags * 4));
     NPGE_TRY(ensure(ctx->r_pos, max_frags * 4));
     NPGE_TRY(ensure(ctx->r_ori, max_frags));
+    if (fetch_mode() != kFetchPlain) NPGE_TRY(ensure(ctx->r_pay, max_frags * 4));
     NPGE_TRY(ensure(ctx->r_block_off, (max_frags / 2 + 2) * 8));
     NPGE_TRY(ensure(ctx->r_block_hash, (max_frags / 2 + 2) * 8));
     if (similar) {
@@ -550,6 +575,8 @@ int find_device_msd(npge_anchor_ctx* ctx, const npge_anchor_params* p,
     }
     NPGE_CUDA(cudaEventRecord(ctx->ev[2], st));
     BucketArgs a = bucket_args(ctx, plan, mb, mb.rec[0], mb.hi[0], n_used, limit);
+    const bool with_pay = fetch_mode() != kFetchPlain;
+    a.r_pay = with_pay ? ptr<uint32_t>(ctx->r_pay) : nullptr;
     launch_bucket(a, similar, np ? max_records : 0, st, &ctx->ev[4], &launches);
     NPGE_CUDA(cudaGetLastError());
     NPGE_CUDA(cudaEventRecord(ctx->ev[3], st));
@@ -593,6 +620,7 @@ int find_device_msd(npge_anchor_ctx* ctx, const npge_anchor_params* p,
     ctx->total_selected = summary[kSumFragments];
     ctx->plan = plan;
     ctx->msd = true;
+    ctx->have_pay = with_pay;
     ctx->last_params = *p;
     ctx->have_result = true;
     if (stats) *stats = s;
@@ -628,6 +656,7 @@ extern "C" int npge_anchor_find_device(npge_anchor_ctx* ctx,
         }
     }
     ctx->msd = false;
+    ctx->have_pay = false;
     const int k = p->anchor_size;
     const SortPlan plan = make_sort_plan(k, digit_bits_preference());
     const int passes = plan.passes;
@@ -936,6 +965,182 @@ int fix_cut_group(npge_anchor_ctx* ctx, HostResult& r, uint64_t limit) {
 
 }  // namespace
 
+// ---- compact fetch ------------------------------------------------------------------
+// The fragment arrays of a large result are 9 bytes per fragment and PCIe is the
+// slowest link of the host-buffer call.  The emit kernel also leaves the 4-byte
+// payload (position in the packed genome << 1 | strand) of every fragment; only
+// that crosses the bus, in chunks, and host threads turn each chunk into
+// (sequence, position, strand) while the next one is copied.
+namespace {
+
+// Persistent worker threads: creating a dozen std::threads per call costs about
+// as much as the work they would do.
+class WorkerPool {
+public:
+    static WorkerPool& instance() {
+        static WorkerPool* pool = new WorkerPool;  // never destroyed: threads are detached
+        return *pool;
+    }
+    // one job at a time: hold this from start() to wait()
+    std::mutex& serial() { return serial_; }
+    void start(const std::function<void(int)>& job) {
+        std::lock_guard<std::mutex> lock(mu_);
+        job_ = job;
+        pending_ = n_;
+        gen_++;
+        cv_.notify_all();
+    }
+    void wait() {
+        std::unique_lock<std::mutex> lock(mu_);
+        done_.wait(lock, [this] { return pending_ == 0; });
+    }
+private:
+    WorkerPool() {
+        unsigned hw = std::thread::hardware_concurrency();
+        int n = int(hw ? hw : 4) - 1;  // the caller's thread drives the copies
+        if (const char* e = getenv("NPGE_FETCH_THREADS")) n = atoi(e);
+        n_ = std::max(1, std::min(n, 32));
+        for (int i = 0; i < n_; i++) std::thread([this, i] { loop(i); }).detach();
+    }
+    void loop(int index) {
+        uint64_t seen = 0;
+        while (true) {
+            std::function<void(int)> job;
+            {
+                std::unique_lock<std::mutex> lock(mu_);
+                cv_.wait(lock, [&] { return gen_ != seen; });
+                seen = gen_;
+                job = job_;
+            }
+            job(index);
+            std::lock_guard<std::mutex> lock(mu_);
+            if (--pending_ == 0) done_.notify_all();
+        }
+    }
+    std::mutex mu_, serial_;
+    std::condition_variable cv_, done_;
+    std::function<void(int)> job_;
+    uint64_t gen_ = 0;
+    int pending_ = 0, n_ = 1;
+};
+
+constexpr uint64_t kFetchCompactMin = uint64_t(1) << 20;  // fragments; below: plain copies
+constexpr uint64_t kFetchChunk = uint64_t(1) << 22;       // fragments per PCIe chunk
+constexpr uint64_t kFetchPiece = uint64_t(1) << 16;       // fragments per unit of host work
+
+bool fetch_compact_wanted(const npge_anchor_ctx* ctx, uint64_t nf, uint64_t limit) {
+    if (!ctx->have_pay || !ctx->msd || ctx->dist || nf == 0) return false;
+    if (ctx->total_selected > limit && limit > 0) return false;  // cut group fix-up: plain path
+    const int mode = fetch_mode();
+    if (mode == kFetchPlain) return false;
+    if (mode == kFetchCompact) return true;
+    return nf >= kFetchCompactMin;  // auto: only where PCIe time dominates
+}
+
+// payloads [lo, hi) -> the three fragment arrays (locate() of bucket_kernels.cu).
+// The arrays are written once and not read by this thread again: streaming
+// stores keep them out of the cache and skip the read-for-ownership of every
+// line, which halves the memory traffic of the expansion (it is bandwidth-bound:
+// 13 bytes per fragment over all cores).  lo is a multiple of 8 (kFetchPiece).
+void expand_payloads(const npge_anchor_ctx* ctx, const uint32_t* pay, uint64_t lo, uint64_t hi,
+                     uint32_t* seq, uint32_t* pos, int8_t* ori) {
+    const uint32_t* lut = ctx->h_lut.data();
+    const uint32_t* start = ctx->h_start32.data();  // [S + 1], the last one = all positions
+    const uint32_t* caller = ctx->h_caller.data();
+    const int shift = ctx->lut_shift;
+    uint64_t f = lo;
+#if defined(__x86_64__)
+    for (; f + 8 <= hi; f += 8) {
+        uint64_t oris = 0;
+        for (int j = 0; j < 8; j++) {
+            const uint32_t p = pay[f + j], g = p >> 1;
+            uint32_t s = lut[g >> shift];
+            while (start[s + 1] <= g) s++;
+            _mm_stream_si32(reinterpret_cast<int*>(seq + f + j), int(caller[s]));
+            _mm_stream_si32(reinterpret_cast<int*>(pos + f + j), int(g - start[s]));
+            oris |= uint64_t((p & 1) ? 0x01u : 0xffu) << (8 * j);
+        }
+        _mm_stream_si64(reinterpret_cast<long long*>(ori + f), static_cast<long long>(oris));
+    }
+#endif
+    for (; f < hi; f++) {
+        const uint32_t p = pay[f], g = p >> 1;
+        uint32_t s = lut[g >> shift];
+        while (start[s + 1] <= g) s++;
+        seq[f] = caller[s];
+        pos[f] = g - start[s];
+        ori[f] = (p & 1) ? 1 : -1;
+    }
+#if defined(__x86_64__)
+    _mm_sfence();  // the streaming stores are visible before the piece counts as done
+#endif
+}
+
+int fetch_compact(npge_anchor_ctx* ctx, HostResult* r, uint64_t nf, uint64_t nb) {
+    cudaStream_t st = ctx->stream;
+    PinnedVector<uint32_t> pay;
+    try {
+        pay.resize(nf);
+    } catch (std::bad_alloc&) {
+        return fail(NPGE_ANCHOR_ERR_MEMORY, "out of host memory for the result");
+    }
+    const uint64_t n_chunks = (nf + kFetchChunk - 1) / kFetchChunk;
+    while (ctx->fetch_ev.size() < n_chunks) {
+        cudaEvent_t ev = nullptr;
+        NPGE_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+        ctx->fetch_ev.push_back(ev);
+    }
+    for (uint64_t c = 0; c < n_chunks; c++) {
+        const uint64_t lo = c * kFetchChunk, hi = std::min(nf, lo + kFetchChunk);
+        NPGE_CUDA(cudaMemcpyAsync(pay.data() + lo, ptr<uint32_t>(ctx->r_pay) + lo, (hi - lo) * 4,
+                                  cudaMemcpyDeviceToHost, st));
+        NPGE_CUDA(cudaEventRecord(ctx->fetch_ev[c], st));
+    }
+    NPGE_CUDA(cudaMemcpyAsync(r->block_offsets.data(), ctx->r_block_off.ptr, (nb + 1) * 8,
+                              cudaMemcpyDeviceToHost, st));
+    if (nb) {
+        NPGE_CUDA(cudaMemcpyAsync(r->block_hash.data(), ctx->r_block_hash.ptr, nb * 8,
+                                  cudaMemcpyDeviceToHost, st));
+    }
+    // the workers take pieces in order and wait until the chunk of their piece
+    // has arrived; this thread announces the arrivals
+    std::atomic<uint64_t> ready(0), next(0);
+    std::atomic<bool> abort(false);
+    const uint64_t n_pieces = (nf + kFetchPiece - 1) / kFetchPiece;
+    uint32_t* seq = r->frag_seq.data();
+    uint32_t* pos = r->frag_min_pos.data();
+    int8_t* ori = r->frag_ori.data();
+    const uint32_t* pay_h = pay.data();
+    WorkerPool& pool = WorkerPool::instance();
+    std::lock_guard<std::mutex> one_job(pool.serial());
+    pool.start([&, ctx, nf, n_pieces, seq, pos, ori, pay_h](int) {
+        while (true) {
+            const uint64_t piece = next.fetch_add(1);
+            if (piece >= n_pieces) return;
+            const uint64_t lo = piece * kFetchPiece, hi = std::min(nf, lo + kFetchPiece);
+            while (ready.load(std::memory_order_acquire) < hi) {
+                if (abort.load()) return;
+                std::this_thread::yield();
+            }
+            expand_payloads(ctx, pay_h, lo, hi, seq, pos, ori);
+        }
+    });
+    cudaError_t err = cudaSuccess;
+    for (uint64_t c = 0; c < n_chunks && err == cudaSuccess; c++) {
+        err = cudaEventSynchronize(ctx->fetch_ev[c]);
+        if (err == cudaSuccess) {
+            ready.store(std::min(nf, (c + 1) * kFetchChunk), std::memory_order_release);
+        }
+    }
+    if (err != cudaSuccess) abort.store(true);
+    pool.wait();  // the job refers to this frame: never return before it is done
+    NPGE_CUDA(err);
+    NPGE_CUDA(cudaStreamSynchronize(st));
+    return NPGE_ANCHOR_OK;
+}
+
+}  // namespace
+
 extern "C" int npge_anchor_fetch(npge_anchor_ctx* ctx, npge_anchor_result* out) {
     if (!ctx || !out) return fail(NPGE_ANCHOR_ERR_PARAMS, "NULL argument");
     memset(out, 0, sizeof(*out));
@@ -962,21 +1167,25 @@ extern "C" int npge_anchor_fetch(npge_anchor_ctx* ctx, npge_anchor_result* out) 
     uint64_t used_n = 0;
     auto body = [&]() -> int {
         cudaStream_t st = ctx->stream;
-        if (nf) {
-            NPGE_CUDA(cudaMemcpyAsync(r->frag_seq.data(), ctx->r_seq.ptr, nf * 4,
-                                      cudaMemcpyDeviceToHost, st));
-            NPGE_CUDA(cudaMemcpyAsync(r->frag_min_pos.data(), ctx->r_pos.ptr, nf * 4,
-                                      cudaMemcpyDeviceToHost, st));
-            NPGE_CUDA(cudaMemcpyAsync(r->frag_ori.data(), ctx->r_ori.ptr, nf,
-                                      cudaMemcpyDeviceToHost, st));
+        if (fetch_compact_wanted(ctx, nf, limit)) {
+            NPGE_TRY(fetch_compact(ctx, r, nf, nb));
+        } else {
+            if (nf) {
+                NPGE_CUDA(cudaMemcpyAsync(r->frag_seq.data(), ctx->r_seq.ptr, nf * 4,
+                                          cudaMemcpyDeviceToHost, st));
+                NPGE_CUDA(cudaMemcpyAsync(r->frag_min_pos.data(), ctx->r_pos.ptr, nf * 4,
+                                          cudaMemcpyDeviceToHost, st));
+                NPGE_CUDA(cudaMemcpyAsync(r->frag_ori.data(), ctx->r_ori.ptr, nf,
+                                          cudaMemcpyDeviceToHost, st));
+            }
+            NPGE_CUDA(cudaMemcpyAsync(r->block_offsets.data(), ctx->r_block_off.ptr,
+                                      (nb + 1) * 8, cudaMemcpyDeviceToHost, st));
+            if (nb) {
+                NPGE_CUDA(cudaMemcpyAsync(r->block_hash.data(), ctx->r_block_hash.ptr,
+                                          nb * 8, cudaMemcpyDeviceToHost, st));
+            }
+            NPGE_CUDA(cudaStreamSynchronize(st));
         }
-        NPGE_CUDA(cudaMemcpyAsync(r->block_offsets.data(), ctx->r_block_off.ptr,
-                                  (nb + 1) * 8, cudaMemcpyDeviceToHost, st));
-        if (nb) {
-            NPGE_CUDA(cudaMemcpyAsync(r->block_hash.data(), ctx->r_block_hash.ptr,
-                                      nb * 8, cudaMemcpyDeviceToHost, st));
-        }
-        NPGE_CUDA(cudaStreamSynchronize(st));
         out->digest[0] = ctx->stats.digest[0];
         out->digest[1] = ctx->stats.digest[1];
         bool lone_tail = false;
@@ -1653,6 +1862,7 @@ extern "C" int npge_anchor_dist_emit(npge_anchor_ctx* ctx, const npge_anchor_par
                     9 * s.n_fragments + 16 * s.n_blocks;
     ctx->total_selected = summary[kSumFragments];
     ctx->msd = true;
+    ctx->have_pay = false;
     ctx->last_params = *p;
     ctx->last_params.max_anchor_fragments = int64_t(std::min<uint64_t>(local_limit, uint64_t(INT64_MAX)));
     ctx->have_result = true;

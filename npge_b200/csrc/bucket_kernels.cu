@@ -239,6 +239,7 @@ __device__ __forceinline__ void unit_write(BucketSmem<WIDE>& sm, const Chunk<WID
                 a.r_seq[f] = seq;
                 a.r_pos[f] = pos;
                 a.r_ori[f] = (pay & 1) ? 1 : -1;
+                if (a.r_pay) a.r_pay[f] = pay;
                 const uint64_t t = (uint64_t(seq) << 33) | (uint64_t(pos) << 1) | (pay & 1);
                 uint64_t x, y;
                 digest_terms(t, key, x, y);

@@ -184,6 +184,13 @@ struct npge_anchor_ctx {
     // device result
     npge_b200::DeviceBuffer r_seq, r_pos, r_ori, r_block_off, r_block_hash;
     npge_b200::DeviceBuffer scan_status, summary;
+    // compact fetch (api.cu: fetch_compact): the emit kernel also leaves the
+    // 4-byte payload (position << 1 | strand) of every fragment; the host turns it
+    // into (sequence, position, strand) while the next chunk crosses PCIe
+    npge_b200::DeviceBuffer r_pay;
+    bool have_pay = false;
+    std::vector<uint32_t> h_start32, h_caller, h_lut;  // host copies of the position tables
+    std::vector<cudaEvent_t> fetch_ev;
 
     bool have_result = false;
     int result_buf = 0;       // which of the double buffers holds sorted records

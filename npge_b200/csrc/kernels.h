@@ -138,6 +138,7 @@ struct BucketArgs {
     uint32_t* r_seq;
     uint32_t* r_pos;
     int8_t* r_ori;
+    uint32_t* r_pay;             // optional: payload (position << 1 | strand) per fragment
     uint64_t* r_block_off;
     uint64_t* r_block_hash;
     uint64_t* unit_tot;          // per unit: blocks << 31 | fragments, then its prefix
