@@ -9,7 +9,7 @@ CSRC = os.path.join(HERE, "csrc")
 SOURCES = ["api.cu", "scan_kernels.cu", "sort_kernels.cu", "group_kernels.cu",
            "msd_kernels.cu", "bucket_kernels.cu", "fragment_kernels.cu",
            "ingest_kernels.cu", "block_hash_kernels.cu"]
-HEADERS = ["common.cuh", "kernels.h", "rank.cuh", "block_hash_core.h", "block_hash_names.h", os.path.join("..", "..", "include",
+HEADERS = ["common.cuh", "kernels.h", "rank.cuh", "block_hash_core.h", "block_hash_names.h", "fetch_expand.h", os.path.join("..", "..", "include",
                                                      "npge_anchor.h")]
 LIB = os.path.join(HERE, "libnpge_anchor.so")
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3",

@@ -5,9 +5,6 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
-#if defined(__x86_64__)
-#include <immintrin.h>
-#endif
 #include <atomic>
 #include <condition_variable>
 #include <mutex>
@@ -17,6 +14,7 @@
 
 #include "block_hash_core.h"
 #include "block_hash_names.h"
+#include "fetch_expand.h"
 #include "kernels.h"
 
 using namespace npge_b200;
@@ -1037,45 +1035,6 @@ bool fetch_compact_wanted(const npge_anchor_ctx* ctx, uint64_t nf, uint64_t limi
     return nf >= kFetchCompactMin;  // auto: only where PCIe time dominates
 }
 
-// payloads [lo, hi) -> the three fragment arrays (locate() of bucket_kernels.cu).
-// The arrays are written once and not read by this thread again: streaming
-// stores keep them out of the cache and skip the read-for-ownership of every
-// line, which halves the memory traffic of the expansion (it is bandwidth-bound:
-// 13 bytes per fragment over all cores).  lo is a multiple of 8 (kFetchPiece).
-void expand_payloads(const npge_anchor_ctx* ctx, const uint32_t* pay, uint64_t lo, uint64_t hi,
-                     uint32_t* seq, uint32_t* pos, int8_t* ori) {
-    const uint32_t* lut = ctx->h_lut.data();
-    const uint32_t* start = ctx->h_start32.data();  // [S + 1], the last one = all positions
-    const uint32_t* caller = ctx->h_caller.data();
-    const int shift = ctx->lut_shift;
-    uint64_t f = lo;
-#if defined(__x86_64__)
-    for (; f + 8 <= hi; f += 8) {
-        uint64_t oris = 0;
-        for (int j = 0; j < 8; j++) {
-            const uint32_t p = pay[f + j], g = p >> 1;
-            uint32_t s = lut[g >> shift];
-            while (start[s + 1] <= g) s++;
-            _mm_stream_si32(reinterpret_cast<int*>(seq + f + j), int(caller[s]));
-            _mm_stream_si32(reinterpret_cast<int*>(pos + f + j), int(g - start[s]));
-            oris |= uint64_t((p & 1) ? 0x01u : 0xffu) << (8 * j);
-        }
-        _mm_stream_si64(reinterpret_cast<long long*>(ori + f), static_cast<long long>(oris));
-    }
-#endif
-    for (; f < hi; f++) {
-        const uint32_t p = pay[f], g = p >> 1;
-        uint32_t s = lut[g >> shift];
-        while (start[s + 1] <= g) s++;
-        seq[f] = caller[s];
-        pos[f] = g - start[s];
-        ori[f] = (p & 1) ? 1 : -1;
-    }
-#if defined(__x86_64__)
-    _mm_sfence();  // the streaming stores are visible before the piece counts as done
-#endif
-}
-
 int fetch_compact(npge_anchor_ctx* ctx, HostResult* r, uint64_t nf, uint64_t nb) {
     cudaStream_t st = ctx->stream;
     PinnedVector<uint32_t> pay;
@@ -1122,7 +1081,8 @@ int fetch_compact(npge_anchor_ctx* ctx, HostResult* r, uint64_t nf, uint64_t nb)
                 if (abort.load()) return;
                 std::this_thread::yield();
             }
-            expand_payloads(ctx, pay_h, lo, hi, seq, pos, ori);
+            expand_payloads(pay_h, lo, hi, ctx->h_lut.data(), ctx->lut_shift,
+                            ctx->h_start32.data(), ctx->h_caller.data(), seq, pos, ori);
         }
     });
     cudaError_t err = cudaSuccess;
