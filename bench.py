@@ -288,6 +288,22 @@ def run_gpu(args, rank, world, local_rank):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         t_dev = float(t.item())
     parity_stats = runner.finish(stats)
+    # the row next to the path: the reference's block_hash of
+    # every anchor block, on the result that is still resident.  Reported beside
+    # the headline, not part of it; never allowed to break the line.
+    block_hash = None
+    if world == 1 and not args.profile:
+        try:
+            best = None
+            for _ in range(3):
+                _, total = eng.anchor_block_hashes(names, want_hashes=False)
+                ms = eng.block_hashes_ms()
+                best = ms if best is None else min(best, ms)
+            block_hash = {"kernel": "block_hash_kernel", "device_ms": best,
+                          "blocks_per_s": parity_stats["n_blocks_global"] / (best * 1e-3),
+                          "blockset_hash": "%016x" % total}
+        except Exception as exc:  # noqa: BLE001
+            block_hash = {"error": str(exc)[:200]}
     if args.profile:
         if rank == 0:
             emit({"profile_run": True, "steps": args.steps,
@@ -436,6 +452,8 @@ def run_gpu(args, rank, world, local_rank):
         "gpu_launches": int(kern_launches),
         "clocks": clocks,
     }
+    if block_hash is not None:
+        line["block_hash"] = block_hash
     if world == 1 and not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline(args.cpu_scale)
     emit(line)
