@@ -58,7 +58,8 @@ typedef struct npge_anchor_ctx npge_anchor_ctx; /* opaque: device, stream, scrat
 typedef struct {
     int32_t anchor_size;          /* option anchor-size, 1..32 */
     int32_t anchor_similar;       /* option anchor-similar, 0/1 */
-    int64_t max_anchor_fragments; /* option max-anchor-fragments, >= 0 */
+    int64_t max_anchor_fragments; /* option max-anchor-fragments; negative = no limit
+                                     (compared as size_t, AnchorFinder.cpp:361) */
 } npge_anchor_params;
 
 /* Host result. All arrays are owned by the library until
@@ -102,6 +103,11 @@ typedef struct {
 
 int npge_anchor_create(npge_anchor_ctx** ctx, int device);
 void npge_anchor_destroy(npge_anchor_ctx* ctx);
+
+/* Test hook: force the digit plan a much larger job would get (fine_bits =
+ * log2 of the (A, B) bins, first_split = bits of pass A; 0 = automatic), so that
+ * the wide-row kernels are exercised on small inputs.  Results never depend on it. */
+int npge_anchor_debug_plan(npge_anchor_ctx* ctx, int32_t fine_bits, int32_t first_split);
 
 /* Thread-local text of the last error returned to this thread. */
 const char* npge_anchor_last_error(void);

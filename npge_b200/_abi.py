@@ -19,6 +19,7 @@ EXPORTS = [
     "npge_fragment_find", "npge_fragment_find_device", "npge_fragment_result_free",
     "npge_anchor_upload_raw", "npge_anchor_dist_scatter_local",
     "npge_block_hashes", "npge_anchor_block_hashes", "npge_block_hashes_last_ms",
+    "npge_anchor_debug_plan",
 ]
 IPC_BYTES = 128
 

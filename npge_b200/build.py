@@ -6,8 +6,7 @@ import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-SOURCES = ["api.cu", "scan_kernels.cu", "sort_kernels.cu", "group_kernels.cu",
-           "msd_kernels.cu", "bucket_kernels.cu", "fragment_kernels.cu",
+SOURCES = ["api.cu", "scan_kernels.cu", "msd_kernels.cu", "bucket_kernels.cu", "fragment_kernels.cu",
            "ingest_kernels.cu", "block_hash_kernels.cu"]
 HEADERS = ["common.cuh", "kernels.h", "rank.cuh", "block_hash_core.h", "block_hash_names.h", "fetch_expand.h", os.path.join("..", "..", "include",
                                                      "npge_anchor.h")]

@@ -81,13 +81,6 @@ T* ptr(const DeviceBuffer& b) {
     return static_cast<T*>(b.ptr);
 }
 
-int digit_bits_preference() {
-    // experiments only: NPGE_ANCHOR_DIGIT_BITS=8 restores byte digits
-    const char* e = getenv("NPGE_ANCHOR_DIGIT_BITS");
-    int b = e ? atoi(e) : kMaxDigitBits;
-    return b;
-}
-
 // Pinned host memory for the result arrays: device -> host copies run at PCIe
 // speed only into page-locked memory, and cudaHostAlloc is far too slow to call
 // per result, so freed blocks are kept (up to kPoolLimit bytes) and reused.
@@ -193,9 +186,9 @@ int check_params(const npge_anchor_params* p) {
     if (p->anchor_size > NPGE_ANCHOR_MAX_SIZE) {
         return fail(NPGE_ANCHOR_ERR_PARAMS, "anchor-size <= 32 is violated");
     }
-    if (p->max_anchor_fragments < 0) {
-        return fail(NPGE_ANCHOR_ERR_PARAMS, "max-anchor-fragments >= 0 is violated");
-    }
+    // max-anchor-fragments has no rule in the reference: a negative value is
+    // compared as size_t (AnchorFinder.cpp:361) and never truncates.  Here
+    // uint64_t(p->max_anchor_fragments) gives the same "no limit".
     return NPGE_ANCHOR_OK;
 }
 
@@ -207,6 +200,14 @@ extern "C" const char* npge_anchor_last_error(void) {
 
 extern "C" const char* npge_anchor_version(void) {
     return "npge_anchor 0.1 sm_100a";
+}
+
+extern "C" int npge_anchor_debug_plan(npge_anchor_ctx* ctx, int32_t fine_bits,
+                                      int32_t first_split) {
+    if (!ctx) return fail(NPGE_ANCHOR_ERR_PARAMS, "ctx is NULL");
+    ctx->force_f = fine_bits;
+    ctx->force_wa = first_split;
+    return NPGE_ANCHOR_OK;
 }
 
 extern "C" int npge_anchor_create(npge_anchor_ctx** out, int device) {
@@ -227,7 +228,6 @@ extern "C" int npge_anchor_create(npge_anchor_ctx** out, int device) {
     if (!ctx) return fail(NPGE_ANCHOR_ERR_MEMORY, "out of host memory");
     ctx->device = device;
     NPGE_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
-    exp_set_nochain(getenv("NPGE_EXP_NOCHAIN") ? 1 : 0);
     for (auto& ev : ctx->ev) NPGE_CUDA(cudaEventCreate(&ev));
     for (auto& ev : ctx->ev_pass) NPGE_CUDA(cudaEventCreate(&ev));
     *out = ctx;
@@ -239,13 +239,11 @@ extern "C" void npge_anchor_destroy(npge_anchor_ctx* ctx) {
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     DeviceBuffer* all[] = {&ctx->ascii, &ctx->packed, &ctx->nmask, &ctx->seq_start,
-                           &ctx->seq_caller, &ctx->klo[0], &ctx->klo[1],
-                           &ctx->khi[0], &ctx->khi[1], &ctx->pay[0], &ctx->pay[1],
-                           &ctx->hist, &ctx->status, &ctx->status2, &ctx->counters, &ctx->used,
-                           &ctx->found_bits, &ctx->head_idx, &ctx->sel,
+                           &ctx->seq_caller, &ctx->counters, &ctx->used,
+                           &ctx->found_bits, &ctx->sel,
                            &ctx->r_seq, &ctx->r_pos, &ctx->r_ori,
                            &ctx->r_block_off, &ctx->r_block_hash,
-                           &ctx->scan_status, &ctx->summary, &ctx->rows, &ctx->blk,
+                           &ctx->summary, &ctx->rows, &ctx->blk,
                            &ctx->segtab, &ctx->fine_start,
                            &ctx->bstatus, &ctx->units, &ctx->rec[0], &ctx->rec[1], &ctx->rhi[0],
                            &ctx->rhi[1], &ctx->seq_lut, &ctx->g_seq_start, &ctx->g_seq_caller,
@@ -498,6 +496,8 @@ BucketArgs bucket_args(npge_anchor_ctx* ctx, const MsdPlan& plan, const MsdBuffe
     return a;
 }
 
+int fix_cut_resident(npge_anchor_ctx* ctx, uint64_t limit);
+
 int find_device_msd(npge_anchor_ctx* ctx, const npge_anchor_params* p,
                     const uint64_t* used_sorted, uint64_t n_used,
                     npge_anchor_stats* stats) {
@@ -509,7 +509,7 @@ int find_device_msd(npge_anchor_ctx* ctx, const npge_anchor_params* p,
         return fail(NPGE_ANCHOR_ERR_CAPACITY,
                     "more than 2^30-1 windows per device; shard the input");
     }
-    const MsdPlan plan = make_msd_plan(k, max_records);
+    const MsdPlan plan = make_msd_plan(k, max_records, ctx->force_f, ctx->force_wa);
     const uint64_t limit = uint64_t(p->max_anchor_fragments);
     const uint64_t max_frags = std::min<uint64_t>(max_records, limit);
     const size_t bins_a = size_t(1) << plan.capa;
@@ -617,9 +617,9 @@ int find_device_msd(npge_anchor_ctx* ctx, const npge_anchor_params* p,
                     9 * s.n_fragments + 16 * s.n_blocks;
     ctx->total_selected = summary[kSumFragments];
     ctx->plan = plan;
-    ctx->msd = true;
     ctx->have_pay = with_pay;
     ctx->last_params = *p;
+    NPGE_TRY(fix_cut_resident(ctx, limit));
     ctx->have_result = true;
     if (stats) *stats = s;
     return NPGE_ANCHOR_OK;
@@ -647,178 +647,7 @@ extern "C" int npge_anchor_find_device(npge_anchor_ctx* ctx,
     }
     NPGE_CUDA(cudaSetDevice(ctx->device));
     ctx->have_result = false;
-    {
-        const char* path = getenv("NPGE_ANCHOR_PATH");  // experiments: "lsd"
-        if (!path || strcmp(path, "lsd") != 0) {
-            return find_device_msd(ctx, p, used_sorted, n_used, stats);
-        }
-    }
-    ctx->msd = false;
-    ctx->have_pay = false;
-    const int k = p->anchor_size;
-    const SortPlan plan = make_sort_plan(k, digit_bits_preference());
-    const int passes = plan.passes;
-    const bool has_hi = k > 16;
-    const bool similar = p->anchor_similar != 0;
-    const uint64_t np = ctx->n_padded;
-    const uint64_t max_records = ctx->n_positions;  // upper bound on windows
-    if (max_records > kMaxRecords) {
-        return fail(NPGE_ANCHOR_ERR_CAPACITY,
-                    "more than 2^30-1 windows per device; shard the input");
-    }
-    const uint64_t limit = uint64_t(p->max_anchor_fragments);
-    const uint64_t max_frags = std::min<uint64_t>(max_records, limit);
-    const size_t tiles0 = size_t(np / kTile);
-    const size_t summary_words = group_summary_words();
-    const size_t scan_tiles = group_scan_tiles(max_records);
-    for (int b = 0; b < 2; b++) {
-        NPGE_TRY(ensure(ctx->klo[b], max_records * 4));
-        if (has_hi) NPGE_TRY(ensure(ctx->khi[b], max_records * 4));
-        NPGE_TRY(ensure(ctx->pay[b], max_records * 4));
-    }
-    const size_t hist_bytes = size_t(passes) * plan.bins() * 4;
-    const size_t status_bytes = (tiles0 + 1) * plan.bins() * 4;  // one pass
-    NPGE_TRY(ensure(ctx->hist, hist_bytes));
-    NPGE_TRY(ensure(ctx->status, status_bytes));
-    NPGE_TRY(ensure(ctx->status2, status_bytes));
-    NPGE_TRY(ensure(ctx->counters, kCntWords * 4));
-    NPGE_TRY(ensure(ctx->summary, summary_words * 8));
-    NPGE_TRY(ensure(ctx->scan_status, scan_tiles * 8));
-    NPGE_TRY(ensure(ctx->used, n_used * 8));
-    NPGE_TRY(ensure(ctx->r_seq, max_frags * 4));
-    NPGE_TRY(ensure(ctx->r_pos, max_frags * 4));
-    NPGE_TRY(ensure(ctx->r_ori, max_frags));
-    NPGE_TRY(ensure(ctx->r_block_off, (max_frags / 2 + 2) * 8));
-    NPGE_TRY(ensure(ctx->r_block_hash, (max_frags / 2 + 2) * 8));
-    if (similar) {
-        NPGE_TRY(ensure(ctx->found_bits, np / 8 + 256));
-        NPGE_TRY(ensure(ctx->sel, max_records));
-    }
-    cudaStream_t st = ctx->stream;
-    uint32_t launches = 0;
-    if (n_used) {
-        NPGE_CUDA(cudaMemcpyAsync(ctx->used.ptr, used_sorted, n_used * 8,
-                                  cudaMemcpyHostToDevice, st));
-    }
-    NPGE_CUDA(cudaEventRecord(ctx->ev[0], st));
-    NPGE_CUDA(cudaMemsetAsync(ctx->hist.ptr, 0, hist_bytes, st));
-    // look-back rows of pass 0; every pass clears the rows of the next one
-    NPGE_CUDA(cudaMemsetAsync(ctx->status.ptr, 0, status_bytes, st));
-    NPGE_CUDA(cudaMemsetAsync(ctx->counters.ptr, 0, kCntWords * 4, st));
-    NPGE_CUDA(cudaMemsetAsync(ctx->summary.ptr, 0, summary_words * 8, st));
-    NPGE_CUDA(cudaMemsetAsync(ctx->scan_status.ptr, 0, scan_tiles * 8, st));
-    if (similar) {
-        NPGE_CUDA(cudaMemsetAsync(ctx->found_bits.ptr, 0, np / 8 + 256, st));
-        NPGE_CUDA(cudaMemsetAsync(ctx->sel.ptr, 0, std::max<uint64_t>(max_records, 1), st));
-    }
-    int final_buf = 0;
-    if (np) {
-        int n_sms = 148;
-        cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, ctx->device);
-        uint32_t* hist = ptr<uint32_t>(ctx->hist);
-        uint32_t* counters = ptr<uint32_t>(ctx->counters);
-        uint32_t* status[2] = {ptr<uint32_t>(ctx->status), ptr<uint32_t>(ctx->status2)};
-        launch_hist(plan, ptr<uint32_t>(ctx->packed), ptr<uint32_t>(ctx->nmask), np,
-                    k, hist, n_sms, st);
-        launch_scan_hist(plan, hist, counters, st);
-        launches += 2;
-        NPGE_CUDA(cudaEventRecord(ctx->ev[1], st));
-        NPGE_CUDA(cudaEventRecord(ctx->ev_pass[0], st));
-        launch_sort_pass0(plan, ptr<uint32_t>(ctx->packed),
-                          ptr<uint32_t>(ctx->nmask), np, k, hist, status[0],
-                          passes > 1 ? status[1] : nullptr, counters,
-                          ptr<uint32_t>(ctx->klo[0]), ptr<uint32_t>(ctx->khi[0]),
-                          ptr<uint32_t>(ctx->pay[0]), st);
-        launches++;
-        NPGE_CUDA(cudaEventRecord(ctx->ev_pass[1], st));
-        for (int pass = 1; pass < passes; pass++) {
-            int in = (pass - 1) & 1, out = pass & 1;
-            launch_sort_pass(plan, pass, k, max_records, ptr<uint32_t>(ctx->klo[in]),
-                             ptr<uint32_t>(ctx->khi[in]), ptr<uint32_t>(ctx->pay[in]),
-                             hist, status[pass & 1],
-                             pass + 1 < passes ? status[(pass + 1) & 1] : nullptr,
-                             counters, ptr<uint32_t>(ctx->klo[out]),
-                             ptr<uint32_t>(ctx->khi[out]), ptr<uint32_t>(ctx->pay[out]),
-                             st);
-            launches++;
-            NPGE_CUDA(cudaEventRecord(ctx->ev_pass[pass + 1], st));
-        }
-        final_buf = (passes - 1) & 1;
-    } else {
-        NPGE_CUDA(cudaEventRecord(ctx->ev[1], st));
-    }
-    NPGE_CUDA(cudaEventRecord(ctx->ev[2], st));
-    GroupArgs a = {};
-    a.klo = ptr<uint32_t>(ctx->klo[final_buf]);
-    a.khi = has_hi ? ptr<uint32_t>(ctx->khi[final_buf]) : nullptr;
-    a.pay = ptr<uint32_t>(ctx->pay[final_buf]);
-    a.max_records = np ? max_records : 0;
-    a.counters = ptr<uint32_t>(ctx->counters);
-    a.used = ptr<uint64_t>(ctx->used);
-    a.n_used = n_used;
-    a.seq_start = ptr<uint64_t>(ctx->seq_start);
-    a.seq_caller = ptr<uint32_t>(ctx->seq_caller);
-    a.n_seqs = uint32_t(ctx->seqs.size());
-    a.max_fragments = limit;
-    a.found_bits = ptr<uint32_t>(ctx->found_bits);
-    a.head_idx = nullptr;
-    a.sel = ptr<uint8_t>(ctx->sel);
-    a.r_seq = ptr<uint32_t>(ctx->r_seq);
-    a.r_pos = ptr<uint32_t>(ctx->r_pos);
-    a.r_ori = ptr<int8_t>(ctx->r_ori);
-    a.r_block_off = ptr<uint64_t>(ctx->r_block_off);
-    a.r_block_hash = ptr<uint64_t>(ctx->r_block_hash);
-    a.scan_status = ptr<uint64_t>(ctx->scan_status);
-    a.tickets = ptr<uint32_t>(ctx->counters) + kCntScanTicket;
-    a.cut_index = ptr<uint32_t>(ctx->counters) + kCntCutIndex;
-    a.summary = ptr<uint64_t>(ctx->summary);
-    if (similar) launch_similar(a, np, st, &launches);
-    launch_group_emit(a, similar, st);
-    launches += a.max_records ? 2 : 1;
-    NPGE_CUDA(cudaGetLastError());
-    NPGE_CUDA(cudaEventRecord(ctx->ev[3], st));
-    uint64_t summary[kSumWords];
-    uint32_t counters_h[kCntWords];
-    NPGE_CUDA(cudaMemcpyAsync(summary, ctx->summary.ptr, sizeof(summary),
-                              cudaMemcpyDeviceToHost, st));
-    NPGE_CUDA(cudaMemcpyAsync(counters_h, ctx->counters.ptr, sizeof(counters_h),
-                              cudaMemcpyDeviceToHost, st));
-    NPGE_CUDA(cudaStreamSynchronize(st));
-    npge_anchor_stats& s = ctx->stats;
-    memset(&s, 0, sizeof(s));
-    s.n_positions = ctx->n_bases;
-    s.n_windows = counters_h[kCntValid];
-    s.n_fragments = summary[kSumEmitted];
-    s.n_blocks = summary[kSumBlocksEmitted];
-    s.digest[0] = summary[kSumDigest0];
-    s.digest[1] = summary[kSumDigest1];
-    s.radix_passes = uint32_t(passes);
-    s.gpu_launches = launches;
-    cudaEventElapsedTime(&s.ms_hist, ctx->ev[0], ctx->ev[1]);
-    cudaEventElapsedTime(&s.ms_sort, ctx->ev[1], ctx->ev[2]);
-    cudaEventElapsedTime(&s.ms_group, ctx->ev[2], ctx->ev[3]);
-    cudaEventElapsedTime(&s.ms_total, ctx->ev[0], ctx->ev[3]);
-    for (int pass = 0; np && pass < passes; pass++) {
-        cudaEventElapsedTime(&s.ms_pass[pass], ctx->ev_pass[pass], ctx->ev_pass[pass + 1]);
-    }
-    // SURVEY 8d model: N * (0.375 + 12 + 8 + 24 P(k) + 12) + 9 F + 16 B with
-    // P(k) = ceil(2k / 8) byte-digit passes, whatever this build really runs
-    const int model_passes = (2 * k + 7) / 8;
-    s.bytes_algorithmic = uint64_t(double(ctx->n_bases) * (32.375 + 24.0 * model_passes)) +
-                          9 * s.n_fragments + 16 * s.n_blocks;
-    // compulsory traffic of the passes this build runs: genome read twice (hist,
-    // pass 0), records written once per pass and read once per later pass and
-    // by the grouping, results written
-    const double rec = has_hi ? 12.0 : 8.0;
-    s.bytes_moved = uint64_t(double(ctx->n_bases) * 0.75 +
-                             double(s.n_windows) * rec * (2.0 * passes)) +
-                    9 * s.n_fragments + 16 * s.n_blocks;
-    ctx->total_selected = summary[kSumFragments];
-    ctx->result_buf = final_buf;
-    ctx->last_params = *p;
-    ctx->have_result = true;
-    if (stats) *stats = s;
-    return NPGE_ANCHOR_OK;
+    return find_device_msd(ctx, p, used_sorted, n_used, stats);
 }
 
 extern "C" int npge_anchor_get_stats(npge_anchor_ctx* ctx,
@@ -832,58 +661,30 @@ extern "C" int npge_anchor_get_stats(npge_anchor_ctx* ctx,
 // ---- fetch: device result -> host arrays ------------------------------------------
 namespace {
 
-int read_key(npge_anchor_ctx* ctx, uint64_t i, uint64_t* key) {
-    uint32_t lo = 0, hi = 0;
-    const int b = ctx->result_buf;
-    NPGE_CUDA(cudaMemcpyAsync(&lo, ptr<uint32_t>(ctx->klo[b]) + i, 4,
-                              cudaMemcpyDeviceToHost, ctx->stream));
-    if (ctx->last_params.anchor_size > 16) {
-        NPGE_CUDA(cudaMemcpyAsync(&hi, ptr<uint32_t>(ctx->khi[b]) + i, 4,
-                                  cudaMemcpyDeviceToHost, ctx->stream));
-    }
-    NPGE_CUDA(cudaStreamSynchronize(ctx->stream));
-    *key = (uint64_t(hi) << 32) | lo;
-    return NPGE_ANCHOR_OK;
-}
-
-// Members of the cut group in the reference's order (caller sequence index,
-// pos') -> the first `keep` of them replace the device's (scan order) choice.
-void rebuild_cut_members(npge_anchor_ctx* ctx, HostResult& r,
-                         const std::vector<uint32_t>& pay, uint64_t first,
-                         uint64_t keep) {
-    struct Member { uint32_t seq; uint64_t pos2; uint32_t pos; int8_t ori; };
-    std::vector<Member> members;
-    members.reserve(pay.size());
-    for (uint32_t pw : pay) {
-        uint64_t g = pw >> 1;
-        size_t a = 0, b = ctx->gseqs.size();
-        while (b - a > 1) {
-            size_t mid = (a + b) / 2;
-            if (ctx->gseqs[mid].start <= g) a = mid; else b = mid;
-        }
-        const SeqEntry& e = ctx->gseqs[a];
-        uint32_t pos = uint32_t(g - e.start);
-        bool direct = pw & 1;
-        members.push_back({e.caller_index, direct ? pos : pos + e.size, pos,
-                           int8_t(direct ? 1 : -1)});
-    }
-    std::sort(members.begin(), members.end(), [](const Member& x, const Member& y) {
-        return x.seq != y.seq ? x.seq < y.seq : x.pos2 < y.pos2;
-    });
-    for (uint64_t j = 0; j < keep; j++) {
-        r.frag_seq[first + j] = members[j].seq;
-        r.frag_min_pos[first + j] = members[j].pos;
-        r.frag_ori[first + j] = members[j].ori;
-    }
-}
-
-// MSD path: the unit holding the cut record was written back sorted; its
-// bounds and the cut record's index are in the counters.
-int fix_cut_group_msd(npge_anchor_ctx* ctx, HostResult& r, uint64_t limit) {
+// The reference cuts the list sorted by (hash, Sequence*, pos') at
+// max-anchor-fragments (AnchorFinder.cpp:361-363), pos' = pos + size for the
+// reverse strand (:295-301).  The device order inside a group is the scan order,
+// so only the group the cut falls into can differ.  Right after the emit kernels
+// (find_device / dist_emit have synchronised anyway) the kept members of that one
+// group are rebuilt in the reference's order and patched into the resident result,
+// a group cut down to one member is dropped (a singleton of the reference's list:
+// no block, but its hash still counts as used, :385), and the digest is corrected:
+// stats, resident arrays and npge_anchor_fetch all describe the same answer.
+// The unit holding the cut record was written back sorted; its bounds and the cut
+// record's index are in the counters.
+int fix_cut_resident(npge_anchor_ctx* ctx, uint64_t limit) {
+    ctx->lone_tail = false;
+    npge_anchor_stats& st = ctx->stats;
+    if (!(ctx->total_selected > limit && limit > 0) || st.n_blocks == 0) return NPGE_ANCHOR_OK;
+    cudaStream_t s = ctx->stream;
     uint32_t c[kCntWords];
-    NPGE_CUDA(cudaMemcpyAsync(c, ctx->counters.ptr, sizeof(c), cudaMemcpyDeviceToHost,
-                              ctx->stream));
-    NPGE_CUDA(cudaStreamSynchronize(ctx->stream));
+    uint64_t tail[2] = {0, 0};  // offset and hash of the last block
+    NPGE_CUDA(cudaMemcpyAsync(c, ctx->counters.ptr, sizeof(c), cudaMemcpyDeviceToHost, s));
+    NPGE_CUDA(cudaMemcpyAsync(&tail[0], ptr<uint64_t>(ctx->r_block_off) + st.n_blocks - 1, 8,
+                              cudaMemcpyDeviceToHost, s));
+    NPGE_CUDA(cudaMemcpyAsync(&tail[1], ptr<uint64_t>(ctx->r_block_hash) + st.n_blocks - 1, 8,
+                              cudaMemcpyDeviceToHost, s));
+    NPGE_CUDA(cudaStreamSynchronize(s));
     const uint32_t cut = c[kCntCutIndex], cs = c[kCntCutStart], cn = c[kCntCutSize];
     if (cn == 0 || cut < cs || cut >= cs + cn) {
         return fail(NPGE_ANCHOR_ERR_CUDA, "internal: cut record outside its unit");
@@ -891,12 +692,12 @@ int fix_cut_group_msd(npge_anchor_ctx* ctx, HostResult& r, uint64_t limit) {
     std::vector<uint64_t> rec(cn);
     std::vector<uint32_t> hi(ctx->plan.wide ? cn : 0);
     NPGE_CUDA(cudaMemcpyAsync(rec.data(), ptr<uint64_t>(ctx->rec[1]) + cs, size_t(cn) * 8,
-                              cudaMemcpyDeviceToHost, ctx->stream));
+                              cudaMemcpyDeviceToHost, s));
     if (ctx->plan.wide) {
-        NPGE_CUDA(cudaMemcpyAsync(hi.data(), ptr<uint32_t>(ctx->rhi[1]) + cs,
-                                  size_t(cn) * 4, cudaMemcpyDeviceToHost, ctx->stream));
+        NPGE_CUDA(cudaMemcpyAsync(hi.data(), ptr<uint32_t>(ctx->rhi[1]) + cs, size_t(cn) * 4,
+                                  cudaMemcpyDeviceToHost, s));
     }
-    NPGE_CUDA(cudaStreamSynchronize(ctx->stream));
+    NPGE_CUDA(cudaStreamSynchronize(s));
     auto K = [&](uint32_t i) {
         return (uint64_t(ctx->plan.wide ? hi[i] : 0u) << 32) | (rec[i] >> 32);
     };
@@ -904,60 +705,64 @@ int fix_cut_group_msd(npge_anchor_ctx* ctx, HostResult& r, uint64_t limit) {
     uint32_t gs = ci, ge = ci + 1;
     while (gs > 0 && K(gs - 1) == K(ci)) gs--;
     while (ge < cn && K(ge) == K(ci)) ge++;
-    if (r.block_hash.empty()) {
+    const uint64_t first = tail[0], key = tail[1];
+    if (first >= limit || ci - gs + 1 != limit - first) {
         return fail(NPGE_ANCHOR_ERR_CUDA, "internal: cut group is not the last block");
     }
-    const uint64_t first = r.block_offsets[r.block_hash.size() - 1];
     const uint64_t keep = limit - first;
-    if (ge - gs > keep) {
-        std::vector<uint32_t> pay(ge - gs);
-        for (uint32_t i = gs; i < ge; i++) pay[i - gs] = uint32_t(rec[i]);
-        rebuild_cut_members(ctx, r, pay, first, keep);
+    struct Member { uint32_t seq; uint64_t pos2; uint32_t pos; int8_t ori; };
+    auto member = [&](uint32_t i) {
+        const uint32_t pw = uint32_t(rec[i]);
+        const uint64_t g = pw >> 1;
+        size_t a = 0, b = ctx->gseqs.size();
+        while (b - a > 1) {
+            size_t mid = (a + b) / 2;
+            if (ctx->gseqs[mid].start <= g) a = mid; else b = mid;
+        }
+        const SeqEntry& e = ctx->gseqs[a];
+        const uint32_t pos = uint32_t(g - e.start);
+        const bool direct = pw & 1;
+        return Member{e.caller_index, direct ? pos : pos + e.size, pos, int8_t(direct ? 1 : -1)};
+    };
+    auto term = [&](const Member& m, uint64_t& d0, uint64_t& d1, bool add) {
+        const uint64_t t = (uint64_t(m.seq) << 33) | (uint64_t(m.pos) << 1) | (m.ori == 1 ? 1 : 0);
+        uint64_t x, y;
+        digest_terms(t, key, x, y);
+        d0 += add ? x : 0 - x;
+        d1 += add ? y : 0 - y;
+    };
+    std::vector<Member> members;
+    members.reserve(ge - gs);
+    for (uint32_t i = gs; i < ge; i++) members.push_back(member(i));
+    uint64_t d0 = st.digest[0], d1 = st.digest[1];
+    for (uint64_t j = 0; j < keep; j++) term(members[j], d0, d1, false);  // the device's choice
+    std::sort(members.begin(), members.end(), [](const Member& x, const Member& y) {
+        return x.seq != y.seq ? x.seq < y.seq : x.pos2 < y.pos2;
+    });
+    if (keep == 1) {
+        ctx->lone_tail = true;
+        ctx->lone_hash = key;
+        st.n_blocks -= 1;      // r_block_off[n_blocks] == first == the new fragment count
+        st.n_fragments -= 1;
+    } else {
+        std::vector<uint32_t> q(keep), o(keep);
+        std::vector<int8_t> r(keep);
+        for (uint64_t j = 0; j < keep; j++) {
+            term(members[j], d0, d1, true);
+            q[j] = members[j].seq;
+            o[j] = members[j].pos;
+            r[j] = members[j].ori;
+        }
+        NPGE_CUDA(cudaMemcpyAsync(ptr<uint32_t>(ctx->r_seq) + first, q.data(), keep * 4,
+                                  cudaMemcpyHostToDevice, s));
+        NPGE_CUDA(cudaMemcpyAsync(ptr<uint32_t>(ctx->r_pos) + first, o.data(), keep * 4,
+                                  cudaMemcpyHostToDevice, s));
+        NPGE_CUDA(cudaMemcpyAsync(ptr<int8_t>(ctx->r_ori) + first, r.data(), keep,
+                                  cudaMemcpyHostToDevice, s));
+        NPGE_CUDA(cudaStreamSynchronize(s));
     }
-    return NPGE_ANCHOR_OK;
-}
-
-// The reference cuts the list sorted by (hash, Sequence*, pos') at
-// max-anchor-fragments (AnchorFinder.cpp:361-363), pos' = pos + size for the
-// reverse strand (:295-301).  The device order inside a group is (seq, pos), so
-// only the group the cut falls into can differ: rebuild its kept members here.
-int fix_cut_group(npge_anchor_ctx* ctx, HostResult& r, uint64_t limit) {
-    uint32_t cut = 0;
-    NPGE_CUDA(cudaMemcpyAsync(&cut, ptr<uint32_t>(ctx->counters) + kCntCutIndex, 4,
-                              cudaMemcpyDeviceToHost, ctx->stream));
-    NPGE_CUDA(cudaStreamSynchronize(ctx->stream));
-    uint64_t key = 0;
-    NPGE_TRY(read_key(ctx, cut, &key));
-    const uint64_t n = ctx->stats.n_windows;
-    // group bounds [gs, ge) in the sorted records, by binary search
-    uint64_t lo = 0, hi = cut;
-    while (lo < hi) {
-        uint64_t mid = (lo + hi) / 2, km = 0;
-        NPGE_TRY(read_key(ctx, mid, &km));
-        if (km < key) lo = mid + 1; else hi = mid;
-    }
-    const uint64_t gs = lo;
-    lo = cut + 1;
-    hi = n;
-    while (lo < hi) {
-        uint64_t mid = (lo + hi) / 2, km = 0;
-        NPGE_TRY(read_key(ctx, mid, &km));
-        if (km <= key) lo = mid + 1; else hi = mid;
-    }
-    const uint64_t ge = lo;
-    if (r.block_hash.empty() || r.block_hash.back() != key) {
-        return fail(NPGE_ANCHOR_ERR_CUDA, "internal: cut group is not the last block");
-    }
-    const uint64_t first = r.block_offsets[r.block_hash.size() - 1];
-    const uint64_t keep = limit - first;
-    if (ge - gs > keep) {
-        std::vector<uint32_t> pay(ge - gs);
-        NPGE_CUDA(cudaMemcpyAsync(pay.data(),
-                                  ptr<uint32_t>(ctx->pay[ctx->result_buf]) + gs,
-                                  (ge - gs) * 4, cudaMemcpyDeviceToHost, ctx->stream));
-        NPGE_CUDA(cudaStreamSynchronize(ctx->stream));
-        rebuild_cut_members(ctx, r, pay, first, keep);
-    }
+    st.digest[0] = d0;
+    st.digest[1] = d1;
     return NPGE_ANCHOR_OK;
 }
 
@@ -1027,8 +832,8 @@ constexpr uint64_t kFetchChunk = uint64_t(1) << 22;       // fragments per PCIe 
 constexpr uint64_t kFetchPiece = uint64_t(1) << 16;       // fragments per unit of host work
 
 bool fetch_compact_wanted(const npge_anchor_ctx* ctx, uint64_t nf, uint64_t limit) {
-    if (!ctx->have_pay || !ctx->msd || ctx->dist || nf == 0) return false;
-    if (ctx->total_selected > limit && limit > 0) return false;  // cut group fix-up: plain path
+    if (!ctx->have_pay || ctx->dist || nf == 0) return false;
+    if (ctx->total_selected > limit && limit > 0) return false;  // patched cut group: plain path
     const int mode = fetch_mode();
     if (mode == kFetchPlain) return false;
     if (mode == kFetchCompact) return true;
@@ -1148,41 +953,8 @@ extern "C" int npge_anchor_fetch(npge_anchor_ctx* ctx, npge_anchor_result* out) 
         }
         out->digest[0] = ctx->stats.digest[0];
         out->digest[1] = ctx->stats.digest[1];
-        bool lone_tail = false;
-        uint64_t lone_hash = 0;
-        if (ctx->total_selected > limit && limit > 0) {
-            if (ctx->msd) {
-                NPGE_TRY(fix_cut_group_msd(ctx, *r, limit));
-            } else {
-                NPGE_TRY(fix_cut_group(ctx, *r, limit));
-            }
-            // a group cut down to one member is a singleton in the reference's
-            // list: no block, but its hash is still recorded as used (:385)
-            if (r->block_offsets[nb] - r->block_offsets[nb - 1] == 1) {
-                lone_tail = true;
-                lone_hash = r->block_hash[nb - 1];
-                r->block_hash.pop_back();
-                r->block_offsets.pop_back();
-                r->frag_seq.pop_back();
-                r->frag_min_pos.pop_back();
-                r->frag_ori.pop_back();
-            }
-            uint64_t d0 = 0, d1 = 0;
-            for (size_t b = 0; b < r->block_hash.size(); b++) {
-                uint64_t h = r->block_hash[b];
-                for (uint64_t f = r->block_offsets[b]; f < r->block_offsets[b + 1]; f++) {
-                    uint64_t t = (uint64_t(r->frag_seq[f]) << 33) |
-                                 (uint64_t(r->frag_min_pos[f]) << 1) |
-                                 (r->frag_ori[f] == 1 ? 1 : 0);
-                    uint64_t x, y;
-                    digest_terms(t, h, x, y);
-                    d0 += x;
-                    d1 += y;
-                }
-            }
-            out->digest[0] = d0;
-            out->digest[1] = d1;
-        }
+        const bool lone_tail = ctx->lone_tail;
+        const uint64_t lone_hash = ctx->lone_hash;
         // used_hashes.push_back for every distinct hash of the list but the
         // first (AnchorFinder.cpp:366-387)
         // (several GPUs: every hash of this rank's range; the caller drops the
@@ -1345,7 +1117,8 @@ int dist_count_a(npge_anchor_ctx* ctx, const npge_anchor_params* p, bool scatter
     NPGE_CUDA(cudaSetDevice(ctx->device));
     ctx->have_result = false;
     ctx->a_counted = false;
-    const MsdPlan plan = make_msd_plan(p->anchor_size, ctx->g_positions);
+    const MsdPlan plan = make_msd_plan(p->anchor_size, ctx->g_positions, ctx->force_f,
+                                       ctx->force_wa);
     const uint32_t bins_a = 1u << plan.capa;
     if (hist_cap < bins_a) return fail(NPGE_ANCHOR_ERR_PARAMS, "hist_out too small");
     *n_bins = bins_a;
@@ -1821,10 +1594,10 @@ extern "C" int npge_anchor_dist_emit(npge_anchor_ctx* ctx, const npge_anchor_par
                              double(max_records) * rec * (similar ? 6.0 : 4.0)) +
                     9 * s.n_fragments + 16 * s.n_blocks;
     ctx->total_selected = summary[kSumFragments];
-    ctx->msd = true;
     ctx->have_pay = false;
     ctx->last_params = *p;
     ctx->last_params.max_anchor_fragments = int64_t(std::min<uint64_t>(local_limit, uint64_t(INT64_MAX)));
+    NPGE_TRY(fix_cut_resident(ctx, local_limit));
     ctx->have_result = true;
     if (stats) *stats = s;
     return NPGE_ANCHOR_OK;
@@ -2149,12 +1922,6 @@ extern "C" int npge_anchor_block_hashes(npge_anchor_ctx* ctx, const char* const*
     if (!ctx) return fail(NPGE_ANCHOR_ERR_PARAMS, "ctx is NULL");
     if (!ctx->have_result) {
         return fail(NPGE_ANCHOR_ERR_STATE, "npge_anchor_find_device has not run");
-    }
-    const uint64_t limit = uint64_t(ctx->last_params.max_anchor_fragments);
-    if (ctx->total_selected > limit && limit > 0) {
-        return fail(NPGE_ANCHOR_ERR_STATE,
-                    "max-anchor-fragments cut the list: the last block is completed by "
-                    "npge_anchor_fetch; hash the fetched arrays with npge_block_hashes");
     }
     const uint32_t need = ctx->dist ? uint32_t(ctx->gseqs.size()) : ctx->n_caller_seqs;
     if (n_seqs < need) {

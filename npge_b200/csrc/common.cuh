@@ -27,20 +27,8 @@ namespace npge_b200 {
 constexpr int kSortThreads = 512;
 constexpr int kSortItems = 8;
 constexpr int kTile = kSortThreads * kSortItems;  // 4096 records / positions
-constexpr int kMaxDigitBits = 10;                 // widest radix digit
-constexpr int kMaxPasses = 16;                    // ceil(64 / 4)
-
-// Radix plan for 2k-bit keys: `passes` digits of `width` bits each (the last
-// may be narrower); histograms and look-back rows hold 1 << capbits bins.
-struct SortPlan {
-    int passes = 0, width = 0, capbits = 0;
-    __host__ __device__ int bins() const { return 1 << capbits; }
-    __host__ __device__ uint32_t mask(int pass, int k) const {
-        int left = 2 * k - pass * width;
-        int w = left < width ? left : width;
-        return (1u << w) - 1;
-    }
-};
+constexpr int kMaxDigitBits = 10;                 // widest partition digit
+constexpr int kMaxPasses = 16;                    // event slots per find
 
 // Plan of the MSD partition + shared-memory bucket sort for 2k-bit keys
 // (msd_kernels.cu): pass A takes the top wa bits, pass B the next wb, the bucket
@@ -58,11 +46,7 @@ constexpr int kWindow = kBucketCap / 2;  // bins starting in one window = one un
 // positions are padded so every tile can bulk-copy tile + 16 B of halo
 constexpr uint64_t kPosAlign = 4096;
 
-// look-back status word: [31:30] flag, [29:0] value
-constexpr uint32_t kFlagAggregate = 1u << 30;
-constexpr uint32_t kFlagInclusive = 2u << 30;
-constexpr uint32_t kValueMask = (1u << 30) - 1;
-constexpr uint64_t kMaxRecords = kValueMask;         // per sort
+constexpr uint64_t kMaxRecords = (1u << 30) - 1;      // per sort
 constexpr uint64_t kMaxPositions = (1ull << 31) - 1; // payload = gpos << 1 | ori
 
 __host__ __device__ inline uint64_t splitmix64(uint64_t x) {
@@ -146,15 +130,14 @@ struct npge_anchor_ctx {
     npge_b200::DeviceBuffer ascii, packed, nmask, seq_start, seq_caller;
 
     // sort / grouping scratch
-    npge_b200::DeviceBuffer klo[2], khi[2], pay[2];
-    npge_b200::DeviceBuffer hist, status, status2, counters, used;
-    npge_b200::DeviceBuffer found_bits, head_idx, sel;
+    npge_b200::DeviceBuffer counters, used;
+    npge_b200::DeviceBuffer found_bits, sel;
     // MSD partition + bucket sort (msd_kernels.cu, bucket_kernels.cu)
     npge_b200::DeviceBuffer rows, blk, segtab, fine_start, bstatus, units;
     npge_b200::DeviceBuffer rec[2], rhi[2], seq_lut;
     int lut_shift = 12;
     npge_b200::MsdPlan plan;
-    bool msd = true;          // which path produced the result
+    int force_f = 0, force_wa = 0;  // npge_anchor_debug_plan (tests)
     // several GPUs (npge_anchor_dist_*): job-wide sequence table and exchange
     bool dist = false;
     std::vector<npge_b200::SeqEntry> gseqs;  // ALL sequences, job-wide scan order
@@ -183,7 +166,7 @@ struct npge_anchor_ctx {
     float dist_ms[8] = {};
     // device result
     npge_b200::DeviceBuffer r_seq, r_pos, r_ori, r_block_off, r_block_hash;
-    npge_b200::DeviceBuffer scan_status, summary;
+    npge_b200::DeviceBuffer summary;
     // compact fetch (api.cu: fetch_compact): the emit kernel also leaves the
     // 4-byte payload (position << 1 | strand) of every fragment; the host turns it
     // into (sequence, position, strand) while the next chunk crosses PCIe
@@ -193,8 +176,9 @@ struct npge_anchor_ctx {
     std::vector<cudaEvent_t> fetch_ev;
 
     bool have_result = false;
-    int result_buf = 0;       // which of the double buffers holds sorted records
     npge_anchor_params last_params = {0, 0, 0};
     npge_anchor_stats stats = {};
     uint64_t total_selected = 0;  // before truncation
+    bool lone_tail = false;       // the cut left one member of a group: dropped,
+    uint64_t lone_hash = 0;       // but its hash is appended to new_used
 };

@@ -9,8 +9,6 @@ namespace npge_b200 {
 enum {
     kCntValid = 0,      // number of N-free windows (records)
     kCntBadInput = 1,   // bytes outside ATGCN seen by pack
-    kCntTicket0 = 2,    // tile tickets, one per radix pass (kMaxPasses slots)
-    kCntScanTicket = 18,  // tickets of the grouping scans (4 slots)
     kCntCutIndex = 22,  // sorted index of the record with selected-rank M-1
     kCntWindows = 23,   // bucket-sort windows of the last partition
     kCntCutStart = 24,  // unit holding the cut record: first record, size
@@ -31,34 +29,6 @@ enum {
 
 void launch_pack(const uint8_t* ascii, uint32_t* packed, uint32_t* nmask,
                  uint64_t n_padded, uint32_t* counters, cudaStream_t s);
-
-SortPlan make_sort_plan(int k, int max_digit_bits);
-void exp_set_nochain(int v);
-
-// hist[passes][plan.bins()]: digit histograms of every valid canonical k-mer
-void launch_hist(const SortPlan& plan, const uint32_t* packed,
-                 const uint32_t* nmask, uint64_t n_padded, int k, uint32_t* hist,
-                 int n_sms, cudaStream_t s);
-
-// counts -> exclusive bases in place; counters[kCntValid] = n
-void launch_scan_hist(const SortPlan& plan, uint32_t* hist, uint32_t* counters,
-                      cudaStream_t s);
-
-// pass 0: generate keys from the packed genome and scatter by digit 0
-void launch_sort_pass0(const SortPlan& plan, const uint32_t* packed,
-                       const uint32_t* nmask, uint64_t n_padded, int k,
-                       const uint32_t* hist_base, uint32_t* status,
-                       uint32_t* status_next, uint32_t* counters,
-                       uint32_t* klo_out, uint32_t* khi_out, uint32_t* pay_out,
-                       cudaStream_t s);
-
-// pass p >= 1: scatter records by digit p (bits [p*width, (p+1)*width) of the key)
-void launch_sort_pass(const SortPlan& plan, int pass, int k, uint64_t max_records,
-                      const uint32_t* klo_in, const uint32_t* khi_in,
-                      const uint32_t* pay_in, const uint32_t* hist_base,
-                      uint32_t* status, uint32_t* status_next, uint32_t* counters,
-                      uint32_t* klo_out, uint32_t* khi_out, uint32_t* pay_out,
-                      cudaStream_t s);
 
 // ---- MSD partition + bucket sort (msd_kernels.cu, bucket_kernels.cu) -----------
 // Segments of pass B: segment s holds records [seg_begin[s], seg_end[s]) of the
@@ -97,7 +67,8 @@ struct MsdBuffers {
     uint32_t* hi[2];       // key bits [32, rem) when plan.wide
 };
 
-MsdPlan make_msd_plan(int k, uint64_t n_positions);
+// force_f / force_wa > 0 override the fine bits and the first split (tests)
+MsdPlan make_msd_plan(int k, uint64_t n_positions, int force_f = 0, int force_wa = 0);
 size_t msd_rows_needed(const MsdPlan& plan, uint64_t n_padded, uint64_t max_records,
                        uint32_t max_seg);
 size_t msd_blk_needed(const MsdPlan& plan, uint64_t n_padded, uint64_t max_records,
@@ -223,43 +194,5 @@ void launch_block_hash_cuts(const uint64_t* block_off, uint64_t n_blocks, uint64
                             uint32_t n_cuts, uint64_t* cut_block, uint64_t* cut_frag,
                             cudaStream_t s);
 void launch_block_hash(const BlockHashArgs& a, cudaStream_t s);
-
-struct GroupArgs {
-    const uint32_t* klo;
-    const uint32_t* khi;   // nullptr when k <= 16
-    const uint32_t* pay;
-    uint64_t max_records;  // upper bound used for the grid; real n on device
-    const uint32_t* counters;
-    const uint64_t* used;
-    uint64_t n_used;
-    const uint64_t* seq_start;    // [S+1] global start of each scan-order seq
-    const uint32_t* seq_caller;   // [S] caller index
-    uint32_t n_seqs;
-    uint64_t max_fragments;       // truncation M
-    // anchor-similar scratch
-    uint32_t* found_bits;         // 1 bit per global position
-    uint32_t* head_idx;           // per record: index of its group's first record
-    uint8_t* sel;                 // per record index: group selected (at head)
-    // outputs
-    uint32_t* r_seq;
-    uint32_t* r_pos;
-    int8_t* r_ori;
-    uint64_t* r_block_off;
-    uint64_t* r_block_hash;
-    uint64_t* scan_status;
-    uint32_t* tickets;            // counters + kCntScanTicket
-    uint32_t* cut_index;          // counters + kCntCutIndex
-    uint64_t* summary;
-};
-
-// anchor-similar: found bits, group heads, candidate -> group selection
-void launch_similar(const GroupArgs& a, uint64_t n_padded, cudaStream_t s,
-                    uint32_t* launches);
-// run-length grouping + compaction into the flat result arrays
-void launch_group_emit(const GroupArgs& a, bool similar, cudaStream_t s);
-
-// sizes of the grouping scratch (u64 words / tiles) for the host side
-size_t group_summary_words();
-size_t group_scan_tiles(uint64_t max_records);
 
 }  // namespace npge_b200

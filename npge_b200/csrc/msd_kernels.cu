@@ -18,23 +18,18 @@
 //
 // Replaces std::sort of FoundFragments (src/algo/AnchorFinder.cpp:234-238,358;
 // src/util/SortedVector.hpp:47-49) together with bucket_kernels.cu.
-#include <cstdlib>
-
 #include "kernels.h"
 #include "rank.cuh"
 
 namespace npge_b200 {
 
-MsdPlan make_msd_plan(int k, uint64_t n_positions) {
+MsdPlan make_msd_plan(int k, uint64_t n_positions, int force_f, int force_wa) {
     MsdPlan p;
     p.k = k;
     p.total = 2 * k;
     int f = 2;  // fine bits so that a fine bin holds ~1024 records
     while (f < 20 && (uint64_t(1024) << f) < n_positions) f++;
-    if (const char* e = getenv("NPGE_EXP_F")) {  // tests: exercise the wider digit plans
-        const int v = atoi(e);
-        if (v >= 2 && v <= 20) f = v;
-    }
+    if (force_f >= 2 && force_f <= 20) f = force_f;  // tests: the wider digit plans
     if (f > p.total) f = p.total;
     const int need = p.total - 32;  // bits a narrow (8 B) record cannot hold
     // the smaller half goes to pass A: fewer buckets = longer scatter runs (and
@@ -43,10 +38,8 @@ MsdPlan make_msd_plan(int k, uint64_t n_positions) {
     int wa = f / 2;
     if (need > 0 && need <= kMaxDigitBits && wa < need) wa = need;
     if (wa > kMaxDigitBits) wa = kMaxDigitBits;
-    if (const char* e = getenv("NPGE_EXP_WA")) {  // experiments: force the first split
-        const int v = atoi(e);
-        if (v >= 1 && v <= kMaxDigitBits && (need <= 0 || need > kMaxDigitBits || v >= need)) wa = v;
-    }
+    if (force_wa >= 1 && force_wa <= kMaxDigitBits &&
+        (need <= 0 || need > kMaxDigitBits || force_wa >= need)) wa = force_wa;
     if (wa > p.total) wa = p.total;
     if (wa < 1) wa = 1;
     int wb = f - wa;
@@ -60,7 +53,6 @@ MsdPlan make_msd_plan(int k, uint64_t n_positions) {
     p.capa = wa <= 8 ? 8 : (wa == 9 ? 9 : 10);  // histogram rows of 256 / 512 / 1024 bins
     p.capb = wb <= 8 ? 8 : (wb == 9 ? 9 : 10);
     p.smem_passes = (p.rem + 7) / 8;
-    if (const char* e = getenv("NPGE_EXP_SMEM_PASSES")) p.smem_passes = atoi(e);  // timing only
     return p;
 }
 

@@ -76,7 +76,7 @@ class AnchorResult:
 def _stats_dict(s):
     d = {name: getattr(s, name) for name, _ in s._fields_
          if name not in ("digest", "ms_pass")}
-    d["ms_pass"] = [float(x) for x in s.ms_pass][:int(s.radix_passes)]
+    d["ms_pass"] = [float(x) for x in s.ms_pass][:8]
     d["digest"] = (int(s.digest[0]), int(s.digest[1]))
     return d
 
@@ -110,6 +110,10 @@ class AnchorEngine:
         u = np.ascontiguousarray(np.sort(np.asarray(
             used if used is not None else [], dtype=np.uint64)))
         return u, (u.ctypes.data if len(u) else None)
+
+    def debug_plan(self, fine_bits=0, first_split=0):
+        """Test hook (npge_anchor_debug_plan): force the digit plan of a larger job."""
+        self._check(self._lib.npge_anchor_debug_plan(self._ctx, fine_bits, first_split))
 
     def find(self, seqs, k, similar=True, max_frags=100000, used=None):
         """npge_anchor_find with host buffers (the drop-in call)."""

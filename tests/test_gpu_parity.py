@@ -206,13 +206,14 @@ def test_device_resident_variant(eng):
 
 # ---- the digit plans of bigger jobs (512- and 1024-bin partition passes) -----------
 @pytest.mark.parametrize("f,wa", [(17, None), (18, None), (19, None), (20, None), (16, 9), (18, 8)])
-def test_wide_digit_plans(eng, monkeypatch, f, wa):
-    """NPGE_EXP_F / NPGE_EXP_WA force the plan a 100 M - 1 G position job would
+def test_wide_digit_plans(eng, f, wa):
+    """npge_anchor_debug_plan forces the plan a 100 M - 1 G position job would
     get (wa, wb in 8..10), on an input small enough for the oracle."""
-    monkeypatch.setenv("NPGE_EXP_F", str(f))
-    if wa is not None:
-        monkeypatch.setenv("NPGE_EXP_WA", str(wa))
-    names, seqs = synth.generate("small")
-    for k, similar, limit in ((20, False, BIG), (20, True, 100000), (27, False, BIG)):
-        got = eng.find(seqs, k, similar=similar, max_frags=limit)
-        same(got, oracle.find_ideal(seqs, k, similar=similar, max_frags=limit))
+    eng.debug_plan(f, wa or 0)
+    try:
+        names, seqs = synth.generate("small")
+        for k, similar, limit in ((20, False, BIG), (20, True, 100000), (27, False, BIG)):
+            got = eng.find(seqs, k, similar=similar, max_frags=limit)
+            same(got, oracle.find_ideal(seqs, k, similar=similar, max_frags=limit))
+    finally:
+        eng.debug_plan(0, 0)
