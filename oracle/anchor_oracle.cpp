@@ -17,6 +17,7 @@
 #include "anchor_oracle.h"
 
 #include <algorithm>
+#include <atomic>
 #include <chrono>
 #include <cmath>
 #include <cstdlib>
@@ -842,6 +843,252 @@ extern "C" void oracle_digest(const oracle_result* r, uint64_t digest[2]) {
     }
     digest[0] = d0;
     digest[1] = d1;
+}
+
+/* ====================================================================== */
+/* ref_ideal in hash-range slices: the same exact semantics as find_ideal  */
+/* with O(N / S) memory, for the configurations whose window list does not */
+/* fit (C3-C5 of BASELINE.json; 10^9 windows at C5).                       */
+/* ====================================================================== */
+/* Slice s holds the canonical hashes whose top `slice_bits` bits (of the
+ * 2k significant ones) equal s, so slices ascend with the hash and a
+ * group never spans two of them.  Every slice re-scans the sequences
+ * (rolling the two hashes as find_ideal does) and keeps only its own
+ * windows; the slices are independent, so they run on `threads` threads.
+ *   parity mode      one sweep: groups of >= 2 unused windows -> blocks
+ *   anchor-similar   sweep 1 sets found(rank) (every member of such a
+ *                    group but the first in scan order), sweep 2 selects
+ *                    the groups holding a candidate (found(p) and not
+ *                    found(p-1), BloomTask::test_and_add :170-182)
+ * With a finite max-anchor-fragments the selected records are gathered in
+ * ascending slice order until the cut is covered and then go through the
+ * same build_blocks as find_ideal (sort by (hash, seq, pos'), cut, group). */
+namespace {
+
+struct SliceRec {
+    hash_t hash;
+    uint64_t t;  /* scan index of the sequence << 33 | pos << 1 | direct */
+    bool operator<(const SliceRec& o) const {
+        return hash != o.hash ? hash < o.hash : t < o.t;
+    }
+};
+
+struct SliceScan {
+    std::vector<SeqView> seqs;          /* scan order */
+    std::vector<uint64_t> scan_base;    /* rank of position 0 of every sequence */
+    int k;
+    int shift;                          /* hash >> shift = slice */
+    hash_t mask;
+};
+
+/* every N-free window of slice `slice`, sorted by (hash, scan rank) */
+void slice_windows(const SliceScan& sc, uint64_t slice, std::vector<SliceRec>& out) {
+    out.clear();
+    const int k = sc.k;
+    for (size_t si = 0; si < sc.seqs.size(); si++) {
+        const SeqView& seq = sc.seqs[si];
+        hash_t dir = 0, rev = 0;
+        int valid = 0;
+        for (size_t i = 0; i < seq.size; i++) {
+            const char c = seq.data[i];
+            if (c == 'N') {
+                valid = 0;
+                dir = rev = 0;
+                continue;
+            }
+            const hash_t code = letter_code(c);
+            dir = (dir >> 2) | (code << (2 * (k - 1)));
+            rev = ((rev << 2) | (code ^ 1)) & sc.mask;
+            valid++;
+            if (valid >= k) {
+                const hash_t h = std::min(dir, rev);
+                if ((sc.shift >= 64 ? 0 : (h >> sc.shift)) == slice) {
+                    const uint64_t pos = i + 1 - k;
+                    SliceRec r = {h, (uint64_t(si) << 33) | (pos << 1) | (h == dir ? 1u : 0u)};
+                    out.push_back(r);
+                }
+            }
+        }
+    }
+    std::sort(out.begin(), out.end());
+}
+
+inline uint64_t rank_of(const SliceScan& sc, uint64_t t) {
+    return sc.scan_base[t >> 33] + ((t >> 1) & 0xffffffffull);
+}
+
+template <typename Fn>
+void parallel_slices(uint64_t n_slices, int threads, Fn fn) {
+    std::atomic<uint64_t> next(0);
+    std::vector<std::thread> pool;
+    std::vector<std::string> errors(threads);
+    for (int w = 0; w < threads; w++) {
+        pool.emplace_back([&, w]() {
+            try {
+                while (true) {
+                    const uint64_t s = next.fetch_add(1);
+                    if (s >= n_slices) break;
+                    fn(s, w);
+                }
+            } catch (std::exception& e) {
+                errors[w] = e.what();
+            }
+        });
+    }
+    for (auto& t : pool) t.join();
+    for (auto& e : errors) {
+        if (!e.empty()) throw std::runtime_error(e);
+    }
+}
+
+}  // namespace
+
+extern "C" int oracle_find_ideal_sliced(const oracle_params* p, const char* bases,
+                                        const uint64_t* offsets, uint32_t n_seqs,
+                                        const uint64_t* used, uint64_t n_used,
+                                        int32_t slice_bits, int32_t threads,
+                                        oracle_summary* out) {
+    memset(out, 0, sizeof(*out));
+    const int k = p->anchor_size;
+    if (k <= 0 || k > MAX_ANCHOR || slice_bits < 0 || slice_bits > 16) {
+        return 1;
+    }
+    try {
+        auto t0 = std::chrono::steady_clock::now();
+        if (slice_bits > 2 * k) slice_bits = 2 * k;
+        if (threads < 1) threads = std::max(1u, std::thread::hardware_concurrency());
+        SliceScan sc;
+        sc.seqs = make_seqs(bases, offsets, n_seqs, k, false);
+        sc.scan_base.assign(sc.seqs.size() + 1, 0);
+        for (size_t si = 0; si < sc.seqs.size(); si++) {
+            sc.scan_base[si + 1] = sc.scan_base[si] + sc.seqs[si].size;
+        }
+        sc.k = k;
+        sc.shift = 2 * k - slice_bits;
+        sc.mask = k == 32 ? ~hash_t(0) : ((hash_t(1) << (2 * k)) - 1);
+        const uint64_t n_slices = uint64_t(1) << slice_bits;
+        const bool similar = p->anchor_similar != 0;
+        const bool limited = p->max_anchor_fragments >= 0 &&
+                             uint64_t(p->max_anchor_fragments) < (uint64_t(1) << 62);
+        std::vector<std::atomic<uint64_t> > found;
+        std::atomic<uint64_t> n_windows(0);
+        if (similar) {
+            std::vector<std::atomic<uint64_t> > bits(sc.scan_base.back() / 64 + 2);
+            found.swap(bits);
+            for (auto& w : found) w.store(0, std::memory_order_relaxed);
+            parallel_slices(n_slices, threads, [&](uint64_t s, int) {
+                std::vector<SliceRec> ws;
+                slice_windows(sc, s, ws);
+                for (size_t i = 0; i < ws.size();) {
+                    size_t j = i;
+                    while (j < ws.size() && ws[j].hash == ws[i].hash) j++;
+                    if (j - i >= 2 && !has_elem(used, n_used, ws[i].hash)) {
+                        for (size_t t = i + 1; t < j; t++) {
+                            const uint64_t r = rank_of(sc, ws[t].t);
+                            found[r >> 6].fetch_or(uint64_t(1) << (r & 63),
+                                                   std::memory_order_relaxed);
+                        }
+                    }
+                    i = j;
+                }
+            });
+        }
+        auto is_found = [&](uint64_t r) {
+            return (found[r >> 6].load(std::memory_order_relaxed) >> (r & 63)) & 1;
+        };
+        /* selected records of one slice as FoundFragments, in list order */
+        auto select = [&](uint64_t s, std::vector<Found>& ffs) {
+            std::vector<SliceRec> ws;
+            slice_windows(sc, s, ws);
+            n_windows.fetch_add(ws.size());
+            ffs.clear();
+            for (size_t i = 0; i < ws.size();) {
+                size_t j = i;
+                while (j < ws.size() && ws[j].hash == ws[i].hash) j++;
+                bool ok = j - i >= 2 && !has_elem(used, n_used, ws[i].hash);
+                if (ok && similar) {
+                    ok = false;
+                    for (size_t t = i; t < j && !ok; t++) {
+                        const uint64_t r = rank_of(sc, ws[t].t);
+                        const uint64_t pos = (ws[t].t >> 1) & 0xffffffffull;
+                        ok = is_found(r) && (pos == 0 || !is_found(r - 1));
+                    }
+                }
+                if (ok) {
+                    for (size_t t = i; t < j; t++) {
+                        const SeqView& seq = sc.seqs[ws[t].t >> 33];
+                        const uint64_t pos = (ws[t].t >> 1) & 0xffffffffull;
+                        Found f = {ws[t].hash, seq.index,
+                                   pos + ((ws[t].t & 1) ? 0 : seq.size)};
+                        ffs.push_back(f);
+                    }
+                }
+                i = j;
+            }
+        };
+        if (!limited) {
+            struct Acc { uint64_t nf = 0, nb = 0, d0 = 0, d1 = 0; };
+            std::vector<Acc> acc(threads);
+            parallel_slices(n_slices, threads, [&](uint64_t s, int w) {
+                std::vector<Found> ffs;
+                select(s, ffs);
+                Acc& a = acc[w];
+                for (size_t i = 0; i < ffs.size(); i++) {
+                    const Found& f = ffs[i];
+                    const uint64_t size = offsets[f.seq + 1] - offsets[f.seq];
+                    const bool direct = f.pos < size;
+                    const uint64_t t = (uint64_t(f.seq) << 33) |
+                                       ((direct ? f.pos : f.pos - size) << 1) |
+                                       (direct ? 1 : 0);
+                    uint64_t x, y;
+                    digest_terms(t, f.hash, x, y);
+                    a.d0 += x;
+                    a.d1 += y;
+                    a.nf++;
+                    if (i == 0 || ffs[i - 1].hash != f.hash) a.nb++;
+                }
+            });
+            for (const Acc& a : acc) {
+                out->n_fragments += a.nf;
+                out->n_blocks += a.nb;
+                out->digest[0] += a.d0;
+                out->digest[1] += a.d1;
+            }
+            out->total_selected = out->n_fragments;
+            out->n_new_used = out->n_blocks ? out->n_blocks - 1 : 0;
+            out->n_windows = n_windows.load();
+        } else {
+            /* batches of `threads` slices in ascending order until the cut is covered */
+            const uint64_t M = uint64_t(p->max_anchor_fragments);
+            std::vector<Found> all;
+            bool complete = true;
+            for (uint64_t s0 = 0; s0 < n_slices; s0 += threads) {
+                const uint64_t n = std::min<uint64_t>(threads, n_slices - s0);
+                std::vector<std::vector<Found> > part(n);
+                parallel_slices(n, int(n), [&](uint64_t s, int) { select(s0 + s, part[s]); });
+                for (auto& v : part) all.insert(all.end(), v.begin(), v.end());
+                if (all.size() > M) {
+                    complete = s0 + n >= n_slices;
+                    break;
+                }
+            }
+            out->total_selected = complete ? all.size() : 0;  /* 0: not counted */
+            out->n_windows = complete ? n_windows.load() : 0;
+            oracle_result r;
+            memset(&r, 0, sizeof(r));
+            build_blocks(all, p, offsets, &r);
+            out->n_fragments = r.n_fragments;
+            out->n_blocks = r.n_blocks;
+            out->n_new_used = r.n_new_used;
+            oracle_digest(&r, out->digest);
+            oracle_result_free(&r);
+        }
+        out->seconds = std::chrono::duration<double>(
+                           std::chrono::steady_clock::now() - t0).count();
+    } catch (std::exception&) {
+        return 2;
+    }
+    return 0;
 }
 
 /* ====================================================================== */

@@ -83,6 +83,22 @@ int oracle_find_ideal(const oracle_params* p, const char* bases,
 
 void oracle_result_free(oracle_result* r);
 
+/* The same exact semantics in 2^slice_bits hash-range slices on `threads`
+ * threads (<= 0: all cores): O(N / slices) memory per thread, counts and the
+ * 128-bit digest only.  For BASELINE.json's large configurations.  With a
+ * finite max-anchor-fragments that is reached before the last slice,
+ * total_selected and n_windows are 0 (not counted). */
+typedef struct {
+    uint64_t n_windows, n_fragments, n_blocks, total_selected, n_new_used;
+    uint64_t digest[2];
+    double seconds;
+} oracle_summary;
+int oracle_find_ideal_sliced(const oracle_params* p, const char* bases,
+                             const uint64_t* offsets, uint32_t n_seqs,
+                             const uint64_t* used_sorted, uint64_t n_used,
+                             int32_t slice_bits, int32_t threads,
+                             oracle_summary* out);
+
 /* blockset_hash (block_hash.cpp:29-54,125-130) over blocks given as flat
  * arrays; names[s] is the sequence name used by Fragment::id() (Fragment.cpp:173-183) */
 uint64_t oracle_blockset_hash(const char* const* names, uint64_t n_blocks,

@@ -218,6 +218,39 @@ def find_ideal(seqs, k, similar=False, max_frags=2**62, used=None):
     return Result(r)
 
 
+class OracleSummary(C.Structure):
+    _fields_ = [("n_windows", C.c_uint64), ("n_fragments", C.c_uint64),
+                ("n_blocks", C.c_uint64), ("total_selected", C.c_uint64),
+                ("n_new_used", C.c_uint64), ("digest", C.c_uint64 * 2),
+                ("seconds", C.c_double)]
+
+
+def find_ideal_sliced(seqs, k, similar=False, max_frags=2**62, used=None,
+                      slice_bits=6, threads=0):
+    """find_ideal in 2**slice_bits hash-range slices: counts + digest only, O(N /
+    slices) memory per thread.  seqs: list of sequences or (bases, offsets)."""
+    bases, offsets = seqs if isinstance(seqs, tuple) else concat(seqs)
+    offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
+    used = np.ascontiguousarray(
+        np.sort(np.asarray(used if used is not None else [], dtype=np.uint64)))
+    p = _params(k, similar, max_frags)
+    r = OracleSummary()
+    L = lib()
+    L.oracle_find_ideal_sliced.restype = C.c_int
+    L.oracle_find_ideal_sliced.argtypes = [
+        C.POINTER(OracleParams), C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p,
+        C.c_uint64, C.c_int32, C.c_int32, C.POINTER(OracleSummary)]
+    rc = L.oracle_find_ideal_sliced(
+        C.byref(p), bases.ctypes.data, offsets.ctypes.data, len(offsets) - 1,
+        used.ctypes.data, len(used), slice_bits, threads, C.byref(r))
+    if rc != 0:
+        raise ValueError("oracle_find_ideal_sliced failed: %d" % rc)
+    return dict(n_windows=int(r.n_windows), n_fragments=int(r.n_fragments),
+                n_blocks=int(r.n_blocks), total_selected=int(r.total_selected),
+                n_new_used=int(r.n_new_used),
+                digest=(int(r.digest[0]), int(r.digest[1])), seconds=float(r.seconds))
+
+
 def find_faithful(seqs, k, similar=True, max_frags=100000, fp=0.1, workers=1,
                   seed=1, exact_bloom=False, asserts=True, genome_ids=None,
                   used=None):

@@ -161,3 +161,38 @@ def test_oracle_hash_matches_reference_code():
             a, b = s[0:1], s[n:n + 1]
             assert (L.oracle_reuse_hash(d, n, a, b, fwd)
                     == R.ref_reuse_hash(d, n, a, b, fwd))
+
+
+# ---- the sliced oracle behind tests/golden/digests.json ---------------------------------
+@pytest.mark.parametrize("k", [1, 7, 20, 32])
+def test_sliced_oracle_equals_find_ideal(k):
+    """oracle_find_ideal_sliced (hash-range slices, threads) gives find_ideal's counts
+    and digest in both modes, with cuts inside a group and with used hashes."""
+    names, seqs = synth.generate("tiny")
+    seqs = seqs + _random_seqs(random.Random(k), 5, 300)
+    base = oracle.find_ideal(seqs, k, similar=False)
+    used = base.block_hash[::4].copy()
+    for similar, limit, u in ((False, 2**62, None), (True, 2**62, None), (True, 100000, None),
+                              (False, 1001, None), (True, 3, None), (False, 0, None),
+                              (False, 2**62, used), (True, 555, used)):
+        want = oracle.find_ideal(seqs, k, similar=similar, max_frags=limit, used=u)
+        for bits, threads in ((0, 1), (5, 3)):
+            got = oracle.find_ideal_sliced(seqs, k, similar=similar, max_frags=limit, used=u,
+                                           slice_bits=bits, threads=threads)
+            assert got["n_fragments"] == want.n_fragments
+            assert got["n_blocks"] == want.n_blocks
+            assert got["digest"] == want.digest
+            assert got["n_new_used"] == len(want.new_used)
+
+
+def test_golden_digests_match_find_ideal_on_c1():
+    """digests.json (written by tests/golden/make_digests.py) is what find_ideal says
+    on the configuration small enough to run here: C1 brucella3."""
+    from golden_util import load
+    table = load("digests.json")
+    names, seqs = synth.generate("brucella3")
+    for mode, (similar, limit) in {"parity": (False, 2**62), "default": (True, 100000)}.items():
+        g = table["brucella3|k=20|%s" % mode]
+        want = oracle.find_ideal(seqs, 20, similar=similar, max_frags=limit)
+        assert (g["n_fragments"], g["n_blocks"]) == (want.n_fragments, want.n_blocks)
+        assert tuple(int(x, 16) for x in g["digest"]) == want.digest
