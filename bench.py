@@ -4,18 +4,25 @@
 A step = one pass of the hot path (AnchorFinder::run_impl,
 src/algo/AnchorFinder.cpp:393-406) over the whole synthetic genome set:
   value   bases scanned per second with the packed genome resident in HBM and
-          the anchors left in HBM (npge_anchor_find_device), timed with CUDA
-          events on the library's own stream, L2 flushed between steps
+          the anchors left in HBM (npge_anchor_find_device), CUDA events around
+          the whole step (the same definition at every N), L2 flushed between
+          steps
   e2e     the same metric through the drop-in call npge_anchor_find with HOST
           buffers: pinned ASCII bases in, Fragment arrays out, copies included
+  parity  counts and 128-bit digest of every timed result against
+          tests/golden/digests.json (written by the CPU oracle in hash-range
+          slices, tests/golden/make_digests.py); the run FAILS (rc 1) on a mismatch
+  c5      the north-star configuration (1 Gbp pangenome, k = 20) sharded over the
+          N GPUs of the run (strong scaling), its own parity check, and at N = 1
+          the k = 24 / 28 / 32 sweep
   --impl reference   the reference's CPU algorithm (oracle/ restatement; the
-          reference itself cannot be built here) on the host cores
+          reference itself cannot be built here) on the host cores,
+          on the same full-size workload
 
-Workload: BASELINE.json configs[1], 17 synthetic Brucella-shaped genomes
+Headline workload: BASELINE.json configs[1], 17 synthetic Brucella-shaped genomes
 (~56 Mbp), anchor-size 20, parity mode (anchor-similar=false, no truncation);
 the default options are timed beside it (`default_mode`).  At N>1 every rank
-holds its own 17 strains of the same ancestor (weak scaling), k-mers are
-repartitioned by hash range with one NCCL all-to-all.
+holds its own 17 strains (weak scaling), k-mers are repartitioned by hash range.
 """
 import argparse
 import json
@@ -31,6 +38,7 @@ sys.path.insert(0, ROOT)
 import numpy as np  # noqa: E402
 
 WORKLOAD = "brucella17"
+C5 = "pangenome1g"
 K = 20
 BIG = 2 ** 62
 METRIC = "Gbp scanned/sec (AnchorFinder)"
@@ -44,6 +52,36 @@ def peaks():
             p = json.load(f)
         return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
     return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def golden(workload, k, mode):
+    """(n_fragments, n_blocks, digest) the CPU oracle holds for a workload, or None."""
+    path = os.path.join(ROOT, "tests", "golden", "digests.json")
+    if not os.path.exists(path):
+        return None
+    with open(path) as f:
+        g = json.load(f).get("%s|k=%d|%s" % (workload, k, mode))
+    if g is None:
+        return None
+    return g["n_fragments"], g["n_blocks"], tuple(int(x, 16) for x in g["digest"])
+
+
+def check_parity(workload, k, mode, st):
+    """Compares a job's counts and digest with the golden entry."""
+    want = golden(workload, k, mode)
+    got = (st["n_fragments_global"], st["n_blocks_global"], tuple(st["digest"]))
+    out = {"workload": workload, "anchor_size": k, "mode": mode,
+           "source": "tests/golden/digests.json", "fragments": got[0], "blocks": got[1],
+           "digest": ["%016x" % d for d in got[2]]}
+    if want is None:
+        out["digest_equal"] = None
+        out["note"] = "no golden entry"
+    else:
+        out["digest_equal"] = bool(got == want)
+        if got != want:
+            out["expected"] = {"fragments": want[0], "blocks": want[1],
+                               "digest": ["%016x" % d for d in want[2]]}
+    return out
 
 
 class ClockSampler:
@@ -106,39 +144,34 @@ class ClockSampler:
                 "reasons": sorted(reasons)}
 
 
-def make_workload(rank, world, scale=1.0):
-    """Rank r's strains: the same ancestor for every rank (same seed), its own
-    17 strains.  Returns (names, seqs, offset of this rank's first caller
-    sequence index)."""
-    from npge_b200 import synth
-    if world == 1:
-        names, seqs = synth.generate(WORKLOAD, scale=scale)
-        return names, seqs
-    return synth.generate_shard(WORKLOAD, rank, world, scale=scale)
+def base_config(world, n_total, n_seqs):
+    """The keys both arms share (the reference arm prints exactly these)."""
+    return {
+        "workload": WORKLOAD + (" x%d (one 17-strain cluster per GPU, independent "
+                                "ancestors)" % world if world > 1 else ""),
+        "anchor_size": K,
+        "mode": "parity (anchor-similar=false, no truncation)",
+        "bases_per_step": int(n_total), "sequences": int(n_seqs),
+    }
 
 
 # ---------------------------------------------------------------------------
 def run_reference(args, rank, world):
     """The reference's CPU algorithm (two-pass Bloom AnchorFinder restated in
-    oracle/anchor_oracle.cpp) on the host cores, all threads, on a bounded
-    sample of the same workload."""
+    oracle/anchor_oracle.cpp) on the host cores, all threads.  N = 1: the GPU
+    arm's workload at full size (same config).  N > 1: the job is N clusters;
+    every step runs ONE of them (rank 0's, 56 Mbp) so that the run stays within
+    minutes -- per-base throughput of the CPU does not depend on which."""
     if rank != 0:
         return
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import oracle
     from npge_b200 import synth
     cores = os.cpu_count() or 1
-    # bound the whole run to ~150 s of CPU work: probe the rate on a 1 % sample
-    names, seqs = synth.generate(WORKLOAD, scale=0.01)
-    t = time.perf_counter()
-    oracle.find_faithful(seqs, K, similar=False, max_frags=BIG, workers=cores,
-                         genome_ids=synth.genome_ids(names), asserts=True)
-    rate = synth.total_bases(seqs) / (time.perf_counter() - t)
-    full = 56.1e6
-    scale = min(args.cpu_scale,
-                rate * 150.0 / (args.steps + args.warmup) / full)
-    scale = max(scale, 0.005)
-    names, seqs = synth.generate(WORKLOAD, scale=scale)
+    if world == 1:
+        names, seqs = synth.generate(WORKLOAD, scale=args.cpu_scale)
+    else:
+        names, seqs = synth.generate_shard(WORKLOAD, 0, world, scale=args.cpu_scale)
     n = synth.total_bases(seqs)
     gid = synth.genome_ids(names)
     times = []
@@ -153,19 +186,20 @@ def run_reference(args, rank, world):
             times.append(dt)
     total = sum(times)
     value = n * len(times) / total / 1e9
-    sample = ("%s at scale %.3g: %d sequences, %.2f Mbp, k=%d, parity mode; "
+    sample = ("%s%s at scale %.3g: %d sequences, %.2f Mbp, k=%d, parity mode; "
               "two-pass Bloom restatement (oracle find_faithful, range "
               "checks on), %d std::threads, one task per sequence"
-              % (WORKLOAD, scale, len(seqs), n / 1e6, K, cores))
+              % (WORKLOAD, "" if world == 1 else " (one of the job's %d clusters per step)" % world,
+                 args.cpu_scale, len(seqs), n / 1e6, K, cores))
+    config = base_config(world, n * world if args.cpu_scale == 1.0 else n, len(seqs) * world)
+    if world > 1 or args.cpu_scale != 1.0:
+        config["cpu_sample_bases_per_step"] = n
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT,
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1e3 * total / len(times), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u64",
-        "data": "synthetic",
-        "config": {"workload": WORKLOAD, "anchor_size": K,
-                   "mode": "parity (anchor-similar=false, no truncation)",
-                   "sample_scale": scale, "bases_per_step": n},
+        "data": "synthetic", "config": config,
         "anchors_per_s": frags * len(times) / total,
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores,
                          "kind": "port", "sample": sample},
@@ -177,14 +211,35 @@ def run_reference(args, rank, world):
 
 
 # ---------------------------------------------------------------------------
-def cpu_baseline(scale):
+def cpu_baseline(budget_s):
+    """The CPU legs of SURVEY 8(d), on this box's host cores, beside the GPU run:
+    the headline workload (brucella17, full size, all threads, parity mode: one
+    run) and the designated CPU configuration C1 (brucella3) with workers = 1 and
+    all cores, range checks on and off, parity mode and the default options."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import oracle
     from npge_b200 import synth
-    names, seqs = synth.generate(WORKLOAD, scale=scale)
+    cores = os.cpu_count() or 1
+    t_all = time.perf_counter()
+    names, seqs = synth.generate("brucella3")
+    n1 = synth.total_bases(seqs)
+    gid = synth.genome_ids(names)
+    legs = []
+    for mode, similar, limit in (("parity", False, BIG), ("default", True, 100000)):
+        for workers in (cores, 1):
+            for asserts in (True, False):
+                if time.perf_counter() - t_all > budget_s:
+                    continue
+                t = time.perf_counter()
+                r = oracle.find_faithful(seqs, K, similar=similar, max_frags=limit,
+                                         workers=workers, genome_ids=gid, asserts=asserts)
+                dt = time.perf_counter() - t
+                legs.append({"workload": "brucella3", "mode": mode, "workers": workers,
+                             "range_checks": asserts, "seconds": dt,
+                             "value": n1 / dt / 1e9, "fragments": r.n_fragments})
+    names, seqs = synth.generate(WORKLOAD)
     n = synth.total_bases(seqs)
     gid = synth.genome_ids(names)
-    cores = os.cpu_count() or 1
     t = time.perf_counter()
     r = oracle.find_faithful(seqs, K, similar=False, max_frags=BIG,
                              workers=cores, genome_ids=gid, asserts=True)
@@ -195,13 +250,108 @@ def cpu_baseline(scale):
     dt_default = time.perf_counter() - t1
     return {
         "value": n / dt / 1e9, "unit": UNIT, "cores": cores, "kind": "port",
-        "sample": ("%s at scale %.3g (%d sequences, %.2f Mbp), k=%d, parity "
+        "sample": ("%s at full size (%d sequences, %.2f Mbp), k=%d, parity "
                    "mode, oracle find_faithful (two-pass Bloom restatement of "
-                   "AnchorFinder.cpp, range checks on), %d threads, %.1f s"
-                   % (WORKLOAD, scale, len(seqs), n / 1e6, K, cores, dt)),
+                   "AnchorFinder.cpp, range checks on), %d threads, one run of %.1f s"
+                   % (WORKLOAD, len(seqs), n / 1e6, K, cores, dt)),
         "anchors_per_s": r.n_fragments / dt,
         "default_mode_value": n / dt_default / 1e9,
+        "c1": {"workload": "brucella3", "bases": n1, "cores": cores, "unit": UNIT,
+               "note": "SURVEY 8(d): the designated CPU configuration; the reference "
+                       "runs one task per sequence (6 here), so more than 6 workers idle",
+               "legs": legs},
     }
+
+
+def timed_steps(runner, torch, flush, steps, k, similar, limit):
+    """`steps` timed passes; returns (sum of whole-step ms, list of stats)."""
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    total, out = 0.0, []
+    for _ in range(steps):
+        flush.fill_(1)
+        torch.cuda.synchronize()
+        e0.record()
+        st = runner.step(k, similar, limit)
+        e1.record()
+        e1.synchronize()
+        total += e0.elapsed_time(e1)
+        out.append(st)
+    return total, out
+
+
+def max_over_ranks(x, world, dist, torch):
+    if world == 1:
+        return x
+    t = torch.tensor([x], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def run_c5(args, rank, world, runner_factory, torch, dist, flush, hbm_peak):
+    """The 1 Gbp pangenome sharded over the N GPUs of this run (strong scaling)."""
+    from npge_b200 import synth
+    from npge_b200.engine import concat
+    names, seqs = synth.generate(C5)
+    n_seqs = len(seqs)
+    n_total = synth.total_bases(seqs)
+    per = (n_seqs + world - 1) // world  # caller order, contiguous: job index = index
+    mine = seqs[rank * per:(rank + 1) * per]
+    bases, offsets = concat(mine)
+    del seqs, mine
+    runner = runner_factory(bases, offsets)
+    steps = max(3, min(args.steps, 5))
+    out = {"workload": C5, "anchor_size": K, "n_gpus": world, "bases": n_total,
+           "sequences": n_seqs, "scaling": "strong", "steps": steps,
+           "mode": "parity (anchor-similar=false, no truncation)"}
+    sweep = []
+    for k in ((20, 24, 28, 32) if world == 1 else (20,)):
+        runner.upload(k)
+        for _ in range(2):
+            runner.step(k, False, BIG)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        ms, sts = timed_steps(runner, torch, flush, steps, k, False, BIG)
+        ms = max_over_ranks(ms, world, dist, torch) / steps
+        st = runner.finish(sts[-1])
+        par = check_parity(C5, k, "parity", st)
+        row = {"anchor_size": k, "ms_per_step": ms, "gbp_s": n_total / (ms * 1e-3) / 1e9,
+               "fragments": st["n_fragments_global"], "blocks": st["n_blocks_global"],
+               "digest_equal": par["digest_equal"],
+               "survey_model_frac": st["bytes_algorithmic_job"] / (ms * 1e-3) / 1e9 / hbm_peak / world,
+               "compulsory_frac": st["bytes_moved_job"] / (ms * 1e-3) / 1e9 / hbm_peak / world}
+        if k == K:
+            out.update(row)
+            out["parity"] = par
+            out["kernel_ms_rank0"] = float(np.mean([x["ms_total"] for x in sts]))
+            if world > 1:
+                sent = float(np.mean([x.get("nvlink_bytes_sent", 0) for x in sts]))
+                x_ms = float(np.mean([x.get("nvlink_ms", 0.0) for x in sts]))
+                out["nvlink"] = {
+                    "bytes_per_gpu": sent, "ms": x_ms,
+                    "gb_s": sent / (x_ms * 1e-3) / 1e9 if x_ms > 0 else None,
+                    "frac_of_900": sent / (x_ms * 1e-3) / 900e9 if x_ms > 0 else None,
+                    "survey_model_bytes_per_gpu": 12.0 * n_total / world * (world - 1) / world,
+                    "exchange": sts[-1].get("exchange"),
+                    "note": "rank 0: bytes it wrote into the other ranks' HBM / device "
+                            "time of its exchange stage"}
+            # default options on the same resident genome
+            for _ in range(2):
+                runner.step(k, True, 100000)
+            dms, dsts = timed_steps(runner, torch, flush, steps, k, True, 100000)
+            dms = max_over_ranks(dms, world, dist, torch) / steps
+            dst = runner.finish(dsts[-1])
+            dpar = check_parity(C5, k, "default", dst)
+            out["default_mode"] = {"ms_per_step": dms, "gbp_s": n_total / (dms * 1e-3) / 1e9,
+                                   "digest_equal": dpar["digest_equal"],
+                                   "fragments": dst["n_fragments_global"],
+                                   "blocks": dst["n_blocks_global"]}
+        else:
+            sweep.append(row)
+    if sweep:
+        out["k_sweep"] = sweep
+    runner.close()
+    return out
 
 
 def run_gpu(args, rank, world, local_rank):
@@ -221,14 +371,20 @@ def run_gpu(args, rank, world, local_rank):
     hbm_peak, peak_src = peaks()
     if world == 1:
         names, seqs = synth.generate(WORKLOAD)
-        bases, offsets = concat(seqs)
         eng = AnchorEngine(local_rank)
-        runner = SingleRunner(eng, bases, offsets)
+
+        def runner_factory(b, o):
+            return SingleRunner(eng, b, o)
     else:
         from npge_b200.dist import DistAnchorFinder
         names, seqs = synth.generate_shard(WORKLOAD, rank, world)
-        bases, offsets = concat(seqs)
-        runner = DistRunner(DistAnchorFinder(local_rank), bases, offsets)
+        finder = DistAnchorFinder(local_rank)
+
+        def runner_factory(b, o):
+            return DistRunner(finder, b, o)
+    bases, offsets = concat(seqs)
+    runner = runner_factory(bases, offsets)
+    job_name = WORKLOAD if world == 1 else "%s_x%d" % (WORKLOAD, world)
     n_local = int(offsets[-1])
     n_total = n_local
     if world > 1:
@@ -247,47 +403,33 @@ def run_gpu(args, rank, world, local_rank):
 
     # ---- device-resident: value ------------------------------------------
     runner.upload(K)
-    stats = None
     for _ in range(args.warmup):
-        stats = runner.step(K, False, BIG)
+        runner.step(K, False, BIG)
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
     barrier()
-    ev_ms, pass_ms, kern_launches = 0.0, [], 0
-    hist_ms = group_ms = step_ms = 0.0
-    exch_ms, host_ms = {}, {}
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     wall0 = time.perf_counter()
-    for _ in range(args.steps):
-        flush.fill_(1)
-        torch.cuda.synchronize()
-        e0.record()
-        stats = runner.step(K, False, BIG)
-        e1.record()
-        e1.synchronize()
-        step_ms += e0.elapsed_time(e1)
-        for nm, v in stats.get("exchange_ms", {}).items():
-            exch_ms[nm] = exch_ms.get(nm, 0.0) + v
-        for nm, v in stats.get("host_ms", {}).items():
-            host_ms[nm] = host_ms.get(nm, 0.0) + v
-        ev_ms += stats["ms_total"]
-        hist_ms += stats["ms_hist"]
-        group_ms += stats["ms_group"]
-        pass_ms.append(stats["ms_pass"])
-        kern_launches += stats["gpu_launches"]
+    step_ms, all_stats = timed_steps(runner, torch, flush, args.steps, K, False, BIG)
     barrier()
     wall = time.perf_counter() - wall0
     clocks = sampler.stop() if rank == 0 else None
-    # one GPU: the library's own events on its stream (first kernel .. last
-    # kernel of every step); several GPUs: events around the whole step, i.e.
-    # kernels + collectives + the host tables between them
-    t_dev = (ev_ms if world == 1 else step_ms) / 1e3
-    if world > 1:
-        t = torch.tensor([t_dev], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        t_dev = float(t.item())
+    ev_ms = sum(st["ms_total"] for st in all_stats)
+    hist_ms = sum(st["ms_hist"] for st in all_stats)
+    pass_ms = [st["ms_pass"] for st in all_stats]
+    kern_launches = sum(st["gpu_launches"] for st in all_stats)
+    exch_ms, host_ms = {}, {}
+    for st in all_stats:
+        for nm, v in st.get("exchange_ms", {}).items():
+            exch_ms[nm] = exch_ms.get(nm, 0.0) + v
+        for nm, v in st.get("host_ms", {}).items():
+            host_ms[nm] = host_ms.get(nm, 0.0) + v
+    stats = all_stats[-1]
+    # CUDA events around the whole step (kernels, exchanges, host tables and the
+    # call's own synchronisation) at every N, max over ranks
+    t_dev = max_over_ranks(step_ms, world, dist, torch) / 1e3
     parity_stats = runner.finish(stats)
+    parity = check_parity(job_name, K, "parity", parity_stats)
     # the row next to the path: the reference's block_hash of
     # every anchor block, on the result that is still resident.  Reported beside
     # the headline, not part of it; never allowed to break the line.
@@ -308,28 +450,19 @@ def run_gpu(args, rank, world, local_rank):
         if rank == 0:
             emit({"profile_run": True, "steps": args.steps,
                   "ms_per_step": 1e3 * t_dev / args.steps,
+                  "kernel_ms_per_step": ev_ms / args.steps,
+                  "digest_equal": parity["digest_equal"],
                   "stats": {k: v for k, v in stats.items() if k != "digest"}})
         return
 
     # ---- default options (anchor-similar=true, 100000 fragments) -----------
     for _ in range(2):
         runner.step(K, True, 100000)
-    dflt_ms = 0.0
     dsteps = max(3, args.steps // 2)
-    for _ in range(dsteps):
-        flush.fill_(1)
-        torch.cuda.synchronize()
-        e0.record()
-        st = runner.step(K, True, 100000)
-        e1.record()
-        e1.synchronize()
-        dflt_ms += st["ms_total"] if world == 1 else e0.elapsed_time(e1)
-        kern_launches += 0  # not part of the timed headline region
-    if world > 1:
-        t = torch.tensor([dflt_ms], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dflt_ms = float(t.item())
-    default_stats = runner.finish(st)
+    dflt_ms, dstats = timed_steps(runner, torch, flush, dsteps, K, True, 100000)
+    dflt_ms = max_over_ranks(dflt_ms, world, dist, torch)
+    default_stats = runner.finish(dstats[-1])
+    parity_default = check_parity(job_name, K, "default", default_stats)
 
     # ---- end to end through the drop-in call, host buffers -------------------
     pinned = torch.from_numpy(bases).pin_memory()
@@ -342,11 +475,7 @@ def run_gpu(args, rank, world, local_rank):
     for _ in range(e2e_steps):
         d2h = runner.find_host(pinned_np, offsets, K, False, BIG)
     barrier()
-    e2e_t = time.perf_counter() - t0
-    if world > 1:
-        t = torch.tensor([e2e_t], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_t = float(t.item())
+    e2e_t = max_over_ranks(time.perf_counter() - t0, world, dist, torch)
     h2d = int(bases.nbytes + offsets.nbytes)
     if world > 1:  # job totals of the copies and of the launches
         t = torch.tensor([h2d, int(d2h), kern_launches], dtype=torch.int64, device="cuda")
@@ -359,23 +488,31 @@ def run_gpu(args, rank, world, local_rank):
         d2h_default = runner.find_host(pinned_np, offsets, K, True, 100000)
     barrier()
     e2e_default_t = time.perf_counter() - t0
+    del pinned, pinned_np
+
+    # ---- the north-star configuration under the same clock ---------------------
+    c5 = None
+    if not args.no_c5:
+        try:
+            c5 = run_c5(args, rank, world, runner_factory, torch, dist, flush, hbm_peak)
+        except Exception as exc:  # noqa: BLE001  (every rank fails alike or the job hangs)
+            c5 = {"workload": C5, "error": str(exc)[:300]}
 
     if rank != 0:
         return
     value = n_total * args.steps / t_dev / 1e9
     nw = parity_stats.get("local_records", parity_stats["n_windows"])  # rank 0's
-    passes = parity_stats["radix_passes"]
-    # stages of one step (CUDA events inside npge_anchor_find_device):
+    # stages of one step (CUDA events inside the library):
     # count A + scan | pass A | count B + scan | pass B | bucket sort | scan + emit
-    names = ["pass_a", "count_b_scan", "pass_b", "bucket_sort", "scan_emit"]
+    names_s = ["pass_a", "count_b_scan", "pass_b", "bucket_sort", "scan_emit"]
     stage = {"count_a_scan": hist_ms / args.steps}
-    for i, nm in enumerate(names):
+    for i, nm in enumerate(names_s):
         stage[nm] = float(np.mean([p[i] for p in pass_ms]))
+    stage["kernels"] = ev_ms / args.steps
+    stage["step"] = step_ms / args.steps
     if world > 1:  # rank 0's view of the step
         for nm, v in exch_ms.items():
             stage["exchange_" + nm] = v / args.steps
-        stage["kernels"] = ev_ms / args.steps
-        stage["step"] = step_ms / args.steps
         stage["host_wall_by_phase"] = {nm: v / args.steps for nm, v in host_ms.items()}
         stage["host_tables_and_syncs"] = (
             stage["step"] - stage["kernels"] - sum(exch_ms.values()) / args.steps)
@@ -389,42 +526,35 @@ def run_gpu(args, rank, world, local_rank):
     moved_gbs = moved * args.steps / (ev_ms * 1e-3) / 1e9
     pipeline_bytes = parity_stats["bytes_algorithmic"]
     pipeline_gbs = pipeline_bytes * args.steps / (ev_ms * 1e-3) / 1e9
+    config = base_config(world, n_total, int(len(offsets) - 1) * world)
+    config.update({
+        "l2": "512 MiB flush buffer rewritten between timed steps",
+        "timed": "CUDA events around the whole step (kernels, exchanges, host tables, "
+                 "the call's own synchronisation), max over ranks",
+        "parallelism": ("1 GPU" if world == 1 else
+                        "sequences sharded per GPU; k-mers repartitioned by hash "
+                        "range x%d, exchange=%s" % (world, parity_stats.get("exchange", "?"))),
+    })
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1e3 * t_dev / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u64",
-        "data": "synthetic",
-        "config": {
-            "workload": WORKLOAD + (" x%d (one 17-strain cluster per GPU, "
-                                    "independent ancestors)" % world
-                                    if world > 1 else ""),
-            "anchor_size": K,
-            "mode": "parity (anchor-similar=false, no truncation)",
-            "bases_per_step": n_total, "sequences": int(len(offsets) - 1) * world,
-            "l2": "512 MiB flush buffer rewritten between timed steps",
-            "timed": ("library CUDA events on its stream, first to last kernel "
-                      "of the step" if world == 1 else
-                      "CUDA events around the whole step (kernels, NCCL "
-                      "exchanges, host tables), max over ranks"),
-            "parallelism": ("1 GPU" if world == 1 else
-                            "sequences sharded per GPU; k-mers repartitioned by hash "
-                            "range x%d, exchange=%s (peer: pass A scatters into the "
-                            "owners' HBM over NVLink; bulk: copy kernel into peer "
-                            "memory; collective: NCCL all-to-all)"
-                            % (world, parity_stats.get("exchange", "?"))),
-        },
+        "data": "synthetic", "config": config,
+        "parity": parity,
         "anchors_per_s": parity_stats["n_fragments_global"] * args.steps / t_dev,
         "fragments": parity_stats["n_fragments_global"],
         "blocks": parity_stats["n_blocks_global"],
         "windows": parity_stats["n_windows_global"],
+        "kernel_ms_per_step": ev_ms / args.steps,
         "wall_ms_per_step": 1e3 * wall / args.steps,
         "stage_ms": stage,
         "default_mode": {
             "value": n_total * dsteps / (dflt_ms * 1e-3) / 1e9, "unit": UNIT,
             "options": "anchor-similar=true, max-anchor-fragments=100000",
             "fragments": default_stats["n_fragments_global"],
-            "blocks": default_stats["n_blocks_global"]},
+            "blocks": default_stats["n_blocks_global"],
+            "digest_equal": parity_default["digest_equal"]},
         "roofline": {
             "bound": "hbm", "kernel": runner.dominant_kernel,
             "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
@@ -440,7 +570,8 @@ def run_gpu(args, rank, world, local_rank):
                              pipeline_bytes / float(n_local),
                          "compulsory_bytes_per_step": moved,
                          "compulsory_gbs": moved_gbs,
-                         "compulsory_frac": moved_gbs / hbm_peak}},
+                         "compulsory_frac": moved_gbs / hbm_peak,
+                         "over": "the library's own events, first to last kernel"}},
         "e2e": {"value": n_total * e2e_steps / e2e_t / 1e9, "unit": UNIT,
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": int(d2h),
                 "steps": e2e_steps,
@@ -452,11 +583,19 @@ def run_gpu(args, rank, world, local_rank):
         "gpu_launches": int(kern_launches),
         "clocks": clocks,
     }
+    if c5 is not None:
+        line["c5"] = c5
     if block_hash is not None:
         line["block_hash"] = block_hash
     if world == 1 and not args.no_cpu:
-        line["cpu_baseline"] = cpu_baseline(args.cpu_scale)
+        line["cpu_baseline"] = cpu_baseline(args.cpu_budget)
     emit(line)
+    bad = [p for p in (parity, parity_default, (c5 or {}).get("parity"))
+           if p and p.get("digest_equal") is False]
+    if bad or (c5 and c5.get("default_mode", {}).get("digest_equal") is False):
+        sys.stderr.write("bench.py: PARITY FAILURE against tests/golden/digests.json: %s\n"
+                         % json.dumps(bad))
+        sys.exit(1)
 
 
 class SingleRunner:
@@ -476,7 +615,12 @@ class SingleRunner:
         return st
 
     def finish(self, st):
+        st["bytes_algorithmic_job"] = st["bytes_algorithmic"]
+        st["bytes_moved_job"] = st["bytes_moved"]
         return st
+
+    def close(self):
+        pass
 
     def find_host(self, bases, offsets, k, similar, max_frags):
         r = self.eng.find_counts((bases, offsets), k, similar=similar,
@@ -558,8 +702,13 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--cpu-scale", type=float, default=0.2,
-                    help="chromosome length scale of the bounded CPU sample")
+    ap.add_argument("--cpu-scale", type=float, default=1.0,
+                    help="chromosome length scale of the --impl reference workload "
+                         "(1.0 = the GPU arm's workload)")
+    ap.add_argument("--cpu-budget", type=float, default=60.0,
+                    help="seconds the C1 legs of cpu_baseline may take")
+    ap.add_argument("--no-c5", action="store_true",
+                    help="skip the 1 Gbp pangenome block")
     ap.add_argument("--no-cpu", action="store_true",
                     help="skip the cpu_baseline leg")
     ap.add_argument("--profile", action="store_true",

@@ -681,7 +681,14 @@ class DistAnchorFinder:
             n_positions=self.n_job_bases, local_fragments=s["n_fragments"],
             local_records=s["n_windows"], total_selected=int(tot_all[:, 0].sum()),
             exchange_ms=dict(self.exchange_ms), exchange=self.exchange,
-            host_ms=trace, bucket_cuts=[int(c) for c in cuts])
+            host_ms=trace, bucket_cuts=[int(c) for c in cuts],
+            # records this rank wrote into other ranks' HBM, and the device time of
+            # the stage that moved them (bulk: the copy kernels; peer: pass A itself)
+            nvlink_bytes_sent=int(hist.sum() - hist[int(cuts[self.rank]):int(cuts[self.rank + 1])].sum())
+            * (12 if k > 21 else 8),
+            nvlink_ms=(s["ms_pass"][5] if self.exchange == "bulk"
+                       else s["ms_pass"][0] if self.exchange == "peer"
+                       else self.exchange_ms.get("records", 0.0)))
         self._last = out
         if job_stats:
             self.job_stats()
@@ -692,13 +699,17 @@ class DistAnchorFinder:
         launches and digest (collective)."""
         s, out = self.local_stats, self._last
         dev = self.comm.torch.device("cuda", self.device) if self.comm.nccl else None
-        d = np.asarray([s["n_blocks"], s["gpu_launches"]], dtype=np.int64)
+        d = np.asarray([s["n_blocks"], s["gpu_launches"], s.get("bytes_algorithmic", 0),
+                        s.get("bytes_moved", 0), s["n_fragments"]], dtype=np.int64)
         dg = np.asarray([s["digest"][0], s["digest"][1]], dtype=np.uint64).view(np.int64)
         job = self.comm.gather_array(np.concatenate([d, dg]), dev)
         mask = (1 << 64) - 1
         out.update(n_blocks=int(job[:, 0].sum()), job_launches=int(job[:, 1].sum()),
-                   digest=(sum(int(x) & mask for x in job[:, 2]) & mask,
-                           sum(int(x) & mask for x in job[:, 3]) & mask))
+                   bytes_algorithmic_job=int(job[:, 2].sum()),
+                   bytes_moved_job=int(job[:, 3].sum()),
+                   n_fragments=int(job[:, 4].sum()),
+                   digest=(sum(int(x) & mask for x in job[:, 5]) & mask,
+                           sum(int(x) & mask for x in job[:, 6]) & mask))
         return out
 
     def fetch(self):
