@@ -274,12 +274,29 @@ def test_gpu_block_hashes_errors(engine):
     with pytest.raises(AnchorError) as e:      # offsets not ascending
         engine.block_hashes(["a", "b"], np.array([0, 2, 1], np.uint64), seq, mn, ori, frag_len=4)
     assert e.value.code == _abi.ERR_PARAMS
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("limit", [7, 8, 9, 300, 1001])
+def test_gpu_block_hashes_after_a_cut(engine, limit):
+    """max-anchor-fragments cuts the list inside a block: find_device patches the
+    resident result (reference order inside the cut group, a lone tail dropped), so
+    the device-side hashes equal those of the fetched arrays."""
     names, seqs = synth.generate("tiny")
     engine.upload(seqs, 20)
-    engine.find_device(20, similar=False, max_frags=7)   # cut inside the list
-    with pytest.raises(AnchorError) as e:
-        engine.anchor_block_hashes(names)
-    assert e.value.code == _abi.ERR_STATE
+    for similar in (False, True):
+        st = engine.find_device(20, similar=similar, max_frags=limit)
+        want_r = oracle.find_ideal(seqs, 20, similar=similar, max_frags=limit)
+        assert (st["n_fragments"], st["n_blocks"], st["digest"]) == (
+            want_r.n_fragments, want_r.n_blocks, want_r.digest)
+        got, total = engine.anchor_block_hashes(names)
+        r = engine.fetch()
+        assert r.blocks() == want_r.blocks() and r.digest == want_r.digest
+        assert list(r.new_used) == list(want_r.new_used)
+        offs = np.asarray(r.block_offsets, np.uint64)
+        mn = np.asarray(r.frag_min_pos, np.uint32)
+        want = oracle.block_hashes(names, offs, r.frag_seq, mn, mn + np.uint32(19), r.frag_ori)
+        assert len(got) == r.n_blocks and np.array_equal(got, want)
 
 
 # ---- the C++ processor npge::gpu::MoveUnchanged ---------------------------------------------
