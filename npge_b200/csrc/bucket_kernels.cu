@@ -47,7 +47,6 @@ __device__ __forceinline__ bool found_bit(const BucketArgs& a, uint32_t g) {
 
 template <bool WIDE>
 struct __align__(16) BucketSmem {
-    RankSmem<8> rk;
     uint32_t grun[256];       // slow path: running digit bases of the unit
     uint64_t warp_tot[kRW];
     int32_t warp_head[kRW];
@@ -60,7 +59,13 @@ struct __align__(16) BucketSmem {
         uint64_t buf[kCap + 2];
         uint32_t hib[WIDE ? kCap + 2 : 4];
     } half[2];
-    static constexpr size_t kSingle() { return sizeof(BucketSmem) - sizeof(Half); }
+    // ranking scratch of the sort kernel: byte digits, and the wider last digit
+    // (key bits + bin index inside the unit)
+    union {
+        RankSmem<8> rk;
+        RankSmem<10> rk10;
+    };
+    static constexpr size_t kSingle() { return sizeof(BucketSmem) - sizeof(Half) - sizeof(RankSmem<10>); }
 };
 
 // One sorted chunk of a unit in shared memory: records at K[1 .. cn], halo
@@ -354,21 +359,32 @@ unit_build_kernel(BucketArgs a, uint32_t* __restrict__ unit_cnt) {
         for (int o = 16; o > 0; o >>= 1) out += __shfl_xor_sync(0xffffffffu, out, o);
     }
     const uint32_t end_all = fs[nb];
+    const uint32_t max_bins = 1u << a.plan.bin_bits;  // the sort ranks by bin inside a unit
     uint32_t cur = 0, count = 0;
     while (cur < nb) {
         const uint32_t s = fs[cur];
         if (s == end_all) break;  // only empty bins are left
+        {   // skip empty bins: a unit starts with a record
+            const uint32_t probe = cur + lane;
+            const uint32_t m = __ballot_sync(0xffffffffu, probe < nb && fs[probe + 1] == s);
+            const int run = m == 0xffffffffu ? 32 : __ffs(~m) - 1;
+            if (run) {
+                cur += run;
+                continue;
+            }
+        }
         uint32_t e = cur + 1;     // the unit is [cur, e); grows while it fits
         while (true) {
             const uint32_t probe = e + lane;  // candidate bin to add: [cur, probe]
-            const bool fits = probe < nb && fs[probe + 1] - s <= uint32_t(kCap);
+            const bool fits = probe < nb && probe - cur < max_bins &&
+                              fs[probe + 1] - s <= uint32_t(kCap);
             const uint32_t m = __ballot_sync(0xffffffffu, fits);
             const int run = m == 0xffffffffu ? 32 : __ffs(~m) - 1;
             e += run;
             if (run < 32) break;
         }
         if (WRITE && lane == 0) {
-            a.units[out + count] = make_uint4(s, fs[e] - s, ab, 0u);
+            a.units[out + count] = make_uint4(s, fs[e] - s, ab, cur);
         }
         count++;
         cur = e;
@@ -384,7 +400,7 @@ unit_build_kernel(BucketArgs a, uint32_t* __restrict__ unit_cnt) {
 template <bool WIDE>
 __device__ __forceinline__ bool unit_of_window(BucketSmem<WIDE>& sm, const BucketArgs& a,
                                                uint32_t w, uint32_t& s, uint32_t& n,
-                                               uint64_t& key_hi) {
+                                               uint64_t& key_hi, uint32_t* bin0 = nullptr) {
     if (w >= a.counters[kCntWindows]) return false;
     const uint4 u = a.units[w];
     if (threadIdx.x == 0) sm.cut = 0;
@@ -392,6 +408,7 @@ __device__ __forceinline__ bool unit_of_window(BucketSmem<WIDE>& sm, const Bucke
     s = u.x;
     n = u.y;
     key_hi = uint64_t(u.z) << a.plan.rem;
+    if (bin0) *bin0 = u.w;  // B digit of the unit's first bin
     return true;
 }
 
@@ -427,17 +444,19 @@ __device__ __forceinline__ void store_unit(BucketSmem<WIDE>& sm, const BucketArg
     }
 }
 
-// LSD radix sort of sm.half[0].buf[1..n] by the low `rem` key bits, byte digits,
-// stable.  Returns the buffer holding the result.  Contains barriers.
+// LSD radix sort of sm.half[0].buf[1..n], whose records arrive sorted by bin, by
+// the `low` key bits below the B digit: stable byte passes, the last one ranking by
+// (bin index inside the unit, remaining key bits) so that the bin order survives.
+// Returns the buffer holding the result.  Contains barriers.
 template <bool WIDE>
 __device__ __forceinline__ int sort_unit_smem(BucketSmem<WIDE>& sm, const MsdPlan& pl,
-                                              uint32_t n) {
+                                              uint32_t n, uint32_t bin0) {
     const int warp = threadIdx.x >> 5;
     const uint32_t first = warp * (32 * kRI);
     const int rounds = first >= n ? 0 : int(min(uint32_t(kRI), (n - first + 31) / 32));
     int cur = 0;
 #pragma unroll 1
-    for (int pass = 0; pass < pl.smem_passes; pass++) {
+    for (int pass = 0; pass + 1 < pl.smem_passes; pass++) {
         uint64_t rec[kRI];
         uint32_t hi[kRI], digit[kRI], slot[kRI];
 #pragma unroll
@@ -452,7 +471,41 @@ __device__ __forceinline__ int sort_unit_smem(BucketSmem<WIDE>& sm, const MsdPla
         tile_rank<8>(sm.rk, digit, rounds, slot, c0, c1);
 #pragma unroll
         for (int i = 0; i < kRI; i++) {
-            if (digit[i] < 256u) {
+            if (item_index(i) < n) {
+                sm.half[cur ^ 1].buf[1 + slot[i]] = rec[i];
+                if (WIDE) sm.half[cur ^ 1].hib[1 + slot[i]] = hi[i];
+            }
+        }
+        __syncthreads();
+        cur ^= 1;
+    }
+    if (pl.smem_passes > 0) {
+        const int shift = 8 * (pl.smem_passes - 1);
+        const uint32_t kmask = (1u << pl.last_bits) - 1, bmask = (1u << pl.wb) - 1;
+        const bool narrow = pl.last_bits + pl.bin_bits <= 8;  // block-uniform
+        uint64_t rec[kRI];
+        uint32_t hi[kRI], digit[kRI], slot[kRI];
+#pragma unroll
+        for (int i = 0; i < kRI; i++) {
+            const uint32_t j = item_index(i);
+            const bool in = j < n;
+            rec[i] = in ? sm.half[cur].buf[1 + j] : 0ull;
+            hi[i] = (WIDE && in) ? sm.half[cur].hib[1 + j] : 0u;
+            const uint64_t kr = rem_key(rec[i], hi[i]);
+            const uint32_t bin = (uint32_t(kr >> pl.low) & bmask) - bin0;
+            digit[i] = in ? ((bin << pl.last_bits) | (uint32_t(kr >> shift) & kmask))
+                          : (narrow ? 256u : 1024u);
+        }
+        uint32_t c0, c1;
+        if (narrow) {
+            tile_rank<8>(sm.rk, digit, rounds, slot, c0, c1);
+        } else {
+            tile_rank<10>(sm.rk10, digit, rounds, slot, c0, c1);
+        }
+#pragma unroll
+        for (int i = 0; i < kRI; i++) {
+            const uint32_t j = item_index(i);
+            if (j < n) {
                 sm.half[cur ^ 1].buf[1 + slot[i]] = rec[i];
                 if (WIDE) sm.half[cur ^ 1].hib[1 + slot[i]] = hi[i];
             }
@@ -475,7 +528,7 @@ __device__ void sort_unit_global(BucketSmem<WIDE>& sm, const BucketArgs& a, uint
     uint64_t* dst = a.scratch_rec;
     uint32_t* dsth = a.scratch_hi;
 #pragma unroll 1
-    for (int pass = 0; pass < pl.smem_passes; pass++) {
+    for (int pass = 0; pass < pl.slow_passes; pass++) {  // one bin: only the low bits differ
         const int shift = 8 * pass;
         __syncthreads();
         if (tid < 256) sm.grun[tid] = 0;
@@ -614,15 +667,15 @@ bucket_sort_kernel(BucketArgs a) {
     extern __shared__ __align__(16) unsigned char raw[];
     BucketSmem<WIDE>& sm = *reinterpret_cast<BucketSmem<WIDE>*>(raw);
     const uint32_t w = blockIdx.x;
-    uint32_t s, n;
+    uint32_t s, n, bin0;
     uint64_t key_hi;
-    if (!unit_of_window<WIDE>(sm, a, w, s, n, key_hi)) return;
+    if (!unit_of_window<WIDE>(sm, a, w, s, n, key_hi, &bin0)) return;
     Chunk<WIDE> ch;
     uint32_t valid, preveq, inb, sel;
     uint64_t tot = 0;
     if (n <= uint32_t(kCap)) {
         load_unit<WIDE>(sm, a, s, n);
-        const int cur = sort_unit_smem<WIDE>(sm, a.plan, n);
+        const int cur = sort_unit_smem<WIDE>(sm, a.plan, n, bin0);
         whole_unit_chunk<WIDE>(sm, s, n, cur, ch);
         unit_flags<WIDE>(ch, valid, preveq, inb);
         if (MODE == 1) {
@@ -796,7 +849,14 @@ size_t bucket_summary_words() { return kSumWords + kPartials * 4; }
 // upper bound on the units of the bucket sort (two neighbours never fit in one):
 // the grid of its kernels and the size of the unit tables
 uint32_t bucket_max_windows(const MsdPlan& plan, uint64_t max_records) {
-    return uint32_t((max_records + kWindow - 1) / kWindow) + (2u << plan.capa) + 1;
+    // a unit that is not the last of its bucket is either full (it and its successor
+    // hold more than kCap records together) or holds 1 << bin_bits bins; it never
+    // outnumbers the records either
+    const uint64_t by_size = (max_records + kWindow - 1) / kWindow;
+    const uint64_t by_bins = ((uint64_t(1) << (plan.wa + plan.wb)) >> plan.bin_bits) + 1;
+    uint64_t n = by_size + by_bins;
+    if (n > max_records) n = max_records;
+    return uint32_t(n + (2u << plan.capa) + 1);
 }
 
 // The stages of the bucket sort, one launcher each so that the multi-GPU driver

@@ -37,7 +37,13 @@ struct MsdPlan {
     int k = 0, total = 0, wa = 0, wb = 0, rem = 0;
     int capa = 8, capb = 8;  // histogram rows hold 1 << cap bins
     int wide = 0;            // rem > 32: records carry a second u32 of key bits
-    int smem_passes = 0;
+    // shared-memory sort of a unit: the `low` = rem - wb key bits below the B digit
+    // in `smem_passes` stable passes; all but the last take a byte, the last takes
+    // the remaining `last_bits` key bits TOGETHER with the record's bin index inside
+    // the unit (`bin_bits` bits, so a unit holds at most 1 << bin_bits bins): the
+    // records arrive sorted by bin, and this way no pass is spent on restoring that
+    int low = 0, smem_passes = 0, last_bits = 0, bin_bits = 0;
+    int slow_passes = 0;     // oversized unit (one bin): byte passes over `low` bits
 };
 
 constexpr int kBucketCap = kTile;        // records one CTA sorts in shared memory

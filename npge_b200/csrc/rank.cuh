@@ -76,7 +76,7 @@ __device__ __forceinline__ void stage_genome_tile(GenomeStage& st,
 template <int CAPBITS>
 struct __align__(16) RankSmem {
     static constexpr int BINS = 1 << CAPBITS;
-    uint16_t warp_hist[kRW][BINS];  // per-warp digit counts, then warp offsets
+    uint16_t warp_hist[kRW][BINS];  // per-warp digit counts, then the first slot of (warp, digit)
     uint32_t tile_off[BINS];        // first slot of the digit in tile-sorted order
     uint32_t scan_tmp[kRW];
     uint32_t total;                 // items in the tile
@@ -148,27 +148,35 @@ __device__ __forceinline__ void tile_rank(RankSmem<CAPBITS>& sm,
     } else {
         warp_rank<CAPBITS, false>(sm, digit, rounds, rank);
     }
+    // digit and rank share a register from here on (digit <= 1024, rank <= 256):
+    // a caller that does not read digit[] after the call frees its registers
+    uint32_t dr[kRI];
+#pragma unroll
+    for (int i = 0; i < kRI; i++) dr[i] = digit[i] | (rank[i] << 16);
     __syncthreads();
+    // column scan: the thread owning a digit walks the kRW per-warp counts and
+    // keeps their exclusive prefixes in registers (two 16-bit values per word);
+    // once the digit's first slot is known it writes back, per warp, the ABSOLUTE
+    // first slot of (warp, digit): one lookup per item afterwards
     c0 = 0;
     c1 = 0;
+    uint32_t pre[PER == 2 ? kRW : kRW / 2];
     if (PER == 2) {
         uint32_t run = 0;  // two packed 16-bit running sums (each <= kTile)
 #pragma unroll
         for (int w = 0; w < kRW; w++) {
-            uint32_t* p = reinterpret_cast<uint32_t*>(sm.warp_hist[w]) + tid;
-            uint32_t v = *p;
-            *p = run;
-            run += v;
+            pre[w] = run;
+            run += reinterpret_cast<const uint32_t*>(sm.warp_hist[w])[tid];
         }
         c0 = run & 0xffff;
         c1 = run >> 16;
     } else if (tid < BINS) {
         uint32_t run = 0;
 #pragma unroll
-        for (int w = 0; w < kRW; w++) {
-            uint32_t v = sm.warp_hist[w][tid];
-            sm.warp_hist[w][tid] = uint16_t(run);
-            run += v;
+        for (int w = 0; w < kRW; w += 2) {
+            const uint32_t v0 = sm.warp_hist[w][tid], v1 = sm.warp_hist[w + 1][tid];
+            pre[w / 2] = run | ((run + v0) << 16);
+            run += v0 + v1;
         }
         c0 = run;
     }
@@ -189,15 +197,25 @@ __device__ __forceinline__ void tile_rank(RankSmem<CAPBITS>& sm,
     if (PER == 2) {
         sm.tile_off[2 * tid] = toff0;
         sm.tile_off[2 * tid + 1] = toff0 + c0;
+        const uint32_t add = toff0 | ((toff0 + c0) << 16);  // no carry: slots <= kTile
+#pragma unroll
+        for (int w = 0; w < kRW; w++) {
+            reinterpret_cast<uint32_t*>(sm.warp_hist[w])[tid] = pre[w] + add;
+        }
     } else if (tid < BINS) {
         sm.tile_off[tid] = toff0;
+#pragma unroll
+        for (int w = 0; w < kRW; w += 2) {
+            sm.warp_hist[w][tid] = uint16_t(toff0 + (pre[w / 2] & 0xffff));
+            sm.warp_hist[w + 1][tid] = uint16_t(toff0 + (pre[w / 2] >> 16));
+        }
     }
     if (tid == kRT - 1) sm.total = toff0 + mine;
     __syncthreads();
 #pragma unroll
     for (int i = 0; i < kRI; i++) {
-        const uint32_t d = digit[i];
-        slot[i] = d < BINS ? sm.tile_off[d] + sm.warp_hist[warp][d] + rank[i] : 0u;
+        const uint32_t d = dr[i] & 0xffffu;
+        slot[i] = d < BINS ? sm.warp_hist[warp][d] + (dr[i] >> 16) : 0u;
     }
 }
 
