@@ -4,7 +4,9 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libnpge_anchor.so")
+# NPGE_ANCHOR_LIB: another build of the same library (kernel experiments, build.py
+# build_variant); the product default is the in-tree libnpge_anchor.so
+LIB_PATH = os.environ.get("NPGE_ANCHOR_LIB") or os.path.join(_HERE, "libnpge_anchor.so")
 
 EXPORTS = [
     "npge_anchor_create", "npge_anchor_destroy", "npge_anchor_last_error",

@@ -23,6 +23,17 @@ def stale():
                for f in SOURCES + HEADERS)
 
 
+def build_variant(name, defines):
+    """libnpge_anchor_<name>.so with extra -D flags: kernel experiments that are
+    compared on the GPU box in one session (NPGE_ANCHOR_LIB selects it in _abi)."""
+    out = os.path.join(HERE, "libnpge_anchor_%s.so" % name)
+    nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+    cmd = [nvcc] + NVCC_FLAGS + ["-D" + d for d in defines] + ["-o", out] + \
+        [os.path.join(CSRC, f) for f in SOURCES]
+    subprocess.check_call(cmd)
+    return out
+
+
 def build(force=False, verbose=False):
     if not force and not stale():
         return LIB

@@ -61,11 +61,16 @@ struct __align__(16) BucketSmem {
     } half[2];
     // ranking scratch of the sort kernel: byte digits, and the wider last digit
     // (key bits + bin index inside the unit)
+#if NPGE_BIN_LAST
     union {
         RankSmem<8> rk;
         RankSmem<10> rk10;
     };
     static constexpr size_t kSingle() { return sizeof(BucketSmem) - sizeof(Half) - sizeof(RankSmem<10>); }
+#else
+    RankSmem<8> rk;
+    static constexpr size_t kSingle() { return sizeof(BucketSmem) - sizeof(Half) - sizeof(RankSmem<8>); }
+#endif
 };
 
 // One sorted chunk of a unit in shared memory: records at K[1 .. cn], halo
@@ -359,7 +364,8 @@ unit_build_kernel(BucketArgs a, uint32_t* __restrict__ unit_cnt) {
         for (int o = 16; o > 0; o >>= 1) out += __shfl_xor_sync(0xffffffffu, out, o);
     }
     const uint32_t end_all = fs[nb];
-    const uint32_t max_bins = 1u << a.plan.bin_bits;  // the sort ranks by bin inside a unit
+    // the sort may rank by bin inside a unit: then a unit holds max_bins bins at most
+    const uint32_t max_bins = a.plan.max_bins ? uint32_t(a.plan.max_bins) : 0xffffffffu;
     uint32_t cur = 0, count = 0;
     while (cur < nb) {
         const uint32_t s = fs[cur];
@@ -384,7 +390,7 @@ unit_build_kernel(BucketArgs a, uint32_t* __restrict__ unit_cnt) {
             if (run < 32) break;
         }
         if (WRITE && lane == 0) {
-            a.units[out + count] = make_uint4(s, fs[e] - s, ab, cur);
+            a.units[out + count] = make_uint4(s, fs[e] - s, ab, a.plan.max_bins ? cur : 0u);
         }
         count++;
         cur = e;
@@ -492,16 +498,17 @@ __device__ __forceinline__ int sort_unit_smem(BucketSmem<WIDE>& sm, const MsdPla
             rec[i] = in ? sm.half[cur].buf[1 + j] : 0ull;
             hi[i] = (WIDE && in) ? sm.half[cur].hib[1 + j] : 0u;
             const uint64_t kr = rem_key(rec[i], hi[i]);
-            const uint32_t bin = (uint32_t(kr >> pl.low) & bmask) - bin0;
+            const uint32_t bin = pl.max_bins ? (uint32_t(kr >> pl.low) & bmask) - bin0 : 0u;
             digit[i] = in ? ((bin << pl.last_bits) | (uint32_t(kr >> shift) & kmask))
                           : (narrow ? 256u : 1024u);
         }
         uint32_t c0, c1;
-        if (narrow) {
-            tile_rank<8>(sm.rk, digit, rounds, slot, c0, c1);
-        } else {
+#if NPGE_BIN_LAST
+        if (!narrow) {
             tile_rank<10>(sm.rk10, digit, rounds, slot, c0, c1);
-        }
+        } else
+#endif
+        tile_rank<8>(sm.rk, digit, rounds, slot, c0, c1);
 #pragma unroll
         for (int i = 0; i < kRI; i++) {
             const uint32_t j = item_index(i);
@@ -853,7 +860,8 @@ uint32_t bucket_max_windows(const MsdPlan& plan, uint64_t max_records) {
     // hold more than kCap records together) or holds 1 << bin_bits bins; it never
     // outnumbers the records either
     const uint64_t by_size = (max_records + kWindow - 1) / kWindow;
-    const uint64_t by_bins = ((uint64_t(1) << (plan.wa + plan.wb)) >> plan.bin_bits) + 1;
+    const uint64_t by_bins =
+        plan.max_bins ? ((uint64_t(1) << (plan.wa + plan.wb)) >> plan.bin_bits) + 1 : 0;
     uint64_t n = by_size + by_bins;
     if (n > max_records) n = max_records;
     return uint32_t(n + (2u << plan.capa) + 1);

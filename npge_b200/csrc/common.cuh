@@ -24,8 +24,16 @@ namespace npge_b200 {
 // make_hash (make_hash.hpp:29-42): the forward hash of the window at g is bits
 // [2g, 2g+2k) of the packed stream.
 
-constexpr int kSortThreads = 512;
-constexpr int kSortItems = 8;
+#ifndef NPGE_SORT_THREADS
+#define NPGE_SORT_THREADS 512
+#endif
+constexpr int kSortThreads = NPGE_SORT_THREADS;
+constexpr int kSortItems = 4096 / NPGE_SORT_THREADS;
+// the bucket sort ranks its last digit together with the bin index inside the unit
+// (one pass fewer, 1024 counters in that pass): measured slower, kept as a variant
+#ifndef NPGE_BIN_LAST
+#define NPGE_BIN_LAST 0
+#endif
 constexpr int kTile = kSortThreads * kSortItems;  // 4096 records / positions
 constexpr int kMaxDigitBits = 10;                 // widest partition digit
 constexpr int kMaxPasses = 16;                    // event slots per find
@@ -44,6 +52,7 @@ struct MsdPlan {
     // records arrive sorted by bin, and this way no pass is spent on restoring that
     int low = 0, smem_passes = 0, last_bits = 0, bin_bits = 0;
     int slow_passes = 0;     // oversized unit (one bin): byte passes over `low` bits
+    int max_bins = 0;        // bins per unit (0: no limit)
 };
 
 constexpr int kBucketCap = kTile;        // records one CTA sorts in shared memory

@@ -52,12 +52,23 @@ MsdPlan make_msd_plan(int k, uint64_t n_positions, int force_f, int force_wa) {
     p.wide = p.rem > 32;
     p.capa = wa <= 8 ? 8 : (wa == 9 ? 9 : 10);  // histogram rows of 256 / 512 / 1024 bins
     p.capb = wb <= 8 ? 8 : (wb == 9 ? 9 : 10);
+#if NPGE_BIN_LAST
     p.low = p.rem - wb;
     p.slow_passes = (p.low + 7) / 8;
     p.smem_passes = p.slow_passes;
     p.last_bits = p.low - 8 * (p.smem_passes - 1);  // 1..8 (0 passes: unused)
     if (p.smem_passes == 0) p.last_bits = 0;
     p.bin_bits = 10 - p.last_bits < 4 ? 10 - p.last_bits : 4;
+    p.max_bins = 1 << p.bin_bits;
+#else
+    // byte passes over all rem bits: the top one(s) restore the bin order
+    p.low = p.rem;
+    p.slow_passes = (p.rem - wb + 7) / 8;
+    p.smem_passes = (p.rem + 7) / 8;
+    p.last_bits = 8;
+    p.bin_bits = 0;
+    p.max_bins = 0;
+#endif
     return p;
 }
 
@@ -260,8 +271,11 @@ struct __align__(16) PassSmem {
 // registers let four CTAs share an SM; the kernel is latency-bound, occupancy pays
 // (measured on brucella17: 0.545 ms at 2 CTAs, 0.483 at 3, 0.467 at 4; pass B is
 // best at 3: 0.608 / 0.495 / 0.522).
+#ifndef NPGE_PASS_A_CTAS
+#define NPGE_PASS_A_CTAS 4
+#endif
 template <int CAPBITS, bool WIDE, bool GLOBAL>
-__global__ void __launch_bounds__(kRT, WIDE ? 2 : (CAPBITS == 8 ? 4 : (CAPBITS == 9 ? 3 : 2)))
+__global__ void __launch_bounds__(kRT, WIDE ? 2 : (CAPBITS == 8 ? NPGE_PASS_A_CTAS : (CAPBITS == 9 ? 3 : 2)))
 pass_a_kernel(const uint32_t* __restrict__ packed, const uint32_t* __restrict__ nmask,
               MsdPlan plan, const uint32_t* __restrict__ rows, PosMap pm,
               uint64_t* __restrict__ out_rec, uint32_t* __restrict__ out_hi) {
@@ -287,8 +301,10 @@ pass_a_kernel(const uint32_t* __restrict__ packed, const uint32_t* __restrict__ 
     const uint64_t rmask = (1ull << plan.rem) - 1;  // rem <= 63
     const bool one_seq = GLOBAL && sm.tile_seq[0] == sm.tile_seq[1];
     const uint32_t delta0 = one_seq ? pm.delta[sm.tile_seq[0]] : 0u;
-    uint64_t rec[kRI];
-    uint32_t hi[kRI], digit[kRI], slot[kRI];
+    // only the key bits stay in registers across the ranking: the payload (position
+    // and strand bit) is rebuilt when the record is written into the sorted tile
+    uint32_t klo[kRI], hi[kRI], digit[kRI], slot[kRI];
+    uint32_t obits = 0;
 #pragma unroll
     for (int i = 0; i < kRI; i++) {
         uint32_t rel = warp * (32 * kRI) + i * 32 + lane;
@@ -296,21 +312,9 @@ pass_a_kernel(const uint32_t* __restrict__ packed, const uint32_t* __restrict__ 
         uint32_t ob;
         bool ok = window_key(sm.st, rel, plan.k, h, ob);
         uint64_t kr = h & rmask;
-        // payload: position << 1 | (ori == +1)
-        uint32_t g = gbase + rel;
-        if (GLOBAL && one_seq) {
-            g += delta0;
-        } else if (GLOBAL && ok) {
-            const uint32_t q = g >> pm.lut_shift;
-            uint32_t lo = pm.lut[q], hi2 = pm.lut[q + 1] + 1;  // answer in [lo, hi2)
-            while (hi2 - lo > 1) {
-                uint32_t mid = (lo + hi2) >> 1;
-                if (pm.seq_start[mid] <= g) lo = mid; else hi2 = mid;
-            }
-            g += pm.delta[lo];
-        }
-        rec[i] = (uint64_t(uint32_t(kr)) << 32) | ((g << 1) | ob);
+        klo[i] = uint32_t(kr);
         hi[i] = uint32_t(kr >> 32);
+        obits |= ob << i;
         digit[i] = ok ? uint32_t(h >> sa) : uint32_t(BINS);
     }
     uint32_t c0, c1;
@@ -325,7 +329,20 @@ pass_a_kernel(const uint32_t* __restrict__ packed, const uint32_t* __restrict__ 
 #pragma unroll
     for (int i = 0; i < kRI; i++) {
         if (digit[i] < BINS) {
-            sm.rec[slot[i]] = rec[i];
+            // payload: position << 1 | (ori == +1)
+            uint32_t g = gbase + warp * (32 * kRI) + i * 32 + lane;
+            if (GLOBAL && one_seq) {
+                g += delta0;
+            } else if (GLOBAL) {
+                const uint32_t q = g >> pm.lut_shift;
+                uint32_t lo = pm.lut[q], hi2 = pm.lut[q + 1] + 1;  // answer in [lo, hi2)
+                while (hi2 - lo > 1) {
+                    uint32_t mid = (lo + hi2) >> 1;
+                    if (pm.seq_start[mid] <= g) lo = mid; else hi2 = mid;
+                }
+                g += pm.delta[lo];
+            }
+            sm.rec[slot[i]] = (uint64_t(klo[i]) << 32) | ((g << 1) | ((obits >> i) & 1u));
             if (WIDE) sm.hi[slot[i]] = hi[i];
             sm.dig[slot[i]] = uint16_t(digit[i]);
         }

@@ -85,6 +85,66 @@ struct __align__(16) RankSmem {
 // Rank of every item among the items of its own warp with the same digit, and
 // the warp's digit counts in sm.warp_hist[warp].  FULL: all kRI rounds hold
 // items (straight-line code); otherwise rounds >= `rounds` are skipped.
+#ifndef NPGE_RANK_ATOMIC
+#define NPGE_RANK_ATOMIC 1
+#endif
+#ifndef NPGE_RANK_BATCH
+#define NPGE_RANK_BATCH 4
+#endif
+#if NPGE_RANK_ATOMIC
+// The leader of every group of equal digits (match.any) adds the group's size to
+// the warp's counter with ONE shared-memory atomic that returns the count of the
+// earlier rounds.  Two 16-bit counters share a word (a warp holds 32 * kRI = 256
+// items: the low half never carries).  The atomics of the kRI rounds do not depend
+// on one another, so their latencies overlap; the rounds stay ordered because the
+// warp reconverges between them and shared memory executes in order.
+template <int CAPBITS, bool FULL>
+__device__ __forceinline__ void warp_rank(RankSmem<CAPBITS>& sm,
+                                          const uint32_t (&digit)[kRI], int rounds,
+                                          uint32_t (&rank)[kRI]) {
+    constexpr int BINS = 1 << CAPBITS;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t lt = (1u << lane) - 1;
+    uint32_t* wh = reinterpret_cast<uint32_t*>(sm.warp_hist[warp]);
+    // in batches of kBatch rounds (registers: two words per round in flight)
+    constexpr int kBatch = NPGE_RANK_BATCH < kRI ? NPGE_RANK_BATCH : kRI;
+#pragma unroll
+    for (int b = 0; b < kRI; b += kBatch) {
+        uint32_t info[kBatch];  // leader lane | items before this lane << 8 | group size << 16
+        uint32_t old[kBatch];
+#pragma unroll
+        for (int j = 0; j < kBatch; j++) {
+            const int i = b + j;
+            info[j] = 0;
+            if (FULL || i < rounds) {
+                const uint32_t p = __match_any_sync(0xffffffffu, digit[i]);
+                info[j] = uint32_t(__ffs(p) - 1) | (__popc(p & lt) << 8) | (__popc(p) << 16);
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < kBatch; j++) {
+            const int i = b + j;
+            old[j] = 0;
+            if (FULL || i < rounds) {
+                const uint32_t d = digit[i];
+                if (lane == int(info[j] & 0xff) && d < BINS) {
+                    old[j] = atomicAdd(&wh[d >> 1], (info[j] >> 16) << (16 * (d & 1)));
+                }
+                __syncwarp();
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < kBatch; j++) {
+            const int i = b + j;
+            rank[i] = 0;
+            if (FULL || i < rounds) {
+                const uint32_t o = __shfl_sync(0xffffffffu, old[j], info[j] & 0xff);
+                rank[i] = ((o >> (16 * (digit[i] & 1))) & 0xffffu) + ((info[j] >> 8) & 0xff);
+            }
+        }
+    }
+}
+#else
 template <int CAPBITS, bool FULL>
 __device__ __forceinline__ void warp_rank(RankSmem<CAPBITS>& sm,
                                           const uint32_t (&digit)[kRI], int rounds,
@@ -115,6 +175,7 @@ __device__ __forceinline__ void warp_rank(RankSmem<CAPBITS>& sm,
         }
     }
 }
+#endif
 
 // Stable rank of the tile's items by digit.  Item i of lane l of warp w is
 // element w * 32 * kRI + i * 32 + l of the tile (ascending input order);
@@ -127,6 +188,10 @@ __device__ __forceinline__ void warp_rank(RankSmem<CAPBITS>& sm,
 // All match.any of a thread are issued back to back: the instruction has
 // ~200 cycles of latency on sm_100a (profiles/r01b_*), so the rounds must
 // overlap; only the counter updates are ordered.
+#ifndef NPGE_RANK_ABS
+#define NPGE_RANK_ABS 0
+#endif
+#if NPGE_RANK_ABS
 template <int CAPBITS>
 __device__ __forceinline__ void tile_rank(RankSmem<CAPBITS>& sm,
                                           const uint32_t (&digit)[kRI], int rounds,
@@ -218,5 +283,82 @@ __device__ __forceinline__ void tile_rank(RankSmem<CAPBITS>& sm,
         slot[i] = d < BINS ? sm.warp_hist[warp][d] + (dr[i] >> 16) : 0u;
     }
 }
+
+#else
+template <int CAPBITS>
+__device__ __forceinline__ void tile_rank(RankSmem<CAPBITS>& sm,
+                                          const uint32_t (&digit)[kRI], int rounds,
+                                          uint32_t (&slot)[kRI], uint32_t& c0,
+                                          uint32_t& c1) {
+    constexpr int BINS = 1 << CAPBITS;
+    constexpr int PER = BINS / kRT > 0 ? BINS / kRT : 1;
+    static_assert(PER == 1 || PER == 2, "one or two digits per thread");
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    {
+        uint4* wh = reinterpret_cast<uint4*>(sm.warp_hist[warp]);
+#pragma unroll
+        for (int i = 0; i < BINS / 256; i++) wh[lane + 32 * i] = make_uint4(0, 0, 0, 0);
+    }
+    __syncwarp();
+    uint32_t rank[kRI];
+    if (rounds == kRI) {
+        warp_rank<CAPBITS, true>(sm, digit, rounds, rank);
+    } else {
+        warp_rank<CAPBITS, false>(sm, digit, rounds, rank);
+    }
+    __syncthreads();
+    c0 = 0;
+    c1 = 0;
+    if (PER == 2) {
+        uint32_t run = 0;  // two packed 16-bit running sums (each <= kTile)
+#pragma unroll
+        for (int w = 0; w < kRW; w++) {
+            uint32_t* p = reinterpret_cast<uint32_t*>(sm.warp_hist[w]) + tid;
+            uint32_t v = *p;
+            *p = run;
+            run += v;
+        }
+        c0 = run & 0xffff;
+        c1 = run >> 16;
+    } else if (tid < BINS) {
+        uint32_t run = 0;
+#pragma unroll
+        for (int w = 0; w < kRW; w++) {
+            uint32_t v = sm.warp_hist[w][tid];
+            sm.warp_hist[w][tid] = uint16_t(run);
+            run += v;
+        }
+        c0 = run;
+    }
+    const uint32_t mine = c0 + c1;
+    uint32_t incl = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        uint32_t u = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += u;
+    }
+    if (lane == 31) sm.scan_tmp[warp] = incl;
+    __syncthreads();
+    // sum of the totals of the warps before this one: one load + a butterfly
+    uint32_t wbase = (lane < kRW && lane < warp) ? sm.scan_tmp[lane] : 0u;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) wbase += __shfl_xor_sync(0xffffffffu, wbase, o);
+    const uint32_t toff0 = wbase + incl - mine;
+    if (PER == 2) {
+        sm.tile_off[2 * tid] = toff0;
+        sm.tile_off[2 * tid + 1] = toff0 + c0;
+    } else if (tid < BINS) {
+        sm.tile_off[tid] = toff0;
+    }
+    if (tid == kRT - 1) sm.total = toff0 + mine;
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < kRI; i++) {
+        const uint32_t d = digit[i];
+        slot[i] = d < BINS ? sm.tile_off[d] + sm.warp_hist[warp][d] + rank[i] : 0u;
+    }
+}
+
+#endif
 
 }  // namespace npge_b200
