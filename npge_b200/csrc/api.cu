@@ -239,13 +239,13 @@ extern "C" void npge_anchor_destroy(npge_anchor_ctx* ctx) {
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     DeviceBuffer* all[] = {&ctx->ascii, &ctx->packed, &ctx->nmask, &ctx->seq_start,
-                           &ctx->seq_caller, &ctx->counters, &ctx->used,
+                           &ctx->seq_caller, &ctx->seq_pair, &ctx->g_seq_pair, &ctx->counters, &ctx->used,
                            &ctx->found_bits, &ctx->sel,
                            &ctx->r_seq, &ctx->r_pos, &ctx->r_ori,
                            &ctx->r_block_off, &ctx->r_block_hash,
                            &ctx->summary, &ctx->rows, &ctx->blk,
                            &ctx->segtab, &ctx->fine_start,
-                           &ctx->bstatus, &ctx->units, &ctx->rec[0], &ctx->rec[1], &ctx->rhi[0],
+                           &ctx->bstatus, &ctx->unit_wtot, &ctx->units, &ctx->rec[0], &ctx->rec[1], &ctx->rhi[0],
                            &ctx->rhi[1], &ctx->seq_lut, &ctx->g_seq_start, &ctx->g_seq_caller,
                            &ctx->g_seq_lut, &ctx->pos_delta, &ctx->recv_rec, &ctx->recv_hi,
                            &ctx->peer_tab, &ctx->frag_pat, &ctx->frag_tiles, &ctx->frag_out,
@@ -320,6 +320,11 @@ int upload_common(npge_anchor_ctx* ctx, int32_t anchor_size, const uint64_t* siz
                                   starts.size() * 8, cudaMemcpyHostToDevice, st));
         NPGE_CUDA(cudaMemcpyAsync(ctx->seq_caller.ptr, callers.data(),
                                   callers.size() * 4, cudaMemcpyHostToDevice, st));
+        std::vector<uint2> pairs(starts.size());
+        for (size_t i = 0; i < starts.size(); i++) pairs[i] = make_uint2(uint32_t(starts[i]), callers[i]);
+        NPGE_TRY(ensure(ctx->seq_pair, pairs.size() * 8));
+        NPGE_CUDA(cudaMemcpyAsync(ctx->seq_pair.ptr, pairs.data(), pairs.size() * 8,
+                                  cudaMemcpyHostToDevice, st));
         // seq_lut[q] = scan-order sequence holding position q << lut_shift
         // (pads count for the sequence before them)
         const uint64_t n_chunks = (np >> ctx->lut_shift) + 2;
@@ -477,10 +482,12 @@ BucketArgs bucket_args(npge_anchor_ctx* ctx, const MsdPlan& plan, const MsdBuffe
         a.seq_start = ptr<uint64_t>(ctx->g_seq_start);
         a.seq_caller = ptr<uint32_t>(ctx->g_seq_caller);
         a.seq_lut = ptr<uint32_t>(ctx->g_seq_lut);
+        a.seq_pair = ptr<uint2>(ctx->g_seq_pair);
     } else {
         a.seq_start = ptr<uint64_t>(ctx->seq_start);
         a.seq_caller = ptr<uint32_t>(ctx->seq_caller);
         a.seq_lut = ptr<uint32_t>(ctx->seq_lut);
+        a.seq_pair = ptr<uint2>(ctx->seq_pair);
     }
     a.lut_shift = ctx->lut_shift;
     a.max_fragments = limit;
@@ -492,6 +499,7 @@ BucketArgs bucket_args(npge_anchor_ctx* ctx, const MsdPlan& plan, const MsdBuffe
     a.r_block_off = ptr<uint64_t>(ctx->r_block_off);
     a.r_block_hash = ptr<uint64_t>(ctx->r_block_hash);
     a.unit_tot = ptr<uint64_t>(ctx->bstatus);
+    a.unit_wtot = ptr<uint32_t>(ctx->unit_wtot);
     a.summary = ptr<uint64_t>(ctx->summary);
     return a;
 }
@@ -525,6 +533,7 @@ int find_device_msd(npge_anchor_ctx* ctx, const npge_anchor_params* p,
         if (plan.wide) NPGE_TRY(ensure(ctx->rhi[b], (max_records + 16) * 4));
     }
     NPGE_TRY(ensure(ctx->bstatus, size_t(max_win + 1) * 8 + bins_a * 4));
+    NPGE_TRY(ensure(ctx->unit_wtot, size_t(max_win + 1) * (kSortThreads / 32) * 4));
     NPGE_TRY(ensure(ctx->units, size_t(max_win + 1) * 16));
     NPGE_TRY(ensure(ctx->counters, kCntWords * 4));
     NPGE_TRY(ensure(ctx->summary, summary_words * 8));
@@ -1085,6 +1094,13 @@ extern "C" int npge_anchor_dist_upload(npge_anchor_ctx* ctx, int32_t anchor_size
                               cudaMemcpyHostToDevice, st));
     NPGE_CUDA(cudaMemcpyAsync(ctx->g_seq_lut.ptr, lut.data(), n_chunks * 4,
                               cudaMemcpyHostToDevice, st));
+    std::vector<uint2> pairs(size_t(n_global) + 1);
+    for (uint32_t i = 0; i <= n_global; i++) {
+        pairs[i] = make_uint2(uint32_t(global_start[i]), callers[i]);
+    }
+    NPGE_TRY(ensure(ctx->g_seq_pair, pairs.size() * 8));
+    NPGE_CUDA(cudaMemcpyAsync(ctx->g_seq_pair.ptr, pairs.data(), pairs.size() * 8,
+                              cudaMemcpyHostToDevice, st));
     NPGE_CUDA(cudaStreamSynchronize(st));
     ctx->dist = true;
     ctx->uploaded = true;
@@ -1458,6 +1474,7 @@ extern "C" int npge_anchor_dist_sort(npge_anchor_ctx* ctx, const npge_anchor_par
         NPGE_TRY(ensure(ctx->rec[1], (max_records + 16) * 8));
         if (plan.wide) NPGE_TRY(ensure(ctx->rhi[1], (max_records + 16) * 4));
         NPGE_TRY(ensure(ctx->bstatus, size_t(max_win + 1) * 8 + bins_a * 4));
+        NPGE_TRY(ensure(ctx->unit_wtot, size_t(max_win + 1) * (kSortThreads / 32) * 4));
         NPGE_TRY(ensure(ctx->units, size_t(max_win + 1) * 16));
         NPGE_TRY(ensure(ctx->summary, summary_words * 8));
         NPGE_TRY(ensure(ctx->used, n_used * 8));

@@ -16,8 +16,17 @@
 // A unit larger than kBucketCap (one (A, B) bin with thousands of records: a
 // k-mer repeated thousands of times, low-complexity sequence) takes the slow
 // path of the same CTA: the same passes, chunk by chunk, through global memory.
+#include <type_traits>
+
 #include "kernels.h"
 #include "rank.cuh"
+
+#ifndef NPGE_EMIT_CTAS
+#define NPGE_EMIT_CTAS 2
+#endif
+#ifndef NPGE_EMIT_DIRECT
+#define NPGE_EMIT_DIRECT 1
+#endif
 
 namespace npge_b200 {
 
@@ -59,18 +68,8 @@ struct __align__(16) BucketSmem {
         uint64_t buf[kCap + 2];
         uint32_t hib[WIDE ? kCap + 2 : 4];
     } half[2];
-    // ranking scratch of the sort kernel: byte digits, and the wider last digit
-    // (key bits + bin index inside the unit)
-#if NPGE_BIN_LAST
-    union {
-        RankSmem<8> rk;
-        RankSmem<10> rk10;
-    };
-    static constexpr size_t kSingle() { return sizeof(BucketSmem) - sizeof(Half) - sizeof(RankSmem<10>); }
-#else
-    RankSmem<8> rk;
+    RankSmem<8> rk;           // ranking scratch of the sort kernel
     static constexpr size_t kSingle() { return sizeof(BucketSmem) - sizeof(Half) - sizeof(RankSmem<8>); }
-#endif
 };
 
 // One sorted chunk of a unit in shared memory: records at K[1 .. cn], halo
@@ -221,6 +220,24 @@ __device__ __forceinline__ void locate(const BucketArgs& a, uint32_t g, uint32_t
     pos = g - uint32_t(a.seq_start[lo]);
 }
 
+// The same from the packed (start, caller) table: two dependent loads per position.
+__device__ __forceinline__ void locate_pair(const uint32_t* __restrict__ lut,
+                                            const uint2* __restrict__ pair, int lut_shift,
+                                            uint32_t g, uint32_t& seq, uint32_t& pos) {
+    const uint32_t q = g >> lut_shift;
+    uint32_t lo = lut[q];
+    const uint32_t hi = lut[q + 1];
+    uint2 p = pair[lo];
+    while (lo < hi) {  // rare: a sequence starts inside this chunk of positions
+        const uint2 nx = pair[lo + 1];
+        if (nx.x > g) break;
+        p = nx;
+        lo++;
+    }
+    seq = p.y;
+    pos = g - p.x;
+}
+
 // Writes the selected items of the chunk; `base` = global ranks before it.
 template <bool WIDE>
 __device__ __forceinline__ void unit_write(BucketSmem<WIDE>& sm, const Chunk<WIDE>& ch,
@@ -364,8 +381,6 @@ unit_build_kernel(BucketArgs a, uint32_t* __restrict__ unit_cnt) {
         for (int o = 16; o > 0; o >>= 1) out += __shfl_xor_sync(0xffffffffu, out, o);
     }
     const uint32_t end_all = fs[nb];
-    // the sort may rank by bin inside a unit: then a unit holds max_bins bins at most
-    const uint32_t max_bins = a.plan.max_bins ? uint32_t(a.plan.max_bins) : 0xffffffffu;
     uint32_t cur = 0, count = 0;
     while (cur < nb) {
         const uint32_t s = fs[cur];
@@ -382,15 +397,14 @@ unit_build_kernel(BucketArgs a, uint32_t* __restrict__ unit_cnt) {
         uint32_t e = cur + 1;     // the unit is [cur, e); grows while it fits
         while (true) {
             const uint32_t probe = e + lane;  // candidate bin to add: [cur, probe]
-            const bool fits = probe < nb && probe - cur < max_bins &&
-                              fs[probe + 1] - s <= uint32_t(kCap);
+            const bool fits = probe < nb && fs[probe + 1] - s <= uint32_t(kCap);
             const uint32_t m = __ballot_sync(0xffffffffu, fits);
             const int run = m == 0xffffffffu ? 32 : __ffs(~m) - 1;
             e += run;
             if (run < 32) break;
         }
         if (WRITE && lane == 0) {
-            a.units[out + count] = make_uint4(s, fs[e] - s, ab, a.plan.max_bins ? cur : 0u);
+            a.units[out + count] = make_uint4(s, fs[e] - s, ab, 0u);
         }
         count++;
         cur = e;
@@ -406,7 +420,7 @@ unit_build_kernel(BucketArgs a, uint32_t* __restrict__ unit_cnt) {
 template <bool WIDE>
 __device__ __forceinline__ bool unit_of_window(BucketSmem<WIDE>& sm, const BucketArgs& a,
                                                uint32_t w, uint32_t& s, uint32_t& n,
-                                               uint64_t& key_hi, uint32_t* bin0 = nullptr) {
+                                               uint64_t& key_hi) {
     if (w >= a.counters[kCntWindows]) return false;
     const uint4 u = a.units[w];
     if (threadIdx.x == 0) sm.cut = 0;
@@ -414,7 +428,6 @@ __device__ __forceinline__ bool unit_of_window(BucketSmem<WIDE>& sm, const Bucke
     s = u.x;
     n = u.y;
     key_hi = uint64_t(u.z) << a.plan.rem;
-    if (bin0) *bin0 = u.w;  // B digit of the unit's first bin
     return true;
 }
 
@@ -450,19 +463,17 @@ __device__ __forceinline__ void store_unit(BucketSmem<WIDE>& sm, const BucketArg
     }
 }
 
-// LSD radix sort of sm.half[0].buf[1..n], whose records arrive sorted by bin, by
-// the `low` key bits below the B digit: stable byte passes, the last one ranking by
-// (bin index inside the unit, remaining key bits) so that the bin order survives.
-// Returns the buffer holding the result.  Contains barriers.
+// LSD radix sort of sm.half[0].buf[1..n] by the low `rem` key bits, byte digits,
+// stable.  Returns the buffer holding the result.  Contains barriers.
 template <bool WIDE>
 __device__ __forceinline__ int sort_unit_smem(BucketSmem<WIDE>& sm, const MsdPlan& pl,
-                                              uint32_t n, uint32_t bin0) {
+                                              uint32_t n) {
     const int warp = threadIdx.x >> 5;
     const uint32_t first = warp * (32 * kRI);
     const int rounds = first >= n ? 0 : int(min(uint32_t(kRI), (n - first + 31) / 32));
     int cur = 0;
 #pragma unroll 1
-    for (int pass = 0; pass + 1 < pl.smem_passes; pass++) {
+    for (int pass = 0; pass < pl.smem_passes; pass++) {
         uint64_t rec[kRI];
         uint32_t hi[kRI], digit[kRI], slot[kRI];
 #pragma unroll
@@ -474,45 +485,10 @@ __device__ __forceinline__ int sort_unit_smem(BucketSmem<WIDE>& sm, const MsdPla
             digit[i] = in ? digit_at(rec[i], hi[i], 8 * pass) : 256u;
         }
         uint32_t c0, c1;
-        tile_rank<8>(sm.rk, digit, rounds, slot, c0, c1);
+        tile_rank_abs<8>(sm.rk, digit, rounds, slot, c0, c1);
 #pragma unroll
         for (int i = 0; i < kRI; i++) {
             if (item_index(i) < n) {
-                sm.half[cur ^ 1].buf[1 + slot[i]] = rec[i];
-                if (WIDE) sm.half[cur ^ 1].hib[1 + slot[i]] = hi[i];
-            }
-        }
-        __syncthreads();
-        cur ^= 1;
-    }
-    if (pl.smem_passes > 0) {
-        const int shift = 8 * (pl.smem_passes - 1);
-        const uint32_t kmask = (1u << pl.last_bits) - 1, bmask = (1u << pl.wb) - 1;
-        const bool narrow = pl.last_bits + pl.bin_bits <= 8;  // block-uniform
-        uint64_t rec[kRI];
-        uint32_t hi[kRI], digit[kRI], slot[kRI];
-#pragma unroll
-        for (int i = 0; i < kRI; i++) {
-            const uint32_t j = item_index(i);
-            const bool in = j < n;
-            rec[i] = in ? sm.half[cur].buf[1 + j] : 0ull;
-            hi[i] = (WIDE && in) ? sm.half[cur].hib[1 + j] : 0u;
-            const uint64_t kr = rem_key(rec[i], hi[i]);
-            const uint32_t bin = pl.max_bins ? (uint32_t(kr >> pl.low) & bmask) - bin0 : 0u;
-            digit[i] = in ? ((bin << pl.last_bits) | (uint32_t(kr >> shift) & kmask))
-                          : (narrow ? 256u : 1024u);
-        }
-        uint32_t c0, c1;
-#if NPGE_BIN_LAST
-        if (!narrow) {
-            tile_rank<10>(sm.rk10, digit, rounds, slot, c0, c1);
-        } else
-#endif
-        tile_rank<8>(sm.rk, digit, rounds, slot, c0, c1);
-#pragma unroll
-        for (int i = 0; i < kRI; i++) {
-            const uint32_t j = item_index(i);
-            if (j < n) {
                 sm.half[cur ^ 1].buf[1 + slot[i]] = rec[i];
                 if (WIDE) sm.half[cur ^ 1].hib[1 + slot[i]] = hi[i];
             }
@@ -674,21 +650,27 @@ bucket_sort_kernel(BucketArgs a) {
     extern __shared__ __align__(16) unsigned char raw[];
     BucketSmem<WIDE>& sm = *reinterpret_cast<BucketSmem<WIDE>*>(raw);
     const uint32_t w = blockIdx.x;
-    uint32_t s, n, bin0;
+    uint32_t s, n;
     uint64_t key_hi;
-    if (!unit_of_window<WIDE>(sm, a, w, s, n, key_hi, &bin0)) return;
+    if (!unit_of_window<WIDE>(sm, a, w, s, n, key_hi)) return;
     Chunk<WIDE> ch;
     uint32_t valid, preveq, inb, sel;
     uint64_t tot = 0;
     if (n <= uint32_t(kCap)) {
         load_unit<WIDE>(sm, a, s, n);
-        const int cur = sort_unit_smem<WIDE>(sm, a.plan, n, bin0);
+        const int cur = sort_unit_smem<WIDE>(sm, a.plan, n);
         whole_unit_chunk<WIDE>(sm, s, n, cur, ch);
         unit_flags<WIDE>(ch, valid, preveq, inb);
         if (MODE == 1) {
             mark_found<WIDE>(ch, a, key_hi, preveq);
         } else {
             tot = unit_select<WIDE, 0>(sm, ch, a, key_hi, valid, preveq, inb, sel);
+            // the emit kernel ranks its fragments from these, without a count of its own
+            if ((threadIdx.x & 31) == 0) {
+                const uint64_t wt = sm.warp_tot[threadIdx.x >> 5];
+                a.unit_wtot[size_t(w) * kRW + (threadIdx.x >> 5)] =
+                    uint32_t(wt & 0xffff) | (uint32_t(wt >> 31) << 16);
+            }
         }
         store_unit<WIDE>(sm, a, s, n, cur);
     } else {
@@ -819,6 +801,190 @@ bucket_emit_kernel(BucketArgs a) {
     flush_digest<WIDE>(sm, a, w, dg);
 }
 
+// ---- kernel 3, parity / exact mode: write the anchors straight from the sorted
+// records.  Every thread reads its kRI records with coalesced loads (item i of lane l
+// of warp w = record w * 32 * kRI + i * 32 + l of the chunk, as in the sort kernel),
+// the neighbours' keys come by warp shuffles, and the first fragment of every warp
+// comes from the per-warp totals the sort kernel left (unit_wtot): no shared-memory
+// copy of the unit, no count pass, no barrier before the writes.  An oversized unit
+// goes chunk by chunk with a count pass per chunk.
+struct __align__(16) DirectSmem {
+    uint64_t warp_tot[kRW];
+    uint64_t red[3][kRW];
+    uint32_t cut;
+};
+
+template <bool WIDE>
+__global__ void __launch_bounds__(kRT, NPGE_EMIT_CTAS)
+bucket_emit_direct_kernel(BucketArgs a) {
+    __shared__ DirectSmem sm;
+    typedef typename std::conditional<WIDE, uint64_t, uint32_t>::type key_t;
+    const uint32_t w = blockIdx.x;
+    if (w >= a.counters[kCntWindows]) return;
+    const uint4 u = a.units[w];
+    const uint32_t s = u.x, n = u.y;
+    const uint64_t key_hi = uint64_t(u.z) << a.plan.rem;
+    uint64_t base = a.unit_tot[w];
+    if ((base & 0x7fffffffull) >= a.max_fragments) return;  // past the cut
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t lt = (1u << lane) - 1;
+    if (tid == 0) sm.cut = 0;
+    const uint64_t* R = a.rec_w + s;
+    const uint32_t* H = a.hi_w + s;
+    auto key_at = [&](uint32_t j) -> key_t {
+        return key_t(rem_key(R[j], WIDE ? H[j] : 0u));
+    };
+    const uint64_t limit = a.max_fragments;
+    uint32_t* __restrict__ r_seq = a.r_seq;
+    uint32_t* __restrict__ r_pos = a.r_pos;
+    int8_t* __restrict__ r_ori = a.r_ori;
+    uint32_t* __restrict__ r_pay = a.r_pay;
+    uint64_t* __restrict__ r_block_off = a.r_block_off;
+    uint64_t* __restrict__ r_block_hash = a.r_block_hash;
+    Digest dg;
+#pragma unroll 1
+    for (uint32_t c0 = 0; c0 < n; c0 += kCap) {
+        const uint32_t cn = min(uint32_t(kCap), n - c0);
+        const uint32_t j0 = c0 + warp * (32 * kRI);  // first record of the warp
+        key_t key[kRI];
+        uint32_t pay[kRI];
+#pragma unroll
+        for (int i = 0; i < kRI; i++) {
+            const uint32_t j = j0 + i * 32 + lane;
+            key[i] = 0;
+            pay[i] = 0;
+            if (j < c0 + cn) {
+                const uint64_t r = R[j];
+                key[i] = key_t(rem_key(r, WIDE ? H[j] : 0u));
+                pay[i] = uint32_t(r);
+            }
+        }
+        // keys just outside the warp's range (lane 0 / lane 31 use them)
+        key_t edge_prev = 0, edge_next = 0;
+        if (lane == 0 && j0 > 0 && j0 - 1 < n) edge_prev = key_at(j0 - 1);
+        if (lane == 31 && j0 + 32 * kRI < n) edge_next = key_at(j0 + 32 * kRI);
+        // (sequence, position) of every record first: independent loads in flight
+        // together, before any store the compiler would have to order them against
+        uint32_t seq[kRI], pos[kRI];
+#pragma unroll
+        for (int i = 0; i < kRI; i++) {
+            seq[i] = pos[i] = 0;
+            if (j0 + i * 32 + lane < c0 + cn) {
+                locate_pair(a.seq_lut, a.seq_pair, a.lut_shift, pay[i] >> 1, seq[i], pos[i]);
+            }
+            pos[i] = (pos[i] << 1) | (pay[i] & 1);  // position << 1 | (ori == +1)
+        }
+        uint32_t preveq = 0, sel = 0;
+#pragma unroll
+        for (int i = 0; i < kRI; i++) {
+            const uint32_t j = j0 + i * 32 + lane;
+            key_t kp = __shfl_up_sync(0xffffffffu, key[i], 1);
+            key_t kn = __shfl_down_sync(0xffffffffu, key[i], 1);
+            const key_t from31 = __shfl_sync(0xffffffffu, key[i > 0 ? i - 1 : 0], 31);
+            const key_t from0 = __shfl_sync(0xffffffffu, key[i < kRI - 1 ? i + 1 : kRI - 1], 0);
+            if (lane == 0) kp = i > 0 ? from31 : edge_prev;
+            if (lane == 31) kn = i < kRI - 1 ? from0 : edge_next;
+            const bool in = j < c0 + cn;
+            const bool pe = in && j > 0 && kp == key[i];
+            const bool ne = in && j + 1 < n && kn == key[i];
+            bool s_ = pe || ne;
+            if (s_ && a.n_used) s_ = !is_used(a, key_hi | uint64_t(key[i]));
+            preveq |= (pe ? 1u : 0u) << i;
+            sel |= (s_ ? 1u : 0u) << i;
+        }
+        // fragments and blocks before this warp's first item
+        uint64_t before = 0, chunk_tot = 0;
+        if (n <= uint32_t(kCap)) {
+            uint32_t x = lane < warp ? a.unit_wtot[size_t(w) * kRW + lane] : 0u;
+            uint32_t f = x & 0xffff, b = x >> 16;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                f += __shfl_xor_sync(0xffffffffu, f, o);
+                b += __shfl_xor_sync(0xffffffffu, b, o);
+            }
+            before = (uint64_t(b) << 31) | f;
+        } else {
+            uint32_t nf = 0, nb = 0;
+#pragma unroll
+            for (int i = 0; i < kRI; i++) {
+                const bool s_ = (sel >> i) & 1;
+                nf += __popc(__ballot_sync(0xffffffffu, s_));
+                nb += __popc(__ballot_sync(0xffffffffu, s_ && !((preveq >> i) & 1)));
+            }
+            __syncthreads();  // warp_tot may still be read for the previous chunk
+            if (lane == 0) sm.warp_tot[warp] = (uint64_t(nb) << 31) | nf;
+            __syncthreads();
+            for (int x = 0; x < kRW; x++) {
+                const uint64_t t = sm.warp_tot[x];
+                if (x < warp) before += t;
+                chunk_tot += t;
+            }
+        }
+        uint64_t fr = (base + before) & 0x7fffffffull, br = (base + before) >> 31;
+#pragma unroll
+        for (int i = 0; i < kRI; i++) {
+            const bool s_ = (sel >> i) & 1;
+            const bool head = s_ && !((preveq >> i) & 1);
+            const uint32_t fb = __ballot_sync(0xffffffffu, s_);
+            const uint32_t bb = __ballot_sync(0xffffffffu, head);
+            if (s_) {
+                const uint64_t f = fr + __popc(fb & lt);
+                if (f < limit) {
+                    const uint64_t k64 = key_hi | uint64_t(key[i]);
+                    r_seq[f] = seq[i];
+                    r_pos[f] = pos[i] >> 1;
+                    r_ori[f] = (pos[i] & 1) ? 1 : -1;
+                    if (r_pay) r_pay[f] = pay[i];
+                    const uint64_t t = (uint64_t(seq[i]) << 33) | pos[i];
+                    uint64_t x, y;
+                    digest_terms(t, k64, x, y);
+                    dg.d0 += x;
+                    dg.d1 += y;
+                    if (head) {
+                        const uint64_t b = br + __popc(bb & lt);
+                        r_block_off[b] = f;
+                        r_block_hash[b] = k64;
+                        dg.nb++;
+                    }
+                    if (f + 1 == limit) {
+                        a.counters[kCntCutIndex] = s + j0 + i * 32 + lane;
+                        sm.cut = 1;
+                    }
+                }
+            }
+            fr += __popc(fb);
+            br += __popc(bb);
+        }
+        base += chunk_tot;
+    }
+    __syncthreads();
+    if (sm.cut && tid == 0) {
+        a.counters[kCntCutStart] = s;
+        a.counters[kCntCutSize] = n;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        dg.d0 += __shfl_xor_sync(0xffffffffu, dg.d0, o);
+        dg.d1 += __shfl_xor_sync(0xffffffffu, dg.d1, o);
+        dg.nb += __shfl_xor_sync(0xffffffffu, dg.nb, o);
+    }
+    if (lane == 0) {
+        sm.red[0][warp] = dg.d0;
+        sm.red[1][warp] = dg.d1;
+        sm.red[2][warp] = dg.nb;
+    }
+    __syncthreads();
+    if (tid < 3) {
+        uint64_t v = 0;
+        for (int x = 0; x < kRW; x++) v += sm.red[tid][x];
+        if (v) {
+            atomicAdd(reinterpret_cast<unsigned long long*>(
+                          a.summary + kSumWords + (w % kPartials) * 4 + tid),
+                      (unsigned long long)v);
+        }
+    }
+}
+
 __global__ void bucket_finalize_kernel(BucketArgs a) {
     if (threadIdx.x >= 32 || blockIdx.x != 0) return;
     uint64_t d0 = 0, d1 = 0, nb = 0;
@@ -856,15 +1022,7 @@ size_t bucket_summary_words() { return kSumWords + kPartials * 4; }
 // upper bound on the units of the bucket sort (two neighbours never fit in one):
 // the grid of its kernels and the size of the unit tables
 uint32_t bucket_max_windows(const MsdPlan& plan, uint64_t max_records) {
-    // a unit that is not the last of its bucket is either full (it and its successor
-    // hold more than kCap records together) or holds 1 << bin_bits bins; it never
-    // outnumbers the records either
-    const uint64_t by_size = (max_records + kWindow - 1) / kWindow;
-    const uint64_t by_bins =
-        plan.max_bins ? ((uint64_t(1) << (plan.wa + plan.wb)) >> plan.bin_bits) + 1 : 0;
-    uint64_t n = by_size + by_bins;
-    if (n > max_records) n = max_records;
-    return uint32_t(n + (2u << plan.capa) + 1);
+    return uint32_t((max_records + kWindow - 1) / kWindow) + (2u << plan.capa) + 1;
 }
 
 // The stages of the bucket sort, one launcher each so that the multi-GPU driver
@@ -915,7 +1073,15 @@ void launch_bucket_stage(const BucketArgs& a, int stage, uint64_t max_records,
         unit_scan_kernel<<<1, 1024, 0, s>>>(a);
         *launches += 1;
         break;
-    case kBucketEmit: NPGE_LAUNCH_W(false, bucket_emit_kernel, 0); break;
+    case kBucketEmit:
+#if NPGE_EMIT_DIRECT
+        if (a.plan.wide) bucket_emit_direct_kernel<true><<<grid, kRT, 0, s>>>(a);
+        else bucket_emit_direct_kernel<false><<<grid, kRT, 0, s>>>(a);
+        *launches += 1;
+#else
+        NPGE_LAUNCH_W(false, bucket_emit_kernel, 0);
+#endif
+        break;
     case kBucketEmitSimilar: NPGE_LAUNCH_W(false, bucket_emit_kernel, 2); break;
     }
 #undef NPGE_LAUNCH_W

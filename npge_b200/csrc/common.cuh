@@ -29,11 +29,6 @@ namespace npge_b200 {
 #endif
 constexpr int kSortThreads = NPGE_SORT_THREADS;
 constexpr int kSortItems = 4096 / NPGE_SORT_THREADS;
-// the bucket sort ranks its last digit together with the bin index inside the unit
-// (one pass fewer, 1024 counters in that pass): measured slower, kept as a variant
-#ifndef NPGE_BIN_LAST
-#define NPGE_BIN_LAST 0
-#endif
 constexpr int kTile = kSortThreads * kSortItems;  // 4096 records / positions
 constexpr int kMaxDigitBits = 10;                 // widest partition digit
 constexpr int kMaxPasses = 16;                    // event slots per find
@@ -45,14 +40,8 @@ struct MsdPlan {
     int k = 0, total = 0, wa = 0, wb = 0, rem = 0;
     int capa = 8, capb = 8;  // histogram rows hold 1 << cap bins
     int wide = 0;            // rem > 32: records carry a second u32 of key bits
-    // shared-memory sort of a unit: the `low` = rem - wb key bits below the B digit
-    // in `smem_passes` stable passes; all but the last take a byte, the last takes
-    // the remaining `last_bits` key bits TOGETHER with the record's bin index inside
-    // the unit (`bin_bits` bits, so a unit holds at most 1 << bin_bits bins): the
-    // records arrive sorted by bin, and this way no pass is spent on restoring that
-    int low = 0, smem_passes = 0, last_bits = 0, bin_bits = 0;
-    int slow_passes = 0;     // oversized unit (one bin): byte passes over `low` bits
-    int max_bins = 0;        // bins per unit (0: no limit)
+    int smem_passes = 0;     // byte passes of the shared-memory sort over the rem bits
+    int slow_passes = 0;     // oversized unit (one bin): byte passes below the B digit
 };
 
 constexpr int kBucketCap = kTile;        // records one CTA sorts in shared memory
@@ -142,13 +131,13 @@ struct npge_anchor_ctx {
     uint64_t n_padded = 0;                  // rounded up to kPosAlign
     uint64_t n_bases = 0;                   // sum(size)
     uint32_t n_caller_seqs = 0;
-    npge_b200::DeviceBuffer ascii, packed, nmask, seq_start, seq_caller;
+    npge_b200::DeviceBuffer ascii, packed, nmask, seq_start, seq_caller, seq_pair;
 
     // sort / grouping scratch
     npge_b200::DeviceBuffer counters, used;
     npge_b200::DeviceBuffer found_bits, sel;
     // MSD partition + bucket sort (msd_kernels.cu, bucket_kernels.cu)
-    npge_b200::DeviceBuffer rows, blk, segtab, fine_start, bstatus, units;
+    npge_b200::DeviceBuffer rows, blk, segtab, fine_start, bstatus, unit_wtot, units;
     npge_b200::DeviceBuffer rec[2], rhi[2], seq_lut;
     int lut_shift = 12;
     npge_b200::MsdPlan plan;
@@ -158,7 +147,7 @@ struct npge_anchor_ctx {
     std::vector<npge_b200::SeqEntry> gseqs;  // ALL sequences, job-wide scan order
     uint64_t g_positions = 0;                // job-wide positions (with pads)
     uint64_t g_padded = 0;
-    npge_b200::DeviceBuffer g_seq_start, g_seq_caller, g_seq_lut, pos_delta;
+    npge_b200::DeviceBuffer g_seq_start, g_seq_caller, g_seq_lut, g_seq_pair, pos_delta;
     npge_b200::DeviceBuffer recv_rec, recv_hi;
     uint64_t n_recv = 0;
     uint32_t dist_launches = 0;

@@ -102,6 +102,7 @@ struct BucketArgs {
     const uint64_t* seq_start;   // [S+1] global start of each scan-order sequence
     const uint32_t* seq_caller;  // [S] caller index
     const uint32_t* seq_lut;     // sequence holding position q << lut_shift
+    const uint2* seq_pair;       // [S + 1] (start, caller index) of every scan-order sequence
     int lut_shift;
     uint64_t max_fragments;      // truncation M
     uint32_t* found_bits;        // anchor-similar: 1 bit per global position
@@ -113,6 +114,7 @@ struct BucketArgs {
     uint64_t* r_block_off;
     uint64_t* r_block_hash;
     uint64_t* unit_tot;          // per unit: blocks << 31 | fragments, then its prefix
+    uint32_t* unit_wtot;         // per unit and warp of the sort CTA: blocks << 16 | fragments
     uint64_t* summary;
 };
 

@@ -52,23 +52,8 @@ MsdPlan make_msd_plan(int k, uint64_t n_positions, int force_f, int force_wa) {
     p.wide = p.rem > 32;
     p.capa = wa <= 8 ? 8 : (wa == 9 ? 9 : 10);  // histogram rows of 256 / 512 / 1024 bins
     p.capb = wb <= 8 ? 8 : (wb == 9 ? 9 : 10);
-#if NPGE_BIN_LAST
-    p.low = p.rem - wb;
-    p.slow_passes = (p.low + 7) / 8;
-    p.smem_passes = p.slow_passes;
-    p.last_bits = p.low - 8 * (p.smem_passes - 1);  // 1..8 (0 passes: unused)
-    if (p.smem_passes == 0) p.last_bits = 0;
-    p.bin_bits = 10 - p.last_bits < 4 ? 10 - p.last_bits : 4;
-    p.max_bins = 1 << p.bin_bits;
-#else
-    // byte passes over all rem bits: the top one(s) restore the bin order
-    p.low = p.rem;
-    p.slow_passes = (p.rem - wb + 7) / 8;
     p.smem_passes = (p.rem + 7) / 8;
-    p.last_bits = 8;
-    p.bin_bits = 0;
-    p.max_bins = 0;
-#endif
+    p.slow_passes = (p.rem - wb + 7) / 8;
     return p;
 }
 

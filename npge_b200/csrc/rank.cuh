@@ -85,66 +85,6 @@ struct __align__(16) RankSmem {
 // Rank of every item among the items of its own warp with the same digit, and
 // the warp's digit counts in sm.warp_hist[warp].  FULL: all kRI rounds hold
 // items (straight-line code); otherwise rounds >= `rounds` are skipped.
-#ifndef NPGE_RANK_ATOMIC
-#define NPGE_RANK_ATOMIC 1
-#endif
-#ifndef NPGE_RANK_BATCH
-#define NPGE_RANK_BATCH 4
-#endif
-#if NPGE_RANK_ATOMIC
-// The leader of every group of equal digits (match.any) adds the group's size to
-// the warp's counter with ONE shared-memory atomic that returns the count of the
-// earlier rounds.  Two 16-bit counters share a word (a warp holds 32 * kRI = 256
-// items: the low half never carries).  The atomics of the kRI rounds do not depend
-// on one another, so their latencies overlap; the rounds stay ordered because the
-// warp reconverges between them and shared memory executes in order.
-template <int CAPBITS, bool FULL>
-__device__ __forceinline__ void warp_rank(RankSmem<CAPBITS>& sm,
-                                          const uint32_t (&digit)[kRI], int rounds,
-                                          uint32_t (&rank)[kRI]) {
-    constexpr int BINS = 1 << CAPBITS;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const uint32_t lt = (1u << lane) - 1;
-    uint32_t* wh = reinterpret_cast<uint32_t*>(sm.warp_hist[warp]);
-    // in batches of kBatch rounds (registers: two words per round in flight)
-    constexpr int kBatch = NPGE_RANK_BATCH < kRI ? NPGE_RANK_BATCH : kRI;
-#pragma unroll
-    for (int b = 0; b < kRI; b += kBatch) {
-        uint32_t info[kBatch];  // leader lane | items before this lane << 8 | group size << 16
-        uint32_t old[kBatch];
-#pragma unroll
-        for (int j = 0; j < kBatch; j++) {
-            const int i = b + j;
-            info[j] = 0;
-            if (FULL || i < rounds) {
-                const uint32_t p = __match_any_sync(0xffffffffu, digit[i]);
-                info[j] = uint32_t(__ffs(p) - 1) | (__popc(p & lt) << 8) | (__popc(p) << 16);
-            }
-        }
-#pragma unroll
-        for (int j = 0; j < kBatch; j++) {
-            const int i = b + j;
-            old[j] = 0;
-            if (FULL || i < rounds) {
-                const uint32_t d = digit[i];
-                if (lane == int(info[j] & 0xff) && d < BINS) {
-                    old[j] = atomicAdd(&wh[d >> 1], (info[j] >> 16) << (16 * (d & 1)));
-                }
-                __syncwarp();
-            }
-        }
-#pragma unroll
-        for (int j = 0; j < kBatch; j++) {
-            const int i = b + j;
-            rank[i] = 0;
-            if (FULL || i < rounds) {
-                const uint32_t o = __shfl_sync(0xffffffffu, old[j], info[j] & 0xff);
-                rank[i] = ((o >> (16 * (digit[i] & 1))) & 0xffffu) + ((info[j] >> 8) & 0xff);
-            }
-        }
-    }
-}
-#else
 template <int CAPBITS, bool FULL>
 __device__ __forceinline__ void warp_rank(RankSmem<CAPBITS>& sm,
                                           const uint32_t (&digit)[kRI], int rounds,
@@ -175,7 +115,6 @@ __device__ __forceinline__ void warp_rank(RankSmem<CAPBITS>& sm,
         }
     }
 }
-#endif
 
 // Stable rank of the tile's items by digit.  Item i of lane l of warp w is
 // element w * 32 * kRI + i * 32 + l of the tile (ascending input order);
@@ -188,12 +127,13 @@ __device__ __forceinline__ void warp_rank(RankSmem<CAPBITS>& sm,
 // All match.any of a thread are issued back to back: the instruction has
 // ~200 cycles of latency on sm_100a (profiles/r01b_*), so the rounds must
 // overlap; only the counter updates are ordered.
-#ifndef NPGE_RANK_ABS
-#define NPGE_RANK_ABS 0
-#endif
-#if NPGE_RANK_ABS
+// tile_rank_abs: the same contract, but the per-warp counters end up holding the
+// ABSOLUTE first slot of (warp, digit), so that an item needs one lookup instead of
+// two.  Costs eight more registers between the barriers: used where registers are
+// not the occupancy limit (the bucket sort; measured -0.04 ms there, +0.04 ms in
+// the partition passes).
 template <int CAPBITS>
-__device__ __forceinline__ void tile_rank(RankSmem<CAPBITS>& sm,
+__device__ __forceinline__ void tile_rank_abs(RankSmem<CAPBITS>& sm,
                                           const uint32_t (&digit)[kRI], int rounds,
                                           uint32_t (&slot)[kRI], uint32_t& c0,
                                           uint32_t& c1) {
@@ -284,7 +224,7 @@ __device__ __forceinline__ void tile_rank(RankSmem<CAPBITS>& sm,
     }
 }
 
-#else
+
 template <int CAPBITS>
 __device__ __forceinline__ void tile_rank(RankSmem<CAPBITS>& sm,
                                           const uint32_t (&digit)[kRI], int rounds,
@@ -359,6 +299,5 @@ __device__ __forceinline__ void tile_rank(RankSmem<CAPBITS>& sm,
     }
 }
 
-#endif
 
 }  // namespace npge_b200
