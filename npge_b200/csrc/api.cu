@@ -245,7 +245,7 @@ extern "C" void npge_anchor_destroy(npge_anchor_ctx* ctx) {
                            &ctx->r_block_off, &ctx->r_block_hash,
                            &ctx->summary, &ctx->rows, &ctx->blk,
                            &ctx->segtab, &ctx->fine_start,
-                           &ctx->bstatus, &ctx->unit_wtot, &ctx->units, &ctx->rec[0], &ctx->rec[1], &ctx->rhi[0],
+                           &ctx->tile_desc, &ctx->bstatus, &ctx->unit_wtot, &ctx->units, &ctx->rec[0], &ctx->rec[1], &ctx->rhi[0],
                            &ctx->rhi[1], &ctx->seq_lut, &ctx->g_seq_start, &ctx->g_seq_caller,
                            &ctx->g_seq_lut, &ctx->pos_delta, &ctx->recv_rec, &ctx->recv_hi,
                            &ctx->peer_tab, &ctx->frag_pat, &ctx->frag_tiles, &ctx->frag_out,
@@ -528,6 +528,7 @@ int find_device_msd(npge_anchor_ctx* ctx, const npge_anchor_params* p,
     NPGE_TRY(ensure(ctx->blk, msd_blk_needed(plan, np, max_records, max_seg) * 4));
     NPGE_TRY(ensure(ctx->segtab, seg_table_words(max_seg, plan) * 4));
     NPGE_TRY(ensure(ctx->fine_start, ((bins_a << plan.wb) + 1) * 4));
+    NPGE_TRY(ensure(ctx->tile_desc, (msd_tiles_b(max_records, max_seg) + 1) * 16));
     for (int b = 0; b < 2; b++) {
         NPGE_TRY(ensure(ctx->rec[b], (max_records + 16) * 8));
         if (plan.wide) NPGE_TRY(ensure(ctx->rhi[b], (max_records + 16) * 4));
@@ -566,6 +567,7 @@ int find_device_msd(npge_anchor_ctx* ctx, const npge_anchor_params* p,
     mb.blk = ptr<uint32_t>(ctx->blk);
     mb.seg = carve_seg_tables(ptr<uint32_t>(ctx->segtab), max_seg, plan);
     mb.fine_start = ptr<uint32_t>(ctx->fine_start);
+    mb.tile_desc = ptr<uint4>(ctx->tile_desc);
     for (int b = 0; b < 2; b++) {
         mb.rec[b] = ptr<uint64_t>(ctx->rec[b]);
         mb.hi[b] = ptr<uint32_t>(ctx->rhi[b]);
@@ -1028,6 +1030,7 @@ MsdBuffers dist_msd_buffers(npge_anchor_ctx* ctx, const MsdPlan& plan, uint32_t 
     mb.blk = ptr<uint32_t>(ctx->blk);
     mb.seg = carve_seg_tables(ptr<uint32_t>(ctx->segtab), max_seg, plan);
     mb.fine_start = ptr<uint32_t>(ctx->fine_start);
+    mb.tile_desc = ptr<uint4>(ctx->tile_desc);
     for (int b = 0; b < 2; b++) {
         mb.rec[b] = ptr<uint64_t>(ctx->rec[b]);
         mb.hi[b] = ptr<uint32_t>(ctx->rhi[b]);
@@ -1471,6 +1474,7 @@ extern "C" int npge_anchor_dist_sort(npge_anchor_ctx* ctx, const npge_anchor_par
         NPGE_TRY(ensure(ctx->blk, msd_blk_needed(plan, ctx->n_padded, max_records, max_seg) * 4));
         NPGE_TRY(ensure(ctx->segtab, seg_table_words(max_seg, plan) * 4));
         NPGE_TRY(ensure(ctx->fine_start, ((size_t(bins_a) << plan.wb) + 1) * 4));
+        NPGE_TRY(ensure(ctx->tile_desc, (msd_tiles_b(max_records, max_seg) + 1) * 16));
         NPGE_TRY(ensure(ctx->rec[1], (max_records + 16) * 8));
         if (plan.wide) NPGE_TRY(ensure(ctx->rhi[1], (max_records + 16) * 4));
         NPGE_TRY(ensure(ctx->bstatus, size_t(max_win + 1) * 8 + bins_a * 4));

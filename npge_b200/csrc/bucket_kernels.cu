@@ -834,7 +834,8 @@ bucket_emit_direct_kernel(BucketArgs a) {
     auto key_at = [&](uint32_t j) -> key_t {
         return key_t(rem_key(R[j], WIDE ? H[j] : 0u));
     };
-    const uint64_t limit = a.max_fragments;
+    // fragment and block indices fit 31 bits (unit_tot packs them so)
+    const uint32_t limit = uint32_t(a.max_fragments < 0x80000000ull ? a.max_fragments : 0x80000000ull);
     uint32_t* __restrict__ r_seq = a.r_seq;
     uint32_t* __restrict__ r_pos = a.r_pos;
     int8_t* __restrict__ r_ori = a.r_ori;
@@ -920,7 +921,7 @@ bucket_emit_direct_kernel(BucketArgs a) {
                 chunk_tot += t;
             }
         }
-        uint64_t fr = (base + before) & 0x7fffffffull, br = (base + before) >> 31;
+        uint32_t fr = uint32_t((base + before) & 0x7fffffffull), br = uint32_t((base + before) >> 31);
 #pragma unroll
         for (int i = 0; i < kRI; i++) {
             const bool s_ = (sel >> i) & 1;
@@ -928,12 +929,12 @@ bucket_emit_direct_kernel(BucketArgs a) {
             const uint32_t fb = __ballot_sync(0xffffffffu, s_);
             const uint32_t bb = __ballot_sync(0xffffffffu, head);
             if (s_) {
-                const uint64_t f = fr + __popc(fb & lt);
+                const uint32_t f = fr + __popc(fb & lt);
                 if (f < limit) {
                     const uint64_t k64 = key_hi | uint64_t(key[i]);
                     r_seq[f] = seq[i];
                     r_pos[f] = pos[i] >> 1;
-                    r_ori[f] = (pos[i] & 1) ? 1 : -1;
+                    r_ori[f] = int8_t(2 * int(pos[i] & 1) - 1);
                     if (r_pay) r_pay[f] = pay[i];
                     const uint64_t t = (uint64_t(seq[i]) << 33) | pos[i];
                     uint64_t x, y;
@@ -941,7 +942,7 @@ bucket_emit_direct_kernel(BucketArgs a) {
                     dg.d0 += x;
                     dg.d1 += y;
                     if (head) {
-                        const uint64_t b = br + __popc(bb & lt);
+                        const uint32_t b = br + __popc(bb & lt);
                         r_block_off[b] = f;
                         r_block_hash[b] = k64;
                         dg.nb++;

@@ -63,6 +63,7 @@ struct MsdBuffers {
     uint32_t* blk;         // block sums of the row scan
     SegTables seg;
     uint32_t* fine_start;  // [((1 << capa) << wb) + 1]
+    uint4* tile_desc;      // per pass-B tile: (first record, end, A bucket, first tile of the bucket)
     uint64_t* rec[2];      // key bits [0, 32) << 32 | payload
     uint32_t* hi[2];       // key bits [32, rem) when plan.wide
 };
@@ -75,6 +76,7 @@ size_t msd_blk_needed(const MsdPlan& plan, uint64_t n_padded, uint64_t max_recor
                       uint32_t max_seg);
 size_t seg_table_words(uint32_t max_seg, const MsdPlan& plan);
 SegTables carve_seg_tables(uint32_t* base, uint32_t max_seg, const MsdPlan& plan);
+size_t msd_tiles_b(uint64_t max_records, uint32_t max_seg);  // pass-B tiles (upper bound)
 // ev (optional): [0] after count A, [1] after pass A, [2] after count B, [3] pass B
 // part: 0 = count + scatter, 1 = count A and the tables only, 2 = the scatter only
 void launch_msd_pass_a(const MsdPlan& plan, const uint32_t* packed,

@@ -82,12 +82,43 @@ count_a_kernel(const uint32_t* __restrict__ packed, const uint32_t* __restrict__
     for (int i = tid; i < bins; i += kRT) hist[i] = 0;
     stage_genome_tile(st, packed, nmask, blockIdx.x);
     const int sa = plan.total - plan.wa;
+    // a histogram does not care which thread sees which window: every thread walks
+    // kRI CONSECUTIVE windows and rolls the two hashes (two bits in, two bits out)
+    // instead of extracting each one from scratch
+    {
+        (void)lane;
+        (void)warp;
+        const int k = plan.k;
+        const uint32_t rel0 = tid * kRI;  // kRI = 8 positions = 16 bits = half a word
+        const uint32_t* W = st.w + (rel0 >> 4);
+        const uint32_t sh = (rel0 & 15) * 2;
+        // 128 bits of bases from position rel0 on (the tile carries 16 B of halo)
+        uint64_t lo = (uint64_t(__funnelshift_r(W[1], W[2], sh)) << 32) |
+                      __funnelshift_r(W[0], W[1], sh);
+        uint64_t hi = (uint64_t(__funnelshift_r(W[3], 0u, sh)) << 32) |
+                      __funnelshift_r(W[2], W[3], sh);
+        const uint32_t* M = st.m + (rel0 >> 5);
+        const uint32_t ms = rel0 & 31;
+        uint64_t mm = (uint64_t(__funnelshift_r(M[1], M[2], ms)) << 32) |
+                      __funnelshift_r(M[0], M[1], ms);
+        const uint64_t kmask = k == 32 ? ~0ull : ((1ull << (2 * k)) - 1);
+        const uint32_t nm = k == 32 ? ~0u : ((1u << k) - 1);
+        uint64_t dir = lo & kmask;
+        uint64_t rev = revcomp_key(dir, k);
 #pragma unroll
-    for (int i = 0; i < kRI; i++) {
-        uint32_t rel = warp * (32 * kRI) + i * 32 + lane;
-        uint64_t h;
-        uint32_t ob;
-        if (window_key(st, rel, plan.k, h, ob)) atomicAdd(&hist[uint32_t(h >> sa)], 1u);
+        for (int i = 0; i < kRI; i++) {
+            if ((uint32_t(mm) & nm) == 0) {
+                const uint64_t h = dir < rev ? dir : rev;
+                atomicAdd(&hist[uint32_t(h >> sa)], 1u);
+            }
+            // the base entering the window: position rel0 + i + k
+            const uint32_t in = uint32_t(k == 32 ? hi : (lo >> (2 * k))) & 3u;
+            lo = (lo >> 2) | (hi << 62);
+            hi >>= 2;
+            mm >>= 1;
+            dir = lo & kmask;
+            rev = ((rev << 2) | (in ^ 1u)) & kmask;
+        }
     }
     __syncthreads();
     uint32_t* row = rows + size_t(blockIdx.x) * bins;
@@ -351,11 +382,27 @@ pass_a_kernel(const uint32_t* __restrict__ packed, const uint32_t* __restrict__ 
     }
 }
 
+// ---- tile descriptors of pass B: the segment search once per tile, not once per CTA of
+// the counting and the scatter kernel (a chain of dependent loads at their start)
+__global__ void __launch_bounds__(256)
+tile_desc_kernel(SegTables t, uint32_t n_tiles, uint4* __restrict__ desc) {
+    const uint32_t tb = blockIdx.x * blockDim.x + threadIdx.x;
+    if (tb >= n_tiles) return;
+    uint4 d = make_uint4(0u, 0u, 0xffffffffu, 0u);
+    if (tb < t.seg_tile[t.n_seg]) {
+        const uint32_t sg = bucket_of(t.seg_tile, t.n_seg, tb);
+        const uint32_t a = t.seg_a[sg];
+        const uint32_t s = t.seg_begin[sg] + (tb - t.seg_tile[sg]) * uint32_t(kTile);
+        d = make_uint4(s, min(s + uint32_t(kTile), t.seg_end[sg]), a, t.a_tile0[a]);
+    }
+    desc[tb] = d;
+}
+
 // ---- count B: one histogram row per bucket-aligned tile of A-sorted records ----------
 template <bool WIDE>
 __global__ void __launch_bounds__(kRT)
 count_b_kernel(const uint64_t* __restrict__ rec, const uint32_t* __restrict__ hi,
-               MsdPlan plan, SegTables t, uint32_t* __restrict__ rows) {
+               MsdPlan plan, const uint4* __restrict__ desc, uint32_t* __restrict__ rows) {
     extern __shared__ __align__(16) unsigned char raw[];
     uint32_t* hist = reinterpret_cast<uint32_t*>(raw);
     const int bins = 1 << plan.capb;
@@ -363,10 +410,9 @@ count_b_kernel(const uint64_t* __restrict__ rec, const uint32_t* __restrict__ hi
     for (int i = tid; i < bins; i += kRT) hist[i] = 0;
     __syncthreads();
     const uint32_t tb = blockIdx.x;
-    if (tb < t.seg_tile[t.n_seg]) {
-        const uint32_t sg = bucket_of(t.seg_tile, t.n_seg, tb);
-        const uint32_t s = t.seg_begin[sg] + (tb - t.seg_tile[sg]) * uint32_t(kTile);
-        const uint32_t e = min(s + uint32_t(kTile), t.seg_end[sg]);
+    const uint4 td = desc[tb];
+    if (td.z != 0xffffffffu) {
+        const uint32_t s = td.x, e = td.y;
         const int sb = plan.rem - plan.wb;
         const uint32_t mb = (1u << plan.wb) - 1;
 #pragma unroll
@@ -405,7 +451,7 @@ fine_tables_kernel(const uint32_t* __restrict__ rows, MsdPlan plan, SegTables t,
 template <int CAPBITS, bool WIDE>
 __global__ void __launch_bounds__(kRT, (CAPBITS <= 9 && !WIDE) ? 3 : 2)
 pass_b_kernel(const uint64_t* __restrict__ in_rec, const uint32_t* __restrict__ in_hi,
-              MsdPlan plan, SegTables t, const uint32_t* __restrict__ rows,
+              MsdPlan plan, const uint4* __restrict__ desc, const uint32_t* __restrict__ rows,
               const uint32_t* __restrict__ fine_start,
               uint64_t* __restrict__ out_rec, uint32_t* __restrict__ out_hi) {
     extern __shared__ __align__(16) unsigned char raw[];
@@ -414,12 +460,9 @@ pass_b_kernel(const uint64_t* __restrict__ in_rec, const uint32_t* __restrict__ 
     constexpr int BINS = Smem::BINS;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t tb = blockIdx.x;
-    if (tb >= t.seg_tile[t.n_seg]) return;
-    const uint32_t sg = bucket_of(t.seg_tile, t.n_seg, tb);
-    const uint32_t a = t.seg_a[sg];
-    const uint32_t t0 = t.a_tile0[a];  // first tile of the bucket (all sources)
-    const uint32_t s = t.seg_begin[sg] + (tb - t.seg_tile[sg]) * uint32_t(kTile);
-    const uint32_t e = min(s + uint32_t(kTile), t.seg_end[sg]);
+    const uint4 td = desc[tb];  // (first record, end, A bucket, first tile of the bucket)
+    if (td.z == 0xffffffffu) return;
+    const uint32_t s = td.x, e = td.y, a = td.z, t0 = td.w;
     const int sb = plan.rem - plan.wb;
     const uint32_t mb = (1u << plan.wb) - 1;
     uint64_t rec[kRI];
@@ -498,6 +541,10 @@ void set_smem(K kernel, size_t bytes) {
 }
 
 }  // namespace
+
+size_t msd_tiles_b(uint64_t max_records, uint32_t max_seg) {
+    return size_t((max_records + kTile - 1) / kTile) + max_seg;
+}
 
 size_t msd_rows_needed(const MsdPlan& plan, uint64_t n_padded, uint64_t max_records,
                        uint32_t max_seg) {
@@ -624,13 +671,15 @@ void launch_msd_pass_b(const MsdPlan& plan, const uint64_t* in_rec, const uint32
                        uint64_t max_records, uint32_t max_seg, const MsdBuffers& b,
                        cudaStream_t s, cudaEvent_t* ev, uint32_t* launches) {
     const int bins_a = 1 << plan.capa, bins_b = 1 << plan.capb;
-    const uint32_t tiles_b = uint32_t((max_records + kTile - 1) / kTile) + max_seg;
+    const uint32_t tiles_b = uint32_t(msd_tiles_b(max_records, max_seg));
+    tile_desc_kernel<<<(tiles_b + 255) / 256, 256, 0, s>>>(b.seg, tiles_b, b.tile_desc);
+    *launches += 1;
     if (plan.wide) {
-        count_b_kernel<true><<<tiles_b, kRT, bins_b * 4, s>>>(in_rec, in_hi, plan, b.seg,
-                                                            b.rows);
+        count_b_kernel<true><<<tiles_b, kRT, bins_b * 4, s>>>(in_rec, in_hi, plan,
+                                                            b.tile_desc, b.rows);
     } else {
-        count_b_kernel<false><<<tiles_b, kRT, bins_b * 4, s>>>(in_rec, in_hi, plan, b.seg,
-                                                             b.rows);
+        count_b_kernel<false><<<tiles_b, kRT, bins_b * 4, s>>>(in_rec, in_hi, plan,
+                                                             b.tile_desc, b.rows);
     }
     scan_rows(b.rows, tiles_b, bins_b, b.blk, s);
     apply_rows(b.rows, tiles_b, bins_b, b.blk, nullptr, s);
@@ -641,7 +690,7 @@ void launch_msd_pass_b(const MsdPlan& plan, const uint64_t* in_rec, const uint32
     do {                                                                           \
         set_smem(pass_b_kernel<CB, W>, sizeof(PassSmem<CB, W>));                   \
         pass_b_kernel<CB, W><<<tiles_b, kRT, sizeof(PassSmem<CB, W>), s>>>(        \
-            in_rec, in_hi, plan, b.seg, b.rows, b.fine_start, b.rec[1], b.hi[1]);  \
+            in_rec, in_hi, plan, b.tile_desc, b.rows, b.fine_start, b.rec[1], b.hi[1]);  \
     } while (0)
     if (plan.capb == 8) {
         if (plan.wide) NPGE_PASS_B(8, true); else NPGE_PASS_B(8, false);
