@@ -21,6 +21,13 @@
 #include "kernels.h"
 #include "rank.cuh"
 
+#ifndef NPGE_EXP_PASSB
+#define NPGE_EXP_PASSB 0
+#endif
+#ifndef NPGE_EXP_SORTPASSES
+#define NPGE_EXP_SORTPASSES -1
+#endif
+
 namespace npge_b200 {
 
 MsdPlan make_msd_plan(int k, uint64_t n_positions, int force_f, int force_wa) {
@@ -53,6 +60,7 @@ MsdPlan make_msd_plan(int k, uint64_t n_positions, int force_f, int force_wa) {
     p.capa = wa <= 8 ? 8 : (wa == 9 ? 9 : 10);  // histogram rows of 256 / 512 / 1024 bins
     p.capb = wb <= 8 ? 8 : (wb == 9 ? 9 : 10);
     p.smem_passes = (p.rem + 7) / 8;
+    if (NPGE_EXP_SORTPASSES >= 0) p.smem_passes = NPGE_EXP_SORTPASSES;  // timing experiment
     p.slow_passes = (p.rem - wb + 7) / 8;
     return p;
 }
@@ -333,14 +341,23 @@ pass_a_kernel(const uint32_t* __restrict__ packed, const uint32_t* __restrict__ 
         obits |= ob << i;
         digit[i] = ok ? uint32_t(h >> sa) : uint32_t(BINS);
     }
+    // the scatter bases of the thread's digit(s): loaded before the ranking, whose
+    // barriers hide the latency
+    const uint32_t* row = rows + size_t(tile) * BINS;
+    uint32_t base0 = 0, base1 = 0;
+    if (BINS > kRT) {
+        base0 = row[2 * tid];
+        base1 = row[2 * tid + 1];
+    } else if (tid < BINS) {
+        base0 = row[tid];
+    }
     uint32_t c0, c1;
     tile_rank<CAPBITS>(sm.rk, digit, kRI, slot, c0, c1);
-    const uint32_t* row = rows + size_t(tile) * BINS;
     if (BINS > kRT) {
-        sm.bin_base[2 * tid] = row[2 * tid] - sm.rk.tile_off[2 * tid];
-        sm.bin_base[2 * tid + 1] = row[2 * tid + 1] - sm.rk.tile_off[2 * tid + 1];
+        sm.bin_base[2 * tid] = base0 - sm.rk.tile_off[2 * tid];
+        sm.bin_base[2 * tid + 1] = base1 - sm.rk.tile_off[2 * tid + 1];
     } else if (tid < BINS) {
-        sm.bin_base[tid] = row[tid] - sm.rk.tile_off[tid];
+        sm.bin_base[tid] = base0 - sm.rk.tile_off[tid];
     }
 #pragma unroll
     for (int i = 0; i < kRI; i++) {
@@ -482,21 +499,34 @@ pass_b_kernel(const uint64_t* __restrict__ in_rec, const uint32_t* __restrict__ 
     }
     const uint32_t first = s + warp * (32 * kRI);
     const int rounds = first >= e ? 0 : int(min(uint32_t(kRI), (e - first + 31) / 32));
-    uint32_t c0, c1;
-    tile_rank<CAPBITS>(sm.rk, digit, rounds, slot, c0, c1);
+    // the scatter bases of the thread's digit(s): loaded before the ranking, whose
+    // barriers hide the latency
     const uint32_t* row = rows + size_t(tb) * BINS;
     const uint32_t* row0 = rows + size_t(t0) * BINS;
     const uint32_t* fs = fine_start + (a << plan.wb);
+    uint32_t base0 = 0, base1 = 0;
     if (BINS > kRT) {
+        const int d = 2 * tid;
+        if (d <= int(mb)) base0 = fs[d] + row[d] - row0[d];
+        if (d + 1 <= int(mb)) base1 = fs[d + 1] + row[d + 1] - row0[d + 1];
+    } else if (tid < BINS && tid <= int(mb)) {
+        base0 = fs[tid] + row[tid] - row0[tid];
+    }
+    uint32_t c0, c1;
+#if NPGE_EXP_PASSB == 1  // timing experiment: no ranking
+    (void)rounds;
 #pragma unroll
-        for (int q = 0; q < 2; q++) {
-            int d = 2 * tid + q;
-            sm.bin_base[d] = d <= int(mb) ? fs[d] + row[d] - row0[d] - sm.rk.tile_off[d]
-                                          : 0u;
-        }
+    for (int i = 0; i < kRI; i++) slot[i] = warp * (32 * kRI) + i * 32 + lane;
+    if (tid == 0) sm.rk.total = e - s;
+    c0 = c1 = 0;
+#else
+    tile_rank<CAPBITS>(sm.rk, digit, rounds, slot, c0, c1);
+#endif
+    if (BINS > kRT) {
+        sm.bin_base[2 * tid] = base0 - sm.rk.tile_off[2 * tid];
+        sm.bin_base[2 * tid + 1] = base1 - sm.rk.tile_off[2 * tid + 1];
     } else if (tid < BINS) {
-        sm.bin_base[tid] = tid <= int(mb)
-                           ? fs[tid] + row[tid] - row0[tid] - sm.rk.tile_off[tid] : 0u;
+        sm.bin_base[tid] = base0 - sm.rk.tile_off[tid];
     }
 #pragma unroll
     for (int i = 0; i < kRI; i++) {
@@ -514,6 +544,9 @@ pass_b_kernel(const uint64_t* __restrict__ in_rec, const uint32_t* __restrict__ 
             uint64_t r = sm.rec[j];
             uint32_t h = WIDE ? sm.hi[j] : 0u;
             uint32_t idx = sm.bin_base[uint32_t(rem_key(r, h) >> sb) & mb] + j;
+#if NPGE_EXP_PASSB  // timing experiment: sequential instead of scattered writes
+            idx = s + j;
+#endif
             out_rec[idx] = r;
             if (WIDE) out_hi[idx] = h;
         }
