@@ -143,34 +143,44 @@ int npge_anchor_find_device(npge_anchor_ctx* ctx, const npge_anchor_params* p,
 int npge_anchor_fetch(npge_anchor_ctx* ctx, npge_anchor_result* out);
 int npge_anchor_get_stats(npge_anchor_ctx* ctx, npge_anchor_stats* stats);
 
-/* ---- several GPUs, one process and one context per GPU ---------------
- * Every rank scans its own sequences; canonical k-mers are repartitioned by
- * hash range between pass A and pass B.  The caller owns the collectives
- * (npge_b200/dist.py uses torch.distributed / NCCL); these entry points are the
- * per-rank stages between them:
- *   dist_upload    local sequences + the job-wide sequence table (positions in
- *                  the payload follow the job-wide scan order, so every rank's
- *                  result is the slice of the one-GPU result it owns)
- *   dist_pass_a    count A + pass A; returns the records per A bucket
- *   [all-gather of the histograms; contiguous bucket ranges are assigned to ranks]
- *   dist_buffers   device pointers of the send / receive buffers
- *   [all-to-all of the records]
- *   dist_sort      stage 0: pass B over the (bucket, source rank) segments of
- *                  the receive buffer (tables built by the caller from the
- *                  all-gathered histograms), bucket sort, and either the
- *                  anchor count (exact mode: totals valid) or the found bits
- *                  (anchor-similar: totals are 0)
- *                  [anchor-similar: all-reduce of the found bitmap; every bit
- *                  is set by exactly one rank, so SUM of the words is OR]
- *                  stage 1 (anchor-similar only): candidate rule + count
- *                  returns the rank's totals {fragments, blocks} before the cut
+/* ---- several GPUs, one context per GPU -------------------------------
+ * The job's sequences, in scan order (size descending, ties by caller index) with one
+ * pad position after each, form ONE position space.  It is cut into equal ranges:
+ * every rank generates the windows that START in its range (it also holds the k - 1
+ * bases after it, the halo), so a sequence may be split between GPUs -- the
+ * reference's unit of parallel work is a whole sequence (AnchorFinder.hpp:27-29).
+ * Canonical k-mers are then repartitioned by hash range between pass A and pass B.
+ * The caller owns the rendezvous between the ranks (npge_b200/dist.py: processes and
+ * torch.distributed; npge_anchor_multi_*: threads of one process); these entry points
+ * are the per-rank stages between them:
+ *   dist_upload_range  this rank's range of the position space
+ *   dist_count_a       count A; returns the records per A bucket
+ *   dist_scatter_local pass A into local memory (asynchronous)
+ *   [all-gather of the histograms; also the step's barrier]
+ *   dist_exchange      the job's tables (who owns which buckets, where every slice
+ *                      lands, the (bucket, source) segments of pass B: dist_plan.h,
+ *                      computed on the host in microseconds) and the copies of this
+ *                      rank's slices into the owners' receive buffers, mapped through
+ *                      CUDA IPC (dist_peer_alloc / dist_peer_open) or peer access:
+ *                      one copy per destination, all in flight at once
+ *   [barrier: every rank's copies have landed]
+ *   dist_sort_planned  stage 0: pass B over the received segments, bucket sort, and
+ *                      either the anchor count (exact mode: totals valid) or the found
+ *                      bits (anchor-similar: totals are 0)
+ *                      [anchor-similar: all-reduce of the found bitmap; every bit
+ *                      is set by exactly one rank, so SUM of the words is OR]
+ *                      stage 1 (anchor-similar only): candidate rule + count
+ *                      returns the rank's totals {fragments, blocks} before the cut
  *   [all-gather of the totals -> every rank's share of max-anchor-fragments]
- *   dist_emit      writes the rank's anchors; npge_anchor_fetch then works as usual,
- *                  except that new_used holds EVERY hash of the rank's list (the
- *                  caller concatenates the ranks and drops the job's first one)
- * Every rank must hold a contiguous range of the job-wide scan order (sequences by
- * size, descending; ties by caller index), ranges ascending with the rank: then the
- * source-rank order of the exchange is the position order and the sort stays stable.
+ *   dist_emit          writes the rank's anchors; npge_anchor_fetch then works as usual,
+ *                      except that new_used holds EVERY hash of the rank's list (the
+ *                      caller concatenates the ranks and drops the job's first one)
+ * Positions in the records are job-wide, so every rank's result is literally the
+ * slice of the one-GPU result for its hash range.
+ * Variants kept for process groups without peer access and for comparison:
+ * dist_pass_a + dist_buffers + an all-to-all by the caller + dist_sort with the
+ * caller's tables ("collective"); dist_scatter_peer, where pass A itself writes every
+ * bucket into the owner's memory over NVLink ("peer").
  */
 typedef struct {
     void* send_rec;      /* u64 records after pass A, bucket a at a_start[a] */
@@ -183,11 +193,18 @@ typedef struct {
     int32_t n_bins;      /* A buckets (1 << capa) */
 } npge_anchor_dist_ptrs;
 
-int npge_anchor_dist_upload(npge_anchor_ctx* ctx, int32_t anchor_size,
-                            const uint8_t* bases, const uint64_t* seq_offsets,
-                            uint32_t n_seqs, const uint64_t* local_gstart,
-                            const uint64_t* global_start,
-                            const uint32_t* global_caller, uint32_t n_global);
+/* bases: host or device memory; piece i = bytes [src_off[i], src_off[i] + len[i]) placed
+ * at LOCAL position dst_pos[i] (job-wide position g0 + dst_pos[i]); local positions no
+ * piece covers are pads.  The rank owns the windows starting in [g0, g0 + n_own) and
+ * holds [g0, g0 + n_have), n_own <= n_have < n_own + anchor_size.
+ * global_start[n_global + 1]: first job-wide position of every sequence in scan order
+ * (size + 1 apart: the pads); global_caller[n_global]: the caller's index of each. */
+int npge_anchor_dist_upload_range(npge_anchor_ctx* ctx, int32_t anchor_size,
+                                  const uint8_t* bases, uint32_t n_pieces,
+                                  const uint64_t* src_off, const uint64_t* dst_pos,
+                                  const uint64_t* len, uint64_t g0, uint64_t n_own,
+                                  uint64_t n_have, const uint64_t* global_start,
+                                  const uint32_t* global_caller, uint32_t n_global);
 int npge_anchor_dist_pass_a(npge_anchor_ctx* ctx, const npge_anchor_params* p,
                             uint32_t* hist_out, uint32_t hist_cap, uint32_t* n_bins);
 /* The exchange without a separate all-to-all: pass A scatters every bucket
@@ -224,6 +241,24 @@ int npge_anchor_dist_scatter_local(npge_anchor_ctx* ctx, const npge_anchor_param
 int npge_anchor_dist_copy_peer(npge_anchor_ctx* ctx, const npge_anchor_params* p,
                                const uint32_t* dest_rank, const int64_t* dest_off,
                                uint32_t n_bins);
+/* hist_all[world][bins]: the all-gathered results of dist_count_a.  n_recv_out[world]
+ * (optional): records every rank receives.  NPGE_ANCHOR_ERR_CAPACITY when a receive
+ * buffer is too small (n_recv_out valid: regrow with dist_peer_alloc and call again). */
+int npge_anchor_dist_exchange(npge_anchor_ctx* ctx, const npge_anchor_params* p,
+                              const uint32_t* hist_all, uint32_t world, uint32_t rank,
+                              uint64_t* n_recv_out);
+int npge_anchor_dist_sort_planned(npge_anchor_ctx* ctx, const npge_anchor_params* p,
+                                  int32_t stage, const uint64_t* used_sorted,
+                                  uint64_t n_used, uint64_t totals[2]);
+/* The tables of dist_exchange alone, on the host (no device needed; tests): cuts
+ * [world + 1], n_recv [world], dest_rank / dest_off [bins] of `rank` as a sender, and
+ * its segment tables as a receiver (seg_* sized world * bins, seg_tile one more,
+ * a_tile0 / a_start [bins + 1]); any pointer may be NULL. */
+int npge_anchor_dist_plan_tables(const uint32_t* hist_all, uint32_t world, uint32_t bins,
+                                 uint32_t rank, uint32_t* cuts, uint64_t* n_recv,
+                                 uint32_t* dest_rank, int64_t* dest_off, uint32_t* n_seg,
+                                 uint32_t* seg_begin, uint32_t* seg_end, uint32_t* seg_a,
+                                 uint32_t* seg_tile, uint32_t* a_tile0, uint32_t* a_start);
 int npge_anchor_dist_buffers(npge_anchor_ctx* ctx, uint64_t n_recv,
                              npge_anchor_dist_ptrs* out);
 int npge_anchor_dist_sort(npge_anchor_ctx* ctx, const npge_anchor_params* p,

@@ -13,7 +13,9 @@ EXPORTS = [
     "npge_anchor_find", "npge_anchor_result_free", "npge_anchor_upload",
     "npge_anchor_find_device", "npge_anchor_fetch", "npge_anchor_get_stats",
     "npge_anchor_version",
-    "npge_anchor_dist_upload", "npge_anchor_dist_pass_a",
+    "npge_anchor_dist_upload_range", "npge_anchor_dist_pass_a",
+    "npge_anchor_dist_exchange", "npge_anchor_dist_sort_planned",
+    "npge_anchor_dist_plan_tables",
     "npge_anchor_dist_buffers", "npge_anchor_dist_sort", "npge_anchor_dist_emit",
     "npge_anchor_dist_peer_alloc", "npge_anchor_dist_peer_open",
     "npge_anchor_dist_peer_close", "npge_anchor_dist_count_a",
@@ -111,10 +113,19 @@ def load():
     L.npge_anchor_fetch.argtypes = [ctx, C.POINTER(Result)]
     L.npge_anchor_get_stats.restype = C.c_int
     L.npge_anchor_get_stats.argtypes = [ctx, C.POINTER(Stats)]
-    L.npge_anchor_dist_upload.restype = C.c_int
-    L.npge_anchor_dist_upload.argtypes = [ctx, C.c_int32, C.c_void_p, C.c_void_p,
-                                          C.c_uint32, C.c_void_p, C.c_void_p,
-                                          C.c_void_p, C.c_uint32]
+    L.npge_anchor_dist_upload_range.restype = C.c_int
+    L.npge_anchor_dist_upload_range.argtypes = [
+        ctx, C.c_int32, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p,
+        C.c_uint64, C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p, C.c_uint32]
+    L.npge_anchor_dist_exchange.restype = C.c_int
+    L.npge_anchor_dist_exchange.argtypes = [ctx, C.POINTER(Params), C.c_void_p, C.c_uint32,
+                                            C.c_uint32, C.c_void_p]
+    L.npge_anchor_dist_sort_planned.restype = C.c_int
+    L.npge_anchor_dist_sort_planned.argtypes = [ctx, C.POINTER(Params), C.c_int32, C.c_void_p,
+                                                C.c_uint64, C.POINTER(C.c_uint64 * 2)]
+    L.npge_anchor_dist_plan_tables.restype = C.c_int
+    L.npge_anchor_dist_plan_tables.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32,
+                                               C.c_uint32] + [C.c_void_p] * 11
     L.npge_anchor_dist_pass_a.restype = C.c_int
     L.npge_anchor_dist_pass_a.argtypes = [ctx, C.POINTER(Params), C.c_void_p,
                                           C.c_uint32, C.POINTER(C.c_uint32)]

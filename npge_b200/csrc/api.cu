@@ -247,7 +247,7 @@ extern "C" void npge_anchor_destroy(npge_anchor_ctx* ctx) {
                            &ctx->segtab, &ctx->fine_start,
                            &ctx->tile_desc, &ctx->bstatus, &ctx->unit_wtot, &ctx->units, &ctx->rec[0], &ctx->rec[1], &ctx->rhi[0],
                            &ctx->rhi[1], &ctx->seq_lut, &ctx->g_seq_start, &ctx->g_seq_caller,
-                           &ctx->g_seq_lut, &ctx->pos_delta, &ctx->recv_rec, &ctx->recv_hi,
+                           &ctx->g_seq_lut, &ctx->recv_rec, &ctx->recv_hi,
                            &ctx->peer_tab, &ctx->frag_pat, &ctx->frag_tiles, &ctx->frag_out,
                            &ctx->raw, &ctx->ingest, &ctx->bh_in, &ctx->bh_names,
                            &ctx->bh_scratch, &ctx->bh_out, &ctx->r_pay};
@@ -256,6 +256,8 @@ extern "C" void npge_anchor_destroy(npge_anchor_ctx* ctx) {
     for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
     for (auto& ev : ctx->ev_pass) if (ev) cudaEventDestroy(ev);
     for (auto& ev : ctx->fetch_ev) if (ev) cudaEventDestroy(ev);
+    for (auto& ev : ctx->copy_events) if (ev) cudaEventDestroy(ev);
+    for (auto& cs : ctx->copy_streams) if (cs) cudaStreamDestroy(cs);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -573,7 +575,7 @@ int find_device_msd(npge_anchor_ctx* ctx, const npge_anchor_params* p,
         mb.hi[b] = ptr<uint32_t>(ctx->rhi[b]);
     }
     if (np) {
-        PosMap pm = {};
+        PosMap pm;
         launch_msd_pass_a(plan, ptr<uint32_t>(ctx->packed), ptr<uint32_t>(ctx->nmask),
                           np, mb, pm, ptr<uint32_t>(ctx->counters), st, ctx->ev_pass,
                           &launches);
@@ -1040,42 +1042,81 @@ MsdBuffers dist_msd_buffers(npge_anchor_ctx* ctx, const MsdPlan& plan, uint32_t 
 
 }  // namespace
 
-extern "C" int npge_anchor_dist_upload(npge_anchor_ctx* ctx, int32_t anchor_size,
-                                       const uint8_t* bases, const uint64_t* seq_offsets,
-                                       uint32_t n_seqs, const uint64_t* local_gstart,
-                                       const uint64_t* global_start,
-                                       const uint32_t* global_caller, uint32_t n_global) {
+// Position-range upload of one rank: the job's sequences, in scan order
+// with one pad after each, form ONE position space [0, P); this rank generates the
+// windows that start in [g0, g0 + n_own) and holds the bases of [g0, g0 + n_have)
+// (n_have - n_own <= k - 1: the halo completing its last windows).  A sequence may
+// be cut anywhere: GPUs are balanced by positions, not by sequences.
+extern "C" int npge_anchor_dist_upload_range(npge_anchor_ctx* ctx, int32_t anchor_size,
+                                             const uint8_t* bases, uint32_t n_pieces,
+                                             const uint64_t* src_off, const uint64_t* dst_pos,
+                                             const uint64_t* len, uint64_t g0, uint64_t n_own,
+                                             uint64_t n_have, const uint64_t* global_start,
+                                             const uint32_t* global_caller,
+                                             uint32_t n_global) {
     if (!ctx) return fail(NPGE_ANCHOR_ERR_PARAMS, "ctx is NULL");
-    if ((n_seqs && !local_gstart) || !global_start || (n_global && !global_caller)) {
-        return fail(NPGE_ANCHOR_ERR_PARAMS, "NULL sequence table");
+    npge_anchor_params probe = {anchor_size, 0, 0};
+    NPGE_TRY(check_params(&probe));
+    if (!global_start || (n_global && !global_caller) ||
+        (n_pieces && (!bases || !src_off || !dst_pos || !len))) {
+        return fail(NPGE_ANCHOR_ERR_PARAMS, "NULL table");
     }
-    NPGE_TRY(npge_anchor_upload(ctx, anchor_size, bases, seq_offsets, n_seqs));
-    ctx->uploaded = false;
     const uint64_t g_positions = global_start[n_global];
     if (g_positions > kMaxPositions) {
         return fail(NPGE_ANCHOR_ERR_CAPACITY, "more than 2^31-1 positions in the job");
     }
-    cudaStream_t st = ctx->stream;
-    // delta of every local scan-order sequence: job-wide start - local start
-    std::vector<uint32_t> delta(ctx->seqs.size() + 1, 0);
-    for (size_t i = 0; i < ctx->seqs.size(); i++) {
-        const SeqEntry& e = ctx->seqs[i];
-        delta[i] = uint32_t(local_gstart[e.caller_index] - e.start);
+    if (n_own > n_have || g0 + n_have > g_positions ||
+        n_have - n_own >= uint64_t(anchor_size)) {
+        return fail(NPGE_ANCHOR_ERR_PARAMS, "bad position range");
     }
-    NPGE_TRY(ensure(ctx->pos_delta, delta.size() * 4));
-    NPGE_CUDA(cudaMemcpyAsync(ctx->pos_delta.ptr, delta.data(), delta.size() * 4,
-                              cudaMemcpyHostToDevice, st));
-    // the job-wide table (the same on every rank) for the emit side
+    for (uint32_t i = 0; i < n_pieces; i++) {
+        if (dst_pos[i] + len[i] > n_have) {
+            return fail(NPGE_ANCHOR_ERR_PARAMS, "piece outside the rank's range");
+        }
+    }
+    NPGE_CUDA(cudaSetDevice(ctx->device));
+    ctx->uploaded = false;
+    ctx->have_result = false;
+    ctx->seqs.clear();
     ctx->gseqs.clear();
+    uint64_t own_bases = 0;
     for (uint32_t i = 0; i < n_global; i++) {
         if (global_start[i + 1] <= global_start[i]) {
             return fail(NPGE_ANCHOR_ERR_PARAMS, "global_start must be increasing");
         }
-        ctx->gseqs.push_back({global_caller[i], global_start[i + 1] - global_start[i] - 1,
-                              global_start[i]});
+        const uint64_t b = global_start[i], e = global_start[i + 1] - 1;  // bases of sequence i
+        ctx->gseqs.push_back({global_caller[i], e - b, b});
+        const uint64_t lo = std::max(b, g0), hi = std::min(e, g0 + n_own);
+        if (hi > lo) own_bases += hi - lo;
     }
+    ctx->n_positions = n_have;
+    ctx->n_bases = own_bases;
+    ctx->n_padded = (n_have + kPosAlign - 1) / kPosAlign * kPosAlign;
+    ctx->n_caller_seqs = n_global;
+    ctx->upload_k = anchor_size;
     ctx->g_positions = g_positions;
     ctx->g_padded = (g_positions + kPosAlign - 1) / kPosAlign * kPosAlign;
+    ctx->dist_g0 = g0;
+    ctx->dist_n_own = n_own;
+    const uint64_t np = ctx->n_padded;
+    const size_t slack = 256;
+    NPGE_TRY(ensure(ctx->ascii, np + slack));
+    NPGE_TRY(ensure(ctx->packed, np / 4 + slack));
+    NPGE_TRY(ensure(ctx->nmask, np / 8 + slack));
+    NPGE_TRY(ensure(ctx->counters, kCntWords * 4));
+    cudaStream_t st = ctx->stream;
+    NPGE_CUDA(cudaMemsetAsync(ctx->counters.ptr, 0, kCntWords * 4, st));
+    NPGE_CUDA(cudaMemsetAsync(ctx->ascii.ptr, 'N', np + slack, st));
+    NPGE_CUDA(cudaMemsetAsync(ptr<uint8_t>(ctx->packed) + np / 4, 0, slack, st));
+    NPGE_CUDA(cudaMemsetAsync(ptr<uint8_t>(ctx->nmask) + np / 8, 0xff, slack, st));
+    for (uint32_t i = 0; i < n_pieces; i++) {
+        if (len[i] == 0) continue;
+        // (cudaMemcpyDefault: `bases` may also be device memory, e.g. the pieces a
+        // multi-process job has just exchanged)
+        NPGE_CUDA(cudaMemcpyAsync(ptr<uint8_t>(ctx->ascii) + dst_pos[i], bases + src_off[i],
+                                  len[i], cudaMemcpyDefault, st));
+    }
+    // the job-wide tables (the same on every rank) for the emit side
     const uint64_t n_chunks = (ctx->g_padded >> ctx->lut_shift) + 2;
     std::vector<uint32_t> lut(n_chunks);
     {
@@ -1086,25 +1127,38 @@ extern "C" int npge_anchor_dist_upload(npge_anchor_ctx* ctx, int32_t anchor_size
             lut[q] = uint32_t(sidx);
         }
     }
-    std::vector<uint32_t> callers(n_global + 1, 0);
+    std::vector<uint32_t> callers(size_t(n_global) + 1, 0);
     for (uint32_t i = 0; i < n_global; i++) callers[i] = global_caller[i];
+    std::vector<uint2> pairs(size_t(n_global) + 1);
+    for (uint32_t i = 0; i <= n_global; i++) {
+        pairs[i] = make_uint2(uint32_t(global_start[i]), callers[i]);
+    }
     NPGE_TRY(ensure(ctx->g_seq_start, (size_t(n_global) + 1) * 8));
     NPGE_TRY(ensure(ctx->g_seq_caller, (size_t(n_global) + 1) * 4));
     NPGE_TRY(ensure(ctx->g_seq_lut, n_chunks * 4));
+    NPGE_TRY(ensure(ctx->g_seq_pair, pairs.size() * 8));
     NPGE_CUDA(cudaMemcpyAsync(ctx->g_seq_start.ptr, global_start, (size_t(n_global) + 1) * 8,
                               cudaMemcpyHostToDevice, st));
     NPGE_CUDA(cudaMemcpyAsync(ctx->g_seq_caller.ptr, callers.data(), callers.size() * 4,
                               cudaMemcpyHostToDevice, st));
     NPGE_CUDA(cudaMemcpyAsync(ctx->g_seq_lut.ptr, lut.data(), n_chunks * 4,
                               cudaMemcpyHostToDevice, st));
-    std::vector<uint2> pairs(size_t(n_global) + 1);
-    for (uint32_t i = 0; i <= n_global; i++) {
-        pairs[i] = make_uint2(uint32_t(global_start[i]), callers[i]);
-    }
-    NPGE_TRY(ensure(ctx->g_seq_pair, pairs.size() * 8));
     NPGE_CUDA(cudaMemcpyAsync(ctx->g_seq_pair.ptr, pairs.data(), pairs.size() * 8,
                               cudaMemcpyHostToDevice, st));
-    NPGE_CUDA(cudaStreamSynchronize(st));
+    NPGE_CUDA(cudaStreamSynchronize(st));  // the tables are locals
+    if (np) {
+        launch_pack(ptr<uint8_t>(ctx->ascii), ptr<uint32_t>(ctx->packed),
+                    ptr<uint32_t>(ctx->nmask), np, ptr<uint32_t>(ctx->counters), st);
+        NPGE_CUDA(cudaGetLastError());
+        uint32_t bad = 0;
+        NPGE_CUDA(cudaMemcpyAsync(&bad, ptr<uint32_t>(ctx->counters) + kCntBadInput, 4,
+                                  cudaMemcpyDeviceToHost, st));
+        NPGE_CUDA(cudaStreamSynchronize(st));
+        if (bad) {
+            return fail(NPGE_ANCHOR_ERR_INPUT, std::to_string(bad) + " bytes outside ATGCN: "
+                        "run Sequence::to_atgcn on the input first");
+        }
+    }
     ctx->dist = true;
     ctx->uploaded = true;
     return NPGE_ANCHOR_OK;
@@ -1113,11 +1167,9 @@ extern "C" int npge_anchor_dist_upload(npge_anchor_ctx* ctx, int32_t anchor_size
 namespace {
 
 PosMap dist_pos_map(npge_anchor_ctx* ctx) {
-    PosMap pm = {};
-    pm.delta = ptr<uint32_t>(ctx->pos_delta);
-    pm.seq_start = ptr<uint64_t>(ctx->seq_start);
-    pm.lut = ptr<uint32_t>(ctx->seq_lut);
-    pm.lut_shift = ctx->lut_shift;
+    PosMap pm;
+    pm.g0 = uint32_t(ctx->dist_g0);
+    pm.win_limit = uint32_t(ctx->dist_n_own);
     return pm;
 }
 
@@ -1401,6 +1453,149 @@ extern "C" int npge_anchor_dist_copy_peer(npge_anchor_ctx* ctx, const npge_ancho
     return NPGE_ANCHOR_OK;
 }
 
+// ---- the exchange, planned and driven from here ---------------------------------------
+// hist_all = the all-gathered per-bucket record counts of every rank ([world][bins]).
+// Builds the job's tables (dist_plan.h, the same on every rank), then sends this rank's
+// slice of every destination into the owner's receive buffer: one asynchronous
+// device-to-device copy per destination, each on its own stream, so that all NVSwitch
+// flows run at once and on the copy engines (the SMs stay free for pass A of a later
+// call or of another context).  The copies wait for pass A (npge_anchor_dist_scatter_local,
+// same context) through an event.  n_recv_out[world]: records every rank receives.
+// NPGE_ANCHOR_ERR_CAPACITY: a receive buffer is too small (n_recv_out is valid: regrow
+// with npge_anchor_dist_peer_alloc / open and call again).
+extern "C" int npge_anchor_dist_exchange(npge_anchor_ctx* ctx, const npge_anchor_params* p,
+                                         const uint32_t* hist_all, uint32_t world,
+                                         uint32_t rank, uint64_t* n_recv_out) {
+    if (!ctx || !hist_all) return fail(NPGE_ANCHOR_ERR_PARAMS, "NULL argument");
+    NPGE_TRY(check_params(p));
+    if (!ctx->dist || !ctx->a_counted || !ctx->a_scattered) {
+        return fail(NPGE_ANCHOR_ERR_STATE, "npge_anchor_dist_scatter_local has not run");
+    }
+    if (rank >= world || ctx->peer_rec.size() != world || ctx->dist_rank != rank) {
+        return fail(NPGE_ANCHOR_ERR_STATE, "npge_anchor_dist_peer_open does not match world/rank");
+    }
+    const MsdPlan plan = ctx->plan;
+    const uint32_t bins_a = 1u << plan.capa;
+    NPGE_CUDA(cudaSetDevice(ctx->device));
+    DistPlan& dp = ctx->dplan;
+    dist_make_plan(hist_all, world, bins_a, rank, dp);
+    ctx->planned = false;
+    uint64_t max_recv = 0;
+    for (uint32_t d = 0; d < world; d++) {
+        if (n_recv_out) n_recv_out[d] = dp.n_recv[d];
+        max_recv = std::max(max_recv, dp.n_recv[d]);
+    }
+    for (uint32_t a = 0; a <= bins_a; a++) {
+        if (dp.a_start_send[a] != ctx->a_start_h[a]) {
+            return fail(NPGE_ANCHOR_ERR_PARAMS, "hist_all[rank] differs from this rank's count A");
+        }
+    }
+    if (max_recv > ctx->peer_capacity) {
+        return fail(NPGE_ANCHOR_ERR_CAPACITY, "a receive buffer is too small for " +
+                    std::to_string(max_recv) + " records");
+    }
+    while (ctx->copy_streams.size() < world) {
+        cudaStream_t cs = nullptr;
+        cudaEvent_t ev = nullptr;
+        NPGE_CUDA(cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking));
+        NPGE_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+        ctx->copy_streams.push_back(cs);
+        ctx->copy_events.push_back(ev);
+    }
+    cudaStream_t st = ctx->stream;
+    NPGE_CUDA(cudaEventRecord(ctx->ev[0], st));  // pass A has been enqueued before
+    // ring order of issue: rank r starts with the owner after itself
+    for (uint32_t step = 0; step < world; step++) {
+        const uint32_t d = (rank + 1 + step) % world;
+        const uint32_t lo = dp.cuts[d], hi = dp.cuts[d + 1];
+        const uint64_t first = dp.a_start_send[lo], n = dp.a_start_send[hi] - first;
+        cudaStream_t cs = ctx->copy_streams[d];
+        NPGE_CUDA(cudaStreamWaitEvent(cs, ctx->ev[0], 0));
+        if (n) {
+            const int64_t to = dp.dest_off[lo] + int64_t(first);
+            NPGE_CUDA(cudaMemcpyAsync(static_cast<uint64_t*>(ctx->peer_rec[d]) + to,
+                                      ptr<uint64_t>(ctx->rec[0]) + first, n * 8,
+                                      cudaMemcpyDeviceToDevice, cs));
+            if (plan.wide) {
+                NPGE_CUDA(cudaMemcpyAsync(static_cast<uint32_t*>(ctx->peer_hi[d]) + to,
+                                          ptr<uint32_t>(ctx->rhi[0]) + first, n * 4,
+                                          cudaMemcpyDeviceToDevice, cs));
+            }
+        }
+        NPGE_CUDA(cudaEventRecord(ctx->copy_events[d], cs));
+        NPGE_CUDA(cudaStreamWaitEvent(st, ctx->copy_events[d], 0));
+    }
+    NPGE_CUDA(cudaEventRecord(ctx->ev[1], st));
+    NPGE_CUDA(cudaStreamSynchronize(st));  // every slice has landed (the peers wait at a barrier)
+    cudaEventElapsedTime(&ctx->dist_ms[7], ctx->ev[0], ctx->ev[1]);
+    if (ctx->a_scatter_async) {
+        cudaEventElapsedTime(&ctx->dist_ms[1], ctx->ev_pass[0], ctx->ev_pass[1]);
+        ctx->a_scatter_async = false;
+    }
+    ctx->a_counted = false;
+    ctx->planned = true;
+    return NPGE_ANCHOR_OK;
+}
+
+int npge_anchor_dist_sort_impl(npge_anchor_ctx* ctx, const npge_anchor_params* p,
+                               int32_t stage, uint64_t n_recv, uint32_t n_seg,
+                               const uint32_t* seg_begin, const uint32_t* seg_end,
+                               const uint32_t* seg_a, const uint32_t* seg_tile,
+                               const uint32_t* a_tile0, const uint32_t* a_start,
+                               const uint64_t* used_sorted, uint64_t n_used,
+                               uint64_t* totals);
+
+// npge_anchor_dist_sort over the tables of the last npge_anchor_dist_exchange.
+extern "C" int npge_anchor_dist_sort_planned(npge_anchor_ctx* ctx,
+                                             const npge_anchor_params* p, int32_t stage,
+                                             const uint64_t* used_sorted, uint64_t n_used,
+                                             uint64_t* totals) {
+    if (!ctx) return fail(NPGE_ANCHOR_ERR_PARAMS, "ctx is NULL");
+    if (!ctx->planned) return fail(NPGE_ANCHOR_ERR_STATE, "npge_anchor_dist_exchange has not run");
+    const DistPlan& dp = ctx->dplan;
+    if (stage == 0) {
+        npge_anchor_dist_ptrs unused;
+        NPGE_TRY(npge_anchor_dist_buffers(ctx, dp.n_recv[dp.rank], &unused));
+    }
+    return npge_anchor_dist_sort_impl(ctx, p, stage, dp.n_recv[dp.rank], dp.n_seg,
+                                      dp.seg_begin.data(), dp.seg_end.data(), dp.seg_a.data(),
+                                      dp.seg_tile.data(), dp.a_tile0.data(), dp.a_start.data(),
+                                      used_sorted, n_used, totals);
+}
+
+// The tables alone, on the host (tests; no device needed): out arrays sized by the
+// caller: cuts[world + 1], n_recv[world], dest_rank[bins], dest_off[bins],
+// seg_begin / seg_end / seg_a [world * bins], seg_tile [world * bins + 1],
+// a_tile0 / a_start [bins + 1].  Returns the number of segments in *n_seg.
+extern "C" int npge_anchor_dist_plan_tables(const uint32_t* hist_all, uint32_t world,
+                                            uint32_t bins, uint32_t rank, uint32_t* cuts,
+                                            uint64_t* n_recv, uint32_t* dest_rank,
+                                            int64_t* dest_off, uint32_t* n_seg,
+                                            uint32_t* seg_begin, uint32_t* seg_end,
+                                            uint32_t* seg_a, uint32_t* seg_tile,
+                                            uint32_t* a_tile0, uint32_t* a_start) {
+    if (!hist_all || !world || !bins || rank >= world) {
+        return fail(NPGE_ANCHOR_ERR_PARAMS, "bad arguments");
+    }
+    DistPlan dp;
+    dist_make_plan(hist_all, world, bins, rank, dp);
+    auto put = [](auto* dst, const auto& v) {
+        if (dst) std::copy(v.begin(), v.end(), dst);
+    };
+    put(cuts, dp.cuts);
+    put(n_recv, dp.n_recv);
+    put(dest_rank, dp.dest_rank);
+    put(dest_off, dp.dest_off);
+    put(seg_begin, dp.seg_begin);
+    put(seg_end, dp.seg_end);
+    put(seg_a, dp.seg_a);
+    put(seg_tile, dp.seg_tile);
+    put(a_tile0, dp.a_tile0);
+    put(a_start, dp.a_start);
+    if (n_seg) *n_seg = dp.n_seg;
+    return NPGE_ANCHOR_OK;
+}
+
 extern "C" int npge_anchor_dist_buffers(npge_anchor_ctx* ctx, uint64_t n_recv,
                                         npge_anchor_dist_ptrs* out) {
     if (!ctx || !out) return fail(NPGE_ANCHOR_ERR_PARAMS, "NULL argument");
@@ -1444,6 +1639,17 @@ extern "C" int npge_anchor_dist_sort(npge_anchor_ctx* ctx, const npge_anchor_par
                                      const uint32_t* a_tile0, const uint32_t* a_start,
                                      const uint64_t* used_sorted, uint64_t n_used,
                                      uint64_t* totals) {
+    return npge_anchor_dist_sort_impl(ctx, p, stage, n_recv, n_seg, seg_begin, seg_end, seg_a,
+                                      seg_tile, a_tile0, a_start, used_sorted, n_used, totals);
+}
+
+int npge_anchor_dist_sort_impl(npge_anchor_ctx* ctx, const npge_anchor_params* p,
+                               int32_t stage, uint64_t n_recv, uint32_t n_seg,
+                               const uint32_t* seg_begin, const uint32_t* seg_end,
+                               const uint32_t* seg_a, const uint32_t* seg_tile,
+                               const uint32_t* a_tile0, const uint32_t* a_start,
+                               const uint64_t* used_sorted, uint64_t n_used,
+                               uint64_t* totals) {
     if (!ctx || !totals) return fail(NPGE_ANCHOR_ERR_PARAMS, "NULL argument");
     NPGE_TRY(check_params(p));
     if (!ctx->dist || !ctx->uploaded) {

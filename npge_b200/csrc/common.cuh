@@ -9,6 +9,7 @@
 #include <vector>
 
 #include "../../include/npge_anchor.h"
+#include "dist_plan.h"
 
 namespace npge_b200 {
 
@@ -147,7 +148,12 @@ struct npge_anchor_ctx {
     std::vector<npge_b200::SeqEntry> gseqs;  // ALL sequences, job-wide scan order
     uint64_t g_positions = 0;                // job-wide positions (with pads)
     uint64_t g_padded = 0;
-    npge_b200::DeviceBuffer g_seq_start, g_seq_caller, g_seq_lut, g_seq_pair, pos_delta;
+    npge_b200::DeviceBuffer g_seq_start, g_seq_caller, g_seq_lut, g_seq_pair;
+    npge_b200::DistPlan dplan;               // tables of the last npge_anchor_dist_exchange
+    bool planned = false;
+    std::vector<cudaStream_t> copy_streams;  // one per destination rank
+    std::vector<cudaEvent_t> copy_events;
+    uint64_t dist_g0 = 0, dist_n_own = 0;    // this rank's range of the job-wide positions
     npge_b200::DeviceBuffer recv_rec, recv_hi;
     uint64_t n_recv = 0;
     uint32_t dist_launches = 0;

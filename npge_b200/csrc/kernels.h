@@ -45,17 +45,18 @@ struct SegTables {
     uint32_t* a_start;   // [(1 << capa) + 1] first OUTPUT record of every bucket
 };
 
-// local position -> job-wide position (several GPUs): delta of the sequence
+// One rank of a multi-GPU job scans a RANGE of the job-wide position space: local
+// position p is job-wide position g0 + p, and only the windows that start before
+// win_limit are this rank's (the k - 1 positions after them are the halo that
+// completes its last windows).  One GPU: g0 = 0, win_limit = all.
 struct PosMap {
-    const uint32_t* delta;      // [S] per local scan-order sequence; nullptr: identity
-    const uint64_t* seq_start;  // [S + 1] local starts
-    const uint32_t* lut;
-    int lut_shift;
+    uint32_t g0 = 0;
+    uint32_t win_limit = 0xffffffffu;
     // optional, per A bucket: where the bucket's records go, as addresses such
     // that element idx (the index in this rank's A-sorted order) lands in the
     // owning rank's receive buffer -- peer memory over NVLink.  nullptr: local.
-    const unsigned long long* peer_rec;
-    const unsigned long long* peer_hi;
+    const unsigned long long* peer_rec = nullptr;
+    const unsigned long long* peer_hi = nullptr;
 };
 
 struct MsdBuffers {

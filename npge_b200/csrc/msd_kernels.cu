@@ -81,7 +81,7 @@ __device__ __forceinline__ bool window_key(const GenomeStage& st, uint32_t rel, 
 // ---- count A: one histogram row per genome tile ---------------------------------
 __global__ void __launch_bounds__(kRT)
 count_a_kernel(const uint32_t* __restrict__ packed, const uint32_t* __restrict__ nmask,
-               MsdPlan plan, uint32_t* __restrict__ rows) {
+               MsdPlan plan, uint32_t win_limit, uint32_t* __restrict__ rows) {
     extern __shared__ __align__(16) unsigned char raw[];
     GenomeStage& st = *reinterpret_cast<GenomeStage*>(raw);
     uint32_t* hist = reinterpret_cast<uint32_t*>(raw + sizeof(GenomeStage));
@@ -98,6 +98,7 @@ count_a_kernel(const uint32_t* __restrict__ packed, const uint32_t* __restrict__
         (void)warp;
         const int k = plan.k;
         const uint32_t rel0 = tid * kRI;  // kRI = 8 positions = 16 bits = half a word
+        const uint32_t g_first = blockIdx.x * uint32_t(kTile) + rel0;
         const uint32_t* W = st.w + (rel0 >> 4);
         const uint32_t sh = (rel0 & 15) * 2;
         // 128 bits of bases from position rel0 on (the tile carries 16 B of halo)
@@ -115,7 +116,7 @@ count_a_kernel(const uint32_t* __restrict__ packed, const uint32_t* __restrict__
         uint64_t rev = revcomp_key(dir, k);
 #pragma unroll
         for (int i = 0; i < kRI; i++) {
-            if ((uint32_t(mm) & nm) == 0) {
+            if ((uint32_t(mm) & nm) == 0 && g_first + i < win_limit) {
                 const uint64_t h = dir < rev ? dir : rev;
                 atomicAdd(&hist[uint32_t(h >> sa)], 1u);
             }
@@ -285,12 +286,13 @@ struct __align__(16) PassSmem {
     uint64_t rec[kTile];
     uint32_t hi[WIDE ? kTile : 4];
     uint16_t dig[kTile];  // pass A: the digit is not part of the record
-    uint32_t tile_seq[2]; // pass A, job-wide positions: sequence of the tile's ends
 };
 
 // ---- pass A: generate + partition by the top wa bits -----------------------------
-// GLOBAL: the payload carries the position in the job-wide scan order of all
-// ranks' sequences (local position + the sequence's delta) instead of the local one.
+// The payload carries the JOB-WIDE position (pm.g0 + local position): one rank of a
+// multi-GPU job scans a range of the job's position space; windows that start at or
+// after pm.win_limit belong to the next rank (their bases are this rank's halo).
+// PEER: every bucket's run goes straight into the owning rank's receive buffer.
 // 8-bit digits with narrow records: 52 KB of shared memory and (at some spill) 32
 // registers let four CTAs share an SM; the kernel is latency-bound, occupancy pays
 // (measured on brucella17: 0.545 ms at 2 CTAs, 0.483 at 3, 0.467 at 4; pass B is
@@ -298,7 +300,7 @@ struct __align__(16) PassSmem {
 #ifndef NPGE_PASS_A_CTAS
 #define NPGE_PASS_A_CTAS 4
 #endif
-template <int CAPBITS, bool WIDE, bool GLOBAL>
+template <int CAPBITS, bool WIDE, bool PEER>
 __global__ void __launch_bounds__(kRT, WIDE ? 2 : (CAPBITS == 8 ? NPGE_PASS_A_CTAS : (CAPBITS == 9 ? 3 : 2)))
 pass_a_kernel(const uint32_t* __restrict__ packed, const uint32_t* __restrict__ nmask,
               MsdPlan plan, const uint32_t* __restrict__ rows, PosMap pm,
@@ -310,21 +312,9 @@ pass_a_kernel(const uint32_t* __restrict__ packed, const uint32_t* __restrict__ 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t tile = blockIdx.x;
     const uint32_t gbase = tile * uint32_t(kTile);
-    if (GLOBAL && tid < 2) {  // most tiles lie inside one sequence: one delta for all
-        const uint32_t g = gbase + (tid ? uint32_t(kTile) - 1 : 0u);
-        const uint32_t q = g >> pm.lut_shift;
-        uint32_t lo = pm.lut[q], hi2 = pm.lut[q + 1] + 1;
-        while (hi2 - lo > 1) {
-            uint32_t mid = (lo + hi2) >> 1;
-            if (pm.seq_start[mid] <= g) lo = mid; else hi2 = mid;
-        }
-        sm.tile_seq[tid] = lo;
-    }
     stage_genome_tile(sm.st, packed, nmask, tile);  // (barrier inside)
     const int sa = plan.rem;
     const uint64_t rmask = (1ull << plan.rem) - 1;  // rem <= 63
-    const bool one_seq = GLOBAL && sm.tile_seq[0] == sm.tile_seq[1];
-    const uint32_t delta0 = one_seq ? pm.delta[sm.tile_seq[0]] : 0u;
     // only the key bits stay in registers across the ranking: the payload (position
     // and strand bit) is rebuilt when the record is written into the sorted tile
     uint32_t klo[kRI], hi[kRI], digit[kRI], slot[kRI];
@@ -334,7 +324,7 @@ pass_a_kernel(const uint32_t* __restrict__ packed, const uint32_t* __restrict__ 
         uint32_t rel = warp * (32 * kRI) + i * 32 + lane;
         uint64_t h;
         uint32_t ob;
-        bool ok = window_key(sm.st, rel, plan.k, h, ob);
+        bool ok = window_key(sm.st, rel, plan.k, h, ob) && gbase + rel < pm.win_limit;
         uint64_t kr = h & rmask;
         klo[i] = uint32_t(kr);
         hi[i] = uint32_t(kr >> 32);
@@ -363,18 +353,7 @@ pass_a_kernel(const uint32_t* __restrict__ packed, const uint32_t* __restrict__ 
     for (int i = 0; i < kRI; i++) {
         if (digit[i] < BINS) {
             // payload: position << 1 | (ori == +1)
-            uint32_t g = gbase + warp * (32 * kRI) + i * 32 + lane;
-            if (GLOBAL && one_seq) {
-                g += delta0;
-            } else if (GLOBAL) {
-                const uint32_t q = g >> pm.lut_shift;
-                uint32_t lo = pm.lut[q], hi2 = pm.lut[q + 1] + 1;  // answer in [lo, hi2)
-                while (hi2 - lo > 1) {
-                    uint32_t mid = (lo + hi2) >> 1;
-                    if (pm.seq_start[mid] <= g) lo = mid; else hi2 = mid;
-                }
-                g += pm.delta[lo];
-            }
+            const uint32_t g = pm.g0 + gbase + warp * (32 * kRI) + i * 32 + lane;
             sm.rec[slot[i]] = (uint64_t(klo[i]) << 32) | ((g << 1) | ((obits >> i) & 1u));
             if (WIDE) sm.hi[slot[i]] = hi[i];
             sm.dig[slot[i]] = uint16_t(digit[i]);
@@ -388,7 +367,7 @@ pass_a_kernel(const uint32_t* __restrict__ packed, const uint32_t* __restrict__ 
         if (j < total) {
             const uint32_t d = sm.dig[j];
             uint32_t idx = sm.bin_base[d] + j;
-            if (GLOBAL && pm.peer_rec) {  // straight into the owner's HBM
+            if (PEER) {  // straight into the owner's HBM
                 reinterpret_cast<uint64_t*>(pm.peer_rec[d])[idx] = sm.rec[j];
                 if (WIDE) reinterpret_cast<uint32_t*>(pm.peer_hi[d])[idx] = sm.hi[j];
             } else {
@@ -624,7 +603,7 @@ void launch_msd_pass_a(const MsdPlan& plan, const uint32_t* packed,
     const int bins_a = 1 << plan.capa;
     if (part != 2) {
         count_a_kernel<<<tiles_a, kRT, sizeof(GenomeStage) + bins_a * 4, s>>>(
-            packed, nmask, plan, b.rows);
+            packed, nmask, plan, pm.win_limit, b.rows);
         scan_rows(b.rows, tiles_a, bins_a, b.blk, s);
         a_tables_kernel<<<1, bins_a, 0, s>>>(b.rows + size_t(tiles_a) * bins_a, b.seg,
                                              counters);
@@ -641,7 +620,7 @@ void launch_msd_pass_a(const MsdPlan& plan, const uint32_t* packed,
     } while (0)
 #define NPGE_PASS_A2(CB, W)                                                        \
     do {                                                                           \
-        if (pm.delta) NPGE_PASS_A(CB, W, true); else NPGE_PASS_A(CB, W, false);    \
+        if (pm.peer_rec) NPGE_PASS_A(CB, W, true); else NPGE_PASS_A(CB, W, false); \
     } while (0)
     if (plan.capa == 8) {
         if (plan.wide) NPGE_PASS_A2(8, true); else NPGE_PASS_A2(8, false);

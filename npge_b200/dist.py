@@ -43,24 +43,34 @@ def scan_order(sizes, k):
     return idx[np.argsort(-sizes[idx], kind="stable")]
 
 
-def plan_shards(sizes, k, world):
-    """Cuts the scan order into `world` contiguous ranges of about equal bases.
+POS_ALIGN = 4096  # cuts of the position space fall on pass-A tile borders
 
-    Returns (order, cuts): rank r owns order[cuts[r]:cuts[r + 1]]."""
-    order = scan_order(sizes, k)
-    sz = np.asarray(sizes, dtype=np.int64)[order]
-    csum = np.concatenate([[0], np.cumsum(sz)])
-    total = int(csum[-1])
-    cuts = [0]
-    for r in range(1, world):
-        target = total * r / world
-        # the boundary whose prefix sum is nearest to the target
-        j = int(np.searchsorted(csum, target))
-        if j > 0 and target - csum[j - 1] < csum[min(j, len(sz))] - target:
-            j -= 1
-        cuts.append(min(max(j, cuts[-1]), len(sz)))
-    cuts.append(len(sz))
-    return order, np.asarray(cuts, dtype=np.int64)
+
+def position_cuts(n_positions, world):
+    """Equal ranges of the job's position space: rank r owns the windows
+    that start in [cuts[r], cuts[r + 1]).  The same as dist_position_cuts in
+    csrc/dist_plan.h."""
+    per = -(-(-(-int(n_positions) // world)) // POS_ALIGN) * POS_ALIGN
+    return np.minimum(np.arange(world + 1, dtype=np.int64) * per, int(n_positions))
+
+
+def range_pieces(gstart, lo, hi):
+    """The parts of the sequences (scan order, job-wide starts `gstart`, one pad after
+    each) that lie in the position range [lo, hi): list of (scan index, first base,
+    one past the last base, job-wide position of the first base)."""
+    gstart = np.asarray(gstart, dtype=np.int64)
+    out = []
+    if hi <= lo:
+        return out
+    first = max(int(np.searchsorted(gstart, lo, side="right")) - 1, 0)
+    for i in range(first, len(gstart) - 1):
+        b, e = int(gstart[i]), int(gstart[i + 1]) - 1  # bases of sequence i
+        if b >= hi:
+            break
+        x, y = max(b, lo), min(e, hi)
+        if y > x:
+            out.append((i, x - b, y - b, x))
+    return out
 
 
 def global_starts(sizes_in_scan_order):
@@ -184,21 +194,38 @@ class CudaStages(AnchorEngine):
         AnchorEngine.__init__(self, device)
         self.device = device
 
-    def dist_upload(self, k, seqs, local_gstart, global_start, global_caller):
-        """seqs: list of sequences, or (bases, offsets) with bases a numpy array
-        or a CUDA uint8 tensor (sequences already on the device)."""
-        if isinstance(seqs, tuple):
-            bases, offsets = seqs
-            offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
-        else:
-            bases, offsets = concat(seqs)
+    def dist_upload_range(self, k, bases, pieces, rng, global_start, global_caller):
+        """bases: numpy array or CUDA uint8 tensor holding the pieces; pieces =
+        (src_off, dst_pos, len) uint64 arrays; rng = (g0, n_own, n_have)."""
         base_ptr = bases.data_ptr() if hasattr(bases, "data_ptr") else bases.ctypes.data
-        lg = np.ascontiguousarray(local_gstart, dtype=np.uint64)
+        so, dp, ln = (np.ascontiguousarray(v, dtype=np.uint64) for v in pieces)
         gs = np.ascontiguousarray(global_start, dtype=np.uint64)
         gc = np.ascontiguousarray(global_caller, dtype=np.uint32)
-        self._check(self._lib.npge_anchor_dist_upload(
-            self._ctx, k, base_ptr, offsets.ctypes.data, len(offsets) - 1,
-            lg.ctypes.data, gs.ctypes.data, gc.ctypes.data, len(gc)))
+        self._check(self._lib.npge_anchor_dist_upload_range(
+            self._ctx, k, base_ptr, len(so), so.ctypes.data, dp.ctypes.data, ln.ctypes.data,
+            int(rng[0]), int(rng[1]), int(rng[2]), gs.ctypes.data, gc.ctypes.data, len(gc)))
+
+    def dist_exchange(self, params, hist_all, world, rank):
+        """Plans the exchange from the all-gathered histograms and copies this rank's
+        slices into the owners' receive buffers.  Returns the records every rank
+        receives; raises AnchorError(ERR_CAPACITY) with .n_recv set when a receive
+        buffer is too small."""
+        h = np.ascontiguousarray(hist_all, dtype=np.uint32)
+        n_recv = np.zeros(world, dtype=np.uint64)
+        rc = self._lib.npge_anchor_dist_exchange(
+            self._ctx, C.byref(params), h.ctypes.data, world, rank, n_recv.ctypes.data)
+        if rc != _abi.OK:
+            e = AnchorError(rc, self._lib.npge_anchor_last_error().decode())
+            e.n_recv = [int(x) for x in n_recv]
+            raise e
+        return [int(x) for x in n_recv]
+
+    def dist_sort_planned(self, params, stage, used):
+        u, up = self._used(used)
+        totals = (C.c_uint64 * 2)()
+        self._check(self._lib.npge_anchor_dist_sort_planned(
+            self._ctx, C.byref(params), stage, up, len(u), C.byref(totals)))
+        return int(totals[0]), int(totals[1])
 
     def dist_pass_a(self, params):
         hist = np.zeros(1024, dtype=np.uint32)
@@ -500,81 +527,79 @@ class DistAnchorFinder:
         self._capacity = capacity
 
     # -- upload ------------------------------------------------------------------------
-    def _plan(self, local_sizes, k):
-        """Job-wide plan from every rank's sequence sizes: (sizes in caller order,
-        first caller index of every rank, scan order, owner rank and source rank
-        of every scan position)."""
-        sizes_by_rank = self.comm.gather_objects([int(x) for x in local_sizes])
+    def _rebalance(self, bases, offsets, k):
+        """Gives every rank the bases of ITS range of the job-wide position space
+        (sequences in scan order, one pad after each, cut into `world` equal ranges;
+        plus the k - 1 bases after the range: the halo), wherever the sequences were
+        loaded: one all-to-all of bytes (on the device with NCCL).  Returns
+        (buffer, pieces, range, gstart, job_caller): `pieces` = arrays (src_off,
+        dst_pos, len) placing parts of `buffer` at local positions; range = (g0, n_own,
+        n_have)."""
+        torch = self.comm.torch
+        off = np.asarray(offsets, dtype=np.int64)
+        sizes_by_rank = self.comm.gather_objects([int(x) for x in np.diff(off)])
         counts = [len(x) for x in sizes_by_rank]
         base = np.concatenate([[0], np.cumsum(counts)]).astype(np.int64)
         sizes = np.asarray([x for r in sizes_by_rank for x in r], dtype=np.int64)
         origin = np.repeat(np.arange(self.world), counts)
-        order, cuts = plan_shards(sizes, k, self.world)
-        owner = np.repeat(np.arange(self.world), np.diff(cuts))  # per scan index
-        return sizes, base, order, owner, origin[order]
-
-    def _rebalance(self, bases, offsets, k):
-        """Moves the sequences so that every rank holds a contiguous range of the
-        job-wide scan order (one all-to-all of bytes; on the device with NCCL).
-        Returns ((bases, offsets) of the local sequences in scan order, their
-        job-wide scan indices, sizes of all sequences in scan order, their
-        job-wide caller indices)."""
-        torch = self.comm.torch
-        off = np.asarray(offsets, dtype=np.int64)
-        sizes, base, order, owner, src_of = self._plan(np.diff(off), k)
+        order = scan_order(sizes, k)              # job-wide caller indices in scan order
+        size_at = sizes[order] if len(order) else np.zeros(0, np.int64)
+        gstart = global_starts(size_at).astype(np.int64)
+        total = int(gstart[-1])
+        cuts = position_cuts(total, self.world)
+        have_end = np.minimum(cuts[1:] + (k - 1), total)  # own range + halo
         me = self.rank
-        # what I send to d / receive from s, in scan order
-        send_idx = [np.flatnonzero((src_of == me) & (owner == d)) for d in range(self.world)]
-        recv_idx = [np.flatnonzero((src_of == s) & (owner == me)) for s in range(self.world)]
-        size_at = sizes[order]
-        in_splits = [int(size_at[ix].sum()) for ix in send_idx]
-        out_splits = [int(size_at[ix].sum()) for ix in recv_idx]
+        src_of = origin[order] if len(order) else np.zeros(0, np.int64)
+        # what rank d needs: pieces of [cuts[d], have_end[d]), in scan order
+        need = [range_pieces(gstart, int(cuts[d]), int(have_end[d])) for d in range(self.world)]
+        send_spans, in_splits = [], []
+        for d in range(self.world):
+            n = 0
+            for (i, x, y, g) in need[d]:
+                if src_of[i] == me:
+                    local = int(order[i] - base[me])   # my caller index of the sequence
+                    send_spans.append((int(off[local]) + x, y - x))
+                    n += y - x
+            in_splits.append(n)
+        recv_from = [[(i, x, y, g) for (i, x, y, g) in need[me] if src_of[i] == s_]
+                     for s_ in range(self.world)]
+        out_splits = [sum(y - x for (_, x, y, _) in lst) for lst in recv_from]
         on_device = self.comm.nccl and isinstance(self.stages, CudaStages)
+        src = torch.from_numpy(np.ascontiguousarray(bases))
         if on_device:
             dev = torch.device("cuda", self.device)
-            src = torch.from_numpy(np.ascontiguousarray(bases)).to(dev, non_blocking=True)
+            src = src.to(dev, non_blocking=True)
+        spans = [(a_, n) for a_, n in send_spans if n]
+        if not spans:
+            send = src[:0]
+        elif all(spans[i][0] + spans[i][1] == spans[i + 1][0] for i in range(len(spans) - 1)):
+            send = src[spans[0][0]:spans[-1][0] + spans[-1][1]]   # already contiguous
         else:
-            src = torch.from_numpy(np.ascontiguousarray(bases))
-
-        def pieces(t, spans):
-            spans = [(a, n) for a, n in spans if n]
-            if not spans:
-                return t[:0]
-            if all(spans[i][0] + spans[i][1] == spans[i + 1][0] for i in range(len(spans) - 1)):
-                return t[spans[0][0]:spans[-1][0] + spans[-1][1]]  # already contiguous
-            return torch.cat([t[a:a + n] for a, n in spans])
-
-        local_of = lambda i: int(order[i] - base[me])  # scan index -> my caller index
-        send = pieces(src, [(int(off[local_of(i)]), int(size_at[i]))
-                            for ix in send_idx for i in ix])
+            send = torch.cat([src[a_:a_ + n] for a_, n in spans])
         recv = torch.empty(sum(out_splits), dtype=torch.uint8, device=src.device)
         if on_device:
             self.comm.all_to_all(recv, send.contiguous(), out_splits, in_splits)
-        else:
-            self.comm._a2a_host(recv, send.contiguous(), out_splits, in_splits)
-        # received: source by source, each in scan order -> one run in scan order
-        where, at = {}, 0
-        for ix in recv_idx:
-            for i in ix:
-                where[int(i)] = (at, int(size_at[i]))
-                at += int(size_at[i])
-        idx = sorted(where)
-        local = pieces(recv, [where[i] for i in idx])
-        local_off = np.zeros(len(idx) + 1, dtype=np.uint64)
-        local_off[1:] = np.cumsum([where[i][1] for i in idx])
-        if on_device:
             torch.cuda.current_stream(dev).synchronize()  # the library reads it on its own stream
         else:
-            local = local.numpy()
-        return (local, local_off), np.asarray(idx, dtype=np.int64), size_at, order
+            self.comm._a2a_host(recv, send.contiguous(), out_splits, in_splits)
+            recv = recv.numpy()
+        g0 = int(cuts[me])
+        src_off, dst_pos, lens, at = [], [], [], 0
+        for lst in recv_from:           # the receive buffer: source by source, scan order
+            for (i, x, y, g) in lst:
+                src_off.append(at)
+                dst_pos.append(g - g0)
+                lens.append(y - x)
+                at += y - x
+        pieces = tuple(np.asarray(v, dtype=np.uint64) for v in (src_off, dst_pos, lens))
+        rng = (g0, int(cuts[me + 1]) - g0, int(have_end[me]) - g0)
+        return recv, pieces, rng, gstart.astype(np.uint64), order
 
     def upload(self, seqs, k):
         bases, offsets = seqs if isinstance(seqs, tuple) else concat(seqs)
-        local, idx, job_sizes, job_caller = self._rebalance(bases, offsets, k)
-        gstart = global_starts(job_sizes)
-        self.n_job_bases = int(job_sizes.sum())
-        self.n_local_bases = int(local[1][-1])
-        self.stages.dist_upload(k, local, gstart[idx], gstart, job_caller)
+        buf, pieces, rng, gstart, job_caller = self._rebalance(bases, offsets, k)
+        self.n_job_bases = int(gstart[-1]) - len(job_caller)
+        self.stages.dist_upload_range(k, buf, pieces, rng, gstart, job_caller)
         self._k = k
         if self._want != "collective":
             # room for an uneven split of the job's windows; grown on demand
@@ -618,54 +643,74 @@ class DistAnchorFinder:
 
         dev = comm.torch.device("cuda", self.device) if comm.nccl else None
         fused = self.exchange == "peer"
-        peer = self.exchange in ("peer", "bulk")
-        if peer:
+        bulk = self.exchange == "bulk"
+        if fused or bulk:
             hist = st.dist_count_a(params)
-            if not fused:  # bulk: pass A runs while the histograms are gathered
+            if bulk:  # pass A runs while the histograms are gathered
                 st.dist_scatter_local(params)
             lap("count_a")
         else:
             hist = st.dist_pass_a(params)
             lap("pass_a")
-        # (also the step's barrier: no rank scatters into a receive buffer whose
+        # (also the step's barrier: no rank writes into a receive buffer whose
         # owner has not finished its previous step)
         hist_all = comm.gather_array(hist, dev)
         lap("gather_hist")
-        cuts = bucket_ranges(hist_all, self.world)
-        tables = segment_tables(hist_all, cuts, self.rank)
-        if peer:
-            dest_rank, dest_off, n_recv = peer_destinations(hist_all, cuts, self.rank)
-            lap("tables")
-            if max(n_recv) > self._capacity:  # the same decision on every rank
-                self._peer_setup(max(n_recv) * 9 // 8 + 65536)
+        if bulk:
+            # tables and copies in the library (csrc/dist_plan.h): no numpy on the path
+            try:
+                n_recv = st.dist_exchange(params, hist_all, self.world, self.rank)
+            except AnchorError as e:
+                if e.code != _abi.ERR_CAPACITY:
+                    raise
+                # the same decision on every rank (same histograms, same capacity)
+                self._peer_setup(max(e.n_recv) * 9 // 8 + 65536)
                 if self.exchange == "collective":
                     raise AnchorError(_abi.ERR_CUDA, "peer buffers could not be regrown")
+                n_recv = st.dist_exchange(params, hist_all, self.world, self.rank)
+            lap("exchange")
+            self._timed("barrier", lambda: comm.barrier(dev))  # every copy has landed
+            lap("barrier")
+            totals = st.dist_sort_planned(params, 0, used)
+            lap("sort")
+            if similar:
+                found = st.dist_buffers(0, n_recv[self.rank])["found"]
+                self._timed("found_bits", lambda: comm.sum_(found))
+                lap("reduce_found")
+                totals = st.dist_sort_planned(params, 1, used)
+                lap("count")
+        else:
+            cuts = bucket_ranges(hist_all, self.world)
+            tables = segment_tables(hist_all, cuts, self.rank)
             if fused:
+                dest_rank, dest_off, n_recv = peer_destinations(hist_all, cuts, self.rank)
+                lap("tables")
+                if max(n_recv) > self._capacity:  # the same decision on every rank
+                    self._peer_setup(max(n_recv) * 9 // 8 + 65536)
+                    if self.exchange == "collective":
+                        raise AnchorError(_abi.ERR_CUDA, "peer buffers could not be regrown")
                 st.dist_scatter_peer(params, dest_rank, dest_off)
                 lap("scatter_peer")
+                self._timed("barrier", lambda: comm.barrier(dev))  # every scatter has landed
+                lap("barrier")
+                buf = st.dist_buffers(0, tables["n_recv"])
             else:
-                st.dist_copy_peer(params, dest_rank, dest_off)
-                lap("copy_peer")
-            self._timed("barrier", lambda: comm.barrier(dev))  # every scatter has landed
-            lap("barrier")
-            buf = st.dist_buffers(0, tables["n_recv"])
-        else:
-            send_splits, recv_splits = exchange_splits(hist_all, cuts, self.rank)
-            lap("tables")
-            buf = st.dist_buffers(sum(send_splits), tables["n_recv"])
-            self._timed("records", lambda: comm.all_to_all(
-                buf["recv_rec"], buf["send_rec"], recv_splits, send_splits))
-            if buf["send_hi"] is not None:
+                send_splits, recv_splits = exchange_splits(hist_all, cuts, self.rank)
+                lap("tables")
+                buf = st.dist_buffers(sum(send_splits), tables["n_recv"])
                 self._timed("records", lambda: comm.all_to_all(
-                    buf["recv_hi"], buf["send_hi"], recv_splits, send_splits))
-            lap("all_to_all")
-        totals = st.dist_sort(params, 0, tables, used)
-        lap("sort")
-        if similar:
-            self._timed("found_bits", lambda: comm.sum_(buf["found"]))
-            lap("reduce_found")
-            totals = st.dist_sort(params, 1, tables, used)
-            lap("count")
+                    buf["recv_rec"], buf["send_rec"], recv_splits, send_splits))
+                if buf["send_hi"] is not None:
+                    self._timed("records", lambda: comm.all_to_all(
+                        buf["recv_hi"], buf["send_hi"], recv_splits, send_splits))
+                lap("all_to_all")
+            totals = st.dist_sort(params, 0, tables, used)
+            lap("sort")
+            if similar:
+                self._timed("found_bits", lambda: comm.sum_(buf["found"]))
+                lap("reduce_found")
+                totals = st.dist_sort(params, 1, tables, used)
+                lap("count")
         tot_all = comm.gather_array(np.asarray(totals, dtype=np.int64), dev)
         lap("gather_totals")
         limits = local_limits(tot_all[:, 0], int(max_frags))
@@ -681,14 +726,8 @@ class DistAnchorFinder:
             n_positions=self.n_job_bases, local_fragments=s["n_fragments"],
             local_records=s["n_windows"], total_selected=int(tot_all[:, 0].sum()),
             exchange_ms=dict(self.exchange_ms), exchange=self.exchange,
-            host_ms=trace, bucket_cuts=[int(c) for c in cuts],
-            # records this rank wrote into other ranks' HBM, and the device time of
-            # the stage that moved them (bulk: the copy kernels; peer: pass A itself)
-            nvlink_bytes_sent=int(hist.sum() - hist[int(cuts[self.rank]):int(cuts[self.rank + 1])].sum())
-            * (12 if k > 21 else 8),
-            nvlink_ms=(s["ms_pass"][5] if self.exchange == "bulk"
-                       else s["ms_pass"][0] if self.exchange == "peer"
-                       else self.exchange_ms.get("records", 0.0)))
+            host_ms=trace)
+        self._hist_all, self._hist = hist_all, hist
         self._last = out
         if job_stats:
             self.job_stats()
@@ -704,6 +743,16 @@ class DistAnchorFinder:
         dg = np.asarray([s["digest"][0], s["digest"][1]], dtype=np.uint64).view(np.int64)
         job = self.comm.gather_array(np.concatenate([d, dg]), dev)
         mask = (1 << 64) - 1
+        # records this rank wrote into other ranks' HBM, and the device time of the
+        # stage that moved them (bulk: the copies; peer: pass A itself)
+        cuts = bucket_ranges(self._hist_all, self.world)
+        hist = np.asarray(self._hist, dtype=np.int64)
+        kept = int(hist[int(cuts[self.rank]):int(cuts[self.rank + 1])].sum())
+        out.update(bucket_cuts=[int(c) for c in cuts],
+                   nvlink_bytes_sent=(int(hist.sum()) - kept) * (12 if self._k > 21 else 8),
+                   nvlink_ms=(s["ms_pass"][5] if self.exchange == "bulk"
+                              else s["ms_pass"][0] if self.exchange == "peer"
+                              else out.get("exchange_ms", {}).get("records", 0.0)))
         out.update(n_blocks=int(job[:, 0].sum()), job_launches=int(job[:, 1].sum()),
                    bytes_algorithmic_job=int(job[:, 2].sum()),
                    bytes_moved_job=int(job[:, 3].sum()),

@@ -45,30 +45,33 @@ class Result:
 
 
 class NumpyStages:
-    def dist_upload(self, k, seqs, local_gstart, global_start, global_caller):
+    def dist_upload_range(self, k, bases, pieces, rng, global_start, global_caller):
+        """This rank's range of the job-wide position space: local position p is
+        job-wide position g0 + p; positions no piece covers are pads."""
         self.k = k
-        if isinstance(seqs, tuple):
-            b, o = seqs
-            seqs = [b[int(o[i]):int(o[i + 1])] for i in range(len(o) - 1)]
-        self.seqs = [np.asarray(s, dtype=np.uint8) for s in seqs]
-        self.lstart = np.asarray(local_gstart, dtype=np.uint64)
+        g0, n_own, n_have = (int(x) for x in rng)
+        buf = np.asarray(bases, dtype=np.uint8)
+        local = np.full(n_have, ord("N"), dtype=np.uint8)
+        for so, dp, ln in zip(*pieces):
+            so, dp, ln = int(so), int(dp), int(ln)
+            assert dp + ln <= n_have
+            local[dp:dp + ln] = buf[so:so + ln]
+        self.local, self.g0, self.n_own = local, g0, n_own
         self.gstart = np.asarray(global_start, dtype=np.uint64)
         self.gcaller = np.asarray(global_caller, dtype=np.uint32)
-        sizes = [len(s) for s in self.seqs]
-        assert sizes == sorted(sizes, reverse=True), "local scan order"
-        assert list(self.lstart) == sorted(self.lstart), "contiguous range"
+        # the range must be what the job-wide layout says: pads exactly at the pads
+        gs = self.gstart.astype(np.int64)
+        pads = gs[1:] - 1
+        pads = pads[(pads >= g0) & (pads < g0 + n_have)] - g0
+        assert np.all(local[pads] == ord("N"))
 
     def dist_pass_a(self, params):
         k = self.k
-        hs, gs, ds = [], [], []
-        for s, g0 in zip(self.seqs, self.lstart):
-            h, pos, d = _windows(s, k)
-            hs.append(h)
-            gs.append(pos + g0)
-            ds.append(d)
-        h = np.concatenate(hs) if hs else np.zeros(0, np.uint64)
-        g = np.concatenate(gs) if gs else np.zeros(0, np.uint64)
-        d = np.concatenate(ds) if ds else np.zeros(0, bool)
+        # the pads keep windows from crossing a sequence end; windows starting in the
+        # halo belong to the next rank
+        h, pos, d = _windows(self.local, k)
+        own = pos < np.uint64(self.n_own)
+        h, g, d = h[own], pos[own] + np.uint64(self.g0), d[own]
         shift = max(2 * k - 8, 0)
         a = (h >> np.uint64(shift)).astype(np.int64)
         order = np.argsort(a, kind="stable")

@@ -46,7 +46,11 @@ def main():
         from dist_standin import NumpyStages
         backend, stages = "gloo", NumpyStages()
     dist.init_process_group(backend, rank=rank, world_size=world)
-    names, seqs = synth.generate(config, scale=scale)
+    if config == "oneseq":  # one chromosome (+ a fragment): fewer sequences than ranks
+        names, parts = synth.generate("tiny", scale=scale)
+        seqs = [np.concatenate(parts), parts[1][50:400]]
+    else:
+        names, seqs = synth.generate(config, scale=scale)
     if config == "tiny":  # some short and some equal-sized sequences too
         seqs = seqs + [seqs[0][:k - 1], seqs[1][100:700], seqs[2][50:650], seqs[0][:0]]
     parts = [placement(len(seqs), r, world, how) for r in range(world)]

@@ -47,16 +47,19 @@ def launch(world, args, timeout=600, extra_env=None):
     return outs
 
 
-def test_scan_order_and_shards():
+def test_scan_order_and_position_ranges():
     sizes = [10, 50, 3, 50, 20, 7]
     order = D.scan_order(sizes, 5)
     assert list(order) == [1, 3, 4, 0, 5]          # size desc, ties by index; 3 < k
-    order, cuts = D.plan_shards(sizes, 5, 2)
-    assert list(cuts) == [0, 1, 5] or list(cuts) == [0, 2, 5]
-    order, cuts = D.plan_shards(sizes, 5, 8)       # more ranks than sequences
-    assert cuts[0] == 0 and cuts[-1] == 5 and np.all(np.diff(cuts) >= 0)
-    order, cuts = D.plan_shards([], 5, 3)
-    assert list(cuts) == [0, 0, 0, 0]
+    cuts = D.position_cuts(10000, 3)               # equal ranges on tile borders
+    assert list(cuts) == [0, 4096, 8192, 10000]
+    assert list(D.position_cuts(100, 4)) == [0, 100, 100, 100, 100]
+    assert list(D.position_cuts(0, 2)) == [0, 0, 0]
+    # sequences of 5 and 3 bases: job positions 0..4 | pad 5 | 6..8 | pad 9
+    gs = D.global_starts([5, 3])
+    assert D.range_pieces(gs, 0, 10) == [(0, 0, 5, 0), (1, 0, 3, 6)]
+    assert D.range_pieces(gs, 3, 7) == [(0, 3, 5, 3), (1, 0, 1, 6)]   # a sequence is cut
+    assert D.range_pieces(gs, 5, 6) == [] and D.range_pieces(gs, 4, 4) == []
     assert list(D.global_starts([5, 3])) == [0, 6, 10]
 
 
@@ -124,6 +127,51 @@ def test_peer_destinations_match_the_receive_layout():
             assert [g[2] for g in got] == list(range(len(got)))
 
 
+def plan_tables_cxx(h, rank):
+    """npge_anchor_dist_plan_tables (csrc/dist_plan.h) through the C ABI; host only."""
+    from npge_b200 import _abi
+    L = _abi.load()
+    h = np.ascontiguousarray(h, dtype=np.uint32)
+    world, bins = h.shape
+    u32 = lambda n: np.zeros(n, dtype=np.uint32)
+    cuts, n_recv = u32(world + 1), np.zeros(world, dtype=np.uint64)
+    dest_rank, dest_off = u32(bins), np.zeros(bins, dtype=np.int64)
+    n_seg = np.zeros(1, dtype=np.uint32)
+    sb, se, sa, stl = u32(world * bins), u32(world * bins), u32(world * bins), u32(world * bins + 1)
+    at0, ast = u32(bins + 1), u32(bins + 1)
+    rc = L.npge_anchor_dist_plan_tables(
+        h.ctypes.data, world, bins, rank, *[x.ctypes.data for x in (
+            cuts, n_recv, dest_rank, dest_off, n_seg, sb, se, sa, stl, at0, ast)])
+    assert rc == 0
+    n = int(n_seg[0])
+    return dict(cuts=cuts, n_recv_all=n_recv, dest_rank=dest_rank, dest_off=dest_off, n_seg=n,
+                seg_begin=sb[:n], seg_end=se[:n], seg_a=sa[:n], seg_tile=stl[:n + 1],
+                a_tile0=at0, a_start=ast)
+
+
+@pytest.mark.parametrize("seed,world,bins", [(1, 2, 256), (2, 3, 16), (3, 8, 1024), (4, 4, 512)])
+def test_cxx_plan_tables_equal_the_numpy_ones(seed, world, bins):
+    """The library plans the exchange in C++ (no numpy on the step's path); the numpy
+    functions of dist.py, which the stand-in job checks against the oracle, are the
+    restatement it must agree with."""
+    rng = np.random.default_rng(seed)
+    h = rng.integers(0, 9000, size=(world, bins))
+    h[rng.random((world, bins)) < 0.3] = 0
+    if seed == 2:
+        h[:, 5:] = 0                       # ranks that receive nothing
+    cuts = D.bucket_ranges(h, world)
+    for rank in range(world):
+        t = plan_tables_cxx(h, rank)
+        assert list(t["cuts"]) == list(cuts)
+        want = D.segment_tables(h, cuts, rank)
+        for key in ("n_seg", "seg_begin", "seg_end", "seg_a", "seg_tile", "a_tile0", "a_start"):
+            assert np.array_equal(np.asarray(t[key]), np.asarray(want[key])), key
+        dest_rank, dest_off, n_recv = D.peer_destinations(h, cuts, rank)
+        assert np.array_equal(t["dest_rank"], dest_rank)
+        assert np.array_equal(t["dest_off"], dest_off)
+        assert [int(x) for x in t["n_recv_all"]] == n_recv
+
+
 def test_local_limits():
     assert D.local_limits([10, 0, 7, 5], 12) == [10, 0, 2, 0]
     assert D.local_limits([10, 7], 100) == [10, 7]
@@ -137,3 +185,9 @@ def test_two_ranks_gloo_standin(how):
 
 def test_three_ranks_gloo_standin_wide_key():
     launch(3, ["standin", "tiny", 1.0, 27, "interleaved"])
+
+
+def test_one_sequence_over_three_ranks_standin():
+    """Positions are sharded, not sequences: one chromosome is cut into
+    three ranges with k - 1 bases of halo and the job equals the oracle's answer."""
+    launch(3, ["standin", "oneseq", 1.0, 16, "interleaved"])

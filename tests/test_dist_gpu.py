@@ -30,3 +30,10 @@ def test_two_ranks_small(exchange):
     out = launch(2, ["cuda", "small", 1.0, 20, "interleaved"],
                  extra_env={"NPGE_ANCHOR_EXCHANGE": exchange})
     assert "blocks" in out[0]
+
+
+@pytest.mark.parametrize("exchange", ["bulk", "collective"])
+def test_one_sequence_over_three_ranks(exchange):
+    """Positions are sharded, not sequences: one chromosome over three ranks."""
+    launch(3, ["cuda", "oneseq", 1.0, 20, "interleaved"],
+           extra_env={"NPGE_ANCHOR_EXCHANGE": exchange})
