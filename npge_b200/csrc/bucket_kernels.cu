@@ -642,66 +642,6 @@ __device__ __forceinline__ void whole_unit_chunk(BucketSmem<WIDE>& sm, uint32_t 
     ch.carry_head = s;
 }
 
-// Parity / exact mode, the sorted unit in sm.half[cur]: every thread reads its kRI
-// records once, gets the neighbours' keys by shuffles, counts the anchors (a group
-// of >= 2 whose hash is not used), leaves the per-warp totals for the emit kernel
-// and writes the records back.  Returns the unit's total (blocks << 31 | fragments).
-template <bool WIDE>
-__device__ __forceinline__ uint64_t count_and_store_unit(BucketSmem<WIDE>& sm,
-                                                         const BucketArgs& a, uint32_t w,
-                                                         uint32_t s, uint32_t n, int cur,
-                                                         uint64_t key_hi) {
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const uint64_t* buf = sm.half[cur].buf + 1;
-    const uint32_t* hib = sm.half[cur].hib + 1;
-    const uint32_t j0 = warp * (32 * kRI);
-    uint64_t rec[kRI], key[kRI];
-    uint32_t hi[kRI];
-#pragma unroll
-    for (int i = 0; i < kRI; i++) {
-        const uint32_t j = j0 + i * 32 + lane;
-        rec[i] = j < n ? buf[j] : 0ull;
-        hi[i] = (WIDE && j < n) ? hib[j] : 0u;
-        key[i] = rem_key(rec[i], hi[i]);
-    }
-    uint64_t edge_prev = 0, edge_next = 0;
-    if (lane == 0 && j0 > 0 && j0 - 1 < n) edge_prev = rem_key(buf[j0 - 1], WIDE ? hib[j0 - 1] : 0u);
-    if (lane == 31 && j0 + 32 * kRI < n) {
-        edge_next = rem_key(buf[j0 + 32 * kRI], WIDE ? hib[j0 + 32 * kRI] : 0u);
-    }
-    uint32_t nf = 0, nb = 0;
-#pragma unroll
-    for (int i = 0; i < kRI; i++) {
-        const uint32_t j = j0 + i * 32 + lane;
-        uint64_t kp = __shfl_up_sync(0xffffffffu, key[i], 1);
-        uint64_t kn = __shfl_down_sync(0xffffffffu, key[i], 1);
-        const uint64_t from31 = __shfl_sync(0xffffffffu, key[i > 0 ? i - 1 : 0], 31);
-        const uint64_t from0 = __shfl_sync(0xffffffffu, key[i < kRI - 1 ? i + 1 : kRI - 1], 0);
-        if (lane == 0) kp = i > 0 ? from31 : edge_prev;
-        if (lane == 31) kn = i < kRI - 1 ? from0 : edge_next;
-        const bool in = j < n;
-        const bool pe = in && j > 0 && kp == key[i];
-        const bool ne = in && j + 1 < n && kn == key[i];
-        bool sel = pe || ne;
-        if (sel && a.n_used) sel = !is_used(a, key_hi | key[i]);
-        nf += __popc(__ballot_sync(0xffffffffu, sel));
-        nb += __popc(__ballot_sync(0xffffffffu, sel && !pe));
-        if (in) {
-            a.rec_w[s + j] = rec[i];
-            if (WIDE) a.hi_w[s + j] = hi[i];
-        }
-    }
-    if (lane == 0) {
-        sm.warp_tot[warp] = (uint64_t(nb) << 31) | nf;
-        a.unit_wtot[size_t(w) * kRW + warp] = nf | (nb << 16);
-    }
-    __syncthreads();
-    uint64_t tot = 0;
-#pragma unroll
-    for (int x = 0; x < kRW; x++) tot += sm.warp_tot[x];
-    return tot;
-}
-
 // ---- kernel 1: sort every unit; MODE 0 also counts its anchors, MODE 1
 // (anchor-similar) sets the found bits instead.  The sorted unit is written back.
 template <bool WIDE, int MODE>
@@ -719,14 +659,20 @@ bucket_sort_kernel(BucketArgs a) {
     if (n <= uint32_t(kCap)) {
         load_unit<WIDE>(sm, a, s, n);
         const int cur = sort_unit_smem<WIDE>(sm, a.plan, n);
+        whole_unit_chunk<WIDE>(sm, s, n, cur, ch);
+        unit_flags<WIDE>(ch, valid, preveq, inb);
         if (MODE == 1) {
-            whole_unit_chunk<WIDE>(sm, s, n, cur, ch);
-            unit_flags<WIDE>(ch, valid, preveq, inb);
             mark_found<WIDE>(ch, a, key_hi, preveq);
-            store_unit<WIDE>(sm, a, s, n, cur);
         } else {
-            tot = count_and_store_unit<WIDE>(sm, a, w, s, n, cur, key_hi);
+            tot = unit_select<WIDE, 0>(sm, ch, a, key_hi, valid, preveq, inb, sel);
+            // the emit kernel ranks its fragments from these, without a count of its own
+            if ((threadIdx.x & 31) == 0) {
+                const uint64_t wt = sm.warp_tot[threadIdx.x >> 5];
+                a.unit_wtot[size_t(w) * kRW + (threadIdx.x >> 5)] =
+                    uint32_t(wt & 0xffff) | (uint32_t(wt >> 31) << 16);
+            }
         }
+        store_unit<WIDE>(sm, a, s, n, cur);
     } else {
         sort_unit_global<WIDE>(sm, a, s, n);
         for (uint32_t c0 = 0; c0 < n; c0 += kCap) {
