@@ -325,14 +325,14 @@ def run_c5(args, rank, world, runner_factory, torch, dist, flush, hbm_peak):
             out["parity"] = par
             out["kernel_ms_rank0"] = float(np.mean([x["ms_total"] for x in sts]))
             if world > 1:
-                sent = float(np.mean([x.get("nvlink_bytes_sent", 0) for x in sts]))
-                x_ms = float(np.mean([x.get("nvlink_ms", 0.0) for x in sts]))
+                sent = float(st.get("nvlink_bytes_sent", 0))  # rank 0, the last timed step
+                x_ms = float(st.get("nvlink_ms", 0.0))
                 out["nvlink"] = {
                     "bytes_per_gpu": sent, "ms": x_ms,
                     "gb_s": sent / (x_ms * 1e-3) / 1e9 if x_ms > 0 else None,
                     "frac_of_900": sent / (x_ms * 1e-3) / 900e9 if x_ms > 0 else None,
                     "survey_model_bytes_per_gpu": 12.0 * n_total / world * (world - 1) / world,
-                    "exchange": sts[-1].get("exchange"),
+                    "exchange": st.get("exchange"),
                     "note": "rank 0: bytes it wrote into the other ranks' HBM / device "
                             "time of its exchange stage"}
             # default options on the same resident genome

@@ -207,9 +207,9 @@ int npge_anchor_dist_upload_range(npge_anchor_ctx* ctx, int32_t anchor_size,
                                   const uint32_t* global_caller, uint32_t n_global);
 int npge_anchor_dist_pass_a(npge_anchor_ctx* ctx, const npge_anchor_params* p,
                             uint32_t* hist_out, uint32_t hist_cap, uint32_t* n_bins);
-/* The exchange without a separate all-to-all: pass A scatters every bucket
- * straight into the owning rank's receive buffer (peer memory over NVLink,
- * mapped through CUDA IPC).
+/* Receive buffers shared between the ranks (CUDA IPC), and the "peer" variant of the
+ * exchange: pass A scatters every bucket straight into the owning rank's receive
+ * buffer over NVLink.
  *   dist_peer_alloc    (re)allocates this rank's receive buffers for `capacity`
  *                      records and returns their IPC handles
  *   [all-gather of the handles]
@@ -231,16 +231,9 @@ int npge_anchor_dist_count_a(npge_anchor_ctx* ctx, const npge_anchor_params* p,
 int npge_anchor_dist_scatter_peer(npge_anchor_ctx* ctx, const npge_anchor_params* p,
                                   const uint32_t* dest_rank, const int64_t* dest_off,
                                   uint32_t n_bins);
-/* The bulk variant of the peer exchange: after dist_pass_a (local pass A) the
- * contiguous slice of every destination is copied into its receive buffer by a
- * copy kernel (same dest_rank / dest_off tables as dist_scatter_peer).
- * dist_count_a + dist_scatter_local is dist_pass_a in two steps; the second only
- * enqueues pass A, so that the all-gather of the histograms and the host tables
- * overlap it. */
+/* dist_count_a + dist_scatter_local is dist_pass_a in two steps; the second only
+ * enqueues pass A, so that the all-gather of the histograms overlaps it. */
 int npge_anchor_dist_scatter_local(npge_anchor_ctx* ctx, const npge_anchor_params* p);
-int npge_anchor_dist_copy_peer(npge_anchor_ctx* ctx, const npge_anchor_params* p,
-                               const uint32_t* dest_rank, const int64_t* dest_off,
-                               uint32_t n_bins);
 /* hist_all[world][bins]: the all-gathered results of dist_count_a.  n_recv_out[world]
  * (optional): records every rank receives.  NPGE_ANCHOR_ERR_CAPACITY when a receive
  * buffer is too small (n_recv_out valid: regrow with dist_peer_alloc and call again). */

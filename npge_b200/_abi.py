@@ -19,7 +19,7 @@ EXPORTS = [
     "npge_anchor_dist_buffers", "npge_anchor_dist_sort", "npge_anchor_dist_emit",
     "npge_anchor_dist_peer_alloc", "npge_anchor_dist_peer_open",
     "npge_anchor_dist_peer_close", "npge_anchor_dist_count_a",
-    "npge_anchor_dist_scatter_peer", "npge_anchor_dist_copy_peer",
+    "npge_anchor_dist_scatter_peer",
     "npge_fragment_find", "npge_fragment_find_device", "npge_fragment_result_free",
     "npge_anchor_upload_raw", "npge_anchor_dist_scatter_local",
     "npge_block_hashes", "npge_anchor_block_hashes", "npge_block_hashes_last_ms",
@@ -142,8 +142,6 @@ def load():
                                                 C.c_void_p, C.c_uint32]
     L.npge_anchor_dist_scatter_local.restype = C.c_int
     L.npge_anchor_dist_scatter_local.argtypes = [ctx, C.POINTER(Params)]
-    L.npge_anchor_dist_copy_peer.restype = C.c_int
-    L.npge_anchor_dist_copy_peer.argtypes = L.npge_anchor_dist_scatter_peer.argtypes
     L.npge_anchor_dist_buffers.restype = C.c_int
     L.npge_anchor_dist_buffers.argtypes = [ctx, C.c_uint64, C.POINTER(DistPtrs)]
     L.npge_anchor_dist_sort.restype = C.c_int

@@ -1364,8 +1364,7 @@ extern "C" int npge_anchor_dist_scatter_peer(npge_anchor_ctx* ctx,
 }
 
 // pass A into this rank's own memory, asynchronously: the caller overlaps the
-// histogram all-gather and its host tables with it; npge_anchor_dist_copy_peer
-// (same stream) follows
+// histogram all-gather with it; npge_anchor_dist_exchange follows
 extern "C" int npge_anchor_dist_scatter_local(npge_anchor_ctx* ctx,
                                               const npge_anchor_params* p) {
     if (!ctx) return fail(NPGE_ANCHOR_ERR_PARAMS, "ctx is NULL");
@@ -1391,65 +1390,6 @@ extern "C" int npge_anchor_dist_scatter_local(npge_anchor_ctx* ctx,
     NPGE_CUDA(cudaEventRecord(ctx->ev_pass[1], st));
     ctx->a_scattered = true;
     ctx->a_scatter_async = true;
-    return NPGE_ANCHOR_OK;
-}
-
-extern "C" int npge_anchor_dist_copy_peer(npge_anchor_ctx* ctx, const npge_anchor_params* p,
-                                          const uint32_t* dest_rank, const int64_t* dest_off,
-                                          uint32_t n_bins) {
-    if (!ctx || !dest_rank || !dest_off) return fail(NPGE_ANCHOR_ERR_PARAMS, "NULL argument");
-    NPGE_TRY(check_params(p));
-    if (!ctx->dist || !ctx->a_counted || !ctx->a_scattered) {
-        return fail(NPGE_ANCHOR_ERR_STATE, "npge_anchor_dist_pass_a has not run");
-    }
-    const MsdPlan plan = ctx->plan;
-    const uint32_t bins_a = 1u << plan.capa;
-    if (n_bins != bins_a) return fail(NPGE_ANCHOR_ERR_PARAMS, "n_bins differs from the plan");
-    if (ctx->peer_rec.empty()) {
-        return fail(NPGE_ANCHOR_ERR_STATE, "npge_anchor_dist_peer_open has not been called");
-    }
-    NPGE_CUDA(cudaSetDevice(ctx->device));
-    cudaStream_t st = ctx->stream;
-    const std::vector<uint32_t>& as = ctx->a_start_h;
-    NPGE_CUDA(cudaEventRecord(ctx->ev[0], st));
-    // one copy per run of buckets with one owner
-    struct Run { uint32_t d; uint64_t first, n; int64_t to; };
-    std::vector<Run> runs;
-    for (uint32_t a = 0; a < bins_a;) {
-        uint32_t e = a + 1;
-        while (e < bins_a && dest_rank[e] == dest_rank[a] && dest_off[e] == dest_off[a]) e++;
-        const uint32_t d = dest_rank[a];
-        if (d >= ctx->peer_rec.size()) return fail(NPGE_ANCHOR_ERR_PARAMS, "dest_rank out of range");
-        const uint64_t first = as[a], n = as[e] - as[a];
-        const int64_t to = dest_off[a] + int64_t(first);
-        if (n && (to < 0 || uint64_t(to) + n > ctx->peer_capacity)) {
-            return fail(NPGE_ANCHOR_ERR_PARAMS, "destination outside the receive buffer");
-        }
-        if (n) runs.push_back({d, first, n, to});
-        a = e;
-    }
-    // ring order: rank r starts with the owner after itself, so that in every
-    // round each receive buffer is written by one sender (no incast on a link)
-    const uint32_t world = uint32_t(ctx->peer_rec.size());
-    std::stable_sort(runs.begin(), runs.end(), [&](const Run& x, const Run& y) {
-        return (x.d + world - ctx->dist_rank - 1) % world < (y.d + world - ctx->dist_rank - 1) % world;
-    });
-    for (const Run& r : runs) {
-        launch_peer_copy(ptr<uint64_t>(ctx->rec[0]) + r.first,
-                         static_cast<uint64_t*>(ctx->peer_rec[r.d]) + r.to,
-                         plan.wide ? ptr<uint32_t>(ctx->rhi[0]) + r.first : nullptr,
-                         plan.wide ? static_cast<uint32_t*>(ctx->peer_hi[r.d]) + r.to : nullptr,
-                         r.n, st, &ctx->dist_launches);
-    }
-    NPGE_CUDA(cudaGetLastError());
-    NPGE_CUDA(cudaEventRecord(ctx->ev[1], st));
-    NPGE_CUDA(cudaStreamSynchronize(st));
-    cudaEventElapsedTime(&ctx->dist_ms[7], ctx->ev[0], ctx->ev[1]);
-    if (ctx->a_scatter_async) {
-        cudaEventElapsedTime(&ctx->dist_ms[1], ctx->ev_pass[0], ctx->ev_pass[1]);
-        ctx->a_scatter_async = false;
-    }
-    ctx->a_counted = false;
     return NPGE_ANCHOR_OK;
 }
 

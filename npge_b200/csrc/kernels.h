@@ -84,9 +84,6 @@ void launch_msd_pass_a(const MsdPlan& plan, const uint32_t* packed,
                        const uint32_t* nmask, uint64_t n_padded, const MsdBuffers& b,
                        const PosMap& pm, uint32_t* counters, cudaStream_t s,
                        cudaEvent_t* ev, uint32_t* launches, int part = 0);
-// contiguous copy of n elements into (possibly peer) memory: the bulk exchange
-void launch_peer_copy(const uint64_t* src, uint64_t* dst, const uint32_t* src_hi,
-                      uint32_t* dst_hi, uint64_t n, cudaStream_t s, uint32_t* launches);
 void launch_msd_pass_b(const MsdPlan& plan, const uint64_t* in_rec, const uint32_t* in_hi,
                        uint64_t max_records, uint32_t max_seg, const MsdBuffers& b,
                        cudaStream_t s, cudaEvent_t* ev, uint32_t* launches);

@@ -635,47 +635,6 @@ void launch_msd_pass_a(const MsdPlan& plan, const uint32_t* packed,
     if (ev) cudaEventRecord(ev[1], s);
 }
 
-// ---- bulk exchange: this rank's slice of one destination, written into the
-// owner's receive buffer (peer memory over NVLink) in 16-byte, fully coalesced
-// stores; the few leading / trailing elements that break the alignment go singly
-__global__ void __launch_bounds__(512)
-peer_copy_kernel(const uint64_t* __restrict__ src, uint64_t* __restrict__ dst,
-                 const uint32_t* __restrict__ src_hi, uint32_t* __restrict__ dst_hi,
-                 uint64_t n) {
-    const uint64_t tid = blockIdx.x * uint64_t(blockDim.x) + threadIdx.x;
-    const uint64_t stride = uint64_t(gridDim.x) * blockDim.x;
-    // records: align the DESTINATION to 16 B (remote stores matter more)
-    uint64_t head = (reinterpret_cast<uintptr_t>(dst) >> 3) & 1;
-    if (head > n) head = n;
-    if (tid < head) dst[tid] = src[tid];
-    const uint64_t pairs = (n - head) / 2;
-    const bool src_ok = ((reinterpret_cast<uintptr_t>(src + head)) & 15) == 0;
-    uint4* d4 = reinterpret_cast<uint4*>(dst + head);
-    if (src_ok) {
-        const uint4* s4 = reinterpret_cast<const uint4*>(src + head);
-        for (uint64_t i = tid; i < pairs; i += stride) d4[i] = s4[i];
-    } else {
-        const uint64_t* s1 = src + head;
-        for (uint64_t i = tid; i < pairs; i += stride) {
-            const uint64_t a = s1[2 * i], b = s1[2 * i + 1];
-            d4[i] = make_uint4(uint32_t(a), uint32_t(a >> 32), uint32_t(b), uint32_t(b >> 32));
-        }
-    }
-    if (tid == 0 && head + 2 * pairs < n) dst[n - 1] = src[n - 1];
-    if (src_hi) {
-        for (uint64_t i = tid; i < n; i += stride) dst_hi[i] = src_hi[i];
-    }
-}
-
-void launch_peer_copy(const uint64_t* src, uint64_t* dst, const uint32_t* src_hi,
-                      uint32_t* dst_hi, uint64_t n, cudaStream_t s, uint32_t* launches) {
-    if (n == 0) return;
-    const uint64_t want = (n / 2 + 511) / 512;
-    const uint32_t grid = uint32_t(want < 148 * 8 ? (want ? want : 1) : 148 * 8);
-    peer_copy_kernel<<<grid, 512, 0, s>>>(src, dst, src_hi, dst_hi, n);
-    *launches += 1;
-}
-
 // records of the segments b.seg describes (in in_rec / in_hi, each segment
 // holding one A bucket) -> sorted by (A, B), stable in segment order, in
 // b.rec[1] / b.hi[1]; b.fine_start gives the first record of every (A, B) bin.

@@ -265,12 +265,6 @@ class CudaStages(AnchorEngine):
     def dist_scatter_local(self, params):
         self._check(self._lib.npge_anchor_dist_scatter_local(self._ctx, C.byref(params)))
 
-    def dist_copy_peer(self, params, dest_rank, dest_off):
-        dr = np.ascontiguousarray(dest_rank, dtype=np.uint32)
-        do = np.ascontiguousarray(dest_off, dtype=np.int64)
-        self._check(self._lib.npge_anchor_dist_copy_peer(
-            self._ctx, C.byref(params), dr.ctypes.data, do.ctypes.data, len(dr)))
-
     def dist_buffers(self, n_send, n_recv):
         import torch
         p = _abi.DistPtrs()
@@ -475,12 +469,13 @@ class DistAnchorFinder:
 
     def __init__(self, device=0, group=None, stages=None, exchange=None):
         """exchange: how the records reach the rank that owns their hash range.
-        "peer": pass A scatters straight into the owners' HBM over NVLink (CUDA
-        IPC; no extra pass, best at 2 GPUs); "bulk": local pass A, then a copy
-        kernel writes every destination's contiguous slice into its receive
-        buffer (large NVLink writes, best at 4+ GPUs); "collective": local pass
-        A + all_to_all_single.  Default ("auto"): peer at 2 ranks, bulk above,
-        collective when a rank cannot map a peer's buffer."""
+        "bulk" (the default): local pass A, then the library copies every
+        destination's contiguous slice into its receive buffer, mapped through
+        CUDA IPC: one asynchronous device-to-device copy per destination, all in
+        flight at once, planned in C++ (csrc/dist_plan.h); "peer": pass A itself
+        scatters every bucket into the owners' HBM over NVLink (no extra pass, but
+        32-byte runs); "collective": local pass A + all_to_all_single, for process
+        groups whose ranks cannot map each other's memory (and the CPU tests)."""
         import os
         self.comm = _Comm(group)
         self.rank, self.world = self.comm.rank, self.comm.world
@@ -522,8 +517,7 @@ class DistAnchorFinder:
                 raise AnchorError(_abi.ERR_CUDA, errs[0])
             self.exchange = "collective"
             return
-        self.exchange = (self._want if self._want != "auto"
-                         else ("peer" if self.world <= 2 else "bulk"))
+        self.exchange = self._want if self._want != "auto" else "bulk"
         self._capacity = capacity
 
     # -- upload ------------------------------------------------------------------------
