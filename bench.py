@@ -326,15 +326,23 @@ def run_c5(args, rank, world, runner_factory, torch, dist, flush, hbm_peak):
             out["kernel_ms_rank0"] = float(np.mean([x["ms_total"] for x in sts]))
             if world > 1:
                 sent = float(st.get("nvlink_bytes_sent", 0))  # rank 0, the last timed step
-                x_ms = float(st.get("nvlink_ms", 0.0))
+                exposed = float(st.get("nvlink_ms", 0.0))
+                window = float(st["ms_pass"][6])   # start of pass A .. last copy landed
+                chunks = int(st.get("chunks", 1))
+                pass_a = float(st["ms_pass"][0]) - exposed
+                # the copies of chunk c start when pass A has finished it: they are in
+                # flight from the end of the first chunk to the end of the window
+                busy = max(window - pass_a / chunks, 1e-6)
                 out["nvlink"] = {
-                    "bytes_per_gpu": sent, "ms": x_ms,
-                    "gb_s": sent / (x_ms * 1e-3) / 1e9 if x_ms > 0 else None,
-                    "frac_of_900": sent / (x_ms * 1e-3) / 900e9 if x_ms > 0 else None,
+                    "bytes_per_gpu": sent, "exposed_ms": exposed, "window_ms": window,
+                    "pass_a_ms": pass_a, "chunks": chunks, "copy_ms": busy,
+                    "gb_s": sent / (busy * 1e-3) / 1e9,
+                    "frac_of_900": sent / (busy * 1e-3) / 900e9,
                     "survey_model_bytes_per_gpu": 12.0 * n_total / world * (world - 1) / world,
                     "exchange": st.get("exchange"),
-                    "note": "rank 0: bytes it wrote into the other ranks' HBM / device "
-                            "time of its exchange stage"}
+                    "note": "rank 0: bytes it wrote into the other ranks' HBM over the time "
+                            "its copies were in flight (window - pass A / chunks); exposed_ms "
+                            "is what they add to the step after pass A"}
             # default options on the same resident genome
             for _ in range(2):
                 runner.step(k, True, 100000)

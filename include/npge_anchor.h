@@ -234,7 +234,11 @@ int npge_anchor_dist_scatter_peer(npge_anchor_ctx* ctx, const npge_anchor_params
 /* dist_count_a + dist_scatter_local is dist_pass_a in two steps; the second only
  * enqueues pass A, so that the all-gather of the histograms overlaps it. */
 int npge_anchor_dist_scatter_local(npge_anchor_ctx* ctx, const npge_anchor_params* p);
-/* hist_all[world][bins]: the all-gathered results of dist_count_a.  n_recv_out[world]
+/* Pass A of the calls that follow runs in `chunks` chunks of tiles (1..8; default 1):
+ * dist_count_a then returns chunks * n_bins counts ([chunk][bucket]), and dist_exchange
+ * copies every finished chunk while the next one is ranked.  The same on every rank. */
+int npge_anchor_dist_set_chunks(npge_anchor_ctx* ctx, int32_t chunks);
+/* hist_all[world][chunks][bins]: the all-gathered results of dist_count_a.  n_recv_out[world]
  * (optional): records every rank receives.  NPGE_ANCHOR_ERR_CAPACITY when a receive
  * buffer is too small (n_recv_out valid: regrow with dist_peer_alloc and call again). */
 int npge_anchor_dist_exchange(npge_anchor_ctx* ctx, const npge_anchor_params* p,
@@ -243,12 +247,14 @@ int npge_anchor_dist_exchange(npge_anchor_ctx* ctx, const npge_anchor_params* p,
 int npge_anchor_dist_sort_planned(npge_anchor_ctx* ctx, const npge_anchor_params* p,
                                   int32_t stage, const uint64_t* used_sorted,
                                   uint64_t n_used, uint64_t totals[2]);
-/* The tables of dist_exchange alone, on the host (no device needed; tests): cuts
- * [world + 1], n_recv [world], dest_rank / dest_off [bins] of `rank` as a sender, and
- * its segment tables as a receiver (seg_* sized world * bins, seg_tile one more,
- * a_tile0 / a_start [bins + 1]); any pointer may be NULL. */
-int npge_anchor_dist_plan_tables(const uint32_t* hist_all, uint32_t world, uint32_t bins,
-                                 uint32_t rank, uint32_t* cuts, uint64_t* n_recv,
+/* The tables of dist_exchange alone, on the host (no device needed; tests).
+ * hist_all[world * chunks][bins]: source rank * chunks + c is chunk c of a rank.
+ * cuts [world + 1], n_recv [world], dest_rank / dest_off [bins] of `rank`'s chunk 0 as a
+ * sender, and its segment tables as a receiver (seg_* sized world * chunks * bins,
+ * seg_tile one more, a_tile0 / a_start [bins + 1]); any pointer may be NULL. */
+int npge_anchor_dist_plan_tables(const uint32_t* hist_all, uint32_t world, uint32_t chunks,
+                                 uint32_t bins, uint32_t rank, uint32_t* cuts,
+                                 uint64_t* n_recv,
                                  uint32_t* dest_rank, int64_t* dest_off, uint32_t* n_seg,
                                  uint32_t* seg_begin, uint32_t* seg_end, uint32_t* seg_a,
                                  uint32_t* seg_tile, uint32_t* a_tile0, uint32_t* a_start);

@@ -15,7 +15,7 @@ EXPORTS = [
     "npge_anchor_version",
     "npge_anchor_dist_upload_range", "npge_anchor_dist_pass_a",
     "npge_anchor_dist_exchange", "npge_anchor_dist_sort_planned",
-    "npge_anchor_dist_plan_tables",
+    "npge_anchor_dist_plan_tables", "npge_anchor_dist_set_chunks",
     "npge_anchor_dist_buffers", "npge_anchor_dist_sort", "npge_anchor_dist_emit",
     "npge_anchor_dist_peer_alloc", "npge_anchor_dist_peer_open",
     "npge_anchor_dist_peer_close", "npge_anchor_dist_count_a",
@@ -125,7 +125,9 @@ def load():
                                                 C.c_uint64, C.POINTER(C.c_uint64 * 2)]
     L.npge_anchor_dist_plan_tables.restype = C.c_int
     L.npge_anchor_dist_plan_tables.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32,
-                                               C.c_uint32] + [C.c_void_p] * 11
+                                               C.c_uint32, C.c_uint32] + [C.c_void_p] * 11
+    L.npge_anchor_dist_set_chunks.restype = C.c_int
+    L.npge_anchor_dist_set_chunks.argtypes = [ctx, C.c_int32]
     L.npge_anchor_dist_pass_a.restype = C.c_int
     L.npge_anchor_dist_pass_a.argtypes = [ctx, C.POINTER(Params), C.c_void_p,
                                           C.c_uint32, C.POINTER(C.c_uint32)]

@@ -245,7 +245,7 @@ extern "C" void npge_anchor_destroy(npge_anchor_ctx* ctx) {
                            &ctx->r_block_off, &ctx->r_block_hash,
                            &ctx->summary, &ctx->rows, &ctx->blk,
                            &ctx->segtab, &ctx->fine_start,
-                           &ctx->tile_desc, &ctx->bstatus, &ctx->unit_wtot, &ctx->units, &ctx->rec[0], &ctx->rec[1], &ctx->rhi[0],
+                           &ctx->tile_desc, &ctx->chunk_tab, &ctx->bstatus, &ctx->unit_wtot, &ctx->units, &ctx->rec[0], &ctx->rec[1], &ctx->rhi[0],
                            &ctx->rhi[1], &ctx->seq_lut, &ctx->g_seq_start, &ctx->g_seq_caller,
                            &ctx->g_seq_lut, &ctx->recv_rec, &ctx->recv_hi,
                            &ctx->peer_tab, &ctx->frag_pat, &ctx->frag_tiles, &ctx->frag_out,
@@ -257,6 +257,7 @@ extern "C" void npge_anchor_destroy(npge_anchor_ctx* ctx) {
     for (auto& ev : ctx->ev_pass) if (ev) cudaEventDestroy(ev);
     for (auto& ev : ctx->fetch_ev) if (ev) cudaEventDestroy(ev);
     for (auto& ev : ctx->copy_events) if (ev) cudaEventDestroy(ev);
+    for (auto& ev : ctx->chunk_events) if (ev) cudaEventDestroy(ev);
     for (auto& cs : ctx->copy_streams) if (cs) cudaStreamDestroy(cs);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -1191,12 +1192,15 @@ int dist_count_a(npge_anchor_ctx* ctx, const npge_anchor_params* p, bool scatter
     const MsdPlan plan = make_msd_plan(p->anchor_size, ctx->g_positions, ctx->force_f,
                                        ctx->force_wa);
     const uint32_t bins_a = 1u << plan.capa;
-    if (hist_cap < bins_a) return fail(NPGE_ANCHOR_ERR_PARAMS, "hist_out too small");
     *n_bins = bins_a;
     const uint64_t np = ctx->n_padded, max_records = ctx->n_positions;
+    const int chunks = scatter ? 1 : ctx->dist_chunks;  // (dist_pass_a: one chunk)
+    if (hist_cap < bins_a * uint32_t(chunks)) return fail(NPGE_ANCHOR_ERR_PARAMS, "hist_out too small");
     NPGE_TRY(ensure(ctx->rows, msd_rows_needed(plan, np, max_records, bins_a) * 4));
-    NPGE_TRY(ensure(ctx->blk, msd_blk_needed(plan, np, max_records, bins_a) * 4));
+    NPGE_TRY(ensure(ctx->blk, (msd_blk_needed(plan, np, max_records, bins_a) +
+                               size_t(kMaxChunks + 1) * bins_a) * 4));
     NPGE_TRY(ensure(ctx->segtab, seg_table_words(bins_a, plan) * 4));
+    NPGE_TRY(ensure(ctx->chunk_tab, size_t(chunks) * (2 * bins_a + 1) * 4));
     if (scatter) {
         NPGE_TRY(ensure(ctx->rec[0], (max_records + 16) * 8));
         if (plan.wide) NPGE_TRY(ensure(ctx->rhi[0], (max_records + 16) * 4));
@@ -1207,20 +1211,30 @@ int dist_count_a(npge_anchor_ctx* ctx, const npge_anchor_params* p, bool scatter
     ctx->dist_launches = 0;
     NPGE_CUDA(cudaMemsetAsync(ctx->counters.ptr, 0, kCntWords * 4, st));
     MsdBuffers mb = dist_msd_buffers(ctx, plan, bins_a);
-    std::vector<uint32_t> a_start(bins_a + 1, 0);
+    // a_start[c][bins + 1]: first record of every (chunk, bucket) of the pass-A output
+    std::vector<uint32_t> a_start(size_t(chunks) * (bins_a + 1), 0);
+    PassAChunks ch = {chunks, ptr<uint32_t>(ctx->chunk_tab),
+                      ptr<uint32_t>(ctx->chunk_tab) + size_t(chunks) * bins_a, nullptr};
     if (np) {
         NPGE_CUDA(cudaEventRecord(ctx->ev[0], st));
         launch_msd_pass_a(plan, ptr<uint32_t>(ctx->packed), ptr<uint32_t>(ctx->nmask), np,
                           mb, dist_pos_map(ctx), ptr<uint32_t>(ctx->counters), st,
-                          ctx->ev_pass, &ctx->dist_launches, scatter ? 0 : 1);
+                          ctx->ev_pass, &ctx->dist_launches, scatter ? 0 : 1,
+                          scatter ? nullptr : &ch);
         NPGE_CUDA(cudaGetLastError());
-        NPGE_CUDA(cudaMemcpyAsync(a_start.data(), mb.seg.a_start, (bins_a + 1) * 4,
-                                  cudaMemcpyDeviceToHost, st));
+        NPGE_CUDA(cudaMemcpyAsync(a_start.data(), scatter ? mb.seg.a_start : ch.chunk_start,
+                                  a_start.size() * 4, cudaMemcpyDeviceToHost, st));
         NPGE_CUDA(cudaStreamSynchronize(st));
         cudaEventElapsedTime(&ctx->dist_ms[0], ctx->ev[0], ctx->ev_pass[0]);
         if (scatter) cudaEventElapsedTime(&ctx->dist_ms[1], ctx->ev_pass[0], ctx->ev_pass[1]);
     }
-    for (uint32_t a = 0; a < bins_a; a++) hist_out[a] = a_start[a + 1] - a_start[a];
+    for (int c = 0; c < chunks; c++) {
+        for (uint32_t a = 0; a < bins_a; a++) {
+            const size_t i = size_t(c) * (bins_a + 1) + a;
+            hist_out[size_t(c) * bins_a + a] = a_start[i + 1] - a_start[i];
+        }
+    }
+    ctx->a_chunks = chunks;
     ctx->plan = plan;
     ctx->a_counted = true;
     ctx->a_scattered = scatter;
@@ -1379,17 +1393,38 @@ extern "C" int npge_anchor_dist_scatter_local(npge_anchor_ctx* ctx,
     NPGE_TRY(ensure(ctx->rec[0], (max_records + 16) * 8));
     if (plan.wide) NPGE_TRY(ensure(ctx->rhi[0], (max_records + 16) * 4));
     cudaStream_t st = ctx->stream;
+    while (ctx->chunk_events.size() < size_t(kMaxChunks)) {
+        cudaEvent_t ev = nullptr;
+        NPGE_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+        ctx->chunk_events.push_back(ev);
+    }
     NPGE_CUDA(cudaEventRecord(ctx->ev_pass[0], st));
     if (np) {
         MsdBuffers mb = dist_msd_buffers(ctx, plan, bins_a);
+        const int chunks = ctx->a_chunks;
+        PassAChunks ch = {chunks, ptr<uint32_t>(ctx->chunk_tab),
+                          ptr<uint32_t>(ctx->chunk_tab) + size_t(chunks) * bins_a,
+                          ctx->chunk_events.data()};
         launch_msd_pass_a(plan, ptr<uint32_t>(ctx->packed), ptr<uint32_t>(ctx->nmask), np,
                           mb, dist_pos_map(ctx), ptr<uint32_t>(ctx->counters), st, nullptr,
-                          &ctx->dist_launches, 2);
+                          &ctx->dist_launches, 2, &ch);
         NPGE_CUDA(cudaGetLastError());
+    } else {
+        for (int c = 0; c < ctx->a_chunks; c++) NPGE_CUDA(cudaEventRecord(ctx->chunk_events[c], st));
     }
     NPGE_CUDA(cudaEventRecord(ctx->ev_pass[1], st));
     ctx->a_scattered = true;
     ctx->a_scatter_async = true;
+    return NPGE_ANCHOR_OK;
+}
+
+// Pass A of the following npge_anchor_dist_count_a / scatter_local / exchange runs in
+// `chunks` chunks of tiles (1..8), the copies of a finished chunk overlapping the
+// ranking of the next.  The same on every rank of a job.
+extern "C" int npge_anchor_dist_set_chunks(npge_anchor_ctx* ctx, int32_t chunks) {
+    if (!ctx) return fail(NPGE_ANCHOR_ERR_PARAMS, "ctx is NULL");
+    if (chunks < 1 || chunks > kMaxChunks) return fail(NPGE_ANCHOR_ERR_PARAMS, "chunks must be 1..8");
+    ctx->dist_chunks = chunks;
     return NPGE_ANCHOR_OK;
 }
 
@@ -1418,16 +1453,23 @@ extern "C" int npge_anchor_dist_exchange(npge_anchor_ctx* ctx, const npge_anchor
     const uint32_t bins_a = 1u << plan.capa;
     NPGE_CUDA(cudaSetDevice(ctx->device));
     DistPlan& dp = ctx->dplan;
-    dist_make_plan(hist_all, world, bins_a, rank, dp);
+    const uint32_t chunks = uint32_t(ctx->a_chunks);
+    // hist_all: [world][chunks][bins] = [world * chunks sources][bins]
+    dist_make_plan(hist_all, world, chunks, bins_a, rank, ctx->a_start_h.data(), dp);
     ctx->planned = false;
     uint64_t max_recv = 0;
     for (uint32_t d = 0; d < world; d++) {
         if (n_recv_out) n_recv_out[d] = dp.n_recv[d];
         max_recv = std::max(max_recv, dp.n_recv[d]);
     }
-    for (uint32_t a = 0; a <= bins_a; a++) {
-        if (dp.a_start_send[a] != ctx->a_start_h[a]) {
-            return fail(NPGE_ANCHOR_ERR_PARAMS, "hist_all[rank] differs from this rank's count A");
+    for (uint32_t c = 0; c < chunks; c++) {
+        for (uint32_t a = 0; a < bins_a; a++) {
+            const size_t i = size_t(c) * (bins_a + 1) + a;
+            if (hist_all[(size_t(rank) * chunks + c) * bins_a + a] !=
+                ctx->a_start_h[i + 1] - ctx->a_start_h[i]) {
+                return fail(NPGE_ANCHOR_ERR_PARAMS,
+                            "hist_all[rank] differs from this rank's count A");
+            }
         }
     }
     if (max_recv > ctx->peer_capacity) {
@@ -1443,16 +1485,17 @@ extern "C" int npge_anchor_dist_exchange(npge_anchor_ctx* ctx, const npge_anchor
         ctx->copy_events.push_back(ev);
     }
     cudaStream_t st = ctx->stream;
-    NPGE_CUDA(cudaEventRecord(ctx->ev[0], st));  // pass A has been enqueued before
-    // ring order of issue: rank r starts with the owner after itself
-    for (uint32_t step = 0; step < world; step++) {
-        const uint32_t d = (rank + 1 + step) % world;
-        const uint32_t lo = dp.cuts[d], hi = dp.cuts[d + 1];
-        const uint64_t first = dp.a_start_send[lo], n = dp.a_start_send[hi] - first;
-        cudaStream_t cs = ctx->copy_streams[d];
-        NPGE_CUDA(cudaStreamWaitEvent(cs, ctx->ev[0], 0));
-        if (n) {
-            const int64_t to = dp.dest_off[lo] + int64_t(first);
+    NPGE_CUDA(cudaEventRecord(ctx->ev[0], st));  // (pass A has been enqueued before)
+    // chunk by chunk, as pass A finishes them; inside a chunk in ring order (rank r
+    // starts with the owner after itself)
+    for (uint32_t c = 0; c < chunks; c++) {
+        for (uint32_t step = 0; step < world; step++) {
+            const uint32_t d = (rank + 1 + step) % world;
+            const size_t i = size_t(c) * world + d;
+            const uint64_t first = dp.send_first[i], n = dp.send_n[i], to = dp.send_to[i];
+            if (n == 0) continue;
+            cudaStream_t cs = ctx->copy_streams[d];
+            NPGE_CUDA(cudaStreamWaitEvent(cs, ctx->chunk_events[c], 0));
             NPGE_CUDA(cudaMemcpyAsync(static_cast<uint64_t*>(ctx->peer_rec[d]) + to,
                                       ptr<uint64_t>(ctx->rec[0]) + first, n * 8,
                                       cudaMemcpyDeviceToDevice, cs));
@@ -1462,16 +1505,21 @@ extern "C" int npge_anchor_dist_exchange(npge_anchor_ctx* ctx, const npge_anchor
                                           cudaMemcpyDeviceToDevice, cs));
             }
         }
-        NPGE_CUDA(cudaEventRecord(ctx->copy_events[d], cs));
+    }
+    for (uint32_t d = 0; d < world; d++) {
+        NPGE_CUDA(cudaEventRecord(ctx->copy_events[d], ctx->copy_streams[d]));
         NPGE_CUDA(cudaStreamWaitEvent(st, ctx->copy_events[d], 0));
     }
     NPGE_CUDA(cudaEventRecord(ctx->ev[1], st));
     NPGE_CUDA(cudaStreamSynchronize(st));  // every slice has landed (the peers wait at a barrier)
-    cudaEventElapsedTime(&ctx->dist_ms[7], ctx->ev[0], ctx->ev[1]);
+    // dist_ms[1]: pass A; dist_ms[7]: what the copies add after its last chunk (the
+    // rest of them overlapped it)
+    cudaEventElapsedTime(&ctx->dist_ms[7], ctx->ev_pass[1], ctx->ev[1]);
     if (ctx->a_scatter_async) {
         cudaEventElapsedTime(&ctx->dist_ms[1], ctx->ev_pass[0], ctx->ev_pass[1]);
         ctx->a_scatter_async = false;
     }
+    cudaEventElapsedTime(&ctx->dist_exchange_ms, ctx->ev_pass[0], ctx->ev[1]);
     ctx->a_counted = false;
     ctx->planned = true;
     return NPGE_ANCHOR_OK;
@@ -1508,17 +1556,18 @@ extern "C" int npge_anchor_dist_sort_planned(npge_anchor_ctx* ctx,
 // seg_begin / seg_end / seg_a [world * bins], seg_tile [world * bins + 1],
 // a_tile0 / a_start [bins + 1].  Returns the number of segments in *n_seg.
 extern "C" int npge_anchor_dist_plan_tables(const uint32_t* hist_all, uint32_t world,
-                                            uint32_t bins, uint32_t rank, uint32_t* cuts,
+                                            uint32_t chunks, uint32_t bins, uint32_t rank,
+                                            uint32_t* cuts,
                                             uint64_t* n_recv, uint32_t* dest_rank,
                                             int64_t* dest_off, uint32_t* n_seg,
                                             uint32_t* seg_begin, uint32_t* seg_end,
                                             uint32_t* seg_a, uint32_t* seg_tile,
                                             uint32_t* a_tile0, uint32_t* a_start) {
-    if (!hist_all || !world || !bins || rank >= world) {
+    if (!hist_all || !world || !bins || !chunks || rank >= world) {
         return fail(NPGE_ANCHOR_ERR_PARAMS, "bad arguments");
     }
     DistPlan dp;
-    dist_make_plan(hist_all, world, bins, rank, dp);
+    dist_make_plan(hist_all, world, chunks, bins, rank, nullptr, dp);
     auto put = [](auto* dst, const auto& v) {
         if (dst) std::copy(v.begin(), v.end(), dst);
     };
@@ -1745,8 +1794,9 @@ extern "C" int npge_anchor_dist_emit(npge_anchor_ctx* ctx, const npge_anchor_par
     // (+ candidate count)] [scan + emit]
     s.ms_hist = ctx->dist_ms[0];
     for (int i = 0; i < 3; i++) s.ms_pass[i] = ctx->dist_ms[i + 1];
-    s.ms_pass[0] += ctx->dist_ms[7];  // bulk exchange: the peer copies belong to pass A
+    s.ms_pass[0] += ctx->dist_ms[7];  // bulk exchange: what the copies add to pass A
     s.ms_pass[5] = ctx->dist_ms[7];
+    s.ms_pass[6] = ctx->dist_exchange_ms;  // start of pass A .. last copy landed
     s.ms_pass[3] = ctx->dist_ms[4] + ctx->dist_ms[5];
     s.ms_pass[4] = ctx->dist_ms[6];
     s.ms_sort = ctx->dist_ms[0] + ctx->dist_ms[1] + ctx->dist_ms[2] + ctx->dist_ms[3] +

@@ -153,6 +153,10 @@ struct npge_anchor_ctx {
     bool planned = false;
     std::vector<cudaStream_t> copy_streams;  // one per destination rank
     std::vector<cudaEvent_t> copy_events;
+    std::vector<cudaEvent_t> chunk_events;   // pass A chunk c has been scattered
+    int dist_chunks = 1;                     // chunks of pass A (npge_anchor_dist_set_chunks)
+    int a_chunks = 1;                        // chunks of the last count A
+    npge_b200::DeviceBuffer chunk_tab;       // per-chunk column totals and bucket starts
     uint64_t dist_g0 = 0, dist_n_own = 0;    // this rank's range of the job-wide positions
     npge_b200::DeviceBuffer recv_rec, recv_hi;
     uint64_t n_recv = 0;
@@ -174,6 +178,7 @@ struct npge_anchor_ctx {
     bool a_scattered = false;                // rec[0] holds the local pass A output
     uint64_t dist_n_used = 0;
     float dist_ms[8] = {};
+    float dist_exchange_ms = 0.f;            // start of pass A .. last copy landed
     // device result
     npge_b200::DeviceBuffer r_seq, r_pos, r_ori, r_block_off, r_block_hash;
     npge_b200::DeviceBuffer summary;

@@ -16,18 +16,24 @@ namespace npge_b200 {
 
 constexpr uint32_t kPlanTile = 4096;  // records per pass-B tile (kTile)
 
+// Every rank runs pass A in `chunks` chunks of its tiles (the copies of a finished
+// chunk overlap the ranking of the next); a (rank, chunk) pair is one SOURCE of the
+// exchange: n_src = world * chunks histograms, source rank * chunks + c.
 struct DistPlan {
-    uint32_t world = 0, bins = 0, rank = 0;
+    uint32_t world = 0, chunks = 1, bins = 0, rank = 0;
     std::vector<uint32_t> cuts;       // [world + 1] rank r owns buckets cuts[r] .. cuts[r + 1] - 1
     std::vector<uint64_t> n_recv;     // [world] records every rank receives
-    // this rank as a SENDER: bucket a goes to dest_rank[a]; element idx of this rank's
-    // A-sorted order lands at record dest_off[a] + idx of the owner's receive buffer
+    // this rank as a SENDER, for every one of its chunks c and every destination d:
+    // records [send_first, send_first + send_n) of its pass-A output (chunk-major) go
+    // to records [send_to, ...) of d's receive buffer
+    std::vector<uint64_t> send_first, send_n, send_to;  // [chunks][world]
+    // per bucket, chunk 0 (the fused scatter runs unchunked): element idx of the
+    // A-sorted order lands at record dest_off[a] + idx of dest_rank[a]'s buffer
     std::vector<uint32_t> dest_rank;  // [bins]
     std::vector<int64_t> dest_off;    // [bins]
-    std::vector<uint32_t> a_start_send;  // [bins + 1] this rank's A-sorted order
     // this rank as a RECEIVER: the receive buffer holds source 0's slice, then source
     // 1's, ...; inside a slice the buckets ascend.  Segments are bucket-major, sources
-    // in rank (= position) order inside a bucket, so that pass B stays stable.
+    // in order (= position order) inside a bucket, so that pass B stays stable.
     std::vector<uint32_t> seg_begin, seg_end, seg_a, seg_tile;  // seg_tile: [n_seg + 1]
     std::vector<uint32_t> a_tile0, a_start;                     // [bins + 1]
     uint32_t n_seg = 0;
@@ -36,12 +42,12 @@ struct DistPlan {
 // Contiguous bucket ranges balanced by records: the boundary whose prefix sum is
 // nearest to r / world of the total (the canonical minimum skews the k-mer
 // distribution; a fixed split of the hash space would overload rank 0).
-inline void dist_bucket_ranges(const uint32_t* hist_all, uint32_t world, uint32_t bins,
-                               std::vector<uint32_t>& cuts) {
+inline void dist_bucket_ranges(const uint32_t* hist_all, uint32_t n_src, uint32_t world,
+                               uint32_t bins, std::vector<uint32_t>& cuts) {
     std::vector<uint64_t> csum(bins + 1, 0);
     for (uint32_t a = 0; a < bins; a++) {
         uint64_t t = 0;
-        for (uint32_t s = 0; s < world; s++) t += hist_all[size_t(s) * bins + a];
+        for (uint32_t s = 0; s < n_src; s++) t += hist_all[size_t(s) * bins + a];
         csum[a + 1] = csum[a] + t;
     }
     const uint64_t total = csum[bins];
@@ -70,43 +76,63 @@ inline void dist_bucket_ranges(const uint32_t* hist_all, uint32_t world, uint32_
     cuts[world] = bins;
 }
 
-inline void dist_make_plan(const uint32_t* hist_all, uint32_t world, uint32_t bins,
-                           uint32_t rank, DistPlan& p) {
+// a_first[c][bins + 1]: first record of every bucket of chunk c in this rank's pass-A
+// output (chunk-major), as the device computed it.
+inline void dist_make_plan(const uint32_t* hist_all, uint32_t world, uint32_t chunks,
+                           uint32_t bins, uint32_t rank, const uint32_t* a_first,
+                           DistPlan& p) {
+    const uint32_t n_src = world * chunks;
     p.world = world;
+    p.chunks = chunks;
     p.bins = bins;
     p.rank = rank;
-    dist_bucket_ranges(hist_all, world, bins, p.cuts);
+    dist_bucket_ranges(hist_all, n_src, world, bins, p.cuts);
     auto H = [&](uint32_t s, uint32_t a) -> uint64_t { return hist_all[size_t(s) * bins + a]; };
     // sender side
-    p.a_start_send.assign(bins + 1, 0);
-    for (uint32_t a = 0; a < bins; a++) p.a_start_send[a + 1] = p.a_start_send[a] + uint32_t(H(rank, a));
+    p.send_first.assign(size_t(chunks) * world, 0);
+    p.send_n.assign(size_t(chunks) * world, 0);
+    p.send_to.assign(size_t(chunks) * world, 0);
     p.dest_rank.assign(bins, 0);
     p.dest_off.assign(bins, 0);
     p.n_recv.assign(world, 0);
     for (uint32_t d = 0; d < world; d++) {
         const uint32_t lo = p.cuts[d], hi = p.cuts[d + 1];
-        uint64_t before_me = 0, all = 0;
-        for (uint32_t s = 0; s < world; s++) {
+        uint64_t before = 0;  // records of the sources before the current one
+        for (uint32_t s = 0; s < n_src; s++) {
             uint64_t t = 0;
             for (uint32_t a = lo; a < hi; a++) t += H(s, a);
-            if (s < rank) before_me += t;
-            all += t;
+            if (s / chunks == rank) {
+                const uint32_t c = s % chunks;
+                // without a_first: a single chunk whose buckets start at the prefix sums
+                uint64_t first = 0;
+                if (a_first) {
+                    first = a_first[size_t(c) * (bins + 1) + lo];
+                } else {
+                    for (uint32_t a = 0; a < lo; a++) first += H(s, a);
+                }
+                p.send_first[size_t(c) * world + d] = first;
+                p.send_n[size_t(c) * world + d] = t;
+                p.send_to[size_t(c) * world + d] = before;
+                if (c == 0) {
+                    for (uint32_t a = lo; a < hi; a++) {
+                        p.dest_rank[a] = d;
+                        p.dest_off[a] = int64_t(before) - int64_t(first);
+                    }
+                }
+            }
+            before += t;
         }
-        p.n_recv[d] = all;
-        for (uint32_t a = lo; a < hi; a++) {
-            p.dest_rank[a] = d;
-            p.dest_off[a] = int64_t(before_me) - int64_t(p.a_start_send[lo]);
-        }
+        p.n_recv[d] = before;
     }
     // receiver side
     const uint32_t lo = p.cuts[rank], hi = p.cuts[rank + 1];
-    std::vector<uint64_t> src_base(world + 1, 0);
-    for (uint32_t s = 0; s < world; s++) {
+    std::vector<uint64_t> src_base(n_src + 1, 0);
+    for (uint32_t s = 0; s < n_src; s++) {
         uint64_t t = 0;
         for (uint32_t a = lo; a < hi; a++) t += H(s, a);
         src_base[s + 1] = src_base[s] + t;
     }
-    std::vector<uint64_t> inside(world, 0);  // offset of the current bucket in every slice
+    std::vector<uint64_t> inside(n_src, 0);  // offset of the current bucket in every slice
     p.seg_begin.clear();
     p.seg_end.clear();
     p.seg_a.clear();
@@ -119,7 +145,7 @@ inline void dist_make_plan(const uint32_t* hist_all, uint32_t world, uint32_t bi
         p.a_tile0[a] = tiles;
         p.a_start[a] = uint32_t(records);
         if (a < lo || a >= hi) continue;
-        for (uint32_t s = 0; s < world; s++) {
+        for (uint32_t s = 0; s < n_src; s++) {
             const uint64_t c = H(s, a);
             if (c) {
                 const uint64_t b = src_base[s] + inside[s];

@@ -80,10 +80,19 @@ SegTables carve_seg_tables(uint32_t* base, uint32_t max_seg, const MsdPlan& plan
 size_t msd_tiles_b(uint64_t max_records, uint32_t max_seg);  // pass-B tiles (upper bound)
 // ev (optional): [0] after count A, [1] after pass A, [2] after count B, [3] pass B
 // part: 0 = count + scatter, 1 = count A and the tables only, 2 = the scatter only
+// Several GPUs: pass A in chunks of tiles, output chunk-major (msd_kernels.cu)
+struct PassAChunks {
+    int n_chunks;
+    uint32_t* chunk_tot;    // [n_chunks][bins] column totals of every chunk
+    uint32_t* chunk_start;  // [n_chunks][bins + 1] first record of every (chunk, bucket)
+    cudaEvent_t* done;      // [n_chunks] recorded after the scatter of every chunk (optional)
+};
 void launch_msd_pass_a(const MsdPlan& plan, const uint32_t* packed,
                        const uint32_t* nmask, uint64_t n_padded, const MsdBuffers& b,
                        const PosMap& pm, uint32_t* counters, cudaStream_t s,
-                       cudaEvent_t* ev, uint32_t* launches, int part = 0);
+                       cudaEvent_t* ev, uint32_t* launches, int part = 0,
+                       const PassAChunks* ch = nullptr);
+constexpr int kMaxChunks = 8;
 void launch_msd_pass_b(const MsdPlan& plan, const uint64_t* in_rec, const uint32_t* in_hi,
                        uint64_t max_records, uint32_t max_seg, const MsdBuffers& b,
                        cudaStream_t s, cudaEvent_t* ev, uint32_t* launches);

@@ -261,6 +261,27 @@ a_tables_kernel(const uint32_t* __restrict__ totals, SegTables t,
     }
 }
 
+// Several GPUs, pass A in chunks of tiles (so that the copies of a finished chunk
+// overlap the ranking of the next): the output is chunk-major, bucket-major inside a
+// chunk.  chunk_start[c][d] = first record of bucket d of chunk c (c's end in entry
+// [bins]), from the per-chunk column totals.  One CTA of 1 << capa threads.
+__global__ void __launch_bounds__(1024)
+chunk_tables_kernel(const uint32_t* __restrict__ chunk_tot, int n_chunks,
+                    uint32_t* __restrict__ chunk_start, uint32_t* __restrict__ counters) {
+    __shared__ uint32_t tmp[32];
+    const int bins = blockDim.x, d = threadIdx.x;
+    uint32_t base = 0;
+    for (int c = 0; c < n_chunks; c++) {
+        const uint32_t v = chunk_tot[size_t(c) * bins + d];
+        uint32_t all;
+        const uint32_t s = block_excl_scan(v, tmp, &all);
+        chunk_start[size_t(c) * (bins + 1) + d] = base + s;
+        if (d == bins - 1) chunk_start[size_t(c) * (bins + 1) + bins] = base + all;
+        base += all;
+    }
+    if (d == 0) counters[kCntValid] = base;
+}
+
 // key bits kept in a record after pass A (the low `rem` bits of the k-mer)
 __device__ __forceinline__ uint64_t rem_key(uint64_t rec, uint32_t hi) {
     return (uint64_t(hi) << 32) | (rec >> 32);
@@ -303,14 +324,14 @@ struct __align__(16) PassSmem {
 template <int CAPBITS, bool WIDE, bool PEER>
 __global__ void __launch_bounds__(kRT, WIDE ? 2 : (CAPBITS == 8 ? NPGE_PASS_A_CTAS : (CAPBITS == 9 ? 3 : 2)))
 pass_a_kernel(const uint32_t* __restrict__ packed, const uint32_t* __restrict__ nmask,
-              MsdPlan plan, const uint32_t* __restrict__ rows, PosMap pm,
+              MsdPlan plan, const uint32_t* __restrict__ rows, PosMap pm, uint32_t tile0,
               uint64_t* __restrict__ out_rec, uint32_t* __restrict__ out_hi) {
     extern __shared__ __align__(16) unsigned char raw[];
     using Smem = PassSmem<CAPBITS, WIDE>;
     Smem& sm = *reinterpret_cast<Smem*>(raw);
     constexpr int BINS = Smem::BINS;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint32_t tile = blockIdx.x;
+    const uint32_t tile = blockIdx.x + tile0;  // (a chunk of the tiles per launch)
     const uint32_t gbase = tile * uint32_t(kTile);
     stage_genome_tile(sm.st, packed, nmask, tile);  // (barrier inside)
     const int sa = plan.rem;
@@ -532,12 +553,13 @@ pass_b_kernel(const uint64_t* __restrict__ in_rec, const uint32_t* __restrict__ 
     }
 }
 
+// totals: where the column totals go (default: the row after the last one)
 void scan_rows(uint32_t* rows, uint32_t n_rows, int bins, uint32_t* blk,
-               cudaStream_t s) {
+               cudaStream_t s, uint32_t* totals = nullptr) {
     const uint32_t n_blk = (n_rows + kScanRows - 1) / kScanRows;
     scan_rows_sum_kernel<<<n_blk, bins, 0, s>>>(rows, n_rows, blk);
-    scan_rows_blk_kernel<<<bins / 32, 1024, 0, s>>>(blk, n_blk, bins,
-                                                    rows + size_t(n_rows) * bins);
+    scan_rows_blk_kernel<<<bins / 32, 1024, 0, s>>>(
+        blk, n_blk, bins, totals ? totals : rows + size_t(n_rows) * bins);
 }
 
 void apply_rows(uint32_t* rows, uint32_t n_rows, int bins, const uint32_t* blk,
@@ -597,41 +619,78 @@ size_t seg_table_words(uint32_t max_seg, const MsdPlan& plan) {
 void launch_msd_pass_a(const MsdPlan& plan, const uint32_t* packed,
                        const uint32_t* nmask, uint64_t n_padded, const MsdBuffers& b,
                        const PosMap& pm, uint32_t* counters, cudaStream_t s,
-                       cudaEvent_t* ev, uint32_t* launches, int part) {
+                       cudaEvent_t* ev, uint32_t* launches, int part,
+                       const PassAChunks* ch) {
     const uint32_t tiles_a = uint32_t(n_padded / kTile);
     if (tiles_a == 0) return;
     const int bins_a = 1 << plan.capa;
+    const int n_chunks = ch ? ch->n_chunks : 1;
+    // chunk c = tiles [c * per, (c + 1) * per)
+    const uint32_t per = (tiles_a + n_chunks - 1) / n_chunks;
     if (part != 2) {
         count_a_kernel<<<tiles_a, kRT, sizeof(GenomeStage) + bins_a * 4, s>>>(
             packed, nmask, plan, pm.win_limit, b.rows);
-        scan_rows(b.rows, tiles_a, bins_a, b.blk, s);
-        a_tables_kernel<<<1, bins_a, 0, s>>>(b.rows + size_t(tiles_a) * bins_a, b.seg,
-                                             counters);
-        apply_rows(b.rows, tiles_a, bins_a, b.blk, b.seg.a_start, s);
-        *launches += 5;
+        *launches += 1;
+        if (!ch) {
+            scan_rows(b.rows, tiles_a, bins_a, b.blk, s);
+            a_tables_kernel<<<1, bins_a, 0, s>>>(b.rows + size_t(tiles_a) * bins_a, b.seg,
+                                                 counters);
+            apply_rows(b.rows, tiles_a, bins_a, b.blk, b.seg.a_start, s);
+            *launches += 4;
+        } else {
+            for (int c = 0; c < n_chunks; c++) {
+                const uint32_t t0 = min(uint32_t(c) * per, tiles_a), t1 = min(t0 + per, tiles_a);
+                uint32_t* tot = ch->chunk_tot + size_t(c) * bins_a;
+                if (t1 > t0) {
+                    scan_rows(b.rows + size_t(t0) * bins_a, t1 - t0, bins_a,
+                              b.blk + (size_t(t0) / kScanRows + c) * bins_a, s, tot);
+                    *launches += 2;
+                } else {
+                    cudaMemsetAsync(tot, 0, size_t(bins_a) * 4, s);
+                }
+            }
+            chunk_tables_kernel<<<1, bins_a, 0, s>>>(ch->chunk_tot, n_chunks, ch->chunk_start,
+                                                     counters);
+            *launches += 1;
+            for (int c = 0; c < n_chunks; c++) {
+                const uint32_t t0 = min(uint32_t(c) * per, tiles_a), t1 = min(t0 + per, tiles_a);
+                if (t1 > t0) {
+                    apply_rows(b.rows + size_t(t0) * bins_a, t1 - t0, bins_a,
+                               b.blk + (size_t(t0) / kScanRows + c) * bins_a,
+                               ch->chunk_start + size_t(c) * (bins_a + 1), s);
+                    *launches += 1;
+                }
+            }
+        }
         if (ev) cudaEventRecord(ev[0], s);
     }
     if (part == 1) return;
 #define NPGE_PASS_A(CB, W, G)                                                      \
     do {                                                                           \
         set_smem(pass_a_kernel<CB, W, G>, sizeof(PassSmem<CB, W>));                \
-        pass_a_kernel<CB, W, G><<<tiles_a, kRT, sizeof(PassSmem<CB, W>), s>>>(     \
-            packed, nmask, plan, b.rows, pm, b.rec[0], b.hi[0]);                   \
+        pass_a_kernel<CB, W, G><<<t1 - t0, kRT, sizeof(PassSmem<CB, W>), s>>>(     \
+            packed, nmask, plan, b.rows, pm, t0, b.rec[0], b.hi[0]);               \
     } while (0)
 #define NPGE_PASS_A2(CB, W)                                                        \
     do {                                                                           \
         if (pm.peer_rec) NPGE_PASS_A(CB, W, true); else NPGE_PASS_A(CB, W, false); \
     } while (0)
-    if (plan.capa == 8) {
-        if (plan.wide) NPGE_PASS_A2(8, true); else NPGE_PASS_A2(8, false);
-    } else if (plan.capa == 9) {
-        if (plan.wide) NPGE_PASS_A2(9, true); else NPGE_PASS_A2(9, false);
-    } else {
-        if (plan.wide) NPGE_PASS_A2(10, true); else NPGE_PASS_A2(10, false);
+    for (int c = 0; c < n_chunks; c++) {
+        const uint32_t t0 = min(uint32_t(c) * per, tiles_a), t1 = min(t0 + per, tiles_a);
+        if (t1 > t0) {
+            if (plan.capa == 8) {
+                if (plan.wide) NPGE_PASS_A2(8, true); else NPGE_PASS_A2(8, false);
+            } else if (plan.capa == 9) {
+                if (plan.wide) NPGE_PASS_A2(9, true); else NPGE_PASS_A2(9, false);
+            } else {
+                if (plan.wide) NPGE_PASS_A2(10, true); else NPGE_PASS_A2(10, false);
+            }
+            *launches += 1;
+        }
+        if (ch && ch->done) cudaEventRecord(ch->done[c], s);
     }
 #undef NPGE_PASS_A2
 #undef NPGE_PASS_A
-    *launches += 1;
     if (ev) cudaEventRecord(ev[1], s);
 }
 

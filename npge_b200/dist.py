@@ -234,12 +234,20 @@ class CudaStages(AnchorEngine):
             self._ctx, C.byref(params), hist.ctypes.data, len(hist), C.byref(n_bins)))
         return hist[:n_bins.value].copy()
 
+    _chunks = 1
+
+    def dist_set_chunks(self, chunks):
+        """Pass A of the following steps runs in `chunks` chunks of tiles; dist_count_a
+        then returns chunks * bins counts ([chunk][bucket])."""
+        self._check(self._lib.npge_anchor_dist_set_chunks(self._ctx, chunks))
+        self._chunks = chunks
+
     def dist_count_a(self, params):
-        hist = np.zeros(1024, dtype=np.uint32)
+        hist = np.zeros(8 * 1024, dtype=np.uint32)
         n_bins = C.c_uint32()
         self._check(self._lib.npge_anchor_dist_count_a(
             self._ctx, C.byref(params), hist.ctypes.data, len(hist), C.byref(n_bins)))
-        return hist[:n_bins.value].copy()
+        return hist[:n_bins.value * self._chunks].copy()
 
     def dist_peer_close(self):
         self._check(self._lib.npge_anchor_dist_peer_close(self._ctx))
@@ -315,7 +323,7 @@ class _ShmGather:
     number, written after the payload (x86 keeps the store order).  Buffers
     alternate; a rank cannot run two gathers ahead of the slowest one, because
     it needs everybody's row of the gather in between."""
-    CAP = 1100
+    CAP = 8 * 1024 + 64
 
     def __init__(self, comm):
         import os
@@ -495,6 +503,9 @@ class DistAnchorFinder:
         self._want = want
         self.exchange = "collective"
         self._capacity = 0
+        # chunks of pass A in the bulk exchange: the copies of a finished chunk overlap
+        # the ranking of the next
+        self.chunks = max(1, min(8, int(os.environ.get("NPGE_ANCHOR_CHUNKS", "4"))))
 
     def _peer_setup(self, capacity):
         """(Re)allocates the receive buffers and maps them on every rank.
@@ -639,6 +650,9 @@ class DistAnchorFinder:
         fused = self.exchange == "peer"
         bulk = self.exchange == "bulk"
         if fused or bulk:
+            chunks = self.chunks if bulk else 1
+            if getattr(st, "_chunks", 1) != chunks:
+                st.dist_set_chunks(chunks)
             hist = st.dist_count_a(params)
             if bulk:  # pass A runs while the histograms are gathered
                 st.dist_scatter_local(params)
@@ -720,7 +734,7 @@ class DistAnchorFinder:
             n_positions=self.n_job_bases, local_fragments=s["n_fragments"],
             local_records=s["n_windows"], total_selected=int(tot_all[:, 0].sum()),
             exchange_ms=dict(self.exchange_ms), exchange=self.exchange,
-            host_ms=trace)
+            chunks=(self.chunks if bulk else 1), host_ms=trace)
         self._hist_all, self._hist = hist_all, hist
         self._last = out
         if job_stats:
@@ -739,11 +753,13 @@ class DistAnchorFinder:
         mask = (1 << 64) - 1
         # records this rank wrote into other ranks' HBM, and the device time of the
         # stage that moved them (bulk: the copies; peer: pass A itself)
-        cuts = bucket_ranges(self._hist_all, self.world)
-        hist = np.asarray(self._hist, dtype=np.int64)
+        bins = len(self._hist) // max(1, getattr(self.stages, "_chunks", 1) if self.exchange == "bulk" else 1)
+        cuts = bucket_ranges(np.asarray(self._hist_all).reshape(-1, bins), self.world)
+        hist = np.asarray(self._hist, dtype=np.int64).reshape(-1, bins).sum(axis=0)
         kept = int(hist[int(cuts[self.rank]):int(cuts[self.rank + 1])].sum())
         out.update(bucket_cuts=[int(c) for c in cuts],
                    nvlink_bytes_sent=(int(hist.sum()) - kept) * (12 if self._k > 21 else 8),
+                   # bulk: ms_pass[5] is what the copies add after the last chunk of pass A
                    nvlink_ms=(s["ms_pass"][5] if self.exchange == "bulk"
                               else s["ms_pass"][0] if self.exchange == "peer"
                               else out.get("exchange_ms", {}).get("records", 0.0)))

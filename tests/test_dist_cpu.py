@@ -127,20 +127,22 @@ def test_peer_destinations_match_the_receive_layout():
             assert [g[2] for g in got] == list(range(len(got)))
 
 
-def plan_tables_cxx(h, rank):
-    """npge_anchor_dist_plan_tables (csrc/dist_plan.h) through the C ABI; host only."""
+def plan_tables_cxx(h, rank, chunks=1):
+    """npge_anchor_dist_plan_tables (csrc/dist_plan.h) through the C ABI; host only.
+    h: [world * chunks sources][bins]."""
     from npge_b200 import _abi
     L = _abi.load()
     h = np.ascontiguousarray(h, dtype=np.uint32)
-    world, bins = h.shape
+    n_src, bins = h.shape
+    world = n_src // chunks
     u32 = lambda n: np.zeros(n, dtype=np.uint32)
     cuts, n_recv = u32(world + 1), np.zeros(world, dtype=np.uint64)
     dest_rank, dest_off = u32(bins), np.zeros(bins, dtype=np.int64)
     n_seg = np.zeros(1, dtype=np.uint32)
-    sb, se, sa, stl = u32(world * bins), u32(world * bins), u32(world * bins), u32(world * bins + 1)
+    sb, se, sa, stl = u32(n_src * bins), u32(n_src * bins), u32(n_src * bins), u32(n_src * bins + 1)
     at0, ast = u32(bins + 1), u32(bins + 1)
     rc = L.npge_anchor_dist_plan_tables(
-        h.ctypes.data, world, bins, rank, *[x.ctypes.data for x in (
+        h.ctypes.data, world, chunks, bins, rank, *[x.ctypes.data for x in (
             cuts, n_recv, dest_rank, dest_off, n_seg, sb, se, sa, stl, at0, ast)])
     assert rc == 0
     n = int(n_seg[0])
@@ -170,6 +172,22 @@ def test_cxx_plan_tables_equal_the_numpy_ones(seed, world, bins):
         assert np.array_equal(t["dest_rank"], dest_rank)
         assert np.array_equal(t["dest_off"], dest_off)
         assert [int(x) for x in t["n_recv_all"]] == n_recv
+
+
+def test_cxx_plan_tables_with_chunked_sources():
+    """Pass A in chunks: every (rank, chunk) is a source of the exchange; the receive
+    layout is source-major, so the numpy tables over the virtual sources describe it."""
+    rng = np.random.default_rng(9)
+    world, chunks, bins = 3, 4, 64
+    h = rng.integers(0, 6000, size=(world * chunks, bins))
+    cuts = D.bucket_ranges(h, world)
+    for rank in range(world):
+        t = plan_tables_cxx(h, rank, chunks)
+        assert list(t["cuts"]) == list(cuts)
+        want = D.segment_tables(h, cuts, rank)
+        for key in ("n_seg", "seg_begin", "seg_end", "seg_a", "seg_tile", "a_tile0", "a_start"):
+            assert np.array_equal(np.asarray(t[key]), np.asarray(want[key])), key
+        assert int(t["n_recv_all"][rank]) == want["n_recv"]
 
 
 def test_local_limits():
