@@ -270,6 +270,47 @@ int npge_anchor_dist_sort(npge_anchor_ctx* ctx, const npge_anchor_params* p,
 int npge_anchor_dist_emit(npge_anchor_ctx* ctx, const npge_anchor_params* p,
                           uint64_t local_limit, npge_anchor_stats* stats);
 
+/* Contexts of ONE process (npge_anchor_multi_* below): the other ranks' receive buffers
+ * are plain device pointers (rec[r], hi[r]; devices[r] = their CUDA device), reached
+ * through peer access, which is enabled here.  After dist_peer_alloc on every rank. */
+int npge_anchor_dist_peer_attach(npge_anchor_ctx* ctx, uint32_t world, uint32_t rank,
+                                 void* const* rec, void* const* hi, const int* devices);
+/* anchor-similar inside one process: this rank's found bitmap := OR of all ranks'
+ * (found[r]: their current bitmaps), built in a second buffer; dist_found_swap on
+ * every rank once all of them have finished reading. */
+int npge_anchor_dist_found_or(npge_anchor_ctx* ctx, uint32_t world, const void* const* found);
+int npge_anchor_dist_found_swap(npge_anchor_ctx* ctx);
+
+/* ---- several GPUs of one process: the host NPGE's Processor calls -----------------------
+ * One context and one host thread per GPU, the same per-rank stages as above with
+ * in-process rendezvous (a barrier, a shared histogram table, peer access).  The
+ * result is the one-GPU result, bit for bit: blocks in ascending hash order, the ranks'
+ * slices joined.  device_ids may repeat a device (several ranks on one GPU: tests).
+ *   multi_find          host buffers in, host arrays out (AnchorFinder::run_impl,
+ *                       src/algo/AnchorFinder.cpp:393-406)
+ *   multi_upload / multi_find_device / multi_fetch   the same in three steps; the packed
+ *                       genome stays resident, so that a Processor re-run on the same
+ *                       sequences (AnchorLoop, src/algo/MetaProcessor.cpp:32-38) skips
+ *                       the upload
+ *   multi_get_stats     rank >= 0: that rank's stats; rank < 0: the job's (counts and
+ *                       digest summed, times = max over ranks) */
+typedef struct npge_anchor_multi npge_anchor_multi;
+int npge_anchor_multi_create(npge_anchor_multi** m, const int* device_ids, int n_devices);
+void npge_anchor_multi_destroy(npge_anchor_multi* m);
+int npge_anchor_multi_devices(const npge_anchor_multi* m);
+int npge_anchor_multi_find(npge_anchor_multi* m, const npge_anchor_params* p,
+                           const uint8_t* bases, const uint64_t* seq_offsets, uint32_t n_seqs,
+                           const uint64_t* used_sorted, uint64_t n_used,
+                           npge_anchor_result* out);
+int npge_anchor_multi_upload(npge_anchor_multi* m, int32_t anchor_size, const uint8_t* bases,
+                             const uint64_t* seq_offsets, uint32_t n_seqs);
+int npge_anchor_multi_find_device(npge_anchor_multi* m, const npge_anchor_params* p,
+                                  const uint64_t* used_sorted, uint64_t n_used,
+                                  npge_anchor_stats* job_stats);
+int npge_anchor_multi_fetch(npge_anchor_multi* m, npge_anchor_result* out);
+void npge_anchor_multi_result_free(npge_anchor_result* out);
+int npge_anchor_multi_get_stats(npge_anchor_multi* m, int rank, npge_anchor_stats* stats);
+
 /* ---- FragmentFinder (src/algo/FragmentFinder.cpp:42-171) ---------------------------
  * Every exact occurrence of `pattern` (ATGCN bytes, N matches only N) on either
  * strand of the sequences: ori = +1 where the text equals the pattern, -1 where

@@ -24,6 +24,10 @@ EXPORTS = [
     "npge_anchor_upload_raw", "npge_anchor_dist_scatter_local",
     "npge_block_hashes", "npge_anchor_block_hashes", "npge_block_hashes_last_ms",
     "npge_anchor_debug_plan",
+    "npge_anchor_dist_peer_attach", "npge_anchor_dist_found_or", "npge_anchor_dist_found_swap",
+    "npge_anchor_multi_create", "npge_anchor_multi_destroy", "npge_anchor_multi_devices",
+    "npge_anchor_multi_find", "npge_anchor_multi_upload", "npge_anchor_multi_find_device",
+    "npge_anchor_multi_fetch", "npge_anchor_multi_result_free", "npge_anchor_multi_get_stats",
 ]
 IPC_BYTES = 128
 
@@ -174,5 +178,25 @@ def load():
                                            C.c_void_p, C.POINTER(C.c_uint64)]
     L.npge_block_hashes_last_ms.restype = C.c_float
     L.npge_block_hashes_last_ms.argtypes = [ctx]
+    L.npge_anchor_multi_create.restype = C.c_int
+    L.npge_anchor_multi_create.argtypes = [C.POINTER(ctx), C.c_void_p, C.c_int]
+    L.npge_anchor_multi_destroy.restype = None
+    L.npge_anchor_multi_destroy.argtypes = [ctx]
+    L.npge_anchor_multi_devices.restype = C.c_int
+    L.npge_anchor_multi_devices.argtypes = [ctx]
+    L.npge_anchor_multi_find.restype = C.c_int
+    L.npge_anchor_multi_find.argtypes = [ctx, C.POINTER(Params), C.c_void_p, C.c_void_p,
+                                         C.c_uint32, C.c_void_p, C.c_uint64, C.POINTER(Result)]
+    L.npge_anchor_multi_upload.restype = C.c_int
+    L.npge_anchor_multi_upload.argtypes = [ctx, C.c_int32, C.c_void_p, C.c_void_p, C.c_uint32]
+    L.npge_anchor_multi_find_device.restype = C.c_int
+    L.npge_anchor_multi_find_device.argtypes = [ctx, C.POINTER(Params), C.c_void_p, C.c_uint64,
+                                                C.POINTER(Stats)]
+    L.npge_anchor_multi_fetch.restype = C.c_int
+    L.npge_anchor_multi_fetch.argtypes = [ctx, C.POINTER(Result)]
+    L.npge_anchor_multi_result_free.restype = None
+    L.npge_anchor_multi_result_free.argtypes = [C.POINTER(Result)]
+    L.npge_anchor_multi_get_stats.restype = C.c_int
+    L.npge_anchor_multi_get_stats.argtypes = [ctx, C.c_int, C.POINTER(Stats)]
     _lib = L
     return L

@@ -7,8 +7,8 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 SOURCES = ["api.cu", "scan_kernels.cu", "msd_kernels.cu", "bucket_kernels.cu", "fragment_kernels.cu",
-           "ingest_kernels.cu", "block_hash_kernels.cu"]
-HEADERS = ["common.cuh", "kernels.h", "rank.cuh", "block_hash_core.h", "block_hash_names.h", "fetch_expand.h", os.path.join("..", "..", "include",
+           "ingest_kernels.cu", "block_hash_kernels.cu", "multi.cu"]
+HEADERS = ["common.cuh", "kernels.h", "rank.cuh", "dist_plan.h", "block_hash_core.h", "block_hash_names.h", "fetch_expand.h", os.path.join("..", "..", "include",
                                                      "npge_anchor.h")]
 LIB = os.path.join(HERE, "libnpge_anchor.so")
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3",
@@ -50,7 +50,11 @@ HOST = os.path.join(HERE, "host")
 SHIM_LIB = os.path.join(HOST, "libnpge_gpu_processors.so")
 SHIM_TEST = os.path.join(HOST, "test_gpu_anchor_finder")
 SHIM_TEST_MOVE = os.path.join(HOST, "test_gpu_move_unchanged")
+# the same processors compiled in the reference's own spelling (NPGE_B200_REAL_HEADERS:
+# string option rules, 3-argument add_gopt, add_opt_check) against host/ref_api
+SHIM_TEST_REFAPI = os.path.join(HOST, "test_gpu_anchor_finder_refapi")
 SHIM_SOURCES = ["gpu_anchor_finder.cpp", "gpu_anchor_finder.hpp", "npge_facade.hpp",
+                os.path.join("ref_api", "Processor.hpp"),
                 "test_gpu_anchor_finder.cpp", "test_gpu_move_unchanged.cpp"]
 
 
@@ -59,7 +63,7 @@ def build_shim(force=False):
     linked against libnpge_anchor.so) and its unit-test binary."""
     build(force=False)
     srcs = [os.path.join(HOST, f) for f in SHIM_SOURCES] + [LIB]
-    outs = [SHIM_LIB, SHIM_TEST, SHIM_TEST_MOVE]
+    outs = [SHIM_LIB, SHIM_TEST, SHIM_TEST_MOVE, SHIM_TEST_REFAPI]
     if (not force and all(os.path.exists(f) for f in outs) and
             all(os.path.getmtime(f) <= min(os.path.getmtime(o) for o in outs) for f in srcs)):
         return SHIM_TEST
@@ -74,6 +78,10 @@ def build_shim(force=False):
     subprocess.check_call([cxx] + common + ["-o", SHIM_TEST_MOVE,
                                             os.path.join(HOST, "test_gpu_move_unchanged.cpp"),
                                             "-L", HOST, "-lnpge_gpu_processors"] + link)
+    subprocess.check_call([cxx] + common + ["-DNPGE_B200_REAL_HEADERS", "-I",
+                                            os.path.join(HOST, "ref_api"), "-o", SHIM_TEST_REFAPI,
+                                            os.path.join(HOST, "test_gpu_anchor_finder.cpp"),
+                                            os.path.join(HOST, "gpu_anchor_finder.cpp")] + link)
     return SHIM_TEST
 
 

@@ -28,6 +28,14 @@ int fail(int code, const std::string& msg) {
     return code;
 }
 
+}  // namespace
+
+namespace npge_b200 {
+int set_last_error(int code, const std::string& msg) { return fail(code, msg); }
+}  // namespace npge_b200
+
+namespace {
+
 #define NPGE_CUDA(expr)                                                        \
     do {                                                                       \
         cudaError_t e__ = (expr);                                              \
@@ -240,7 +248,7 @@ extern "C" void npge_anchor_destroy(npge_anchor_ctx* ctx) {
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     DeviceBuffer* all[] = {&ctx->ascii, &ctx->packed, &ctx->nmask, &ctx->seq_start,
                            &ctx->seq_caller, &ctx->seq_pair, &ctx->g_seq_pair, &ctx->counters, &ctx->used,
-                           &ctx->found_bits, &ctx->sel,
+                           &ctx->found_bits, &ctx->found_tmp, &ctx->sel,
                            &ctx->r_seq, &ctx->r_pos, &ctx->r_ori,
                            &ctx->r_block_off, &ctx->r_block_hash,
                            &ctx->summary, &ctx->rows, &ctx->blk,
@@ -1324,6 +1332,64 @@ extern "C" int npge_anchor_dist_peer_open(npge_anchor_ctx* ctx, uint32_t world,
         ctx->peer_rec[r] = q[0];
         ctx->peer_hi[r] = q[1];
     }
+    return NPGE_ANCHOR_OK;
+}
+
+// Contexts of ONE process (npge_anchor_multi_*): the receive buffers of the other
+// ranks are plain device pointers; peer access between the devices is enabled here.
+extern "C" int npge_anchor_dist_peer_attach(npge_anchor_ctx* ctx, uint32_t world, uint32_t rank,
+                                            void* const* rec, void* const* hi,
+                                            const int* devices) {
+    if (!ctx || !rec || !hi || !devices) return fail(NPGE_ANCHOR_ERR_PARAMS, "NULL argument");
+    if (rank >= world) return fail(NPGE_ANCHOR_ERR_PARAMS, "rank >= world");
+    if (!ctx->recv_rec.ptr || !ctx->peer_capacity) {
+        return fail(NPGE_ANCHOR_ERR_STATE, "npge_anchor_dist_peer_alloc first");
+    }
+    NPGE_TRY(npge_anchor_dist_peer_close(ctx));
+    NPGE_CUDA(cudaSetDevice(ctx->device));
+    ctx->peer_rec.assign(world, nullptr);
+    ctx->peer_hi.assign(world, nullptr);
+    ctx->dist_rank = rank;
+    for (uint32_t r = 0; r < world; r++) {
+        if (devices[r] != ctx->device) {
+            int can = 0;
+            NPGE_CUDA(cudaDeviceCanAccessPeer(&can, ctx->device, devices[r]));
+            if (!can) return fail(NPGE_ANCHOR_ERR_CUDA, "no peer access between the devices");
+            cudaError_t e = cudaDeviceEnablePeerAccess(devices[r], 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) {
+                return fail(NPGE_ANCHOR_ERR_CUDA, std::string("cudaDeviceEnablePeerAccess: ") +
+                            cudaGetErrorString(e));
+            }
+            cudaGetLastError();
+        }
+        ctx->peer_rec[r] = r == rank ? ctx->recv_rec.ptr : rec[r];
+        ctx->peer_hi[r] = r == rank ? ctx->recv_hi.ptr : hi[r];
+    }
+    return NPGE_ANCHOR_OK;
+}
+
+// The found bitmap of an anchor-similar job inside one process: this rank's bitmap
+// becomes the OR of all ranks' (found[r]: their current bitmaps, peer pointers).  The
+// result is built in a second buffer; call npge_anchor_dist_found_swap on every rank
+// after all of them have finished reading.
+extern "C" int npge_anchor_dist_found_or(npge_anchor_ctx* ctx, uint32_t world,
+                                         const void* const* found) {
+    if (!ctx || !found || world == 0 || world > 8) return fail(NPGE_ANCHOR_ERR_PARAMS, "bad arguments");
+    NPGE_CUDA(cudaSetDevice(ctx->device));
+    const size_t bytes = (ctx->g_padded / 8 + 256) / 16 * 16;
+    NPGE_TRY(ensure(ctx->found_tmp, ctx->g_padded / 8 + 256));
+    const uint32_t* srcs[8];
+    for (uint32_t r = 0; r < world; r++) srcs[r] = static_cast<const uint32_t*>(found[r]);
+    launch_found_or(srcs, int(world), ptr<uint32_t>(ctx->found_tmp), bytes, ctx->stream,
+                    &ctx->dist_launches);
+    NPGE_CUDA(cudaGetLastError());
+    NPGE_CUDA(cudaStreamSynchronize(ctx->stream));
+    return NPGE_ANCHOR_OK;
+}
+
+extern "C" int npge_anchor_dist_found_swap(npge_anchor_ctx* ctx) {
+    if (!ctx) return fail(NPGE_ANCHOR_ERR_PARAMS, "ctx is NULL");
+    std::swap(ctx->found_bits, ctx->found_tmp);
     return NPGE_ANCHOR_OK;
 }
 

@@ -1010,6 +1010,29 @@ __global__ void bucket_finalize_kernel(BucketArgs a) {
     a.r_block_off[nb] = emitted;
 }
 
+// ---- found bitmap of a multi-GPU job inside one process: dst = OR of the ranks'
+// bitmaps, read through peer pointers (every bit is set by exactly one rank)
+struct FoundSources {
+    const uint32_t* src[8];
+    int n;
+};
+
+__global__ void __launch_bounds__(256)
+found_or_kernel(FoundSources fs, uint32_t* __restrict__ dst, size_t n_vec) {
+    const size_t stride = size_t(gridDim.x) * blockDim.x;
+    for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n_vec; i += stride) {
+        uint4 v = make_uint4(0, 0, 0, 0);
+        for (int r = 0; r < fs.n; r++) {
+            const uint4 x = reinterpret_cast<const uint4*>(fs.src[r])[i];
+            v.x |= x.x;
+            v.y |= x.y;
+            v.z |= x.z;
+            v.w |= x.w;
+        }
+        reinterpret_cast<uint4*>(dst)[i] = v;
+    }
+}
+
 template <typename K>
 void set_smem(K kernel, size_t bytes) {
     cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -1087,6 +1110,18 @@ void launch_bucket_stage(const BucketArgs& a, int stage, uint64_t max_records,
     }
 #undef NPGE_LAUNCH_W
 #undef NPGE_LAUNCH
+}
+
+void launch_found_or(const uint32_t* const* srcs, int n_src, uint32_t* dst, size_t bytes,
+                     cudaStream_t s, uint32_t* launches) {
+    FoundSources fs = {};
+    fs.n = n_src < 8 ? n_src : 8;
+    for (int r = 0; r < fs.n; r++) fs.src[r] = srcs[r];
+    const size_t n_vec = bytes / 16;
+    if (n_vec == 0) return;
+    const size_t want = (n_vec + 255) / 256;
+    found_or_kernel<<<uint32_t(want < 148 * 8 ? want : 148 * 8), 256, 0, s>>>(fs, dst, n_vec);
+    *launches += 1;
 }
 
 void launch_bucket(const BucketArgs& a, bool similar, uint64_t max_records,

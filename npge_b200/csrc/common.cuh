@@ -136,7 +136,7 @@ struct npge_anchor_ctx {
 
     // sort / grouping scratch
     npge_b200::DeviceBuffer counters, used;
-    npge_b200::DeviceBuffer found_bits, sel;
+    npge_b200::DeviceBuffer found_bits, found_tmp, sel;
     // MSD partition + bucket sort (msd_kernels.cu, bucket_kernels.cu)
     npge_b200::DeviceBuffer rows, blk, segtab, fine_start, tile_desc, bstatus, unit_wtot, units;
     npge_b200::DeviceBuffer rec[2], rhi[2], seq_lut;

@@ -136,6 +136,9 @@ enum {
 };
 void launch_bucket_stage(const BucketArgs& a, int stage, uint64_t max_records,
                          cudaStream_t s, uint32_t* launches);
+// dst = OR of n_src (<= 8) bitmaps of `bytes` bytes (a multiple of 16), peer pointers
+void launch_found_or(const uint32_t* const* srcs, int n_src, uint32_t* dst, size_t bytes,
+                     cudaStream_t s, uint32_t* launches);
 // ev (optional, 1 event): recorded after the sort (+ count) kernels
 void launch_bucket(const BucketArgs& a, bool similar, uint64_t max_records,
                    cudaStream_t s, cudaEvent_t* ev, uint32_t* launches);
@@ -205,5 +208,8 @@ void launch_block_hash_cuts(const uint64_t* block_off, uint64_t n_blocks, uint64
                             uint32_t n_cuts, uint64_t* cut_block, uint64_t* cut_frag,
                             cudaStream_t s);
 void launch_block_hash(const BlockHashArgs& a, cudaStream_t s);
+
+// thread-local error text of the C ABI (api.cu), for the other translation units
+int set_last_error(int code, const std::string& msg);
 
 }  // namespace npge_b200

@@ -270,3 +270,69 @@ class AnchorEngine:
         s = _abi.Stats()
         self._check(self._lib.npge_anchor_get_stats(self._ctx, C.byref(s)))
         return _stats_dict(s)
+
+
+class MultiEngine:
+    """AnchorFinder over several GPUs of this process (npge_anchor_multi_*): what
+    npge::gpu::AnchorFinder::set_devices drives.  `devices` may repeat a device
+    (several ranks on one GPU)."""
+
+    def __init__(self, devices):
+        self._lib = _abi.load()
+        self._m = C.c_void_p()
+        ids = (C.c_int * len(devices))(*devices)
+        self._check(self._lib.npge_anchor_multi_create(C.byref(self._m), ids, len(devices)))
+
+    def close(self):
+        if self._m:
+            self._lib.npge_anchor_multi_destroy(self._m)
+            self._m = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc):
+        if rc != _abi.OK:
+            raise AnchorError(rc, self._lib.npge_anchor_last_error().decode())
+
+    def upload(self, seqs, k):
+        bases, offsets = seqs if isinstance(seqs, tuple) else concat(seqs)
+        self._check(self._lib.npge_anchor_multi_upload(
+            self._m, k, bases.ctypes.data, offsets.ctypes.data, len(offsets) - 1))
+
+    def find_device(self, k, similar=True, max_frags=100000, used=None):
+        u, up = AnchorEngine._used(used)
+        p = _abi.Params(k, int(bool(similar)), int(max_frags))
+        s = _abi.Stats()
+        self._check(self._lib.npge_anchor_multi_find_device(
+            self._m, C.byref(p), up, len(u), C.byref(s)))
+        return _stats_dict(s)
+
+    def fetch(self):
+        r = _abi.Result()
+        self._check(self._lib.npge_anchor_multi_fetch(self._m, C.byref(r)))
+        try:
+            return AnchorResult(r)
+        finally:
+            self._lib.npge_anchor_multi_result_free(C.byref(r))
+
+    def find(self, seqs, k, similar=True, max_frags=100000, used=None):
+        bases, offsets = seqs if isinstance(seqs, tuple) else concat(seqs)
+        u, up = AnchorEngine._used(used)
+        p = _abi.Params(k, int(bool(similar)), int(max_frags))
+        r = _abi.Result()
+        self._check(self._lib.npge_anchor_multi_find(
+            self._m, C.byref(p), bases.ctypes.data, offsets.ctypes.data,
+            len(offsets) - 1, up, len(u), C.byref(r)))
+        try:
+            return AnchorResult(r)
+        finally:
+            self._lib.npge_anchor_multi_result_free(C.byref(r))
+
+    def rank_stats(self, rank):
+        s = _abi.Stats()
+        self._check(self._lib.npge_anchor_multi_get_stats(self._m, rank, C.byref(s)))
+        return _stats_dict(s)

@@ -18,6 +18,8 @@
 #include "../../include/npge_anchor.h"
 
 #ifdef NPGE_B200_REAL_HEADERS
+#include <boost/bind.hpp>
+
 #include "Sequence.hpp"
 #include "Fragment.hpp"
 #include "Block.hpp"
@@ -29,9 +31,24 @@ namespace npge {
 namespace gpu {
 
 struct AnchorFinder::Impl {
-    npge_anchor_ctx* ctx = nullptr;
-    int device = 0;
+    npge_anchor_ctx* ctx = nullptr;      // one device
+    npge_anchor_multi* multi = nullptr;  // several devices
+    std::vector<int> devices = std::vector<int>(1, 0);
     std::vector<uint64_t> used_hashes;  // sorted; AnchorFinderImpl::used_hashes_ (:30-32)
+    // the genome resident on the device(s): AnchorLoop re-runs this instance on the same
+    // sequences (src/algo/MetaProcessor.cpp:32-38, src/algo/Pipe.cpp:41-61)
+    std::vector<const Sequence*> up_seqs;
+    std::vector<uint64_t> up_sizes;
+    uint64_t up_probe = 0;
+    int up_k = 0;
+    bool resident = false, reused = false;
+    void drop() {
+        if (ctx) npge_anchor_destroy(ctx);
+        if (multi) npge_anchor_multi_destroy(multi);
+        ctx = nullptr;
+        multi = nullptr;
+        resident = false;
+    }
 };
 
 AnchorFinder::AnchorFinder() : impl_(new Impl) {
@@ -67,16 +84,22 @@ AnchorFinder::AnchorFinder() : impl_(new Impl) {
 }
 
 AnchorFinder::~AnchorFinder() {
-    if (impl_->ctx) npge_anchor_destroy(impl_->ctx);
+    impl_->drop();
     delete impl_;
 }
 
 void AnchorFinder::set_device(int device) {
-    if (impl_->ctx) {
-        npge_anchor_destroy(impl_->ctx);
-        impl_->ctx = nullptr;
-    }
-    impl_->device = device;
+    set_devices(std::vector<int>(1, device));
+}
+
+void AnchorFinder::set_devices(const std::vector<int>& devices) {
+    if (devices.empty() || devices.size() > 8) throw Exception("AnchorFinder (GPU): 1..8 devices");
+    impl_->drop();
+    impl_->devices = devices;
+}
+
+bool AnchorFinder::last_run_reused_upload() const {
+    return impl_->reused;
 }
 
 namespace {
@@ -102,6 +125,27 @@ void check_block(const Block* block) {
     }
 }
 
+// A cheap fingerprint of the sequences' letters (the ends and 256 evenly spaced
+// positions of each): the resident genome is reused when the same Sequence objects,
+// with the same sizes and the same fingerprint, come again.
+uint64_t probe_sequences(const std::vector<SequencePtr>& seqs) {
+    uint64_t h = 0xcbf29ce484222325ull;
+    auto mix = [&](uint64_t v) {
+        h ^= v;
+        h *= 0x100000001b3ull;
+    };
+    for (size_t i = 0; i < seqs.size(); i++) {
+        const Sequence& s = *seqs[i];
+        const size_t n = s.size();
+        mix(n);
+        const size_t edge = n < 32 ? n : 32;
+        for (size_t j = 0; j < edge; j++) mix(uint8_t(s.char_at(j)));
+        for (size_t j = 0; j < edge; j++) mix(uint8_t(s.char_at(n - 1 - j)));
+        for (size_t j = 0; j < 256 && n > 64; j++) mix(uint8_t(s.char_at((n - 1) / 256 * j)));
+    }
+    return h;
+}
+
 }  // namespace
 
 void AnchorFinder::run_impl() const {
@@ -109,23 +153,61 @@ void AnchorFinder::run_impl() const {
     npge_anchor_params params;
     params.anchor_size = opt_value("anchor-size").as<int>();
     params.anchor_similar = opt_value("anchor-similar").as<bool>() ? 1 : 0;
+    // (a negative value never truncates: size_t comparison, AnchorFinder.cpp:361)
     params.max_anchor_fragments = opt_value("max-anchor-fragments").as<int>();
     BlockSet& bs = *block_set();
-    // one contiguous ASCII buffer + offsets; the caller index of a sequence is
-    // its index in `seqs` and comes back in frag_seq
+    // the caller index of a sequence is its index in `seqs` and comes back in frag_seq
     std::vector<SequencePtr> seqs = bs.seqs();
-    std::vector<uint64_t> offsets(seqs.size() + 1, 0);
-    for (size_t i = 0; i < seqs.size(); i++) offsets[i + 1] = offsets[i] + seqs[i]->size();
-    std::string bases;
-    bases.reserve(offsets.back());
-    for (size_t i = 0; i < seqs.size(); i++) bases += seqs[i]->contents();
-    if (!st.ctx) check(npge_anchor_create(&st.ctx, st.device), "no CUDA device");
+    const bool many = st.devices.size() > 1;
+    if (many && !st.multi) {
+        check(npge_anchor_multi_create(&st.multi, st.devices.data(), int(st.devices.size())),
+              "no CUDA device");
+    }
+    if (!many && !st.ctx) check(npge_anchor_create(&st.ctx, st.devices[0]), "no CUDA device");
+    // is the genome of the previous run still the one on the device(s)?
+    std::vector<const Sequence*> ptrs(seqs.size());
+    std::vector<uint64_t> sizes(seqs.size());
+    for (size_t i = 0; i < seqs.size(); i++) {
+        ptrs[i] = seqs[i].get();
+        sizes[i] = seqs[i]->size();
+    }
+    const uint64_t probe = probe_sequences(seqs);
+    st.reused = st.resident && st.up_k == params.anchor_size && st.up_seqs == ptrs &&
+                st.up_sizes == sizes && st.up_probe == probe;
+    if (!st.reused) {
+        // one contiguous ASCII buffer + offsets
+        std::vector<uint64_t> offsets(seqs.size() + 1, 0);
+        for (size_t i = 0; i < seqs.size(); i++) offsets[i + 1] = offsets[i] + sizes[i];
+        std::string bases;
+        bases.reserve(offsets.back());
+        for (size_t i = 0; i < seqs.size(); i++) bases += seqs[i]->contents();
+        st.resident = false;
+        const uint8_t* b = reinterpret_cast<const uint8_t*>(bases.data());
+        if (many) {
+            check(npge_anchor_multi_upload(st.multi, params.anchor_size, b, offsets.data(),
+                                           uint32_t(seqs.size())), "npge_anchor_multi_upload");
+        } else {
+            check(npge_anchor_upload(st.ctx, params.anchor_size, b, offsets.data(),
+                                     uint32_t(seqs.size())), "npge_anchor_upload");
+        }
+        st.up_seqs = ptrs;
+        st.up_sizes = sizes;
+        st.up_probe = probe;
+        st.up_k = params.anchor_size;
+        st.resident = true;
+    }
     npge_anchor_result r;
-    check(npge_anchor_find(st.ctx, &params,
-                           reinterpret_cast<const uint8_t*>(bases.data()), offsets.data(),
-                           uint32_t(seqs.size()), st.used_hashes.data(),
-                           st.used_hashes.size(), &r),
-          "npge_anchor_find");
+    if (many) {
+        check(npge_anchor_multi_find_device(st.multi, &params, st.used_hashes.data(),
+                                            st.used_hashes.size(), nullptr),
+              "npge_anchor_multi_find_device");
+        check(npge_anchor_multi_fetch(st.multi, &r), "npge_anchor_multi_fetch");
+    } else {
+        check(npge_anchor_find_device(st.ctx, &params, st.used_hashes.data(),
+                                      st.used_hashes.size(), nullptr),
+              "npge_anchor_find_device");
+        check(npge_anchor_fetch(st.ctx, &r), "npge_anchor_fetch");
+    }
     const size_t k = size_t(params.anchor_size);
     try {
         for (uint64_t b = 0; b < r.n_blocks; b++) {
@@ -144,10 +226,10 @@ void AnchorFinder::run_impl() const {
         st.used_hashes.erase(std::unique(st.used_hashes.begin(), st.used_hashes.end()),
                              st.used_hashes.end());
     } catch (...) {
-        npge_anchor_result_free(&r);
+        if (many) npge_anchor_multi_result_free(&r); else npge_anchor_result_free(&r);
         throw;
     }
-    npge_anchor_result_free(&r);
+    if (many) npge_anchor_multi_result_free(&r); else npge_anchor_result_free(&r);
 }
 
 const char* AnchorFinder::name_impl() const {
@@ -159,6 +241,19 @@ struct FragmentFinder::Impl {
     npge_anchor_ctx* ctx = nullptr;
     int device = 0;
 };
+
+#ifdef NPGE_B200_REAL_HEADERS
+// the option check of the reference's processor, FragmentFinder.cpp:18-28
+static bool pattern_length(const Processor* f, std::string& message) {
+    std::string p = f->opt_value("pattern").as<std::string>();
+    Sequence::to_atgcn(p);
+    if (p.empty()) {
+        message = "'pattern' should not be empty";
+        return false;
+    }
+    return true;
+}
+#endif
 
 FragmentFinder::FragmentFinder() : impl_(new Impl) {
     add_opt("pattern", "Sequence searched for", std::string(""));

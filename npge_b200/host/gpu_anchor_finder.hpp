@@ -24,6 +24,12 @@ public:
 
     // the CUDA device of this instance (default 0); call before run()
     void set_device(int device);
+    // several GPUs: positions are sharded over them, k-mers repartitioned by hash
+    // range (npge_anchor_multi_*); one id may repeat (tests on one GPU)
+    void set_devices(const std::vector<int>& devices);
+    // how the last run() got its sequences onto the device(s): true = the packed
+    // genome of the previous run was still valid (same sequences) and was reused
+    bool last_run_reused_upload() const;
 
 protected:
     void run_impl() const;          // Processor.hpp:482

@@ -310,6 +310,37 @@ protected:
         add_opt(name, description, default_value);
     }
     void add_opt_rule(const Rule& rule) { rules_.push_back(rule); }
+    // ---- the reference's own spellings (src/algo/Processor.hpp:225-238,359-372), so that
+    // the NPGE_B200_REAL_HEADERS branch of the processors compiles and runs here too ----
+    typedef std::function<bool(std::string&)> OptionsChecker;
+    void add_opt_check(const OptionsChecker& checker) { rules_.push_back(checker); }
+    // "name op integer", op one of > >= < <= == != (the form every rule on this path has)
+    void add_opt_rule(const std::string& rule) {
+        std::istringstream in(rule);
+        std::string name, op;
+        long long rhs = 0;
+        if (!(in >> name >> op >> rhs)) throw Exception("bad option rule: " + rule);
+        rules_.push_back([this, name, op, rhs, rule](std::string& message) {
+            const long long v = opt_value(name).as<int>();
+            message = rule;
+            if (op == ">") return v > rhs;
+            if (op == ">=") return v >= rhs;
+            if (op == "<") return v < rhs;
+            if (op == "<=") return v <= rhs;
+            if (op == "==") return v == rhs;
+            if (op == "!=") return v != rhs;
+            throw Exception("bad option rule: " + rule);
+        });
+    }
+    // the default comes from the configuration (src/global/opts.lua; CMakeLists.txt:41-46)
+    void add_gopt(const std::string& name, const std::string& description,
+                  const std::string& global_name) {
+        if (global_name == "ANCHOR_SIZE") add_opt(name, description, 20);
+        else if (global_name == "ANCHOR_FP") add_opt(name, description, 0.1);
+        else if (global_name == "MAX_ANCHOR_FRAGMENTS") add_opt(name, description, 100000);
+        else if (global_name == "MAX_MATCHES") add_opt(name, description, 1000);
+        else throw Exception("unknown global option " + global_name);
+    }
     void declare_bs(const std::string& /*name*/, const std::string& /*description*/) {}
     virtual void run_impl() const = 0;
     virtual const char* name_impl() const { return ""; }

@@ -4,6 +4,7 @@
 //
 //   test_gpu_anchor_finder            all cases (needs a CUDA device)
 //   test_gpu_anchor_finder --no-gpu   only the cases that never reach the device
+#include <algorithm>
 #include <cstdio>
 #include <cstring>
 #include <memory>
@@ -203,6 +204,90 @@ static void truncation() {
     CHECK(frags <= 4 && bs->size() >= 1);
 }
 
+// canonical text of a blockset: sorted blocks of sorted "seq:min:max:ori" tuples (a
+// sequence is named by its size: the blockset orders its sequences by address)
+static std::string canonical(const BlockSet& bs) {
+    std::vector<std::string> blocks;
+    for (BlockSet::const_iterator b = bs.begin(); b != bs.end(); ++b) {
+        std::vector<std::string> fr;
+        for (Block::const_iterator f = (*b)->begin(); f != (*b)->end(); ++f) {
+            fr.push_back(std::to_string((*f)->seq()->size()) + ":" + std::to_string((*f)->min_pos()) + ":" +
+                         std::to_string((*f)->max_pos()) + ":" + std::to_string((*f)->ori()));
+        }
+        std::sort(fr.begin(), fr.end());
+        std::string t;
+        for (size_t i = 0; i < fr.size(); i++) t += fr[i] + " ";
+        blocks.push_back(t);
+    }
+    std::sort(blocks.begin(), blocks.end());
+    std::string out;
+    for (size_t i = 0; i < blocks.size(); i++) out += blocks[i] + "\n";
+    return out;
+}
+
+static std::string pseudo_genome(unsigned seed, size_t n) {
+    std::string s(n, 'A');
+    unsigned x = seed * 2654435761u + 12345u;
+    for (size_t i = 0; i < n; i++) {
+        x = x * 1664525u + 1013904223u;
+        s[i] = "ATGC"[(x >> 24) & 3];
+    }
+    return s;
+}
+
+// several GPUs behind the Processor (set_devices): the 2- and 3-rank jobs (ranks share
+// the devices of this box) give the blockset of the one-device run
+static void several_devices_equal_one_device() {
+    const std::string a = pseudo_genome(1, 9000);
+    std::string b = a.substr(2000, 5000) + pseudo_genome(2, 1500) + a.substr(100, 900);
+    std::string c = pseudo_genome(3, 700) + a.substr(4000, 2500) + "NNNNNNNN" + b.substr(10, 600);
+    for (int similar = 0; similar < 2; similar++) {
+        std::string want;
+        for (int ranks = 1; ranks <= 3; ranks++) {
+            BlockSetPtr bs = blockset_of({a.c_str(), b.c_str(), c.c_str()});
+            gpu::AnchorFinder af;
+            af.set_devices(std::vector<int>(size_t(ranks), 0));
+            af.set_block_set(bs);
+            af.set_opt_value("anchor-size", 16);
+            af.set_opt_value("anchor-similar", similar != 0);
+            af.set_opt_value("max-anchor-fragments", similar ? 500 : -1);  // negative: no limit
+            af.run();
+            CHECK(bs->size() > 0);
+            if (ranks == 1) want = canonical(*bs);
+            CHECK(canonical(*bs) == want);
+        }
+    }
+}
+
+// AnchorLoop re-runs one instance on the same sequences (MetaProcessor.cpp:32-38): the
+// second run finds the packed genome still on the device and skips the upload
+static void resident_genome_is_reused() {
+    const std::string a = pseudo_genome(7, 6000);
+    const std::string b = a.substr(1000, 3000) + pseudo_genome(8, 800);
+    for (int ranks = 1; ranks <= 2; ranks++) {
+        BlockSetPtr bs = blockset_of({a.c_str(), b.c_str()});
+        gpu::AnchorFinder af;
+        af.set_devices(std::vector<int>(size_t(ranks), 0));
+        af.set_block_set(bs);
+        af.set_opt_value("anchor-size", 12);
+        af.set_opt_value("anchor-similar", false);
+        af.run();
+        CHECK(!af.last_run_reused_upload());
+        const size_t first = bs->size();
+        CHECK(first > 0);
+        af.run();  // same blockset, same sequences: used hashes leave at most one block
+        CHECK(af.last_run_reused_upload());
+        CHECK(bs->size() <= first + 1);
+        af.set_opt_value("anchor-size", 13);  // another k: the layout changes
+        af.run();
+        CHECK(!af.last_run_reused_upload());
+        BlockSetPtr other = blockset_of({b.c_str(), a.c_str()});
+        af.set_block_set(other);
+        af.run();
+        CHECK(!af.last_run_reused_upload());
+    }
+}
+
 // ---- FragmentFinder ---------------------------------------------------------------
 static void fragment_finder_options() {
     gpu::FragmentFinder ff;
@@ -279,6 +364,8 @@ int main(int argc, char** argv) {
             AnchorFinder_several_sequences(2);
             used_hashes_across_runs();
             truncation();
+            several_devices_equal_one_device();
+            resident_genome_is_reused();
             fragment_finder_run();
         } catch (const std::exception& e) {
             failures++;

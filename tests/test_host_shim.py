@@ -31,9 +31,20 @@ def test_shim_library_exports_the_processor(binary):
     assert "npge::gpu::AnchorFinder::run_impl() const" in syms
     assert "npge::gpu::AnchorFinder::name_impl() const" in syms
     assert "npge_anchor_find" in syms  # bound to the C ABI, not to a copy of the kernels
+    assert "npge_anchor_multi_find_device" in syms  # set_devices: the several-GPU host
+
+
+def test_reference_spelling_of_the_processors_compiles_and_runs(binary):
+    """The NPGE_B200_REAL_HEADERS branch (string option rules, 3-argument add_gopt,
+    add_opt_check(boost::bind(pattern_length, this, _1))) is built against
+    host/ref_api and passes the same device-free cases."""
+    out = run(build.SHIM_TEST_REFAPI, "--no-gpu")
+    assert "no-gpu subset" in out
 
 
 @pytest.mark.gpu
 def test_reference_unit_cases_on_the_gpu(binary):
     out = run(binary)
+    assert "no-gpu" not in out
+    out = run(build.SHIM_TEST_REFAPI)   # and in the reference's own spelling
     assert "no-gpu" not in out
