@@ -337,6 +337,28 @@ int npge_fragment_find_device(npge_anchor_ctx* ctx, const uint8_t* pattern,
                               npge_fragment_result* out);
 void npge_fragment_result_free(npge_fragment_result* out);
 
+/* npge_fragment_find_device without any allocation.  NO COUNTERPART IN THE REFERENCE:
+ * added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * The kernels' scratch is a file-scope device array of fixed size (about 193 KiB, held by
+ * every GPU that loads the library until exit), hence the limits: at most
+ * NPGE_FRAGMENT_NOALLOC_MAX_POSITIONS uploaded positions (bases + one pad per sequence,
+ * rounded up to 4096) and patterns of at most NPGE_FRAGMENT_NOALLOC_MAX_PATTERN bases;
+ * beyond either the call fails with NPGE_ANCHOR_ERR_CAPACITY.
+ *   d_frag_seq / d_frag_min_pos / d_frag_ori   DEVICE arrays of `capacity` elements the
+ *       caller allocated; at most min(max_matches, capacity) matches are written, in the
+ *       order of npge_fragment_find_device
+ *   n_matches, total_matches   host pointers (optional): matches written / found
+ * Calls no cudaMalloc, cudaFree, cudaHostAlloc or other allocating routine.  All calls on
+ * one GPU share the scratch array: calls that overlap on the GPU race, serialise them. */
+#define NPGE_FRAGMENT_NOALLOC_MAX_POSITIONS (1u << 26)
+#define NPGE_FRAGMENT_NOALLOC_MAX_PATTERN 1024
+int npge_fragment_find_device_noalloc(npge_anchor_ctx* ctx, const uint8_t* pattern,
+                                      uint32_t pattern_len, int64_t max_matches,
+                                      uint32_t* d_frag_seq, uint32_t* d_frag_min_pos,
+                                      int8_t* d_frag_ori, uint64_t capacity,
+                                      uint64_t* n_matches, uint64_t* total_matches);
+
 /* ---- block_hash / blockset_hash (src/model/block_hash.cpp:29-54,125-130) ------------
  * The reference's own fingerprint of a block: the ids "name_begin_last"
  * (Fragment::id, src/model/Fragment.cpp:173-183) of its fragments, as they are

@@ -23,7 +23,7 @@ EXPORTS = [
     "npge_fragment_find", "npge_fragment_find_device", "npge_fragment_result_free",
     "npge_anchor_upload_raw", "npge_anchor_dist_scatter_local",
     "npge_block_hashes", "npge_anchor_block_hashes", "npge_block_hashes_last_ms",
-    "npge_anchor_debug_plan",
+    "npge_anchor_debug_plan", "npge_fragment_find_device_noalloc",
     "npge_anchor_dist_peer_attach", "npge_anchor_dist_found_or", "npge_anchor_dist_found_swap",
     "npge_anchor_multi_create", "npge_anchor_multi_destroy", "npge_anchor_multi_devices",
     "npge_anchor_multi_find", "npge_anchor_multi_upload", "npge_anchor_multi_find_device",
@@ -166,6 +166,10 @@ def load():
     L.npge_fragment_find_device.restype = C.c_int
     L.npge_fragment_find_device.argtypes = [ctx, C.c_char_p, C.c_uint32, C.c_int64,
                                             C.POINTER(FragmentResult)]
+    L.npge_fragment_find_device_noalloc.restype = C.c_int
+    L.npge_fragment_find_device_noalloc.argtypes = [
+        ctx, C.c_char_p, C.c_uint32, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p,
+        C.c_uint64, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
     L.npge_fragment_result_free.restype = None
     L.npge_fragment_result_free.argtypes = [C.POINTER(FragmentResult)]
     L.npge_block_hashes.restype = C.c_int

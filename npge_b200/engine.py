@@ -225,6 +225,18 @@ class AnchorEngine:
         out, total = self._matches(r)
         return (out, total) if with_total else out
 
+    def find_fragments_device_noalloc(self, pattern, max_matches, d_seq, d_pos, d_ori,
+                                      capacity):
+        """npge_fragment_find_device_noalloc: the library allocates nothing; d_seq /
+        d_pos / d_ori are DEVICE pointers (ints) to arrays of `capacity` elements the
+        caller owns.  Returns (matches written, matches found)."""
+        p = pattern.encode() if isinstance(pattern, str) else bytes(pattern)
+        n, total = C.c_uint64(0), C.c_uint64(0)
+        self._check(self._lib.npge_fragment_find_device_noalloc(
+            self._ctx, p, len(p), int(max_matches), d_seq, d_pos, d_ori, int(capacity),
+            C.byref(n), C.byref(total)))
+        return int(n.value), int(total.value)
+
     # ---- block_hash / blockset_hash (src/model/block_hash.cpp) -----------------------
     @staticmethod
     def _names(names):
