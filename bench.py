@@ -496,6 +496,17 @@ def run_gpu(args, rank, world, local_rank):
         d2h_default = runner.find_host(pinned_np, offsets, K, True, 100000)
     barrier()
     e2e_default_t = time.perf_counter() - t0
+    e2e_full = None
+    if world == 1:  # the full-layout call beside it (9 bytes per fragment over PCIe)
+        runner.find_host(pinned_np, offsets, K, False, BIG, full=True)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            d2h_full = runner.find_host(pinned_np, offsets, K, False, BIG, full=True)
+        torch.cuda.synchronize()
+        e2e_full = {"value": n_total * e2e_steps / (time.perf_counter() - t0) / 1e9,
+                    "d2h_bytes_per_step": int(d2h_full),
+                    "call": "npge_anchor_find (fragment arrays seq / min_pos / ori out)"}
     del pinned, pinned_np
 
     # ---- the north-star configuration under the same clock ---------------------
@@ -583,8 +594,8 @@ def run_gpu(args, rank, world, local_rank):
         "e2e": {"value": n_total * e2e_steps / e2e_t / 1e9, "unit": UNIT,
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": int(d2h),
                 "steps": e2e_steps,
-                "call": "npge_anchor_find (pinned ASCII bases in, fragment "
-                        "arrays out, pinned)",
+                "call": runner.e2e_call,
+                "full_layout": e2e_full,
                 "default_mode": {
                     "value": n_total * e2e_steps / e2e_default_t / 1e9,
                     "d2h_bytes_per_step": int(d2h_default)}},
@@ -630,9 +641,16 @@ class SingleRunner:
     def close(self):
         pass
 
-    def find_host(self, bases, offsets, k, similar, max_frags):
-        r = self.eng.find_counts((bases, offsets), k, similar=similar,
-                                 max_frags=max_frags)
+    e2e_call = ("npge_anchor_find_compact (pinned ASCII bases in; blocks + 4-byte "
+                "(position, strand) fragments + layout table out, pinned)")
+
+    def find_host(self, bases, offsets, k, similar, max_frags, full=False):
+        if full:  # the 9-bytes-per-fragment arrays of npge_anchor_find
+            r = self.eng.find_counts((bases, offsets), k, similar=similar,
+                                     max_frags=max_frags)
+        else:
+            r = self.eng.find_compact((bases, offsets), k, similar=similar,
+                                      max_frags=max_frags, counts=True)
         return r["result_bytes"]
 
     def ncu_traffic(self, n_windows):
@@ -672,7 +690,10 @@ class DistRunner(SingleRunner):
     def finish(self, st):
         return self._job(self.f.job_stats()) if st is self.f._last else self._job(st)
 
-    def find_host(self, bases, offsets, k, similar, max_frags):
+    e2e_call = ("DistAnchorFinder.find (pinned ASCII bases in, every rank's slice of the "
+                "fragment arrays out, pinned)")
+
+    def find_host(self, bases, offsets, k, similar, max_frags, full=True):
         st = self.f.find_counts((bases, offsets), k, similar=similar,
                                 max_frags=max_frags)
         return st["result_bytes"]

@@ -79,6 +79,46 @@ typedef struct {
     void* owner_;                  /* private */
 } npge_anchor_result;
 
+/* The compact result layout: 4 bytes per fragment instead of 9 on the device and over
+ * PCIe (the bus is the slowest link of the host-buffer call at parity-mode sizes).  A
+ * fragment is frag_pos_ori = (position in the scan-order LAYOUT << 1) | (ori == +1);
+ * the layout is the sequences with size >= anchor_size in scan order (size descending,
+ * ties by caller index, SeqBase::make_seqs), one pad position after each:
+ * sequence layout_seq[i] (the caller's index) occupies positions
+ * [layout_start[i], layout_start[i + 1] - 1).  npge_decode_compact() below maps a
+ * fragment to (seq, min_pos, ori); a caller that builds Fragment objects anyway (the
+ * Processor shim) does it while it builds them.  Blocks, hashes, new_used and digest
+ * are those of npge_anchor_result. */
+enum { NPGE_ANCHOR_LAYOUT_FULL = 0, NPGE_ANCHOR_LAYOUT_COMPACT = 1 };
+typedef struct {
+    uint64_t n_blocks, n_fragments;
+    const uint64_t* block_offsets; /* [n_blocks+1] into frag_pos_ori */
+    const uint64_t* block_hash;    /* [n_blocks] */
+    const uint32_t* frag_pos_ori;  /* [n_fragments] */
+    uint32_t n_layout;
+    int32_t anchor_size;           /* max_pos = min_pos + anchor_size - 1 */
+    const uint64_t* layout_start;  /* [n_layout+1] */
+    const uint32_t* layout_seq;    /* [n_layout] */
+    uint64_t n_new_used;
+    const uint64_t* new_used;
+    uint64_t digest[2];
+    void* owner_;
+} npge_anchor_compact_result;
+
+/* (seq, min_pos, ori) of fragment f of a compact result */
+static inline void npge_decode_compact(const npge_anchor_compact_result* r, uint64_t f,
+                                       uint32_t* seq, uint32_t* min_pos, int* ori) {
+    const uint64_t g = r->frag_pos_ori[f] >> 1;
+    uint32_t lo = 0, hi = r->n_layout; /* last i with layout_start[i] <= g */
+    while (hi - lo > 1) {
+        const uint32_t mid = (lo + hi) / 2;
+        if (r->layout_start[mid] <= g) lo = mid; else hi = mid;
+    }
+    *seq = r->layout_seq[lo];
+    *min_pos = (uint32_t)(g - r->layout_start[lo]);
+    *ori = (r->frag_pos_ori[f] & 1) ? 1 : -1;
+}
+
 /* Counters and device timings of the last find; always available, also when
  * the result itself stays on the device. */
 typedef struct {
@@ -141,6 +181,18 @@ int npge_anchor_find_device(npge_anchor_ctx* ctx, const npge_anchor_params* p,
                             const uint64_t* used_sorted, uint64_t n_used,
                             npge_anchor_stats* stats);
 int npge_anchor_fetch(npge_anchor_ctx* ctx, npge_anchor_result* out);
+/* The compact layout.  set_result_layout(COMPACT) makes the following find_device calls
+ * write payloads only (npge_anchor_fetch still works: it expands them on the host;
+ * npge_anchor_block_hashes on the resident result does not); fetch_compact returns
+ * them as they are; find_compact = upload + find_device + fetch_compact with host
+ * buffers in, whatever the context's layout.  Single-GPU contexts only. */
+int npge_anchor_set_result_layout(npge_anchor_ctx* ctx, int32_t layout);
+int npge_anchor_fetch_compact(npge_anchor_ctx* ctx, npge_anchor_compact_result* out);
+int npge_anchor_find_compact(npge_anchor_ctx* ctx, const npge_anchor_params* p,
+                             const uint8_t* bases, const uint64_t* seq_offsets,
+                             uint32_t n_seqs, const uint64_t* used_sorted, uint64_t n_used,
+                             npge_anchor_compact_result* out);
+void npge_anchor_compact_result_free(npge_anchor_compact_result* out);
 int npge_anchor_get_stats(npge_anchor_ctx* ctx, npge_anchor_stats* stats);
 
 /* ---- several GPUs, one context per GPU -------------------------------

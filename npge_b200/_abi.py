@@ -24,6 +24,8 @@ EXPORTS = [
     "npge_anchor_upload_raw", "npge_anchor_dist_scatter_local",
     "npge_block_hashes", "npge_anchor_block_hashes", "npge_block_hashes_last_ms",
     "npge_anchor_debug_plan", "npge_fragment_find_device_noalloc",
+    "npge_anchor_set_result_layout", "npge_anchor_fetch_compact", "npge_anchor_find_compact",
+    "npge_anchor_compact_result_free",
     "npge_anchor_dist_peer_attach", "npge_anchor_dist_found_or", "npge_anchor_dist_found_swap",
     "npge_anchor_multi_create", "npge_anchor_multi_destroy", "npge_anchor_multi_devices",
     "npge_anchor_multi_find", "npge_anchor_multi_upload", "npge_anchor_multi_find_device",
@@ -32,6 +34,7 @@ EXPORTS = [
 IPC_BYTES = 128
 
 OK, ERR_PARAMS, ERR_CUDA, ERR_MEMORY, ERR_CAPACITY, ERR_INPUT, ERR_STATE = range(7)
+LAYOUT_FULL, LAYOUT_COMPACT = 0, 1
 
 
 class Params(C.Structure):
@@ -47,6 +50,20 @@ class Result(C.Structure):
         ("frag_seq", C.POINTER(C.c_uint32)),
         ("frag_min_pos", C.POINTER(C.c_uint32)),
         ("frag_ori", C.POINTER(C.c_int8)),
+        ("n_new_used", C.c_uint64), ("new_used", C.POINTER(C.c_uint64)),
+        ("digest", C.c_uint64 * 2), ("owner_", C.c_void_p),
+    ]
+
+
+class CompactResult(C.Structure):
+    _fields_ = [
+        ("n_blocks", C.c_uint64), ("n_fragments", C.c_uint64),
+        ("block_offsets", C.POINTER(C.c_uint64)),
+        ("block_hash", C.POINTER(C.c_uint64)),
+        ("frag_pos_ori", C.POINTER(C.c_uint32)),
+        ("n_layout", C.c_uint32), ("anchor_size", C.c_int32),
+        ("layout_start", C.POINTER(C.c_uint64)),
+        ("layout_seq", C.POINTER(C.c_uint32)),
         ("n_new_used", C.c_uint64), ("new_used", C.POINTER(C.c_uint64)),
         ("digest", C.c_uint64 * 2), ("owner_", C.c_void_p),
     ]
@@ -115,6 +132,16 @@ def load():
                                           C.c_uint64, C.POINTER(Stats)]
     L.npge_anchor_fetch.restype = C.c_int
     L.npge_anchor_fetch.argtypes = [ctx, C.POINTER(Result)]
+    L.npge_anchor_set_result_layout.restype = C.c_int
+    L.npge_anchor_set_result_layout.argtypes = [ctx, C.c_int32]
+    L.npge_anchor_fetch_compact.restype = C.c_int
+    L.npge_anchor_fetch_compact.argtypes = [ctx, C.POINTER(CompactResult)]
+    L.npge_anchor_find_compact.restype = C.c_int
+    L.npge_anchor_find_compact.argtypes = [ctx, C.POINTER(Params), C.c_void_p, C.c_void_p,
+                                           C.c_uint32, C.c_void_p, C.c_uint64,
+                                           C.POINTER(CompactResult)]
+    L.npge_anchor_compact_result_free.restype = None
+    L.npge_anchor_compact_result_free.argtypes = [C.POINTER(CompactResult)]
     L.npge_anchor_get_stats.restype = C.c_int
     L.npge_anchor_get_stats.argtypes = [ctx, C.POINTER(Stats)]
     L.npge_anchor_dist_upload_range.restype = C.c_int

@@ -550,10 +550,14 @@ int find_device_msd(npge_anchor_ctx* ctx, const npge_anchor_params* p,
     NPGE_TRY(ensure(ctx->counters, kCntWords * 4));
     NPGE_TRY(ensure(ctx->summary, summary_words * 8));
     NPGE_TRY(ensure(ctx->used, n_used * 8));
-    NPGE_TRY(ensure(ctx->r_seq, max_frags * 4));
-    NPGE_TRY(ensure(ctx->r_pos, max_frags * 4));
-    NPGE_TRY(ensure(ctx->r_ori, max_frags));
-    if (fetch_mode() != kFetchPlain) NPGE_TRY(ensure(ctx->r_pay, max_frags * 4));
+    const bool compact = ctx->layout == 1;  // payloads only (npge_anchor_set_result_layout)
+    const bool with_pay = compact || fetch_mode() != kFetchPlain;
+    if (!compact) {
+        NPGE_TRY(ensure(ctx->r_seq, max_frags * 4));
+        NPGE_TRY(ensure(ctx->r_pos, max_frags * 4));
+        NPGE_TRY(ensure(ctx->r_ori, max_frags));
+    }
+    if (with_pay) NPGE_TRY(ensure(ctx->r_pay, max_frags * 4));
     NPGE_TRY(ensure(ctx->r_block_off, (max_frags / 2 + 2) * 8));
     NPGE_TRY(ensure(ctx->r_block_hash, (max_frags / 2 + 2) * 8));
     if (similar) {
@@ -595,8 +599,12 @@ int find_device_msd(npge_anchor_ctx* ctx, const npge_anchor_params* p,
     }
     NPGE_CUDA(cudaEventRecord(ctx->ev[2], st));
     BucketArgs a = bucket_args(ctx, plan, mb, mb.rec[0], mb.hi[0], n_used, limit);
-    const bool with_pay = fetch_mode() != kFetchPlain;
     a.r_pay = with_pay ? ptr<uint32_t>(ctx->r_pay) : nullptr;
+    if (compact) {
+        a.r_seq = nullptr;
+        a.r_pos = nullptr;
+        a.r_ori = nullptr;
+    }
     launch_bucket(a, similar, np ? max_records : 0, st, &ctx->ev[4], &launches);
     NPGE_CUDA(cudaGetLastError());
     NPGE_CUDA(cudaEventRecord(ctx->ev[3], st));
@@ -636,10 +644,11 @@ int find_device_msd(npge_anchor_ctx* ctx, const npge_anchor_params* p,
     const double rec = plan.wide ? 12.0 : 8.0;
     s.bytes_moved = uint64_t(double(ctx->n_bases) * 0.75 +
                              double(s.n_windows) * rec * (similar ? 7.0 : 5.0)) +
-                    9 * s.n_fragments + 16 * s.n_blocks;
+                    (compact ? 4 : 9) * s.n_fragments + 16 * s.n_blocks;
     ctx->total_selected = summary[kSumFragments];
     ctx->plan = plan;
     ctx->have_pay = with_pay;
+    ctx->result_compact = compact;
     ctx->last_params = *p;
     NPGE_TRY(fix_cut_resident(ctx, limit));
     ctx->have_result = true;
@@ -732,7 +741,7 @@ int fix_cut_resident(npge_anchor_ctx* ctx, uint64_t limit) {
         return fail(NPGE_ANCHOR_ERR_CUDA, "internal: cut group is not the last block");
     }
     const uint64_t keep = limit - first;
-    struct Member { uint32_t seq; uint64_t pos2; uint32_t pos; int8_t ori; };
+    struct Member { uint32_t seq; uint64_t pos2; uint32_t pos; int8_t ori; uint32_t pay; };
     auto member = [&](uint32_t i) {
         const uint32_t pw = uint32_t(rec[i]);
         const uint64_t g = pw >> 1;
@@ -744,7 +753,7 @@ int fix_cut_resident(npge_anchor_ctx* ctx, uint64_t limit) {
         const SeqEntry& e = ctx->gseqs[a];
         const uint32_t pos = uint32_t(g - e.start);
         const bool direct = pw & 1;
-        return Member{e.caller_index, direct ? pos : pos + e.size, pos, int8_t(direct ? 1 : -1)};
+        return Member{e.caller_index, direct ? pos : pos + e.size, pos, int8_t(direct ? 1 : -1), pw};
     };
     auto term = [&](const Member& m, uint64_t& d0, uint64_t& d1, bool add) {
         const uint64_t t = (uint64_t(m.seq) << 33) | (uint64_t(m.pos) << 1) | (m.ori == 1 ? 1 : 0);
@@ -767,20 +776,27 @@ int fix_cut_resident(npge_anchor_ctx* ctx, uint64_t limit) {
         st.n_blocks -= 1;      // r_block_off[n_blocks] == first == the new fragment count
         st.n_fragments -= 1;
     } else {
-        std::vector<uint32_t> q(keep), o(keep);
+        std::vector<uint32_t> q(keep), o(keep), y(keep);
         std::vector<int8_t> r(keep);
         for (uint64_t j = 0; j < keep; j++) {
             term(members[j], d0, d1, true);
             q[j] = members[j].seq;
             o[j] = members[j].pos;
             r[j] = members[j].ori;
+            y[j] = members[j].pay;
         }
-        NPGE_CUDA(cudaMemcpyAsync(ptr<uint32_t>(ctx->r_seq) + first, q.data(), keep * 4,
-                                  cudaMemcpyHostToDevice, s));
-        NPGE_CUDA(cudaMemcpyAsync(ptr<uint32_t>(ctx->r_pos) + first, o.data(), keep * 4,
-                                  cudaMemcpyHostToDevice, s));
-        NPGE_CUDA(cudaMemcpyAsync(ptr<int8_t>(ctx->r_ori) + first, r.data(), keep,
-                                  cudaMemcpyHostToDevice, s));
+        if (!ctx->result_compact) {
+            NPGE_CUDA(cudaMemcpyAsync(ptr<uint32_t>(ctx->r_seq) + first, q.data(), keep * 4,
+                                      cudaMemcpyHostToDevice, s));
+            NPGE_CUDA(cudaMemcpyAsync(ptr<uint32_t>(ctx->r_pos) + first, o.data(), keep * 4,
+                                      cudaMemcpyHostToDevice, s));
+            NPGE_CUDA(cudaMemcpyAsync(ptr<int8_t>(ctx->r_ori) + first, r.data(), keep,
+                                      cudaMemcpyHostToDevice, s));
+        }
+        if (ctx->have_pay) {
+            NPGE_CUDA(cudaMemcpyAsync(ptr<uint32_t>(ctx->r_pay) + first, y.data(), keep * 4,
+                                      cudaMemcpyHostToDevice, s));
+        }
         NPGE_CUDA(cudaStreamSynchronize(s));
     }
     st.digest[0] = d0;
@@ -854,8 +870,9 @@ constexpr uint64_t kFetchChunk = uint64_t(1) << 22;       // fragments per PCIe 
 constexpr uint64_t kFetchPiece = uint64_t(1) << 16;       // fragments per unit of host work
 
 bool fetch_compact_wanted(const npge_anchor_ctx* ctx, uint64_t nf, uint64_t limit) {
+    (void)limit;
+    if (ctx->result_compact) return true;  // there is nothing else to copy
     if (!ctx->have_pay || ctx->dist || nf == 0) return false;
-    if (ctx->total_selected > limit && limit > 0) return false;  // patched cut group: plain path
     const int mode = fetch_mode();
     if (mode == kFetchPlain) return false;
     if (mode == kFetchCompact) return true;
@@ -1012,6 +1029,129 @@ extern "C" int npge_anchor_fetch(npge_anchor_ctx* ctx, npge_anchor_result* out) 
     out->new_used = used_ptr;
     out->owner_ = r;
     return NPGE_ANCHOR_OK;
+}
+
+// ---- the compact result: 4 bytes per fragment over PCIe ----------------------------------
+namespace {
+
+struct CompactHost {
+    PinnedVector<uint64_t> block_offsets, block_hash;
+    PinnedVector<uint32_t> pos_ori;
+    std::vector<uint64_t> new_used, layout_start;
+    std::vector<uint32_t> layout_seq;
+};
+
+}  // namespace
+
+extern "C" int npge_anchor_set_result_layout(npge_anchor_ctx* ctx, int32_t layout) {
+    if (!ctx) return fail(NPGE_ANCHOR_ERR_PARAMS, "ctx is NULL");
+    if (layout != NPGE_ANCHOR_LAYOUT_FULL && layout != NPGE_ANCHOR_LAYOUT_COMPACT) {
+        return fail(NPGE_ANCHOR_ERR_PARAMS, "unknown result layout");
+    }
+    ctx->layout = layout;
+    return NPGE_ANCHOR_OK;
+}
+
+extern "C" int npge_anchor_fetch_compact(npge_anchor_ctx* ctx, npge_anchor_compact_result* out) {
+    if (!ctx || !out) return fail(NPGE_ANCHOR_ERR_PARAMS, "NULL argument");
+    memset(out, 0, sizeof(*out));
+    if (!ctx->have_result) {
+        return fail(NPGE_ANCHOR_ERR_STATE, "npge_anchor_find_device has not run");
+    }
+    if (!ctx->have_pay || ctx->dist) {
+        return fail(NPGE_ANCHOR_ERR_STATE,
+                    "the resident result holds no payloads: npge_anchor_set_result_layout("
+                    "NPGE_ANCHOR_LAYOUT_COMPACT) before npge_anchor_find_device");
+    }
+    NPGE_CUDA(cudaSetDevice(ctx->device));
+    CompactHost* r = new (std::nothrow) CompactHost;
+    if (!r) return fail(NPGE_ANCHOR_ERR_MEMORY, "out of host memory");
+    const uint64_t nf = ctx->stats.n_fragments, nb = ctx->stats.n_blocks;
+    try {
+        r->pos_ori.resize(nf);
+        r->block_offsets.resize(nb + 1);
+        r->block_hash.resize(nb);
+        r->layout_start.resize(ctx->seqs.size() + 1);
+        r->layout_seq.resize(ctx->seqs.size() + 1);
+    } catch (std::bad_alloc&) {
+        delete r;
+        return fail(NPGE_ANCHOR_ERR_MEMORY, "out of host memory for the result");
+    }
+    auto body = [&]() -> int {
+        cudaStream_t st = ctx->stream;
+        if (nf) {
+            NPGE_CUDA(cudaMemcpyAsync(r->pos_ori.data(), ctx->r_pay.ptr, nf * 4,
+                                      cudaMemcpyDeviceToHost, st));
+        }
+        NPGE_CUDA(cudaMemcpyAsync(r->block_offsets.data(), ctx->r_block_off.ptr, (nb + 1) * 8,
+                                  cudaMemcpyDeviceToHost, st));
+        if (nb) {
+            NPGE_CUDA(cudaMemcpyAsync(r->block_hash.data(), ctx->r_block_hash.ptr, nb * 8,
+                                      cudaMemcpyDeviceToHost, st));
+        }
+        // the layout while the copies run
+        uint64_t end = 0;
+        for (size_t i = 0; i < ctx->seqs.size(); i++) {
+            r->layout_start[i] = ctx->seqs[i].start;
+            r->layout_seq[i] = ctx->seqs[i].caller_index;
+            end = ctx->seqs[i].start + ctx->seqs[i].size + 1;
+        }
+        r->layout_start[ctx->seqs.size()] = end;
+        NPGE_CUDA(cudaStreamSynchronize(st));
+        return NPGE_ANCHOR_OK;
+    };
+    const int rc = body();
+    if (rc != NPGE_ANCHOR_OK) {
+        delete r;
+        return rc;
+    }
+    // used_hashes.push_back for every distinct hash of the list but the first
+    // (AnchorFinder.cpp:366-387); a lone cut tail still counts (:385)
+    if (ctx->lone_tail && nb) {
+        r->new_used.assign(r->block_hash.begin() + 1, r->block_hash.end());
+        r->new_used.push_back(ctx->lone_hash);
+        out->new_used = r->new_used.data();
+        out->n_new_used = r->new_used.size();
+    } else if (nb > 1) {
+        out->new_used = r->block_hash.data() + 1;  // the list IS the tail of block_hash
+        out->n_new_used = nb - 1;
+    }
+    out->n_blocks = nb;
+    out->n_fragments = nf;
+    out->block_offsets = r->block_offsets.data();
+    out->block_hash = r->block_hash.data();
+    out->frag_pos_ori = r->pos_ori.data();
+    out->n_layout = uint32_t(ctx->seqs.size());
+    out->layout_start = r->layout_start.data();
+    out->layout_seq = r->layout_seq.data();
+    out->anchor_size = ctx->last_params.anchor_size;
+    out->digest[0] = ctx->stats.digest[0];
+    out->digest[1] = ctx->stats.digest[1];
+    out->owner_ = r;
+    return NPGE_ANCHOR_OK;
+}
+
+extern "C" void npge_anchor_compact_result_free(npge_anchor_compact_result* out) {
+    if (!out) return;
+    delete static_cast<CompactHost*>(out->owner_);
+    memset(out, 0, sizeof(*out));
+}
+
+extern "C" int npge_anchor_find_compact(npge_anchor_ctx* ctx, const npge_anchor_params* p,
+                                        const uint8_t* bases, const uint64_t* seq_offsets,
+                                        uint32_t n_seqs, const uint64_t* used_sorted,
+                                        uint64_t n_used, npge_anchor_compact_result* out) {
+    if (!out) return fail(NPGE_ANCHOR_ERR_PARAMS, "out is NULL");
+    memset(out, 0, sizeof(*out));
+    if (!ctx) return fail(NPGE_ANCHOR_ERR_PARAMS, "ctx is NULL");
+    NPGE_TRY(check_params(p));
+    const int before = ctx->layout;
+    ctx->layout = NPGE_ANCHOR_LAYOUT_COMPACT;
+    int rc = npge_anchor_upload(ctx, p->anchor_size, bases, seq_offsets, n_seqs);
+    if (rc == NPGE_ANCHOR_OK) rc = npge_anchor_find_device(ctx, p, used_sorted, n_used, nullptr);
+    ctx->layout = before;
+    if (rc != NPGE_ANCHOR_OK) return rc;
+    return npge_anchor_fetch_compact(ctx, out);
 }
 
 extern "C" void npge_anchor_result_free(npge_anchor_result* out) {
@@ -1878,6 +2018,7 @@ extern "C" int npge_anchor_dist_emit(npge_anchor_ctx* ctx, const npge_anchor_par
                     9 * s.n_fragments + 16 * s.n_blocks;
     ctx->total_selected = summary[kSumFragments];
     ctx->have_pay = false;
+    ctx->result_compact = false;
     ctx->last_params = *p;
     ctx->last_params.max_anchor_fragments = int64_t(std::min<uint64_t>(local_limit, uint64_t(INT64_MAX)));
     NPGE_TRY(fix_cut_resident(ctx, local_limit));
@@ -2205,6 +2346,10 @@ extern "C" int npge_anchor_block_hashes(npge_anchor_ctx* ctx, const char* const*
     if (!ctx) return fail(NPGE_ANCHOR_ERR_PARAMS, "ctx is NULL");
     if (!ctx->have_result) {
         return fail(NPGE_ANCHOR_ERR_STATE, "npge_anchor_find_device has not run");
+    }
+    if (ctx->result_compact) {
+        return fail(NPGE_ANCHOR_ERR_STATE, "the resident result is compact (payloads only): "
+                    "find with NPGE_ANCHOR_LAYOUT_FULL, or hash fetched arrays with npge_block_hashes");
     }
     const uint32_t need = ctx->dist ? uint32_t(ctx->gseqs.size()) : ctx->n_caller_seqs;
     if (n_seqs < need) {

@@ -263,9 +263,11 @@ __device__ __forceinline__ void unit_write(BucketSmem<WIDE>& sm, const Chunk<WID
                 const uint64_t key = key_hi | ch.key(j + 1);
                 uint32_t seq, pos;
                 locate(a, pay >> 1, seq, pos);
-                a.r_seq[f] = seq;
-                a.r_pos[f] = pos;
-                a.r_ori[f] = (pay & 1) ? 1 : -1;
+                if (a.r_seq) {  // (nullptr: compact result layout, payloads only)
+                    a.r_seq[f] = seq;
+                    a.r_pos[f] = pos;
+                    a.r_ori[f] = (pay & 1) ? 1 : -1;
+                }
                 if (a.r_pay) a.r_pay[f] = pay;
                 const uint64_t t = (uint64_t(seq) << 33) | (uint64_t(pos) << 1) | (pay & 1);
                 uint64_t x, y;
@@ -932,9 +934,11 @@ bucket_emit_direct_kernel(BucketArgs a) {
                 const uint32_t f = fr + __popc(fb & lt);
                 if (f < limit) {
                     const uint64_t k64 = key_hi | uint64_t(key[i]);
-                    r_seq[f] = seq[i];
-                    r_pos[f] = pos[i] >> 1;
-                    r_ori[f] = int8_t(2 * int(pos[i] & 1) - 1);
+                    if (r_seq) {  // (nullptr: compact result layout, payloads only)
+                        r_seq[f] = seq[i];
+                        r_pos[f] = pos[i] >> 1;
+                        r_ori[f] = int8_t(2 * int(pos[i] & 1) - 1);
+                    }
                     if (r_pay) r_pay[f] = pay[i];
                     const uint64_t t = (uint64_t(seq[i]) << 33) | pos[i];
                     uint64_t x, y;

@@ -187,6 +187,8 @@ struct npge_anchor_ctx {
     // into (sequence, position, strand) while the next chunk crosses PCIe
     npge_b200::DeviceBuffer r_pay;
     bool have_pay = false;
+    int layout = 0;            // npge_anchor_set_result_layout: 0 full, 1 compact
+    bool result_compact = false;  // the resident result holds payloads only
     std::vector<uint32_t> h_start32, h_caller, h_lut;  // host copies of the position tables
     std::vector<cudaEvent_t> fetch_ev;
 

@@ -116,7 +116,7 @@ struct BucketArgs {
     uint64_t max_fragments;      // truncation M
     uint32_t* found_bits;        // anchor-similar: 1 bit per global position
     uint8_t* sel;                // anchor-similar: per record index of a group head
-    uint32_t* r_seq;
+    uint32_t* r_seq;             // nullptr (with r_pos, r_ori): compact layout, only r_pay
     uint32_t* r_pos;
     int8_t* r_ori;
     uint32_t* r_pay;             // optional: payload (position << 1 | strand) per fragment

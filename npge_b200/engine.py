@@ -73,6 +73,37 @@ class AnchorResult:
         return sorted(out)
 
 
+class CompactAnchorResult(AnchorResult):
+    """A compact result (npge_anchor_compact_result) decoded into the arrays of
+    AnchorResult with the layout table, as npge_decode_compact does."""
+
+    def __init__(self, r):
+        nb, nf, nu, nl = int(r.n_blocks), int(r.n_fragments), int(r.n_new_used), int(r.n_layout)
+
+        def arr(p, n, dtype):
+            if n == 0:
+                return np.zeros(0, dtype)
+            return np.ctypeslib.as_array(p, (n,)).astype(dtype, copy=True)
+
+        self.block_offsets = (arr(r.block_offsets, nb + 1, np.uint64)
+                              if r.block_offsets else np.zeros(1, np.uint64))
+        self.block_hash = arr(r.block_hash, nb, np.uint64)
+        self.frag_pos_ori = arr(r.frag_pos_ori, nf, np.uint32)
+        self.layout_start = arr(r.layout_start, nl + 1, np.uint64)
+        self.layout_seq = arr(r.layout_seq, nl, np.uint32)
+        self.new_used = arr(r.new_used, nu, np.uint64)
+        self.digest = (int(r.digest[0]), int(r.digest[1]))
+        g = (self.frag_pos_ori >> np.uint32(1)).astype(np.uint64)
+        if nf:
+            i = np.searchsorted(self.layout_start, g, side="right") - 1
+            self.frag_seq = self.layout_seq[i].astype(np.uint32)
+            self.frag_min_pos = (g - self.layout_start[i]).astype(np.uint32)
+        else:
+            self.frag_seq = np.zeros(0, np.uint32)
+            self.frag_min_pos = np.zeros(0, np.uint32)
+        self.frag_ori = np.where(self.frag_pos_ori & np.uint32(1), 1, -1).astype(np.int8)
+
+
 def _stats_dict(s):
     d = {name: getattr(s, name) for name, _ in s._fields_
          if name not in ("digest", "ms_pass")}
@@ -128,6 +159,37 @@ class AnchorEngine:
             return AnchorResult(r)
         finally:
             self._lib.npge_anchor_result_free(C.byref(r))
+
+    def set_result_layout(self, layout):
+        self._check(self._lib.npge_anchor_set_result_layout(self._ctx, layout))
+
+    def fetch_compact(self):
+        r = _abi.CompactResult()
+        self._check(self._lib.npge_anchor_fetch_compact(self._ctx, C.byref(r)))
+        try:
+            return CompactAnchorResult(r)
+        finally:
+            self._lib.npge_anchor_compact_result_free(C.byref(r))
+
+    def find_compact(self, seqs, k, similar=True, max_frags=100000, used=None, counts=False):
+        """npge_anchor_find_compact with host buffers: the drop-in call with the
+        4-bytes-per-fragment result.  counts=True keeps only the sizes (benchmarks)."""
+        bases, offsets = seqs if isinstance(seqs, tuple) else concat(seqs)
+        u, up = self._used(used)
+        p = _abi.Params(k, int(bool(similar)), int(max_frags))
+        r = _abi.CompactResult()
+        self._check(self._lib.npge_anchor_find_compact(
+            self._ctx, C.byref(p), bases.ctypes.data, offsets.ctypes.data,
+            len(offsets) - 1, up, len(u), C.byref(r)))
+        try:
+            if counts:
+                nb, nf = int(r.n_blocks), int(r.n_fragments)
+                return {"n_blocks": nb, "n_fragments": nf,
+                        "result_bytes": nf * 4 + (nb + 1) * 8 + nb * 8,
+                        "digest": (int(r.digest[0]), int(r.digest[1]))}
+            return CompactAnchorResult(r)
+        finally:
+            self._lib.npge_anchor_compact_result_free(C.byref(r))
 
     def find_counts(self, seqs, k, similar=True, max_frags=100000, used=None):
         """npge_anchor_find, but only the sizes are kept: the host arrays the

@@ -196,19 +196,45 @@ void AnchorFinder::run_impl() const {
         st.up_k = params.anchor_size;
         st.resident = true;
     }
-    npge_anchor_result r;
-    if (many) {
-        check(npge_anchor_multi_find_device(st.multi, &params, st.used_hashes.data(),
-                                            st.used_hashes.size(), nullptr),
-              "npge_anchor_multi_find_device");
-        check(npge_anchor_multi_fetch(st.multi, &r), "npge_anchor_multi_fetch");
-    } else {
+    const size_t k = size_t(params.anchor_size);
+    if (!many) {
+        // one GPU: the compact result (4 bytes per fragment over PCIe); every fragment is
+        // decoded while its Fragment object is built
+        check(npge_anchor_set_result_layout(st.ctx, NPGE_ANCHOR_LAYOUT_COMPACT),
+              "npge_anchor_set_result_layout");
         check(npge_anchor_find_device(st.ctx, &params, st.used_hashes.data(),
                                       st.used_hashes.size(), nullptr),
               "npge_anchor_find_device");
-        check(npge_anchor_fetch(st.ctx, &r), "npge_anchor_fetch");
+        npge_anchor_compact_result c;
+        check(npge_anchor_fetch_compact(st.ctx, &c), "npge_anchor_fetch_compact");
+        try {
+            for (uint64_t b = 0; b < c.n_blocks; b++) {
+                Block* block = new Block;
+                for (uint64_t f = c.block_offsets[b]; f < c.block_offsets[b + 1]; f++) {
+                    uint32_t seq, min_pos;
+                    int ori;
+                    npge_decode_compact(&c, f, &seq, &min_pos, &ori);
+                    block->insert(new Fragment(seqs[seq].get(), min_pos, min_pos + k - 1, ori));
+                }
+                bs.insert(block);  // the blockset owns it from here on
+                check_block(block);
+            }
+            st.used_hashes.insert(st.used_hashes.end(), c.new_used, c.new_used + c.n_new_used);
+            std::sort(st.used_hashes.begin(), st.used_hashes.end());
+            st.used_hashes.erase(std::unique(st.used_hashes.begin(), st.used_hashes.end()),
+                                 st.used_hashes.end());
+        } catch (...) {
+            npge_anchor_compact_result_free(&c);
+            throw;
+        }
+        npge_anchor_compact_result_free(&c);
+        return;
     }
-    const size_t k = size_t(params.anchor_size);
+    npge_anchor_result r;
+    check(npge_anchor_multi_find_device(st.multi, &params, st.used_hashes.data(),
+                                        st.used_hashes.size(), nullptr),
+          "npge_anchor_multi_find_device");
+    check(npge_anchor_multi_fetch(st.multi, &r), "npge_anchor_multi_fetch");
     try {
         for (uint64_t b = 0; b < r.n_blocks; b++) {
             Block* block = new Block;
@@ -226,10 +252,10 @@ void AnchorFinder::run_impl() const {
         st.used_hashes.erase(std::unique(st.used_hashes.begin(), st.used_hashes.end()),
                              st.used_hashes.end());
     } catch (...) {
-        if (many) npge_anchor_multi_result_free(&r); else npge_anchor_result_free(&r);
+        npge_anchor_multi_result_free(&r);
         throw;
     }
-    if (many) npge_anchor_multi_result_free(&r); else npge_anchor_result_free(&r);
+    npge_anchor_multi_result_free(&r);
 }
 
 const char* AnchorFinder::name_impl() const {
