@@ -484,6 +484,12 @@ def run_gpu(args, rank, world, local_rank):
         d2h = runner.find_host(pinned_np, offsets, K, False, BIG)
     barrier()
     e2e_t = max_over_ranks(time.perf_counter() - t0, world, dist, torch)
+    e2e_parity = None
+    if world == 1:  # the host-buffer call's own result against the golden digest
+        h = runner.last_host
+        e2e_parity = check_parity(job_name, K, "parity", {
+            "n_fragments_global": h["n_fragments"], "n_blocks_global": h["n_blocks"],
+            "digest": h["digest"]})["digest_equal"]
     h2d = int(bases.nbytes + offsets.nbytes)
     if world > 1:  # job totals of the copies and of the launches
         t = torch.tensor([h2d, int(d2h), kern_launches], dtype=torch.int64, device="cuda")
@@ -594,7 +600,7 @@ def run_gpu(args, rank, world, local_rank):
         "e2e": {"value": n_total * e2e_steps / e2e_t / 1e9, "unit": UNIT,
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": int(d2h),
                 "steps": e2e_steps,
-                "call": runner.e2e_call,
+                "call": runner.e2e_call, "digest_equal": e2e_parity,
                 "full_layout": e2e_full,
                 "default_mode": {
                     "value": n_total * e2e_steps / e2e_default_t / 1e9,
@@ -611,6 +617,8 @@ def run_gpu(args, rank, world, local_rank):
     emit(line)
     bad = [p for p in (parity, parity_default, (c5 or {}).get("parity"))
            if p and p.get("digest_equal") is False]
+    if e2e_parity is False:
+        bad.append({"e2e": "digest of the host-buffer call differs"})
     if bad or (c5 and c5.get("default_mode", {}).get("digest_equal") is False):
         sys.stderr.write("bench.py: PARITY FAILURE against tests/golden/digests.json: %s\n"
                          % json.dumps(bad))
@@ -651,6 +659,7 @@ class SingleRunner:
         else:
             r = self.eng.find_compact((bases, offsets), k, similar=similar,
                                       max_frags=max_frags, counts=True)
+        self.last_host = r  # counts + digest of the host-buffer call's own result
         return r["result_bytes"]
 
     def ncu_traffic(self, n_windows):

@@ -266,6 +266,8 @@ extern "C" void npge_anchor_destroy(npge_anchor_ctx* ctx) {
     for (auto& ev : ctx->fetch_ev) if (ev) cudaEventDestroy(ev);
     for (auto& ev : ctx->copy_events) if (ev) cudaEventDestroy(ev);
     for (auto& ev : ctx->chunk_events) if (ev) cudaEventDestroy(ev);
+    if (ctx->fetch_stream) cudaStreamDestroy(ctx->fetch_stream);
+    if (ctx->pipe_carry) cudaFreeHost(ctx->pipe_carry);
     for (auto& cs : ctx->copy_streams) if (cs) cudaStreamDestroy(cs);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -517,6 +519,9 @@ BucketArgs bucket_args(npge_anchor_ctx* ctx, const MsdPlan& plan, const MsdBuffe
 
 int fix_cut_resident(npge_anchor_ctx* ctx, uint64_t limit);
 
+constexpr int kPipeRanges = 8;                           // unit ranges of the pipelined call
+constexpr uint64_t kPipeMaxRecords = uint64_t(1) << 28;  // above: 3 GiB+ of pinned buffers
+
 int find_device_msd(npge_anchor_ctx* ctx, const npge_anchor_params* p,
                     const uint64_t* used_sorted, uint64_t n_used,
                     npge_anchor_stats* stats) {
@@ -605,8 +610,76 @@ int find_device_msd(npge_anchor_ctx* ctx, const npge_anchor_params* p,
         a.r_pos = nullptr;
         a.r_ori = nullptr;
     }
-    launch_bucket(a, similar, np ? max_records : 0, st, &ctx->ev[4], &launches);
-    NPGE_CUDA(cudaGetLastError());
+    // (no cut possible and no second sweep: the result of a unit range is final as soon
+    // as that range has been emitted)
+    const bool piped = ctx->pipe && compact && !similar && np && limit >= max_records &&
+                       max_records <= kPipeMaxRecords;
+    if (ctx->pipe) ctx->pipe->used = piped;
+    if (piped) {
+        launch_bucket_stage(a, kBucketUnits, max_records, st, &launches);
+        uint32_t n_units = 0;
+        NPGE_CUDA(cudaMemcpyAsync(&n_units, ptr<uint32_t>(ctx->counters) + kCntWindows, 4,
+                                  cudaMemcpyDeviceToHost, st));
+        NPGE_CUDA(cudaStreamSynchronize(st));
+        if (!ctx->fetch_stream) {
+            NPGE_CUDA(cudaStreamCreateWithFlags(&ctx->fetch_stream, cudaStreamNonBlocking));
+        }
+        if (!ctx->pipe_carry) {
+            NPGE_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&ctx->pipe_carry), kPipeRanges * 8,
+                                    cudaHostAllocDefault));
+        }
+        while (ctx->fetch_ev.size() < size_t(kPipeRanges)) {
+            cudaEvent_t ev = nullptr;
+            NPGE_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+            ctx->fetch_ev.push_back(ev);
+        }
+        const uint32_t per = (n_units + kPipeRanges - 1) / kPipeRanges;
+        int n_ranges = 0;
+        for (int c = 0; c < kPipeRanges; c++) {
+            const uint32_t u0 = uint32_t(c) * per, u1 = std::min(n_units, u0 + per);
+            if (u0 >= u1) break;
+            a.unit_first = u0;
+            a.unit_end = u1;
+            launch_bucket_stage(a, kBucketSort, max_records, st, &launches);
+            launch_bucket_stage(a, kBucketScan, max_records, st, &launches);
+            launch_bucket_stage(a, kBucketEmit, max_records, st, &launches);
+            NPGE_CUDA(cudaMemcpyAsync(&ctx->pipe_carry[c], ptr<uint64_t>(ctx->summary) + kSumCarry,
+                                      8, cudaMemcpyDeviceToHost, st));
+            NPGE_CUDA(cudaEventRecord(ctx->fetch_ev[c], st));
+            n_ranges++;
+        }
+        a.unit_first = 0;
+        a.unit_end = 0;
+        if (n_ranges == 0) launch_bucket_stage(a, kBucketScan, max_records, st, &launches);
+        NPGE_CUDA(cudaEventRecord(ctx->ev[4], st));
+        launch_bucket_stage(a, kBucketFinal, max_records, st, &launches);
+        NPGE_CUDA(cudaGetLastError());
+        // every finished range goes to the host while the next ones are sorted
+        uint64_t f0 = 0, b0 = 0;
+        for (int c = 0; c < n_ranges; c++) {
+            NPGE_CUDA(cudaEventSynchronize(ctx->fetch_ev[c]));
+            const uint64_t f1 = ctx->pipe_carry[c] & 0x7fffffffull, b1 = ctx->pipe_carry[c] >> 31;
+            cudaStream_t fs = ctx->fetch_stream;
+            if (f1 > f0) {
+                NPGE_CUDA(cudaMemcpyAsync(ctx->pipe->pos_ori + f0, ptr<uint32_t>(ctx->r_pay) + f0,
+                                          (f1 - f0) * 4, cudaMemcpyDeviceToHost, fs));
+            }
+            if (b1 > b0) {
+                NPGE_CUDA(cudaMemcpyAsync(ctx->pipe->block_off + b0,
+                                          ptr<uint64_t>(ctx->r_block_off) + b0, (b1 - b0) * 8,
+                                          cudaMemcpyDeviceToHost, fs));
+                NPGE_CUDA(cudaMemcpyAsync(ctx->pipe->block_hash + b0,
+                                          ptr<uint64_t>(ctx->r_block_hash) + b0, (b1 - b0) * 8,
+                                          cudaMemcpyDeviceToHost, fs));
+            }
+            f0 = f1;
+            b0 = b1;
+        }
+        ctx->pipe->block_off[b0] = f0;  // the closing offset
+    } else {
+        launch_bucket(a, similar, np ? max_records : 0, st, &ctx->ev[4], &launches);
+        NPGE_CUDA(cudaGetLastError());
+    }
     NPGE_CUDA(cudaEventRecord(ctx->ev[3], st));
     uint64_t summary[kSumWords];
     uint32_t counters_h[kCntWords];
@@ -1052,63 +1125,25 @@ extern "C" int npge_anchor_set_result_layout(npge_anchor_ctx* ctx, int32_t layou
     return NPGE_ANCHOR_OK;
 }
 
-extern "C" int npge_anchor_fetch_compact(npge_anchor_ctx* ctx, npge_anchor_compact_result* out) {
-    if (!ctx || !out) return fail(NPGE_ANCHOR_ERR_PARAMS, "NULL argument");
-    memset(out, 0, sizeof(*out));
-    if (!ctx->have_result) {
-        return fail(NPGE_ANCHOR_ERR_STATE, "npge_anchor_find_device has not run");
+namespace {
+
+// `r` holds the first nf fragments / nb blocks (+ closing offset): the layout table,
+// new_used and the fields of `out`
+void finish_compact(npge_anchor_ctx* ctx, CompactHost* r, uint64_t nf, uint64_t nb,
+                    npge_anchor_compact_result* out) {
+    r->layout_start.resize(ctx->seqs.size() + 1);
+    r->layout_seq.resize(ctx->seqs.size() + 1);
+    uint64_t end = 0;
+    for (size_t i = 0; i < ctx->seqs.size(); i++) {
+        r->layout_start[i] = ctx->seqs[i].start;
+        r->layout_seq[i] = ctx->seqs[i].caller_index;
+        end = ctx->seqs[i].start + ctx->seqs[i].size + 1;
     }
-    if (!ctx->have_pay || ctx->dist) {
-        return fail(NPGE_ANCHOR_ERR_STATE,
-                    "the resident result holds no payloads: npge_anchor_set_result_layout("
-                    "NPGE_ANCHOR_LAYOUT_COMPACT) before npge_anchor_find_device");
-    }
-    NPGE_CUDA(cudaSetDevice(ctx->device));
-    CompactHost* r = new (std::nothrow) CompactHost;
-    if (!r) return fail(NPGE_ANCHOR_ERR_MEMORY, "out of host memory");
-    const uint64_t nf = ctx->stats.n_fragments, nb = ctx->stats.n_blocks;
-    try {
-        r->pos_ori.resize(nf);
-        r->block_offsets.resize(nb + 1);
-        r->block_hash.resize(nb);
-        r->layout_start.resize(ctx->seqs.size() + 1);
-        r->layout_seq.resize(ctx->seqs.size() + 1);
-    } catch (std::bad_alloc&) {
-        delete r;
-        return fail(NPGE_ANCHOR_ERR_MEMORY, "out of host memory for the result");
-    }
-    auto body = [&]() -> int {
-        cudaStream_t st = ctx->stream;
-        if (nf) {
-            NPGE_CUDA(cudaMemcpyAsync(r->pos_ori.data(), ctx->r_pay.ptr, nf * 4,
-                                      cudaMemcpyDeviceToHost, st));
-        }
-        NPGE_CUDA(cudaMemcpyAsync(r->block_offsets.data(), ctx->r_block_off.ptr, (nb + 1) * 8,
-                                  cudaMemcpyDeviceToHost, st));
-        if (nb) {
-            NPGE_CUDA(cudaMemcpyAsync(r->block_hash.data(), ctx->r_block_hash.ptr, nb * 8,
-                                      cudaMemcpyDeviceToHost, st));
-        }
-        // the layout while the copies run
-        uint64_t end = 0;
-        for (size_t i = 0; i < ctx->seqs.size(); i++) {
-            r->layout_start[i] = ctx->seqs[i].start;
-            r->layout_seq[i] = ctx->seqs[i].caller_index;
-            end = ctx->seqs[i].start + ctx->seqs[i].size + 1;
-        }
-        r->layout_start[ctx->seqs.size()] = end;
-        NPGE_CUDA(cudaStreamSynchronize(st));
-        return NPGE_ANCHOR_OK;
-    };
-    const int rc = body();
-    if (rc != NPGE_ANCHOR_OK) {
-        delete r;
-        return rc;
-    }
+    r->layout_start[ctx->seqs.size()] = end;
     // used_hashes.push_back for every distinct hash of the list but the first
     // (AnchorFinder.cpp:366-387); a lone cut tail still counts (:385)
     if (ctx->lone_tail && nb) {
-        r->new_used.assign(r->block_hash.begin() + 1, r->block_hash.end());
+        r->new_used.assign(r->block_hash.data() + 1, r->block_hash.data() + nb);
         r->new_used.push_back(ctx->lone_hash);
         out->new_used = r->new_used.data();
         out->n_new_used = r->new_used.size();
@@ -1128,6 +1163,54 @@ extern "C" int npge_anchor_fetch_compact(npge_anchor_ctx* ctx, npge_anchor_compa
     out->digest[0] = ctx->stats.digest[0];
     out->digest[1] = ctx->stats.digest[1];
     out->owner_ = r;
+}
+
+}  // namespace
+
+extern "C" int npge_anchor_fetch_compact(npge_anchor_ctx* ctx, npge_anchor_compact_result* out) {
+    if (!ctx || !out) return fail(NPGE_ANCHOR_ERR_PARAMS, "NULL argument");
+    memset(out, 0, sizeof(*out));
+    if (!ctx->have_result) {
+        return fail(NPGE_ANCHOR_ERR_STATE, "npge_anchor_find_device has not run");
+    }
+    if (!ctx->have_pay || ctx->dist) {
+        return fail(NPGE_ANCHOR_ERR_STATE,
+                    "the resident result holds no payloads: npge_anchor_set_result_layout("
+                    "NPGE_ANCHOR_LAYOUT_COMPACT) before npge_anchor_find_device");
+    }
+    NPGE_CUDA(cudaSetDevice(ctx->device));
+    CompactHost* r = new (std::nothrow) CompactHost;
+    if (!r) return fail(NPGE_ANCHOR_ERR_MEMORY, "out of host memory");
+    const uint64_t nf = ctx->stats.n_fragments, nb = ctx->stats.n_blocks;
+    try {
+        r->pos_ori.resize(nf);
+        r->block_offsets.resize(nb + 1);
+        r->block_hash.resize(nb);
+    } catch (std::bad_alloc&) {
+        delete r;
+        return fail(NPGE_ANCHOR_ERR_MEMORY, "out of host memory for the result");
+    }
+    auto body = [&]() -> int {
+        cudaStream_t st = ctx->stream;
+        if (nf) {
+            NPGE_CUDA(cudaMemcpyAsync(r->pos_ori.data(), ctx->r_pay.ptr, nf * 4,
+                                      cudaMemcpyDeviceToHost, st));
+        }
+        NPGE_CUDA(cudaMemcpyAsync(r->block_offsets.data(), ctx->r_block_off.ptr, (nb + 1) * 8,
+                                  cudaMemcpyDeviceToHost, st));
+        if (nb) {
+            NPGE_CUDA(cudaMemcpyAsync(r->block_hash.data(), ctx->r_block_hash.ptr, nb * 8,
+                                      cudaMemcpyDeviceToHost, st));
+        }
+        NPGE_CUDA(cudaStreamSynchronize(st));
+        return NPGE_ANCHOR_OK;
+    };
+    const int rc = body();
+    if (rc != NPGE_ANCHOR_OK) {
+        delete r;
+        return rc;
+    }
+    finish_compact(ctx, r, nf, nb, out);
     return NPGE_ANCHOR_OK;
 }
 
@@ -1145,11 +1228,51 @@ extern "C" int npge_anchor_find_compact(npge_anchor_ctx* ctx, const npge_anchor_
     memset(out, 0, sizeof(*out));
     if (!ctx) return fail(NPGE_ANCHOR_ERR_PARAMS, "ctx is NULL");
     NPGE_TRY(check_params(p));
+    NPGE_TRY(npge_anchor_upload(ctx, p->anchor_size, bases, seq_offsets, n_seqs));
+    // Exact mode without a cut (the case with a result of the size of the input): host
+    // buffers for the largest possible result, filled range by range while the device is
+    // still sorting (find_device_msd).  Anything else: find, then fetch.
+    CompactHost* r = nullptr;
+    npge_anchor_ctx::FetchPipe pipe = {nullptr, nullptr, nullptr, false};
+    const uint64_t max_records = ctx->n_positions;
+    if (!p->anchor_similar && uint64_t(p->max_anchor_fragments) >= max_records &&
+        max_records > 0 && max_records <= kPipeMaxRecords) {
+        r = new (std::nothrow) CompactHost;
+        try {
+            if (r) {
+                r->pos_ori.resize(max_records);
+                r->block_offsets.resize(max_records / 2 + 2);
+                r->block_hash.resize(max_records / 2 + 2);
+                pipe.pos_ori = r->pos_ori.data();
+                pipe.block_off = r->block_offsets.data();
+                pipe.block_hash = r->block_hash.data();
+            }
+        } catch (std::bad_alloc&) {  // not enough pinned memory: the plain way
+            delete r;
+            r = nullptr;
+        }
+    }
     const int before = ctx->layout;
     ctx->layout = NPGE_ANCHOR_LAYOUT_COMPACT;
-    int rc = npge_anchor_upload(ctx, p->anchor_size, bases, seq_offsets, n_seqs);
-    if (rc == NPGE_ANCHOR_OK) rc = npge_anchor_find_device(ctx, p, used_sorted, n_used, nullptr);
+    ctx->pipe = r ? &pipe : nullptr;
+    int rc = npge_anchor_find_device(ctx, p, used_sorted, n_used, nullptr);
+    ctx->pipe = nullptr;
     ctx->layout = before;
+    if (rc == NPGE_ANCHOR_OK && r && pipe.used) {
+        cudaError_t e = cudaStreamSynchronize(ctx->fetch_stream);  // the last ranges
+        if (e != cudaSuccess) {
+            delete r;
+            return fail(NPGE_ANCHOR_ERR_CUDA, std::string("CUDA error: ") + cudaGetErrorString(e));
+        }
+        const uint64_t nf = ctx->stats.n_fragments, nb = ctx->stats.n_blocks;
+        r->pos_ori.resize(nf);
+        r->block_offsets.resize(nb + 1);
+        r->block_hash.resize(nb);
+        finish_compact(ctx, r, nf, nb, out);
+        return NPGE_ANCHOR_OK;
+    }
+    if (r && ctx->fetch_stream) cudaStreamSynchronize(ctx->fetch_stream);
+    delete r;
     if (rc != NPGE_ANCHOR_OK) return rc;
     return npge_anchor_fetch_compact(ctx, out);
 }

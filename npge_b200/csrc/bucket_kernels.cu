@@ -423,7 +423,7 @@ template <bool WIDE>
 __device__ __forceinline__ bool unit_of_window(BucketSmem<WIDE>& sm, const BucketArgs& a,
                                                uint32_t w, uint32_t& s, uint32_t& n,
                                                uint64_t& key_hi) {
-    if (w >= a.counters[kCntWindows]) return false;
+    if (w >= (a.unit_end ? a.unit_end : a.counters[kCntWindows])) return false;
     const uint4 u = a.units[w];
     if (threadIdx.x == 0) sm.cut = 0;
     __syncthreads();
@@ -651,7 +651,7 @@ __global__ void __launch_bounds__(kRT, 2)
 bucket_sort_kernel(BucketArgs a) {
     extern __shared__ __align__(16) unsigned char raw[];
     BucketSmem<WIDE>& sm = *reinterpret_cast<BucketSmem<WIDE>*>(raw);
-    const uint32_t w = blockIdx.x;
+    const uint32_t w = blockIdx.x + a.unit_first;
     uint32_t s, n;
     uint64_t key_hi;
     if (!unit_of_window<WIDE>(sm, a, w, s, n, key_hi)) return;
@@ -696,7 +696,7 @@ __global__ void __launch_bounds__(kRT, WIDE ? 2 : 3)
 bucket_count_kernel(BucketArgs a) {
     extern __shared__ __align__(16) unsigned char raw[];
     BucketSmem<WIDE>& sm = *reinterpret_cast<BucketSmem<WIDE>*>(raw);
-    const uint32_t w = blockIdx.x;
+    const uint32_t w = blockIdx.x + a.unit_first;
     uint32_t s, n;
     uint64_t key_hi;
     if (!unit_of_window<WIDE>(sm, a, w, s, n, key_hi)) return;
@@ -726,9 +726,15 @@ bucket_count_kernel(BucketArgs a) {
 __global__ void __launch_bounds__(1024)
 unit_scan_kernel(BucketArgs a) {
     __shared__ uint64_t part[1024];
-    const uint32_t n_win = a.counters[kCntWindows];
+    // units [u0, u1) (all of them by default), continuing at the carry of the ranges
+    // scanned before (0 after the memset of the summary)
+    const uint32_t u0 = a.unit_first;
+    const uint32_t u1 = a.unit_end ? a.unit_end : a.counters[kCntWindows];
+    const uint32_t n_win = u1 > u0 ? u1 - u0 : 0;
     const uint32_t per = (n_win + 1023) / 1024;
-    const uint32_t b = threadIdx.x * per, e = min(b + per, n_win);
+    const uint32_t b = min(u0 + threadIdx.x * per, u1), e = min(b + per, u1);
+    const uint64_t carry = a.summary[kSumCarry];
+    __syncthreads();  // everybody has read the carry before lane 31 of warp 0 replaces it
     uint64_t sum = 0;
     for (uint32_t i = b; i < e; i++) sum += a.unit_tot[i];
     // block-wide exclusive scan of the 1024 partial sums
@@ -751,12 +757,14 @@ unit_scan_kernel(BucketArgs a) {
         }
         part[32 + lane] = wi - v;  // sum of the warps before this one
         if (lane == 31) {
-            a.summary[kSumFragments] = wi & 0x7fffffffull;  // before truncation
-            a.summary[kSumBlocks] = wi >> 31;
+            const uint64_t all = carry + wi;
+            a.summary[kSumCarry] = all;
+            a.summary[kSumFragments] = all & 0x7fffffffull;  // before truncation
+            a.summary[kSumBlocks] = all >> 31;
         }
     }
     __syncthreads();
-    uint64_t run = part[32 + warp] + incl - sum;
+    uint64_t run = carry + part[32 + warp] + incl - sum;
     for (uint32_t i = b; i < e; i++) {
         uint64_t v = a.unit_tot[i];
         a.unit_tot[i] = run;
@@ -770,7 +778,7 @@ __global__ void __launch_bounds__(kRT, WIDE ? 2 : 3)
 bucket_emit_kernel(BucketArgs a) {
     extern __shared__ __align__(16) unsigned char raw[];
     BucketSmem<WIDE>& sm = *reinterpret_cast<BucketSmem<WIDE>*>(raw);
-    const uint32_t w = blockIdx.x;
+    const uint32_t w = blockIdx.x + a.unit_first;
     uint32_t s, n;
     uint64_t key_hi;
     if (!unit_of_window<WIDE>(sm, a, w, s, n, key_hi)) return;
@@ -821,8 +829,8 @@ __global__ void __launch_bounds__(kRT, NPGE_EMIT_CTAS)
 bucket_emit_direct_kernel(BucketArgs a) {
     __shared__ DirectSmem sm;
     typedef typename std::conditional<WIDE, uint64_t, uint32_t>::type key_t;
-    const uint32_t w = blockIdx.x;
-    if (w >= a.counters[kCntWindows]) return;
+    const uint32_t w = blockIdx.x + a.unit_first;
+    if (w >= (a.unit_end ? a.unit_end : a.counters[kCntWindows])) return;
     const uint4 u = a.units[w];
     const uint32_t s = u.x, n = u.y;
     const uint64_t key_hi = uint64_t(u.z) << a.plan.rem;
@@ -1064,7 +1072,8 @@ uint32_t bucket_max_windows(const MsdPlan& plan, uint64_t max_records) {
 //   kBucketFinal   digest, emitted counts, closing block offset
 void launch_bucket_stage(const BucketArgs& a, int stage, uint64_t max_records,
                          cudaStream_t s, uint32_t* launches) {
-    const uint32_t grid = bucket_max_windows(a.plan, max_records);
+    const uint32_t grid = a.unit_end ? (a.unit_end > a.unit_first ? a.unit_end - a.unit_first : 0u)
+                                     : bucket_max_windows(a.plan, max_records);
 #define NPGE_LAUNCH(KERNEL, BYTES)                                              \
     do {                                                                        \
         set_smem(KERNEL, BYTES);                                                \
@@ -1085,6 +1094,7 @@ void launch_bucket_stage(const BucketArgs& a, int stage, uint64_t max_records,
         return;
     }
     if (max_records == 0) return;
+    if (a.unit_end && grid == 0 && stage != kBucketScan && stage != kBucketUnits) return;
     switch (stage) {
     case kBucketUnits: {
         const uint32_t bins_a = 1u << a.plan.capa;

@@ -188,6 +188,18 @@ struct npge_anchor_ctx {
     npge_b200::DeviceBuffer r_pay;
     bool have_pay = false;
     int layout = 0;            // npge_anchor_set_result_layout: 0 full, 1 compact
+    // npge_anchor_find_compact, exact mode without a cut: the units are sorted and emitted
+    // range by range and every finished range is copied to these HOST buffers while the
+    // next one is sorted (api.cu: find_device_msd)
+    struct FetchPipe {
+        uint32_t* pos_ori;
+        uint64_t* block_off;
+        uint64_t* block_hash;
+        bool used;
+    };
+    FetchPipe* pipe = nullptr;
+    cudaStream_t fetch_stream = nullptr;
+    uint64_t* pipe_carry = nullptr;  // pinned: blocks << 31 | fragments after every range
     bool result_compact = false;  // the resident result holds payloads only
     std::vector<uint32_t> h_start32, h_caller, h_lut;  // host copies of the position tables
     std::vector<cudaEvent_t> fetch_ev;

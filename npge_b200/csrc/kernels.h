@@ -24,6 +24,7 @@ enum {
     kSumDigest1 = 3,
     kSumEmitted = 4,    // fragments actually written (after truncation)
     kSumBlocksEmitted = 5,
+    kSumCarry = 6,      // blocks << 31 | fragments of the unit ranges scanned so far
     kSumWords = 8
 };
 
@@ -122,6 +123,10 @@ struct BucketArgs {
     uint32_t* r_pay;             // optional: payload (position << 1 | strand) per fragment
     uint64_t* r_block_off;
     uint64_t* r_block_hash;
+    // units [unit_first, unit_end) of this launch (unit_end 0: all of them): the
+    // pipelined host-buffer call sorts and emits the units range by range, copying a
+    // finished range to the host while the next one is sorted
+    uint32_t unit_first, unit_end;
     uint64_t* unit_tot;          // per unit: blocks << 31 | fragments, then its prefix
     uint32_t* unit_wtot;         // per unit and warp of the sort CTA: blocks << 16 | fragments
     uint64_t* summary;
