@@ -149,6 +149,12 @@ void npge_anchor_destroy(npge_anchor_ctx* ctx);
  * the wide-row kernels are exercised on small inputs.  Results never depend on it. */
 int npge_anchor_debug_plan(npge_anchor_ctx* ctx, int32_t fine_bits, int32_t first_split);
 
+/* Test hook: every device buffer of the context ends in 256 guard bytes; this reads
+ * them back.  *n_damaged = buffers whose guard was overwritten (a kernel stored past the
+ * end of the buffer); npge_anchor_last_error() then names them.  (Stands in for
+ * compute-sanitizer memcheck, which is closed on the development pool.) */
+int npge_anchor_debug_check(npge_anchor_ctx* ctx, uint32_t* n_damaged);
+
 /* Thread-local text of the last error returned to this thread. */
 const char* npge_anchor_last_error(void);
 
@@ -362,6 +368,7 @@ int npge_anchor_multi_find_device(npge_anchor_multi* m, const npge_anchor_params
 int npge_anchor_multi_fetch(npge_anchor_multi* m, npge_anchor_result* out);
 void npge_anchor_multi_result_free(npge_anchor_result* out);
 int npge_anchor_multi_get_stats(npge_anchor_multi* m, int rank, npge_anchor_stats* stats);
+int npge_anchor_multi_debug_check(npge_anchor_multi* m, uint32_t* n_damaged); /* all ranks */
 
 /* ---- FragmentFinder (src/algo/FragmentFinder.cpp:42-171) ---------------------------
  * Every exact occurrence of `pattern` (ATGCN bytes, N matches only N) on either

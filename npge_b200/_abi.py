@@ -23,13 +23,14 @@ EXPORTS = [
     "npge_fragment_find", "npge_fragment_find_device", "npge_fragment_result_free",
     "npge_anchor_upload_raw", "npge_anchor_dist_scatter_local",
     "npge_block_hashes", "npge_anchor_block_hashes", "npge_block_hashes_last_ms",
-    "npge_anchor_debug_plan", "npge_fragment_find_device_noalloc",
+    "npge_anchor_debug_plan", "npge_anchor_debug_check", "npge_fragment_find_device_noalloc",
     "npge_anchor_set_result_layout", "npge_anchor_fetch_compact", "npge_anchor_find_compact",
     "npge_anchor_compact_result_free",
     "npge_anchor_dist_peer_attach", "npge_anchor_dist_found_or", "npge_anchor_dist_found_swap",
     "npge_anchor_multi_create", "npge_anchor_multi_destroy", "npge_anchor_multi_devices",
     "npge_anchor_multi_find", "npge_anchor_multi_upload", "npge_anchor_multi_find_device",
     "npge_anchor_multi_fetch", "npge_anchor_multi_result_free", "npge_anchor_multi_get_stats",
+    "npge_anchor_multi_debug_check",
 ]
 IPC_BYTES = 128
 
@@ -142,6 +143,8 @@ def load():
                                            C.POINTER(CompactResult)]
     L.npge_anchor_compact_result_free.restype = None
     L.npge_anchor_compact_result_free.argtypes = [C.POINTER(CompactResult)]
+    L.npge_anchor_debug_check.restype = C.c_int
+    L.npge_anchor_debug_check.argtypes = [ctx, C.POINTER(C.c_uint32)]
     L.npge_anchor_get_stats.restype = C.c_int
     L.npge_anchor_get_stats.argtypes = [ctx, C.POINTER(Stats)]
     L.npge_anchor_dist_upload_range.restype = C.c_int
@@ -229,5 +232,7 @@ def load():
     L.npge_anchor_multi_result_free.argtypes = [C.POINTER(Result)]
     L.npge_anchor_multi_get_stats.restype = C.c_int
     L.npge_anchor_multi_get_stats.argtypes = [ctx, C.c_int, C.POINTER(Stats)]
+    L.npge_anchor_multi_debug_check.restype = C.c_int
+    L.npge_anchor_multi_debug_check.argtypes = [ctx, C.POINTER(C.c_uint32)]
     _lib = L
     return L

@@ -47,6 +47,11 @@ namespace {
         }                                                                      \
     } while (0)
 
+// Every device buffer ends in kCanary bytes of 0xA5 past its usable size:
+// npge_anchor_debug_check reads them back (compute-sanitizer is closed on the pool this
+// was developed on; an out-of-bounds store past the end of a buffer lands here first).
+constexpr size_t kCanary = 256;
+
 int ensure(DeviceBuffer& b, size_t bytes) {
     if (bytes == 0) bytes = 256;
     if (b.bytes >= bytes) return NPGE_ANCHOR_OK;
@@ -56,17 +61,25 @@ int ensure(DeviceBuffer& b, size_t bytes) {
         b.bytes = 0;
     }
     // grow with some headroom so repeated runs on slightly larger inputs reuse
-    size_t want = bytes + bytes / 16 + 256;
-    cudaError_t e = cudaMalloc(&b.ptr, want);
+    size_t want = (bytes + bytes / 16 + 256 + 255) / 256 * 256;
+    cudaError_t e = cudaMalloc(&b.ptr, want + kCanary);
     if (e != cudaSuccess) {
         cudaGetLastError();
-        e = cudaMalloc(&b.ptr, bytes);
-        want = bytes;
+        want = (bytes + 255) / 256 * 256;
+        e = cudaMalloc(&b.ptr, want + kCanary);
     }
     if (e != cudaSuccess) {
         cudaGetLastError();
         return fail(NPGE_ANCHOR_ERR_MEMORY,
                     "device allocation of " + std::to_string(bytes) + " bytes failed");
+    }
+    // (cudaMalloc has synchronised the device; nothing uses the new buffer yet)
+    if (cudaMemset(static_cast<uint8_t*>(b.ptr) + want, 0xA5, kCanary) != cudaSuccess ||
+        cudaDeviceSynchronize() != cudaSuccess) {
+        cudaGetLastError();
+        cudaFree(b.ptr);
+        b.ptr = nullptr;
+        return fail(NPGE_ANCHOR_ERR_CUDA, "could not initialise a device buffer");
     }
     b.bytes = want;
     return NPGE_ANCHOR_OK;
@@ -242,11 +255,10 @@ extern "C" int npge_anchor_create(npge_anchor_ctx** out, int device) {
     return NPGE_ANCHOR_OK;
 }
 
-extern "C" void npge_anchor_destroy(npge_anchor_ctx* ctx) {
-    if (!ctx) return;
-    cudaSetDevice(ctx->device);
-    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
-    DeviceBuffer* all[] = {&ctx->ascii, &ctx->packed, &ctx->nmask, &ctx->seq_start,
+namespace {
+
+std::vector<DeviceBuffer*> all_buffers(npge_anchor_ctx* ctx) {
+    return {&ctx->ascii, &ctx->packed, &ctx->nmask, &ctx->seq_start,
                            &ctx->seq_caller, &ctx->seq_pair, &ctx->g_seq_pair, &ctx->counters, &ctx->used,
                            &ctx->found_bits, &ctx->found_tmp, &ctx->sel,
                            &ctx->r_seq, &ctx->r_pos, &ctx->r_ori,
@@ -259,6 +271,42 @@ extern "C" void npge_anchor_destroy(npge_anchor_ctx* ctx) {
                            &ctx->peer_tab, &ctx->frag_pat, &ctx->frag_tiles, &ctx->frag_out,
                            &ctx->raw, &ctx->ingest, &ctx->bh_in, &ctx->bh_names,
                            &ctx->bh_scratch, &ctx->bh_out, &ctx->r_pay};
+}
+
+}  // namespace
+
+// Reads back the guard bytes behind every device buffer of the context (after waiting for
+// its stream).  *n_damaged = buffers whose guard was overwritten, i.e. some kernel stored
+// past the end of that buffer; the last-error text names them.
+extern "C" int npge_anchor_debug_check(npge_anchor_ctx* ctx, uint32_t* n_damaged) {
+    if (!ctx || !n_damaged) return fail(NPGE_ANCHOR_ERR_PARAMS, "NULL argument");
+    *n_damaged = 0;
+    NPGE_CUDA(cudaSetDevice(ctx->device));
+    NPGE_CUDA(cudaStreamSynchronize(ctx->stream));
+    std::vector<DeviceBuffer*> all = all_buffers(ctx);
+    std::string which;
+    uint8_t tail[kCanary];
+    for (size_t i = 0; i < all.size(); i++) {
+        if (!all[i]->ptr) continue;
+        NPGE_CUDA(cudaMemcpy(tail, static_cast<uint8_t*>(all[i]->ptr) + all[i]->bytes, kCanary,
+                             cudaMemcpyDeviceToHost));
+        for (size_t j = 0; j < kCanary; j++) {
+            if (tail[j] != 0xA5) {
+                *n_damaged += 1;
+                which += " #" + std::to_string(i) + "@+" + std::to_string(j);
+                break;
+            }
+        }
+    }
+    if (*n_damaged) g_last_error = "guard bytes overwritten behind buffer(s)" + which;
+    return NPGE_ANCHOR_OK;
+}
+
+extern "C" void npge_anchor_destroy(npge_anchor_ctx* ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    std::vector<DeviceBuffer*> all = all_buffers(ctx);
     for (void* q : ctx->peer_opened) cudaIpcCloseMemHandle(q);
     for (DeviceBuffer* b : all) release(*b);
     for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);

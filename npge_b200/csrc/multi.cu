@@ -449,3 +449,16 @@ extern "C" int npge_anchor_multi_get_stats(npge_anchor_multi* m, int rank,
     }
     return NPGE_ANCHOR_OK;
 }
+
+// Guard bytes of every rank's device buffers (npge_anchor_debug_check), summed.
+extern "C" int npge_anchor_multi_debug_check(npge_anchor_multi* m, uint32_t* n_damaged) {
+    if (!m || !n_damaged) return fail(NPGE_ANCHOR_ERR_PARAMS, "NULL argument");
+    *n_damaged = 0;
+    for (npge_anchor_ctx* c : m->ctx) {
+        uint32_t n = 0;
+        const int rc = npge_anchor_debug_check(c, &n);
+        if (rc) return rc;
+        *n_damaged += n;
+    }
+    return NPGE_ANCHOR_OK;
+}

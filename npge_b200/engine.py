@@ -142,6 +142,15 @@ class AnchorEngine:
             used if used is not None else [], dtype=np.uint64)))
         return u, (u.ctypes.data if len(u) else None)
 
+    def debug_check(self):
+        """npge_anchor_debug_check: number of device buffers whose guard bytes were
+        overwritten (0 = no kernel stored past the end of a buffer)."""
+        n = C.c_uint32(0)
+        self._check(self._lib.npge_anchor_debug_check(self._ctx, C.byref(n)))
+        if n.value:
+            print(self._lib.npge_anchor_last_error().decode())
+        return int(n.value)
+
     def debug_plan(self, fine_bits=0, first_split=0):
         """Test hook (npge_anchor_debug_plan): force the digit plan of a larger job."""
         self._check(self._lib.npge_anchor_debug_plan(self._ctx, fine_bits, first_split))
@@ -405,6 +414,11 @@ class MultiEngine:
             return AnchorResult(r)
         finally:
             self._lib.npge_anchor_multi_result_free(C.byref(r))
+
+    def debug_check(self):
+        n = C.c_uint32(0)
+        self._check(self._lib.npge_anchor_multi_debug_check(self._m, C.byref(n)))
+        return int(n.value)
 
     def rank_stats(self, rank):
         s = _abi.Stats()

@@ -87,6 +87,8 @@ def main():
                 fails.append(tag + ": job counts differ")
         print("rank0", tag, "blocks", got.n_blocks, "frags", got.n_fragments,
               "cuts", got_local.job.get("bucket_cuts"), flush=True)
+    if mode == "cuda" and f.stages.debug_check() != 0:
+        fails.append("guard bytes behind a device buffer were overwritten")
     dist.barrier()
     dist.destroy_process_group()
     if fails:

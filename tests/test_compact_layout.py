@@ -17,6 +17,7 @@ BIG = 2 ** 62
 def eng():
     e = AnchorEngine(0)
     yield e
+    assert e.debug_check() == 0   # no kernel stored past the end of a device buffer
     e.close()
 
 

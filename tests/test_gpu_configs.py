@@ -24,6 +24,7 @@ MODES = {"parity": (False, BIG), "default": (True, 100000)}
 def eng():
     e = AnchorEngine(0)
     yield e
+    assert e.debug_check() == 0   # no kernel stored past the end of a device buffer
     e.close()
 
 

@@ -44,6 +44,7 @@ def eng():
     from npge_b200.engine import AnchorEngine
     e = AnchorEngine(0)
     yield e
+    assert e.debug_check() == 0   # no kernel stored past the end of a device buffer
     e.close()
 
 

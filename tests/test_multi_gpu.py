@@ -33,6 +33,7 @@ def test_multi_equals_oracle(ranks, k):
                                   (False, 777, None), (True, BIG, used), (False, 9, None)):
             got = m.find(seqs, k, similar=similar, max_frags=limit, used=u)
             same(got, oracle.find_ideal(seqs, k, similar=similar, max_frags=limit, used=u))
+        assert m.debug_check() == 0
     finally:
         m.close()
 
@@ -53,6 +54,7 @@ def test_one_chromosome_over_four_ranks():
         assert (st["n_fragments"], st["n_blocks"], st["digest"]) == (
             want.n_fragments, want.n_blocks, want.digest)
         assert sum(m.rank_stats(r)["n_fragments"] for r in range(4)) == want.n_fragments
+        assert m.debug_check() == 0
     finally:
         m.close()
 
@@ -70,5 +72,6 @@ def test_multi_c1_brucella3_two_ranks():
         assert np.array_equal(got.block_hash, want.block_hash)
         assert np.array_equal(got.block_offsets, want.block_offsets)
         assert np.array_equal(got.new_used, want.new_used)
+        assert m.debug_check() == 0
     finally:
         m.close()

@@ -202,6 +202,7 @@ def engine():
     from npge_b200.engine import AnchorEngine
     eng = AnchorEngine(0)
     yield eng
+    assert eng.debug_check() == 0   # no kernel stored past the end of a device buffer
     eng.close()
 
 

@@ -16,6 +16,7 @@ pytestmark = pytest.mark.gpu
 def eng():
     e = AnchorEngine(0)
     yield e
+    assert e.debug_check() == 0   # no kernel stored past the end of a device buffer
     e.close()
 
 

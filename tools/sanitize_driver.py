@@ -52,12 +52,14 @@ def main():
     n, _ = eng.find_fragments_device_noalloc(pat, 50, out[0].data_ptr(), out[1].data_ptr(),
                                              out[2].data_ptr(), 64)
     assert n == len(want)
+    assert eng.debug_check() == 0
     eng.close()
     for ranks in (2, 3):
         m = MultiEngine([0] * ranks)
         for k, similar, limit in ((16, False, BIG), (20, True, 100000), (27, False, 501)):
             same(m.find(seqs, k, similar=similar, max_frags=limit),
                  oracle.find_ideal(seqs, k, similar=similar, max_frags=limit))
+        assert m.debug_check() == 0
         m.close()
     print("driver ok")
 
