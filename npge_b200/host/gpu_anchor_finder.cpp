@@ -11,6 +11,7 @@
 #include "gpu_anchor_finder.hpp"
 
 #include <algorithm>
+#include <chrono>
 #include <cstdint>
 #include <string>
 #include <vector>
@@ -42,6 +43,7 @@ struct AnchorFinder::Impl {
     uint64_t up_probe = 0;
     int up_k = 0;
     bool resident = false, reused = false;
+    double ms[3] = {0, 0, 0};
     void drop() {
         if (ctx) npge_anchor_destroy(ctx);
         if (multi) npge_anchor_multi_destroy(multi);
@@ -102,6 +104,10 @@ bool AnchorFinder::last_run_reused_upload() const {
     return impl_->reused;
 }
 
+const double* AnchorFinder::last_run_ms() const {
+    return impl_->ms;
+}
+
 namespace {
 
 void check(int rc, const char* what) {
@@ -148,8 +154,14 @@ uint64_t probe_sequences(const std::vector<SequencePtr>& seqs) {
 
 }  // namespace
 
+static double wall_ms() {
+    return std::chrono::duration<double, std::milli>(
+               std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
 void AnchorFinder::run_impl() const {
     Impl& st = *impl_;
+    const double t_start = wall_ms();
     npge_anchor_params params;
     params.anchor_size = opt_value("anchor-size").as<int>();
     params.anchor_similar = opt_value("anchor-similar").as<bool>() ? 1 : 0;
@@ -197,6 +209,8 @@ void AnchorFinder::run_impl() const {
         st.resident = true;
     }
     const size_t k = size_t(params.anchor_size);
+    const double t_uploaded = wall_ms();
+    st.ms[0] = t_uploaded - t_start;
     if (!many) {
         // one GPU: the compact result (4 bytes per fragment over PCIe); every fragment is
         // decoded while its Fragment object is built
@@ -207,6 +221,8 @@ void AnchorFinder::run_impl() const {
               "npge_anchor_find_device");
         npge_anchor_compact_result c;
         check(npge_anchor_fetch_compact(st.ctx, &c), "npge_anchor_fetch_compact");
+        const double t_found = wall_ms();
+        st.ms[1] = t_found - t_uploaded;
         try {
             for (uint64_t b = 0; b < c.n_blocks; b++) {
                 Block* block = new Block;
@@ -228,6 +244,7 @@ void AnchorFinder::run_impl() const {
             throw;
         }
         npge_anchor_compact_result_free(&c);
+        st.ms[2] = wall_ms() - t_found;
         return;
     }
     npge_anchor_result r;
@@ -235,6 +252,8 @@ void AnchorFinder::run_impl() const {
                                         st.used_hashes.size(), nullptr),
           "npge_anchor_multi_find_device");
     check(npge_anchor_multi_fetch(st.multi, &r), "npge_anchor_multi_fetch");
+    const double t_found = wall_ms();
+    st.ms[1] = t_found - t_uploaded;
     try {
         for (uint64_t b = 0; b < r.n_blocks; b++) {
             Block* block = new Block;
@@ -256,6 +275,7 @@ void AnchorFinder::run_impl() const {
         throw;
     }
     npge_anchor_multi_result_free(&r);
+    st.ms[2] = wall_ms() - t_found;
 }
 
 const char* AnchorFinder::name_impl() const {

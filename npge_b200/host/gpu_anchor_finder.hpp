@@ -30,6 +30,10 @@ public:
     // how the last run() got its sequences onto the device(s): true = the packed
     // genome of the previous run was still valid (same sequences) and was reused
     bool last_run_reused_upload() const;
+    // wall time of the parts of the last run_impl(), ms: [0] linearising + uploading the
+    // sequences, [1] the device search + the copy of the result, [2] building the
+    // Fragment / Block objects (and check_block)
+    const double* last_run_ms() const;
 
 protected:
     void run_impl() const;          // Processor.hpp:482
