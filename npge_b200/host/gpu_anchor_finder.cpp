@@ -117,16 +117,26 @@ void check(int rc, const char* what) {
     }
 }
 
-// The letters of the anchors of one block must agree up to the strand
-// (check_block, AnchorFinder.cpp:342-354): a cheap end-to-end self-check of the
-// device result against the sequences it was computed from.
-void check_block(const Block* block) {
+// The letters of the anchors of one block must agree up to the strand (check_block,
+// AnchorFinder.cpp:342-354: letter by letter through raw_at, no strings): a cheap
+// end-to-end self-check of the device result against the sequences it came from.
+char letter_at(const Fragment* f, size_t pos) {  // Fragment::raw_at
+    const Sequence* seq = f->seq();
+    return f->ori() == 1 ? seq->char_at(f->min_pos() + pos)
+                         : complement(seq->char_at(f->max_pos() - pos));
+}
+
+void check_block(const Block* block, size_t anchor) {
     if (block->size() < 2) throw Exception("AnchorFinder (GPU): block of one fragment");
-    const std::string first = block->front()->str();
-    for (Block::const_iterator it = block->begin(); it != block->end(); ++it) {
-        if ((*it)->str() != first) {
-            throw Exception("AnchorFinder (GPU): fragments of a block differ: " +
-                            first + " vs " + (*it)->str());
+    const Fragment* first = block->front();
+    if (first->length() != anchor) throw Exception("AnchorFinder (GPU): wrong anchor length");
+    for (size_t pos = 0; pos < anchor; pos++) {
+        const char c = letter_at(first, pos);
+        for (Block::const_iterator it = block->begin(); it != block->end(); ++it) {
+            if (letter_at(*it, pos) != c) {
+                throw Exception("AnchorFinder (GPU): fragments of a block differ: " +
+                                first->str() + " vs " + (*it)->str());
+            }
         }
     }
 }
@@ -233,7 +243,7 @@ void AnchorFinder::run_impl() const {
                     block->insert(new Fragment(seqs[seq].get(), min_pos, min_pos + k - 1, ori));
                 }
                 bs.insert(block);  // the blockset owns it from here on
-                check_block(block);
+                check_block(block, k);
             }
             st.used_hashes.insert(st.used_hashes.end(), c.new_used, c.new_used + c.n_new_used);
             std::sort(st.used_hashes.begin(), st.used_hashes.end());
@@ -263,7 +273,7 @@ void AnchorFinder::run_impl() const {
                                            min_pos + k - 1, r.frag_ori[f]));
             }
             bs.insert(block);  // the blockset owns it from here on
-            check_block(block);
+            check_block(block, k);
         }
         // used_hashes_ stays sorted (SortedVector::extend + sort, :385-389)
         st.used_hashes.insert(st.used_hashes.end(), r.new_used, r.new_used + r.n_new_used);
