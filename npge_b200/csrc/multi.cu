@@ -46,11 +46,72 @@ private:
     uint64_t gen_ = 0;
 };
 
+// The rank threads of one npge_anchor_multi: created once, parked between calls (a
+// call costs a condition-variable handoff per rank, not a thread, and every thread
+// keeps its CUDA per-thread state).  Rank 0 runs on the caller's thread.
+class RankThreads {
+public:
+    explicit RankThreads(int n) : n_(n) {
+        for (int r = 1; r < n; r++) threads_.emplace_back([this, r] { loop(r); });
+    }
+    ~RankThreads() {
+        {
+            std::lock_guard<std::mutex> lock(mu_);
+            stop_ = true;
+            gen_++;
+        }
+        cv_.notify_all();
+        for (auto& t : threads_) t.join();
+    }
+    // fn(rank) on every rank's thread; returns when all of them have returned
+    void run(const std::function<void(int)>& fn) {
+        {
+            std::lock_guard<std::mutex> lock(mu_);
+            fn_ = &fn;
+            pending_ = n_ - 1;
+            gen_++;
+        }
+        cv_.notify_all();
+        fn(0);
+        std::unique_lock<std::mutex> lock(mu_);
+        done_.wait(lock, [&] { return pending_ == 0; });
+        fn_ = nullptr;
+    }
+private:
+    void loop(int r) {
+        uint64_t seen = 0;
+        for (;;) {
+            const std::function<void(int)>* fn = nullptr;
+            {
+                std::unique_lock<std::mutex> lock(mu_);
+                cv_.wait(lock, [&] { return gen_ != seen; });
+                seen = gen_;
+                if (stop_) return;
+                fn = fn_;
+            }
+            (*fn)(r);
+            {
+                std::lock_guard<std::mutex> lock(mu_);
+                if (--pending_ == 0) done_.notify_all();
+            }
+        }
+    }
+    int n_;
+    std::vector<std::thread> threads_;
+    std::mutex mu_;
+    std::condition_variable cv_, done_;
+    const std::function<void(int)>* fn_ = nullptr;
+    uint64_t gen_ = 0;
+    int pending_ = 0;
+    bool stop_ = false;
+};
+
 }  // namespace
 
 struct npge_anchor_multi {
     std::vector<int> devices;
     std::vector<npge_anchor_ctx*> ctx;
+    RankThreads* threads = nullptr;
     int32_t k = 0;
     bool uploaded = false, have_result = false;
     uint64_t capacity = 0;       // records every receive buffer can take
@@ -84,11 +145,8 @@ struct RankError {
     }
 };
 
-void run_ranks(int n, const std::function<void(int)>& fn) {
-    std::vector<std::thread> threads;
-    for (int r = 1; r < n; r++) threads.emplace_back(fn, r);
-    fn(0);
-    for (auto& t : threads) t.join();
+void run_ranks(npge_anchor_multi* m, const std::function<void(int)>& fn) {
+    m->threads->run(fn);
 }
 
 int peer_setup(npge_anchor_multi* m, uint64_t capacity) {
@@ -137,12 +195,14 @@ extern "C" int npge_anchor_multi_create(npge_anchor_multi** out, const int* devi
         m->devices.push_back(device_ids[r]);
     }
     m->stats.resize(n_devices);
+    m->threads = new RankThreads(n_devices);
     *out = m;
     return NPGE_ANCHOR_OK;
 }
 
 extern "C" void npge_anchor_multi_destroy(npge_anchor_multi* m) {
     if (!m) return;
+    delete m->threads;
     for (npge_anchor_ctx* c : m->ctx) npge_anchor_dist_peer_close(c);
     for (npge_anchor_ctx* c : m->ctx) npge_anchor_destroy(c);
     delete m;
@@ -189,7 +249,7 @@ extern "C" int npge_anchor_multi_upload(npge_anchor_multi* m, int32_t anchor_siz
     std::vector<uint64_t> cuts;
     dist_position_cuts(total, uint32_t(G), kPosAlign, cuts);
     RankError err;
-    run_ranks(G, [&](int r) {
+    run_ranks(m, [&](int r) {
         const uint64_t g0 = cuts[r], n_own = cuts[r + 1] - cuts[r];
         const uint64_t have_end = std::min(cuts[r + 1] + uint64_t(anchor_size) - 1, total);
         // the parts of the sequences inside [g0, have_end): straight from the caller's buffer
@@ -247,7 +307,7 @@ extern "C" int npge_anchor_multi_find_device(npge_anchor_multi* m, const npge_an
         Barrier bar(G);
         RankError err;
         bool regrow = false;
-        run_ranks(G, [&](int r) {
+        run_ranks(m, [&](int r) {
             npge_anchor_ctx* c = m->ctx[r];
             // count A, then pass A (asynchronous) while the others arrive
             std::vector<uint32_t> mine(hist_cap, 0);
@@ -355,7 +415,7 @@ extern "C" int npge_anchor_multi_fetch(npge_anchor_multi* m, npge_anchor_result*
     res->parts.resize(G);
     for (auto& r : res->parts) memset(&r, 0, sizeof(r));
     RankError err;
-    run_ranks(G, [&](int r) { err.set(npge_anchor_fetch(m->ctx[r], &res->parts[r])); });
+    run_ranks(m, [&](int r) { err.set(npge_anchor_fetch(m->ctx[r], &res->parts[r])); });
     if (err.failed()) {
         delete res;
         return fail(err.code, err.text);
@@ -382,7 +442,7 @@ extern "C" int npge_anchor_multi_fetch(npge_anchor_multi* m, npge_anchor_result*
         b0[r + 1] = b0[r] + res->parts[r].n_blocks;
         f0[r + 1] = f0[r] + res->parts[r].n_fragments;
     }
-    run_ranks(G, [&](int r) {
+    run_ranks(m, [&](int r) {
         const npge_anchor_result& p = res->parts[r];
         for (uint64_t b = 0; b < p.n_blocks; b++) {
             res->block_offsets[b0[r] + b] = p.block_offsets[b] + f0[r];

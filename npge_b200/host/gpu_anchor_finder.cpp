@@ -36,6 +36,19 @@ struct AnchorFinder::Impl {
     npge_anchor_multi* multi = nullptr;  // several devices
     std::vector<int> devices = std::vector<int>(1, 0);
     std::vector<uint64_t> used_hashes;  // sorted; AnchorFinderImpl::used_hashes_ (:30-32)
+
+    // used_hashes_ stays sorted and unique (SortedVector::extend + sort, :385-389);
+    // the library returns new_used ascending, so a merge does it
+    void extend_used(const uint64_t* more, uint64_t n) {
+        if (!n) return;
+        const size_t old = used_hashes.size();
+        used_hashes.insert(used_hashes.end(), more, more + n);
+        if (!std::is_sorted(used_hashes.begin() + old, used_hashes.end())) {
+            std::sort(used_hashes.begin() + old, used_hashes.end());
+        }
+        std::inplace_merge(used_hashes.begin(), used_hashes.begin() + old, used_hashes.end());
+        used_hashes.erase(std::unique(used_hashes.begin(), used_hashes.end()), used_hashes.end());
+    }
     // the genome resident on the device(s): AnchorLoop re-runs this instance on the same
     // sequences (src/algo/MetaProcessor.cpp:32-38, src/algo/Pipe.cpp:41-61)
     std::vector<const Sequence*> up_seqs;
@@ -43,7 +56,7 @@ struct AnchorFinder::Impl {
     uint64_t up_probe = 0;
     int up_k = 0;
     bool resident = false, reused = false;
-    double ms[3] = {0, 0, 0};
+    double ms[4] = {0, 0, 0, 0};  // [3]: the device search alone (part of [1])
     void drop() {
         if (ctx) npge_anchor_destroy(ctx);
         if (multi) npge_anchor_multi_destroy(multi);
@@ -229,6 +242,7 @@ void AnchorFinder::run_impl() const {
         check(npge_anchor_find_device(st.ctx, &params, st.used_hashes.data(),
                                       st.used_hashes.size(), nullptr),
               "npge_anchor_find_device");
+        st.ms[3] = wall_ms() - t_uploaded;
         npge_anchor_compact_result c;
         check(npge_anchor_fetch_compact(st.ctx, &c), "npge_anchor_fetch_compact");
         const double t_found = wall_ms();
@@ -245,10 +259,7 @@ void AnchorFinder::run_impl() const {
                 bs.insert(block);  // the blockset owns it from here on
                 check_block(block, k);
             }
-            st.used_hashes.insert(st.used_hashes.end(), c.new_used, c.new_used + c.n_new_used);
-            std::sort(st.used_hashes.begin(), st.used_hashes.end());
-            st.used_hashes.erase(std::unique(st.used_hashes.begin(), st.used_hashes.end()),
-                                 st.used_hashes.end());
+            st.extend_used(c.new_used, c.n_new_used);
         } catch (...) {
             npge_anchor_compact_result_free(&c);
             throw;
@@ -261,6 +272,7 @@ void AnchorFinder::run_impl() const {
     check(npge_anchor_multi_find_device(st.multi, &params, st.used_hashes.data(),
                                         st.used_hashes.size(), nullptr),
           "npge_anchor_multi_find_device");
+    st.ms[3] = wall_ms() - t_uploaded;
     check(npge_anchor_multi_fetch(st.multi, &r), "npge_anchor_multi_fetch");
     const double t_found = wall_ms();
     st.ms[1] = t_found - t_uploaded;
@@ -275,11 +287,7 @@ void AnchorFinder::run_impl() const {
             bs.insert(block);  // the blockset owns it from here on
             check_block(block, k);
         }
-        // used_hashes_ stays sorted (SortedVector::extend + sort, :385-389)
-        st.used_hashes.insert(st.used_hashes.end(), r.new_used, r.new_used + r.n_new_used);
-        std::sort(st.used_hashes.begin(), st.used_hashes.end());
-        st.used_hashes.erase(std::unique(st.used_hashes.begin(), st.used_hashes.end()),
-                             st.used_hashes.end());
+        st.extend_used(r.new_used, r.n_new_used);
     } catch (...) {
         npge_anchor_multi_result_free(&r);
         throw;

@@ -32,7 +32,7 @@ public:
     bool last_run_reused_upload() const;
     // wall time of the parts of the last run_impl(), ms: [0] linearising + uploading the
     // sequences, [1] the device search + the copy of the result, [2] building the
-    // Fragment / Block objects (and check_block)
+    // Fragment / Block objects (and check_block), [3] the device search alone (in [1])
     const double* last_run_ms() const;
 
 protected:

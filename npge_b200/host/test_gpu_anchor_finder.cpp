@@ -4,6 +4,7 @@
 //
 //   test_gpu_anchor_finder            all cases (needs a CUDA device)
 //   test_gpu_anchor_finder --no-gpu   only the cases that never reach the device
+#include <malloc.h>
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
@@ -367,6 +368,10 @@ static int bench_run(int n_devices) {
             x = x * 1664525u + 1013904223u;
             g[i] = "ATGC"[(x >> 20) & 3];
         }
+        // distinct sizes: the scan order (size descending) must not depend on the heap
+        // addresses the blockset orders equal-sized sequences by (the result of the
+        // anchor-similar rule depends on that order, in the reference too)
+        g.resize(g.size() - 1000 * st);
         strains.push_back(g);
     }
     for (int mode = 0; mode < 2; mode++) {
@@ -397,8 +402,17 @@ static int bench_run(int n_devices) {
             frags = 0;
             for (BlockSet::const_iterator b = bs->begin(); b != bs->end(); ++b) frags += (*b)->size();
             bs->clear_blocks();
+            // the millions of freed Block / Fragment chunks sit in glibc's fast bins; the
+            // next large malloc would consolidate them (~450 ms here) inside the timed run
+            malloc_trim(0);
             t0 = now_s();
             fresh.run();  // resident genome, used hashes: mostly the fixed costs
+            if (now_s() - t0 < best2) {
+                const double* ms = fresh.last_run_ms();
+                std::printf("  rep %d again (reused upload: %d): linearise + upload %.1f ms, "
+                            "search + copy %.1f ms (search %.1f), objects %.1f ms\n", rep,
+                            int(fresh.last_run_reused_upload()), ms[0], ms[1], ms[3], ms[2]);
+            }
             best2 = std::min(best2, now_s() - t0);
         }
         std::printf("bench %s devices=%d: run() %.1f ms (%zu blocks, %zu fragments); "
