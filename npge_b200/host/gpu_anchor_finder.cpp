@@ -13,6 +13,9 @@
 #include <algorithm>
 #include <chrono>
 #include <cstdint>
+#include <exception>
+#include <mutex>
+#include <thread>
 #include <string>
 #include <vector>
 
@@ -36,6 +39,16 @@ struct AnchorFinder::Impl {
     npge_anchor_multi* multi = nullptr;  // several devices
     std::vector<int> devices = std::vector<int>(1, 0);
     std::vector<uint64_t> used_hashes;  // sorted; AnchorFinderImpl::used_hashes_ (:30-32)
+
+    // threads of the object build: the processor's `workers` option (-1 = all cores,
+    // Processor.cpp workers semantics)
+    static int build_threads(int workers) {
+        if (workers < 0) {
+            const unsigned hc = std::thread::hardware_concurrency();
+            return hc ? int(hc) : 1;
+        }
+        return workers < 1 ? 1 : workers;
+    }
 
     // used_hashes_ stays sorted and unique (SortedVector::extend + sort, :385-389);
     // the library returns new_used ascending, so a merge does it
@@ -154,6 +167,61 @@ void check_block(const Block* block, size_t anchor) {
     }
 }
 
+// One Block per hash group, one Fragment per occurrence (postprocess,
+// AnchorFinder.cpp:356-391), built and self-checked by `threads` threads over
+// contiguous block ranges (the objects of different blocks share nothing but the
+// read-only sequences); the caller inserts them into the block set in order.
+// frag(f, &seq, &min_pos, &ori) decodes fragment f of the result.
+template <typename Frag>
+void build_blocks(const uint64_t* block_offsets, uint64_t n_blocks, Frag frag,
+                  const std::vector<SequencePtr>& seqs, size_t k, int threads,
+                  std::vector<Block*>& built) {
+    built.assign(n_blocks, static_cast<Block*>(0));
+    auto range = [&](uint64_t b0, uint64_t b1) {
+        for (uint64_t b = b0; b < b1; b++) {
+            Block* block = new Block;
+            built[b] = block;  // freed by the caller if anything below throws
+            for (uint64_t f = block_offsets[b]; f < block_offsets[b + 1]; f++) {
+                uint32_t seq, min_pos;
+                int ori;
+                frag(f, &seq, &min_pos, &ori);
+                block->insert(new Fragment(seqs[seq].get(), min_pos, min_pos + k - 1, ori));
+            }
+            check_block(block, k);
+        }
+    };
+    const uint64_t kMinPerThread = 1024;
+    uint64_t T = threads < 1 ? 1 : uint64_t(threads);
+    T = std::min<uint64_t>(T, std::max<uint64_t>(1, n_blocks / kMinPerThread));
+    std::exception_ptr first_error;
+    if (T == 1) {
+        try {
+            range(0, n_blocks);
+        } catch (...) {
+            first_error = std::current_exception();
+        }
+    } else {
+        std::mutex mu;
+        std::vector<std::thread> pool;
+        for (uint64_t t = 0; t < T; t++) {
+            pool.emplace_back([&, t] {
+                try {
+                    range(n_blocks * t / T, n_blocks * (t + 1) / T);
+                } catch (...) {
+                    std::lock_guard<std::mutex> lock(mu);
+                    if (!first_error) first_error = std::current_exception();
+                }
+            });
+        }
+        for (size_t t = 0; t < pool.size(); t++) pool[t].join();
+    }
+    if (first_error) {
+        for (uint64_t b = 0; b < n_blocks; b++) delete built[b];  // a Block owns its fragments
+        built.clear();
+        std::rethrow_exception(first_error);
+    }
+}
+
 // A cheap fingerprint of the sequences' letters (the ends and 256 evenly spaced
 // positions of each): the resident genome is reused when the same Sequence objects,
 // with the same sizes and the same fingerprint, come again.
@@ -248,17 +316,12 @@ void AnchorFinder::run_impl() const {
         const double t_found = wall_ms();
         st.ms[1] = t_found - t_uploaded;
         try {
-            for (uint64_t b = 0; b < c.n_blocks; b++) {
-                Block* block = new Block;
-                for (uint64_t f = c.block_offsets[b]; f < c.block_offsets[b + 1]; f++) {
-                    uint32_t seq, min_pos;
-                    int ori;
-                    npge_decode_compact(&c, f, &seq, &min_pos, &ori);
-                    block->insert(new Fragment(seqs[seq].get(), min_pos, min_pos + k - 1, ori));
-                }
-                bs.insert(block);  // the blockset owns it from here on
-                check_block(block, k);
-            }
+            std::vector<Block*> built;
+            build_blocks(c.block_offsets, c.n_blocks,
+                         [&](uint64_t f, uint32_t* seq, uint32_t* min_pos, int* ori) {
+                             npge_decode_compact(&c, f, seq, min_pos, ori);
+                         }, seqs, k, st.build_threads(workers()), built);
+            for (size_t b = 0; b < built.size(); b++) bs.insert(built[b]);  // owned by the blockset
             st.extend_used(c.new_used, c.n_new_used);
         } catch (...) {
             npge_anchor_compact_result_free(&c);
@@ -277,16 +340,14 @@ void AnchorFinder::run_impl() const {
     const double t_found = wall_ms();
     st.ms[1] = t_found - t_uploaded;
     try {
-        for (uint64_t b = 0; b < r.n_blocks; b++) {
-            Block* block = new Block;
-            for (uint64_t f = r.block_offsets[b]; f < r.block_offsets[b + 1]; f++) {
-                const size_t min_pos = r.frag_min_pos[f];
-                block->insert(new Fragment(seqs[r.frag_seq[f]].get(), min_pos,
-                                           min_pos + k - 1, r.frag_ori[f]));
-            }
-            bs.insert(block);  // the blockset owns it from here on
-            check_block(block, k);
-        }
+        std::vector<Block*> built;
+        build_blocks(r.block_offsets, r.n_blocks,
+                     [&](uint64_t f, uint32_t* seq, uint32_t* min_pos, int* ori) {
+                         *seq = r.frag_seq[f];
+                         *min_pos = r.frag_min_pos[f];
+                         *ori = r.frag_ori[f];
+                     }, seqs, k, st.build_threads(workers()), built);
+        for (size_t b = 0; b < built.size(); b++) bs.insert(built[b]);  // owned by the blockset
         st.extend_used(r.new_used, r.n_new_used);
     } catch (...) {
         npge_anchor_multi_result_free(&r);

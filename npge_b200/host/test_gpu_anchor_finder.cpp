@@ -262,6 +262,30 @@ static void several_devices_equal_one_device() {
     }
 }
 
+// the `workers` option sets the threads that build and check the Block / Fragment
+// objects: the block set does not depend on it
+static void workers_build_the_same_blocks() {
+    const std::string a = pseudo_genome(21, 60000);
+    const std::string b = a.substr(5000, 40000) + pseudo_genome(22, 3000);
+    std::string want;
+    for (int workers = 1; workers <= 5; workers += 2) {
+        for (int ranks = 1; ranks <= 2; ranks++) {
+            BlockSetPtr bs = blockset_of({a.c_str(), b.c_str()});
+            gpu::AnchorFinder af;
+            af.set_devices(std::vector<int>(size_t(ranks), 0));
+            af.set_block_set(bs);
+            af.set_workers(workers);
+            af.set_opt_value("anchor-size", 14);
+            af.set_opt_value("anchor-similar", false);
+            af.set_opt_value("max-anchor-fragments", -1);
+            af.run();
+            CHECK(bs->size() > 20000);
+            if (want.empty()) want = canonical(*bs);
+            CHECK(canonical(*bs) == want);
+        }
+    }
+}
+
 // AnchorLoop re-runs one instance on the same sequences (MetaProcessor.cpp:32-38): the
 // second run finds the packed genome still on the device and skips the upload
 static void resident_genome_is_reused() {
@@ -358,7 +382,7 @@ static double now_s() {
     return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
 }
 
-static int bench_run(int n_devices) {
+static int bench_run(int n_devices, int workers) {
     const std::string anc = pseudo_genome(11, 3300000);
     std::vector<std::string> strains;
     for (unsigned st = 0; st < 3; st++) {
@@ -390,6 +414,7 @@ static int bench_run(int n_devices) {
             fresh.set_block_set(bs);
             fresh.set_opt_value("anchor-similar", mode == 1);
             if (mode == 0) fresh.set_opt_value("max-anchor-fragments", -1);
+            fresh.set_workers(workers);  // threads of the object build
             double t0 = now_s();
             fresh.run();
             if (now_s() - t0 < best) {
@@ -415,9 +440,9 @@ static int bench_run(int n_devices) {
             }
             best2 = std::min(best2, now_s() - t0);
         }
-        std::printf("bench %s devices=%d: run() %.1f ms (%zu blocks, %zu fragments); "
+        std::printf("bench %s devices=%d workers=%d: run() %.1f ms (%zu blocks, %zu fragments); "
                     "second run on the resident genome %.1f ms\n",
-                    mode == 0 ? "parity" : "default", n_devices, best * 1e3, blocks, frags,
+                    mode == 0 ? "parity" : "default", n_devices, workers, best * 1e3, blocks, frags,
                     best2 * 1e3);
     }
     return 0;
@@ -425,7 +450,8 @@ static int bench_run(int n_devices) {
 
 int main(int argc, char** argv) {
     if (argc > 1 && std::strcmp(argv[1], "--bench") == 0) {
-        return bench_run(argc > 2 ? std::atoi(argv[2]) : 1);
+        // --bench [n_devices [workers]]
+        return bench_run(argc > 2 ? std::atoi(argv[2]) : 1, argc > 3 ? std::atoi(argv[3]) : 1);
     }
     const bool no_gpu = argc > 1 && std::strcmp(argv[1], "--no-gpu") == 0;
     options_and_rules();
@@ -446,6 +472,7 @@ int main(int argc, char** argv) {
             truncation();
             several_devices_equal_one_device();
             resident_genome_is_reused();
+    workers_build_the_same_blocks();
             fragment_finder_run();
         } catch (const std::exception& e) {
             failures++;
