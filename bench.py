@@ -484,12 +484,11 @@ def run_gpu(args, rank, world, local_rank):
         d2h = runner.find_host(pinned_np, offsets, K, False, BIG)
     barrier()
     e2e_t = max_over_ranks(time.perf_counter() - t0, world, dist, torch)
-    e2e_parity = None
-    if world == 1:  # the host-buffer call's own result against the golden digest
-        h = runner.last_host
-        e2e_parity = check_parity(job_name, K, "parity", {
-            "n_fragments_global": h["n_fragments"], "n_blocks_global": h["n_blocks"],
-            "digest": h["digest"]})["digest_equal"]
+    # the host-buffer call's own result against the golden digest
+    h = runner.last_host
+    e2e_parity = check_parity(job_name, K, "parity", {
+        "n_fragments_global": h["n_fragments"], "n_blocks_global": h["n_blocks"],
+        "digest": h["digest"]})["digest_equal"]
     h2d = int(bases.nbytes + offsets.nbytes)
     if world > 1:  # job totals of the copies and of the launches
         t = torch.tensor([h2d, int(d2h), kern_launches], dtype=torch.int64, device="cuda")
@@ -699,12 +698,13 @@ class DistRunner(SingleRunner):
     def finish(self, st):
         return self._job(self.f.job_stats()) if st is self.f._last else self._job(st)
 
-    e2e_call = ("DistAnchorFinder.find (pinned ASCII bases in, every rank's slice of the "
-                "fragment arrays out, pinned)")
+    e2e_call = ("DistAnchorFinder.find_compact_counts (pinned ASCII bases in, every rank's "
+                "slice of the blocks + 4-byte (position, strand) fragments out, pinned)")
 
-    def find_host(self, bases, offsets, k, similar, max_frags, full=True):
-        st = self.f.find_counts((bases, offsets), k, similar=similar,
-                                max_frags=max_frags)
+    def find_host(self, bases, offsets, k, similar, max_frags, full=False):
+        fn = self.f.find_counts if full else self.f.find_compact_counts
+        st = fn((bases, offsets), k, similar=similar, max_frags=max_frags)
+        self.last_host = st
         return st["result_bytes"]
 
     def ncu_traffic(self, n_windows):

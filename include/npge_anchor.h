@@ -191,7 +191,9 @@ int npge_anchor_fetch(npge_anchor_ctx* ctx, npge_anchor_result* out);
  * write payloads only (npge_anchor_fetch still works: it expands them on the host;
  * npge_anchor_block_hashes on the resident result does not); fetch_compact returns
  * them as they are; find_compact = upload + find_device + fetch_compact with host
- * buffers in, whatever the context's layout.  Single-GPU contexts only. */
+ * buffers in, whatever the context's layout.  On a rank of a multi-GPU job
+ * (npge_anchor_dist_*) the positions and the layout table are the job's, and new_used
+ * lists every hash of the rank's range. */
 int npge_anchor_set_result_layout(npge_anchor_ctx* ctx, int32_t layout);
 int npge_anchor_fetch_compact(npge_anchor_ctx* ctx, npge_anchor_compact_result* out);
 int npge_anchor_find_compact(npge_anchor_ctx* ctx, const npge_anchor_params* p,
@@ -367,6 +369,12 @@ int npge_anchor_multi_find_device(npge_anchor_multi* m, const npge_anchor_params
                                   npge_anchor_stats* job_stats);
 int npge_anchor_multi_fetch(npge_anchor_multi* m, npge_anchor_result* out);
 void npge_anchor_multi_result_free(npge_anchor_result* out);
+/* The compact layout over several GPUs: after multi_set_result_layout(COMPACT) every
+ * rank writes payloads only, and multi_fetch_compact copies every rank's slice straight
+ * into its place in the job's arrays (4 bytes per fragment over every GPU's PCIe link). */
+int npge_anchor_multi_set_result_layout(npge_anchor_multi* m, int32_t layout);
+int npge_anchor_multi_fetch_compact(npge_anchor_multi* m, npge_anchor_compact_result* out);
+void npge_anchor_multi_compact_result_free(npge_anchor_compact_result* out);
 int npge_anchor_multi_get_stats(npge_anchor_multi* m, int rank, npge_anchor_stats* stats);
 int npge_anchor_multi_debug_check(npge_anchor_multi* m, uint32_t* n_damaged); /* all ranks */
 

@@ -30,6 +30,8 @@ EXPORTS = [
     "npge_anchor_multi_create", "npge_anchor_multi_destroy", "npge_anchor_multi_devices",
     "npge_anchor_multi_find", "npge_anchor_multi_upload", "npge_anchor_multi_find_device",
     "npge_anchor_multi_fetch", "npge_anchor_multi_result_free", "npge_anchor_multi_get_stats",
+    "npge_anchor_multi_set_result_layout", "npge_anchor_multi_fetch_compact",
+    "npge_anchor_multi_compact_result_free",
     "npge_anchor_multi_debug_check",
 ]
 IPC_BYTES = 128
@@ -230,6 +232,12 @@ def load():
     L.npge_anchor_multi_fetch.argtypes = [ctx, C.POINTER(Result)]
     L.npge_anchor_multi_result_free.restype = None
     L.npge_anchor_multi_result_free.argtypes = [C.POINTER(Result)]
+    L.npge_anchor_multi_set_result_layout.restype = C.c_int
+    L.npge_anchor_multi_set_result_layout.argtypes = [ctx, C.c_int32]
+    L.npge_anchor_multi_fetch_compact.restype = C.c_int
+    L.npge_anchor_multi_fetch_compact.argtypes = [ctx, C.POINTER(CompactResult)]
+    L.npge_anchor_multi_compact_result_free.restype = None
+    L.npge_anchor_multi_compact_result_free.argtypes = [C.POINTER(CompactResult)]
     L.npge_anchor_multi_get_stats.restype = C.c_int
     L.npge_anchor_multi_get_stats.argtypes = [ctx, C.c_int, C.POINTER(Stats)]
     L.npge_anchor_multi_debug_check.restype = C.c_int

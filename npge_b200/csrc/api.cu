@@ -1179,32 +1179,36 @@ namespace {
 // new_used and the fields of `out`
 void finish_compact(npge_anchor_ctx* ctx, CompactHost* r, uint64_t nf, uint64_t nb,
                     npge_anchor_compact_result* out) {
-    r->layout_start.resize(ctx->seqs.size() + 1);
-    r->layout_seq.resize(ctx->seqs.size() + 1);
+    // (a rank of a multi-GPU job: positions are job-wide, the layout is the job's)
+    const auto& seqs = ctx->dist ? ctx->gseqs : ctx->seqs;
+    r->layout_start.resize(seqs.size() + 1);
+    r->layout_seq.resize(seqs.size() + 1);
     uint64_t end = 0;
-    for (size_t i = 0; i < ctx->seqs.size(); i++) {
-        r->layout_start[i] = ctx->seqs[i].start;
-        r->layout_seq[i] = ctx->seqs[i].caller_index;
-        end = ctx->seqs[i].start + ctx->seqs[i].size + 1;
+    for (size_t i = 0; i < seqs.size(); i++) {
+        r->layout_start[i] = seqs[i].start;
+        r->layout_seq[i] = seqs[i].caller_index;
+        end = seqs[i].start + seqs[i].size + 1;
     }
-    r->layout_start[ctx->seqs.size()] = end;
+    r->layout_start[seqs.size()] = end;
     // used_hashes.push_back for every distinct hash of the list but the first
     // (AnchorFinder.cpp:366-387); a lone cut tail still counts (:385)
-    if (ctx->lone_tail && nb) {
-        r->new_used.assign(r->block_hash.data() + 1, r->block_hash.data() + nb);
+    // (several GPUs: every hash of this rank's range; the caller drops the job's first)
+    const uint64_t b0 = ctx->dist ? 0 : 1;
+    if (ctx->lone_tail && (ctx->dist || nb)) {
+        r->new_used.assign(r->block_hash.data() + std::min(b0, nb), r->block_hash.data() + nb);
         r->new_used.push_back(ctx->lone_hash);
         out->new_used = r->new_used.data();
         out->n_new_used = r->new_used.size();
-    } else if (nb > 1) {
-        out->new_used = r->block_hash.data() + 1;  // the list IS the tail of block_hash
-        out->n_new_used = nb - 1;
+    } else if (nb > b0) {
+        out->new_used = r->block_hash.data() + b0;  // the list IS the tail of block_hash
+        out->n_new_used = nb - b0;
     }
     out->n_blocks = nb;
     out->n_fragments = nf;
     out->block_offsets = r->block_offsets.data();
     out->block_hash = r->block_hash.data();
     out->frag_pos_ori = r->pos_ori.data();
-    out->n_layout = uint32_t(ctx->seqs.size());
+    out->n_layout = uint32_t(seqs.size());
     out->layout_start = r->layout_start.data();
     out->layout_seq = r->layout_seq.data();
     out->anchor_size = ctx->last_params.anchor_size;
@@ -1221,7 +1225,7 @@ extern "C" int npge_anchor_fetch_compact(npge_anchor_ctx* ctx, npge_anchor_compa
     if (!ctx->have_result) {
         return fail(NPGE_ANCHOR_ERR_STATE, "npge_anchor_find_device has not run");
     }
-    if (!ctx->have_pay || ctx->dist) {
+    if (!ctx->have_pay) {
         return fail(NPGE_ANCHOR_ERR_STATE,
                     "the resident result holds no payloads: npge_anchor_set_result_layout("
                     "NPGE_ANCHOR_LAYOUT_COMPACT) before npge_anchor_find_device");
@@ -1261,6 +1265,39 @@ extern "C" int npge_anchor_fetch_compact(npge_anchor_ctx* ctx, npge_anchor_compa
     finish_compact(ctx, r, nf, nb, out);
     return NPGE_ANCHOR_OK;
 }
+
+namespace npge_b200 {
+
+void* pinned_take(size_t bytes) {
+    return PinnedPool::instance().take(PinnedPool::round_up(bytes));
+}
+
+void pinned_give(void* p, size_t bytes) {
+    if (p) PinnedPool::instance().give(p, PinnedPool::round_up(bytes));
+}
+
+int fetch_compact_into(npge_anchor_ctx* ctx, uint32_t* pos_ori, uint64_t* block_off,
+                       uint64_t* block_hash) {
+    if (!ctx || !ctx->have_result || !ctx->have_pay) {
+        return fail(NPGE_ANCHOR_ERR_STATE, "no compact resident result");
+    }
+    NPGE_CUDA(cudaSetDevice(ctx->device));
+    const uint64_t nf = ctx->stats.n_fragments, nb = ctx->stats.n_blocks;
+    cudaStream_t st = ctx->stream;
+    if (nf) {
+        NPGE_CUDA(cudaMemcpyAsync(pos_ori, ctx->r_pay.ptr, nf * 4, cudaMemcpyDeviceToHost, st));
+    }
+    if (nb) {
+        NPGE_CUDA(cudaMemcpyAsync(block_off, ctx->r_block_off.ptr, nb * 8,
+                                  cudaMemcpyDeviceToHost, st));
+        NPGE_CUDA(cudaMemcpyAsync(block_hash, ctx->r_block_hash.ptr, nb * 8,
+                                  cudaMemcpyDeviceToHost, st));
+    }
+    NPGE_CUDA(cudaStreamSynchronize(st));
+    return NPGE_ANCHOR_OK;
+}
+
+}  // namespace npge_b200
 
 extern "C" void npge_anchor_compact_result_free(npge_anchor_compact_result* out) {
     if (!out) return;
@@ -1453,6 +1490,11 @@ extern "C" int npge_anchor_dist_upload_range(npge_anchor_ctx* ctx, int32_t ancho
     for (uint32_t i = 0; i <= n_global; i++) {
         pairs[i] = make_uint2(uint32_t(global_start[i]), callers[i]);
     }
+    // host copies: npge_anchor_fetch expands a compact resident result with them
+    ctx->h_lut = lut;
+    ctx->h_caller = callers;
+    ctx->h_start32.resize(size_t(n_global) + 1);
+    for (uint32_t i = 0; i <= n_global; i++) ctx->h_start32[i] = uint32_t(global_start[i]);
     NPGE_TRY(ensure(ctx->g_seq_start, (size_t(n_global) + 1) * 8));
     NPGE_TRY(ensure(ctx->g_seq_caller, (size_t(n_global) + 1) * 4));
     NPGE_TRY(ensure(ctx->g_seq_lut, n_chunks * 4));
@@ -2137,15 +2179,27 @@ extern "C" int npge_anchor_dist_emit(npge_anchor_ctx* ctx, const npge_anchor_par
     const bool similar = p->anchor_similar != 0;
     const uint64_t max_records = ctx->n_recv;
     const uint64_t max_frags = std::min<uint64_t>(max_records, local_limit);
-    NPGE_TRY(ensure(ctx->r_seq, max_frags * 4));
-    NPGE_TRY(ensure(ctx->r_pos, max_frags * 4));
-    NPGE_TRY(ensure(ctx->r_ori, max_frags));
+    // compact layout: (job-wide position << 1 | strand) only, as on one GPU
+    const bool compact = ctx->layout == 1;
+    if (compact) {
+        NPGE_TRY(ensure(ctx->r_pay, max_frags * 4));
+    } else {
+        NPGE_TRY(ensure(ctx->r_seq, max_frags * 4));
+        NPGE_TRY(ensure(ctx->r_pos, max_frags * 4));
+        NPGE_TRY(ensure(ctx->r_ori, max_frags));
+    }
     NPGE_TRY(ensure(ctx->r_block_off, (max_frags / 2 + 2) * 8));
     NPGE_TRY(ensure(ctx->r_block_hash, (max_frags / 2 + 2) * 8));
     cudaStream_t st = ctx->stream;
     MsdBuffers mb = dist_msd_buffers(ctx, plan, ctx->dist_max_seg);
     BucketArgs a = bucket_args(ctx, plan, mb, ptr<uint64_t>(ctx->recv_rec),
                                ptr<uint32_t>(ctx->recv_hi), ctx->dist_n_used, local_limit);
+    if (compact) {
+        a.r_pay = ptr<uint32_t>(ctx->r_pay);
+        a.r_seq = nullptr;
+        a.r_pos = nullptr;
+        a.r_ori = nullptr;
+    }
     NPGE_CUDA(cudaEventRecord(ctx->ev[0], st));
     launch_bucket_stage(a, similar ? kBucketEmitSimilar : kBucketEmit, max_records, st,
                         &ctx->dist_launches);
@@ -2186,10 +2240,10 @@ extern "C" int npge_anchor_dist_emit(npge_anchor_ctx* ctx, const npge_anchor_par
     const double rec = plan.wide ? 12.0 : 8.0;
     s.bytes_moved = uint64_t(double(ctx->n_bases) * 0.75 + double(ctx->n_positions) * rec +
                              double(max_records) * rec * (similar ? 6.0 : 4.0)) +
-                    9 * s.n_fragments + 16 * s.n_blocks;
+                    (compact ? 4 : 9) * s.n_fragments + 16 * s.n_blocks;
     ctx->total_selected = summary[kSumFragments];
-    ctx->have_pay = false;
-    ctx->result_compact = false;
+    ctx->have_pay = compact;
+    ctx->result_compact = compact;
     ctx->last_params = *p;
     ctx->last_params.max_anchor_fragments = int64_t(std::min<uint64_t>(local_limit, uint64_t(INT64_MAX)));
     NPGE_TRY(fix_cut_resident(ctx, local_limit));

@@ -217,4 +217,13 @@ void launch_block_hash(const BlockHashArgs& a, cudaStream_t s);
 // thread-local error text of the C ABI (api.cu), for the other translation units
 int set_last_error(int code, const std::string& msg);
 
+// pooled page-locked host memory of the result arrays (api.cu); take throws
+// std::bad_alloc
+void* pinned_take(size_t bytes);
+void pinned_give(void* p, size_t bytes);
+// the compact resident result of a context, copied into the caller's (pinned) arrays:
+// n_fragments payloads, n_blocks offsets (no closing one) and hashes
+int fetch_compact_into(npge_anchor_ctx* ctx, uint32_t* pos_ori, uint64_t* block_off,
+                       uint64_t* block_hash);
+
 }  // namespace npge_b200

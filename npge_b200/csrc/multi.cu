@@ -483,6 +483,136 @@ extern "C" void npge_anchor_multi_result_free(npge_anchor_result* out) {
     memset(out, 0, sizeof(*out));
 }
 
+// ---- the compact layout over several GPUs ----------------------------------------------
+extern "C" int npge_anchor_multi_set_result_layout(npge_anchor_multi* m, int32_t layout) {
+    if (!m) return fail(NPGE_ANCHOR_ERR_PARAMS, "NULL argument");
+    for (npge_anchor_ctx* c : m->ctx) {
+        const int rc = npge_anchor_set_result_layout(c, layout);
+        if (rc) return rc;
+    }
+    return NPGE_ANCHOR_OK;
+}
+
+namespace {
+
+struct MultiCompact {
+    uint32_t* pos_ori = nullptr;
+    uint64_t* block_off = nullptr;
+    uint64_t* block_hash = nullptr;
+    size_t bytes[3] = {0, 0, 0};
+    std::vector<uint64_t> new_used, layout_start;
+    std::vector<uint32_t> layout_seq;
+    ~MultiCompact() {
+        pinned_give(pos_ori, bytes[0]);
+        pinned_give(block_off, bytes[1]);
+        pinned_give(block_hash, bytes[2]);
+    }
+};
+
+}  // namespace
+
+// Every rank copies its slice straight into its place in the job's arrays (positions
+// are job-wide: the slices need no translation, only the block offsets a shift).
+extern "C" int npge_anchor_multi_fetch_compact(npge_anchor_multi* m,
+                                               npge_anchor_compact_result* out) {
+    if (!m || !out) return fail(NPGE_ANCHOR_ERR_PARAMS, "NULL argument");
+    memset(out, 0, sizeof(*out));
+    if (!m->have_result) return fail(NPGE_ANCHOR_ERR_STATE, "npge_anchor_multi_find_device has not run");
+    const int G = int(m->ctx.size());
+    for (npge_anchor_ctx* c : m->ctx) {
+        if (!c->have_pay) {
+            return fail(NPGE_ANCHOR_ERR_STATE, "the resident result holds no payloads: "
+                        "npge_anchor_multi_set_result_layout(NPGE_ANCHOR_LAYOUT_COMPACT) first");
+        }
+    }
+    std::vector<uint64_t> b0(G + 1, 0), f0(G + 1, 0);
+    for (int r = 0; r < G; r++) {
+        b0[r + 1] = b0[r] + m->ctx[r]->stats.n_blocks;
+        f0[r + 1] = f0[r] + m->ctx[r]->stats.n_fragments;
+    }
+    const uint64_t nb = b0[G], nf = f0[G];
+    MultiCompact* res = new (std::nothrow) MultiCompact;
+    if (!res) return fail(NPGE_ANCHOR_ERR_MEMORY, "out of host memory");
+    try {
+        res->bytes[0] = (nf + 1) * 4;
+        res->pos_ori = static_cast<uint32_t*>(pinned_take(res->bytes[0]));
+        res->bytes[1] = (nb + 1) * 8;
+        res->block_off = static_cast<uint64_t*>(pinned_take(res->bytes[1]));
+        res->bytes[2] = (nb + 1) * 8;
+        res->block_hash = static_cast<uint64_t*>(pinned_take(res->bytes[2]));
+    } catch (std::bad_alloc&) {
+        delete res;
+        return fail(NPGE_ANCHOR_ERR_MEMORY, "out of host memory for the result");
+    }
+    RankError err;
+    run_ranks(m, [&](int r) {
+        const int rc = fetch_compact_into(m->ctx[r], res->pos_ori + f0[r], res->block_off + b0[r],
+                                          res->block_hash + b0[r]);
+        err.set(rc);
+        if (!rc && f0[r]) {
+            for (uint64_t b = b0[r]; b < b0[r + 1]; b++) res->block_off[b] += f0[r];
+        }
+    });
+    if (err.failed()) {
+        delete res;
+        return fail(err.code, err.text);
+    }
+    res->block_off[nb] = nf;
+    // the job's list: every hash of every rank's range (+ a rank's lone cut tail,
+    // AnchorFinder.cpp:385) but the job's first one
+    bool lone = false;
+    for (npge_anchor_ctx* c : m->ctx) lone = lone || c->lone_tail;
+    if (lone) {
+        try {
+            for (int r = 0; r < G; r++) {
+                res->new_used.insert(res->new_used.end(), res->block_hash + b0[r],
+                                     res->block_hash + b0[r + 1]);
+                if (m->ctx[r]->lone_tail) res->new_used.push_back(m->ctx[r]->lone_hash);
+            }
+        } catch (std::bad_alloc&) {
+            delete res;
+            return fail(NPGE_ANCHOR_ERR_MEMORY, "out of host memory for the result");
+        }
+        if (!res->new_used.empty()) res->new_used.erase(res->new_used.begin());
+        out->new_used = res->new_used.data();
+        out->n_new_used = res->new_used.size();
+    } else if (nb > 1) {
+        out->new_used = res->block_hash + 1;  // the list IS the tail of block_hash
+        out->n_new_used = nb - 1;
+    }
+    const auto& seqs = m->ctx[0]->gseqs;
+    res->layout_start.resize(seqs.size() + 1);
+    res->layout_seq.resize(seqs.size() + 1);
+    uint64_t end = 0;
+    for (size_t i = 0; i < seqs.size(); i++) {
+        res->layout_start[i] = seqs[i].start;
+        res->layout_seq[i] = seqs[i].caller_index;
+        end = seqs[i].start + seqs[i].size + 1;
+    }
+    res->layout_start[seqs.size()] = end;
+    out->n_blocks = nb;
+    out->n_fragments = nf;
+    out->block_offsets = res->block_off;
+    out->block_hash = res->block_hash;
+    out->frag_pos_ori = res->pos_ori;
+    out->n_layout = uint32_t(seqs.size());
+    out->layout_start = res->layout_start.data();
+    out->layout_seq = res->layout_seq.data();
+    out->anchor_size = m->k;
+    for (npge_anchor_ctx* c : m->ctx) {
+        out->digest[0] += c->stats.digest[0];
+        out->digest[1] += c->stats.digest[1];
+    }
+    out->owner_ = res;
+    return NPGE_ANCHOR_OK;
+}
+
+extern "C" void npge_anchor_multi_compact_result_free(npge_anchor_compact_result* out) {
+    if (!out) return;
+    delete static_cast<MultiCompact*>(out->owner_);
+    memset(out, 0, sizeof(*out));
+}
+
 extern "C" int npge_anchor_multi_find(npge_anchor_multi* m, const npge_anchor_params* p,
                                       const uint8_t* bases, const uint64_t* seq_offsets,
                                       uint32_t n_seqs, const uint64_t* used_sorted,

@@ -790,6 +790,23 @@ class DistAnchorFinder:
         stats["result_bytes"] = self.stages.fetch_counts()["result_bytes"]
         return stats
 
+    def find_compact_counts(self, seqs, k, similar=True, max_frags=100000, used=None):
+        """find_counts() with the compact result layout: every rank's slice crosses
+        PCIe as 4 bytes per fragment (job-wide position << 1 | strand)."""
+        self.stages.set_result_layout(_abi.LAYOUT_COMPACT)
+        try:
+            self.upload(seqs, k)
+            stats = self.find_device(k, similar=similar, max_frags=max_frags, used=used)
+            stats["result_bytes"] = self.stages.fetch_compact_counts()["result_bytes"]
+        finally:
+            self.stages.set_result_layout(_abi.LAYOUT_FULL)
+        return stats
+
+    def fetch_compact(self):
+        """This rank's slice in the compact layout (after a find_device under
+        stages.set_result_layout(LAYOUT_COMPACT)); decoded like AnchorResult."""
+        return self.stages.fetch_compact()
+
     def find(self, seqs, k, similar=True, max_frags=100000, used=None):
         """upload + find_device + fetch (host buffers in, host arrays out)."""
         self.upload(seqs, k)

@@ -260,6 +260,16 @@ class AnchorEngine:
         return {"n_blocks": nb, "n_fragments": nf,
                 "result_bytes": nf * 9 + (nb + 1) * 8 + nb * 8}
 
+    def fetch_compact_counts(self):
+        """npge_anchor_fetch_compact, keeping only the sizes and the digest."""
+        r = _abi.CompactResult()
+        self._check(self._lib.npge_anchor_fetch_compact(self._ctx, C.byref(r)))
+        nb, nf = int(r.n_blocks), int(r.n_fragments)
+        dg = (int(r.digest[0]), int(r.digest[1]))
+        self._lib.npge_anchor_compact_result_free(C.byref(r))
+        return {"n_blocks": nb, "n_fragments": nf, "digest": dg,
+                "result_bytes": nf * 4 + (nb + 1) * 8 + nb * 8}
+
     # ---- FragmentFinder (src/algo/FragmentFinder.cpp) --------------------------------
     def _matches(self, r):
         n = int(r.n_matches)
@@ -401,6 +411,17 @@ class MultiEngine:
             return AnchorResult(r)
         finally:
             self._lib.npge_anchor_multi_result_free(C.byref(r))
+
+    def set_result_layout(self, layout):
+        self._check(self._lib.npge_anchor_multi_set_result_layout(self._m, int(layout)))
+
+    def fetch_compact(self):
+        r = _abi.CompactResult()
+        self._check(self._lib.npge_anchor_multi_fetch_compact(self._m, C.byref(r)))
+        try:
+            return CompactAnchorResult(r)
+        finally:
+            self._lib.npge_anchor_multi_compact_result_free(C.byref(r))
 
     def find(self, seqs, k, similar=True, max_frags=100000, used=None):
         bases, offsets = seqs if isinstance(seqs, tuple) else concat(seqs)

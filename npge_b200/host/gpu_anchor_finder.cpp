@@ -302,58 +302,41 @@ void AnchorFinder::run_impl() const {
     const size_t k = size_t(params.anchor_size);
     const double t_uploaded = wall_ms();
     st.ms[0] = t_uploaded - t_start;
+    // the compact result (4 bytes per fragment over PCIe); every fragment is decoded
+    // while its Fragment object is built
+    npge_anchor_compact_result c;
     if (!many) {
-        // one GPU: the compact result (4 bytes per fragment over PCIe); every fragment is
-        // decoded while its Fragment object is built
         check(npge_anchor_set_result_layout(st.ctx, NPGE_ANCHOR_LAYOUT_COMPACT),
               "npge_anchor_set_result_layout");
         check(npge_anchor_find_device(st.ctx, &params, st.used_hashes.data(),
                                       st.used_hashes.size(), nullptr),
               "npge_anchor_find_device");
         st.ms[3] = wall_ms() - t_uploaded;
-        npge_anchor_compact_result c;
         check(npge_anchor_fetch_compact(st.ctx, &c), "npge_anchor_fetch_compact");
-        const double t_found = wall_ms();
-        st.ms[1] = t_found - t_uploaded;
-        try {
-            std::vector<Block*> built;
-            build_blocks(c.block_offsets, c.n_blocks,
-                         [&](uint64_t f, uint32_t* seq, uint32_t* min_pos, int* ori) {
-                             npge_decode_compact(&c, f, seq, min_pos, ori);
-                         }, seqs, k, st.build_threads(workers()), built);
-            for (size_t b = 0; b < built.size(); b++) bs.insert(built[b]);  // owned by the blockset
-            st.extend_used(c.new_used, c.n_new_used);
-        } catch (...) {
-            npge_anchor_compact_result_free(&c);
-            throw;
-        }
-        npge_anchor_compact_result_free(&c);
-        st.ms[2] = wall_ms() - t_found;
-        return;
+    } else {
+        check(npge_anchor_multi_set_result_layout(st.multi, NPGE_ANCHOR_LAYOUT_COMPACT),
+              "npge_anchor_multi_set_result_layout");
+        check(npge_anchor_multi_find_device(st.multi, &params, st.used_hashes.data(),
+                                            st.used_hashes.size(), nullptr),
+              "npge_anchor_multi_find_device");
+        st.ms[3] = wall_ms() - t_uploaded;
+        check(npge_anchor_multi_fetch_compact(st.multi, &c), "npge_anchor_multi_fetch_compact");
     }
-    npge_anchor_result r;
-    check(npge_anchor_multi_find_device(st.multi, &params, st.used_hashes.data(),
-                                        st.used_hashes.size(), nullptr),
-          "npge_anchor_multi_find_device");
-    st.ms[3] = wall_ms() - t_uploaded;
-    check(npge_anchor_multi_fetch(st.multi, &r), "npge_anchor_multi_fetch");
     const double t_found = wall_ms();
     st.ms[1] = t_found - t_uploaded;
     try {
         std::vector<Block*> built;
-        build_blocks(r.block_offsets, r.n_blocks,
+        build_blocks(c.block_offsets, c.n_blocks,
                      [&](uint64_t f, uint32_t* seq, uint32_t* min_pos, int* ori) {
-                         *seq = r.frag_seq[f];
-                         *min_pos = r.frag_min_pos[f];
-                         *ori = r.frag_ori[f];
+                         npge_decode_compact(&c, f, seq, min_pos, ori);
                      }, seqs, k, st.build_threads(workers()), built);
         for (size_t b = 0; b < built.size(); b++) bs.insert(built[b]);  // owned by the blockset
-        st.extend_used(r.new_used, r.n_new_used);
+        st.extend_used(c.new_used, c.n_new_used);
     } catch (...) {
-        npge_anchor_multi_result_free(&r);
+        if (many) npge_anchor_multi_compact_result_free(&c); else npge_anchor_compact_result_free(&c);
         throw;
     }
-    npge_anchor_multi_result_free(&r);
+    if (many) npge_anchor_multi_compact_result_free(&c); else npge_anchor_compact_result_free(&c);
     st.ms[2] = wall_ms() - t_found;
 }
 

@@ -67,6 +67,17 @@ def main():
             first = oracle.find_ideal(job, k, similar=similar, max_frags=limit)
             used = first.block_hash[::3].copy()
         got_local = f.find(mine, k, similar=similar, max_frags=limit, used=used)
+        if mode == "cuda":
+            # the compact layout of the resident result: the same slice on every rank
+            from npge_b200 import _abi
+            f.stages.set_result_layout(_abi.LAYOUT_COMPACT)
+            f.find_device(k, similar=similar, max_frags=limit, used=used)
+            cl = f.fetch_compact()
+            f.stages.set_result_layout(_abi.LAYOUT_FULL)
+            if (cl.blocks() != got_local.blocks() or
+                    list(cl.block_hash) != list(got_local.block_hash)):
+                fails.append("rank %d similar=%s limit=%d: compact slice differs"
+                             % (rank, similar, limit))
         got = f.gather(got_local)
         if rank != 0:
             continue
@@ -91,7 +102,7 @@ def main():
         fails.append("guard bytes behind a device buffer were overwritten")
     dist.barrier()
     dist.destroy_process_group()
-    if fails:
+    if fails:  # (a rank other than 0 fails on its own checks only)
         print("\n".join(fails), flush=True)
         sys.exit(1)
 

@@ -75,3 +75,35 @@ def test_multi_c1_brucella3_two_ranks():
         assert m.debug_check() == 0
     finally:
         m.close()
+
+
+@pytest.mark.parametrize("ranks", [1, 2, 3])
+def test_multi_compact_layout_equals_oracle(ranks):
+    """npge_anchor_multi_set_result_layout(COMPACT): every rank writes 4-byte
+    (job-wide position, strand) payloads and multi_fetch_compact joins the slices;
+    decoded with the layout table it is the oracle's result, also through the cut,
+    with used hashes, and through the expanding npge_anchor_multi_fetch."""
+    from npge_b200 import _abi
+    names, seqs = synth.generate("tiny")
+    seqs = seqs + [seqs[0][:19], seqs[1][100:700], seqs[2][:0]]
+    k = 20
+    m = MultiEngine(devices(ranks))
+    try:
+        base = oracle.find_ideal(seqs, k, similar=False)
+        used = base.block_hash[::3].copy()
+        m.set_result_layout(_abi.LAYOUT_COMPACT)
+        m.upload(seqs, k)
+        for similar, limit, u in ((False, BIG, None), (True, BIG, None), (True, 1000, None),
+                                  (False, 777, None), (True, BIG, used), (False, 9, None)):
+            want = oracle.find_ideal(seqs, k, similar=similar, max_frags=limit, used=u)
+            st = m.find_device(k, similar=similar, max_frags=limit, used=u)
+            assert st["n_fragments"] == want.n_fragments
+            same(m.fetch_compact(), want)
+            same(m.fetch(), want)  # the host expands the payloads
+        m.set_result_layout(_abi.LAYOUT_FULL)
+        m.find_device(k, similar=False, max_frags=BIG)
+        with pytest.raises(Exception):
+            m.fetch_compact()  # the resident result holds no payloads
+        assert m.debug_check() == 0
+    finally:
+        m.close()
