@@ -719,20 +719,29 @@ class DistAnchorFinder:
                 lap("reduce_found")
                 totals = st.dist_sort(params, 1, tables, used)
                 lap("count")
-        tot_all = comm.gather_array(np.asarray(totals, dtype=np.int64), dev)
-        lap("gather_totals")
-        limits = local_limits(tot_all[:, 0], int(max_frags))
-        s = st.dist_emit(params, limits[self.rank])
-        lap("emit")
+        n_windows = int(np.asarray(hist_all, dtype=np.int64).sum())
+        if int(max_frags) >= n_windows:
+            # max-anchor-fragments cannot bite (every rank sees the same histograms): no
+            # rank needs the others' totals, one rendezvous less in the step
+            s = st.dist_emit(params, int(max_frags))
+            lap("emit")
+            n_frag_job = n_blocks_job = total_selected = None  # job_stats() fills them
+        else:
+            tot_all = comm.gather_array(np.asarray(totals, dtype=np.int64), dev)
+            lap("gather_totals")
+            limits = local_limits(tot_all[:, 0], int(max_frags))
+            s = st.dist_emit(params, limits[self.rank])
+            lap("emit")
+            total_selected = int(tot_all[:, 0].sum())
+            n_frag_job = int(sum(limits))
+            n_blocks_job = None if total_selected > int(max_frags) else int(tot_all[:, 1].sum())
         self.local_stats = s
         out = dict(s)
-        cut = int(tot_all[:, 0].sum()) > int(max_frags)
         out.update(
-            n_fragments=int(sum(limits)),
-            n_blocks=None if cut else int(tot_all[:, 1].sum()),
-            n_windows=int(hist_all.sum()), digest=None,
+            n_fragments=n_frag_job, n_blocks=n_blocks_job,
+            n_windows=n_windows, digest=None,
             n_positions=self.n_job_bases, local_fragments=s["n_fragments"],
-            local_records=s["n_windows"], total_selected=int(tot_all[:, 0].sum()),
+            local_records=s["n_windows"], total_selected=total_selected,
             exchange_ms=dict(self.exchange_ms), exchange=self.exchange,
             chunks=(self.chunks if bulk else 1), host_ms=trace)
         self._hist_all, self._hist = hist_all, hist
