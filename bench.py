@@ -486,6 +486,7 @@ def run_gpu(args, rank, world, local_rank):
     e2e_t = max_over_ranks(time.perf_counter() - t0, world, dist, torch)
     # the host-buffer call's own result against the golden digest
     h = runner.last_host
+    e2e_phases = h.get("host_phases_ms")  # N > 1: rank 0's wall time by phase, last call
     e2e_parity = check_parity(job_name, K, "parity", {
         "n_fragments_global": h["n_fragments"], "n_blocks_global": h["n_blocks"],
         "digest": h["digest"]})["digest_equal"]
@@ -600,6 +601,7 @@ def run_gpu(args, rank, world, local_rank):
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": int(d2h),
                 "steps": e2e_steps,
                 "call": runner.e2e_call, "digest_equal": e2e_parity,
+                "phases_ms_rank0": e2e_phases,
                 "full_layout": e2e_full,
                 "default_mode": {
                     "value": n_total * e2e_steps / e2e_default_t / 1e9,

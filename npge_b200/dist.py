@@ -802,13 +802,22 @@ class DistAnchorFinder:
     def find_compact_counts(self, seqs, k, similar=True, max_frags=100000, used=None):
         """find_counts() with the compact result layout: every rank's slice crosses
         PCIe as 4 bytes per fragment (job-wide position << 1 | strand)."""
+        import time
         self.stages.set_result_layout(_abi.LAYOUT_COMPACT)
         try:
+            t0 = time.perf_counter()
             self.upload(seqs, k)
+            t1 = time.perf_counter()
             stats = self.find_device(k, similar=similar, max_frags=max_frags, used=used)
+            t2 = time.perf_counter()
             stats["result_bytes"] = self.stages.fetch_compact_counts()["result_bytes"]
+            t3 = time.perf_counter()
         finally:
             self.stages.set_result_layout(_abi.LAYOUT_FULL)
+        # this rank's wall time by phase (upload = pieces to their owners + H2D + pack;
+        # find = the step + the job's counts; fetch = this rank's slice over PCIe)
+        stats["host_phases_ms"] = {"upload": 1e3 * (t1 - t0), "find_device": 1e3 * (t2 - t1),
+                                   "fetch": 1e3 * (t3 - t2)}
         return stats
 
     def fetch_compact(self):
