@@ -437,9 +437,10 @@ int npge_fragment_find_device_noalloc(npge_anchor_ctx* ctx, const uint8_t* patte
  * Computed on the device for all blocks of a flat block list at once.
  *
  *  names[s]          name of sequence s (Sequence::name()), NUL-terminated; no
- *                    bytes <= ' ', and no name + "_" may be a prefix of another
- *                    name + "_" (NPGE_ANCHOR_ERR_PARAMS otherwise: the ids
- *                    would not be ordered by name)
+ *                    bytes <= ' ' (NPGE_ANCHOR_ERR_PARAMS otherwise).  Any other
+ *                    name set works; where one name + "_" is a prefix of
+ *                    another ("s1", "s1_2") the ids of those sequences are
+ *                    ordered by their full strings on the device (slower)
  *  block_offsets     [n_blocks + 1] into the fragment arrays, ascending
  *  frag_max_pos      NULL: every fragment is frag_len long (anchors)
  *  hashes            [n_blocks] out (may be NULL)

@@ -2431,13 +2431,19 @@ int block_hashes_device(npge_anchor_ctx* ctx, const char* const* names, uint32_t
     // names: [words u64][seq_rank u32 x n_seqs][pos u32 x ranks][len u32 x ranks]
     const size_t n_words = table.words.size(), n_ranks = table.pos.size();
     static const std::vector<uint16_t> bcd4 = make_bcd4();
-    NPGE_TRY(ensure(ctx->bh_names,
-                    n_words * 8 + (size_t(n_seqs) + 2 * n_ranks) * 4 + bcd4.size() * 2));
+    // + [bcd4 u16 x 10000][slow u8 x ranks]
+    NPGE_TRY(ensure(ctx->bh_names, n_words * 8 + (size_t(n_seqs) + 2 * n_ranks) * 4 +
+                                       bcd4.size() * 2 + n_ranks));
     uint64_t* d_words = ptr<uint64_t>(ctx->bh_names);
     uint32_t* d_rank = reinterpret_cast<uint32_t*>(d_words + n_words);
     uint32_t* d_pos = d_rank + n_seqs;
     uint32_t* d_len = d_pos + n_ranks;
     uint16_t* d_bcd4 = reinterpret_cast<uint16_t*>(d_len + n_ranks);
+    unsigned char* d_slow = nullptr;  // only for name sets that need the string order
+    if (!table.slow.empty()) {
+        d_slow = reinterpret_cast<unsigned char*>(d_bcd4 + bcd4.size());
+        NPGE_CUDA(cudaMemcpyAsync(d_slow, table.slow.data(), n_ranks, cudaMemcpyHostToDevice, st));
+    }
     NPGE_CUDA(cudaMemcpyAsync(d_bcd4, bcd4.data(), bcd4.size() * 2, cudaMemcpyHostToDevice, st));
     NPGE_CUDA(cudaMemcpyAsync(d_words, table.words.data(), n_words * 8, cudaMemcpyHostToDevice,
                               st));
@@ -2493,6 +2499,7 @@ int block_hashes_device(npge_anchor_ctx* ctx, const char* const* names, uint32_t
     a.name_words = d_words;
     a.name_pos = d_pos;
     a.name_len = d_len;
+    a.name_slow = d_slow;
     a.bcd4 = d_bcd4;
     a.scratch = ctx->bh_scratch.ptr;
     a.hashes = d_hashes;

@@ -126,6 +126,62 @@ NPGE_HD uint64_t low_bytes(uint64_t v, uint32_t len) {  // len in 1..8
     return len >= 8 ? v : v & ((uint64_t(1) << (8 * len)) - 1);
 }
 
+// "_" + begin + "_" + last of a key as ASCII bytes, at most 23; returns the count.
+NPGE_HD uint32_t id_tail(const IdKey& k, unsigned char* out) {
+    const uint64_t lo = k.lo;
+    const uint32_t nb = uint32_t(lo) & 0xf, nl = uint32_t(lo >> 4) & 0xf;
+    uint32_t n = 0;
+    out[n++] = '_';
+    const uint64_t b = ((k.hi & 0xffffffffull) << 12) | (lo >> 52);  // 44 bits, digits on top
+    for (uint32_t i = 0; i < nb; i++) out[n++] = (unsigned char)('0' + ((b >> (40 - 4 * i)) & 0xf));
+    out[n++] = '_';
+    if (nl == 0) {
+        out[n++] = '-';
+        out[n++] = '1';
+    } else {
+        const uint64_t l = ((lo >> 8) & 0xfffffffffffull) - last_digit_bias(nl);
+        for (uint32_t i = 0; i < nl; i++) out[n++] = (unsigned char)('0' + ((l >> (40 - 4 * i)) & 0xf));
+    }
+    return n;
+}
+
+// How the ids of a block are ordered.  Two ids with different names are ordered by
+// the rank of name + "_" (the first difference lies inside both prefixes) unless one
+// name + "_" is a prefix of the other ("s1" next to "s1_2"): then the digits of one id
+// meet the letters of the other, and the order is the byte-wise order of the two id
+// strings, regenerated here (slow[rank] marks the names that have such a partner;
+// nullptr: none has).
+struct KeyOrder {
+    const uint64_t* name_words;
+    const uint32_t* name_pos;
+    const uint32_t* name_len;
+    const unsigned char* slow;
+
+    NPGE_HD unsigned char name_byte(uint32_t rank, uint32_t i) const {
+        return (unsigned char)(name_words[name_pos[rank] + i / 8] >> (8 * (i % 8)));
+    }
+    NPGE_HD bool string_less(const IdKey& a, const IdKey& b) const {
+        const uint32_t ra = uint32_t(a.hi >> 32), rb = uint32_t(b.hi >> 32);
+        const uint32_t la = name_len[ra], lb = name_len[rb];
+        unsigned char ta[24], tb[24];
+        const uint32_t na = la + id_tail(a, ta), nb = lb + id_tail(b, tb);
+        const uint32_t n = na < nb ? na : nb;
+        for (uint32_t i = 0; i < n; i++) {
+            const unsigned char ca = i < la ? name_byte(ra, i) : ta[i - la];
+            const unsigned char cb = i < lb ? name_byte(rb, i) : tb[i - lb];
+            if (ca != cb) return ca < cb;
+        }
+        return na < nb;
+    }
+    NPGE_HD bool less(const IdKey& a, const IdKey& b) const {
+        if (slow) {
+            const uint32_t ra = uint32_t(a.hi >> 32), rb = uint32_t(b.hi >> 32);
+            if (ra != rb && slow[ra] && slow[rb]) return string_less(a, b);
+        }
+        return key_less(a, b);
+    }
+};
+
 // Keys of one thread interleaved with those of its neighbours (shared memory of
 // the kernel: element i of thread t at base[i * stride + t]); stride 1 = an array.
 struct KeySlots {
@@ -136,12 +192,12 @@ struct KeySlots {
 
 // In-place ascending sort; ids of one block are distinct, so stability is moot.
 template <typename Keys>
-NPGE_HD void sort_keys(Keys a, uint64_t n) {
+NPGE_HD void sort_keys(Keys a, uint64_t n, const KeyOrder& ord) {
     if (n <= 24) {
         for (uint64_t i = 1; i < n; i++) {
             const IdKey x = a[i];
             uint64_t j = i;
-            while (j > 0 && key_less(x, a[j - 1])) {
+            while (j > 0 && ord.less(x, a[j - 1])) {
                 a[j] = a[j - 1];
                 j--;
             }
@@ -156,8 +212,8 @@ NPGE_HD void sort_keys(Keys a, uint64_t n) {
         while (true) {
             uint64_t c = 2 * root + 1;
             if (c >= n) break;
-            if (c + 1 < n && key_less(a[c], a[c + 1])) c++;
-            if (!key_less(x, a[c])) break;
+            if (c + 1 < n && ord.less(a[c], a[c + 1])) c++;
+            if (!ord.less(x, a[c])) break;
             a[root] = a[c];
             root = c;
         }
@@ -170,8 +226,8 @@ NPGE_HD void sort_keys(Keys a, uint64_t n) {
         while (true) {
             uint64_t c = 2 * root + 1;
             if (c >= end) break;
-            if (c + 1 < end && key_less(a[c], a[c + 1])) c++;
-            if (!key_less(x, a[c])) break;
+            if (c + 1 < end && ord.less(a[c], a[c + 1])) c++;
+            if (!ord.less(x, a[c])) break;
             a[root] = a[c];
             root = c;
         }
@@ -182,10 +238,10 @@ NPGE_HD void sort_keys(Keys a, uint64_t n) {
 // ids_dir < ids_inv of two sorted lists of the same length (std::vector<
 // std::string>::operator<): decided by the first position that differs.
 template <typename Keys>
-NPGE_HD bool list_less(Keys a, Keys b, uint64_t n) {
+NPGE_HD bool list_less(Keys a, Keys b, uint64_t n, const KeyOrder& ord) {
     for (uint64_t i = 0; i < n; i++) {
-        if (key_less(a[i], b[i])) return true;
-        if (key_less(b[i], a[i])) return false;
+        if (ord.less(a[i], b[i])) return true;
+        if (ord.less(b[i], a[i])) return false;
     }
     return false;
 }
@@ -289,6 +345,11 @@ struct FlatBlocks {
     const uint32_t* name_pos;
     const uint32_t* name_len;
     const uint16_t* bcd4;  // [kBcdEntries]
+    const unsigned char* name_slow;  // [ranks] or nullptr (KeyOrder::slow)
+    NPGE_HD KeyOrder order() const {
+        const KeyOrder o = {name_words, name_pos, name_len, name_slow};
+        return o;
+    }
     NPGE_HD void keys(uint64_t f, IdKey& dir, IdKey& inv) const {
         const uint32_t lo = min_pos[f];
         const uint32_t hi = max_pos ? max_pos[f] : lo + frag_len - 1;
@@ -303,10 +364,11 @@ NPGE_HD uint64_t block_hash_two_lists(const FlatBlocks& fb, uint64_t f0, uint64_
     const uint64_t n = f1 - f0;
     IdKey* dir = scratch;
     IdKey* inv = scratch + n;
+    const KeyOrder ord = fb.order();
     for (uint64_t i = 0; i < n; i++) fb.keys(f0 + i, dir[i], inv[i]);
-    sort_keys(dir, n);
-    sort_keys(inv, n);
-    const IdKey* ids = list_less(dir, inv, n) ? dir : inv;
+    sort_keys(dir, n, ord);
+    sort_keys(inv, n, ord);
+    const IdKey* ids = list_less(dir, inv, n, ord) ? dir : inv;
     return fold_sorted(ids, n, fb.name_words, fb.name_pos, fb.name_len);
 }
 
@@ -318,22 +380,23 @@ template <typename Keys>
 NPGE_HD uint64_t block_hash_one_list(const FlatBlocks& fb, uint64_t f0, uint64_t f1,
                                      Keys slots, bool* tie) {
     const uint64_t n = f1 - f0;
-    IdKey min_dir = {~uint64_t(0), ~uint64_t(0)}, min_inv = min_dir;
+    const KeyOrder ord = fb.order();
+    IdKey min_dir = {0, 0}, min_inv = min_dir;
     for (uint64_t i = 0; i < n; i++) {
         IdKey d, v;
         fb.keys(f0 + i, d, v);
-        if (key_less(d, min_dir)) min_dir = d;
-        if (key_less(v, min_inv)) min_inv = v;
+        if (i == 0 || ord.less(d, min_dir)) min_dir = d;
+        if (i == 0 || ord.less(v, min_inv)) min_inv = v;
     }
-    const bool use_dir = key_less(min_dir, min_inv);
-    *tie = !use_dir && !key_less(min_inv, min_dir);
+    const bool use_dir = ord.less(min_dir, min_inv);
+    *tie = !use_dir && !ord.less(min_inv, min_dir);
     if (*tie) return 0;
     for (uint64_t i = 0; i < n; i++) {
         IdKey d, v;
         fb.keys(f0 + i, d, v);
         slots[i] = use_dir ? d : v;
     }
-    sort_keys(slots, n);
+    sort_keys(slots, n, ord);
     return fold_sorted(slots, n, fb.name_words, fb.name_pos, fb.name_len);
 }
 

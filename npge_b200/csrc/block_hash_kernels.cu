@@ -41,7 +41,8 @@ __global__ void __launch_bounds__(kThreads) block_hash_kernel(BlockHashArgs a) {
                 extern __shared__ __align__(16) unsigned char raw[];
                 const KeySlots slots = {reinterpret_cast<IdKey*>(raw) + threadIdx.x, kThreads};
                 const FlatBlocks fb = {a.frag_seq, a.min_pos, a.max_pos, a.frag_len, a.frag_ori,
-                                       a.seq_rank, a.name_words, a.name_pos, a.name_len, a.bcd4};
+                                       a.seq_rank, a.name_words, a.name_pos, a.name_len, a.bcd4,
+                                       a.name_slow};
                 h = block_hash_flat(fb, f0, f1, slots, kFastFrags,
                                     reinterpret_cast<IdKey*>(a.scratch) + 2 * (f0 - a.f_base));
                 // blockset_hash skips blocks of <= 1 fragment (HashGroup::

@@ -3,10 +3,11 @@
 //
 // An id is name + "_" + begin + "_" + last (Fragment::id,
 // src/model/Fragment.cpp:173-183).  Two ids with different names are ordered by
-// name + "_" alone provided no name + "_" is a prefix of another one (then the
+// name + "_" alone provided neither name + "_" is a prefix of the other (then the
 // first difference lies inside both prefixes).  That holds for every name
-// without '_' and for NPGE's "GENOME&chr&c" names; a name set that breaks it
-// (say "s1" next to "s1_2") is refused rather than hashed wrongly.
+// without '_' and for NPGE's "GENOME&chr&c" names; the names of a set that breaks it
+// (say "s1" next to "s1_2") are marked `slow`, and ids of two slow names are ordered
+// by their regenerated strings (KeyOrder::string_less in block_hash_core.h).
 #pragma once
 
 #include <stdint.h>
@@ -23,6 +24,8 @@ struct NameTable {
                                      // every name starting a new word (zero padded)
     std::vector<uint32_t> pos;       // [ranks] first word of the name
     std::vector<uint32_t> len;       // [ranks] its length in bytes
+    std::vector<unsigned char> slow; // [ranks] name + "_" is a prefix of another one, or
+                                     // has one as a prefix; empty: no such name
 };
 
 // bcd4[v] = the decimal digits of v < 10000, one per nibble (block_hash_core.h: bcd10)
@@ -53,13 +56,20 @@ inline std::string build_name_table(const char* const* names, uint32_t n_seqs,
     std::vector<std::string> sorted(key);
     std::sort(sorted.begin(), sorted.end());
     sorted.erase(std::unique(sorted.begin(), sorted.end()), sorted.end());
-    for (size_t i = 0; i + 1 < sorted.size(); i++) {
-        const std::string &a = sorted[i], &b = sorted[i + 1];
-        if (b.size() > a.size() && b.compare(0, a.size(), a) == 0) {
-            return "sequence name '" + a.substr(0, a.size() - 1) + "' followed by '_' is a "
-                   "prefix of '" + b.substr(0, b.size() - 1) + "': ids are not ordered by name";
+    // the keys that have a given key as a prefix follow it directly in sorted order
+    std::vector<unsigned char> slow(sorted.size(), 0);
+    bool any_slow = false;
+    for (size_t i = 0; i < sorted.size(); i++) {
+        const std::string& a = sorted[i];
+        for (size_t j = i + 1; j < sorted.size(); j++) {
+            const std::string& b = sorted[j];
+            if (b.size() <= a.size() || b.compare(0, a.size(), a) != 0) break;
+            slow[i] = slow[j] = 1;
+            any_slow = true;
         }
     }
+    t.slow.clear();
+    if (any_slow) t.slow = slow;
     t.seq_rank.resize(n_seqs);
     for (uint32_t i = 0; i < n_seqs; i++) {
         t.seq_rank[i] = uint32_t(std::lower_bound(sorted.begin(), sorted.end(), key[i]) -

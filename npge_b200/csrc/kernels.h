@@ -203,6 +203,7 @@ struct BlockHashArgs {
     const uint64_t* name_words;  // names in rank order, 8 bytes per word
     const uint32_t* name_pos;    // [ranks] first word of the name
     const uint32_t* name_len;    // [ranks] bytes
+    const unsigned char* name_slow;  // [ranks] or nullptr: names ordered by id strings
     const uint16_t* bcd4;        // [10000] decimal digits of v, one per nibble
     void* scratch;               // 2 IdKey per fragment of the launch
     uint64_t* hashes;            // [n_blocks]

@@ -28,7 +28,7 @@ extern "C" int bh_host_block_hashes(const char* const* names, uint32_t n_seqs,
     static const std::vector<uint16_t> bcd4 = npge_b200::make_bcd4();
     npge_b200::FlatBlocks fb = {frag_seq, min_pos, max_pos, frag_len, frag_ori,
                                 t.seq_rank.data(), t.words.data(), t.pos.data(), t.len.data(),
-                                bcd4.data()};
+                                bcd4.data(), t.slow.empty() ? nullptr : t.slow.data()};
     // the kernel's layout: the slots of a thread interleaved with its neighbours'
     const uint32_t stride = 7, fast_cap = fast_cap_override ? fast_cap_override : 20;
     std::vector<npge_b200::IdKey> slots(size_t(fast_cap) * stride + 1), scratch;
