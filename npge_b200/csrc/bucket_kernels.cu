@@ -1,6 +1,6 @@
 // bucket_kernels.cu -- last stage of the anchor sort, fused with the grouping:
-// every CTA takes one "unit" (the (A, B) bins that start inside one window of
-// kWindow records, at most kBucketCap records unless a bin is oversized), sorts
+// every CTA takes one "unit" (consecutive (A, B) bins of one A bucket packed greedily
+// up to kBucketCap records, unit_build_kernel; an oversized bin is a unit of its own), sorts
 // it by the remaining key bits with an LSD radix sort in shared memory (byte
 // digits, stable), finds the runs of equal canonical k-mers and writes the
 // anchor fragments and blocks.  Three launches, no CTA ever waits on another:
