@@ -1542,7 +1542,7 @@ int dist_count_a(npge_anchor_ctx* ctx, const npge_anchor_params* p, bool scatter
     if (!ctx || !hist_out || !n_bins) return fail(NPGE_ANCHOR_ERR_PARAMS, "NULL argument");
     NPGE_TRY(check_params(p));
     if (!ctx->uploaded || !ctx->dist) {
-        return fail(NPGE_ANCHOR_ERR_STATE, "npge_anchor_dist_upload has not been called");
+        return fail(NPGE_ANCHOR_ERR_STATE, "npge_anchor_dist_upload_range has not been called");
     }
     if (p->anchor_size != ctx->upload_k) {
         return fail(NPGE_ANCHOR_ERR_STATE, "anchor-size differs from the uploaded one");
@@ -2061,7 +2061,7 @@ int npge_anchor_dist_sort_impl(npge_anchor_ctx* ctx, const npge_anchor_params* p
     if (!ctx || !totals) return fail(NPGE_ANCHOR_ERR_PARAMS, "NULL argument");
     NPGE_TRY(check_params(p));
     if (!ctx->dist || !ctx->uploaded) {
-        return fail(NPGE_ANCHOR_ERR_STATE, "npge_anchor_dist_upload has not been called");
+        return fail(NPGE_ANCHOR_ERR_STATE, "npge_anchor_dist_upload_range has not been called");
     }
     if (n_recv != ctx->n_recv) {
         return fail(NPGE_ANCHOR_ERR_STATE, "n_recv differs from npge_anchor_dist_buffers");
@@ -2172,7 +2172,7 @@ extern "C" int npge_anchor_dist_emit(npge_anchor_ctx* ctx, const npge_anchor_par
     if (!ctx) return fail(NPGE_ANCHOR_ERR_PARAMS, "ctx is NULL");
     NPGE_TRY(check_params(p));
     if (!ctx->dist || !ctx->uploaded) {
-        return fail(NPGE_ANCHOR_ERR_STATE, "npge_anchor_dist_upload has not been called");
+        return fail(NPGE_ANCHOR_ERR_STATE, "npge_anchor_dist_upload_range has not been called");
     }
     NPGE_CUDA(cudaSetDevice(ctx->device));
     const MsdPlan plan = ctx->plan;
