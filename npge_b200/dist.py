@@ -412,6 +412,19 @@ class _Comm:
         self.dist.all_gather_into_tensor(out, t.reshape(-1), group=self.group)
         return out.cpu().numpy().reshape((self.world,) + tuple(t.shape))
 
+    def gather_varlen(self, arr, device=None):
+        """all-gather of int64 arrays of different lengths -> list of `world` arrays
+        (two fixed-length gathers: no pickling, and through /dev/shm when it is there)"""
+        a = np.asarray(arr, dtype=np.int64).reshape(-1)
+        counts = self.gather_array(np.asarray([len(a)], dtype=np.int64), device)[:, 0]
+        m = int(counts.max())
+        if m == 0:
+            return [np.zeros(0, np.int64) for _ in range(self.world)]
+        pad = np.zeros(m, dtype=np.int64)
+        pad[:len(a)] = a
+        rows = self.gather_array(pad, device)
+        return [np.asarray(rows[r, :int(counts[r])], dtype=np.int64) for r in range(self.world)]
+
     def _done(self, t):
         # the library's kernels run on its own stream: the collective must have
         # finished (not just been enqueued) before the next stage is launched
@@ -542,7 +555,8 @@ class DistAnchorFinder:
         n_have)."""
         torch = self.comm.torch
         off = np.asarray(offsets, dtype=np.int64)
-        sizes_by_rank = self.comm.gather_objects([int(x) for x in np.diff(off)])
+        dev = torch.device("cuda", self.device) if self.comm.nccl else None
+        sizes_by_rank = self.comm.gather_varlen(np.diff(off), dev)
         counts = [len(x) for x in sizes_by_rank]
         base = np.concatenate([[0], np.cumsum(counts)]).astype(np.int64)
         sizes = np.asarray([x for r in sizes_by_rank for x in r], dtype=np.int64)
