@@ -18,6 +18,8 @@
 //
 // Replaces std::sort of FoundFragments (src/algo/AnchorFinder.cpp:234-238,358;
 // src/util/SortedVector.hpp:47-49) together with bucket_kernels.cu.
+#include <algorithm>
+
 #include "kernels.h"
 #include "rank.cuh"
 
@@ -34,15 +36,25 @@ MsdPlan make_msd_plan(int k, uint64_t n_positions, int force_f, int force_wa) {
     MsdPlan p;
     p.k = k;
     p.total = 2 * k;
-    int f = 2;  // fine bits so that a fine bin holds ~1024 records
-    while (f < 20 && (uint64_t(1024) << f) < n_positions) f++;
+    // Fine bits.  The bucket sort costs a fixed time per unit of up to 4096 records, and
+    // units are whole (A, B) bins packed greedily: bins of ~256 records fill them to
+    // 97 %, bins of ~1024 to 84 % (brucella17: sort 0.98 against 1.21 ms, emit 0.45
+    // against 0.50).  Finer bins need wider rows in the two partition passes, which
+    // cost more than they save beyond 512 bins (9 + 9 bits): so ~256 records per bin up
+    // to 18 bits, and above that what keeps a bin below 512 records (the canonical
+    // minimum skews the key density up to 2x: bins of 1000-2000 records leave units a
+    // third empty, and on several GPUs the rank that owns them sets the step).
+    int f_fine = 2, f_mid = 2;
+    while (f_fine < 20 && (uint64_t(256) << f_fine) < n_positions) f_fine++;
+    while (f_mid < 20 && (uint64_t(512) << f_mid) < n_positions) f_mid++;
+    int f = std::min(f_fine, std::max(f_mid, 18));
     if (force_f >= 2 && force_f <= 20) f = force_f;  // tests: the wider digit plans
     if (f > p.total) f = p.total;
     const int need = p.total - 32;  // bits a narrow (8 B) record cannot hold
-    // the smaller half goes to pass A: fewer buckets = longer scatter runs (and
-    // larger pieces for the multi-GPU exchange), and its kernel gains most from
-    // the occupancy of narrow rows
-    int wa = f / 2;
+    // the halves of f go to pass A and pass B; of an odd f the larger half goes to pass A
+    // while its rows stay at 512 bins (measured: 9 + 8 beats 8 + 9, 9 + 10 beats 10 + 9:
+    // 1024-bin rows cost pass A 0.15 ms per 56 M records, pass B 0.10)
+    int wa = (f + 1) / 2 <= 9 ? (f + 1) / 2 : f / 2;
     if (need > 0 && need <= kMaxDigitBits && wa < need) wa = need;
     if (wa > kMaxDigitBits) wa = kMaxDigitBits;
     if (force_wa >= 1 && force_wa <= kMaxDigitBits &&
