@@ -148,6 +148,10 @@ void npge_anchor_destroy(npge_anchor_ctx* ctx);
  * log2 of the (A, B) bins, first_split = bits of pass A; 0 = automatic), so that
  * the wide-row kernels are exercised on small inputs.  Results never depend on it. */
 int npge_anchor_debug_plan(npge_anchor_ctx* ctx, int32_t fine_bits, int32_t first_split);
+/* Test hook, no device needed: the plan a job of n_windows records gets (bits of the two
+ * partition passes, byte passes of the shared-memory sort). */
+int npge_anchor_debug_plan_of(int32_t anchor_size, uint64_t n_windows, int32_t* bits_a,
+                              int32_t* bits_b, int32_t* sort_passes);
 
 /* Test hook: every device buffer of the context ends in 256 guard bytes; this reads
  * them back.  *n_damaged = buffers whose guard was overwritten (a kernel stored past the

@@ -23,7 +23,7 @@ EXPORTS = [
     "npge_fragment_find", "npge_fragment_find_device", "npge_fragment_result_free",
     "npge_anchor_upload_raw", "npge_anchor_dist_scatter_local",
     "npge_block_hashes", "npge_anchor_block_hashes", "npge_block_hashes_last_ms",
-    "npge_anchor_debug_plan", "npge_anchor_debug_check", "npge_fragment_find_device_noalloc",
+    "npge_anchor_debug_plan", "npge_anchor_debug_plan_of", "npge_anchor_debug_check", "npge_fragment_find_device_noalloc",
     "npge_anchor_set_result_layout", "npge_anchor_fetch_compact", "npge_anchor_find_compact",
     "npge_anchor_compact_result_free",
     "npge_anchor_dist_peer_attach", "npge_anchor_dist_found_or", "npge_anchor_dist_found_swap",
@@ -147,6 +147,8 @@ def load():
     L.npge_anchor_compact_result_free.argtypes = [C.POINTER(CompactResult)]
     L.npge_anchor_debug_check.restype = C.c_int
     L.npge_anchor_debug_check.argtypes = [ctx, C.POINTER(C.c_uint32)]
+    L.npge_anchor_debug_plan_of.restype = C.c_int
+    L.npge_anchor_debug_plan_of.argtypes = [C.c_int32, C.c_uint64] + [C.POINTER(C.c_int32)] * 3
     L.npge_anchor_get_stats.restype = C.c_int
     L.npge_anchor_get_stats.argtypes = [ctx, C.POINTER(Stats)]
     L.npge_anchor_dist_upload_range.restype = C.c_int

@@ -231,6 +231,19 @@ extern "C" int npge_anchor_debug_plan(npge_anchor_ctx* ctx, int32_t fine_bits,
     return NPGE_ANCHOR_OK;
 }
 
+// Test hook without a device: the digit plan of a job of n_windows records.
+extern "C" int npge_anchor_debug_plan_of(int32_t anchor_size, uint64_t n_windows,
+                                         int32_t* bits_a, int32_t* bits_b,
+                                         int32_t* sort_passes) {
+    npge_anchor_params probe = {anchor_size, 0, 0};
+    NPGE_TRY(check_params(&probe));
+    const MsdPlan plan = make_msd_plan(anchor_size, n_windows, 0, 0);
+    if (bits_a) *bits_a = plan.wa;
+    if (bits_b) *bits_b = plan.wb;
+    if (sort_passes) *sort_passes = plan.smem_passes;
+    return NPGE_ANCHOR_OK;
+}
+
 extern "C" int npge_anchor_create(npge_anchor_ctx** out, int device) {
     if (!out) return fail(NPGE_ANCHOR_ERR_PARAMS, "ctx is NULL");
     *out = nullptr;
